@@ -1,0 +1,157 @@
+/*
+ * ngs_dealer.h — C ABI of the B200-native dealer (filter / prioritize / bind evaluation).
+ *
+ * This is the drop-in boundary for the one data-parallel hot path of nano-gpu-scheduler:
+ * the numeric part of pkg/dealer (Dealer interface, /root/reference/pkg/dealer/dealer.go:23-43).
+ * The Go host keeps node names, pod maps, apiserver calls and error strings; everything that
+ * evaluates or mutates per-GPU capacity goes through the calls below.  Nodes are dense
+ * uint32 indices (the shim owns the name<->index map).  All outputs are caller-allocated;
+ * the library never retains a caller pointer after a call returns (cgo pointer rules).
+ *
+ * Every entry point returns an NGS_* status (0 = ok).  One call at a time per handle (the
+ * reference serialises every Dealer method behind one mutex, dealer.go:81,90,139,...); calls
+ * may come from any OS thread.  There is no CPU fallback: without a CUDA device every call
+ * that touches the snapshot fails with NGS_ERR_CUDA.
+ *
+ * Citations are relative to /root/reference/pkg/dealer/ unless stated.
+ */
+#ifndef NGS_DEALER_H
+#define NGS_DEALER_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NGS_ABI_VERSION 1u
+
+#define NGS_MAX_GPUS 8         /* GPUs per node handled by the kernels (row = 8 x int32 = 2 x int4) */
+#define NGS_MAX_CONTAINERS 12  /* containers per pod (Go sort.Sort's <=12-element regime) */
+#define NGS_MAX_PERIODS 4      /* usable PolicySpec.SyncPeriod entries */
+#define NGS_MAX_FREE 65535     /* upper bound of a cell's free percent kept in the snapshot */
+#define NGS_MAX_BATCH 65536    /* pods per ngs_schedule_batch call */
+
+/* status codes */
+enum {
+    NGS_OK = 0,
+    NGS_ERR_INVALID = 1,      /* bad argument (null pointer, count out of range, negative percent) */
+    NGS_ERR_CUDA = 2,         /* CUDA runtime error; ngs_last_error() has the text */
+    NGS_ERR_UNKNOWN_NODE = 3, /* node index out of range or never upserted */
+    NGS_ERR_INFEASIBLE = 4,   /* bind: "assume ... failed" (node.go:74-76) */
+    NGS_ERR_APPLY = 5,        /* apply: "can't apply plan" (allocate.go:113) / index >= G (allocate.go:126) */
+    NGS_ERR_RANGE = 6,        /* a cell would leave [0, NGS_MAX_FREE] */
+    NGS_ERR_UNSUPPORTED = 7   /* gpu_count > NGS_MAX_GPUS, too many containers or periods */
+};
+
+/* policies: Binpack (rater.go:52), Spread (rater.go:55), random = SampleRater plan search
+ * (rater.go:21-50) on a scratch copy + seeded uniform pick over the feasible set */
+enum { NGS_POLICY_BINPACK = 0, NGS_POLICY_SPREAD = 1, NGS_POLICY_RANDOM = 2 };
+
+/* per-node reason codes of ngs_assume (the shim renders the FailedNodes strings) */
+enum {
+    NGS_REASON_OK = 0,
+    NGS_REASON_UNKNOWN_NODE = 1, /* "nano gpu scheduler get node failed" (dealer.go:102) */
+    NGS_REASON_INFEASIBLE = 2    /* "can't allocate ... indexes=" (rater.go:99,152) */
+};
+
+/* load metric tables: DealerImpl.CoreUsage / MemoryUsage (dealer.go:84-85) */
+enum { NGS_METRIC_CORE = 0, NGS_METRIC_MEMORY = 1 };
+
+#define NGS_NOT_NEED_GPU (-1) /* allocate.go:15 */
+#define NGS_SCORE_MIN 0       /* rater.go:12 */
+
+/* isLoadSchedule=true context: PolicySpec.SyncPeriod (type.go:16-27) after the host resolved
+ * getActiveDuration (stats.go:57-66) for each entry, plus the evaluation's time.Now()
+ * (stats.go:48).  Passing NULL where a ngs_load_ctx* is expected means isLoadSchedule=false. */
+typedef struct {
+    int32_t n_periods;                   /* entries whose active duration is non-zero, in order */
+    int32_t metric[NGS_MAX_PERIODS];     /* NGS_METRIC_CORE iff name == "gpu_core_usage_avg" (nodeusage.go:84) */
+    int64_t window_ns[NGS_MAX_PERIODS];  /* period + ExtenderAtivePeriod (type.go:6) */
+    int64_t now_ns;                      /* unix nanoseconds */
+} ngs_load_ctx;
+
+typedef struct {
+    uint64_t node_evals;    /* (pod, node) evaluations done so far */
+    uint64_t kernel_launches;
+    uint64_t pods_scheduled;
+    uint64_t h2d_bytes;
+    uint64_t d2h_bytes;
+} ngs_stats_t;
+
+typedef struct ngs_dealer ngs_dealer;
+
+uint32_t ngs_abi_version(void);
+const char *ngs_strerror(int status);
+const char *ngs_last_error(const ngs_dealer *h);
+
+/* replaces NewDealer's cache construction (dealer.go:45-75): an empty snapshot of max_nodes rows
+ * resident on CUDA device `device`.  stream: a cudaStream_t the handle should use, or NULL to
+ * create its own.  first_node: global index of row 0 (node-range sharding). */
+int ngs_create(ngs_dealer **out, int device, uint32_t max_nodes, uint32_t first_node, void *stream);
+int ngs_destroy(ngs_dealer *h);
+void *ngs_stream(ngs_dealer *h); /* the cudaStream_t every kernel of this handle is launched on */
+int ngs_sync(ngs_dealer *h);
+int ngs_stats(ngs_dealer *h, ngs_stats_t *out);
+
+/* ---- snapshot ownership ---- */
+/* NewNodeInfo (node.go:25-42): gpu_count cells of (100,100,0); gpu_count from
+ * capacity["nano-gpu/gpu-percent"]/100 (pkg/utils/node.go:8-14). */
+int ngs_node_upsert(ngs_dealer *h, uint32_t idx, int gpu_count);
+/* bulk rebuild on start (dealer.go:58-72,279-299 replayed host-side, then one H2D copy).
+ * free is [n][NGS_MAX_GPUS] (NULL = all 100), remain_load [n][NGS_MAX_GPUS] (NULL = 0). */
+int ngs_snapshot_load(ngs_dealer *h, uint32_t first, uint32_t n, const uint8_t *gpu_count, const int32_t *free,
+                      const int8_t *remain_load);
+/* Status() / PrintStatus (dealer.go:303-309,321-323): read rows back. Any output may be NULL. */
+int ngs_snapshot_read(ngs_dealer *h, uint32_t first, uint32_t n, uint8_t *gpu_count, int32_t *free, int8_t *remain_load);
+/* GPUs.Allocate (sign=+1, allocate.go:102-118; all-or-nothing) / GPUs.Release (sign=-1,
+ * allocate.go:120-131) via NodeInfo.Allocate/Release (node.go:86-94).  Drops the node's cached plan. */
+int ngs_node_apply(ngs_dealer *h, uint32_t idx, const int32_t *gpu_idx, const int32_t *percent, int n_containers, int sign);
+
+/* ---- load-usage tables ---- */
+/* AddCoreUsage / AddMemoryUsage (nodeusage.go:58-68): fresh empty per-card map for the node */
+int ngs_load_add_node(ngs_dealer *h, uint32_t idx, int metric);
+/* UpdateCoreUsage / UpdateMemoryUsage (nodeusage.go:70-80) after string parsing: value_ok =
+ * strconv.ParseFloat succeeded (nodeusage.go:103), ts_ok = the time string parsed (stats.go:32-44). */
+int ngs_load_update(ngs_dealer *h, uint32_t idx, int metric, int card, double value, int value_ok, int64_t ts_sec, int ts_ok);
+/* bulk form of the above for [n][NGS_MAX_GPUS] cells (NULL flags = all ok) */
+int ngs_load_update_bulk(ngs_dealer *h, int metric, uint32_t first, uint32_t n, const double *value,
+                         const uint8_t *value_ok, const int64_t *ts_sec, const uint8_t *ts_ok);
+/* host-side parsing helpers for the two strings the metric sync hands over
+ * (pkg/controller/node.go:111-135, pkg/prometheus/prometheus.go:57-62) */
+int ngs_parse_usage(const char *s, double *value_out);      /* strconv.ParseFloat(s, 64); 1 = ok */
+int ngs_parse_update_time(const char *s, int64_t *ts_out);  /* "2006-01-02T15:04:05Z" in Asia/Shanghai; 1 = ok */
+
+/* ---- verbs ---- */
+/* DealerImpl.Assume (dealer.go:89-136): per candidate NodeInfo.Assume -> GPUs.Choose = Rate then
+ * Choose (node.go:44-57, allocate.go:92-100).  idx == NULL means rows 0..n-1.  Outputs (each may
+ * be NULL): feasible[n], reason[n], score[n] (Plan.Score; NGS_SCORE_MIN when not feasible,
+ * node.go:59-68), plan[n][n_containers] (GPUIndexes when feasible, else the partial `indexes` of
+ * rater.go:99 in emission order padded with INT32_MIN), n_emitted[n]. */
+int ngs_assume(ngs_dealer *h, const uint32_t *idx, uint32_t n, const int32_t *percent, int n_containers, int policy,
+               const ngs_load_ctx *load, uint8_t *feasible, int8_t *reason, int32_t *score, int32_t *plan,
+               int32_t *n_emitted);
+/* DealerImpl.Score (dealer.go:138-153): cached Plan.Score of the last ngs_assume with the same
+ * demand, else a fresh evaluation; unknown / infeasible -> NGS_SCORE_MIN. */
+int ngs_score(ngs_dealer *h, const uint32_t *idx, uint32_t n, const int32_t *percent, int n_containers, int policy,
+              const ngs_load_ctx *load, int32_t *score);
+/* NodeInfo.Bind (node.go:70-84): cached or fresh plan -> GPUs.Allocate -> drop the node's cache. */
+int ngs_bind(ngs_dealer *h, uint32_t idx, const int32_t *percent, int n_containers, int policy, const ngs_load_ctx *load,
+             int32_t *gpu_idx_out, int32_t *score_out);
+/* One launch for P pods in order: filter + prioritize over every row, arg-max (highest score,
+ * ties -> lowest node index; NGS_POLICY_RANDOM: splitmix64(seed+seq0+p) mod |feasible|), bind.
+ * Equivalent to P x (Assume, Score, pick, Bind) on the reference dealer.  percent is
+ * [P][max_c]; node_out[p] = global node index or -1; gpu_idx_out [P][max_c] padded with INT32_MIN. */
+int ngs_schedule_batch(ngs_dealer *h, uint32_t n_pods, const int32_t *percent, const int32_t *n_containers, int max_c,
+                       const int32_t *policy, const ngs_load_ctx *load, uint64_t seed, uint64_t seq0, int32_t *node_out,
+                       int32_t *score_out, int32_t *gpu_idx_out);
+/* same, with every array already resident in device memory and no synchronisation:
+ * results are valid after ngs_sync() or once work queued later on ngs_stream() runs. */
+int ngs_schedule_batch_dev(ngs_dealer *h, uint32_t n_pods, const int32_t *d_percent, const int32_t *d_n_containers,
+                           int max_c, const int32_t *d_policy, const ngs_load_ctx *load, uint64_t seed, uint64_t seq0,
+                           int32_t *d_node_out, int32_t *d_score_out, int32_t *d_gpu_idx_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,1233 @@
+// ngs_dealer.cu — CUDA kernels (sm_100a) and the C ABI of the B200-native dealer.
+//
+// Snapshot layout in HBM (struct-of-arrays, one row per node, rows padded to 8 GPUs):
+//   free    int32 [N][8]   GPUResource.Percent per cell (32 B row = 2 x int4)   allocate.go:141-145
+//   gcount  uint8 [N]      len(NodeInfo.GPUs); 0 = node unknown                 node.go:25-42
+//   rl      int8  [N][8]   GPUResource.RemainLoad (written by load-aware Rate)  allocate.go:193
+//   tenths  uint8 [2][N][8] ceil(10*usage) per (metric, node, card); 255 = skip  nodeusage.go:82-111
+//   ts      uint32[2][N][8] update time, unix seconds                            stats.go:30-55
+//   tag     uint32[N], cscore int32[N]   per-node plan cache (NodeInfo.PlanCache, node.go:22)
+//
+// Kernels:
+//   k_assume     K1  one thread per candidate row: Rate + Choose, feasibility / score / plan out
+//   k_schedule   K6  persistent cooperative kernel, rows resident in shared memory, per pod:
+//                    filter+score every row (K1), block + grid arg-max (K2), bind on the owner (K3)
+//   k_bind, k_apply  K3  single-row plan application
+//   k_load_*     K4  usage-table updates
+// All paths relative to /root/reference/pkg/dealer/.
+#include <cooperative_groups.h>
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "ngs_device.cuh"
+
+namespace cg = cooperative_groups;
+using namespace ngs;
+
+namespace {
+
+struct Tables {
+    int32_t* free;
+    uint8_t* gcount;
+    int8_t* rl;
+    uint8_t* tenths;
+    uint32_t* ts;
+    uint32_t* tag;
+    int32_t* cscore;
+    uint32_t n;      // rows in this shard
+    uint32_t first;  // global node index of row 0
+};
+
+struct RowEval {
+    bool known;
+    bool feasible;
+    int score;
+    uint64_t emit;
+    int n_emit;
+};
+
+__device__ __forceinline__ int4 ld_row4(const int32_t* p) { return __ldcg(reinterpret_cast<const int4*>(p)); }
+
+// One full GPUs.Choose (allocate.go:92-100) on a row read from the global tables.
+// do_rate=false is the plan-cache hit of NodeInfo.Bind (node.go:72-78): the plan is re-derived
+// from the RemainLoad the filter pass left behind, without running Rate / LoadUsage again.
+template <bool PLAN>
+__device__ __forceinline__ RowEval eval_row_global(const Tables& T, uint32_t row, const SortedDemand* dem, const LoadParams& lp,
+                                                   bool do_rate) {
+    RowEval ev;
+    ev.known = false;
+    ev.feasible = false;
+    ev.score = NGS_SCORE_MIN;
+    ev.emit = 0;
+    ev.n_emit = 0;
+    const int G = T.gcount[row];
+    if (G == 0) return ev;
+    ev.known = true;
+    const int policy = dem->policy;
+    int f[8];
+    {
+        const int4 a = ld_row4(T.free + (size_t)row * 8), b = ld_row4(T.free + (size_t)row * 8 + 4);
+        f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w;
+        f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+    }
+    int rlc[8];
+    int load_int = 0;
+    if (lp.enabled && do_rate && policy != NGS_POLICY_RANDOM) {
+        // rater.go:62-66 / 116-120: LoadUsage per GPU, which also rewrites RemainLoad
+        uint8_t tenths[2][8];
+        uint32_t ts[2][8];
+#pragma unroll
+        for (int m = 0; m < 2; m++) {
+            const size_t off = ((size_t)m * T.n + row) * 8;
+            const uint2 t8 = __ldcg(reinterpret_cast<const uint2*>(T.tenths + off));
+            const uint4 t0 = __ldcg(reinterpret_cast<const uint4*>(T.ts + off));
+            const uint4 t1 = __ldcg(reinterpret_cast<const uint4*>(T.ts + off + 4));
+#pragma unroll
+            for (int g = 0; g < 4; g++) {
+                tenths[m][g] = (uint8_t)(t8.x >> (8 * g));
+                tenths[m][g + 4] = (uint8_t)(t8.y >> (8 * g));
+            }
+            ts[m][0] = t0.x; ts[m][1] = t0.y; ts[m][2] = t0.z; ts[m][3] = t0.w;
+            ts[m][4] = t1.x; ts[m][5] = t1.y; ts[m][6] = t1.z; ts[m][7] = t1.w;
+        }
+        load_usage_row(tenths, ts, lp, G, rlc, &load_int);
+        uint2 out;
+        out.x = out.y = 0;
+#pragma unroll
+        for (int g = 0; g < 4; g++) {
+            out.x |= (uint32_t)(uint8_t)(int8_t)(g < G ? rlc[g] - 2 : 0) << (8 * g);
+            out.y |= (uint32_t)(uint8_t)(int8_t)(g + 4 < G ? rlc[g + 4] - 2 : 0) << (8 * g);
+        }
+        *reinterpret_cast<uint2*>(T.rl + (size_t)row * 8) = out;
+    } else {
+        const uint2 r8 = __ldcg(reinterpret_cast<const uint2*>(T.rl + (size_t)row * 8));
+#pragma unroll
+        for (int g = 0; g < 4; g++) {
+            rlc[g] = (int)(int8_t)(r8.x >> (8 * g)) + 2;
+            rlc[g + 4] = (int)(int8_t)(r8.y >> (8 * g)) + 2;
+        }
+    }
+    if (do_rate) ev.score = rate_policy(policy, f, G, load_int);
+    if (policy == NGS_POLICY_RANDOM) {
+        ev.feasible = choose_sample<PLAN>(f, G, dem, &ev.emit, &ev.n_emit);
+    } else {
+        uint32_t w[8];
+        bool rl0 = true;
+#pragma unroll
+        for (int g = 0; g < 8; g++) {
+            w[g] = g < G ? pack_cell(f[g], rlc[g], g) : W_PAD;
+            rl0 = rl0 && (g >= G || rlc[g] == 2);
+        }
+        ev.feasible = choose_sorted<PLAN>(w, G, policy == NGS_POLICY_SPREAD, rl0, dem, &ev.emit, &ev.n_emit);
+    }
+    return ev;
+}
+
+enum { MODE_ASSUME = 0, MODE_SCORE = 1 };
+
+// K1.  DealerImpl.Assume / DealerImpl.Score fan-out (dealer.go:109-134, 138-153): one thread
+// per candidate.  MODE_ASSUME recomputes every candidate (cleanPlan + Assume, dealer.go:123-124);
+// MODE_SCORE serves NodeInfo.Score (node.go:59-68) from the per-node cache when it holds a
+// plan for this demand generation.
+template <bool PLAN>
+__global__ void __launch_bounds__(256) k_assume(Tables T, const uint32_t* __restrict__ idx, uint32_t n, PodDemand pd, LoadParams lp,
+                                                int mode, uint32_t gen, uint8_t* __restrict__ feasible,
+                                                int8_t* __restrict__ reason, int32_t* __restrict__ score,
+                                                int32_t* __restrict__ plan, int32_t* __restrict__ n_emitted) {
+    __shared__ SortedDemand dem;
+    if (threadIdx.x == 0) sort_demand(pd.percent, pd.n, pd.policy, &dem);
+    __syncthreads();
+    const int C = pd.n;
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        const uint32_t gidx = idx ? idx[k] : T.first + k;
+        const uint32_t row = gidx - T.first;
+        RowEval ev;
+        ev.known = false;
+        ev.feasible = false;
+        ev.score = NGS_SCORE_MIN;
+        ev.emit = 0;
+        ev.n_emit = 0;
+        bool cached = false;
+        if (gidx >= T.first && row < T.n) {
+            if (mode == MODE_SCORE && T.tag[row] == gen && T.gcount[row] != 0) {
+                ev.known = ev.feasible = cached = true;
+                ev.score = T.cscore[row];
+            } else {
+                ev = eval_row_global<PLAN>(T, row, &dem, lp, true);
+            }
+        }
+        const bool ok = ev.known && ev.feasible;
+        if (ev.known && !cached) {
+            if (ok) {  // node.go:55
+                T.tag[row] = gen;
+                T.cscore[row] = ev.score;
+            } else if (mode == MODE_ASSUME) {
+                T.tag[row] = 0;  // dealer.go:123 cleared it, the failed Assume caches nothing
+            }
+        }
+        if (feasible) feasible[k] = ok ? 1 : 0;
+        if (reason) reason[k] = !ev.known ? NGS_REASON_UNKNOWN_NODE : (ok ? NGS_REASON_OK : NGS_REASON_INFEASIBLE);
+        if (score) score[k] = ok ? ev.score : NGS_SCORE_MIN;
+        if (PLAN) {
+            if (plan) {
+                int32_t* out = plan + (size_t)k * C;
+                if (ev.known) write_plan(out, &dem, dem.policy != NGS_POLICY_RANDOM, ok, ev.emit, ev.n_emit);
+                else for (int j = 0; j < C; j++) out[j] = INT32_MIN;
+            }
+            if (n_emitted) n_emitted[k] = ev.known ? ev.n_emit : 0;
+        }
+    }
+}
+
+struct BindResult {
+    int32_t status;
+    int32_t score;
+    int32_t gpu_idx[NGS_MAX_CONTAINERS];
+};
+
+// K3.  NodeInfo.Bind (node.go:70-84) for one row: cached or fresh plan, GPUs.Allocate, cleanPlan.
+__global__ void k_bind(Tables T, uint32_t gidx, PodDemand pd, LoadParams lp, uint32_t gen, BindResult* res) {
+    __shared__ SortedDemand dem;
+    if (threadIdx.x != 0) return;
+    sort_demand(pd.percent, pd.n, pd.policy, &dem);
+    const uint32_t row = gidx - T.first;
+    for (int j = 0; j < NGS_MAX_CONTAINERS; j++) res->gpu_idx[j] = INT32_MIN;
+    res->score = NGS_SCORE_MIN;
+    if (gidx < T.first || row >= T.n || T.gcount[row] == 0) {
+        res->status = NGS_ERR_UNKNOWN_NODE;
+        return;
+    }
+    const bool hit = T.tag[row] == gen;
+    RowEval ev = eval_row_global<true>(T, row, &dem, lp, !hit);
+    if (!ev.feasible) {  // node.go:74-76
+        res->status = NGS_ERR_INFEASIBLE;
+        return;
+    }
+    int32_t planv[NGS_MAX_CONTAINERS];
+    write_plan(planv, &dem, dem.policy != NGS_POLICY_RANDOM, true, ev.emit, ev.n_emit);
+    int32_t* f = T.free + (size_t)row * 8;
+    for (int k = 0; k < pd.n; k++) {  // GPUs.Allocate (allocate.go:102-118); the plan fits by construction
+        res->gpu_idx[k] = planv[k];
+        if (planv[k] >= 0) f[planv[k]] -= pd.percent[k];
+    }
+    res->score = hit ? T.cscore[row] : ev.score;
+    T.tag[row] = 0;  // node.go:82
+    res->status = NGS_OK;
+}
+
+// K3.  GPUs.Allocate (sign>0, all-or-nothing) / GPUs.Release (sign<0) with a caller-given plan.
+__global__ void k_apply(Tables T, uint32_t gidx, PodDemand pd, const int32_t* __restrict__ gpu_idx_in, int sign, int32_t* status) {
+    if (threadIdx.x != 0) return;
+    const uint32_t row = gidx - T.first;
+    if (gidx < T.first || row >= T.n || T.gcount[row] == 0) {
+        *status = NGS_ERR_UNKNOWN_NODE;
+        return;
+    }
+    const int G = T.gcount[row];
+    int32_t* fp = T.free + (size_t)row * 8;
+    int f[8];
+    for (int g = 0; g < 8; g++) f[g] = fp[g];
+    T.tag[row] = 0;  // node.go:87,92: cleanPlan runs before the apply, whatever its outcome
+    int rc = NGS_OK;
+    if (sign > 0) {
+        for (int k = 0; k < pd.n; k++) {
+            const int gi = gpu_idx_in[k];
+            if (gi < 0) continue;  // allocate.go:105-107
+            if (gi >= G || f[gi] < pd.percent[k]) {  // allocate.go:108 (an index >= G panics in Go)
+                rc = NGS_ERR_APPLY;
+                break;
+            }
+            f[gi] -= pd.percent[k];
+        }
+        if (rc == NGS_OK)
+            for (int g = 0; g < 8; g++) fp[g] = f[g];
+    } else {
+        for (int k = 0; k < pd.n; k++) {
+            const int gi = gpu_idx_in[k];
+            if (gi < 0) continue;
+            if (gi >= G) {  // allocate.go:125-127: earlier containers stay released
+                rc = NGS_ERR_APPLY;
+                break;
+            }
+            if (f[gi] + pd.percent[k] > NGS_MAX_FREE) {
+                rc = NGS_ERR_RANGE;
+                break;
+            }
+            f[gi] += pd.percent[k];
+        }
+        if (rc != NGS_ERR_RANGE)
+            for (int g = 0; g < 8; g++) fp[g] = f[g];
+    }
+    *status = rc;
+}
+
+// NewNodeInfo (node.go:25-42)
+__global__ void k_upsert(Tables T, uint32_t row, int G) {
+    if (threadIdx.x != 0) return;
+    T.gcount[row] = (uint8_t)G;
+    for (int g = 0; g < 8; g++) {
+        T.free[(size_t)row * 8 + g] = g < G ? 100 : 0;
+        T.rl[(size_t)row * 8 + g] = 0;
+    }
+    T.tag[row] = 0;
+}
+
+// K4.  Update{Core,Memory}Usage (nodeusage.go:70-80) on one cell / Add*Usage (nodeusage.go:58-68)
+__global__ void k_load_update(Tables T, uint32_t row, int metric, int card, uint8_t tenths, uint32_t ts) {
+    if (threadIdx.x != 0) return;
+    const size_t off = ((size_t)metric * T.n + row) * 8 + card;
+    T.tenths[off] = tenths;
+    T.ts[off] = ts;
+}
+__global__ void k_load_add_node(Tables T, uint32_t row, int metric) {
+    const size_t off = ((size_t)metric * T.n + row) * 8 + threadIdx.x;
+    if (threadIdx.x < 8) {
+        T.tenths[off] = 255;
+        T.ts[off] = 0;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K6: persistent batch kernel
+// ---------------------------------------------------------------------------------------------
+__global__ void k_prep_demands(const int32_t* __restrict__ percent, const int32_t* __restrict__ ncont, int max_c,
+                               const int32_t* __restrict__ policy, uint32_t P, SortedDemand* __restrict__ out, int32_t* err) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    int C = ncont[p];
+    int pol = policy[p];
+    bool bad = C < 0 || C > NGS_MAX_CONTAINERS || C > max_c || pol < 0 || pol > NGS_POLICY_RANDOM;
+    if (bad) C = 0;
+    int32_t pc[NGS_MAX_CONTAINERS];
+    for (int k = 0; k < NGS_MAX_CONTAINERS; k++) {
+        pc[k] = k < C ? percent[(size_t)p * max_c + k] : 0;
+        if (pc[k] < 0 || pc[k] > NGS_MAX_FREE) bad = true;
+    }
+    if (bad) {
+        atomicExch(err, NGS_ERR_INVALID);
+        for (int k = 0; k < NGS_MAX_CONTAINERS; k++) pc[k] = 0;
+        C = 0;
+        pol = NGS_POLICY_BINPACK;
+    }
+    sort_demand(pc, C, pol, &out[p]);
+}
+
+struct BatchParams {
+    Tables T;
+    const SortedDemand* dem;  // [P]
+    uint32_t P;
+    LoadParams lp;
+    uint64_t seed_seq;  // seed + seq0 of pod 0
+    int32_t* node_out;
+    int32_t* score_out;
+    int32_t* gpu_idx_out;
+    int max_c;
+    unsigned long long* keys;  // [P][gridDim.x], zero before launch
+    uint32_t rows_per_block;
+};
+
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ uint64_t warp_max_u64(uint64_t v) {
+    const uint32_t hi = (uint32_t)(v >> 32);
+    const uint32_t mhi = __reduce_max_sync(0xFFFFFFFFu, hi);
+    const uint32_t lo = hi == mhi ? (uint32_t)v : 0u;
+    const uint32_t mlo = __reduce_max_sync(0xFFFFFFFFu, lo);
+    return ((uint64_t)mhi << 32) | mlo;
+}
+
+// shared-memory row: 8 x u16 free (two uint2), meta = RemainLoad codes [23:0] | G [27:24] | load_int [31:28]
+struct SmemRows {
+    uint2* fA;
+    uint2* fB;
+    uint32_t* meta;
+    int32_t* scB;  // Binpack.Rate of the row's current state
+    int32_t* scS;  // Spread.Rate
+    uint32_t* feasbits;
+};
+
+__device__ __forceinline__ void unpack_free(uint2 a, uint2 b, int (&f)[8]) {
+    f[0] = a.x & 0xFFFF; f[1] = a.x >> 16; f[2] = a.y & 0xFFFF; f[3] = a.y >> 16;
+    f[4] = b.x & 0xFFFF; f[5] = b.x >> 16; f[6] = b.y & 0xFFFF; f[7] = b.y >> 16;
+}
+
+// filter one shared-memory row for the staged demand; feasibility only
+__device__ __forceinline__ bool eval_row_smem(const SmemRows& S, uint32_t r, const SortedDemand* dem, int policy) {
+    const uint32_t meta = S.meta[r];
+    const int G = (meta >> 24) & 15;
+    if (G == 0) return false;
+    int f[8];
+    unpack_free(S.fA[r], S.fB[r], f);
+    if (policy == NGS_POLICY_RANDOM) return choose_sample<false>(f, G, dem, nullptr, nullptr);
+    uint32_t w[8];
+    const bool rl0 = (meta & 0xFFFFFFu) == RL0_META;
+#pragma unroll
+    for (int g = 0; g < 8; g++) w[g] = g < G ? pack_cell(f[g], (meta >> (3 * g)) & 7, g) : W_PAD;
+    return choose_sorted<false>(w, G, policy == NGS_POLICY_SPREAD, rl0, dem, nullptr, nullptr);
+}
+
+// bind on the owning block: exact plan, apply to the shared row, refresh both cached rates,
+// write the row through to the global table and publish the decision.
+__device__ void bind_row_smem(const BatchParams& bp, const SmemRows& S, uint32_t r, uint32_t row, const SortedDemand* dem,
+                              uint32_t p, int score) {
+    const uint32_t meta = S.meta[r];
+    const int G = (meta >> 24) & 15;
+    const int load_int = (int)(meta >> 28);
+    const int policy = dem->policy;
+    int f[8];
+    unpack_free(S.fA[r], S.fB[r], f);
+    uint64_t emit = 0;
+    int n_emit = 0;
+    if (policy == NGS_POLICY_RANDOM) {
+        int f2[8];
+#pragma unroll
+        for (int g = 0; g < 8; g++) f2[g] = f[g];
+        choose_sample<true>(f2, G, dem, &emit, &n_emit);
+    } else {
+        uint32_t w[8];
+        const bool rl0 = (meta & 0xFFFFFFu) == RL0_META;
+#pragma unroll
+        for (int g = 0; g < 8; g++) w[g] = g < G ? pack_cell(f[g], (meta >> (3 * g)) & 7, g) : W_PAD;
+        choose_sorted<true>(w, G, policy == NGS_POLICY_SPREAD, rl0, dem, &emit, &n_emit);
+    }
+    int32_t* out = bp.gpu_idx_out + (size_t)p * bp.max_c;
+    int32_t planv[NGS_MAX_CONTAINERS];
+    write_plan(planv, dem, policy != NGS_POLICY_RANDOM, true, emit, n_emit);
+    for (int k = 0; k < bp.max_c; k++) out[k] = k < dem->C ? planv[k] : INT32_MIN;
+    for (int k = 0; k < dem->C; k++) {  // GPUs.Allocate (allocate.go:102-118)
+        const int gi = planv[k];
+        if (gi < 0) continue;
+        const int d = dem->raw[k];
+#pragma unroll
+        for (int g = 0; g < 8; g++) f[g] -= (g == gi) ? d : 0;
+    }
+    uint2 a, b;
+    a.x = (uint32_t)f[0] | ((uint32_t)f[1] << 16); a.y = (uint32_t)f[2] | ((uint32_t)f[3] << 16);
+    b.x = (uint32_t)f[4] | ((uint32_t)f[5] << 16); b.y = (uint32_t)f[6] | ((uint32_t)f[7] << 16);
+    S.fA[r] = a;
+    S.fB[r] = b;
+    S.scB[r] = rate_binpack(f, G, load_int);
+    S.scS[r] = rate_spread(f, G, load_int);
+    int4* gp = reinterpret_cast<int4*>(bp.T.free + (size_t)row * 8);
+    gp[0] = make_int4(f[0], f[1], f[2], f[3]);
+    gp[1] = make_int4(f[4], f[5], f[6], f[7]);
+    bp.T.tag[row] = 0;  // node.go:82
+    bp.node_out[p] = (int32_t)(bp.T.first + row);
+    bp.score_out[p] = score;
+}
+
+// K6.  One CTA per SM (cooperative launch, so every CTA is resident), each owning a contiguous
+// node range held in shared memory for the whole batch.  Per pod, in order:
+//   1. every thread filters its rows for the pod's demand (Rate is a function of the row only,
+//      allocate.go:96, so both policies' rates are kept beside the row and refreshed on bind);
+//   2. block arg-max -> one 64-bit key per CTA posted to keys[p][cta]; warp 0 of every CTA polls
+//      the pod's key row until all CTAs have posted and reduces it: the same winner everywhere,
+//      one L2 round trip, no atomics;  (random policy: feasible counts + seeded k-th pick)
+//   3. the CTA owning the winning row binds it; no other CTA ever reads that row.
+__global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ SortedDemand s_dem[2];
+    __shared__ uint64_t s_red[32];
+    const uint32_t rpb = bp.rows_per_block;
+    SmemRows S;
+    S.fA = reinterpret_cast<uint2*>(smem_raw);
+    S.fB = S.fA + rpb;
+    S.meta = reinterpret_cast<uint32_t*>(S.fB + rpb);
+    S.scB = reinterpret_cast<int32_t*>(S.meta + rpb);
+    S.scS = S.scB + rpb;
+    S.feasbits = reinterpret_cast<uint32_t*>(S.scS + rpb);
+
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    const uint32_t row0 = blockIdx.x * rpb;
+    const uint32_t my_rows = row0 < bp.T.n ? min(rpb, bp.T.n - row0) : 0u;
+    const Tables& T = bp.T;
+
+    // ---- prologue: rows -> shared memory (and the load-aware quantities, frozen for the batch) ----
+    for (uint32_t r = tid; r < my_rows; r += blockDim.x) {
+        const uint32_t row = row0 + r;
+        const int G = T.gcount[row];
+        int f[8];
+        const int4 a = ld_row4(T.free + (size_t)row * 8), b = ld_row4(T.free + (size_t)row * 8 + 4);
+        f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w;
+        f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+        int rlc[8];
+        int load_int = 0;
+        if (bp.lp.enabled && G > 0) {
+            uint8_t tenths[2][8];
+            uint32_t ts[2][8];
+#pragma unroll
+            for (int m = 0; m < 2; m++) {
+                const size_t off = ((size_t)m * T.n + row) * 8;
+                const uint2 t8 = __ldcg(reinterpret_cast<const uint2*>(T.tenths + off));
+                const uint4 t0 = __ldcg(reinterpret_cast<const uint4*>(T.ts + off));
+                const uint4 t1 = __ldcg(reinterpret_cast<const uint4*>(T.ts + off + 4));
+#pragma unroll
+                for (int g = 0; g < 4; g++) {
+                    tenths[m][g] = (uint8_t)(t8.x >> (8 * g));
+                    tenths[m][g + 4] = (uint8_t)(t8.y >> (8 * g));
+                }
+                ts[m][0] = t0.x; ts[m][1] = t0.y; ts[m][2] = t0.z; ts[m][3] = t0.w;
+                ts[m][4] = t1.x; ts[m][5] = t1.y; ts[m][6] = t1.z; ts[m][7] = t1.w;
+            }
+            load_usage_row(tenths, ts, bp.lp, G, rlc, &load_int);
+        } else {
+            const uint2 r8 = __ldcg(reinterpret_cast<const uint2*>(T.rl + (size_t)row * 8));
+#pragma unroll
+            for (int g = 0; g < 4; g++) {
+                rlc[g] = (int)(int8_t)(r8.x >> (8 * g)) + 2;
+                rlc[g + 4] = (int)(int8_t)(r8.y >> (8 * g)) + 2;
+            }
+        }
+        uint32_t meta = ((uint32_t)G << 24) | ((uint32_t)load_int << 28);
+#pragma unroll
+        for (int g = 0; g < 8; g++) meta |= (uint32_t)(g < G ? rlc[g] : 2) << (3 * g);
+        uint2 pa, pb;
+        pa.x = (uint32_t)f[0] | ((uint32_t)f[1] << 16); pa.y = (uint32_t)f[2] | ((uint32_t)f[3] << 16);
+        pb.x = (uint32_t)f[4] | ((uint32_t)f[5] << 16); pb.y = (uint32_t)f[6] | ((uint32_t)f[7] << 16);
+        S.fA[r] = pa;
+        S.fB[r] = pb;
+        S.meta[r] = meta;
+        S.scB[r] = G ? rate_binpack(f, G, load_int) : 0;
+        S.scS[r] = G ? rate_spread(f, G, load_int) : 0;
+    }
+    if (tid < sizeof(SortedDemand) / 4 && bp.P > 0)
+        reinterpret_cast<uint32_t*>(&s_dem[0])[tid] = reinterpret_cast<const uint32_t*>(&bp.dem[0])[tid];
+    __syncthreads();
+
+    const uint32_t n_iter = (my_rows + blockDim.x - 1) / blockDim.x;
+    for (uint32_t p = 0; p < bp.P; p++) {
+        const SortedDemand* dem = &s_dem[p & 1];
+        const int policy = dem->policy;
+        // stage the next pod's demand while this one is evaluated (last warp: the least loaded)
+        if (warp == nwarps - 1 && p + 1 < bp.P)
+            for (uint32_t i = lane; i < sizeof(SortedDemand) / 4; i += 32)
+                reinterpret_cast<uint32_t*>(&s_dem[(p + 1) & 1])[i] = reinterpret_cast<const uint32_t*>(&bp.dem[p + 1])[i];
+
+        // ---- 1. filter + score my rows ----
+        uint64_t best = 0;
+        uint32_t cnt = 0;
+        for (uint32_t it = 0; it < n_iter; it++) {
+            const uint32_t r = it * blockDim.x + tid;
+            bool ok = false;
+            if (r < my_rows) ok = eval_row_smem(S, r, dem, policy);
+            if (policy == NGS_POLICY_RANDOM) {
+                const uint32_t bal = __ballot_sync(0xFFFFFFFFu, ok);
+                if (lane == 0 && r < my_rows) {
+                    S.feasbits[r >> 5] = bal;
+                    cnt += __popc(bal);
+                }
+            } else if (ok) {
+                const int sc = policy == NGS_POLICY_BINPACK ? S.scB[r] : S.scS[r];
+                const uint64_t key = make_key(sc, T.first + row0 + r);
+                best = key > best ? key : best;
+            }
+        }
+        // ---- 2. block reduce, post, gather ----
+        if (policy == NGS_POLICY_RANDOM) {
+            if (lane == 0) s_red[warp] = cnt;
+        } else {
+            best = warp_max_u64(best);
+            if (lane == 0) s_red[warp] = best;
+        }
+        __syncthreads();
+        if (warp == 0) {
+            unsigned long long* krow = bp.keys + (size_t)p * gridDim.x;
+            uint64_t v = lane < nwarps ? s_red[lane] : 0;
+            if (policy == NGS_POLICY_RANDOM) {
+                uint32_t c = (uint32_t)v;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, o);
+                if (lane == 0) st_relaxed_u64(krow + blockIdx.x, KEY_VALID | c);
+                // contiguous chunk of CTAs per lane so that a prefix over lanes is a prefix over CTAs
+                const uint32_t chunk = (gridDim.x + 31) / 32;
+                const uint32_t j0 = min(lane * chunk, gridDim.x), j1 = min(j0 + chunk, gridDim.x);
+                uint64_t sum = 0;
+                for (uint32_t j = j0; j < j1; j++) {
+                    unsigned long long kv;
+                    do kv = ld_relaxed_u64(krow + j); while (!(kv & KEY_VALID));
+                    sum += kv & 0xFFFFFFFFull;
+                }
+                uint64_t incl = sum;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint64_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+                    if (lane >= (uint32_t)o) incl += t;
+                }
+                const uint64_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+                if (total == 0) {
+                    if (blockIdx.x == 0 && lane == 0) {
+                        bp.node_out[p] = -1;
+                        bp.score_out[p] = NGS_SCORE_MIN;
+                        for (int k = 0; k < bp.max_c; k++) bp.gpu_idx_out[(size_t)p * bp.max_c + k] = INT32_MIN;
+                    }
+                } else {
+                    const uint64_t pick = splitmix64(bp.seed_seq + p) % total;
+                    // rank of the pick inside this CTA, if it falls here
+                    uint64_t run = incl - sum;
+                    long long local_rank = -1;
+                    for (uint32_t j = j0; j < j1; j++) {
+                        const uint64_t cj = ld_relaxed_u64(krow + j) & 0xFFFFFFFFull;
+                        if (j == blockIdx.x && pick >= run && pick < run + cj) local_rank = (long long)(pick - run);
+                        run += cj;
+                    }
+                    // exactly one lane of exactly one CTA sees local_rank >= 0
+                    const uint32_t who = __ballot_sync(0xFFFFFFFFu, local_rank >= 0);
+                    if (who) {
+                        const uint32_t rank = (uint32_t)__shfl_sync(0xFFFFFFFFu, (int)local_rank, __ffs(who) - 1);
+                        // locate the rank-th set bit of feasbits (rows of this CTA in index order)
+                        const uint32_t nwords = (my_rows + 31) / 32;
+                        const uint32_t wchunk = (nwords + 31) / 32;
+                        const uint32_t w0 = min(lane * wchunk, nwords), w1 = min(w0 + wchunk, nwords);
+                        uint32_t s = 0;
+                        for (uint32_t wi = w0; wi < w1; wi++) s += __popc(S.feasbits[wi]);
+                        uint32_t inc = s;
+#pragma unroll
+                        for (int o = 1; o < 32; o <<= 1) {
+                            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+                            if (lane >= (uint32_t)o) inc += t;
+                        }
+                        uint32_t before = inc - s;
+                        if (rank >= before && rank < before + s) {
+                            uint32_t need = rank - before;
+                            for (uint32_t wi = w0; wi < w1; wi++) {
+                                uint32_t bits = S.feasbits[wi];
+                                const uint32_t pc = __popc(bits);
+                                if (need < pc) {
+                                    for (uint32_t q = 0; q < need; q++) bits &= bits - 1;
+                                    const uint32_t r = wi * 32 + (__ffs(bits) - 1);
+                                    bind_row_smem(bp, S, r, row0 + r, dem, p, 100);
+                                    break;
+                                }
+                                need -= pc;
+                            }
+                        }
+                    }
+                }
+            } else {
+                v = warp_max_u64(v);
+                if (lane == 0) st_relaxed_u64(krow + blockIdx.x, KEY_VALID | v);
+                uint64_t m = 0;
+                for (uint32_t j = lane; j < gridDim.x; j += 32) {
+                    unsigned long long kv;
+                    do kv = ld_relaxed_u64(krow + j); while (!(kv & KEY_VALID));
+                    m = kv > m ? kv : m;
+                }
+                m = warp_max_u64(m);
+                if (lane == 0) {
+                    if (!(m & KEY_FEASIBLE)) {
+                        if (blockIdx.x == 0) {
+                            bp.node_out[p] = -1;
+                            bp.score_out[p] = NGS_SCORE_MIN;
+                            for (int k = 0; k < bp.max_c; k++) bp.gpu_idx_out[(size_t)p * bp.max_c + k] = INT32_MIN;
+                        }
+                    } else {
+                        const uint32_t row = key_node(m) - T.first;
+                        // ---- 3. bind on the owner ----
+                        if (row >= row0 && row < row0 + my_rows) bind_row_smem(bp, S, row - row0, row, dem, p, key_score(m));
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+}  // namespace
+
+struct ngs_dealer {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    Tables T{};
+    int num_sms = 0;
+    int smem_optin = 0;
+    int coop = 0;
+    // plan-cache generation (NodeInfo.PlanCache keyed by Demand.Hash, allocate.go:72-75)
+    uint32_t gen = 1;
+    std::vector<int32_t> cur_demand;
+    // device scratch
+    uint32_t* d_idx = nullptr;
+    uint8_t* d_feas = nullptr;
+    int8_t* d_reason = nullptr;
+    int32_t* d_score = nullptr;
+    int32_t* d_plan = nullptr;
+    int32_t* d_nem = nullptr;
+    size_t verb_cap = 0;   // candidates the verb scratch holds
+    size_t plan_cap = 0;   // int32 entries d_plan holds
+    BindResult* d_bind = nullptr;
+    BindResult* h_bind = nullptr;  // pinned
+    int32_t* d_small = nullptr;    // gpu_idx in / status out for k_apply
+    int32_t* h_small = nullptr;    // pinned
+    // batch
+    uint32_t batch_cap = 0;  // pods per launch chunk
+    SortedDemand* d_dem = nullptr;
+    unsigned long long* d_keys = nullptr;
+    int32_t* d_pod_in = nullptr;   // percent [cap][12] | ncont [cap] | policy [cap]
+    int32_t* d_pod_out = nullptr;  // node [cap] | score [cap] | gpu_idx [cap][12]
+    int32_t* h_pod_in = nullptr;   // pinned mirrors
+    int32_t* h_pod_out = nullptr;
+    int32_t* d_err = nullptr;
+    int32_t* h_err = nullptr;
+    ngs_stats_t stats{};
+    char err[512] = {0};
+};
+
+namespace {
+
+constexpr uint32_t BATCH_CHUNK = 4096;
+
+int fail(ngs_dealer* h, int code, const char* fmt, ...) {
+    if (h) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(h->err, sizeof(h->err), fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+
+#define CU(h, call)                                                                                   \
+    do {                                                                                              \
+        cudaError_t e_ = (call);                                                                      \
+        if (e_ != cudaSuccess)                                                                        \
+            return fail(h, NGS_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+int make_demand(ngs_dealer* h, const int32_t* percent, int n, int policy, PodDemand* pd) {
+    if (n < 0 || (n > 0 && !percent)) return fail(h, NGS_ERR_INVALID, "demand: bad container count %d", n);
+    if (n > NGS_MAX_CONTAINERS) return fail(h, NGS_ERR_UNSUPPORTED, "demand: %d containers > NGS_MAX_CONTAINERS", n);
+    if (policy < 0 || policy > NGS_POLICY_RANDOM) return fail(h, NGS_ERR_INVALID, "unknown policy %d", policy);
+    memset(pd, 0, sizeof(*pd));
+    pd->n = n;
+    pd->policy = policy;
+    for (int i = 0; i < n; i++) {
+        if (percent[i] < 0 || percent[i] > NGS_MAX_FREE) return fail(h, NGS_ERR_INVALID, "demand: percent[%d]=%d out of range", i, percent[i]);
+        pd->percent[i] = percent[i];
+    }
+    return NGS_OK;
+}
+
+// floor division for possibly negative numerators
+int64_t floor_div(int64_t a, int64_t b) {
+    int64_t q = a / b, r = a % b;
+    return (r != 0 && ((r < 0) != (b < 0))) ? q - 1 : q;
+}
+
+int make_load(ngs_dealer* h, const ngs_load_ctx* L, LoadParams* lp) {
+    memset(lp, 0, sizeof(*lp));
+    if (!L) return NGS_OK;
+    if (L->n_periods < 0) return fail(h, NGS_ERR_INVALID, "load ctx: n_periods < 0");
+    if (L->n_periods > NGS_MAX_PERIODS) return fail(h, NGS_ERR_UNSUPPORTED, "load ctx: %d periods > NGS_MAX_PERIODS", L->n_periods);
+    lp->enabled = 1;
+    lp->n_periods = L->n_periods;
+    for (int e = 0; e < L->n_periods; e++) {
+        if (L->metric[e] != NGS_METRIC_CORE && L->metric[e] != NGS_METRIC_MEMORY) return fail(h, NGS_ERR_INVALID, "load ctx: metric[%d]", e);
+        lp->metric[e] = L->metric[e];
+        // now < ts*1e9 + window  <=>  ts >= floor((now - window) / 1e9) + 1
+        const int64_t min_ts = floor_div(L->now_ns - L->window_ns[e], 1000000000LL) + 1;
+        if (min_ts <= 0) lp->min_ts[e] = 0;
+        else if (min_ts > 0xFFFFFFFFLL) lp->never[e] = 1;
+        else lp->min_ts[e] = (uint32_t)min_ts;
+    }
+    return NGS_OK;
+}
+
+// Demand.Hash keyed plan cache (node.go:45-47): a new demand opens a new generation
+uint32_t demand_generation(ngs_dealer* h, const PodDemand& pd) {
+    std::vector<int32_t> d(pd.percent, pd.percent + pd.n);
+    if (d != h->cur_demand) {
+        h->cur_demand.swap(d);
+        h->gen++;
+        if (h->gen == 0) h->gen = 1;
+    }
+    return h->gen;
+}
+
+int ensure_verb_scratch(ngs_dealer* h, size_t n, size_t plan_entries) {
+    if (n > h->verb_cap) {
+        size_t cap = n < 1024 ? 1024 : n;
+        cudaFree(h->d_idx); cudaFree(h->d_feas); cudaFree(h->d_reason); cudaFree(h->d_score); cudaFree(h->d_nem);
+        h->d_idx = nullptr; h->d_feas = nullptr; h->d_reason = nullptr; h->d_score = nullptr; h->d_nem = nullptr;
+        h->verb_cap = 0;
+        CU(h, cudaMalloc(&h->d_idx, cap * 4));
+        CU(h, cudaMalloc(&h->d_feas, cap));
+        CU(h, cudaMalloc(&h->d_reason, cap));
+        CU(h, cudaMalloc(&h->d_score, cap * 4));
+        CU(h, cudaMalloc(&h->d_nem, cap * 4));
+        h->verb_cap = cap;
+    }
+    if (plan_entries > h->plan_cap) {
+        cudaFree(h->d_plan);
+        h->d_plan = nullptr;
+        h->plan_cap = 0;
+        CU(h, cudaMalloc(&h->d_plan, plan_entries * 4));
+        h->plan_cap = plan_entries;
+    }
+    return NGS_OK;
+}
+
+int ensure_batch(ngs_dealer* h) {
+    if (h->batch_cap) return NGS_OK;
+    const uint32_t cap = BATCH_CHUNK;
+    const size_t in_words = (size_t)cap * (NGS_MAX_CONTAINERS + 2), out_words = (size_t)cap * (NGS_MAX_CONTAINERS + 2);
+    CU(h, cudaMalloc(&h->d_dem, sizeof(SortedDemand) * cap));
+    CU(h, cudaMalloc(&h->d_keys, sizeof(unsigned long long) * cap * h->num_sms));
+    CU(h, cudaMalloc(&h->d_pod_in, in_words * 4));
+    CU(h, cudaMalloc(&h->d_pod_out, out_words * 4));
+    CU(h, cudaMallocHost(&h->h_pod_in, in_words * 4));
+    CU(h, cudaMallocHost(&h->h_pod_out, out_words * 4));
+    h->batch_cap = cap;
+    return NGS_OK;
+}
+
+// launch K6 for one chunk of <= BATCH_CHUNK pods whose inputs are in device memory
+int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const int32_t* d_ncont, int max_c, const int32_t* d_policy,
+                    const LoadParams& lp, uint64_t seed_seq, int32_t* d_node, int32_t* d_score, int32_t* d_gidx) {
+    if (!h->coop) return fail(h, NGS_ERR_CUDA, "device lacks cooperative launch");
+    const uint32_t N = h->T.n;
+    uint32_t grid = (N + 63) / 64;
+    if (grid < 1) grid = 1;
+    if (grid > (uint32_t)h->num_sms) grid = (uint32_t)h->num_sms;
+    const uint32_t rpb = (N + grid - 1) / grid;
+    uint32_t block = ((rpb + 31) / 32) * 32;
+    if (block < 64) block = 64;
+    if (block > 1024) block = 1024;
+    const size_t smem = (size_t)rpb * 28 + (size_t)((rpb + 31) / 32) * 4 + 16;
+    if (smem > (size_t)h->smem_optin)
+        return fail(h, NGS_ERR_UNSUPPORTED, "%u rows per SM need %zu B shared memory (> %d): shard the cluster over more GPUs", rpb, smem, h->smem_optin);
+    CU(h, cudaFuncSetAttribute(k_schedule, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_prep_demands<<<(P + 127) / 128, 128, 0, h->stream>>>(d_percent, d_ncont, max_c, d_policy, P, h->d_dem, h->d_err);
+    CU(h, cudaGetLastError());
+    CU(h, cudaMemsetAsync(h->d_keys, 0, sizeof(unsigned long long) * (size_t)P * grid, h->stream));
+    BatchParams bp;
+    bp.T = h->T;
+    bp.dem = h->d_dem;
+    bp.P = P;
+    bp.lp = lp;
+    bp.seed_seq = seed_seq;
+    bp.node_out = d_node;
+    bp.score_out = d_score;
+    bp.gpu_idx_out = d_gidx;
+    bp.max_c = max_c;
+    bp.keys = h->d_keys;
+    bp.rows_per_block = rpb;
+    void* args[] = {&bp};
+    CU(h, cudaLaunchCooperativeKernel((void*)k_schedule, dim3(grid), dim3(block), args, smem, h->stream));
+    h->stats.kernel_launches += 2;
+    h->stats.node_evals += (uint64_t)P * N;
+    h->stats.pods_scheduled += P;
+    return NGS_OK;
+}
+
+int check_dev_err(ngs_dealer* h) {
+    if (*h->h_err != NGS_OK) {
+        int e = *h->h_err;
+        *h->h_err = NGS_OK;
+        cudaMemsetAsync(h->d_err, 0, 4, h->stream);
+        return fail(h, e, "device-side validation failed (bad container count, percent or policy in a batch)");
+    }
+    return NGS_OK;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------
+extern "C" {
+
+uint32_t ngs_abi_version(void) { return NGS_ABI_VERSION; }
+
+const char* ngs_strerror(int s) {
+    switch (s) {
+        case NGS_OK: return "ok";
+        case NGS_ERR_INVALID: return "invalid argument";
+        case NGS_ERR_CUDA: return "CUDA error";
+        case NGS_ERR_UNKNOWN_NODE: return "unknown node";
+        case NGS_ERR_INFEASIBLE: return "assume failed: demand does not fit the node";
+        case NGS_ERR_APPLY: return "can't apply plan";
+        case NGS_ERR_RANGE: return "capacity out of range";
+        case NGS_ERR_UNSUPPORTED: return "unsupported size";
+        default: return "unknown status";
+    }
+}
+
+const char* ngs_last_error(const ngs_dealer* h) { return h ? h->err : ""; }
+
+int ngs_create(ngs_dealer** out, int device, uint32_t max_nodes, uint32_t first_node, void* stream) {
+    if (!out || max_nodes == 0) return NGS_ERR_INVALID;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return NGS_ERR_CUDA;
+    ngs_dealer* h = new (std::nothrow) ngs_dealer();
+    if (!h) return NGS_ERR_INVALID;
+    h->device = device;
+    *out = h;  // handed out even on failure so that ngs_last_error() can be read; destroy it either way
+    CU(h, cudaSetDevice(device));
+    CU(h, cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
+    CU(h, cudaDeviceGetAttribute(&h->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+    CU(h, cudaDeviceGetAttribute(&h->coop, cudaDevAttrCooperativeLaunch, device));
+    if (stream) {
+        h->stream = (cudaStream_t)stream;
+    } else {
+        CU(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+        h->own_stream = true;
+    }
+    const size_t N = max_nodes;
+    h->T.n = max_nodes;
+    h->T.first = first_node;
+    CU(h, cudaMalloc(&h->T.free, N * 8 * 4));
+    CU(h, cudaMalloc(&h->T.gcount, N));
+    CU(h, cudaMalloc(&h->T.rl, N * 8));
+    CU(h, cudaMalloc(&h->T.tenths, 2 * N * 8));
+    CU(h, cudaMalloc(&h->T.ts, 2 * N * 8 * 4));
+    CU(h, cudaMalloc(&h->T.tag, N * 4));
+    CU(h, cudaMalloc(&h->T.cscore, N * 4));
+    CU(h, cudaMemsetAsync(h->T.free, 0, N * 8 * 4, h->stream));
+    CU(h, cudaMemsetAsync(h->T.gcount, 0, N, h->stream));
+    CU(h, cudaMemsetAsync(h->T.rl, 0, N * 8, h->stream));
+    CU(h, cudaMemsetAsync(h->T.tenths, 0xFF, 2 * N * 8, h->stream));
+    CU(h, cudaMemsetAsync(h->T.ts, 0, 2 * N * 8 * 4, h->stream));
+    CU(h, cudaMemsetAsync(h->T.tag, 0, N * 4, h->stream));
+    CU(h, cudaMemsetAsync(h->T.cscore, 0, N * 4, h->stream));
+    CU(h, cudaMalloc(&h->d_bind, sizeof(BindResult)));
+    CU(h, cudaMallocHost(&h->h_bind, sizeof(BindResult)));
+    CU(h, cudaMalloc(&h->d_small, 64 * 4));
+    CU(h, cudaMallocHost(&h->h_small, 64 * 4));
+    CU(h, cudaMalloc(&h->d_err, 4));
+    CU(h, cudaMallocHost(&h->h_err, 4));
+    *h->h_err = 0;
+    CU(h, cudaMemsetAsync(h->d_err, 0, 4, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return NGS_OK;
+}
+
+int ngs_destroy(ngs_dealer* h) {
+    if (!h) return NGS_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    cudaFree(h->T.free); cudaFree(h->T.gcount); cudaFree(h->T.rl); cudaFree(h->T.tenths); cudaFree(h->T.ts);
+    cudaFree(h->T.tag); cudaFree(h->T.cscore);
+    cudaFree(h->d_idx); cudaFree(h->d_feas); cudaFree(h->d_reason); cudaFree(h->d_score); cudaFree(h->d_plan); cudaFree(h->d_nem);
+    cudaFree(h->d_bind); cudaFreeHost(h->h_bind); cudaFree(h->d_small); cudaFreeHost(h->h_small);
+    cudaFree(h->d_dem); cudaFree(h->d_keys); cudaFree(h->d_pod_in); cudaFree(h->d_pod_out);
+    cudaFreeHost(h->h_pod_in); cudaFreeHost(h->h_pod_out);
+    cudaFree(h->d_err); cudaFreeHost(h->h_err);
+    if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return NGS_OK;
+}
+
+void* ngs_stream(ngs_dealer* h) { return h ? (void*)h->stream : nullptr; }
+
+int ngs_sync(ngs_dealer* h) {
+    if (!h) return NGS_ERR_INVALID;
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaMemcpyAsync(h->h_err, h->d_err, 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return check_dev_err(h);
+}
+
+int ngs_stats(ngs_dealer* h, ngs_stats_t* out) {
+    if (!h || !out) return NGS_ERR_INVALID;
+    *out = h->stats;
+    return NGS_OK;
+}
+
+int ngs_node_upsert(ngs_dealer* h, uint32_t idx, int gpu_count) {
+    if (!h) return NGS_ERR_INVALID;
+    if (idx < h->T.first || idx - h->T.first >= h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "node %u outside this shard", idx);
+    if (gpu_count < 0) return fail(h, NGS_ERR_INVALID, "gpu_count %d", gpu_count);
+    if (gpu_count > NGS_MAX_GPUS) return fail(h, NGS_ERR_UNSUPPORTED, "gpu_count %d > NGS_MAX_GPUS", gpu_count);
+    CU(h, cudaSetDevice(h->device));
+    k_upsert<<<1, 32, 0, h->stream>>>(h->T, idx - h->T.first, gpu_count);
+    CU(h, cudaGetLastError());
+    h->stats.kernel_launches++;
+    return NGS_OK;
+}
+
+int ngs_snapshot_load(ngs_dealer* h, uint32_t first, uint32_t n, const uint8_t* gpu_count, const int32_t* free, const int8_t* remain_load) {
+    if (!h || !gpu_count) return NGS_ERR_INVALID;
+    if (first < h->T.first || (uint64_t)(first - h->T.first) + n > h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "rows [%u,%u) outside this shard", first, first + n);
+    if (n == 0) return NGS_OK;
+    const uint32_t r0 = first - h->T.first;
+    std::vector<int32_t> fr((size_t)n * 8);
+    std::vector<int8_t> rl((size_t)n * 8, 0);
+    for (uint32_t i = 0; i < n; i++) {
+        const int G = gpu_count[i];
+        if (G > NGS_MAX_GPUS) return fail(h, NGS_ERR_UNSUPPORTED, "row %u: gpu_count %d > NGS_MAX_GPUS", first + i, G);
+        for (int g = 0; g < 8; g++) {
+            int32_t v = g < G ? (free ? free[(size_t)i * 8 + g] : 100) : 0;
+            if (v < 0 || v > NGS_MAX_FREE) return fail(h, NGS_ERR_RANGE, "row %u cell %d: free %d out of range", first + i, g, v);
+            fr[(size_t)i * 8 + g] = v;
+            int r = (g < G && remain_load) ? remain_load[(size_t)i * 8 + g] : 0;
+            if (r < -2 || r > 2) return fail(h, NGS_ERR_RANGE, "row %u cell %d: remain_load %d out of range", first + i, g, r);
+            rl[(size_t)i * 8 + g] = (int8_t)r;
+        }
+    }
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaMemcpyAsync(h->T.free + (size_t)r0 * 8, fr.data(), fr.size() * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(h->T.rl + (size_t)r0 * 8, rl.data(), rl.size(), cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(h->T.gcount + r0, gpu_count, n, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemsetAsync(h->T.tag + r0, 0, (size_t)n * 4, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    h->stats.h2d_bytes += fr.size() * 4 + rl.size() + n;
+    return NGS_OK;
+}
+
+int ngs_snapshot_read(ngs_dealer* h, uint32_t first, uint32_t n, uint8_t* gpu_count, int32_t* free, int8_t* remain_load) {
+    if (!h) return NGS_ERR_INVALID;
+    if (first < h->T.first || (uint64_t)(first - h->T.first) + n > h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "rows [%u,%u) outside this shard", first, first + n);
+    if (n == 0) return NGS_OK;
+    const uint32_t r0 = first - h->T.first;
+    CU(h, cudaSetDevice(h->device));
+    if (gpu_count) CU(h, cudaMemcpyAsync(gpu_count, h->T.gcount + r0, n, cudaMemcpyDeviceToHost, h->stream));
+    if (free) CU(h, cudaMemcpyAsync(free, h->T.free + (size_t)r0 * 8, (size_t)n * 32, cudaMemcpyDeviceToHost, h->stream));
+    if (remain_load) CU(h, cudaMemcpyAsync(remain_load, h->T.rl + (size_t)r0 * 8, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    h->stats.d2h_bytes += (gpu_count ? n : 0) + (free ? (size_t)n * 32 : 0) + (remain_load ? (size_t)n * 8 : 0);
+    return NGS_OK;
+}
+
+int ngs_node_apply(ngs_dealer* h, uint32_t idx, const int32_t* gpu_idx, const int32_t* percent, int n_containers, int sign) {
+    if (!h || sign == 0) return NGS_ERR_INVALID;
+    PodDemand pd;
+    int rc = make_demand(h, percent, n_containers, NGS_POLICY_BINPACK, &pd);
+    if (rc) return rc;
+    if (n_containers > 0 && !gpu_idx) return fail(h, NGS_ERR_INVALID, "apply: gpu_idx is NULL");
+    CU(h, cudaSetDevice(h->device));
+    for (int i = 0; i < n_containers; i++) h->h_small[i] = gpu_idx[i];
+    CU(h, cudaMemcpyAsync(h->d_small, h->h_small, NGS_MAX_CONTAINERS * 4, cudaMemcpyHostToDevice, h->stream));
+    k_apply<<<1, 32, 0, h->stream>>>(h->T, idx, pd, h->d_small, sign, h->d_small + 32);
+    CU(h, cudaGetLastError());
+    CU(h, cudaMemcpyAsync(h->h_small + 32, h->d_small + 32, 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    h->stats.kernel_launches++;
+    rc = h->h_small[32];
+    if (rc) return fail(h, rc, "apply on node %u: %s", idx, ngs_strerror(rc));
+    return NGS_OK;
+}
+
+static uint8_t encode_tenths(double value, int value_ok, int64_t ts_sec, int ts_ok) {
+    // nodeusage.go:99-110 + allocate.go:190: every early-out means "skip this entry"
+    if (!value_ok || !ts_ok || std::isnan(value) || value < 0 || value > 1) return 255;
+    if (ts_sec < 0 || ts_sec > 0xFFFFFFFFLL) return 255;
+    return (uint8_t)std::ceil(10 * value);
+}
+
+int ngs_load_add_node(ngs_dealer* h, uint32_t idx, int metric) {
+    if (!h || metric < 0 || metric > 1) return NGS_ERR_INVALID;
+    if (idx < h->T.first || idx - h->T.first >= h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "node %u outside this shard", idx);
+    CU(h, cudaSetDevice(h->device));
+    k_load_add_node<<<1, 32, 0, h->stream>>>(h->T, idx - h->T.first, metric);
+    CU(h, cudaGetLastError());
+    h->stats.kernel_launches++;
+    return NGS_OK;
+}
+
+int ngs_load_update(ngs_dealer* h, uint32_t idx, int metric, int card, double value, int value_ok, int64_t ts_sec, int ts_ok) {
+    if (!h || metric < 0 || metric > 1) return NGS_ERR_INVALID;
+    if (idx < h->T.first || idx - h->T.first >= h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "node %u outside this shard", idx);
+    if (card < 0) return fail(h, NGS_ERR_INVALID, "card %d", card);
+    if (card >= NGS_MAX_GPUS) return NGS_OK;  // a card the kernels never look at (LoadUsage walks gpus only)
+    CU(h, cudaSetDevice(h->device));
+    const uint8_t t10 = encode_tenths(value, value_ok, ts_sec, ts_ok);
+    k_load_update<<<1, 32, 0, h->stream>>>(h->T, idx - h->T.first, metric, card, t10, t10 == 255 ? 0u : (uint32_t)ts_sec);
+    CU(h, cudaGetLastError());
+    h->stats.kernel_launches++;
+    return NGS_OK;
+}
+
+int ngs_load_update_bulk(ngs_dealer* h, int metric, uint32_t first, uint32_t n, const double* value, const uint8_t* value_ok,
+                         const int64_t* ts_sec, const uint8_t* ts_ok) {
+    if (!h || metric < 0 || metric > 1 || !value || !ts_sec) return NGS_ERR_INVALID;
+    if (first < h->T.first || (uint64_t)(first - h->T.first) + n > h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "rows [%u,%u) outside this shard", first, first + n);
+    if (n == 0) return NGS_OK;
+    const size_t cells = (size_t)n * 8;
+    std::vector<uint8_t> t10(cells);
+    std::vector<uint32_t> ts(cells);
+    for (size_t i = 0; i < cells; i++) {
+        t10[i] = encode_tenths(value[i], value_ok ? value_ok[i] : 1, ts_sec[i], ts_ok ? ts_ok[i] : 1);
+        ts[i] = t10[i] == 255 ? 0u : (uint32_t)ts_sec[i];
+    }
+    const size_t off = ((size_t)metric * h->T.n + (first - h->T.first)) * 8;
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaMemcpyAsync(h->T.tenths + off, t10.data(), cells, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(h->T.ts + off, ts.data(), cells * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    h->stats.h2d_bytes += cells * 5;
+    return NGS_OK;
+}
+
+static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, const int32_t* percent, int n_containers, int policy,
+                      const ngs_load_ctx* load, uint8_t* feasible, int8_t* reason, int32_t* score, int32_t* plan, int32_t* n_emitted) {
+    if (!h) return NGS_ERR_INVALID;
+    PodDemand pd;
+    LoadParams lp;
+    int rc = make_demand(h, percent, n_containers, policy, &pd);
+    if (rc) return rc;
+    rc = make_load(h, load, &lp);
+    if (rc) return rc;
+    if (!idx && n > h->T.n) return fail(h, NGS_ERR_INVALID, "n=%u exceeds the %u rows of this shard", n, h->T.n);
+    if (n == 0) return NGS_OK;
+    CU(h, cudaSetDevice(h->device));
+    const bool want_plan = plan || n_emitted;
+    rc = ensure_verb_scratch(h, n, want_plan ? (size_t)n * (n_containers > 0 ? n_containers : 1) : 0);
+    if (rc) return rc;
+    const uint32_t gen = demand_generation(h, pd);
+    if (idx) {
+        CU(h, cudaMemcpyAsync(h->d_idx, idx, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+        h->stats.h2d_bytes += (size_t)n * 4;
+    }
+    const int block = 256;
+    int grid = (int)((n + block - 1) / block);
+    const int max_grid = h->num_sms * 8;
+    if (grid > max_grid) grid = max_grid;
+    if (want_plan)
+        k_assume<true><<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, feasible ? h->d_feas : nullptr,
+                                                     reason ? h->d_reason : nullptr, score ? h->d_score : nullptr,
+                                                     plan ? h->d_plan : nullptr, n_emitted ? h->d_nem : nullptr);
+    else
+        k_assume<false><<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, feasible ? h->d_feas : nullptr,
+                                                      reason ? h->d_reason : nullptr, score ? h->d_score : nullptr, nullptr, nullptr);
+    CU(h, cudaGetLastError());
+    if (feasible) CU(h, cudaMemcpyAsync(feasible, h->d_feas, n, cudaMemcpyDeviceToHost, h->stream));
+    if (reason) CU(h, cudaMemcpyAsync(reason, h->d_reason, n, cudaMemcpyDeviceToHost, h->stream));
+    if (score) CU(h, cudaMemcpyAsync(score, h->d_score, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (plan && n_containers > 0) CU(h, cudaMemcpyAsync(plan, h->d_plan, (size_t)n * n_containers * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (n_emitted) CU(h, cudaMemcpyAsync(n_emitted, h->d_nem, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    h->stats.kernel_launches++;
+    h->stats.node_evals += n;
+    h->stats.d2h_bytes += (feasible ? n : 0) + (reason ? n : 0) + (score ? (size_t)n * 4 : 0) +
+                          (plan ? (size_t)n * n_containers * 4 : 0) + (n_emitted ? (size_t)n * 4 : 0);
+    return NGS_OK;
+}
+
+int ngs_assume(ngs_dealer* h, const uint32_t* idx, uint32_t n, const int32_t* percent, int n_containers, int policy,
+               const ngs_load_ctx* load, uint8_t* feasible, int8_t* reason, int32_t* score, int32_t* plan, int32_t* n_emitted) {
+    return run_assume(h, MODE_ASSUME, idx, n, percent, n_containers, policy, load, feasible, reason, score, plan, n_emitted);
+}
+
+int ngs_score(ngs_dealer* h, const uint32_t* idx, uint32_t n, const int32_t* percent, int n_containers, int policy,
+              const ngs_load_ctx* load, int32_t* score) {
+    if (!score) return NGS_ERR_INVALID;
+    return run_assume(h, MODE_SCORE, idx, n, percent, n_containers, policy, load, nullptr, nullptr, score, nullptr, nullptr);
+}
+
+int ngs_bind(ngs_dealer* h, uint32_t idx, const int32_t* percent, int n_containers, int policy, const ngs_load_ctx* load,
+             int32_t* gpu_idx_out, int32_t* score_out) {
+    if (!h) return NGS_ERR_INVALID;
+    PodDemand pd;
+    LoadParams lp;
+    int rc = make_demand(h, percent, n_containers, policy, &pd);
+    if (rc) return rc;
+    rc = make_load(h, load, &lp);
+    if (rc) return rc;
+    CU(h, cudaSetDevice(h->device));
+    const uint32_t gen = demand_generation(h, pd);
+    k_bind<<<1, 32, 0, h->stream>>>(h->T, idx, pd, lp, gen, h->d_bind);
+    CU(h, cudaGetLastError());
+    CU(h, cudaMemcpyAsync(h->h_bind, h->d_bind, sizeof(BindResult), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    h->stats.kernel_launches++;
+    h->stats.node_evals++;
+    h->stats.d2h_bytes += sizeof(BindResult);
+    rc = h->h_bind->status;
+    if (rc) return fail(h, rc, "bind on node %u: %s", idx, ngs_strerror(rc));
+    for (int i = 0; i < n_containers; i++)
+        if (gpu_idx_out) gpu_idx_out[i] = h->h_bind->gpu_idx[i];
+    if (score_out) *score_out = h->h_bind->score;
+    h->stats.pods_scheduled++;
+    return NGS_OK;
+}
+
+int ngs_schedule_batch_dev(ngs_dealer* h, uint32_t n_pods, const int32_t* d_percent, const int32_t* d_n_containers, int max_c,
+                           const int32_t* d_policy, const ngs_load_ctx* load, uint64_t seed, uint64_t seq0, int32_t* d_node_out,
+                           int32_t* d_score_out, int32_t* d_gpu_idx_out) {
+    if (!h || !d_percent || !d_n_containers || !d_policy || !d_node_out || !d_score_out || !d_gpu_idx_out) return NGS_ERR_INVALID;
+    if (max_c < 1 || max_c > NGS_MAX_CONTAINERS) return fail(h, NGS_ERR_UNSUPPORTED, "max_c %d outside [1, NGS_MAX_CONTAINERS]", max_c);
+    if (n_pods > NGS_MAX_BATCH) return fail(h, NGS_ERR_UNSUPPORTED, "%u pods > NGS_MAX_BATCH", n_pods);
+    LoadParams lp;
+    int rc = make_load(h, load, &lp);
+    if (rc) return rc;
+    CU(h, cudaSetDevice(h->device));
+    rc = ensure_batch(h);
+    if (rc) return rc;
+    for (uint32_t p0 = 0; p0 < n_pods; p0 += BATCH_CHUNK) {
+        const uint32_t P = n_pods - p0 < BATCH_CHUNK ? n_pods - p0 : BATCH_CHUNK;
+        rc = launch_schedule(h, P, d_percent + (size_t)p0 * max_c, d_n_containers + p0, max_c, d_policy + p0, lp, seed + seq0 + p0,
+                             d_node_out + p0, d_score_out + p0, d_gpu_idx_out + (size_t)p0 * max_c);
+        if (rc) return rc;
+    }
+    return NGS_OK;
+}
+
+int ngs_schedule_batch(ngs_dealer* h, uint32_t n_pods, const int32_t* percent, const int32_t* n_containers, int max_c,
+                       const int32_t* policy, const ngs_load_ctx* load, uint64_t seed, uint64_t seq0, int32_t* node_out,
+                       int32_t* score_out, int32_t* gpu_idx_out) {
+    if (!h || !percent || !n_containers || !policy || !node_out || !score_out || !gpu_idx_out) return NGS_ERR_INVALID;
+    if (max_c < 1 || max_c > NGS_MAX_CONTAINERS) return fail(h, NGS_ERR_UNSUPPORTED, "max_c %d outside [1, NGS_MAX_CONTAINERS]", max_c);
+    if (n_pods > NGS_MAX_BATCH) return fail(h, NGS_ERR_UNSUPPORTED, "%u pods > NGS_MAX_BATCH", n_pods);
+    for (uint32_t p = 0; p < n_pods; p++) {
+        if (n_containers[p] < 0 || n_containers[p] > max_c) return fail(h, NGS_ERR_INVALID, "pod %u: %d containers", p, n_containers[p]);
+        if (policy[p] < 0 || policy[p] > NGS_POLICY_RANDOM) return fail(h, NGS_ERR_INVALID, "pod %u: policy %d", p, policy[p]);
+        for (int k = 0; k < n_containers[p]; k++) {
+            const int32_t v = percent[(size_t)p * max_c + k];
+            if (v < 0 || v > NGS_MAX_FREE) return fail(h, NGS_ERR_INVALID, "pod %u: percent[%d]=%d out of range", p, k, v);
+        }
+    }
+    LoadParams lp;
+    int rc = make_load(h, load, &lp);
+    if (rc) return rc;
+    CU(h, cudaSetDevice(h->device));
+    rc = ensure_batch(h);
+    if (rc) return rc;
+    for (uint32_t p0 = 0; p0 < n_pods; p0 += BATCH_CHUNK) {
+        const uint32_t P = n_pods - p0 < BATCH_CHUNK ? n_pods - p0 : BATCH_CHUNK;
+        // pinned staging: percent [P][max_c] | ncont [P] | policy [P]
+        int32_t* hin = h->h_pod_in;
+        memcpy(hin, percent + (size_t)p0 * max_c, (size_t)P * max_c * 4);
+        memcpy(hin + (size_t)P * max_c, n_containers + p0, (size_t)P * 4);
+        memcpy(hin + (size_t)P * max_c + P, policy + p0, (size_t)P * 4);
+        const size_t in_bytes = ((size_t)P * max_c + 2 * (size_t)P) * 4;
+        CU(h, cudaMemcpyAsync(h->d_pod_in, hin, in_bytes, cudaMemcpyHostToDevice, h->stream));
+        int32_t* d_node = h->d_pod_out;
+        int32_t* d_score = d_node + P;
+        int32_t* d_gidx = d_score + P;
+        rc = launch_schedule(h, P, h->d_pod_in, h->d_pod_in + (size_t)P * max_c, max_c, h->d_pod_in + (size_t)P * max_c + P, lp,
+                             seed + seq0 + p0, d_node, d_score, d_gidx);
+        if (rc) return rc;
+        const size_t out_bytes = (2 * (size_t)P + (size_t)P * max_c) * 4;
+        CU(h, cudaMemcpyAsync(h->h_pod_out, h->d_pod_out, out_bytes, cudaMemcpyDeviceToHost, h->stream));
+        CU(h, cudaMemcpyAsync(h->h_err, h->d_err, 4, cudaMemcpyDeviceToHost, h->stream));
+        CU(h, cudaStreamSynchronize(h->stream));
+        rc = check_dev_err(h);
+        if (rc) return rc;
+        memcpy(node_out + p0, h->h_pod_out, (size_t)P * 4);
+        memcpy(score_out + p0, h->h_pod_out + P, (size_t)P * 4);
+        memcpy(gpu_idx_out + (size_t)p0 * max_c, h->h_pod_out + 2 * (size_t)P, (size_t)P * max_c * 4);
+        h->stats.h2d_bytes += in_bytes;
+        h->stats.d2h_bytes += out_bytes;
+    }
+    return NGS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,315 @@
+// ngs_device.cuh — device-side building blocks of the dealer kernels (sm_100a).
+//
+// Everything here is integer / fp64-scalar work on one node row held in registers; the
+// kernels in ngs_dealer.cu decide how rows reach the registers (int4 global loads for the
+// per-verb scans, shared-memory resident rows for the persistent batch kernel).
+//
+// Reference semantics (paths relative to /root/reference/pkg/dealer/):
+//   GPUs.Choose            allocate.go:92-100   Rate on the pre-placement state, then Choose
+//   Binpack/Spread.Choose  rater.go:74-110,127-163
+//   SampleRater.Choose     rater.go:28-50 (scratch copy; SURVEY §8 a9')
+//   Binpack/Spread.Rate    rater.go:59-70,113-123
+//   GPUResource.LoadUsage  allocate.go:173-195 (+ nodeusage.go:82-111, stats.go:30-55)
+//   sort.Sort              Go 1.16 standard library (go.mod:3): for <= 12 elements one gap-6
+//                          shell pass, then insertion sort (stable).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/ngs_dealer.h"
+
+namespace ngs {
+
+// ---------------------------------------------------------------------------------------------
+// Packed GPU cell.  One 32-bit word per cell so that Go's "re-sort, then first fit" becomes
+// min/max compare-exchanges on plain unsigned integers:
+//   [31:9]  key + 128, key = free + 50*RemainLoad        (SortableGPUs.Less, allocate.go:247)
+//   [8:6]   position in the current arrangement           (makes equal keys keep their order)
+//   [5:3]   RemainLoad + 2                                (RemainLoad in [-2, 2])
+//   [2:0]   original GPU index                            (GPUResourceWithIndex.index)
+// Cells beyond the node's GPU count are PAD (all ones): they sort last and stay at
+// positions >= G through the gap pass, so a position mask excludes them from every fit test.
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t W_KEY_SHIFT = 9;
+constexpr uint32_t W_POS_MASK = 7u << 6;
+constexpr uint32_t W_PAD = 0xFFFFFFFFu;
+constexpr int KEY_BIAS = 128;
+constexpr uint32_t RL0_META = 0x492492u;  // eight 3-bit RemainLoad codes, all == 2 (RemainLoad 0)
+
+__device__ __forceinline__ uint32_t pack_cell(int free, int rlc, int g) {
+    // 50*(rlc-2) + 128 == 50*rlc + 28
+    return ((uint32_t)(free + 50 * rlc + 28) << W_KEY_SHIFT) | ((uint32_t)rlc << 3) | (uint32_t)(g * 65);
+}
+__device__ __forceinline__ int cell_free(uint32_t w) { return (int)(w >> W_KEY_SHIFT) - 28 - 50 * (int)((w >> 3) & 7u); }
+
+// Sorted demand of one pod, staged in shared memory (BASELINE north_star: "staging each pod's
+// demand vector in shared memory").  d[] is the processing order of rater.go:82 (largest
+// first) restricted to non-zero percents; order[k] is the container the k-th processed entry
+// belongs to (zeros, which emit NotNeedGPU, follow the non-zeros).
+struct SortedDemand {
+    int32_t C;       // containers
+    int32_t nz;      // containers with percent != 0
+    int32_t policy;  // NGS_POLICY_*
+    int32_t pad_;
+    int32_t raw[NGS_MAX_CONTAINERS];    // container order (SampleRater walks this)
+    int32_t d[NGS_MAX_CONTAINERS];      // processing order, non-zero entries first
+    int32_t order[NGS_MAX_CONTAINERS];  // container index of each processed entry
+};
+static_assert(sizeof(SortedDemand) == 160, "SortedDemand layout");
+
+// By-value pod demand for the per-verb kernels.
+struct PodDemand {
+    int32_t n;
+    int32_t policy;
+    int32_t percent[NGS_MAX_CONTAINERS];
+};
+
+// isLoadSchedule context resolved on the host: a timestamp is inside the update window
+// (stats.go:48-53: now.Before(t + activeDuration)) iff ts_sec >= min_ts[e].
+struct LoadParams {
+    int32_t enabled;  // isLoadSchedule
+    int32_t n_periods;
+    int32_t metric[NGS_MAX_PERIODS];
+    uint32_t min_ts[NGS_MAX_PERIODS];
+    uint32_t never[NGS_MAX_PERIODS];  // window lies beyond the representable range: nothing valid
+};
+
+// sort.Sort(sortableDemand) (rater.go:81,134) with the Go 1.16 small-slice rule, then the
+// traversal order of rater.go:82.  Serial, executed by one thread per block.
+__device__ inline void sort_demand(const int32_t* percent, int C, int policy, SortedDemand* out) {
+    int key[NGS_MAX_CONTAINERS], idx[NGS_MAX_CONTAINERS];
+    for (int i = 0; i < NGS_MAX_CONTAINERS; i++) {
+        key[i] = i < C ? percent[i] : 0;
+        idx[i] = i;
+    }
+    for (int i = 6; i < C; i++)  // gap-6 shell pass
+        if (key[i] < key[i - 6]) {
+            int t = key[i]; key[i] = key[i - 6]; key[i - 6] = t;
+            t = idx[i]; idx[i] = idx[i - 6]; idx[i - 6] = t;
+        }
+    for (int i = 1; i < C; i++)  // insertionSort
+        for (int j = i; j > 0 && key[j] < key[j - 1]; j--) {
+            int t = key[j]; key[j] = key[j - 1]; key[j - 1] = t;
+            t = idx[j]; idx[j] = idx[j - 1]; idx[j - 1] = t;
+        }
+    out->C = C;
+    out->policy = policy;
+    out->pad_ = 0;
+    int nz = 0;
+    for (int k = 0; k < NGS_MAX_CONTAINERS; k++) {
+        int j = C - 1 - k;  // rater.go:82: j runs from the largest demand down
+        out->raw[k] = k < C ? percent[k] : 0;
+        out->d[k] = j >= 0 ? key[j] : 0;
+        out->order[k] = j >= 0 ? idx[j] : 0;
+        if (j >= 0 && key[j] != 0) nz++;
+    }
+    out->nz = nz;  // percents are >= 0 (checked at the boundary), so non-zeros come first
+}
+
+__device__ __forceinline__ void cex(uint32_t& a, uint32_t& b) {
+    uint32_t lo = min(a, b), hi = max(a, b);
+    a = lo;
+    b = hi;
+}
+// gap-6 step of Go 1.16 quickSort: if Less(i, i-6) then Swap — compares keys only
+__device__ __forceinline__ void gap_swap(uint32_t& hi_pos, uint32_t& lo_pos) {
+    bool sw = (hi_pos >> W_KEY_SHIFT) < (lo_pos >> W_KEY_SHIFT);
+    uint32_t a = sw ? hi_pos : lo_pos, b = sw ? lo_pos : hi_pos;
+    lo_pos = a;
+    hi_pos = b;
+}
+
+// sort.Sort(sortableGpus) (rater.go:87,140) on the current arrangement: gap-6 pass, stamp
+// positions, then a 19-comparator network.  Positions make all words distinct, so the network
+// reproduces the (stable) insertion sort exactly.
+__device__ __forceinline__ void go_sort8(uint32_t (&w)[8]) {
+    gap_swap(w[6], w[0]);
+    gap_swap(w[7], w[1]);
+#pragma unroll
+    for (int i = 0; i < 8; i++) w[i] = (w[i] & ~W_POS_MASK) | ((uint32_t)i << 6);
+    cex(w[0], w[2]); cex(w[1], w[3]); cex(w[4], w[6]); cex(w[5], w[7]);
+    cex(w[0], w[4]); cex(w[1], w[5]); cex(w[2], w[6]); cex(w[3], w[7]);
+    cex(w[0], w[1]); cex(w[2], w[3]); cex(w[4], w[5]); cex(w[6], w[7]);
+    cex(w[2], w[4]); cex(w[3], w[5]);
+    cex(w[1], w[4]); cex(w[3], w[6]);
+    cex(w[1], w[2]); cex(w[3], w[4]); cex(w[5], w[6]);
+}
+
+// bit i set iff the cell at position i can take `d` (GPUResource.CanAllocate, allocate.go:159)
+__device__ __forceinline__ uint32_t fit_mask(const uint32_t (&w)[8], int d, uint32_t gmask, bool rl0) {
+    uint32_t m = 0;
+    if (rl0) {
+        const uint32_t thr = (uint32_t)(d + KEY_BIAS) << W_KEY_SHIFT;
+#pragma unroll
+        for (int i = 0; i < 8; i++) m |= (uint32_t)(w[i] >= thr) << i;
+    } else {
+#pragma unroll
+        for (int i = 0; i < 8; i++) m |= (uint32_t)(cell_free(w[i]) >= d) << i;
+    }
+    return m & gmask;
+}
+
+// Binpack.Choose / Spread.Choose on the packed row.  Returns feasibility (rater.go:98-100).
+// PLAN: `emit` receives the `indexes` slice in emission order, 4 bits per entry (0xF = -1),
+// and n_emit its length; the greedy loop then runs to the end even after a miss, exactly as
+// the reference does.  Without PLAN only feasibility is wanted: a miss returns at once and the
+// last non-zero container needs no sort (any cell that fits will do).
+template <bool PLAN>
+__device__ __forceinline__ bool choose_sorted(uint32_t (&w)[8], int G, bool spread, bool rl0, const SortedDemand* dem,
+                                              uint64_t* emit, int* n_emit) {
+    const uint32_t gmask = (1u << G) - 1u;
+    const int nz = dem->nz;
+    uint64_t em = 0;
+    int ne = 0;
+    bool ok = true;
+    for (int k = 0; k < nz; k++) {
+        const int d = dem->d[k];
+        if (!PLAN && k == nz - 1) return fit_mask(w, d, gmask, rl0) != 0;
+        go_sort8(w);
+        const uint32_t m = fit_mask(w, d, gmask, rl0);
+        if (m == 0) {
+            if (!PLAN) return false;
+            ok = false;
+            continue;  // rater.go:88-95: nothing appended, later containers still placed
+        }
+        const int sel = spread ? 31 - __clz(m) : __ffs(m) - 1;  // rater.go:141 / :88
+        const uint32_t dec = (uint32_t)d << W_KEY_SHIFT;
+        uint32_t chosen = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const bool hit = sel == i;
+            if (PLAN && hit) chosen = w[i] & 7u;
+            w[i] -= hit ? dec : 0u;
+        }
+        if (PLAN) {
+            em |= (uint64_t)chosen << (4 * ne);
+            ne++;
+        }
+    }
+    if (PLAN) {
+        for (int k = nz; k < dem->C; k++) {  // zero-percent containers: NotNeedGPU (rater.go:83-86)
+            em |= (uint64_t)0xF << (4 * ne);
+            ne++;
+        }
+        *emit = em;
+        *n_emit = ne;
+    }
+    return ok;
+}
+
+// SampleRater.Choose: containers in pod order, GPUs in index order, no sorting.
+template <bool PLAN>
+__device__ __forceinline__ bool choose_sample(int (&f)[8], int G, const SortedDemand* dem, uint64_t* emit, int* n_emit) {
+    uint64_t em = 0;
+    int ne = 0;
+    bool ok = true;
+    for (int k = 0; k < dem->C; k++) {
+        const int d = dem->raw[k];
+        if (d == 0) {
+            if (PLAN) { em |= (uint64_t)0xF << (4 * ne); ne++; }
+            continue;
+        }
+        uint32_t m = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) m |= (uint32_t)(i < G && f[i] >= d) << i;
+        if (m == 0) {
+            if (!PLAN) return false;
+            ok = false;
+            continue;
+        }
+        const int sel = __ffs(m) - 1;
+#pragma unroll
+        for (int i = 0; i < 8; i++) f[i] -= (sel == i) ? d : 0;
+        if (PLAN) { em |= (uint64_t)sel << (4 * ne); ne++; }
+    }
+    if (PLAN) { *emit = em; *n_emit = ne; }
+    return ok;
+}
+
+// Un-permute the emission list into container order (rater.go:102-105) or expose the partial
+// list as the error text of rater.go:99 does.  out has dem->C entries.
+__device__ inline void write_plan(int32_t* out, const SortedDemand* dem, bool sorted_policy, bool ok, uint64_t emit, int n_emit) {
+    const int C = dem->C;
+    if (ok) {
+        for (int k = 0; k < C; k++) {
+            int e = (int)((emit >> (4 * k)) & 0xF);
+            int v = e == 0xF ? NGS_NOT_NEED_GPU : e;
+            out[sorted_policy ? dem->order[k] : k] = v;
+        }
+    } else {
+        for (int k = 0; k < C; k++) {
+            int e = (int)((emit >> (4 * k)) & 0xF);
+            out[k] = k < n_emit ? (e == 0xF ? NGS_NOT_NEED_GPU : e) : INT32_MIN;
+        }
+    }
+}
+
+// Binpack.Rate (rater.go:59-70) with GPUs.Usage (allocate.go:164-171): the fp64 division and
+// multiplication are done in IEEE round-to-nearest with explicit intrinsics (no contraction),
+// then truncated toward zero like Go's int(float64).
+__device__ __forceinline__ int rate_binpack(const int (&f)[8], int G, int load_int) {
+    int used = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) used += i < G ? 100 - f[i] : 0;
+    const double usage = __ddiv_rn((double)used, (double)(100 * G));
+    return __double2int_rz(__dmul_rn(usage, 100.0)) + load_int * 50 - G;
+}
+// Spread.Rate (rater.go:113-123) with PercentAvailableAndFreeGpuCount (allocate.go:205-213)
+__device__ __forceinline__ int rate_spread(const int (&f)[8], int G, int load_int) {
+    int avail = 0, cnt = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        avail += i < G ? f[i] : 0;
+        cnt += (i < G && f[i] == 100) ? 1 : 0;
+    }
+    return 100 * cnt + avail / 10 - G - load_int;
+}
+__device__ __forceinline__ int rate_policy(int policy, const int (&f)[8], int G, int load_int) {
+    if (policy == NGS_POLICY_BINPACK) return rate_binpack(f, G, load_int);
+    if (policy == NGS_POLICY_SPREAD) return rate_spread(f, G, load_int);
+    return 100;  // SampleRater.Rate -> ScoreMax (rater.go:24-26)
+}
+
+// GPUResource.LoadUsage for the 8 cells of one row.  tenths[m] holds ceil(10*usage) per card
+// (255 = the reference would skip this entry: node or card missing, unparsable or stale
+// timestamp, unparsable or out-of-range value), ts[m] the update time in unix seconds.
+// Per card the SyncPeriod entries are summed in order, the node sum runs in GPU-index order
+// (rater.go:63-65), both in fp64 exactly as the reference does.  rlc[] = RemainLoad + 2.
+__device__ __forceinline__ void load_usage_row(const uint8_t (&tenths)[2][8], const uint32_t (&ts)[2][8], const LoadParams& lp,
+                                               int G, int (&rlc)[8], int* load_int) {
+    double lu = 0.0;
+#pragma unroll
+    for (int g = 0; g < 8; g++) {
+        double u = 0.0;
+        for (int e = 0; e < lp.n_periods; e++) {
+            const int m = lp.metric[e];
+            const uint32_t t10 = m ? tenths[1][g] : tenths[0][g];
+            const uint32_t t = m ? ts[1][g] : ts[0][g];
+            if (t10 == 255u || lp.never[e] || t < lp.min_ts[e]) continue;
+            u = __dadd_rn(u, __ddiv_rn((double)t10, 10.0));  // ceil(10*u)/10, allocate.go:190-191
+        }
+        const int rl = 2 - __double2int_rz(u);  // allocate.go:193 (LoadTotal = 2)
+        rlc[g] = g < G ? rl + 2 : 2;
+        if (g < G) lu = __dadd_rn(lu, u);
+    }
+    *load_int = __double2int_rz(lu) / G;  // rater.go:68,121
+}
+
+__device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ULL;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
+    return x ^ (x >> 31);
+}
+
+// arg-max key: highest score wins, ties go to the lowest global node index.
+constexpr uint64_t KEY_VALID = 1ULL << 63;
+constexpr uint64_t KEY_FEASIBLE = 1ULL << 62;
+constexpr int SCORE_BIAS = 1 << 29;
+__device__ __forceinline__ uint64_t make_key(int score, uint32_t global_node) {
+    return KEY_FEASIBLE | ((uint64_t)(uint32_t)(score + SCORE_BIAS) << 32) | (uint64_t)(0xFFFFFFFFu - global_node);
+}
+__device__ __forceinline__ uint32_t key_node(uint64_t k) { return 0xFFFFFFFFu - (uint32_t)k; }
+__device__ __forceinline__ int key_score(uint64_t k) { return (int)((k >> 32) & 0x3FFFFFFFu) - SCORE_BIAS; }
+
+}  // namespace ngs

@@ -1,0 +1,541 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the CPU oracle on the same
+seeded inputs.  Everything here is integer / index work: the bar is bit-exact."""
+import numpy as np
+import pytest
+
+import oracle as o
+from tests.parity_util import (NOW_NS, NOW_S, assert_same_snapshot, fill_load_tables, load_ctx_pair, make_pair)
+
+pytestmark = pytest.mark.gpu
+
+POL = {"binpack": 0, "spread": 1, "random": 2}
+
+
+@pytest.fixture(scope="module")
+def ngs(built):
+    import nano_gpu_scheduler_b200 as m
+
+    return m
+
+
+def single_node(ngs, free, rl=None):
+    G = len(free)
+    d = ngs.GpuDealer(1, device=0)
+    row = np.zeros((1, 8), dtype=np.int32)
+    row[0, :G] = free
+    rlrow = None
+    if rl is not None:
+        rlrow = np.zeros((1, 8), dtype=np.int8)
+        rlrow[0, :G] = rl
+    d.snapshot_load(np.array([G], dtype=np.uint8), row, rlrow)
+    return d
+
+
+# ---- the reference's own known-answer tests, through the GPU ----------------------------------
+@pytest.mark.parametrize("policy", ["binpack", "spread"])
+def test_choose_kats_on_gpu(ngs, kats, policy):  # rater_test.go:133-401
+    for c in kats[policy + "_choose"]["cases"]:
+        with single_node(ngs, c["free"]) as d:
+            r = d.assume(c["demand"], POL[policy], want_plan=True)
+            assert bool(r["feasible"][0]) == (not c["expect_failed"])
+            if not c["expect_failed"]:
+                assert r["plan"][0].tolist() == c["expected"]
+                assert r["reason"][0] == ngs.REASON_OK
+            else:
+                assert r["reason"][0] == ngs.REASON_INFEASIBLE and r["score"][0] == 0
+
+
+def test_rate_kats_on_gpu(ngs, kats, derived):  # rater_test.go:9-131
+    def score(policy, free):
+        with single_node(ngs, free) as d:
+            return int(d.assume([0], POL[policy])["score"][0])
+
+    for c in kats["binpack_rate"]["cases"]:
+        assert (score("binpack", c["gpus1"]) < score("binpack", c["gpus2"])) == c["first_lower"]
+    for c in kats["spread_rate"]["cases"]:
+        assert (score("spread", c["gpus1"]) > score("spread", c["gpus2"])) == c["first_preferred"]
+    for v in derived["rates"]:
+        assert score(v["policy"], v["free"]) == v["score"], v
+
+
+def test_sample_choose_kats_on_gpu(ngs, kats):  # allocate_test.go:160-190
+    for c in kats["sample_choose"]["cases"]:
+        with single_node(ngs, c["free"]) as d:
+            r = d.assume(c["demand"], POL["random"])
+            assert bool(r["feasible"][0]) == c["success"]
+            assert r["score"][0] == (100 if c["success"] else 0)
+
+
+def test_gpu_resource_kats_on_gpu(ngs, kats):  # allocate_test.go:16-86
+    g = kats["gpu_resource"]
+    for c in g["sub"] + g["sub_if_available"]:
+        with single_node(ngs, [c["origin"]]) as d:
+            rc = d.node_apply(0, [0], [c["target"]], +1)
+            assert (rc == 0) == (c["origin"] >= c["target"])
+            assert d.snapshot_read()[1][0, 0] == c["expect"]
+    for c in g["add"]:
+        with single_node(ngs, [c["origin"]]) as d:
+            assert d.node_apply(0, [0], [c["target"]], -1) == 0
+            assert d.snapshot_read()[1][0, 0] == c["expect"]
+
+
+def test_go116_tie_order_on_gpu(ngs, derived):
+    """the GPU follows the pinned Go 1.16 sort.Sort (gap-6 pass), not the >= 1.19 rule"""
+    for v in derived["sort_rule_choose"]:
+        with single_node(ngs, v["free"]) as d:
+            r = d.assume(v["demand"], POL[v["policy"]], want_plan=True)
+            assert r["feasible"][0] == 1 and r["plan"][0].tolist() == v["go116"]
+
+
+def test_fp64_truncation_points_on_gpu(ngs):
+    """every used total 0..800 of an 8-GPU node: Binpack.Rate must truncate like Go's fp64"""
+    n = 801
+    free = np.full((n, 8), 100, dtype=np.int32)
+    for used in range(n):
+        left = used
+        for g in range(8):
+            take = min(100, left)
+            free[used, g] -= take
+            left -= take
+    with ngs.GpuDealer(n, device=0) as d:
+        d.snapshot_load(np.full(n, 8, dtype=np.uint8), free)
+        sc = d.assume([0], POL["binpack"])["score"]
+    want = np.array([int(float(u) / 800.0 * 100) - 8 for u in range(n)])
+    assert np.array_equal(sc, want)
+    assert sc[232] == 20 and sc[456] == 48 and sc[464] == 49
+
+
+# ---- differential tests on random snapshots -----------------------------------------------------
+@pytest.mark.parametrize("policy", ["binpack", "spread", "random"])
+@pytest.mark.parametrize("hetero", [False, True])
+def test_assume_random_snapshots(ngs, policy, hetero):
+    n = 4096
+    oc, d, _, _ = make_pair(ngs, n, 0.6, 0xA11CE + hetero, hetero=hetero)
+    rng = np.random.default_rng(11)
+    with d:
+        for trial in range(24):
+            C = int(rng.integers(1, 7))
+            demand = (rng.integers(0, 13, C) * 5).astype(np.int32)
+            if trial == 0:
+                demand = np.array([0], dtype=np.int32)  # a pod that needs no GPU fits everywhere
+            a = d.assume(demand, POL[policy], want_plan=True)
+            b = oc.assume(demand, POL[policy], want_plan=True)
+            for k in ("feasible", "reason", "score", "n_emitted", "plan"):
+                assert np.array_equal(a[k], b[k]), (policy, trial, k, demand)
+            # without the plan outputs the fast feasibility-only path runs: same answers
+            a2 = d.assume(demand, POL[policy])
+            assert np.array_equal(a2["feasible"], b["feasible"]) and np.array_equal(a2["score"], b["score"])
+
+
+def test_assume_remain_load_in_sort_key(ngs):
+    """non-load evaluation with a persisted RemainLoad: key = free + 50*rl (allocate.go:247)"""
+    n = 2048
+    rng = np.random.default_rng(5)
+    free = (rng.integers(0, 11, (n, 8)) * 10).astype(np.int32)
+    rl = rng.integers(0, 3, (n, 8)).astype(np.int8)
+    oc = o.OracleCluster(n)
+    for i in range(n):
+        oc.node_set(i, free[i].astype(np.int64), rl[i].astype(np.int64))
+    with ngs.GpuDealer(n, device=0) as d:
+        d.snapshot_load(np.full(n, 8, dtype=np.uint8), free, rl)
+        for trial in range(16):
+            C = int(rng.integers(1, 5))
+            demand = (rng.integers(1, 9, C) * 10).astype(np.int32)
+            for pol in (0, 1):
+                a = d.assume(demand, pol, want_plan=True)
+                b = oc.assume(demand, pol, want_plan=True)
+                for k in ("feasible", "score", "n_emitted", "plan"):
+                    assert np.array_equal(a[k], b[k]), (pol, trial, k)
+
+
+@pytest.mark.parametrize("policy", ["binpack", "spread"])
+def test_assume_load_mode(ngs, policy):
+    """isLoadSchedule=true: LoadUsage sums (fp64), RemainLoad write-back, stale / absent entries"""
+    n = 3000
+    oc, d, _, _ = make_pair(ngs, n, 0.5, 0x10AD)
+    with d:
+        fill_load_tables(oc, d, n, 0x10AD, stale_frac=0.1, absent_frac=0.05)
+        gl, ol = load_ctx_pair(ngs)
+        rng = np.random.default_rng(9)
+        for trial in range(12):
+            C = int(rng.integers(1, 5))
+            demand = (rng.integers(0, 13, C) * 5).astype(np.int32)
+            a = d.assume(demand, POL[policy], load=gl, want_plan=True)
+            b = oc.assume(demand, POL[policy], load=ol, want_plan=True)
+            for k in ("feasible", "score", "n_emitted", "plan"):
+                assert np.array_equal(a[k], b[k]), (policy, trial, k)
+            assert_same_snapshot(oc, d)  # RemainLoad side effect (allocate.go:193)
+        # the window edge: one nanosecond decides (stats.go:48-53)
+        ts = NOW_S - 100
+        for i in range(8):
+            for m in (0, 1):
+                oc.load_update(i, m, 0, 0.95, ts)
+                d.load_update(i, m, 0, 0.95, ts)
+        for delta in (-1, 0, 1):
+            win = (NOW_NS - ts * 10**9) + delta
+            gl2, ol2 = load_ctx_pair(ngs, periods=[(0, win), (1, win)])
+            a = d.assume([30], POL[policy], load=gl2, idx=np.arange(8, dtype=np.uint32))
+            b = oc.assume([30], POL[policy], load=ol2, idx=np.arange(8, dtype=np.uint32))
+            assert np.array_equal(a["score"], b["score"]) and np.array_equal(a["feasible"], b["feasible"])
+            assert_same_snapshot(oc, d)
+
+
+def test_load_usage_value_edge_cases(ngs):
+    """values the reference skips (nodeusage.go:99-110) and the ceil(10u)/10 rounding"""
+    vals = [0.0, 0.00001, 0.1, 0.10001, 0.3, 0.7, 0.70001, 0.99999, 1.0, 1.00001, -0.1, 0.55]
+    n = len(vals)
+    oc, d, _, _ = make_pair(ngs, n, 0.0, 1)
+    with d:
+        for i, v in enumerate(vals):
+            for m in (0, 1):
+                oc.load_add_node(i, m)
+                for g in range(8):
+                    vv = v if g % 2 == 0 else 0.2
+                    oc.load_update(i, m, g, vv, NOW_S - 1, value_ok=(g != 3), ts_ok=(g != 5))
+                    d.load_update(i, m, g, vv, NOW_S - 1, value_ok=(g != 3), ts_ok=(g != 5))
+        gl, ol = load_ctx_pair(ngs)
+        for pol in (0, 1):
+            a = d.assume([10], pol, load=gl, want_plan=True)
+            b = oc.assume([10], pol, load=ol, want_plan=True)
+            assert np.array_equal(a["score"], b["score"]) and np.array_equal(a["plan"], b["plan"])
+            assert_same_snapshot(oc, d)
+
+
+def test_candidate_lists_and_unknown_nodes(ngs):
+    n = 1000
+    oc, d, gcount, free = make_pair(ngs, n, 0.5, 77)
+    with d:
+        # rows 10..19 are not known to the dealer
+        gcount2 = gcount.copy()
+        gcount2[10:20] = 0
+        d.snapshot_load(gcount2, free)
+        for i in range(10, 20):
+            oc.node_upsert(i, 0)
+        idx = np.array([5, 12, 999, 1000, 4_000_000_000, 5, 0, 19, 20], dtype=np.uint32)
+        a = d.assume([30, 20], 0, idx=idx, want_plan=True)
+        b = oc.assume([30, 20], 0, idx=idx, want_plan=True)
+        for k in ("feasible", "reason", "score", "plan", "n_emitted"):
+            assert np.array_equal(a[k], b[k]), k
+        assert a["reason"][1] == ngs.REASON_UNKNOWN_NODE and a["reason"][3] == ngs.REASON_UNKNOWN_NODE
+        # empty candidate list
+        e = d.assume([30], 0, idx=np.zeros(0, dtype=np.uint32))
+        assert len(e["feasible"]) == 0
+
+
+def test_boundary_rejects_bad_input(ngs):
+    with ngs.GpuDealer(8, device=0) as d:
+        d.node_upsert(0, 8)
+        with pytest.raises(ngs.NgsError) as e:
+            d.assume([-5], 0)
+        assert e.value.status == ngs.ERR_INVALID
+        with pytest.raises(ngs.NgsError) as e:
+            d.assume([10] * 13, 0)
+        assert e.value.status == ngs.ERR_UNSUPPORTED
+        with pytest.raises(ngs.NgsError) as e:
+            d.node_upsert(1, 9)
+        assert e.value.status == ngs.ERR_UNSUPPORTED
+        with pytest.raises(ngs.NgsError) as e:
+            d.node_upsert(8, 8)
+        assert e.value.status == ngs.ERR_UNKNOWN_NODE
+        with pytest.raises(ngs.NgsError):
+            d.assume([10], 7)
+        # twelve containers (the insertion-sort regime limit) are fine
+        r = d.assume([5] * 12, 0, want_plan=True)
+        assert r["feasible"][0] == 1
+
+
+def test_twelve_container_demand_sort(ngs):
+    """demands of 7..12 containers exercise the gap-6 pass of the *demand* sort (rater.go:81)"""
+    n = 512
+    oc, d, _, _ = make_pair(ngs, n, 0.3, 0xD3)
+    rng = np.random.default_rng(12)
+    with d:
+        for C in (7, 8, 9, 12):
+            for _ in range(6):
+                demand = (rng.integers(0, 4, C) * 10).astype(np.int32)
+                for pol in (0, 1, 2):
+                    a = d.assume(demand, pol, want_plan=True)
+                    b = oc.assume(demand, pol, want_plan=True)
+                    for k in ("feasible", "score", "plan", "n_emitted"):
+                        assert np.array_equal(a[k], b[k]), (C, pol, k)
+
+
+# ---- sequences: assume -> score -> bind -> release ---------------------------------------------
+def test_bind_release_sequences(ngs):
+    n = 300
+    oc, d, _, _ = make_pair(ngs, n, 0.4, 0x5E0)
+    rng = np.random.default_rng(21)
+    live = []
+    with d:
+        for step in range(400):
+            pol = int(rng.integers(0, 3))
+            C = int(rng.integers(1, 4))
+            demand = (rng.integers(0, 11, C) * 5).astype(np.int32)
+            node = int(rng.integers(0, n))
+            if rng.random() < 0.6 or not live:
+                rc, gi, sc = d.bind(node, demand, pol)
+                orc, ogi, osc = oc.bind(node, demand, pol)
+                assert (rc == 0) == (orc == 0), step
+                if rc == 0:
+                    assert np.array_equal(gi, ogi) and sc == osc
+                    live.append((node, demand, gi))
+                else:
+                    assert rc == ngs.ERR_INFEASIBLE
+            else:
+                node, demand, gi = live.pop(int(rng.integers(0, len(live))))
+                assert d.node_apply(node, gi, demand, -1) == 0
+                assert oc.node_apply(node, gi, demand, -1) == 0
+            if step % 50 == 0:
+                assert_same_snapshot(oc, d)
+        assert_same_snapshot(oc, d)
+
+
+def test_apply_error_paths(ngs):
+    with single_node(ngs, [50, 20]) as d:
+        oc = o.OracleCluster(1)
+        oc.node_set(0, [50, 20])
+        # second container does not fit: nothing is applied (all-or-nothing)
+        assert d.node_apply(0, [0, 1], [30, 30], +1) == ngs.ERR_APPLY
+        assert oc.node_apply(0, [0, 1], [30, 30], +1) != 0
+        assert d.snapshot_read()[1][0, :2].tolist() == [50, 20] == oc.node_get(0)[1].tolist()
+        # -1 entries are skipped (allocate.go:105-107)
+        assert d.node_apply(0, [-1, 0], [70, 30], +1) == 0 and oc.node_apply(0, [-1, 0], [70, 30], +1) == 0
+        # release with an index >= G: earlier containers stay released (allocate.go:120-131)
+        assert d.node_apply(0, [1, 5], [10, 10], -1) == ngs.ERR_APPLY
+        assert oc.node_apply(0, [1, 5], [10, 10], -1) != 0
+        assert d.snapshot_read()[1][0, :2].tolist() == oc.node_get(0)[1].tolist() == [20, 30]
+        # two containers on the same GPU are checked cumulatively
+        assert d.node_apply(0, [1, 1], [20, 20], +1) == ngs.ERR_APPLY
+        assert d.node_apply(0, [1, 1], [20, 10], +1) == 0
+        assert d.node_apply(3, [0], [1], +1) == ngs.ERR_UNKNOWN_NODE
+
+
+def test_score_uses_plan_cache(ngs):
+    """NodeInfo.Score returns the Plan.Score cached by the filter pass (node.go:59-68) until the
+    node changes; a different demand or a changed node is evaluated afresh."""
+    n = 64
+    oc, d, _, _ = make_pair(ngs, n, 0.5, 0xCAC4E)
+    with d:
+        fill_load_tables(oc, d, n, 3, stale_frac=0.0, absent_frac=0.0)
+        gl, ol = load_ctx_pair(ngs)
+        demand = [30, 20]
+        a = d.assume(demand, 0, load=gl)
+        # usage tables move on after the filter pass; the cached score must not
+        for i in range(n):
+            d.load_update(i, 0, 0, 1.0, NOW_S)
+            d.load_update(i, 1, 0, 1.0, NOW_S)
+        s_cached = d.score(demand, 0, load=gl)
+        assert np.array_equal(s_cached, a["score"])
+        # a node that changed is re-evaluated (cleanPlan, node.go:82,87,92)
+        feas = np.flatnonzero(a["feasible"])
+        target = int(feas[0])
+        rc, gi, sc = d.bind(target, demand, 0, load=gl)
+        assert rc == 0 and sc == a["score"][target]  # bind reuses the cached plan and score
+        s2 = d.score(demand, 0, load=gl)
+        same = np.ones(n, dtype=bool)
+        same[target] = False
+        assert np.array_equal(s2[same], a["score"][same])
+        fresh = d.assume(demand, 0, load=gl, idx=np.array([target], dtype=np.uint32))
+        assert s2[target] == fresh["score"][0]
+        # a new demand opens a new cache generation: everything is computed fresh
+        s3 = d.score([10], 0, load=gl)
+        f3 = d.assume([10], 0, load=gl)
+        assert np.array_equal(s3, f3["score"])
+
+
+# ---- the batch kernel ---------------------------------------------------------------------------
+def run_batch_pair(ngs, n, p_used, pods, c_rng, pct_rng, policy, seed, load=False, hetero=False, max_c=None):
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    oc, d, _, _ = make_pair(ngs, n, p_used, seed, hetero=hetero)
+    pc, nc = wl.make_pods(pods, c_rng[0], c_rng[1], pct_rng[0], pct_rng[1], seed, max_c=max_c)
+    with d:
+        gl = ol = None
+        if load:
+            fill_load_tables(oc, d, n, seed)
+            gl, ol = load_ctx_pair(ngs)
+        node, score, gidx = d.schedule_batch(pc, nc, policy, load=gl, seed=seed, seq0=5)
+        onode, oscore, ogidx = oc.schedule_batch(pc, nc, policy, load=ol, seed=seed, seq0=5)
+        assert np.array_equal(node, onode)
+        assert np.array_equal(score, oscore)
+        assert np.array_equal(gidx, ogidx)
+        assert_same_snapshot(oc, d)
+        return node
+
+
+def test_batch_config_c1(ngs):
+    """BASELINE configs[0]: 10 nodes x 8 GPUs, 100 single-container pods, binpack"""
+    node = run_batch_pair(ngs, 10, 0.0, 100, (1, 1), (1, 20), 0, 0xB2000001)
+    assert (node >= 0).sum() > 50
+
+
+@pytest.mark.parametrize("policy", [0, 1, 2])
+def test_batch_small_clusters(ngs, policy):
+    for n in (1, 7, 63, 64, 65, 1000, 9473):
+        run_batch_pair(ngs, n, 0.5, 150, (1, 3), (0, 12), policy, 100 + n)
+
+
+def test_batch_config_c2_scaled(ngs):
+    """configs[1] shape (spread, single container) at a size the oracle finishes in seconds"""
+    run_batch_pair(ngs, 5000, 0.3, 1500, (1, 1), (1, 20), 1, 0xB2000002)
+
+
+def test_batch_config_c3_scaled(ngs):
+    """configs[2] shape: multi-container pods, binpack, load-aware"""
+    run_batch_pair(ngs, 20000, 0.5, 400, (2, 4), (0, 12), 0, 0xB2000003, load=True, max_c=4)
+
+
+def test_batch_hetero_gpu_counts(ngs):
+    run_batch_pair(ngs, 3000, 0.4, 300, (1, 4), (0, 12), 0, 0x4E7, hetero=True)
+    run_batch_pair(ngs, 3000, 0.4, 300, (1, 4), (0, 12), 1, 0x4E8, hetero=True, load=True)
+
+
+def test_batch_mixed_policy_churn(ngs):
+    """configs[4] shape: interleaved schedule / release with the policy cycling per pod"""
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    n = 5000
+    oc, d, _, _ = make_pair(ngs, n, 0.5, 0xB2000005)
+    rng = np.random.default_rng(55)
+    live = []
+    with d:
+        for rnd in range(12):
+            P = 200
+            pc, nc = wl.make_pods(P, 1, 3, 1, 12, 0xB2000005 + rnd)
+            pol = (np.arange(P) + rnd) % 3  # random / binpack / spread cycling
+            node, score, gidx = d.schedule_batch(pc, nc, pol, seed=99, seq0=rnd * P)
+            onode, oscore, ogidx = oc.schedule_batch(pc, nc, pol, seed=99, seq0=rnd * P)
+            assert np.array_equal(node, onode) and np.array_equal(score, oscore) and np.array_equal(gidx, ogidx)
+            for p in range(P):
+                if node[p] >= 0:
+                    live.append((int(node[p]), pc[p, : nc[p]].copy(), gidx[p, : nc[p]].copy()))
+            # release a random third of the live pods (forget is bookkeeping only, dealer.go:311-319)
+            for _ in range(len(live) // 3):
+                nd, dem, gi = live.pop(int(rng.integers(0, len(live))))
+                assert d.node_apply(nd, gi, dem, -1) == 0 and oc.node_apply(nd, gi, dem, -1) == 0
+        assert_same_snapshot(oc, d)
+
+
+def test_batch_matches_verb_by_verb(ngs):
+    """one launch for P pods == P x (assume, score, arg-max, bind) through the single-pod verbs"""
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    n, P = 2000, 60
+    gcount, free = wl.make_cluster(n, 0.5, 31)
+    pc, nc = wl.make_pods(P, 1, 3, 0, 12, 31)
+    with ngs.GpuDealer(n, device=0) as a, ngs.GpuDealer(n, device=0) as b:
+        a.snapshot_load(gcount, free)
+        b.snapshot_load(gcount, free)
+        node, score, gidx = a.schedule_batch(pc, nc, 1)
+        for p in range(P):
+            dem = pc[p, : nc[p]]
+            r = b.assume(dem, 1)
+            s = b.score(dem, 1)
+            cand = np.flatnonzero(r["feasible"])
+            if len(cand) == 0:
+                assert node[p] == -1
+                continue
+            best = cand[np.argmax(s[cand])]  # first maximum = lowest index
+            assert node[p] == best and score[p] == s[best]
+            rc, gi, sc = b.bind(int(best), dem, 1)
+            assert rc == 0 and np.array_equal(gi, gidx[p, : nc[p]])
+        assert np.array_equal(a.snapshot_read()[1], b.snapshot_read()[1])
+
+
+def test_batch_rejects_bad_pods(ngs):
+    with ngs.GpuDealer(100, device=0) as d:
+        d.snapshot_load(np.full(100, 8, dtype=np.uint8))
+        with pytest.raises(ngs.NgsError):
+            d.schedule_batch(np.array([[-1, 0]], dtype=np.int32), [2], 0)
+        with pytest.raises(ngs.NgsError):
+            d.schedule_batch(np.array([[10, 0]], dtype=np.int32), [3], 0)
+        node, _, _ = d.schedule_batch(np.zeros((0, 2), dtype=np.int32), np.zeros(0, dtype=np.int32), 0)
+        assert len(node) == 0
+
+
+def test_batch_chunking_across_launches(ngs):
+    """more pods than one launch holds (4096): chunks continue the same sequence"""
+    run_batch_pair(ngs, 400, 0.2, 5000, (1, 2), (1, 6), 2, 0xC4)
+    run_batch_pair(ngs, 400, 0.2, 5000, (1, 2), (1, 6), 0, 0xC5)
+
+
+# ---- full-size, size-independent properties ----------------------------------------------------
+def test_full_size_c3_properties(ngs):
+    """100k nodes, load-aware binpack (BASELINE configs[2]): the oracle is too slow for every pod,
+    so check (a) the oracle on a prefix of pods, (b) conservation: capacity removed from the
+    snapshot == sum of placed demands, (c) every placed container fits where it was put,
+    (d) schedule -> release of everything restores the snapshot bit for bit."""
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    n, P = 100_000, 3000
+    gcount, free = wl.make_cluster(n, 0.5, 0xB2000003)
+    pc, nc = wl.make_pods(P, 2, 4, 0, 12, 0xB2000003, max_c=4)
+    with ngs.GpuDealer(n, device=0) as d:
+        d.snapshot_load(gcount, free)
+        tables = wl.make_load_tables(n, 0xB2000003, NOW_S)
+        for m, (value, ts, absent) in enumerate(tables):
+            ok = np.repeat(~absent[:, None], 8, axis=1).astype(np.uint8)
+            d.load_update_bulk(m, value, ts, value_ok=ok, ts_ok=ok)
+        gl, ol = load_ctx_pair(ngs)
+        node, score, gidx = d.schedule_batch(pc, nc, 0, load=gl)
+        _, after, _ = d.snapshot_read()
+        placed = node >= 0
+        assert placed.sum() > P // 2
+        # (b) conservation
+        removed = (free.astype(np.int64) - after).sum()
+        assert removed == pc[placed].sum()
+        # (c) replay the decisions on the host: every container fits at its turn
+        cur = free.copy()
+        for p in np.flatnonzero(placed):
+            for k in range(nc[p]):
+                g = gidx[p, k]
+                if pc[p, k] == 0:
+                    assert g == -1
+                else:
+                    assert 0 <= g < 8 and cur[node[p], g] >= pc[p, k]
+                    cur[node[p], g] -= pc[p, k]
+        assert np.array_equal(cur, after)
+        # (a) oracle on a prefix
+        K = 12
+        oc = o.OracleCluster(n)
+        oc.load_snapshot(gcount, free)
+        for m, (value, ts, absent) in enumerate(tables):
+            oc.load_update_bulk(m, value, ts, ok=np.repeat(~absent[:, None], 8, axis=1).astype(np.uint8))
+        onode, oscore, ogidx = oc.schedule_batch(pc[:K], nc[:K], 0, load=ol, n_threads=4)
+        assert np.array_equal(node[:K], onode) and np.array_equal(score[:K], oscore) and np.array_equal(gidx[:K], ogidx)
+        # (d) round trip
+        for p in np.flatnonzero(placed):
+            assert d.node_apply(int(node[p]), gidx[p, : nc[p]], pc[p, : nc[p]], -1) == 0
+        assert np.array_equal(d.snapshot_read()[1], free)
+
+
+def test_full_size_million_nodes(ngs):
+    """1M nodes (BASELINE configs[3], one shard): filter parity on a sampled candidate list and
+    batch decisions against a numpy restatement of the single-container arg-max."""
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    n = 1_000_000
+    gcount, free = wl.make_cluster(n, 0.5, 0xB2000004)
+    with ngs.GpuDealer(n, device=0) as d:
+        d.snapshot_load(gcount, free)
+        r = d.assume([45], 0)
+        # single container, RemainLoad 0: feasible iff some cell has >= 45 free; Binpack.Rate in fp64
+        assert np.array_equal(r["feasible"].astype(bool), (free >= 45).any(axis=1))
+        used = (100 - free.astype(np.int64)).sum(axis=1)
+        want = (used.astype(np.float64) / 800.0 * 100.0).astype(np.int64) - 8
+        assert np.array_equal(r["score"][r["feasible"] == 1], want[r["feasible"] == 1])
+        pc, nc = wl.make_pods(64, 1, 1, 1, 20, 0xB2000004)
+        node, score, gidx = d.schedule_batch(pc, nc, 0)
+        cur = free.copy()
+        for p in range(64):
+            dem = pc[p, 0]
+            feas = (cur >= dem).any(axis=1)
+            u = (100 - cur.astype(np.int64)).sum(axis=1)
+            sc = (u.astype(np.float64) / 800.0 * 100.0).astype(np.int64) - 8
+            sc[~feas] = -(2**40)
+            best = int(np.argmax(sc))
+            assert node[p] == best and score[p] == sc[best]
+            # binpack picks the fullest cell that still fits (ties are interchangeable here)
+            assert cur[best, gidx[p, 0]] == cur[best][cur[best] >= dem].min()
+            cur[best, gidx[p, 0]] -= dem
+        assert np.array_equal(d.snapshot_read()[1], cur)

@@ -1,0 +1,147 @@
+"""The oracle against every known-answer vector the reference's own tests hold for the path
+(tests/golden/reference_kats.json, extracted from pkg/dealer/*_test.go) plus the derived vectors
+of SURVEY.md §8c.  CPU only."""
+import numpy as np
+import pytest
+
+import oracle as o
+from tests import go_sort_py as gs
+
+POL = {"binpack": o.POLICY_BINPACK, "spread": o.POLICY_SPREAD, "random": o.POLICY_RANDOM}
+
+
+def test_binpack_choose_kats(kats):  # rater_test.go:133-266
+    assert len(kats["binpack_choose"]["cases"]) == 5
+    for c in kats["binpack_choose"]["cases"]:
+        ok, idx, _ = o.choose(o.POLICY_BINPACK, c["free"], c["demand"])
+        assert ok == (not c["expect_failed"])
+        if ok:
+            assert idx == c["expected"]
+
+
+def test_spread_choose_kats(kats):  # rater_test.go:268-401
+    assert len(kats["spread_choose"]["cases"]) == 5
+    for c in kats["spread_choose"]["cases"]:
+        ok, idx, _ = o.choose(o.POLICY_SPREAD, c["free"], c["demand"])
+        assert ok == (not c["expect_failed"])
+        if ok:
+            assert idx == c["expected"]
+
+
+def test_binpack_rate_kat(kats):  # rater_test.go:9-37
+    for c in kats["binpack_rate"]["cases"]:
+        assert (o.rate(o.POLICY_BINPACK, c["gpus1"]) < o.rate(o.POLICY_BINPACK, c["gpus2"])) == c["first_lower"]
+
+
+def test_spread_rate_kats(kats):  # rater_test.go:39-131
+    assert len(kats["spread_rate"]["cases"]) == 4
+    for c in kats["spread_rate"]["cases"]:
+        assert (o.rate(o.POLICY_SPREAD, c["gpus1"]) > o.rate(o.POLICY_SPREAD, c["gpus2"])) == c["first_preferred"]
+
+
+def test_sample_choose_kats(kats):  # allocate_test.go:160-190
+    assert len(kats["sample_choose"]["cases"]) == 4
+    for c in kats["sample_choose"]["cases"]:
+        ok, _, _ = o.choose(o.POLICY_RANDOM, c["free"], c["demand"])
+        assert ok == c["success"]
+
+
+def test_sortable_gpus_kat(kats):  # allocate_test.go:213-230
+    for c in kats["sortable_gpus"]["cases"]:
+        f, _, idx = o.go_sort(c["free"])
+        assert f.tolist() == c["expected_free"] and idx.tolist() == c["expected_index"]
+
+
+def test_gpu_resource_kats(kats):  # allocate_test.go:16-86 through GPUs.Allocate / Release on one cell
+    g = kats["gpu_resource"]
+    for c in g["sub"]:
+        oc = o.OracleCluster(1)
+        oc.node_set(0, [c["origin"]])
+        assert oc.node_apply(0, [0], [c["target"]], +1) == 0
+        assert oc.node_get(0)[1].tolist() == [c["expect"]]
+    for c in g["add"]:
+        oc = o.OracleCluster(1)
+        oc.node_set(0, [c["origin"]])
+        assert oc.node_apply(0, [0], [c["target"]], -1) == 0
+        assert oc.node_get(0)[1].tolist() == [c["expect"]]
+    for c in g["sub_if_available"]:  # CanAllocate gate: a demand that does not fit changes nothing
+        oc = o.OracleCluster(1)
+        oc.node_set(0, [c["origin"]])
+        rc = oc.node_apply(0, [0], [c["target"]], +1)
+        assert (rc == 0) == (c["origin"] >= c["target"])
+        assert oc.node_get(0)[1].tolist() == [c["expect"]]
+
+
+def test_derived_sort_rule_vectors(derived):
+    for v in derived["sort_rule_choose"]:
+        ok, idx, _ = o.choose(POL[v["policy"]], v["free"], v["demand"], rule=o.SORT_GO116)
+        assert ok and idx == v["go116"]
+        ok, idx, _ = o.choose(POL[v["policy"]], v["free"], v["demand"], rule=o.SORT_GO119)
+        assert ok and idx == v["go119"]
+
+
+def test_derived_rates(derived):
+    for v in derived["rates"]:
+        assert o.rate(POL[v["policy"]], v["free"]) == v["score"], v
+
+
+def test_binpack_rate_is_fp64_not_integer():
+    """int(float64(used)/float64(sum)*100) differs from used*100//sum exactly where fp64 rounds down"""
+    diffs = []
+    for used in range(0, 801):
+        free = [100] * 8
+        left = used
+        for g in range(8):
+            take = min(100, left)
+            free[g] -= take
+            left -= take
+        r = o.rate(o.POLICY_BINPACK, free) + 8
+        assert r == int(float(used) / float(800) * 100)
+        if r != used * 100 // 800:
+            diffs.append(used)
+    assert diffs == [232, 456, 464]
+
+
+@pytest.mark.parametrize("n", [2, 3, 6, 7, 8, 9, 12, 13, 20, 41, 64])
+def test_go_sort_matches_python_restatement(n):
+    rng = np.random.default_rng(1234 + n)
+    for _ in range(300):
+        free = rng.integers(0, 6, n) * 20  # many ties
+        rl = rng.integers(0, 3, n)
+        f, r, idx = o.go_sort(free, rl)
+        cells = gs.Cells(free.tolist(), rl.tolist(), range(n))
+        gs.go116_sort(cells)
+        assert [c[2] for c in cells.a] == idx.tolist()
+        keys = (f + 50 * r).tolist()
+        assert keys == sorted(keys)
+
+
+def test_choose_matches_python_restatement():
+    rng = np.random.default_rng(7)
+    for trial in range(3000):
+        G = int(rng.integers(1, 13))
+        C = int(rng.integers(1, 7))
+        free = (rng.integers(0, 11, G) * 10).tolist()
+        rl = rng.integers(0, 3, G).tolist() if trial % 2 else [0] * G
+        demand = (rng.integers(0, 8, C) * 10).tolist()
+        for spread in (False, True):
+            ok, idx, ne = o.choose(o.POLICY_SPREAD if spread else o.POLICY_BINPACK, free, demand, rl=rl)
+            pok, pidx = gs.choose(free, rl, demand, spread)
+            assert ok == pok
+            if ok:
+                assert idx == pidx
+            else:
+                assert idx[:ne] == pidx
+
+
+def test_go119_rule_differs_sometimes():
+    rng = np.random.default_rng(3)
+    differ = 0
+    for _ in range(2000):
+        free = (rng.integers(0, 6, 8) * 20).tolist()
+        d = [int(rng.integers(1, 6) * 10)]
+        a = o.choose(o.POLICY_SPREAD, free, d, rule=o.SORT_GO116)
+        b = o.choose(o.POLICY_SPREAD, free, d, rule=o.SORT_GO119)
+        assert a[0] == b[0]  # feasibility never depends on the tie order when RemainLoad is 0
+        differ += a[1] != b[1]
+    assert differ > 100
