@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--pods-per-step", type=int, default=2048)
     ap.add_argument("--nodes", type=int, default=0, help="override nodes per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--skip-e2e", action="store_true", help="profiling runs: only the device-resident arm")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     return ap.parse_args()
 
@@ -293,7 +294,7 @@ def run_b200(args):
         # ---- end-to-end arm: host buffers through the C ABI (pinned staging + H2D + D2H inside) ----
         base = steps_total * P
         e2e_times = []
-        for s in range(steps_total):
+        for s in range(0 if args.skip_e2e else steps_total):
             lo = base + s * P
             flush.fill_(s & 0xFF)
             torch.cuda.synchronize()
@@ -305,7 +306,7 @@ def run_b200(args):
         # ---- per-pod decision latency: single-pod calls through the host API ----
         lat = []
         lo = base
-        for s in range(300):
+        for s in range(60 if args.skip_e2e else 300):
             t0 = time.perf_counter()
             d.schedule_batch(pc[lo + s:lo + s + 1], nc[lo + s:lo + s + 1], policy[lo + s:lo + s + 1], load=load, seed=1, seq0=s)
             lat.append(time.perf_counter() - t0)
@@ -314,6 +315,8 @@ def run_b200(args):
     total_ms = float(sum(step_ms))
     evals_per_step = P * n * world
     value = evals_per_step * args.steps / (total_ms / 1e3)
+    if not e2e_times:
+        e2e_times = [float("nan")]
     e2e_value = evals_per_step * len(e2e_times) / sum(e2e_times)
     peak, peak_src = measured_peak()
     bpe = BYTES_PER_EVAL[bool(cfg["load"])]

@@ -41,7 +41,8 @@ enum {
     NGS_ERR_INFEASIBLE = 4,   /* bind: "assume ... failed" (node.go:74-76) */
     NGS_ERR_APPLY = 5,        /* apply: "can't apply plan" (allocate.go:113) / index >= G (allocate.go:126) */
     NGS_ERR_RANGE = 6,        /* a cell would leave [0, NGS_MAX_FREE] */
-    NGS_ERR_UNSUPPORTED = 7   /* gpu_count > NGS_MAX_GPUS, too many containers or periods */
+    NGS_ERR_UNSUPPORTED = 7,  /* gpu_count > NGS_MAX_GPUS, too many containers or periods */
+    NGS_ERR_TIMEOUT = 8       /* the batch kernel gave up waiting for a peer (never expected) */
 };
 
 /* policies: Binpack (rater.go:52), Spread (rater.go:55), random = SampleRater plan search

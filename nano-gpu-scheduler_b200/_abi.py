@@ -16,7 +16,7 @@ MAX_FREE = 65535
 MAX_BATCH = 65536
 INT32_MIN = -(2**31)
 
-OK, ERR_INVALID, ERR_CUDA, ERR_UNKNOWN_NODE, ERR_INFEASIBLE, ERR_APPLY, ERR_RANGE, ERR_UNSUPPORTED = range(8)
+OK, ERR_INVALID, ERR_CUDA, ERR_UNKNOWN_NODE, ERR_INFEASIBLE, ERR_APPLY, ERR_RANGE, ERR_UNSUPPORTED, ERR_TIMEOUT = range(9)
 POLICY_BINPACK, POLICY_SPREAD, POLICY_RANDOM = 0, 1, 2
 REASON_OK, REASON_UNKNOWN_NODE, REASON_INFEASIBLE = 0, 1, 2
 METRIC_CORE, METRIC_MEMORY = 0, 1

@@ -115,6 +115,13 @@ __device__ __forceinline__ RowEval eval_row_global(const Tables& T, uint32_t row
         }
     }
     if (do_rate) ev.score = rate_policy(policy, f, G, load_int);
+    if (!PLAN) {
+        const int cls = classify_row(f, dem, policy != NGS_POLICY_RANDOM);
+        if (cls != FEAS_UNDECIDED) {
+            ev.feasible = cls == FEAS_YES;
+            return ev;
+        }
+    }
     if (policy == NGS_POLICY_RANDOM) {
         ev.feasible = choose_sample<PLAN>(f, G, dem, &ev.emit, &ev.n_emit);
     } else {
@@ -330,6 +337,7 @@ struct BatchParams {
     int32_t* gpu_idx_out;
     int max_c;
     unsigned long long* keys;  // [P][gridDim.x], zero before launch
+    int32_t* err;              // device error word (0 = ok)
     uint32_t rows_per_block;
 };
 
@@ -339,6 +347,26 @@ __device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned l
 __device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
     unsigned long long v;
     asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// Bounded spin on a key slot: gives up (and raises the batch's error word so that every CTA
+// leaves the pod loop) if a peer has not posted within ~1 s or has already given up.
+constexpr long long SPIN_TIMEOUT_CYCLES = 2000000000LL;
+__device__ __forceinline__ unsigned long long poll_key(const unsigned long long* p, int32_t* err, bool& dead) {
+    unsigned long long v = ld_relaxed_u64(p);
+    if (v & KEY_VALID) return v;
+    const long long t0 = clock64();
+    uint32_t spins = 0;
+    while (!((v = ld_relaxed_u64(p)) & KEY_VALID)) {
+        if ((++spins & 1023u) == 0) {
+            if (*reinterpret_cast<volatile int32_t*>(err) != 0 || clock64() - t0 > SPIN_TIMEOUT_CYCLES) {
+                atomicCAS(err, 0, NGS_ERR_TIMEOUT);
+                dead = true;
+                return KEY_VALID;
+            }
+        }
+    }
     return v;
 }
 
@@ -372,6 +400,8 @@ __device__ __forceinline__ bool eval_row_smem(const SmemRows& S, uint32_t r, con
     if (G == 0) return false;
     int f[8];
     unpack_free(S.fA[r], S.fB[r], f);
+    const int cls = classify_row(f, dem, policy != NGS_POLICY_RANDOM);
+    if (cls != FEAS_UNDECIDED) return cls == FEAS_YES;
     if (policy == NGS_POLICY_RANDOM) return choose_sample<false>(f, G, dem, nullptr, nullptr);
     uint32_t w[8];
     const bool rl0 = (meta & 0xFFFFFFu) == RL0_META;
@@ -380,54 +410,72 @@ __device__ __forceinline__ bool eval_row_smem(const SmemRows& S, uint32_t r, con
     return choose_sorted<false>(w, G, policy == NGS_POLICY_SPREAD, rl0, dem, nullptr, nullptr);
 }
 
-// bind on the owning block: exact plan, apply to the shared row, refresh both cached rates,
-// write the row through to the global table and publish the decision.
-__device__ void bind_row_smem(const BatchParams& bp, const SmemRows& S, uint32_t r, uint32_t row, const SortedDemand* dem,
-                              uint32_t p, int score) {
+// The decision for one shared-memory row, held in registers until it is known to be the winner.
+struct Commit {
+    uint2 fA, fB;  // row after GPUs.Allocate
+    int32_t scB, scS;
+    int32_t f[8];
+    uint64_t emit;
+    int32_t n_emit;
+};
+
+// exact plan (Rater.Choose with index tracking) and the row it leaves behind
+__device__ __forceinline__ void plan_row_smem(const SmemRows& S, uint32_t r, const SortedDemand* dem, Commit& cm) {
     const uint32_t meta = S.meta[r];
     const int G = (meta >> 24) & 15;
     const int load_int = (int)(meta >> 28);
     const int policy = dem->policy;
     int f[8];
     unpack_free(S.fA[r], S.fB[r], f);
-    uint64_t emit = 0;
-    int n_emit = 0;
+    cm.emit = 0;
+    cm.n_emit = 0;
     if (policy == NGS_POLICY_RANDOM) {
-        int f2[8];
-#pragma unroll
-        for (int g = 0; g < 8; g++) f2[g] = f[g];
-        choose_sample<true>(f2, G, dem, &emit, &n_emit);
+        choose_sample<true>(f, G, dem, &cm.emit, &cm.n_emit);  // places on f directly
     } else {
         uint32_t w[8];
+        int placed[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         const bool rl0 = (meta & 0xFFFFFFu) == RL0_META;
 #pragma unroll
         for (int g = 0; g < 8; g++) w[g] = g < G ? pack_cell(f[g], (meta >> (3 * g)) & 7, g) : W_PAD;
-        choose_sorted<true>(w, G, policy == NGS_POLICY_SPREAD, rl0, dem, &emit, &n_emit);
-    }
-    int32_t* out = bp.gpu_idx_out + (size_t)p * bp.max_c;
-    int32_t planv[NGS_MAX_CONTAINERS];
-    write_plan(planv, dem, policy != NGS_POLICY_RANDOM, true, emit, n_emit);
-    for (int k = 0; k < bp.max_c; k++) out[k] = k < dem->C ? planv[k] : INT32_MIN;
-    for (int k = 0; k < dem->C; k++) {  // GPUs.Allocate (allocate.go:102-118)
-        const int gi = planv[k];
-        if (gi < 0) continue;
-        const int d = dem->raw[k];
+        choose_sorted<true>(w, G, policy == NGS_POLICY_SPREAD, rl0, dem, &cm.emit, &cm.n_emit, &placed);
 #pragma unroll
-        for (int g = 0; g < 8; g++) f[g] -= (g == gi) ? d : 0;
+        for (int g = 0; g < 8; g++) f[g] -= placed[g];  // GPUs.Allocate (allocate.go:102-118)
     }
-    uint2 a, b;
-    a.x = (uint32_t)f[0] | ((uint32_t)f[1] << 16); a.y = (uint32_t)f[2] | ((uint32_t)f[3] << 16);
-    b.x = (uint32_t)f[4] | ((uint32_t)f[5] << 16); b.y = (uint32_t)f[6] | ((uint32_t)f[7] << 16);
-    S.fA[r] = a;
-    S.fB[r] = b;
-    S.scB[r] = rate_binpack(f, G, load_int);
-    S.scS[r] = rate_spread(f, G, load_int);
+#pragma unroll
+    for (int g = 0; g < 8; g++) cm.f[g] = f[g];
+    cm.fA.x = (uint32_t)f[0] | ((uint32_t)f[1] << 16); cm.fA.y = (uint32_t)f[2] | ((uint32_t)f[3] << 16);
+    cm.fB.x = (uint32_t)f[4] | ((uint32_t)f[5] << 16); cm.fB.y = (uint32_t)f[6] | ((uint32_t)f[7] << 16);
+    cm.scB = rate_binpack(f, G, load_int);
+    cm.scS = rate_spread(f, G, load_int);
+}
+
+// publish a winning decision: shared row, cached rates, the global table and the pod's outputs
+__device__ __forceinline__ void publish_commit(const BatchParams& bp, const SmemRows& S, uint32_t r, uint32_t row,
+                                               const SortedDemand* dem, uint32_t p, int score, const Commit& cm) {
+    S.fA[r] = cm.fA;
+    S.fB[r] = cm.fB;
+    S.scB[r] = cm.scB;
+    S.scS[r] = cm.scS;
     int4* gp = reinterpret_cast<int4*>(bp.T.free + (size_t)row * 8);
-    gp[0] = make_int4(f[0], f[1], f[2], f[3]);
-    gp[1] = make_int4(f[4], f[5], f[6], f[7]);
+    gp[0] = make_int4(cm.f[0], cm.f[1], cm.f[2], cm.f[3]);
+    gp[1] = make_int4(cm.f[4], cm.f[5], cm.f[6], cm.f[7]);
     bp.T.tag[row] = 0;  // node.go:82
     bp.node_out[p] = (int32_t)(bp.T.first + row);
     bp.score_out[p] = score;
+    int32_t* out = bp.gpu_idx_out + (size_t)p * bp.max_c;
+    const int C = dem->C;
+    const bool sorted_policy = dem->policy != NGS_POLICY_RANDOM;
+    for (int k = C; k < bp.max_c; k++) out[k] = INT32_MIN;
+    for (int k = 0; k < C; k++) {  // rater.go:102-105: un-permute the emission order
+        const int e = (int)((cm.emit >> (4 * k)) & 0xF);
+        out[sorted_policy ? dem->order[k] : k] = e == 0xF ? NGS_NOT_NEED_GPU : e;
+    }
+}
+
+__device__ __forceinline__ void publish_none(const BatchParams& bp, uint32_t p) {
+    bp.node_out[p] = -1;
+    bp.score_out[p] = NGS_SCORE_MIN;
+    for (int k = 0; k < bp.max_c; k++) bp.gpu_idx_out[(size_t)p * bp.max_c + k] = INT32_MIN;
 }
 
 // K6.  One CTA per SM (cooperative launch, so every CTA is resident), each owning a contiguous
@@ -442,7 +490,9 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ SortedDemand s_dem[2];
     __shared__ uint64_t s_red[32];
+    __shared__ int s_abort;
     const uint32_t rpb = bp.rows_per_block;
+    if (threadIdx.x == 0) s_abort = 0;
     SmemRows S;
     S.fA = reinterpret_cast<uint2*>(smem_raw);
     S.fB = S.fA + rpb;
@@ -509,9 +559,28 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     __syncthreads();
 
     const uint32_t n_iter = (my_rows + blockDim.x - 1) / blockDim.x;
+    bool rl_pending = bp.lp.enabled != 0;  // RemainLoad write-back of the first load-aware Rate
     for (uint32_t p = 0; p < bp.P; p++) {
         const SortedDemand* dem = &s_dem[p & 1];
         const int policy = dem->policy;
+        if (rl_pending && policy != NGS_POLICY_RANDOM) {
+            // allocate.go:193: LoadUsage leaves RemainLoad in the live node state.  SampleRater.Rate
+            // never calls it, so the table is only touched once a binpack/spread pod comes by.
+            rl_pending = false;
+            for (uint32_t r = tid; r < my_rows; r += blockDim.x) {
+                const uint32_t meta = S.meta[r];
+                const int G = (meta >> 24) & 15;
+                if (G == 0) continue;
+                uint2 out;
+                out.x = out.y = 0;
+#pragma unroll
+                for (int g = 0; g < 4; g++) {
+                    out.x |= (uint32_t)(uint8_t)(int8_t)(g < G ? (int)((meta >> (3 * g)) & 7) - 2 : 0) << (8 * g);
+                    out.y |= (uint32_t)(uint8_t)(int8_t)(g + 4 < G ? (int)((meta >> (3 * (g + 4))) & 7) - 2 : 0) << (8 * g);
+                }
+                *reinterpret_cast<uint2*>(T.rl + (size_t)(row0 + r) * 8) = out;
+            }
+        }
         // stage the next pod's demand while this one is evaluated (last warp: the least loaded)
         if (warp == nwarps - 1 && p + 1 < bp.P)
             for (uint32_t i = lane; i < sizeof(SortedDemand) / 4; i += 32)
@@ -545,6 +614,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
         }
         __syncthreads();
         if (warp == 0) {
+            bool dead = false;
             unsigned long long* krow = bp.keys + (size_t)p * gridDim.x;
             uint64_t v = lane < nwarps ? s_red[lane] : 0;
             if (policy == NGS_POLICY_RANDOM) {
@@ -557,8 +627,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                 const uint32_t j0 = min(lane * chunk, gridDim.x), j1 = min(j0 + chunk, gridDim.x);
                 uint64_t sum = 0;
                 for (uint32_t j = j0; j < j1; j++) {
-                    unsigned long long kv;
-                    do kv = ld_relaxed_u64(krow + j); while (!(kv & KEY_VALID));
+                    const unsigned long long kv = poll_key(krow + j, bp.err, dead);
                     sum += kv & 0xFFFFFFFFull;
                 }
                 uint64_t incl = sum;
@@ -569,11 +638,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                 }
                 const uint64_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
                 if (total == 0) {
-                    if (blockIdx.x == 0 && lane == 0) {
-                        bp.node_out[p] = -1;
-                        bp.score_out[p] = NGS_SCORE_MIN;
-                        for (int k = 0; k < bp.max_c; k++) bp.gpu_idx_out[(size_t)p * bp.max_c + k] = INT32_MIN;
-                    }
+                    if (blockIdx.x == 0 && lane == 0) publish_none(bp, p);
                 } else {
                     const uint64_t pick = splitmix64(bp.seed_seq + p) % total;
                     // rank of the pick inside this CTA, if it falls here
@@ -609,7 +674,9 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                                 if (need < pc) {
                                     for (uint32_t q = 0; q < need; q++) bits &= bits - 1;
                                     const uint32_t r = wi * 32 + (__ffs(bits) - 1);
-                                    bind_row_smem(bp, S, r, row0 + r, dem, p, 100);
+                                    Commit cm;
+                                    plan_row_smem(S, r, dem, cm);
+                                    publish_commit(bp, S, r, row0 + r, dem, p, 100, cm);
                                     break;
                                 }
                                 need -= pc;
@@ -620,29 +687,30 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
             } else {
                 v = warp_max_u64(v);
                 if (lane == 0) st_relaxed_u64(krow + blockIdx.x, KEY_VALID | v);
+                // while the other CTAs' keys are in flight, lane 0 works out the exact plan of this
+                // CTA's best row; it is published only if that row turns out to be the global winner
+                Commit cm;
+                const uint32_t my_r = key_node(v) - T.first - row0;
+                if (lane == 0 && (v & KEY_FEASIBLE)) plan_row_smem(S, my_r, dem, cm);
                 uint64_t m = 0;
                 for (uint32_t j = lane; j < gridDim.x; j += 32) {
-                    unsigned long long kv;
-                    do kv = ld_relaxed_u64(krow + j); while (!(kv & KEY_VALID));
+                    const unsigned long long kv = poll_key(krow + j, bp.err, dead);
                     m = kv > m ? kv : m;
                 }
                 m = warp_max_u64(m);
                 if (lane == 0) {
                     if (!(m & KEY_FEASIBLE)) {
-                        if (blockIdx.x == 0) {
-                            bp.node_out[p] = -1;
-                            bp.score_out[p] = NGS_SCORE_MIN;
-                            for (int k = 0; k < bp.max_c; k++) bp.gpu_idx_out[(size_t)p * bp.max_c + k] = INT32_MIN;
-                        }
-                    } else {
-                        const uint32_t row = key_node(m) - T.first;
+                        if (blockIdx.x == 0) publish_none(bp, p);
+                    } else if (m == (v | KEY_VALID)) {
                         // ---- 3. bind on the owner ----
-                        if (row >= row0 && row < row0 + my_rows) bind_row_smem(bp, S, row - row0, row, dem, p, key_score(m));
+                        publish_commit(bp, S, my_r, row0 + my_r, dem, p, key_score(m), cm);
                     }
                 }
             }
+            if (__any_sync(0xFFFFFFFFu, dead) && lane == 0) s_abort = 1;
         }
         __syncthreads();
+        if (s_abort) break;  // a peer CTA never posted: give up instead of hanging the GPU
     }
 }
 
@@ -827,6 +895,7 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     bp.gpu_idx_out = d_gidx;
     bp.max_c = max_c;
     bp.keys = h->d_keys;
+    bp.err = h->d_err;
     bp.rows_per_block = rpb;
     void* args[] = {&bp};
     CU(h, cudaLaunchCooperativeKernel((void*)k_schedule, dim3(grid), dim3(block), args, smem, h->stream));
@@ -841,6 +910,7 @@ int check_dev_err(ngs_dealer* h) {
         int e = *h->h_err;
         *h->h_err = NGS_OK;
         cudaMemsetAsync(h->d_err, 0, 4, h->stream);
+        if (e == NGS_ERR_TIMEOUT) return fail(h, e, "batch kernel gave up waiting for a peer CTA (results of this batch are incomplete)");
         return fail(h, e, "device-side validation failed (bad container count, percent or policy in a batch)");
     }
     return NGS_OK;
@@ -865,6 +935,7 @@ const char* ngs_strerror(int s) {
         case NGS_ERR_APPLY: return "can't apply plan";
         case NGS_ERR_RANGE: return "capacity out of range";
         case NGS_ERR_UNSUPPORTED: return "unsupported size";
+        case NGS_ERR_TIMEOUT: return "device-side wait timed out";
         default: return "unknown status";
     }
 }

@@ -149,6 +149,38 @@ __device__ __forceinline__ uint32_t fit_mask(const uint32_t (&w)[8], int d, uint
     return m & gmask;
 }
 
+// Exact shortcuts for the feasibility question (rater.go:98-100), valid for every policy because
+// they only use "each container goes to SOME cell that fits it" (first fit in whatever order):
+//   * no cell holds the largest demand d1           -> that container can never be placed: NO
+//   * at least nz cells hold d1 (nz = non-zero containers) -> when the j-th container is placed at
+//     most j-1 cells have been touched, so an untouched cell with free >= d1 >= dj remains: YES
+//   * sorted policies, nz == 2, exactly one cell c holds d1: d1 is forced onto c, so the pod fits
+//     iff c still holds d2 afterwards or a second cell holds d2.
+// Everything else runs the exact greedy search.  Cells beyond the GPU count hold free = 0 and
+// demands here are > 0, so they never count.
+enum { FEAS_NO = 0, FEAS_YES = 1, FEAS_UNDECIDED = 2 };
+__device__ __forceinline__ int classify_row(const int (&f)[8], const SortedDemand* dem, bool sorted_policy) {
+    const int nz = dem->nz;
+    if (nz == 0) return FEAS_YES;
+    const int d1 = dem->d[0];
+    int cnt = 0, fmax = 0;
+#pragma unroll
+    for (int g = 0; g < 8; g++) {
+        cnt += f[g] >= d1 ? 1 : 0;
+        fmax = max(fmax, f[g]);
+    }
+    if (cnt == 0) return FEAS_NO;
+    if (cnt >= nz) return FEAS_YES;
+    if (sorted_policy && nz == 2) {  // cnt == 1: the cell holding d1 is the row maximum
+        const int d2 = dem->d[1];
+        int cnt2 = 0;
+#pragma unroll
+        for (int g = 0; g < 8; g++) cnt2 += f[g] >= d2 ? 1 : 0;
+        return (cnt2 >= 2 || fmax - d1 >= d2) ? FEAS_YES : FEAS_NO;
+    }
+    return FEAS_UNDECIDED;
+}
+
 // Binpack.Choose / Spread.Choose on the packed row.  Returns feasibility (rater.go:98-100).
 // PLAN: `emit` receives the `indexes` slice in emission order, 4 bits per entry (0xF = -1),
 // and n_emit its length; the greedy loop then runs to the end even after a miss, exactly as
@@ -156,7 +188,7 @@ __device__ __forceinline__ uint32_t fit_mask(const uint32_t (&w)[8], int d, uint
 // last non-zero container needs no sort (any cell that fits will do).
 template <bool PLAN>
 __device__ __forceinline__ bool choose_sorted(uint32_t (&w)[8], int G, bool spread, bool rl0, const SortedDemand* dem,
-                                              uint64_t* emit, int* n_emit) {
+                                              uint64_t* emit, int* n_emit, int (*placed)[8] = nullptr) {
     const uint32_t gmask = (1u << G) - 1u;
     const int nz = dem->nz;
     uint64_t em = 0;
@@ -184,6 +216,10 @@ __device__ __forceinline__ bool choose_sorted(uint32_t (&w)[8], int G, bool spre
         if (PLAN) {
             em |= (uint64_t)chosen << (4 * ne);
             ne++;
+            if (placed) {  // percent taken from each GPU, by original index (GPUs.Allocate's effect)
+#pragma unroll
+                for (int g = 0; g < 8; g++) (*placed)[g] += (chosen == (uint32_t)g) ? d : 0;
+            }
         }
     }
     if (PLAN) {
