@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libngs_dealer.so")
+LIB_PATH = os.environ.get("NGS_DEALER_LIB") or os.path.join(HERE, "libngs_dealer.so")  # override: profiling builds
 
 MAX_GPUS = 8
 MAX_CONTAINERS = 12

@@ -336,9 +336,13 @@ struct BatchParams {
     int32_t* score_out;
     int32_t* gpu_idx_out;
     int max_c;
-    unsigned long long* keys;  // [P][gridDim.x], zero before launch
+    unsigned long long* keys;  // [P][gridDim.x] one slot per CTA per pod, zero before launch
+    uint32_t* done;            // [P] arrival counters, zero before launch
     int32_t* err;              // device error word (0 = ok)
     uint32_t rows_per_block;
+#ifdef NGS_PHASE_TIMING
+    unsigned long long* dbg;   // [gridDim.x][8] accumulated cycles per phase (profiling builds only)
+#endif
 };
 
 __device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
@@ -350,25 +354,7 @@ __device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long
     return v;
 }
 
-// Bounded spin on a key slot: gives up (and raises the batch's error word so that every CTA
-// leaves the pod loop) if a peer has not posted within ~1 s or has already given up.
-constexpr long long SPIN_TIMEOUT_CYCLES = 2000000000LL;
-__device__ __forceinline__ unsigned long long poll_key(const unsigned long long* p, int32_t* err, bool& dead) {
-    unsigned long long v = ld_relaxed_u64(p);
-    if (v & KEY_VALID) return v;
-    const long long t0 = clock64();
-    uint32_t spins = 0;
-    while (!((v = ld_relaxed_u64(p)) & KEY_VALID)) {
-        if ((++spins & 1023u) == 0) {
-            if (*reinterpret_cast<volatile int32_t*>(err) != 0 || clock64() - t0 > SPIN_TIMEOUT_CYCLES) {
-                atomicCAS(err, 0, NGS_ERR_TIMEOUT);
-                dead = true;
-                return KEY_VALID;
-            }
-        }
-    }
-    return v;
-}
+constexpr long long SPIN_TIMEOUT_CYCLES = 2000000000LL;  // ~1 s
 
 __device__ __forceinline__ uint64_t warp_max_u64(uint64_t v) {
     const uint32_t hi = (uint32_t)(v >> 32);
@@ -386,89 +372,99 @@ struct SmemRows {
     int32_t* scB;  // Binpack.Rate of the row's current state
     int32_t* scS;  // Spread.Rate
     uint32_t* feasbits;
+    uint16_t* queue;  // rows whose feasibility the shortcuts could not decide
 };
 
 __device__ __forceinline__ void unpack_free(uint2 a, uint2 b, int (&f)[8]) {
     f[0] = a.x & 0xFFFF; f[1] = a.x >> 16; f[2] = a.y & 0xFFFF; f[3] = a.y >> 16;
     f[4] = b.x & 0xFFFF; f[5] = b.x >> 16; f[6] = b.y & 0xFFFF; f[7] = b.y >> 16;
 }
+__device__ __forceinline__ int smem_cell(const SmemRows& S, uint32_t r, int g) {
+    const uint16_t* p16 = reinterpret_cast<const uint16_t*>(g < 4 ? &S.fA[r] : &S.fB[r]);
+    return p16[g & 3];
+}
 
-// filter one shared-memory row for the staged demand; feasibility only
-__device__ __forceinline__ bool eval_row_smem(const SmemRows& S, uint32_t r, const SortedDemand* dem, int policy) {
+// thread-per-row exact filter (used for the random policy, whose plan search has no sorting)
+__device__ __forceinline__ bool eval_row_sample(const SmemRows& S, uint32_t r, const SortedDemand* dem) {
     const uint32_t meta = S.meta[r];
     const int G = (meta >> 24) & 15;
     if (G == 0) return false;
     int f[8];
     unpack_free(S.fA[r], S.fB[r], f);
-    const int cls = classify_row(f, dem, policy != NGS_POLICY_RANDOM);
+    const int cls = classify_row(f, dem, false);
     if (cls != FEAS_UNDECIDED) return cls == FEAS_YES;
-    if (policy == NGS_POLICY_RANDOM) return choose_sample<false>(f, G, dem, nullptr, nullptr);
-    uint32_t w[8];
-    const bool rl0 = (meta & 0xFFFFFFu) == RL0_META;
-#pragma unroll
-    for (int g = 0; g < 8; g++) w[g] = g < G ? pack_cell(f[g], (meta >> (3 * g)) & 7, g) : W_PAD;
-    return choose_sorted<false>(w, G, policy == NGS_POLICY_SPREAD, rl0, dem, nullptr, nullptr);
+    return choose_sample<false>(f, G, dem, nullptr, nullptr);
 }
 
-// The decision for one shared-memory row, held in registers until it is known to be the winner.
-struct Commit {
-    uint2 fA, fB;  // row after GPUs.Allocate
-    int32_t scB, scS;
-    int32_t f[8];
-    uint64_t emit;
+// The decision for one row, spread over the 8 lanes that searched its plan (lane = GPU cell)
+// and held in registers until the row is known to be the global winner.
+struct GroupCommit {
+    int32_t fr;      // this lane's cell after GPUs.Allocate
+    uint64_t emit;   // emission list (same in all 8 lanes)
     int32_t n_emit;
 };
 
-// exact plan (Rater.Choose with index tracking) and the row it leaves behind
-__device__ __forceinline__ void plan_row_smem(const SmemRows& S, uint32_t r, const SortedDemand* dem, Commit& cm) {
+// publish a winning decision (called by lanes 0..7 of warp 0): shared row, cached rates, the
+// global table and the pod's outputs
+__device__ __forceinline__ void publish_group(const BatchParams& bp, const SmemRows& S, uint32_t r, uint32_t row,
+                                              const SortedDemand* dem, uint32_t p, int score, const GroupCommit& cm, int g) {
     const uint32_t meta = S.meta[r];
     const int G = (meta >> 24) & 15;
     const int load_int = (int)(meta >> 28);
-    const int policy = dem->policy;
-    int f[8];
-    unpack_free(S.fA[r], S.fB[r], f);
-    cm.emit = 0;
-    cm.n_emit = 0;
-    if (policy == NGS_POLICY_RANDOM) {
-        choose_sample<true>(f, G, dem, &cm.emit, &cm.n_emit);  // places on f directly
-    } else {
-        uint32_t w[8];
-        int placed[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        const bool rl0 = (meta & 0xFFFFFFu) == RL0_META;
-#pragma unroll
-        for (int g = 0; g < 8; g++) w[g] = g < G ? pack_cell(f[g], (meta >> (3 * g)) & 7, g) : W_PAD;
-        choose_sorted<true>(w, G, policy == NGS_POLICY_SPREAD, rl0, dem, &cm.emit, &cm.n_emit, &placed);
-#pragma unroll
-        for (int g = 0; g < 8; g++) f[g] -= placed[g];  // GPUs.Allocate (allocate.go:102-118)
+    const bool valid = g < G;
+    const int fr = valid ? cm.fr : 0;
+    reinterpret_cast<uint16_t*>(g < 4 ? &S.fA[r] : &S.fB[r])[g & 3] = (uint16_t)fr;
+    bp.T.free[(size_t)row * 8 + g] = fr;  // 8 lanes: one 32 B row store
+    // both rates of the new state (Rate is a function of the row only, allocate.go:96)
+    const int sumf = __reduce_add_sync(0xFFu, fr);
+    const int cnt100 = __popc(__ballot_sync(0xFFu, valid && fr == 100));
+    if (g == 0) {
+        const double usage = __ddiv_rn((double)(100 * G - sumf), (double)(100 * G));       // allocate.go:164-171
+        S.scB[r] = __double2int_rz(__dmul_rn(usage, 100.0)) + load_int * 50 - G;           // rater.go:69
+        S.scS[r] = 100 * cnt100 + sumf / 10 - G - load_int;                                // rater.go:122
+        bp.T.tag[row] = 0;  // node.go:82
+        bp.node_out[p] = (int32_t)(bp.T.first + row);
+        bp.score_out[p] = score;
     }
-#pragma unroll
-    for (int g = 0; g < 8; g++) cm.f[g] = f[g];
-    cm.fA.x = (uint32_t)f[0] | ((uint32_t)f[1] << 16); cm.fA.y = (uint32_t)f[2] | ((uint32_t)f[3] << 16);
-    cm.fB.x = (uint32_t)f[4] | ((uint32_t)f[5] << 16); cm.fB.y = (uint32_t)f[6] | ((uint32_t)f[7] << 16);
-    cm.scB = rate_binpack(f, G, load_int);
-    cm.scS = rate_spread(f, G, load_int);
-}
-
-// publish a winning decision: shared row, cached rates, the global table and the pod's outputs
-__device__ __forceinline__ void publish_commit(const BatchParams& bp, const SmemRows& S, uint32_t r, uint32_t row,
-                                               const SortedDemand* dem, uint32_t p, int score, const Commit& cm) {
-    S.fA[r] = cm.fA;
-    S.fB[r] = cm.fB;
-    S.scB[r] = cm.scB;
-    S.scS[r] = cm.scS;
-    int4* gp = reinterpret_cast<int4*>(bp.T.free + (size_t)row * 8);
-    gp[0] = make_int4(cm.f[0], cm.f[1], cm.f[2], cm.f[3]);
-    gp[1] = make_int4(cm.f[4], cm.f[5], cm.f[6], cm.f[7]);
-    bp.T.tag[row] = 0;  // node.go:82
-    bp.node_out[p] = (int32_t)(bp.T.first + row);
-    bp.score_out[p] = score;
     int32_t* out = bp.gpu_idx_out + (size_t)p * bp.max_c;
     const int C = dem->C;
-    const bool sorted_policy = dem->policy != NGS_POLICY_RANDOM;
-    for (int k = C; k < bp.max_c; k++) out[k] = INT32_MIN;
-    for (int k = 0; k < C; k++) {  // rater.go:102-105: un-permute the emission order
+    for (int k = g; k < bp.max_c; k += 8) {
+        if (k >= C) out[k] = INT32_MIN;
+    }
+    for (int k = g; k < C; k += 8) {  // rater.go:102-105: un-permute the emission order
         const int e = (int)((cm.emit >> (4 * k)) & 0xF);
-        out[sorted_policy ? dem->order[k] : k] = e == 0xF ? NGS_NOT_NEED_GPU : e;
+        out[dem->order[k]] = e == 0xF ? NGS_NOT_NEED_GPU : e;
+    }
+}
+
+// thread-serial publish for the random policy (plan search without sorting)
+__device__ __forceinline__ void publish_sample(const BatchParams& bp, const SmemRows& S, uint32_t r, uint32_t row,
+                                               const SortedDemand* dem, uint32_t p) {
+    const uint32_t meta = S.meta[r];
+    const int G = (meta >> 24) & 15;
+    const int load_int = (int)(meta >> 28);
+    int f[8];
+    unpack_free(S.fA[r], S.fB[r], f);
+    uint64_t emit = 0;
+    int n_emit = 0;
+    choose_sample<true>(f, G, dem, &emit, &n_emit);  // places on f directly
+    uint2 a, b;
+    a.x = (uint32_t)f[0] | ((uint32_t)f[1] << 16); a.y = (uint32_t)f[2] | ((uint32_t)f[3] << 16);
+    b.x = (uint32_t)f[4] | ((uint32_t)f[5] << 16); b.y = (uint32_t)f[6] | ((uint32_t)f[7] << 16);
+    S.fA[r] = a;
+    S.fB[r] = b;
+    S.scB[r] = rate_binpack(f, G, load_int);
+    S.scS[r] = rate_spread(f, G, load_int);
+    int4* gp = reinterpret_cast<int4*>(bp.T.free + (size_t)row * 8);
+    gp[0] = make_int4(f[0], f[1], f[2], f[3]);
+    gp[1] = make_int4(f[4], f[5], f[6], f[7]);
+    bp.T.tag[row] = 0;
+    bp.node_out[p] = (int32_t)(bp.T.first + row);
+    bp.score_out[p] = 100;  // SampleRater.Rate (rater.go:24-26)
+    int32_t* out = bp.gpu_idx_out + (size_t)p * bp.max_c;
+    for (int k = 0; k < bp.max_c; k++) {
+        const int e = (int)((emit >> (4 * k)) & 0xF);
+        out[k] = k < dem->C ? (e == 0xF ? NGS_NOT_NEED_GPU : e) : INT32_MIN;
     }
 }
 
@@ -478,21 +474,61 @@ __device__ __forceinline__ void publish_none(const BatchParams& bp, uint32_t p) 
     for (int k = 0; k < bp.max_c; k++) bp.gpu_idx_out[(size_t)p * bp.max_c + k] = INT32_MIN;
 }
 
+// grid-wide exchange: every CTA stores its 64-bit slot, then bumps the pod's arrival counter
+// with release semantics; one lane per CTA spins (acquire) on that single word, after which the
+// slots are read once.  Bounded: gives up and raises the batch's error word after ~1 s.
+__device__ __forceinline__ void post_slot(unsigned long long* slot, unsigned long long v, uint32_t* done) {
+    st_relaxed_u64(slot, v | KEY_VALID);
+    asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(done) : "memory");
+}
+// The arrival counter is only a cheap thing to spin on (one word, one lane per CTA): it is not
+// ordered against the slot stores, so readers still check each slot's VALID bit (read_slot).
+__device__ __forceinline__ bool wait_done(const uint32_t* done, uint32_t target, int32_t* err) {
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(done) : "memory");
+    if (v >= target) return true;
+    const long long t0 = clock64();
+    uint32_t spins = 0;
+    for (;;) {
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(done) : "memory");
+        if (v >= target) return true;
+        if ((++spins & 255u) == 0) {
+            if (*reinterpret_cast<volatile int32_t*>(err) != 0 || clock64() - t0 > SPIN_TIMEOUT_CYCLES) {
+                atomicCAS(err, 0, NGS_ERR_TIMEOUT);
+                return false;
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ unsigned long long read_slot(const unsigned long long* slot, bool dead) {
+    unsigned long long v = ld_relaxed_u64(slot);
+    while (!(v & KEY_VALID) && !dead) v = ld_relaxed_u64(slot);  // normally valid at the first read
+    return v & ~KEY_VALID;
+}
+
 // K6.  One CTA per SM (cooperative launch, so every CTA is resident), each owning a contiguous
 // node range held in shared memory for the whole batch.  Per pod, in order:
-//   1. every thread filters its rows for the pod's demand (Rate is a function of the row only,
-//      allocate.go:96, so both policies' rates are kept beside the row and refreshed on bind);
-//   2. block arg-max -> one 64-bit key per CTA posted to keys[p][cta]; warp 0 of every CTA polls
-//      the pod's key row until all CTAs have posted and reduces it: the same winner everywhere,
-//      one L2 round trip, no atomics;  (random policy: feasible counts + seeded k-th pick)
-//   3. the CTA owning the winning row binds it; no other CTA ever reads that row.
+//   1. filter: one thread per row settles feasibility with the exact shortcuts of classify_row;
+//      the few rows they leave open are queued and searched exactly, 8 lanes per row
+//      (choose_group8).  Rate is a function of the row only (allocate.go:96), so both policies'
+//      rates sit beside the row and are refreshed when the row changes.
+//   2. arg-max: block reduce -> one 64-bit key per CTA -> slot + arrival counter in L2; while the
+//      other CTAs' keys are in flight, 8 lanes of warp 0 work out the exact plan of this CTA's
+//      best row.  Every CTA then reads all slots and finds the same winner.
+//      (random policy: slots carry feasible counts; seeded k-th pick over the feasible set)
+//   3. bind: the CTA owning the winning row publishes its plan; no other CTA ever reads that row.
 __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ SortedDemand s_dem[2];
     __shared__ uint64_t s_red[32];
+    __shared__ uint32_t s_qn;
     __shared__ int s_abort;
     const uint32_t rpb = bp.rows_per_block;
-    if (threadIdx.x == 0) s_abort = 0;
+    if (threadIdx.x == 0) {
+        s_abort = 0;
+        s_qn = 0;
+    }
     SmemRows S;
     S.fA = reinterpret_cast<uint2*>(smem_raw);
     S.fB = S.fA + rpb;
@@ -500,11 +536,13 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     S.scB = reinterpret_cast<int32_t*>(S.meta + rpb);
     S.scS = S.scB + rpb;
     S.feasbits = reinterpret_cast<uint32_t*>(S.scS + rpb);
+    S.queue = reinterpret_cast<uint16_t*>(S.feasbits + (rpb + 31) / 32);
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
     const uint32_t row0 = blockIdx.x * rpb;
     const uint32_t my_rows = row0 < bp.T.n ? min(rpb, bp.T.n - row0) : 0u;
     const Tables& T = bp.T;
+    const int g = lane & 7, gbase = lane & 24;
 
     // ---- prologue: rows -> shared memory (and the load-aware quantities, frozen for the batch) ----
     for (uint32_t r = tid; r < my_rows; r += blockDim.x) {
@@ -526,9 +564,9 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                 const uint4 t0 = __ldcg(reinterpret_cast<const uint4*>(T.ts + off));
                 const uint4 t1 = __ldcg(reinterpret_cast<const uint4*>(T.ts + off + 4));
 #pragma unroll
-                for (int g = 0; g < 4; g++) {
-                    tenths[m][g] = (uint8_t)(t8.x >> (8 * g));
-                    tenths[m][g + 4] = (uint8_t)(t8.y >> (8 * g));
+                for (int c = 0; c < 4; c++) {
+                    tenths[m][c] = (uint8_t)(t8.x >> (8 * c));
+                    tenths[m][c + 4] = (uint8_t)(t8.y >> (8 * c));
                 }
                 ts[m][0] = t0.x; ts[m][1] = t0.y; ts[m][2] = t0.z; ts[m][3] = t0.w;
                 ts[m][4] = t1.x; ts[m][5] = t1.y; ts[m][6] = t1.z; ts[m][7] = t1.w;
@@ -537,14 +575,14 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
         } else {
             const uint2 r8 = __ldcg(reinterpret_cast<const uint2*>(T.rl + (size_t)row * 8));
 #pragma unroll
-            for (int g = 0; g < 4; g++) {
-                rlc[g] = (int)(int8_t)(r8.x >> (8 * g)) + 2;
-                rlc[g + 4] = (int)(int8_t)(r8.y >> (8 * g)) + 2;
+            for (int c = 0; c < 4; c++) {
+                rlc[c] = (int)(int8_t)(r8.x >> (8 * c)) + 2;
+                rlc[c + 4] = (int)(int8_t)(r8.y >> (8 * c)) + 2;
             }
         }
         uint32_t meta = ((uint32_t)G << 24) | ((uint32_t)load_int << 28);
 #pragma unroll
-        for (int g = 0; g < 8; g++) meta |= (uint32_t)(g < G ? rlc[g] : 2) << (3 * g);
+        for (int c = 0; c < 8; c++) meta |= (uint32_t)(c < G ? rlc[c] : 2) << (3 * c);
         uint2 pa, pb;
         pa.x = (uint32_t)f[0] | ((uint32_t)f[1] << 16); pa.y = (uint32_t)f[2] | ((uint32_t)f[3] << 16);
         pb.x = (uint32_t)f[4] | ((uint32_t)f[5] << 16); pb.y = (uint32_t)f[6] | ((uint32_t)f[7] << 16);
@@ -558,11 +596,23 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
         reinterpret_cast<uint32_t*>(&s_dem[0])[tid] = reinterpret_cast<const uint32_t*>(&bp.dem[0])[tid];
     __syncthreads();
 
+#ifdef NGS_PHASE_TIMING
+    long long ph[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long tq = clock64();
+#define PHASE(i) do { const long long t_ = clock64(); ph[i] += t_ - tq; tq = t_; } while (0)
+// BAR.SYNC blocks lazily (at the first instruction that needs the barrier): consume a shared word
+// before reading the clock so that the wait lands in the phase it belongs to
+#define PHASE_AFTER_BARRIER(i) do { if (*reinterpret_cast<volatile int*>(&s_abort) == 0x7fffffff) ph[7]++; PHASE(i); } while (0)
+#else
+#define PHASE(i) do { } while (0)
+#define PHASE_AFTER_BARRIER(i) do { } while (0)
+#endif
     const uint32_t n_iter = (my_rows + blockDim.x - 1) / blockDim.x;
     bool rl_pending = bp.lp.enabled != 0;  // RemainLoad write-back of the first load-aware Rate
     for (uint32_t p = 0; p < bp.P; p++) {
         const SortedDemand* dem = &s_dem[p & 1];
         const int policy = dem->policy;
+        const bool spread = policy == NGS_POLICY_SPREAD;
         if (rl_pending && policy != NGS_POLICY_RANDOM) {
             // allocate.go:193: LoadUsage leaves RemainLoad in the live node state.  SampleRater.Rate
             // never calls it, so the table is only touched once a binpack/spread pod comes by.
@@ -574,9 +624,9 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                 uint2 out;
                 out.x = out.y = 0;
 #pragma unroll
-                for (int g = 0; g < 4; g++) {
-                    out.x |= (uint32_t)(uint8_t)(int8_t)(g < G ? (int)((meta >> (3 * g)) & 7) - 2 : 0) << (8 * g);
-                    out.y |= (uint32_t)(uint8_t)(int8_t)(g + 4 < G ? (int)((meta >> (3 * (g + 4))) & 7) - 2 : 0) << (8 * g);
+                for (int c = 0; c < 4; c++) {
+                    out.x |= (uint32_t)(uint8_t)(int8_t)(c < G ? (int)((meta >> (3 * c)) & 7) - 2 : 0) << (8 * c);
+                    out.y |= (uint32_t)(uint8_t)(int8_t)(c + 4 < G ? (int)((meta >> (3 * (c + 4))) & 7) - 2 : 0) << (8 * c);
                 }
                 *reinterpret_cast<uint2*>(T.rl + (size_t)(row0 + r) * 8) = out;
             }
@@ -589,47 +639,91 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
         // ---- 1. filter + score my rows ----
         uint64_t best = 0;
         uint32_t cnt = 0;
-        for (uint32_t it = 0; it < n_iter; it++) {
-            const uint32_t r = it * blockDim.x + tid;
-            bool ok = false;
-            if (r < my_rows) ok = eval_row_smem(S, r, dem, policy);
-            if (policy == NGS_POLICY_RANDOM) {
+        if (policy == NGS_POLICY_RANDOM) {
+            for (uint32_t it = 0; it < n_iter; it++) {
+                const uint32_t r = it * blockDim.x + tid;
+                const bool ok = r < my_rows && eval_row_sample(S, r, dem);
                 const uint32_t bal = __ballot_sync(0xFFFFFFFFu, ok);
                 if (lane == 0 && r < my_rows) {
                     S.feasbits[r >> 5] = bal;
                     cnt += __popc(bal);
                 }
-            } else if (ok) {
-                const int sc = policy == NGS_POLICY_BINPACK ? S.scB[r] : S.scS[r];
-                const uint64_t key = make_key(sc, T.first + row0 + r);
-                best = key > best ? key : best;
             }
-        }
-        // ---- 2. block reduce, post, gather ----
-        if (policy == NGS_POLICY_RANDOM) {
+            PHASE(0);
             if (lane == 0) s_red[warp] = cnt;
         } else {
+            // 1a. one thread per row: exact shortcuts; undecided rows go to the queue
+            for (uint32_t it = 0; it < n_iter; it++) {
+                const uint32_t r = it * blockDim.x + tid;
+                int cls = FEAS_NO;
+                if (r < my_rows) {
+                    const uint32_t meta = S.meta[r];
+                    if (((meta >> 24) & 15) != 0) {
+                        int f[8];
+                        unpack_free(S.fA[r], S.fB[r], f);
+                        cls = classify_row(f, dem, true);
+                    }
+                }
+                if (cls == FEAS_YES) {
+                    const int sc = spread ? S.scS[r] : S.scB[r];
+                    const uint64_t key = make_key(sc, T.first + row0 + r);
+                    best = key > best ? key : best;
+                }
+                const uint32_t und = __ballot_sync(0xFFFFFFFFu, cls == FEAS_UNDECIDED);
+                if (und) {
+                    uint32_t base = 0;
+                    if (lane == 0) base = atomicAdd(&s_qn, __popc(und));
+                    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                    if (cls == FEAS_UNDECIDED) S.queue[base + __popc(und & ((1u << lane) - 1u))] = (uint16_t)r;
+                }
+            }
+            PHASE(0);
+            __syncthreads();
+            PHASE_AFTER_BARRIER(1);
+            // 1b. exact search of the queued rows, 8 lanes per row
+            const uint32_t n_q = s_qn;
+            for (uint32_t q0 = warp * 4; q0 < n_q; q0 += nwarps * 4) {
+                const uint32_t e = q0 + (lane >> 3);
+                const bool has = e < n_q;
+                const uint32_t r = has ? S.queue[e] : 0u;
+                const uint32_t meta = S.meta[r];
+                const int G = has ? (int)((meta >> 24) & 15) : 0;
+                const bool ok = choose_group8<false>(g, gbase, smem_cell(S, r, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem,
+                                                     nullptr, nullptr, nullptr);
+                if (has && ok && g == 0) {
+                    const int sc = spread ? S.scS[r] : S.scB[r];
+                    const uint64_t key = make_key(sc, T.first + row0 + r);
+                    best = key > best ? key : best;
+                }
+            }
+            PHASE(2);
             best = warp_max_u64(best);
             if (lane == 0) s_red[warp] = best;
         }
         __syncthreads();
+        PHASE_AFTER_BARRIER(3);
+        // ---- 2. block reduce, post, gather ----
         if (warp == 0) {
             bool dead = false;
             unsigned long long* krow = bp.keys + (size_t)p * gridDim.x;
+            uint32_t* done = bp.done + p;
             uint64_t v = lane < nwarps ? s_red[lane] : 0;
+            if (lane == 0) s_qn = 0;  // the queue is drained; next pod starts empty
             if (policy == NGS_POLICY_RANDOM) {
                 uint32_t c = (uint32_t)v;
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, o);
-                if (lane == 0) st_relaxed_u64(krow + blockIdx.x, KEY_VALID | c);
+                if (lane == 0) {
+                    post_slot(krow + blockIdx.x, c, done);
+                    dead = !wait_done(done, gridDim.x, bp.err);
+                }
+                __syncwarp();
                 // contiguous chunk of CTAs per lane so that a prefix over lanes is a prefix over CTAs
                 const uint32_t chunk = (gridDim.x + 31) / 32;
                 const uint32_t j0 = min(lane * chunk, gridDim.x), j1 = min(j0 + chunk, gridDim.x);
                 uint64_t sum = 0;
-                for (uint32_t j = j0; j < j1; j++) {
-                    const unsigned long long kv = poll_key(krow + j, bp.err, dead);
-                    sum += kv & 0xFFFFFFFFull;
-                }
+                dead = __any_sync(0xFFFFFFFFu, dead);
+                for (uint32_t j = j0; j < j1; j++) sum += read_slot(krow + j, dead);
                 uint64_t incl = sum;
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
@@ -645,7 +739,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                     uint64_t run = incl - sum;
                     long long local_rank = -1;
                     for (uint32_t j = j0; j < j1; j++) {
-                        const uint64_t cj = ld_relaxed_u64(krow + j) & 0xFFFFFFFFull;
+                        const uint64_t cj = read_slot(krow + j, dead);
                         if (j == blockIdx.x && pick >= run && pick < run + cj) local_rank = (long long)(pick - run);
                         run += cj;
                     }
@@ -657,16 +751,16 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                         const uint32_t nwords = (my_rows + 31) / 32;
                         const uint32_t wchunk = (nwords + 31) / 32;
                         const uint32_t w0 = min(lane * wchunk, nwords), w1 = min(w0 + wchunk, nwords);
-                        uint32_t s = 0;
-                        for (uint32_t wi = w0; wi < w1; wi++) s += __popc(S.feasbits[wi]);
-                        uint32_t inc = s;
+                        uint32_t sb = 0;
+                        for (uint32_t wi = w0; wi < w1; wi++) sb += __popc(S.feasbits[wi]);
+                        uint32_t inc = sb;
 #pragma unroll
                         for (int o = 1; o < 32; o <<= 1) {
                             const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
                             if (lane >= (uint32_t)o) inc += t;
                         }
-                        uint32_t before = inc - s;
-                        if (rank >= before && rank < before + s) {
+                        const uint32_t before = inc - sb;
+                        if (rank >= before && rank < before + sb) {
                             uint32_t need = rank - before;
                             for (uint32_t wi = w0; wi < w1; wi++) {
                                 uint32_t bits = S.feasbits[wi];
@@ -674,9 +768,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                                 if (need < pc) {
                                     for (uint32_t q = 0; q < need; q++) bits &= bits - 1;
                                     const uint32_t r = wi * 32 + (__ffs(bits) - 1);
-                                    Commit cm;
-                                    plan_row_smem(S, r, dem, cm);
-                                    publish_commit(bp, S, r, row0 + r, dem, p, 100, cm);
+                                    publish_sample(bp, S, r, row0 + r, dem, p);
                                     break;
                                 }
                                 need -= pc;
@@ -686,32 +778,74 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                 }
             } else {
                 v = warp_max_u64(v);
-                if (lane == 0) st_relaxed_u64(krow + blockIdx.x, KEY_VALID | v);
-                // while the other CTAs' keys are in flight, lane 0 works out the exact plan of this
+                if (lane == 0) post_slot(krow + blockIdx.x, v, done);
+                PHASE(4);
+#ifdef NGS_PHASE_TIMING
+                if (lane == 0 && bp.dbg && p < 256) {
+                    unsigned long long gt;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+                    bp.dbg[4096 + ((size_t)p * 256 + blockIdx.x) * 4 + 0] = gt;
+                }
+#endif
+                // while the other CTAs' keys are in flight, 8 lanes work out the exact plan of this
                 // CTA's best row; it is published only if that row turns out to be the global winner
-                Commit cm;
-                const uint32_t my_r = key_node(v) - T.first - row0;
-                if (lane == 0 && (v & KEY_FEASIBLE)) plan_row_smem(S, my_r, dem, cm);
+                GroupCommit cm;
+                cm.fr = 0;
+                cm.emit = 0;
+                cm.n_emit = 0;
+                const bool have = (v & KEY_FEASIBLE) != 0;
+                const uint32_t my_r = have ? key_node(v) - T.first - row0 : 0u;
+                if (have) {  // all four groups search the same row; group 0's copy is the one published
+                    const uint32_t meta = S.meta[my_r];
+                    const int G = (meta >> 24) & 15;
+                    choose_group8<true>(g, gbase, smem_cell(S, my_r, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem, &cm.emit,
+                                        &cm.n_emit, &cm.fr);
+                }
+                PHASE(5);
+                if (lane == 0) dead = !wait_done(done, gridDim.x, bp.err);
+                dead = __any_sync(0xFFFFFFFFu, dead);
                 uint64_t m = 0;
                 for (uint32_t j = lane; j < gridDim.x; j += 32) {
-                    const unsigned long long kv = poll_key(krow + j, bp.err, dead);
+                    const unsigned long long kv = read_slot(krow + j, dead);
                     m = kv > m ? kv : m;
                 }
                 m = warp_max_u64(m);
-                if (lane == 0) {
-                    if (!(m & KEY_FEASIBLE)) {
-                        if (blockIdx.x == 0) publish_none(bp, p);
-                    } else if (m == (v | KEY_VALID)) {
-                        // ---- 3. bind on the owner ----
-                        publish_commit(bp, S, my_r, row0 + my_r, dem, p, key_score(m), cm);
-                    }
+                PHASE(6);
+#ifdef NGS_PHASE_TIMING
+                if (lane == 0 && bp.dbg && p < 256) {
+                    unsigned long long gt;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+                    bp.dbg[4096 + ((size_t)p * 256 + blockIdx.x) * 4 + 1] = gt;
+                    bp.dbg[4096 + ((size_t)p * 256 + blockIdx.x) * 4 + 3] = (have && m == v) ? 1 : 0;
                 }
+#endif
+                if (!(m & KEY_FEASIBLE)) {
+                    if (blockIdx.x == 0 && lane == 0) publish_none(bp, p);
+                } else if (have && m == v && lane < 8) {
+                    // ---- 3. bind on the owner ----
+                    publish_group(bp, S, my_r, row0 + my_r, dem, p, key_score(m), cm, g);
+                }
+#ifdef NGS_PHASE_TIMING
+                __syncwarp();
+                if (lane == 0 && bp.dbg && p < 256) {
+                    unsigned long long gt;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+                    bp.dbg[4096 + ((size_t)p * 256 + blockIdx.x) * 4 + 2] = gt;
+                }
+#endif
             }
-            if (__any_sync(0xFFFFFFFFu, dead) && lane == 0) s_abort = 1;
+            if (dead && lane == 0) s_abort = 1;
         }
         __syncthreads();
+        PHASE_AFTER_BARRIER(7);
         if (s_abort) break;  // a peer CTA never posted: give up instead of hanging the GPU
     }
+#ifdef NGS_PHASE_TIMING
+    if (tid == 0 && bp.dbg)
+        for (int i = 0; i < 8; i++) bp.dbg[blockIdx.x * 16 + i] = (unsigned long long)ph[i];
+    if (tid == 32 && bp.dbg)
+        for (int i = 0; i < 8; i++) bp.dbg[blockIdx.x * 16 + 8 + i] = (unsigned long long)ph[i];
+#endif
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -754,6 +888,8 @@ struct ngs_dealer {
     int32_t* d_err = nullptr;
     int32_t* h_err = nullptr;
     ngs_stats_t stats{};
+    unsigned long long* d_dbg = nullptr;  // profiling builds only
+    uint32_t dbg_grid = 0;
     char err[512] = {0};
 };
 
@@ -856,7 +992,8 @@ int ensure_batch(ngs_dealer* h) {
     const uint32_t cap = BATCH_CHUNK;
     const size_t in_words = (size_t)cap * (NGS_MAX_CONTAINERS + 2), out_words = (size_t)cap * (NGS_MAX_CONTAINERS + 2);
     CU(h, cudaMalloc(&h->d_dem, sizeof(SortedDemand) * cap));
-    CU(h, cudaMalloc(&h->d_keys, sizeof(unsigned long long) * cap * h->num_sms));
+    // key slots [cap][num_sms] followed by the arrival counters [cap]
+    CU(h, cudaMalloc(&h->d_keys, sizeof(unsigned long long) * cap * h->num_sms + sizeof(uint32_t) * cap));
     CU(h, cudaMalloc(&h->d_pod_in, in_words * 4));
     CU(h, cudaMalloc(&h->d_pod_out, out_words * 4));
     CU(h, cudaMallocHost(&h->h_pod_in, in_words * 4));
@@ -877,13 +1014,15 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     uint32_t block = ((rpb + 31) / 32) * 32;
     if (block < 64) block = 64;
     if (block > 1024) block = 1024;
-    const size_t smem = (size_t)rpb * 28 + (size_t)((rpb + 31) / 32) * 4 + 16;
+    const size_t smem = (size_t)rpb * 30 + (size_t)((rpb + 31) / 32) * 4 + 16;  // rows + feasbits + queue
     if (smem > (size_t)h->smem_optin)
         return fail(h, NGS_ERR_UNSUPPORTED, "%u rows per SM need %zu B shared memory (> %d): shard the cluster over more GPUs", rpb, smem, h->smem_optin);
     CU(h, cudaFuncSetAttribute(k_schedule, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_prep_demands<<<(P + 127) / 128, 128, 0, h->stream>>>(d_percent, d_ncont, max_c, d_policy, P, h->d_dem, h->d_err);
     CU(h, cudaGetLastError());
+    uint32_t* d_done = reinterpret_cast<uint32_t*>(h->d_keys + (size_t)h->batch_cap * h->num_sms);
     CU(h, cudaMemsetAsync(h->d_keys, 0, sizeof(unsigned long long) * (size_t)P * grid, h->stream));
+    CU(h, cudaMemsetAsync(d_done, 0, sizeof(uint32_t) * (size_t)P, h->stream));
     BatchParams bp;
     bp.T = h->T;
     bp.dem = h->d_dem;
@@ -895,8 +1034,15 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     bp.gpu_idx_out = d_gidx;
     bp.max_c = max_c;
     bp.keys = h->d_keys;
+    bp.done = d_done;
     bp.err = h->d_err;
     bp.rows_per_block = rpb;
+#ifdef NGS_PHASE_TIMING
+    if (!h->d_dbg) CU(h, cudaMalloc(&h->d_dbg, sizeof(unsigned long long) * (4096 + 256 * 256 * 4)));
+    CU(h, cudaMemsetAsync(h->d_dbg, 0, sizeof(unsigned long long) * (4096 + 256 * 256 * 4), h->stream));
+    bp.dbg = h->d_dbg;
+    h->dbg_grid = grid;
+#endif
     void* args[] = {&bp};
     CU(h, cudaLaunchCooperativeKernel((void*)k_schedule, dim3(grid), dim3(block), args, smem, h->stream));
     h->stats.kernel_launches += 2;
@@ -1015,6 +1161,17 @@ int ngs_sync(ngs_dealer* h) {
     CU(h, cudaStreamSynchronize(h->stream));
     return check_dev_err(h);
 }
+
+#ifdef NGS_PHASE_TIMING
+// profiling builds only: per-CTA cycles per phase of the last k_schedule launch ([grid][16])
+int ngs_debug_phases(ngs_dealer* h, unsigned long long* out, uint32_t* grid) {
+    if (!h || !h->d_dbg) return NGS_ERR_INVALID;
+    CU(h, cudaMemcpyAsync(out, h->d_dbg, sizeof(unsigned long long) * (4096 + 256 * 256 * 4), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    *grid = h->dbg_grid;
+    return NGS_OK;
+}
+#endif
 
 int ngs_stats(ngs_dealer* h, ngs_stats_t* out) {
     if (!h || !out) return NGS_ERR_INVALID;

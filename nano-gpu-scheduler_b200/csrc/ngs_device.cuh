@@ -233,6 +233,91 @@ __device__ __forceinline__ bool choose_sorted(uint32_t (&w)[8], int G, bool spre
     return ok;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Binpack.Choose / Spread.Choose with one GPU cell per lane (8 lanes = one node, 4 nodes per
+// warp).  The O(G^2) comparisons of the re-sort are spread over the G lanes: each lane counts the
+// cells that sort before its own (7 shuffles), which is exactly the position the stable
+// insertion sort gives it.  `pos` persists between containers, as the slice does in the
+// reference.  All 32 lanes of the warp must call this together (the four groups may look at four
+// different rows); every warp-synchronous op runs with the full mask and only ever exchanges
+// data inside the caller's 8-lane group, and no such op sits under divergent control flow.
+//   g      cell index (lane & 7)        gbase   first lane of the group (lane & 24)
+//   fr     free percent of the cell (cells >= G: anything)   rlc   RemainLoad + 2
+// Returns feasibility; with PLAN the emission list (4 bits per entry, GPU index, 0xF =
+// NotNeedGPU) and, in *fr_out, the cell's free percent after GPUs.Allocate.
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t FULL = 0xFFFFFFFFu;
+template <bool PLAN>
+__device__ __forceinline__ bool choose_group8(int g, int gbase, int fr, int rlc, bool valid, bool spread, const SortedDemand* dem,
+                                              uint64_t* emit, int* n_emit, int* fr_out) {
+    uint32_t key = valid ? (uint32_t)(fr + 50 * rlc + 28) : 0x0FFFFFFFu;  // biased key; padding sorts last
+    if (!valid) fr = -1;                                                   // and never fits
+    int pos = g;
+    const int nz = dem->nz;
+    bool ok = true;
+    uint64_t em = 0;
+    int ne = 0;
+    for (int k = 0; k < nz; k++) {
+        const int d = dem->d[k];
+        if (!PLAN && k == nz - 1) {  // last container, feasibility only: any cell that fits will do
+            // (the ballot must not sit behind the short-circuit of `ok &&`: every lane has to take part)
+            const uint32_t anyfit = (__ballot_sync(FULL, fr >= d) >> gbase) & 0xFFu;
+            ok = ok && anyfit != 0u;
+            break;
+        }
+        // gap-6 pass of Go 1.16 sort.Sort on the current arrangement: (6,0) then (7,1)
+        const uint32_t b0 = (__ballot_sync(FULL, pos == 0) >> gbase) & 0xFFu;
+        const uint32_t b1 = (__ballot_sync(FULL, pos == 1) >> gbase) & 0xFFu;
+        const uint32_t b6 = (__ballot_sync(FULL, pos == 6) >> gbase) & 0xFFu;
+        const uint32_t b7 = (__ballot_sync(FULL, pos == 7) >> gbase) & 0xFFu;
+        const uint32_t k0 = __shfl_sync(FULL, key, gbase + __ffs(b0) - 1);
+        const uint32_t k1 = __shfl_sync(FULL, key, gbase + __ffs(b1) - 1);
+        const uint32_t k6 = __shfl_sync(FULL, key, gbase + __ffs(b6) - 1);
+        const uint32_t k7 = __shfl_sync(FULL, key, gbase + __ffs(b7) - 1);
+        const bool s06 = k6 < k0, s17 = k7 < k1;
+        int np = pos;
+        np = (s06 && pos == 0) ? 6 : np;
+        np = (s06 && pos == 6) ? 0 : np;
+        np = (s17 && pos == 1) ? 7 : np;
+        np = (s17 && pos == 7) ? 1 : np;
+        // insertion sort (stable): new position = number of cells ordered before this one
+        const uint32_t c = (key << 3) | (uint32_t)np;
+        int rank = 0;
+#pragma unroll
+        for (int sft = 1; sft < 8; sft++) rank += __shfl_xor_sync(FULL, c, sft) < c ? 1 : 0;
+        pos = rank;
+        // first fit from the low end (binpack, rater.go:88) or the high end (spread, rater.go:141):
+        // min (max) position over the cells that fit, by a 3-step butterfly inside the group
+        const bool fit = fr >= d;
+        int v = fit ? (spread ? pos : 7 - pos) : -1;  // larger is better in both cases
+        v = max(v, __shfl_xor_sync(FULL, v, 1));
+        v = max(v, __shfl_xor_sync(FULL, v, 2));
+        v = max(v, __shfl_xor_sync(FULL, v, 4));
+        const int sel = spread ? v : 7 - v;  // 8 / -1 when nothing fits: matches no position
+        const bool chosen = fit && pos == sel;
+        ok = ok && v >= 0;
+        fr -= chosen ? d : 0;
+        key -= chosen ? (uint32_t)d : 0u;
+        if (PLAN) {
+            const uint32_t cb = (__ballot_sync(FULL, chosen) >> gbase) & 0xFFu;
+            if (cb) {
+                em |= (uint64_t)(__ffs(cb) - 1) << (4 * ne);
+                ne++;
+            }
+        }
+    }
+    if (PLAN) {
+        for (int k = nz; k < dem->C; k++) {  // zero-percent containers: NotNeedGPU (rater.go:83-86)
+            em |= (uint64_t)0xF << (4 * ne);
+            ne++;
+        }
+        *emit = em;
+        *n_emit = ne;
+        *fr_out = fr;
+    }
+    return ok;
+}
+
 // SampleRater.Choose: containers in pod order, GPUs in index order, no sorting.
 template <bool PLAN>
 __device__ __forceinline__ bool choose_sample(int (&f)[8], int G, const SortedDemand* dem, uint64_t* emit, int* n_emit) {

@@ -1,0 +1,77 @@
+#!/usr/bin/env python
+"""Per-phase cycle breakdown of k_schedule (profiling build with -DNGS_PHASE_TIMING).
+
+usage (on a GPU box):  python profiles/tools/phase_timing.py [workload] [pods]
+Builds nano-gpu-scheduler_b200/libngs_dealer_dbg.so, runs one batch and prints, for thread 0
+(warp 0: control path) and thread 32 (a plain worker) the average cycles per pod per phase,
+as min / median / max over CTAs."""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+PKG = os.path.join(ROOT, "nano-gpu-scheduler_b200")
+DBG = os.path.join(PKG, "libngs_dealer_dbg.so")
+subprocess.run(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-shared", "-Xcompiler", "-fPIC",
+                "-diag-suppress", "177", "-DNGS_PHASE_TIMING", "-o", DBG, os.path.join(PKG, "csrc", "ngs_dealer.cu"),
+                os.path.join(PKG, "csrc", "ngs_parse.cpp")], check=True)
+os.environ["NGS_DEALER_LIB"] = DBG
+import bench  # noqa: E402
+import nano_gpu_scheduler_b200 as ngs  # noqa: E402
+from nano_gpu_scheduler_b200 import workloads as wl  # noqa: E402
+
+name = sys.argv[1] if len(sys.argv) > 1 else "C3"
+P = int(sys.argv[2]) if len(sys.argv) > 2 else 2048
+cfg = bench.workload_spec(name)
+gcount, free, pc, nc, tables = bench.build_inputs(cfg, 0, 1, 2 * P)
+d = ngs.GpuDealer(cfg["nodes"])
+d.snapshot_load(gcount, free)
+load = None
+if cfg["load"]:
+    for m, (value, ts, absent) in enumerate(tables):
+        ok = np.repeat(~absent[:, None], 8, axis=1).astype(np.uint8)
+        d.load_update_bulk(m, value, ts, value_ok=ok, ts_ok=ok)
+    load = ngs.make_load_ctx(wl.DEFAULT_PERIODS, bench.NOW_NS)
+pol = np.full(2 * P, cfg["policy"], dtype=np.int32)
+d.schedule_batch(pc[:P], nc[:P], pol[:P], load=load)
+d.schedule_batch(pc[P:], nc[P:], pol[P:], load=load)
+lib = ngs._abi.load()
+lib.ngs_debug_phases.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)]
+buf = np.zeros(4096 + 256 * 256 * 4, dtype=np.uint64)
+grid = C.c_uint32(0)
+assert lib.ngs_debug_phases(d._h, buf.ctypes.data_as(C.c_void_p), C.byref(grid)) == 0
+g = grid.value
+a = buf[: 16 * g].reshape(g, 16).astype(np.float64) / P
+names = ["classify", "queue barrier", "exact (queue)", "reduce barrier", "reduce+post", "spec plan", "gather", "publish+end"]
+print(f"{name}: {cfg['nodes']} nodes, {P} pods, grid {g}; cycles per pod (min / median / max over CTAs)")
+for who, off in (("thread 0 (control warp)", 0), ("thread 32 (worker)", 8)):
+    print(who)
+    for i in range(8):
+        col = a[:, off + i]
+        print(f"  {names[i]:14s} {col.min():8.0f} {np.median(col):8.0f} {col.max():8.0f}")
+    print(f"  {'total':14s} {a[:, off:off + 8].sum(axis=1).mean():8.0f}")
+
+# cross-CTA skew from %globaltimer stamps of the first 256 pods: [pod][cta][post, arrived, published, owner]
+st = buf[4096:].reshape(256, 256, 4)[:, :g, :].astype(np.int64)
+post, arr, pub, own = st[..., 0], st[..., 1], st[..., 2], st[..., 3]
+ok = post[:, 0] > 0
+print("per pod (ns): spread of post times over CTAs, last-post -> median arrived, owner publish time")
+rows = []
+for p in range(1, 256):
+    if not ok[p]:
+        continue
+    last = int(np.argmax(post[p]))
+    prev_owner = int(np.argmax(own[p - 1])) if own[p - 1].any() else -1
+    rows.append((post[p].max() - np.median(post[p]), np.median(arr[p]) - post[p].max(), last == prev_owner,
+                 (pub[p - 1][prev_owner] - arr[p - 1][prev_owner]) if prev_owner >= 0 else -1,
+                 np.median(post[p]) - np.median(arr[p - 1]), post[p].max() - np.median(arr[p - 1])))
+rows = np.array(rows, dtype=np.float64)
+print(f"  last post - median post      : median {np.median(rows[:, 0]):7.0f} ns   p90 {np.percentile(rows[:, 0], 90):7.0f}")
+print(f"  median arrived - last post   : median {np.median(rows[:, 1]):7.0f} ns")
+print(f"  last poster == previous owner: {rows[:, 2].mean() * 100:5.1f} % of pods")
+print(f"  owner: arrived -> published  : median {np.median(rows[:, 3]):7.0f} ns")
+print(f"  arrived(p-1) -> median post(p): median {np.median(rows[:, 4]):7.0f} ns;  -> last post(p): {np.median(rows[:, 5]):7.0f} ns")
