@@ -338,6 +338,7 @@ struct BatchParams {
     int max_c;
     unsigned long long* keys;  // [P][gridDim.x] one slot per CTA per pod, zero before launch
     uint32_t* done;            // [P] arrival counters, zero before launch
+    unsigned long long* mx;    // [P] arg-max words (atomicMax), zero before launch
     int32_t* err;              // device error word (0 = ok)
     uint32_t rows_per_block;
 #ifdef NGS_PHASE_TIMING
@@ -372,7 +373,6 @@ struct SmemRows {
     int32_t* scB;  // Binpack.Rate of the row's current state
     int32_t* scS;  // Spread.Rate
     uint32_t* feasbits;
-    uint16_t* queue;  // rows whose feasibility the shortcuts could not decide
 };
 
 __device__ __forceinline__ void unpack_free(uint2 a, uint2 b, int (&f)[8]) {
@@ -522,13 +522,10 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ SortedDemand s_dem[2];
     __shared__ uint64_t s_red[32];
-    __shared__ uint32_t s_qn;
+    __shared__ uint64_t s_win;  // the pod's winning key, handed from the exchange warp to the plan warp
     __shared__ int s_abort;
     const uint32_t rpb = bp.rows_per_block;
-    if (threadIdx.x == 0) {
-        s_abort = 0;
-        s_qn = 0;
-    }
+    if (threadIdx.x == 0) s_abort = 0;
     SmemRows S;
     S.fA = reinterpret_cast<uint2*>(smem_raw);
     S.fB = S.fA + rpb;
@@ -536,7 +533,6 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     S.scB = reinterpret_cast<int32_t*>(S.meta + rpb);
     S.scS = S.scB + rpb;
     S.feasbits = reinterpret_cast<uint32_t*>(S.scS + rpb);
-    S.queue = reinterpret_cast<uint16_t*>(S.feasbits + (rpb + 31) / 32);
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
     const uint32_t row0 = blockIdx.x * rpb;
@@ -652,7 +648,8 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
             PHASE(0);
             if (lane == 0) s_red[warp] = cnt;
         } else {
-            // 1a. one thread per row: exact shortcuts; undecided rows go to the queue
+            // one thread per row: exact shortcuts; the rows they leave open are searched right away
+            // by this warp, 8 lanes per row, four rows at a time
             for (uint32_t it = 0; it < n_iter; it++) {
                 const uint32_t r = it * blockDim.x + tid;
                 int cls = FEAS_NO;
@@ -669,47 +666,42 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                     const uint64_t key = make_key(sc, T.first + row0 + r);
                     best = key > best ? key : best;
                 }
-                const uint32_t und = __ballot_sync(0xFFFFFFFFu, cls == FEAS_UNDECIDED);
-                if (und) {
-                    uint32_t base = 0;
-                    if (lane == 0) base = atomicAdd(&s_qn, __popc(und));
-                    base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                    if (cls == FEAS_UNDECIDED) S.queue[base + __popc(und & ((1u << lane) - 1u))] = (uint16_t)r;
+                uint32_t und = __ballot_sync(0xFFFFFFFFu, cls == FEAS_UNDECIDED);
+                while (und) {  // warp-uniform
+                    uint32_t t = und;
+                    for (uint32_t q = 0; q < (lane >> 3); q++) t &= t - 1;  // group j takes the j-th open row
+                    const bool has = t != 0;
+                    const uint32_t rr = __shfl_sync(0xFFFFFFFFu, r, has ? __ffs(t) - 1 : 0);
+                    und &= und - 1;
+                    und &= und - 1;
+                    und &= und - 1;
+                    und &= und - 1;
+                    const uint32_t meta = S.meta[rr];
+                    const int G = has ? (int)((meta >> 24) & 15) : 0;
+                    const bool ok = choose_group8<false>(g, gbase, smem_cell(S, rr, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem,
+                                                         nullptr, nullptr, nullptr);
+                    if (has && ok && g == 0) {
+                        const int sc = spread ? S.scS[rr] : S.scB[rr];
+                        const uint64_t key = make_key(sc, T.first + row0 + rr);
+                        best = key > best ? key : best;
+                    }
                 }
             }
             PHASE(0);
-            __syncthreads();
-            PHASE_AFTER_BARRIER(1);
-            // 1b. exact search of the queued rows, 8 lanes per row
-            const uint32_t n_q = s_qn;
-            for (uint32_t q0 = warp * 4; q0 < n_q; q0 += nwarps * 4) {
-                const uint32_t e = q0 + (lane >> 3);
-                const bool has = e < n_q;
-                const uint32_t r = has ? S.queue[e] : 0u;
-                const uint32_t meta = S.meta[r];
-                const int G = has ? (int)((meta >> 24) & 15) : 0;
-                const bool ok = choose_group8<false>(g, gbase, smem_cell(S, r, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem,
-                                                     nullptr, nullptr, nullptr);
-                if (has && ok && g == 0) {
-                    const int sc = spread ? S.scS[r] : S.scB[r];
-                    const uint64_t key = make_key(sc, T.first + row0 + r);
-                    best = key > best ? key : best;
-                }
-            }
             PHASE(2);
             best = warp_max_u64(best);
             if (lane == 0) s_red[warp] = best;
         }
         __syncthreads();
         PHASE_AFTER_BARRIER(3);
-        // ---- 2. block reduce, post, gather ----
-        if (warp == 0) {
+        // ---- 2. block reduce, exchange, plan ----
+        if (policy == NGS_POLICY_RANDOM) {
+          if (warp == 0) {
             bool dead = false;
             unsigned long long* krow = bp.keys + (size_t)p * gridDim.x;
             uint32_t* done = bp.done + p;
             uint64_t v = lane < nwarps ? s_red[lane] : 0;
-            if (lane == 0) s_qn = 0;  // the queue is drained; next pod starts empty
-            if (policy == NGS_POLICY_RANDOM) {
+            {
                 uint32_t c = (uint32_t)v;
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, o);
@@ -776,65 +768,52 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                         }
                     }
                 }
-            } else {
-                v = warp_max_u64(v);
-                if (lane == 0) post_slot(krow + blockIdx.x, v, done);
-                PHASE(4);
-#ifdef NGS_PHASE_TIMING
-                if (lane == 0 && bp.dbg && p < 256) {
-                    unsigned long long gt;
-                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
-                    bp.dbg[4096 + ((size_t)p * 256 + blockIdx.x) * 4 + 0] = gt;
+            }
+            if (dead && lane == 0) s_abort = 1;
+          }
+        } else if (warp < 2) {
+            // warp 1 runs the exchange while warp 0 works out the exact plan of this CTA's best row
+            // (8 lanes per row); the plan is published only if that row is the global winner
+            uint64_t v = lane < nwarps ? s_red[lane] : 0;
+            v = warp_max_u64(v);
+            const bool have = (v & KEY_FEASIBLE) != 0;
+            const uint32_t my_r = have ? key_node(v) - T.first - row0 : 0u;
+            GroupCommit cm;
+            cm.fr = 0;
+            cm.emit = 0;
+            cm.n_emit = 0;
+            if (warp == 1) {
+                // exchange (fastest variant of profiles/tools/xchg_bench.cu): atomicMax into the pod's
+                // word; the arrival counter is bumped only after that atomic has returned (data
+                // dependence), so a full counter implies every CTA's key is in the word
+                if (lane == 0) {
+                    uint32_t* done = bp.done + p;
+                    const unsigned long long old = atomicMax(bp.mx + p, (unsigned long long)v);
+                    const uint32_t one = 1u + (uint32_t)(old >> 63);  // bit 63 is never set: always 1
+                    asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(done), "r"(one) : "memory");
+                    const bool dead = !wait_done(done, gridDim.x, bp.err);
+                    s_win = ld_relaxed_u64(bp.mx + p);
+                    if (dead) s_abort = 1;
                 }
-#endif
-                // while the other CTAs' keys are in flight, 8 lanes work out the exact plan of this
-                // CTA's best row; it is published only if that row turns out to be the global winner
-                GroupCommit cm;
-                cm.fr = 0;
-                cm.emit = 0;
-                cm.n_emit = 0;
-                const bool have = (v & KEY_FEASIBLE) != 0;
-                const uint32_t my_r = have ? key_node(v) - T.first - row0 : 0u;
-                if (have) {  // all four groups search the same row; group 0's copy is the one published
-                    const uint32_t meta = S.meta[my_r];
-                    const int G = (meta >> 24) & 15;
-                    choose_group8<true>(g, gbase, smem_cell(S, my_r, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem, &cm.emit,
-                                        &cm.n_emit, &cm.fr);
-                }
-                PHASE(5);
-                if (lane == 0) dead = !wait_done(done, gridDim.x, bp.err);
-                dead = __any_sync(0xFFFFFFFFu, dead);
-                uint64_t m = 0;
-                for (uint32_t j = lane; j < gridDim.x; j += 32) {
-                    const unsigned long long kv = read_slot(krow + j, dead);
-                    m = kv > m ? kv : m;
-                }
-                m = warp_max_u64(m);
-                PHASE(6);
-#ifdef NGS_PHASE_TIMING
-                if (lane == 0 && bp.dbg && p < 256) {
-                    unsigned long long gt;
-                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
-                    bp.dbg[4096 + ((size_t)p * 256 + blockIdx.x) * 4 + 1] = gt;
-                    bp.dbg[4096 + ((size_t)p * 256 + blockIdx.x) * 4 + 3] = (have && m == v) ? 1 : 0;
-                }
-#endif
+            } else if (have) {
+                const uint32_t meta = S.meta[my_r];
+                const int G = (meta >> 24) & 15;
+                choose_group8<true>(g, gbase, smem_cell(S, my_r, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem, &cm.emit,
+                                    &cm.n_emit, &cm.fr);
+            }
+            PHASE(4);
+            asm volatile("bar.sync 1, 64;" ::: "memory");  // warps 0 and 1 only
+            PHASE_AFTER_BARRIER(5);
+            if (warp == 0) {
+                const uint64_t m = s_win;
                 if (!(m & KEY_FEASIBLE)) {
                     if (blockIdx.x == 0 && lane == 0) publish_none(bp, p);
                 } else if (have && m == v && lane < 8) {
                     // ---- 3. bind on the owner ----
                     publish_group(bp, S, my_r, row0 + my_r, dem, p, key_score(m), cm, g);
                 }
-#ifdef NGS_PHASE_TIMING
-                __syncwarp();
-                if (lane == 0 && bp.dbg && p < 256) {
-                    unsigned long long gt;
-                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
-                    bp.dbg[4096 + ((size_t)p * 256 + blockIdx.x) * 4 + 2] = gt;
-                }
-#endif
+                PHASE(6);
             }
-            if (dead && lane == 0) s_abort = 1;
         }
         __syncthreads();
         PHASE_AFTER_BARRIER(7);
@@ -993,7 +972,8 @@ int ensure_batch(ngs_dealer* h) {
     const size_t in_words = (size_t)cap * (NGS_MAX_CONTAINERS + 2), out_words = (size_t)cap * (NGS_MAX_CONTAINERS + 2);
     CU(h, cudaMalloc(&h->d_dem, sizeof(SortedDemand) * cap));
     // key slots [cap][num_sms] followed by the arrival counters [cap]
-    CU(h, cudaMalloc(&h->d_keys, sizeof(unsigned long long) * cap * h->num_sms + sizeof(uint32_t) * cap));
+    // + one arg-max word per pod [cap]
+    CU(h, cudaMalloc(&h->d_keys, sizeof(unsigned long long) * cap * h->num_sms + sizeof(unsigned long long) * cap + sizeof(uint32_t) * cap));
     CU(h, cudaMalloc(&h->d_pod_in, in_words * 4));
     CU(h, cudaMalloc(&h->d_pod_out, out_words * 4));
     CU(h, cudaMallocHost(&h->h_pod_in, in_words * 4));
@@ -1014,14 +994,16 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     uint32_t block = ((rpb + 31) / 32) * 32;
     if (block < 64) block = 64;
     if (block > 1024) block = 1024;
-    const size_t smem = (size_t)rpb * 30 + (size_t)((rpb + 31) / 32) * 4 + 16;  // rows + feasbits + queue
+    const size_t smem = (size_t)rpb * 28 + (size_t)((rpb + 31) / 32) * 4 + 16;  // rows + feasbits
     if (smem > (size_t)h->smem_optin)
         return fail(h, NGS_ERR_UNSUPPORTED, "%u rows per SM need %zu B shared memory (> %d): shard the cluster over more GPUs", rpb, smem, h->smem_optin);
     CU(h, cudaFuncSetAttribute(k_schedule, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_prep_demands<<<(P + 127) / 128, 128, 0, h->stream>>>(d_percent, d_ncont, max_c, d_policy, P, h->d_dem, h->d_err);
     CU(h, cudaGetLastError());
-    uint32_t* d_done = reinterpret_cast<uint32_t*>(h->d_keys + (size_t)h->batch_cap * h->num_sms);
+    unsigned long long* d_mx = h->d_keys + (size_t)h->batch_cap * h->num_sms;
+    uint32_t* d_done = reinterpret_cast<uint32_t*>(d_mx + h->batch_cap);
     CU(h, cudaMemsetAsync(h->d_keys, 0, sizeof(unsigned long long) * (size_t)P * grid, h->stream));
+    CU(h, cudaMemsetAsync(d_mx, 0, sizeof(unsigned long long) * (size_t)P, h->stream));
     CU(h, cudaMemsetAsync(d_done, 0, sizeof(uint32_t) * (size_t)P, h->stream));
     BatchParams bp;
     bp.T = h->T;
@@ -1035,6 +1017,7 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     bp.max_c = max_c;
     bp.keys = h->d_keys;
     bp.done = d_done;
+    bp.mx = d_mx;
     bp.err = h->d_err;
     bp.rows_per_block = rpb;
 #ifdef NGS_PHASE_TIMING

@@ -46,32 +46,12 @@ grid = C.c_uint32(0)
 assert lib.ngs_debug_phases(d._h, buf.ctypes.data_as(C.c_void_p), C.byref(grid)) == 0
 g = grid.value
 a = buf[: 16 * g].reshape(g, 16).astype(np.float64) / P
-names = ["classify", "queue barrier", "exact (queue)", "reduce barrier", "reduce+post", "spec plan", "gather", "publish+end"]
+names = ["filter", "-", "-", "reduce barrier", "plan (w0) / exchange (w1)", "pair barrier", "publish", "end barrier"]
 print(f"{name}: {cfg['nodes']} nodes, {P} pods, grid {g}; cycles per pod (min / median / max over CTAs)")
 for who, off in (("thread 0 (control warp)", 0), ("thread 32 (worker)", 8)):
     print(who)
     for i in range(8):
         col = a[:, off + i]
-        print(f"  {names[i]:14s} {col.min():8.0f} {np.median(col):8.0f} {col.max():8.0f}")
+        print(f"  {names[i]:26s} {col.min():8.0f} {np.median(col):8.0f} {col.max():8.0f}")
     print(f"  {'total':14s} {a[:, off:off + 8].sum(axis=1).mean():8.0f}")
 
-# cross-CTA skew from %globaltimer stamps of the first 256 pods: [pod][cta][post, arrived, published, owner]
-st = buf[4096:].reshape(256, 256, 4)[:, :g, :].astype(np.int64)
-post, arr, pub, own = st[..., 0], st[..., 1], st[..., 2], st[..., 3]
-ok = post[:, 0] > 0
-print("per pod (ns): spread of post times over CTAs, last-post -> median arrived, owner publish time")
-rows = []
-for p in range(1, 256):
-    if not ok[p]:
-        continue
-    last = int(np.argmax(post[p]))
-    prev_owner = int(np.argmax(own[p - 1])) if own[p - 1].any() else -1
-    rows.append((post[p].max() - np.median(post[p]), np.median(arr[p]) - post[p].max(), last == prev_owner,
-                 (pub[p - 1][prev_owner] - arr[p - 1][prev_owner]) if prev_owner >= 0 else -1,
-                 np.median(post[p]) - np.median(arr[p - 1]), post[p].max() - np.median(arr[p - 1])))
-rows = np.array(rows, dtype=np.float64)
-print(f"  last post - median post      : median {np.median(rows[:, 0]):7.0f} ns   p90 {np.percentile(rows[:, 0], 90):7.0f}")
-print(f"  median arrived - last post   : median {np.median(rows[:, 1]):7.0f} ns")
-print(f"  last poster == previous owner: {rows[:, 2].mean() * 100:5.1f} % of pods")
-print(f"  owner: arrived -> published  : median {np.median(rows[:, 3]):7.0f} ns")
-print(f"  arrived(p-1) -> median post(p): median {np.median(rows[:, 4]):7.0f} ns;  -> last post(p): {np.median(rows[:, 5]):7.0f} ns")
