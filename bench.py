@@ -242,7 +242,15 @@ def run_b200(args):
     policy = np.full(len(pc), cfg["policy"], dtype=np.int32)
 
     stream = torch.cuda.Stream()
-    d = ngs.GpuDealer(n, device=local_rank, first_node=rank * n, stream=stream.cuda_stream)
+    sd = None
+    if world > 1:
+        from nano_gpu_scheduler_b200.sharded import ShardedDealer
+
+        with torch.cuda.stream(stream):
+            sd = ShardedDealer(n, rank=rank, world=world, device=local_rank, stream=stream.cuda_stream)
+        d = sd.local
+    else:
+        d = ngs.GpuDealer(n, device=local_rank, first_node=rank * n, stream=stream.cuda_stream)
     d.snapshot_load(gcount, free, first=rank * n)
     load = None
     if cfg["load"]:
@@ -250,9 +258,6 @@ def run_b200(args):
             ok = np.repeat(~absent[:, None], 8, axis=1).astype(np.uint8)
             d.load_update_bulk(m, value, ts, value_ok=ok, ts_ok=ok, first=rank * n)
         load = ngs.make_load_ctx(wl.DEFAULT_PERIODS, NOW_NS)
-
-    if world > 1:
-        raise SystemExit("bench.py: multi-GPU combine is not wired into the bench yet")
 
     dev = torch.device("cuda", local_rank)
     t_pc = torch.from_numpy(pc).to(dev)
@@ -264,10 +269,18 @@ def run_b200(args):
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
     torch.cuda.synchronize()
 
+    t_out = torch.empty((2 + MAX_C) * P, dtype=torch.int32, device=dev)
+
     def dev_step(s):
         lo = s * P
-        d.schedule_batch_dev(P, t_pc[lo:].data_ptr(), t_nc[lo:].data_ptr(), MAX_C, t_pol[lo:].data_ptr(),
-                             t_node[lo:].data_ptr(), t_score[lo:].data_ptr(), t_gidx[lo:].data_ptr(), load=load, seed=1, seq0=lo)
+        if sd is not None:
+            # every rank scans its own node range; the per-pod arg-max is traded between the kernels over
+            # NVLink; one small allreduce-max merges the owner's plans (handle stream == current stream)
+            sd.schedule_batch_dev(P, t_pc[lo:lo + P], t_nc[lo:lo + P], MAX_C, t_pol[lo:lo + P], load=load, seed=1, seq0=lo,
+                                  out=t_out, same_stream=True)
+        else:
+            d.schedule_batch_dev(P, t_pc[lo:].data_ptr(), t_nc[lo:].data_ptr(), MAX_C, t_pol[lo:].data_ptr(),
+                                 t_node[lo:].data_ptr(), t_score[lo:].data_ptr(), t_gidx[lo:].data_ptr(), load=load, seed=1, seq0=lo)
 
     sampler = ClockSampler(local_rank)
     with torch.cuda.stream(stream):
@@ -280,6 +293,8 @@ def run_b200(args):
         # ---- device-resident arm: CUDA events around each step, L2 flushed in between ----
         evs = []
         torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
         for s in range(args.warmup, steps_total):
             flush.fill_(s & 0xFF)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -288,8 +303,14 @@ def run_b200(args):
             e1.record(stream)
             evs.append((e0, e1))
         torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
         d.sync()
         step_ms = [a.elapsed_time(b) for a, b in evs]
+        if dist is not None:  # a step ends when its slowest rank ends: max over ranks, per step
+            t_ms = torch.tensor(step_ms, dtype=torch.float64, device=dev)
+            dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+            step_ms = t_ms.cpu().tolist()
         launches = d.stats()["kernel_launches"] - launches0
         # ---- end-to-end arm: host buffers through the C ABI (pinned staging + H2D + D2H inside) ----
         base = steps_total * P
@@ -298,9 +319,18 @@ def run_b200(args):
             lo = base + s * P
             flush.fill_(s & 0xFF)
             torch.cuda.synchronize()
+            if dist is not None:
+                dist.barrier()
             t0 = time.perf_counter()
-            node, score, gidx = d.schedule_batch(pc[lo:lo + P], nc[lo:lo + P], policy[lo:lo + P], load=load, seed=1, seq0=lo)
+            if sd is not None:
+                node, score, gidx = sd.schedule_batch(pc[lo:lo + P], nc[lo:lo + P], policy[lo:lo + P], load=load, seed=1, seq0=lo)
+            else:
+                node, score, gidx = d.schedule_batch(pc[lo:lo + P], nc[lo:lo + P], policy[lo:lo + P], load=load, seed=1, seq0=lo)
             dt = time.perf_counter() - t0
+            if dist is not None:
+                t_dt = torch.tensor([dt], dtype=torch.float64, device=dev)
+                dist.all_reduce(t_dt, op=dist.ReduceOp.MAX)
+                dt = float(t_dt.item())
             if s >= args.warmup:
                 e2e_times.append(dt)
         # ---- per-pod decision latency: single-pod calls through the host API ----
@@ -308,7 +338,10 @@ def run_b200(args):
         lo = base
         for s in range(60 if args.skip_e2e else 300):
             t0 = time.perf_counter()
-            d.schedule_batch(pc[lo + s:lo + s + 1], nc[lo + s:lo + s + 1], policy[lo + s:lo + s + 1], load=load, seed=1, seq0=s)
+            if sd is not None:
+                sd.schedule_batch(pc[lo + s:lo + s + 1], nc[lo + s:lo + s + 1], policy[lo + s:lo + s + 1], load=load, seed=1, seq0=s)
+            else:
+                d.schedule_batch(pc[lo + s:lo + s + 1], nc[lo + s:lo + s + 1], policy[lo + s:lo + s + 1], load=load, seed=1, seq0=s)
             lat.append(time.perf_counter() - t0)
         sampler.stop()
 
@@ -329,7 +362,9 @@ def run_b200(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": kernel_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "int32+f64", "data": "synthetic",
-        "config": {"workload": workload_name(args, cfg), "nodes_per_gpu": n, "pods_per_step": P, "max_containers": MAX_C,
+        "config": {"workload": workload_name(args, cfg), "nodes_per_gpu": n, "total_nodes": n * world, "pods_per_step": P,
+                   "max_containers": MAX_C,
+                   "sharding": "none" if world == 1 else f"node ranges over {world} GPUs; per-pod arg-max traded between kernels over NVLink peer memory, one allreduce-max of plans per step",
                    "l2": "flushed between timed steps (256 MiB write); the snapshot itself (12 MB) is smaller than L2",
                    "semantics": "pods applied strictly in order, bit-exact vs the CPU oracle (tests/test_gpu_parity.py)"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(P * (MAX_C + 2) * 4),

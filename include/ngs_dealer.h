@@ -31,6 +31,8 @@ extern "C" {
 #define NGS_MAX_PERIODS 4      /* usable PolicySpec.SyncPeriod entries */
 #define NGS_MAX_FREE 65535     /* upper bound of a cell's free percent kept in the snapshot */
 #define NGS_MAX_BATCH 65536    /* pods per ngs_schedule_batch call */
+#define NGS_MAX_RANKS 8        /* GPUs of one box a cluster can be sharded over */
+#define NGS_IPC_HANDLE_BYTES 64
 
 /* status codes */
 enum {
@@ -151,6 +153,19 @@ int ngs_schedule_batch(ngs_dealer *h, uint32_t n_pods, const int32_t *percent, c
 int ngs_schedule_batch_dev(ngs_dealer *h, uint32_t n_pods, const int32_t *d_percent, const int32_t *d_n_containers,
                            int max_c, const int32_t *d_policy, const ngs_load_ctx *load, uint64_t seed, uint64_t seq0,
                            int32_t *d_node_out, int32_t *d_score_out, int32_t *d_gpu_idx_out);
+
+/* ---- node-range sharding over the GPUs of one box (no reference counterpart: the reference is a
+ * single process) ----
+ * One process and one handle per GPU, each created with its own first_node / max_nodes range.
+ * ngs_schedule_batch[_dev] then has to be called by every rank with the same pods: each rank scans
+ * its own rows, the per-pod best (score, node) keys are traded between the ranks' kernels through
+ * peer-mapped memory over NVLink, and the rank owning the winner binds it.  On return node_out and
+ * score_out are complete on every rank; gpu_idx_out holds the plan only on the owning rank and
+ * INT32_MIN elsewhere (merge with an element-wise max, e.g. one small NCCL allreduce-max).
+ *   ngs_xchg_export: writes this rank's NGS_IPC_HANDLE_BYTES-byte handle of its exchange buffer;
+ *   ngs_xchg_attach: takes the `world` handles gathered from all ranks (rank-major) and maps them. */
+int ngs_xchg_export(ngs_dealer *h, void *handle_out);
+int ngs_xchg_attach(ngs_dealer *h, int rank, int world, const void *handles);
 
 #ifdef __cplusplus
 }

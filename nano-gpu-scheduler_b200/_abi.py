@@ -26,8 +26,10 @@ SYMBOLS = [
     "ngs_abi_version", "ngs_strerror", "ngs_last_error", "ngs_create", "ngs_destroy", "ngs_stream", "ngs_sync",
     "ngs_stats", "ngs_node_upsert", "ngs_snapshot_load", "ngs_snapshot_read", "ngs_node_apply", "ngs_load_add_node",
     "ngs_load_update", "ngs_load_update_bulk", "ngs_parse_usage", "ngs_parse_update_time", "ngs_assume", "ngs_score",
-    "ngs_bind", "ngs_schedule_batch", "ngs_schedule_batch_dev",
+    "ngs_bind", "ngs_schedule_batch", "ngs_schedule_batch_dev", "ngs_xchg_export", "ngs_xchg_attach",
 ]
+MAX_RANKS = 8
+IPC_HANDLE_BYTES = 64
 
 
 class LoadCtx(C.Structure):
@@ -90,6 +92,8 @@ def load():
     L.ngs_bind.argtypes = [vp, u32, vp, ci, ci, vp, vp, vp]
     L.ngs_schedule_batch.argtypes = [vp, u32, vp, vp, ci, vp, vp, u64, u64, vp, vp, vp]
     L.ngs_schedule_batch_dev.argtypes = [vp, u32, vp, vp, ci, vp, vp, u64, u64, vp, vp, vp]
+    L.ngs_xchg_export.argtypes = [vp, vp]
+    L.ngs_xchg_attach.argtypes = [vp, ci, ci, vp]
     for name in SYMBOLS:
         fn = getattr(L, name)
         if fn.restype is C.c_int and name not in ("ngs_parse_usage", "ngs_parse_update_time"):

@@ -339,6 +339,12 @@ struct BatchParams {
     unsigned long long* keys;  // [P][gridDim.x] one slot per CTA per pod, zero before launch
     uint32_t* done;            // [P] arrival counters, zero before launch
     unsigned long long* mx;    // [P] arg-max words (atomicMax), zero before launch
+    // node-range sharding over the GPUs of one box: every rank runs this same kernel on
+    // its own rows; CTA 0 of each rank trades the rank's result with the peers through
+    // peer-mapped memory (plain 8-byte stores over NVLink), then tells its own CTAs
+    uint32_t world, rank;
+    unsigned long long* xslots[NGS_MAX_RANKS];  // [rank r] -> r's slot array [P][NGS_MAX_RANKS] (this batch's parity half)
+    unsigned long long* gwin;                   // [P] this rank's copy of the global result, zero before launch
     int32_t* err;              // device error word (0 = ok)
     uint32_t rows_per_block;
 #ifdef NGS_PHASE_TIMING
@@ -499,6 +505,44 @@ __device__ __forceinline__ bool wait_done(const uint32_t* done, uint32_t target,
             }
         }
     }
+}
+
+__device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+// bounded wait for a VALID word (written by a peer GPU or by this rank's CTA 0)
+__device__ __forceinline__ unsigned long long wait_valid(const unsigned long long* p, int32_t* err, bool& dead) {
+    unsigned long long v = ld_relaxed_sys_u64(p);
+    if (v & KEY_VALID) return v & ~KEY_VALID;
+    const long long t0 = clock64();
+    uint32_t spins = 0;
+    while (!((v = ld_relaxed_sys_u64(p)) & KEY_VALID)) {
+        if ((++spins & 255u) == 0) {
+            if (*reinterpret_cast<volatile int32_t*>(err) != 0 || clock64() - t0 > SPIN_TIMEOUT_CYCLES) {
+                atomicCAS(err, 0, NGS_ERR_TIMEOUT);
+                dead = true;
+                return 0;
+            }
+        }
+    }
+    return v & ~KEY_VALID;
+}
+// CTA 0, one full warp: post this rank's word to every rank's slot array, collect all ranks'
+// words from our own array.  Returns lane j's word of rank j (0 for lanes >= world).
+__device__ __forceinline__ unsigned long long cross_rank_exchange(const BatchParams& bp, uint32_t p, unsigned long long mine,
+                                                                  uint32_t lane, bool& dead) {
+    unsigned long long got = 0;
+    if (lane < bp.world) {
+        st_relaxed_sys_u64(bp.xslots[lane] + (size_t)p * NGS_MAX_RANKS + bp.rank, mine | KEY_VALID);
+        got = wait_valid(bp.xslots[bp.rank] + (size_t)p * NGS_MAX_RANKS + lane, bp.err, dead);
+    }
+    dead = __any_sync(0xFFFFFFFFu, dead);
+    return got;
 }
 
 __device__ __forceinline__ unsigned long long read_slot(const unsigned long long* slot, bool dead) {
@@ -722,11 +766,41 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                     const uint64_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
                     if (lane >= (uint32_t)o) incl += t;
                 }
-                const uint64_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+                const uint64_t ltotal = __shfl_sync(0xFFFFFFFFu, incl, 31);  // feasible rows on this rank
+                uint64_t total = ltotal, before_rank = 0;
+                if (bp.world > 1) {
+                    // K5: ranks trade their totals; rank r's feasible rows follow those of ranks < r
+                    unsigned long long packed = 0;
+                    if (blockIdx.x == 0) {
+                        const unsigned long long cj = cross_rank_exchange(bp, p, ltotal, lane, dead);
+                        unsigned long long inc2 = cj;
+#pragma unroll
+                        for (int o = 1; o < 32; o <<= 1) {
+                            const unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, inc2, o);
+                            if (lane >= (uint32_t)o) inc2 += t;
+                        }
+                        const unsigned long long gt = __shfl_sync(0xFFFFFFFFu, inc2, 31);
+                        const unsigned long long bf = __shfl_sync(0xFFFFFFFFu, inc2 - cj, bp.rank);
+                        packed = (gt << 31) | bf;
+                        if (lane == 0) st_relaxed_u64(bp.gwin + p, packed | KEY_VALID);
+                    } else {
+                        if (lane == 0) packed = wait_valid(bp.gwin + p, bp.err, dead);
+                        packed = __shfl_sync(0xFFFFFFFFu, packed, 0);
+                        dead = __any_sync(0xFFFFFFFFu, dead);
+                    }
+                    total = packed >> 31;
+                    before_rank = packed & 0x7FFFFFFFull;
+                }
                 if (total == 0) {
                     if (blockIdx.x == 0 && lane == 0) publish_none(bp, p);
                 } else {
-                    const uint64_t pick = splitmix64(bp.seed_seq + p) % total;
+                    const uint64_t gpick = splitmix64(bp.seed_seq + p) % total;
+                    const bool mine = gpick >= before_rank && gpick < before_rank + ltotal;
+                    if (!mine && blockIdx.x == 0 && lane == 0) {
+                        publish_none(bp, p);  // another rank owns the pick; it reports node and plan
+                        bp.score_out[p] = 100;
+                    }
+                    const uint64_t pick = mine ? gpick - before_rank : ~0ull;  // ~0: matches no CTA
                     // rank of the pick inside this CTA, if it falls here
                     uint64_t run = incl - sum;
                     long long local_rank = -1;
@@ -786,15 +860,36 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                 // exchange (fastest variant of profiles/tools/xchg_bench.cu): atomicMax into the pod's
                 // word; the arrival counter is bumped only after that atomic has returned (data
                 // dependence), so a full counter implies every CTA's key is in the word
+                uint32_t* done = bp.done + p;
+                bool dead = false;
                 if (lane == 0) {
-                    uint32_t* done = bp.done + p;
                     const unsigned long long old = atomicMax(bp.mx + p, (unsigned long long)v);
                     const uint32_t one = 1u + (uint32_t)(old >> 63);  // bit 63 is never set: always 1
                     asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(done), "r"(one) : "memory");
-                    const bool dead = !wait_done(done, gridDim.x, bp.err);
-                    s_win = ld_relaxed_u64(bp.mx + p);
-                    if (dead) s_abort = 1;
                 }
+                if (bp.world == 1) {
+                    if (lane == 0) {
+                        dead = !wait_done(done, gridDim.x, bp.err);
+                        s_win = ld_relaxed_u64(bp.mx + p);
+                    }
+                } else if (blockIdx.x == 0) {
+                    // K5: this rank's best key goes to every peer; the best over all ranks comes back
+                    unsigned long long mloc = 0;
+                    if (lane == 0) {
+                        dead = !wait_done(done, gridDim.x, bp.err);
+                        mloc = ld_relaxed_u64(bp.mx + p);
+                    }
+                    mloc = __shfl_sync(0xFFFFFFFFu, mloc, 0);
+                    dead = __any_sync(0xFFFFFFFFu, dead);
+                    const uint64_t mg = warp_max_u64(cross_rank_exchange(bp, p, mloc, lane, dead));
+                    if (lane == 0) {
+                        st_relaxed_u64(bp.gwin + p, mg | KEY_VALID);
+                        s_win = mg;
+                    }
+                } else if (lane == 0) {
+                    s_win = wait_valid(bp.gwin + p, bp.err, dead);
+                }
+                if (dead && lane == 0) s_abort = 1;
             } else if (have) {
                 const uint32_t meta = S.meta[my_r];
                 const int G = (meta >> 24) & 15;
@@ -808,6 +903,12 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                 const uint64_t m = s_win;
                 if (!(m & KEY_FEASIBLE)) {
                     if (blockIdx.x == 0 && lane == 0) publish_none(bp, p);
+                } else if (blockIdx.x == 0 && lane == 0 && key_node(m) - T.first >= T.n) {
+                    // the winner lives on another rank: node and score are known from the key, the
+                    // plan is filled in by the owner (merged on the host side by an allreduce-max)
+                    publish_none(bp, p);
+                    bp.node_out[p] = (int32_t)key_node(m);
+                    bp.score_out[p] = key_score(m);
                 } else if (have && m == v && lane < 8) {
                     // ---- 3. bind on the owner ----
                     publish_group(bp, S, my_r, row0 + my_r, dem, p, key_score(m), cm, g);
@@ -866,6 +967,12 @@ struct ngs_dealer {
     int32_t* h_pod_out = nullptr;
     int32_t* d_err = nullptr;
     int32_t* h_err = nullptr;
+    // cross-GPU exchange (K5)
+    int world = 1, rank = 0;
+    unsigned long long* d_xslots = nullptr;               // own buffer: [2 parities][BATCH_CHUNK][NGS_MAX_RANKS]
+    unsigned long long* peer_xslots[NGS_MAX_RANKS] = {};  // peer-mapped bases (own entry = d_xslots)
+    unsigned long long* d_gwin = nullptr;                 // [BATCH_CHUNK]
+    uint64_t xbatch = 0;                                  // launches so far: selects the parity half
     ngs_stats_t stats{};
     unsigned long long* d_dbg = nullptr;  // profiling builds only
     uint32_t dbg_grid = 0;
@@ -875,6 +982,7 @@ struct ngs_dealer {
 namespace {
 
 constexpr uint32_t BATCH_CHUNK = 4096;
+constexpr size_t XSLOT_HALF = (size_t)BATCH_CHUNK * NGS_MAX_RANKS;  // u64 words per parity half
 
 int fail(ngs_dealer* h, int code, const char* fmt, ...) {
     if (h) {
@@ -1018,6 +1126,20 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     bp.keys = h->d_keys;
     bp.done = d_done;
     bp.mx = d_mx;
+    bp.world = (uint32_t)h->world;
+    bp.rank = (uint32_t)h->rank;
+    bp.gwin = h->d_gwin;
+    for (int r = 0; r < NGS_MAX_RANKS; r++) bp.xslots[r] = nullptr;
+    if (h->world > 1) {
+        // Parity halves instead of a cross-rank barrier per batch: batch i uses half i&1 on every
+        // rank; the other half is cleared now, before this batch starts.  A peer can only write into
+        // that half once it has finished batch i, which needs this rank's batch-i posts first.
+        const size_t cur = (size_t)(h->xbatch & 1), nxt = cur ^ 1;
+        CU(h, cudaMemsetAsync(h->d_xslots + nxt * XSLOT_HALF, 0, sizeof(unsigned long long) * XSLOT_HALF, h->stream));
+        CU(h, cudaMemsetAsync(h->d_gwin, 0, sizeof(unsigned long long) * (size_t)P, h->stream));
+        for (int r = 0; r < h->world; r++) bp.xslots[r] = h->peer_xslots[r] + cur * XSLOT_HALF;
+        h->xbatch++;
+    }
     bp.err = h->d_err;
     bp.rows_per_block = rpb;
 #ifdef NGS_PHASE_TIMING
@@ -1130,6 +1252,10 @@ int ngs_destroy(ngs_dealer* h) {
     cudaFree(h->d_dem); cudaFree(h->d_keys); cudaFree(h->d_pod_in); cudaFree(h->d_pod_out);
     cudaFreeHost(h->h_pod_in); cudaFreeHost(h->h_pod_out);
     cudaFree(h->d_err); cudaFreeHost(h->h_err);
+    for (int r = 0; r < NGS_MAX_RANKS; r++)
+        if (h->peer_xslots[r] && r != h->rank) cudaIpcCloseMemHandle(h->peer_xslots[r]);
+    cudaFree(h->d_xslots); cudaFree(h->d_gwin);
+    cudaFree(h->d_dbg);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return NGS_OK;
@@ -1438,6 +1564,45 @@ int ngs_schedule_batch(ngs_dealer* h, uint32_t n_pods, const int32_t* percent, c
         h->stats.h2d_bytes += in_bytes;
         h->stats.d2h_bytes += out_bytes;
     }
+    return NGS_OK;
+}
+
+int ngs_xchg_export(ngs_dealer* h, void* handle_out) {
+    if (!h || !handle_out) return NGS_ERR_INVALID;
+    static_assert(sizeof(cudaIpcMemHandle_t) == NGS_IPC_HANDLE_BYTES, "IPC handle size");
+    CU(h, cudaSetDevice(h->device));
+    if (!h->d_xslots) {
+        CU(h, cudaMalloc(&h->d_xslots, sizeof(unsigned long long) * 2 * XSLOT_HALF));
+        CU(h, cudaMalloc(&h->d_gwin, sizeof(unsigned long long) * BATCH_CHUNK));
+        CU(h, cudaMemset(h->d_xslots, 0, sizeof(unsigned long long) * 2 * XSLOT_HALF));
+        CU(h, cudaMemset(h->d_gwin, 0, sizeof(unsigned long long) * BATCH_CHUNK));
+        CU(h, cudaDeviceSynchronize());  // cleared before any peer can learn the handle
+    }
+    cudaIpcMemHandle_t mh;
+    CU(h, cudaIpcGetMemHandle(&mh, h->d_xslots));
+    memcpy(handle_out, &mh, sizeof(mh));
+    return NGS_OK;
+}
+
+int ngs_xchg_attach(ngs_dealer* h, int rank, int world, const void* handles) {
+    if (!h || !handles || world < 1 || world > NGS_MAX_RANKS || rank < 0 || rank >= world) return NGS_ERR_INVALID;
+    if (!h->d_xslots) return fail(h, NGS_ERR_INVALID, "ngs_xchg_attach before ngs_xchg_export");
+    CU(h, cudaSetDevice(h->device));
+    const unsigned char* hb = static_cast<const unsigned char*>(handles);
+    for (int r = 0; r < world; r++) {
+        if (r == rank) {
+            h->peer_xslots[r] = h->d_xslots;
+            continue;
+        }
+        cudaIpcMemHandle_t mh;
+        memcpy(&mh, hb + (size_t)r * NGS_IPC_HANDLE_BYTES, sizeof(mh));
+        void* ptr = nullptr;
+        CU(h, cudaIpcOpenMemHandle(&ptr, mh, cudaIpcMemLazyEnablePeerAccess));
+        h->peer_xslots[r] = static_cast<unsigned long long*>(ptr);
+    }
+    h->rank = rank;
+    h->world = world;
+    h->xbatch = 0;
     return NGS_OK;
 }
 

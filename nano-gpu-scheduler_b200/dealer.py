@@ -187,6 +187,17 @@ class GpuDealer:
                                                      seq0, d_node, d_score, d_gidx))
 
 
+    # -- node-range sharding over the GPUs of one box ------------------------------------------
+    def xchg_export(self) -> bytes:
+        buf = C.create_string_buffer(_abi.IPC_HANDLE_BYTES)
+        self._check(self._lib.ngs_xchg_export(self._h, buf))
+        return buf.raw
+
+    def xchg_attach(self, rank, world, handles: bytes):
+        assert len(handles) == world * _abi.IPC_HANDLE_BYTES
+        self._check(self._lib.ngs_xchg_attach(self._h, rank, world, handles))
+
+
 def parse_usage(s: str):
     v = C.c_double(0.0)
     ok = _abi.load().ngs_parse_usage(s.encode(), C.byref(v))

@@ -1,0 +1,74 @@
+"""Run under torchrun (one rank per GPU): the node-range sharded path against the CPU oracle on
+the whole cluster.  Rank 0 prints SHARDED OK on success."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import nano_gpu_scheduler_b200 as ngs  # noqa: E402
+import oracle as o  # noqa: E402
+from nano_gpu_scheduler_b200 import workloads as wl  # noqa: E402
+from nano_gpu_scheduler_b200.sharded import ShardedDealer  # noqa: E402
+from tests.parity_util import NOW_NS, NOW_S  # noqa: E402
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    n = int(sys.argv[1]) if len(sys.argv) > 1 else 3000  # nodes per rank
+    N = n * world
+    gcount, free = wl.make_cluster(N, 0.5, 0x5A4D)
+    tables = wl.make_load_tables(N, 0x5A4D, NOW_S)
+    sd = ShardedDealer(n, device=local)
+    lo, hi = rank * n, (rank + 1) * n
+    sd.local.snapshot_load(gcount[lo:hi], free[lo:hi], first=lo)
+    for m, (value, ts, absent) in enumerate(tables):
+        ok = np.repeat(~absent[lo:hi, None], 8, axis=1).astype(np.uint8)
+        sd.local.load_update_bulk(m, value[lo:hi], ts[lo:hi], value_ok=ok, ts_ok=ok, first=lo)
+    oc = None
+    if rank == 0:
+        oc = o.OracleCluster(N)
+        oc.load_snapshot(gcount, free)
+        for m, (value, ts, absent) in enumerate(tables):
+            oc.load_update_bulk(m, value, ts, ok=np.repeat(~absent[:, None], 8, axis=1).astype(np.uint8))
+    failures = 0
+    seq = 0
+    for rnd, (policy, load_on, P) in enumerate([(0, False, 300), (1, False, 300), (2, False, 200), (0, True, 300), (None, False, 300),
+                                                (1, True, 100)]):
+        pc, nc = wl.make_pods(P, 1, 4, 0, 12, 0x77 + rnd, max_c=4)
+        pol = np.full(P, policy, dtype=np.int32) if policy is not None else (np.arange(P) % 3).astype(np.int32)
+        gl = ngs.make_load_ctx(wl.DEFAULT_PERIODS, NOW_NS) if load_on else None
+        node, score, gidx = sd.schedule_batch(pc, nc, pol, load=gl, seed=42, seq0=seq)
+        if rank == 0:
+            ol = o.make_load_ctx(wl.DEFAULT_PERIODS, NOW_NS) if load_on else None
+            onode, oscore, ogidx = oc.schedule_batch(pc, nc, pol, load=ol, seed=42, seq0=seq, n_threads=4)
+            good = np.array_equal(node, onode) and np.array_equal(score, oscore) and np.array_equal(gidx, ogidx)
+            if not good:
+                failures += 1
+                bad = np.flatnonzero((node != onode) | (score != oscore))
+                print(f"round {rnd} policy {policy} load {load_on}: MISMATCH at pods {bad[:8]}", flush=True)
+        seq += P
+    # the shards together hold exactly the oracle's snapshot
+    _, fr, rl = sd.local.snapshot_read(first=lo, n=n)
+    t = torch.from_numpy(fr.astype(np.int32)).cuda()
+    allfr = [torch.empty_like(t) for _ in range(world)]
+    dist.all_gather(allfr, t)
+    if rank == 0:
+        got = torch.cat(allfr).cpu().numpy()
+        _, ofr, _ = oc.snapshot()
+        if not np.array_equal(got, ofr):
+            failures += 1
+            print("snapshot MISMATCH", flush=True)
+        print("SHARDED OK" if failures == 0 else f"SHARDED FAILED ({failures})", flush=True)
+    sd.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
