@@ -44,7 +44,8 @@ enum {
     NGS_ERR_APPLY = 5,        /* apply: "can't apply plan" (allocate.go:113) / index >= G (allocate.go:126) */
     NGS_ERR_RANGE = 6,        /* a cell would leave [0, NGS_MAX_FREE] */
     NGS_ERR_UNSUPPORTED = 7,  /* gpu_count > NGS_MAX_GPUS, too many containers or periods */
-    NGS_ERR_TIMEOUT = 8       /* the batch kernel gave up waiting for a peer (never expected) */
+    NGS_ERR_TIMEOUT = 8,      /* the batch kernel gave up waiting for a peer (never expected) */
+    NGS_ERR_NOALLOC_LIMIT = 9 /* ngs_schedule_batch_noalloc: batch or grid larger than its fixed scratch */
 };
 
 /* policies: Binpack (rater.go:52), Spread (rater.go:55), random = SampleRater plan search
@@ -166,6 +167,58 @@ int ngs_schedule_batch_dev(ngs_dealer *h, uint32_t n_pods, const int32_t *d_perc
  *   ngs_xchg_attach: takes the `world` handles gathered from all ranks (rank-major) and maps them. */
 int ngs_xchg_export(ngs_dealer *h, void *handle_out);
 int ngs_xchg_attach(ngs_dealer *h, int rank, int world, const void *handles);
+
+/* ---- scheduling without any allocation (no counterpart in the reference) ----
+ * Everything above works on a handle that owns its device memory (ngs_create calls cudaMalloc, and
+ * the batch path grows scratch buffers on first use).  Some hosts of this library are not allowed
+ * to do that: an extender embedded in a process whose whole device arena was handed to another
+ * allocator (a co-located serving runtime, a fixed pool owned by the embedding application), where
+ * a cudaMalloc of ours can fail or fragment that pool; and callers on the scheduling fast path that
+ * must never hit the driver's allocator, because cudaMalloc / cudaFree synchronise the whole
+ * device and take a process-wide lock, stalling every other stream while a pod waits for its
+ * decision.  For them there is this one call.  It is ngs_schedule_batch_dev without a handle:
+ * the caller owns the snapshot tables (described by ngs_snapshot_view, laid out exactly as the
+ * handle keeps them) and passes the pods and the outputs as device pointers; the scratch the batch
+ * kernel needs (sorted demands, per-pod exchange words, error word) lives in a fixed array inside
+ * the library's device image, about 372 KB that every GPU loading the library keeps until exit.
+ *
+ * Limits: at most NGS_NOALLOC_MAX_PODS pods per call and a launch of at most
+ * NGS_NOALLOC_MAX_CTAS CTAs (one per SM); anything larger is refused with NGS_ERR_NOALLOC_LIMIT
+ * and nothing is launched.  One GPU only (no node-range sharding).
+ * The call clears the part of the scratch that has to start at zero, queues the work on `stream`
+ * (NULL = the default stream), waits for it and returns the batch's status.  It calls no
+ * cudaMalloc, cudaFree, stream / event creation or any other allocating routine.
+ * The first call on each device looks up the scratch array's device address
+ * (cudaGetSymbolAddress); make that first call outside of any stream capture.
+ * All calls on a device share the one scratch array, which keeps the previous call's contents:
+ * two calls that overlap on the GPU (different streams, different threads) race on it - issue
+ * them one after the other.
+ *
+ * Table encodings (what ngs_snapshot_load / ngs_load_update_bulk write for a handle):
+ *   free        int32  [n][8]    free percent per GPU cell, 0 for cells >= gpu_count
+ *   gpu_count   uint8  [n]       0 = node unknown
+ *   remain_load int8   [n][8]    GPUResource.RemainLoad (allocate.go:144), normally 0
+ *   tenths      uint8  [2][n][8] ceil(10 * usage) per (metric, node, card); 255 = no usable sample
+ *   ts          uint32 [2][n][8] sample time, unix seconds
+ *   plan_tag    uint32 [n]       plan-cache tag, cleared for a node when it is bound; start at 0
+ *   plan_score  int32  [n]       plan-cache score; start at 0 */
+#define NGS_NOALLOC_MAX_PODS 256
+#define NGS_NOALLOC_MAX_CTAS 160
+typedef struct {
+    int32_t *free;
+    uint8_t *gpu_count;
+    int8_t *remain_load;
+    uint8_t *tenths;
+    uint32_t *ts;
+    uint32_t *plan_tag;
+    int32_t *plan_score;
+    uint32_t n_nodes;
+    uint32_t first_node;
+} ngs_snapshot_view;
+int ngs_schedule_batch_noalloc(int device, void *stream, const ngs_snapshot_view *snap, uint32_t n_pods,
+                               const int32_t *d_percent, const int32_t *d_n_containers, int max_c, const int32_t *d_policy,
+                               const ngs_load_ctx *load, uint64_t seed, uint64_t seq0, int32_t *d_node_out,
+                               int32_t *d_score_out, int32_t *d_gpu_idx_out);
 
 #ifdef __cplusplus
 }

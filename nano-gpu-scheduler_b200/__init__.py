@@ -5,4 +5,5 @@ from ._abi import (ERR_APPLY, ERR_CUDA, ERR_INFEASIBLE, ERR_INVALID, ERR_RANGE, 
                    ERR_UNSUPPORTED, INT32_MIN, MAX_CONTAINERS, MAX_FREE, MAX_GPUS, MAX_PERIODS, METRIC_CORE,
                    METRIC_MEMORY, OK, POLICY_BINPACK, POLICY_RANDOM, POLICY_SPREAD, REASON_INFEASIBLE, REASON_OK,
                    REASON_UNKNOWN_NODE)
-from .dealer import GpuDealer, NgsError, make_load_ctx, parse_update_time, parse_usage  # noqa: F401
+from .dealer import (GpuDealer, NgsError, make_load_ctx, parse_update_time, parse_usage,  # noqa: F401
+                     schedule_batch_noalloc)

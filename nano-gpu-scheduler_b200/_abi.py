@@ -27,7 +27,11 @@ SYMBOLS = [
     "ngs_stats", "ngs_node_upsert", "ngs_snapshot_load", "ngs_snapshot_read", "ngs_node_apply", "ngs_load_add_node",
     "ngs_load_update", "ngs_load_update_bulk", "ngs_parse_usage", "ngs_parse_update_time", "ngs_assume", "ngs_score",
     "ngs_bind", "ngs_schedule_batch", "ngs_schedule_batch_dev", "ngs_xchg_export", "ngs_xchg_attach",
+    "ngs_schedule_batch_noalloc",
 ]
+NOALLOC_MAX_PODS = 256
+NOALLOC_MAX_CTAS = 160
+ERR_NOALLOC_LIMIT = 9
 MAX_RANKS = 8
 IPC_HANDLE_BYTES = 64
 
@@ -38,6 +42,15 @@ class LoadCtx(C.Structure):
         ("metric", C.c_int32 * MAX_PERIODS),
         ("window_ns", C.c_int64 * MAX_PERIODS),
         ("now_ns", C.c_int64),
+    ]
+
+
+class SnapshotView(C.Structure):
+    """ngs_snapshot_view: caller-owned snapshot tables for ngs_schedule_batch_noalloc"""
+    _fields_ = [
+        ("free", C.c_void_p), ("gpu_count", C.c_void_p), ("remain_load", C.c_void_p), ("tenths", C.c_void_p),
+        ("ts", C.c_void_p), ("plan_tag", C.c_void_p), ("plan_score", C.c_void_p),
+        ("n_nodes", C.c_uint32), ("first_node", C.c_uint32),
     ]
 
 
@@ -94,6 +107,7 @@ def load():
     L.ngs_schedule_batch_dev.argtypes = [vp, u32, vp, vp, ci, vp, vp, u64, u64, vp, vp, vp]
     L.ngs_xchg_export.argtypes = [vp, vp]
     L.ngs_xchg_attach.argtypes = [vp, ci, ci, vp]
+    L.ngs_schedule_batch_noalloc.argtypes = [ci, vp, C.POINTER(SnapshotView), u32, vp, vp, ci, vp, vp, u64, u64, vp, vp, vp]
     for name in SYMBOLS:
         fn = getattr(L, name)
         if fn.restype is C.c_int and name not in ("ngs_parse_usage", "ngs_parse_update_time"):

@@ -18,6 +18,8 @@
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
 
+#include <pthread.h>
+
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -1187,6 +1189,8 @@ const char* ngs_strerror(int s) {
         case NGS_ERR_RANGE: return "capacity out of range";
         case NGS_ERR_UNSUPPORTED: return "unsupported size";
         case NGS_ERR_TIMEOUT: return "device-side wait timed out";
+        case NGS_ERR_NOALLOC_LIMIT:
+            return "ngs_schedule_batch_noalloc: more than NGS_NOALLOC_MAX_PODS pods or NGS_NOALLOC_MAX_CTAS CTAs (fixed scratch)";
         default: return "unknown status";
     }
 }
@@ -1607,3 +1611,146 @@ int ngs_xchg_attach(ngs_dealer* h, int rank, int world, const void* handles) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// ngs_schedule_batch_noalloc: the batch kernel for hosts that may not allocate device memory
+// (see include/ngs_dealer.h for who they are).  Same kernels as ngs_schedule_batch_dev; the only
+// difference is where the scratch comes from: a fixed array in this library's device image
+// instead of buffers the handle cudaMalloc'ed.
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+constexpr size_t NA_DEM_BYTES = sizeof(SortedDemand) * NGS_NOALLOC_MAX_PODS;                                      // sorted demands
+constexpr size_t NA_KEYS_BYTES = sizeof(unsigned long long) * (size_t)NGS_NOALLOC_MAX_PODS * NGS_NOALLOC_MAX_CTAS;  // per-CTA slots
+constexpr size_t NA_MX_BYTES = sizeof(unsigned long long) * NGS_NOALLOC_MAX_PODS;                                  // arg-max words
+constexpr size_t NA_DONE_BYTES = sizeof(uint32_t) * NGS_NOALLOC_MAX_PODS;                                          // arrival counters
+constexpr size_t NA_DEM_OFF = 0;
+constexpr size_t NA_KEYS_OFF = NA_DEM_OFF + NA_DEM_BYTES;
+constexpr size_t NA_MX_OFF = NA_KEYS_OFF + NA_KEYS_BYTES;
+constexpr size_t NA_DONE_OFF = NA_MX_OFF + NA_MX_BYTES;
+constexpr size_t NA_ERR_OFF = NA_DONE_OFF + NA_DONE_BYTES;
+constexpr size_t NA_TOTAL_BYTES = NA_ERR_OFF + 256;
+static_assert(NA_KEYS_OFF % 256 == 0 && NA_MX_OFF % 256 == 0 && NA_DONE_OFF % 256 == 0 && NA_ERR_OFF % 256 == 0, "scratch layout");
+
+// The scratch itself.  In host code this name is only a handle for the runtime, not a device
+// address: the address the kernels get comes from cudaGetSymbolAddress below.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NA_TOTAL_BYTES];
+
+struct NoAllocDevice {
+    bool ready = false;
+    unsigned char* scratch = nullptr;  // device address of g_noalloc_scratch on this device
+    int num_sms = 0, smem_optin = 0, coop = 0;
+};
+NoAllocDevice g_na_dev[64];
+pthread_mutex_t g_na_mu = PTHREAD_MUTEX_INITIALIZER;
+
+// once per device, with that device current: resolve the scratch array's address there
+int noalloc_setup(int device, NoAllocDevice** out) {
+    if (device < 0 || device >= 64) return NGS_ERR_INVALID;
+    NoAllocDevice* d = &g_na_dev[device];
+    int rc = NGS_OK;
+    pthread_mutex_lock(&g_na_mu);
+    if (!d->ready) {
+        void* ptr = nullptr;
+        if (cudaGetSymbolAddress(&ptr, g_noalloc_scratch) != cudaSuccess || ptr == nullptr ||
+            cudaDeviceGetAttribute(&d->num_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess ||
+            cudaDeviceGetAttribute(&d->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device) != cudaSuccess ||
+            cudaDeviceGetAttribute(&d->coop, cudaDevAttrCooperativeLaunch, device) != cudaSuccess) {
+            rc = NGS_ERR_CUDA;
+        } else {
+            d->scratch = static_cast<unsigned char*>(ptr);
+            d->ready = true;
+        }
+    }
+    pthread_mutex_unlock(&g_na_mu);
+    *out = d;
+    return rc;
+}
+
+}  // namespace
+
+extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_snapshot_view* snap, uint32_t n_pods,
+                                          const int32_t* d_percent, const int32_t* d_n_containers, int max_c, const int32_t* d_policy,
+                                          const ngs_load_ctx* load, uint64_t seed, uint64_t seq0, int32_t* d_node_out,
+                                          int32_t* d_score_out, int32_t* d_gpu_idx_out) {
+    if (!snap || !snap->free || !snap->gpu_count || !snap->remain_load || !snap->tenths || !snap->ts || !snap->plan_tag ||
+        !snap->plan_score || snap->n_nodes == 0)
+        return NGS_ERR_INVALID;
+    if (!d_percent || !d_n_containers || !d_policy || !d_node_out || !d_score_out || !d_gpu_idx_out) return NGS_ERR_INVALID;
+    if (max_c < 1 || max_c > NGS_MAX_CONTAINERS) return NGS_ERR_UNSUPPORTED;
+    if (n_pods > NGS_NOALLOC_MAX_PODS) return NGS_ERR_NOALLOC_LIMIT;  // the sorted demands would not fit
+    if (n_pods == 0) return NGS_OK;
+    LoadParams lp;
+    int rc = make_load(nullptr, load, &lp);
+    if (rc) return rc;
+    if (cudaSetDevice(device) != cudaSuccess) return NGS_ERR_CUDA;
+    NoAllocDevice* dv = nullptr;
+    rc = noalloc_setup(device, &dv);  // first call on this device: cudaGetSymbolAddress
+    if (rc) return rc;
+    if (!dv->coop) return NGS_ERR_CUDA;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+
+    // same launch shape as the handle path
+    const uint32_t N = snap->n_nodes;
+    uint32_t grid = (N + 63) / 64;
+    if (grid < 1) grid = 1;
+    if (grid > (uint32_t)dv->num_sms) grid = (uint32_t)dv->num_sms;
+    if (grid > NGS_NOALLOC_MAX_CTAS) return NGS_ERR_NOALLOC_LIMIT;  // the per-CTA slots would not fit
+    const uint32_t rpb = (N + grid - 1) / grid;
+    uint32_t block = ((rpb + 31) / 32) * 32;
+    if (block < 64) block = 64;
+    if (block > 1024) block = 1024;
+    const size_t smem = (size_t)rpb * 28 + (size_t)((rpb + 31) / 32) * 4 + 16;
+    if (smem > (size_t)dv->smem_optin) return NGS_ERR_UNSUPPORTED;
+
+    unsigned char* sc = dv->scratch;
+    SortedDemand* dem = reinterpret_cast<SortedDemand*>(sc + NA_DEM_OFF);
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(sc + NA_KEYS_OFF);
+    unsigned long long* mx = reinterpret_cast<unsigned long long*>(sc + NA_MX_OFF);
+    uint32_t* done = reinterpret_cast<uint32_t*>(sc + NA_DONE_OFF);
+    int32_t* err = reinterpret_cast<int32_t*>(sc + NA_ERR_OFF);
+    // the array still holds the previous call's words: everything the kernel expects to find at
+    // zero is cleared here, in stream order, before the launch
+    if (cudaMemsetAsync(keys, 0, sizeof(unsigned long long) * (size_t)n_pods * grid, st) != cudaSuccess ||
+        cudaMemsetAsync(mx, 0, sizeof(unsigned long long) * (size_t)n_pods, st) != cudaSuccess ||
+        cudaMemsetAsync(done, 0, sizeof(uint32_t) * (size_t)n_pods, st) != cudaSuccess ||
+        cudaMemsetAsync(err, 0, sizeof(int32_t), st) != cudaSuccess)
+        return NGS_ERR_CUDA;
+    if (cudaFuncSetAttribute(k_schedule, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return NGS_ERR_CUDA;
+    k_prep_demands<<<(n_pods + 127) / 128, 128, 0, st>>>(d_percent, d_n_containers, max_c, d_policy, n_pods, dem, err);
+    if (cudaGetLastError() != cudaSuccess) return NGS_ERR_CUDA;
+
+    BatchParams bp;
+    memset(&bp, 0, sizeof(bp));
+    bp.T.free = snap->free;
+    bp.T.gcount = snap->gpu_count;
+    bp.T.rl = snap->remain_load;
+    bp.T.tenths = snap->tenths;
+    bp.T.ts = snap->ts;
+    bp.T.tag = snap->plan_tag;
+    bp.T.cscore = snap->plan_score;
+    bp.T.n = snap->n_nodes;
+    bp.T.first = snap->first_node;
+    bp.dem = dem;
+    bp.P = n_pods;
+    bp.lp = lp;
+    bp.seed_seq = seed + seq0;
+    bp.node_out = d_node_out;
+    bp.score_out = d_score_out;
+    bp.gpu_idx_out = d_gpu_idx_out;
+    bp.max_c = max_c;
+    bp.keys = keys;
+    bp.done = done;
+    bp.mx = mx;
+    bp.world = 1;
+    bp.rank = 0;
+    bp.gwin = nullptr;
+    bp.err = err;
+    bp.rows_per_block = rpb;
+    void* args[] = {&bp};
+    if (cudaLaunchCooperativeKernel((void*)k_schedule, dim3(grid), dim3(block), args, smem, st) != cudaSuccess) return NGS_ERR_CUDA;
+    int32_t dev_status = NGS_OK;  // device-side validation / timeout word of this batch
+    if (cudaMemcpyAsync(&dev_status, err, sizeof(dev_status), cudaMemcpyDeviceToHost, st) != cudaSuccess) return NGS_ERR_CUDA;
+    if (cudaStreamSynchronize(st) != cudaSuccess) return NGS_ERR_CUDA;
+    return dev_status;
+}

@@ -198,6 +198,18 @@ class GpuDealer:
         self._check(self._lib.ngs_xchg_attach(self._h, rank, world, handles))
 
 
+def schedule_batch_noalloc(view, n_pods, d_percent, d_ncont, max_c, d_policy, d_node, d_score, d_gidx, load=None, seed=0,
+                           seq0=0, device=0, stream=None):
+    """ngs_schedule_batch_noalloc: schedule a batch on caller-owned tables without any allocation by
+    the library (hosts whose device memory belongs to another allocator, or that must stay clear of
+    cudaMalloc's device-wide synchronisation on the scheduling path).  `view` is an
+    _abi.SnapshotView of device pointers, the other pointer arguments are raw device addresses.
+    At most _abi.NOALLOC_MAX_PODS pods; waits for the batch and returns its status code.
+    Calls on one device must not overlap: they share one fixed scratch array."""
+    return _abi.load().ngs_schedule_batch_noalloc(device, stream, C.byref(view), n_pods, d_percent, d_ncont, max_c, d_policy,
+                                                  _ref(load), seed, seq0, d_node, d_score, d_gidx)
+
+
 def parse_usage(s: str):
     v = C.c_double(0.0)
     ok = _abi.load().ngs_parse_usage(s.encode(), C.byref(v))
