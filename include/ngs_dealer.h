@@ -135,6 +135,10 @@ int ngs_parse_update_time(const char *s, int64_t *ts_out);  /* "2006-01-02T15:04
 int ngs_assume(ngs_dealer *h, const uint32_t *idx, uint32_t n, const int32_t *percent, int n_containers, int policy,
                const ngs_load_ctx *load, uint8_t *feasible, int8_t *reason, int32_t *score, int32_t *plan,
                int32_t *n_emitted);
+/* ngs_assume over rows 0..n-1 with feasible[n] / score[n] (either may be NULL) left in DEVICE memory:
+ * no copies and no synchronisation; results are valid after ngs_sync() (dealer.go:89-153). */
+int ngs_assume_dev(ngs_dealer *h, uint32_t n, const int32_t *percent, int n_containers, int policy,
+                   const ngs_load_ctx *load, uint8_t *d_feasible, int32_t *d_score);
 /* DealerImpl.Score (dealer.go:138-153): cached Plan.Score of the last ngs_assume with the same
  * demand, else a fresh evaluation; unknown / infeasible -> NGS_SCORE_MIN. */
 int ngs_score(ngs_dealer *h, const uint32_t *idx, uint32_t n, const int32_t *percent, int n_containers, int policy,

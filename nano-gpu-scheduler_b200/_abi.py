@@ -25,7 +25,7 @@ METRIC_CORE, METRIC_MEMORY = 0, 1
 SYMBOLS = [
     "ngs_abi_version", "ngs_strerror", "ngs_last_error", "ngs_create", "ngs_destroy", "ngs_stream", "ngs_sync",
     "ngs_stats", "ngs_node_upsert", "ngs_snapshot_load", "ngs_snapshot_read", "ngs_node_apply", "ngs_load_add_node",
-    "ngs_load_update", "ngs_load_update_bulk", "ngs_parse_usage", "ngs_parse_update_time", "ngs_assume", "ngs_score",
+    "ngs_load_update", "ngs_load_update_bulk", "ngs_parse_usage", "ngs_parse_update_time", "ngs_assume", "ngs_assume_dev", "ngs_score",
     "ngs_bind", "ngs_schedule_batch", "ngs_schedule_batch_dev", "ngs_xchg_export", "ngs_xchg_attach",
     "ngs_schedule_batch_noalloc",
 ]
@@ -101,6 +101,7 @@ def load():
     L.ngs_parse_usage.argtypes = [C.c_char_p, C.POINTER(dbl)]
     L.ngs_parse_update_time.argtypes = [C.c_char_p, C.POINTER(i64)]
     L.ngs_assume.argtypes = [vp, vp, u32, vp, ci, ci, vp, vp, vp, vp, vp, vp]
+    L.ngs_assume_dev.argtypes = [vp, u32, vp, ci, ci, vp, vp, vp]
     L.ngs_score.argtypes = [vp, vp, u32, vp, ci, ci, vp, vp]
     L.ngs_bind.argtypes = [vp, u32, vp, ci, ci, vp, vp, vp]
     L.ngs_schedule_batch.argtypes = [vp, u32, vp, vp, ci, vp, vp, u64, u64, vp, vp, vp]

@@ -339,8 +339,8 @@ struct BatchParams {
     int32_t* gpu_idx_out;
     int max_c;
     unsigned long long* keys;  // [P][gridDim.x] one slot per CTA per pod, zero before launch
-    uint32_t* done;            // [P] arrival counters, zero before launch
-    unsigned long long* mx;    // [P] arg-max words (atomicMax), zero before launch
+    uint32_t* done;            // [P] arrival counters of the random-policy exchange, zero before launch
+    ulonglong2* xw;            // [P] arg-max exchange words {x: atomicMax key, y: arrival counter}, zero before launch
     // node-range sharding over the GPUs of one box: every rank runs this same kernel on
     // its own rows; CTA 0 of each rank trades the rank's result with the peers through
     // peer-mapped memory (plain 8-byte stores over NVLink), then tells its own CTAs
@@ -547,40 +547,150 @@ __device__ __forceinline__ unsigned long long cross_rank_exchange(const BatchPar
     return got;
 }
 
+// arg-max exchange word: the key (atomicMax) and the arrival counter share one 16-byte word, so one
+// 16-byte load returns both.  A CTA bumps the counter only after its atomicMax has returned, hence
+// a load that sees the counter full also sees the final key.  Returns false on time-out.
+__device__ __forceinline__ bool wait_exchange(const ulonglong2* w, uint32_t target, int32_t* err, unsigned long long* key) {
+    unsigned long long a, b;
+    const long long t0 = clock64();
+    uint32_t spins = 0;
+    for (;;) {
+        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(w) : "memory");
+        if ((uint32_t)b >= target) {
+            *key = a;
+            return true;
+        }
+        if ((++spins & 255u) == 0) {
+            if (*reinterpret_cast<volatile int32_t*>(err) != 0 || clock64() - t0 > SPIN_TIMEOUT_CYCLES) {
+                atomicCAS(err, 0, NGS_ERR_TIMEOUT);
+                *key = 0;
+                return false;
+            }
+        }
+    }
+}
+
 __device__ __forceinline__ unsigned long long read_slot(const unsigned long long* slot, bool dead) {
     unsigned long long v = ld_relaxed_u64(slot);
     while (!(v & KEY_VALID) && !dead) v = ld_relaxed_u64(slot);  // normally valid at the first read
     return v & ~KEY_VALID;
 }
 
+// filter (and rate) this worker warp's rows for one pod.  Argmax policies: every thread keeps the
+// best key of its rows in spec_key.  Random policy: one feasibility bit per row in spec_ok and in
+// the pod's feasbits words, the warp's count in cnt (lane 0).  FIXUP re-does only the thread that
+// owns row `dirty` (the row the previous pod was just bound to); the other lanes keep their
+// results and merely take part in the warp-wide votes.  Must be called by all 32 lanes.
+template <bool FIXUP>
+__device__ __forceinline__ void filter_pass(const SmemRows& S, const SortedDemand* dem, uint32_t wt, uint32_t WT, uint32_t n_iter,
+                                            uint32_t my_rows, uint32_t node0, uint32_t lane, int g, int gbase, int dirty,
+                                            uint32_t* fb, uint64_t& spec_key, uint64_t& spec_ok, uint32_t& cnt) {
+    const int policy = dem->policy;
+    const bool spread = policy == NGS_POLICY_SPREAD;
+    const bool mine = !FIXUP || ((uint32_t)dirty % WT == wt);
+    if (policy == NGS_POLICY_RANDOM) {
+        uint32_t c = 0;
+        for (uint32_t it = 0; it < n_iter; it++) {
+            const uint32_t r = it * WT + wt;
+            bool ok;
+            if (mine) {
+                ok = r < my_rows && eval_row_sample(S, r, dem);
+                spec_ok = (spec_ok & ~(1ull << it)) | ((uint64_t)ok << it);
+            } else {
+                ok = (spec_ok >> it) & 1ull;
+            }
+            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, ok);
+            if (lane == 0 && r < my_rows) {
+                fb[r >> 5] = bal;
+                c += __popc(bal);
+            }
+        }
+        cnt = c;
+        return;
+    }
+    if (mine) spec_key = 0;
+    for (uint32_t it = 0; it < n_iter; it++) {
+        const uint32_t r = it * WT + wt;
+        int cls = FEAS_NO;
+        if (mine && r < my_rows) {
+            const uint32_t meta = S.meta[r];
+            if (((meta >> 24) & 15) != 0) {
+                int f[8];
+                unpack_free(S.fA[r], S.fB[r], f);
+                cls = classify_row(f, dem, true);
+            }
+        }
+        // rows the shortcuts leave open are searched exactly right away, 8 lanes per row, 4 rows a time;
+        // the verdict goes back to the lane that owns the row
+        uint32_t und = __ballot_sync(0xFFFFFFFFu, cls == FEAS_UNDECIDED);
+        while (und) {  // warp-uniform
+            uint32_t t = und;
+            for (uint32_t q = 0; q < (lane >> 3); q++) t &= t - 1;  // group j takes the j-th open row
+            const bool has = t != 0;
+            const uint32_t rr = __shfl_sync(0xFFFFFFFFu, r, has ? __ffs(t) - 1 : 0);
+            const uint32_t meta = S.meta[rr];
+            const int G = has ? (int)((meta >> 24) & 15) : 0;
+            const bool ok = choose_group8<false>(g, gbase, smem_cell(S, rr, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem,
+                                                 nullptr, nullptr, nullptr);
+            const uint32_t okb = __ballot_sync(0xFFFFFFFFu, has && ok && g == 0);  // group j's verdict at bit 8j
+            if ((und >> lane) & 1u) {
+                const uint32_t j = __popc(und & ((1u << lane) - 1u));
+                if (j < 4) cls = ((okb >> (8 * j)) & 1u) ? FEAS_YES : FEAS_NO;
+            }
+            und &= und - 1;
+            und &= und - 1;
+            und &= und - 1;
+            und &= und - 1;
+        }
+        if (cls == FEAS_YES) {
+            const uint64_t key = make_key(spread ? S.scS[r] : S.scB[r], node0 + r);
+            spec_key = key > spec_key ? key : spec_key;
+        }
+    }
+}
+
 // K6.  One CTA per SM (cooperative launch, so every CTA is resident), each owning a contiguous
-// node range held in shared memory for the whole batch.  Per pod, in order:
-//   1. filter: one thread per row settles feasibility with the exact shortcuts of classify_row;
-//      the few rows they leave open are queued and searched exactly, 8 lanes per row
-//      (choose_group8).  Rate is a function of the row only (allocate.go:96), so both policies'
-//      rates sit beside the row and are refreshed when the row changes.
-//   2. arg-max: block reduce -> one 64-bit key per CTA -> slot + arrival counter in L2; while the
-//      other CTAs' keys are in flight, 8 lanes of warp 0 work out the exact plan of this CTA's
-//      best row.  Every CTA then reads all slots and finds the same winner.
+// node range held in shared memory for the whole batch.  Warps 0 and 1 are control warps, the
+// others ("workers") own the rows.  Pods are decided strictly in order, but the work is pipelined:
+// while the control warps settle pod p, the workers already filter pod p+1 on the rows as they
+// stand; binding pod p changes exactly one row, so afterwards only that row is filtered again.
+//   filter (workers): one thread per row settles feasibility with the exact shortcuts of
+//      classify_row; the ~1% of rows they leave open are searched exactly right away, 8 lanes per
+//      row (choose_group8).  Rate is a function of the row only (allocate.go:96), so both
+//      policies' rates sit beside the row and are refreshed when the row changes.
+//   arg-max (warp 1): per-warp maxima -> one 64-bit key per CTA -> atomicMax into the pod's word in
+//      L2, arrival counter, spin, read (K5: plus the cross-GPU trade).  Meanwhile warp 0 works out the
+//      exact plan of this CTA's best row, 8 lanes per row.
 //      (random policy: slots carry feasible counts; seeded k-th pick over the feasible set)
-//   3. bind: the CTA owning the winning row publishes its plan; no other CTA ever reads that row.
+//   bind (warp 0 of the CTA that owns the winner): publish the plan, update the row.
 __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    __shared__ SortedDemand s_dem[2];
-    __shared__ uint64_t s_red[32];
+    __shared__ SortedDemand s_dem[4];
+    __shared__ uint64_t s_red[2][32];
     __shared__ uint64_t s_win;  // the pod's winning key, handed from the exchange warp to the plan warp
+    __shared__ int s_dirty;     // row of this CTA the pod was bound to, -1 if none
     __shared__ int s_abort;
     const uint32_t rpb = bp.rows_per_block;
-    if (threadIdx.x == 0) s_abort = 0;
+    if (threadIdx.x == 0) {
+        s_abort = 0;
+        s_dirty = -1;
+    }
+    const uint32_t fwords = (rpb + 31) / 32;
     SmemRows S;
     S.fA = reinterpret_cast<uint2*>(smem_raw);
     S.fB = S.fA + rpb;
     S.meta = reinterpret_cast<uint32_t*>(S.fB + rpb);
     S.scB = reinterpret_cast<int32_t*>(S.meta + rpb);
     S.scS = S.scB + rpb;
-    S.feasbits = reinterpret_cast<uint32_t*>(S.scS + rpb);
+    S.feasbits = reinterpret_cast<uint32_t*>(S.scS + rpb);  // two buffers of fwords words (pod parity)
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    // the two control warps are the LAST two: the SM's issue arbiter favours high warp ids, and the
+    // control path (exchange, plan) is the latency-critical one
+    const uint32_t NW = nwarps - 2, WT = blockDim.x - 64;  // worker warps / threads
+    const uint32_t wt = tid, ww = warp;                    // worker ids (meaningful for warp < NW)
+    const bool is_worker = warp < NW;
+    const uint32_t cw = warp - NW;                         // control warp 0 (plan, bind) / 1 (exchange)
     const uint32_t row0 = blockIdx.x * rpb;
     const uint32_t my_rows = row0 < bp.T.n ? min(rpb, bp.T.n - row0) : 0u;
     const Tables& T = bp.T;
@@ -634,8 +744,8 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
         S.scB[r] = G ? rate_binpack(f, G, load_int) : 0;
         S.scS[r] = G ? rate_spread(f, G, load_int) : 0;
     }
-    if (tid < sizeof(SortedDemand) / 4 && bp.P > 0)
-        reinterpret_cast<uint32_t*>(&s_dem[0])[tid] = reinterpret_cast<const uint32_t*>(&bp.dem[0])[tid];
+    for (uint32_t i = tid; i < 2 * sizeof(SortedDemand) / 4; i += blockDim.x)
+        if (i / (sizeof(SortedDemand) / 4) < bp.P) reinterpret_cast<uint32_t*>(&s_dem[0])[i] = reinterpret_cast<const uint32_t*>(&bp.dem[0])[i];
     __syncthreads();
 
 #ifdef NGS_PHASE_TIMING
@@ -649,104 +759,75 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
 #define PHASE(i) do { } while (0)
 #define PHASE_AFTER_BARRIER(i) do { } while (0)
 #endif
-    const uint32_t n_iter = (my_rows + blockDim.x - 1) / blockDim.x;
+    const uint32_t n_iter = (my_rows + WT - 1) / WT;
     bool rl_pending = bp.lp.enabled != 0;  // RemainLoad write-back of the first load-aware Rate
+    uint64_t spec_key = 0, spec_ok = 0;    // this worker's results for the pod being filtered
+    uint32_t cnt = 0;
+
+    // allocate.go:193: LoadUsage leaves RemainLoad in the live node state.  SampleRater.Rate never
+    // calls it, so the table is only touched once a binpack/spread pod comes by.
+    auto write_back_rl = [&]() {
+        for (uint32_t r = tid; r < my_rows; r += blockDim.x) {
+            const uint32_t meta = S.meta[r];
+            const int G = (meta >> 24) & 15;
+            if (G == 0) continue;
+            uint2 out;
+            out.x = out.y = 0;
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                out.x |= (uint32_t)(uint8_t)(int8_t)(c < G ? (int)((meta >> (3 * c)) & 7) - 2 : 0) << (8 * c);
+                out.y |= (uint32_t)(uint8_t)(int8_t)(c + 4 < G ? (int)((meta >> (3 * (c + 4))) & 7) - 2 : 0) << (8 * c);
+            }
+            *reinterpret_cast<uint2*>(T.rl + (size_t)(row0 + r) * 8) = out;
+        }
+    };
+
+    // pod 0 is filtered before the loop; inside the loop the workers are always one pod ahead
+    if (bp.P > 0) {
+        if (rl_pending && s_dem[0].policy != NGS_POLICY_RANDOM) {
+            rl_pending = false;
+            write_back_rl();
+        }
+        if (is_worker) {
+            filter_pass<false>(S, &s_dem[0], wt, WT, n_iter, my_rows, T.first + row0, lane, g, gbase, -1, S.feasbits, spec_key, spec_ok, cnt);
+            if (s_dem[0].policy != NGS_POLICY_RANDOM) {
+                const uint64_t b = warp_max_u64(spec_key);
+                if (lane == 0) s_red[0][ww] = b;
+            } else if (lane == 0) {
+                s_red[0][ww] = cnt;
+            }
+        }
+    }
+    __syncthreads();
+
     for (uint32_t p = 0; p < bp.P; p++) {
-        const SortedDemand* dem = &s_dem[p & 1];
+        const SortedDemand* dem = &s_dem[p & 3];
         const int policy = dem->policy;
         const bool spread = policy == NGS_POLICY_SPREAD;
-        if (rl_pending && policy != NGS_POLICY_RANDOM) {
-            // allocate.go:193: LoadUsage leaves RemainLoad in the live node state.  SampleRater.Rate
-            // never calls it, so the table is only touched once a binpack/spread pod comes by.
+        const bool more = p + 1 < bp.P;
+        const SortedDemand* dem_next = &s_dem[(p + 1) & 3];
+        if (more && rl_pending && dem_next->policy != NGS_POLICY_RANDOM) {
             rl_pending = false;
-            for (uint32_t r = tid; r < my_rows; r += blockDim.x) {
-                const uint32_t meta = S.meta[r];
-                const int G = (meta >> 24) & 15;
-                if (G == 0) continue;
-                uint2 out;
-                out.x = out.y = 0;
-#pragma unroll
-                for (int c = 0; c < 4; c++) {
-                    out.x |= (uint32_t)(uint8_t)(int8_t)(c < G ? (int)((meta >> (3 * c)) & 7) - 2 : 0) << (8 * c);
-                    out.y |= (uint32_t)(uint8_t)(int8_t)(c + 4 < G ? (int)((meta >> (3 * (c + 4))) & 7) - 2 : 0) << (8 * c);
-                }
-                *reinterpret_cast<uint2*>(T.rl + (size_t)(row0 + r) * 8) = out;
-            }
+            write_back_rl();
         }
-        // stage the next pod's demand while this one is evaluated (last warp: the least loaded)
-        if (warp == nwarps - 1 && p + 1 < bp.P)
-            for (uint32_t i = lane; i < sizeof(SortedDemand) / 4; i += 32)
-                reinterpret_cast<uint32_t*>(&s_dem[(p + 1) & 1])[i] = reinterpret_cast<const uint32_t*>(&bp.dem[p + 1])[i];
-
-        // ---- 1. filter + score my rows ----
-        uint64_t best = 0;
-        uint32_t cnt = 0;
-        if (policy == NGS_POLICY_RANDOM) {
-            for (uint32_t it = 0; it < n_iter; it++) {
-                const uint32_t r = it * blockDim.x + tid;
-                const bool ok = r < my_rows && eval_row_sample(S, r, dem);
-                const uint32_t bal = __ballot_sync(0xFFFFFFFFu, ok);
-                if (lane == 0 && r < my_rows) {
-                    S.feasbits[r >> 5] = bal;
-                    cnt += __popc(bal);
-                }
-            }
+        if (is_worker) {
+            // ---- workers: filter pod p+1 on the rows as they stand (pod p's bind is still in flight) ----
+            if (more)
+                filter_pass<false>(S, dem_next, wt, WT, n_iter, my_rows, T.first + row0, lane, g, gbase, -1,
+                                   S.feasbits + ((p + 1) & 1) * fwords, spec_key, spec_ok, cnt);
             PHASE(0);
-            if (lane == 0) s_red[warp] = cnt;
-        } else {
-            // one thread per row: exact shortcuts; the rows they leave open are searched right away
-            // by this warp, 8 lanes per row, four rows at a time
-            for (uint32_t it = 0; it < n_iter; it++) {
-                const uint32_t r = it * blockDim.x + tid;
-                int cls = FEAS_NO;
-                if (r < my_rows) {
-                    const uint32_t meta = S.meta[r];
-                    if (((meta >> 24) & 15) != 0) {
-                        int f[8];
-                        unpack_free(S.fA[r], S.fB[r], f);
-                        cls = classify_row(f, dem, true);
-                    }
-                }
-                if (cls == FEAS_YES) {
-                    const int sc = spread ? S.scS[r] : S.scB[r];
-                    const uint64_t key = make_key(sc, T.first + row0 + r);
-                    best = key > best ? key : best;
-                }
-                uint32_t und = __ballot_sync(0xFFFFFFFFu, cls == FEAS_UNDECIDED);
-                while (und) {  // warp-uniform
-                    uint32_t t = und;
-                    for (uint32_t q = 0; q < (lane >> 3); q++) t &= t - 1;  // group j takes the j-th open row
-                    const bool has = t != 0;
-                    const uint32_t rr = __shfl_sync(0xFFFFFFFFu, r, has ? __ffs(t) - 1 : 0);
-                    und &= und - 1;
-                    und &= und - 1;
-                    und &= und - 1;
-                    und &= und - 1;
-                    const uint32_t meta = S.meta[rr];
-                    const int G = has ? (int)((meta >> 24) & 15) : 0;
-                    const bool ok = choose_group8<false>(g, gbase, smem_cell(S, rr, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem,
-                                                         nullptr, nullptr, nullptr);
-                    if (has && ok && g == 0) {
-                        const int sc = spread ? S.scS[rr] : S.scB[rr];
-                        const uint64_t key = make_key(sc, T.first + row0 + rr);
-                        best = key > best ? key : best;
-                    }
-                }
-            }
-            PHASE(0);
-            PHASE(2);
-            best = warp_max_u64(best);
-            if (lane == 0) s_red[warp] = best;
-        }
-        __syncthreads();
-        PHASE_AFTER_BARRIER(3);
-        // ---- 2. block reduce, exchange, plan ----
-        if (policy == NGS_POLICY_RANDOM) {
-          if (warp == 0) {
+        } else if (policy == NGS_POLICY_RANDOM) {
+          if (cw == 0) {
+            // ---- control, random policy: counts -> seeded pick -> bind ----
             bool dead = false;
             unsigned long long* krow = bp.keys + (size_t)p * gridDim.x;
             uint32_t* done = bp.done + p;
-            uint64_t v = lane < nwarps ? s_red[lane] : 0;
+            const uint32_t* fb = S.feasbits + (p & 1) * fwords;
+            uint64_t v = lane < NW ? s_red[p & 1][lane] : 0;
+            if (lane == 0) s_dirty = -1;
+            if (p + 2 < bp.P)  // stage the demand the workers will need next
+                for (uint32_t i = lane; i < sizeof(SortedDemand) / 4; i += 32)
+                    reinterpret_cast<uint32_t*>(&s_dem[(p + 2) & 3])[i] = reinterpret_cast<const uint32_t*>(&bp.dem[p + 2])[i];
             {
                 uint32_t c = (uint32_t)v;
 #pragma unroll
@@ -820,7 +901,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                         const uint32_t wchunk = (nwords + 31) / 32;
                         const uint32_t w0 = min(lane * wchunk, nwords), w1 = min(w0 + wchunk, nwords);
                         uint32_t sb = 0;
-                        for (uint32_t wi = w0; wi < w1; wi++) sb += __popc(S.feasbits[wi]);
+                        for (uint32_t wi = w0; wi < w1; wi++) sb += __popc(fb[wi]);
                         uint32_t inc = sb;
 #pragma unroll
                         for (int o = 1; o < 32; o <<= 1) {
@@ -831,12 +912,13 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                         if (rank >= before && rank < before + sb) {
                             uint32_t need = rank - before;
                             for (uint32_t wi = w0; wi < w1; wi++) {
-                                uint32_t bits = S.feasbits[wi];
+                                uint32_t bits = fb[wi];
                                 const uint32_t pc = __popc(bits);
                                 if (need < pc) {
                                     for (uint32_t q = 0; q < need; q++) bits &= bits - 1;
                                     const uint32_t r = wi * 32 + (__ffs(bits) - 1);
                                     publish_sample(bp, S, r, row0 + r, dem, p);
+                                    s_dirty = (int)r;
                                     break;
                                 }
                                 need -= pc;
@@ -847,10 +929,10 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
             }
             if (dead && lane == 0) s_abort = 1;
           }
-        } else if (warp < 2) {
-            // warp 1 runs the exchange while warp 0 works out the exact plan of this CTA's best row
-            // (8 lanes per row); the plan is published only if that row is the global winner
-            uint64_t v = lane < nwarps ? s_red[lane] : 0;
+        } else {
+            // ---- control, arg-max policies: warp 1 runs the exchange while warp 0 works out the exact
+            // plan of this CTA's best row (published only if that row is the global winner) ----
+            uint64_t v = lane < NW ? s_red[p & 1][lane] : 0;
             v = warp_max_u64(v);
             const bool have = (v & KEY_FEASIBLE) != 0;
             const uint32_t my_r = have ? key_node(v) - T.first - row0 : 0u;
@@ -858,29 +940,27 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
             cm.fr = 0;
             cm.emit = 0;
             cm.n_emit = 0;
-            if (warp == 1) {
+            if (cw == 1) {
                 // exchange (fastest variant of profiles/tools/xchg_bench.cu): atomicMax into the pod's
                 // word; the arrival counter is bumped only after that atomic has returned (data
                 // dependence), so a full counter implies every CTA's key is in the word
-                uint32_t* done = bp.done + p;
                 bool dead = false;
+                ulonglong2* xw = bp.xw + p;
                 if (lane == 0) {
-                    const unsigned long long old = atomicMax(bp.mx + p, (unsigned long long)v);
-                    const uint32_t one = 1u + (uint32_t)(old >> 63);  // bit 63 is never set: always 1
-                    asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(done), "r"(one) : "memory");
+                    const unsigned long long old = atomicMax(&xw->x, (unsigned long long)v);
+                    const unsigned long long one = 1ull + (old >> 63);  // bit 63 is never set: always 1
+                    asm volatile("red.relaxed.gpu.global.add.u64 [%0], %1;" ::"l"(&xw->y), "l"(one) : "memory");
                 }
                 if (bp.world == 1) {
                     if (lane == 0) {
-                        dead = !wait_done(done, gridDim.x, bp.err);
-                        s_win = ld_relaxed_u64(bp.mx + p);
+                        unsigned long long m;
+                        dead = !wait_exchange(xw, gridDim.x, bp.err, &m);
+                        s_win = m;
                     }
                 } else if (blockIdx.x == 0) {
                     // K5: this rank's best key goes to every peer; the best over all ranks comes back
                     unsigned long long mloc = 0;
-                    if (lane == 0) {
-                        dead = !wait_done(done, gridDim.x, bp.err);
-                        mloc = ld_relaxed_u64(bp.mx + p);
-                    }
+                    if (lane == 0) dead = !wait_exchange(xw, gridDim.x, bp.err, &mloc);
                     mloc = __shfl_sync(0xFFFFFFFFu, mloc, 0);
                     dead = __any_sync(0xFFFFFFFFu, dead);
                     const uint64_t mg = warp_max_u64(cross_rank_exchange(bp, p, mloc, lane, dead));
@@ -892,16 +972,22 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                     s_win = wait_valid(bp.gwin + p, bp.err, dead);
                 }
                 if (dead && lane == 0) s_abort = 1;
-            } else if (have) {
-                const uint32_t meta = S.meta[my_r];
-                const int G = (meta >> 24) & 15;
-                choose_group8<true>(g, gbase, smem_cell(S, my_r, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem, &cm.emit,
-                                    &cm.n_emit, &cm.fr);
+            } else {
+                if (lane == 0) s_dirty = -1;
+                if (p + 2 < bp.P)  // stage the demand the workers will need next
+                    for (uint32_t i = lane; i < sizeof(SortedDemand) / 4; i += 32)
+                        reinterpret_cast<uint32_t*>(&s_dem[(p + 2) & 3])[i] = reinterpret_cast<const uint32_t*>(&bp.dem[p + 2])[i];
+                if (have) {
+                    const uint32_t meta = S.meta[my_r];
+                    const int G = (meta >> 24) & 15;
+                    choose_group8<true>(g, gbase, smem_cell(S, my_r, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem, &cm.emit,
+                                        &cm.n_emit, &cm.fr);
+                }
             }
             PHASE(4);
-            asm volatile("bar.sync 1, 64;" ::: "memory");  // warps 0 and 1 only
+            asm volatile("bar.sync 1, 64;" ::: "memory");  // the two control warps only
             PHASE_AFTER_BARRIER(5);
-            if (warp == 0) {
+            if (cw == 0) {
                 const uint64_t m = s_win;
                 if (!(m & KEY_FEASIBLE)) {
                     if (blockIdx.x == 0 && lane == 0) publish_none(bp, p);
@@ -912,20 +998,37 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                     bp.node_out[p] = (int32_t)key_node(m);
                     bp.score_out[p] = key_score(m);
                 } else if (have && m == v && lane < 8) {
-                    // ---- 3. bind on the owner ----
+                    // ---- bind on the owner ----
                     publish_group(bp, S, my_r, row0 + my_r, dem, p, key_score(m), cm, g);
+                    if (lane == 0) s_dirty = (int)my_r;
                 }
                 PHASE(6);
             }
         }
+        __syncthreads();  // pod p is bound; the workers' results for pod p+1 are in registers
+        PHASE_AFTER_BARRIER(1);
+        if (s_abort) break;  // a peer never posted: give up instead of hanging the GPU
+        if (is_worker && more) {
+            // ---- fix-up: only the row pod p was bound to can have changed ----
+            const int dirty = s_dirty;
+            if (dirty >= 0 && ((uint32_t)dirty % WT) / 32 == ww)
+                filter_pass<true>(S, dem_next, wt, WT, n_iter, my_rows, T.first + row0, lane, g, gbase, dirty,
+                                  S.feasbits + ((p + 1) & 1) * fwords, spec_key, spec_ok, cnt);
+            if (dem_next->policy != NGS_POLICY_RANDOM) {
+                const uint64_t b = warp_max_u64(spec_key);
+                if (lane == 0) s_red[(p + 1) & 1][ww] = b;
+            } else if (lane == 0) {
+                s_red[(p + 1) & 1][ww] = cnt;
+            }
+            PHASE(2);
+        }
         __syncthreads();
-        PHASE_AFTER_BARRIER(7);
-        if (s_abort) break;  // a peer CTA never posted: give up instead of hanging the GPU
+        PHASE_AFTER_BARRIER(3);
     }
 #ifdef NGS_PHASE_TIMING
-    if (tid == 0 && bp.dbg)
+    if (tid == NW * 32 && bp.dbg)
         for (int i = 0; i < 8; i++) bp.dbg[blockIdx.x * 16 + i] = (unsigned long long)ph[i];
-    if (tid == 32 && bp.dbg)
+    if (tid == NW * 32 + 32 && bp.dbg)
         for (int i = 0; i < 8; i++) bp.dbg[blockIdx.x * 16 + 8 + i] = (unsigned long long)ph[i];
 #endif
 }
@@ -1082,8 +1185,8 @@ int ensure_batch(ngs_dealer* h) {
     const size_t in_words = (size_t)cap * (NGS_MAX_CONTAINERS + 2), out_words = (size_t)cap * (NGS_MAX_CONTAINERS + 2);
     CU(h, cudaMalloc(&h->d_dem, sizeof(SortedDemand) * cap));
     // key slots [cap][num_sms] followed by the arrival counters [cap]
-    // + one arg-max word per pod [cap]
-    CU(h, cudaMalloc(&h->d_keys, sizeof(unsigned long long) * cap * h->num_sms + sizeof(unsigned long long) * cap + sizeof(uint32_t) * cap));
+    // + one 16-byte arg-max exchange word per pod [cap] + the random-policy counters [cap]
+    CU(h, cudaMalloc(&h->d_keys, sizeof(unsigned long long) * cap * h->num_sms + sizeof(ulonglong2) * cap + sizeof(uint32_t) * cap));
     CU(h, cudaMalloc(&h->d_pod_in, in_words * 4));
     CU(h, cudaMalloc(&h->d_pod_out, out_words * 4));
     CU(h, cudaMallocHost(&h->h_pod_in, in_words * 4));
@@ -1101,19 +1204,18 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     if (grid < 1) grid = 1;
     if (grid > (uint32_t)h->num_sms) grid = (uint32_t)h->num_sms;
     const uint32_t rpb = (N + grid - 1) / grid;
-    uint32_t block = ((rpb + 31) / 32) * 32;
-    if (block < 64) block = 64;
+    uint32_t block = ((rpb + 31) / 32) * 32 + 64;  // one worker thread per row (up to 960) + two control warps
     if (block > 1024) block = 1024;
-    const size_t smem = (size_t)rpb * 28 + (size_t)((rpb + 31) / 32) * 4 + 16;  // rows + feasbits
+    const size_t smem = (size_t)rpb * 28 + (size_t)((rpb + 31) / 32) * 8 + 16;  // rows + two feasbits buffers
     if (smem > (size_t)h->smem_optin)
         return fail(h, NGS_ERR_UNSUPPORTED, "%u rows per SM need %zu B shared memory (> %d): shard the cluster over more GPUs", rpb, smem, h->smem_optin);
     CU(h, cudaFuncSetAttribute(k_schedule, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_prep_demands<<<(P + 127) / 128, 128, 0, h->stream>>>(d_percent, d_ncont, max_c, d_policy, P, h->d_dem, h->d_err);
     CU(h, cudaGetLastError());
-    unsigned long long* d_mx = h->d_keys + (size_t)h->batch_cap * h->num_sms;
-    uint32_t* d_done = reinterpret_cast<uint32_t*>(d_mx + h->batch_cap);
+    ulonglong2* d_xw = reinterpret_cast<ulonglong2*>(h->d_keys + (size_t)h->batch_cap * h->num_sms);  // 16 B aligned
+    uint32_t* d_done = reinterpret_cast<uint32_t*>(d_xw + h->batch_cap);
     CU(h, cudaMemsetAsync(h->d_keys, 0, sizeof(unsigned long long) * (size_t)P * grid, h->stream));
-    CU(h, cudaMemsetAsync(d_mx, 0, sizeof(unsigned long long) * (size_t)P, h->stream));
+    CU(h, cudaMemsetAsync(d_xw, 0, sizeof(ulonglong2) * (size_t)P, h->stream));
     CU(h, cudaMemsetAsync(d_done, 0, sizeof(uint32_t) * (size_t)P, h->stream));
     BatchParams bp;
     bp.T = h->T;
@@ -1127,7 +1229,7 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     bp.max_c = max_c;
     bp.keys = h->d_keys;
     bp.done = d_done;
-    bp.mx = d_mx;
+    bp.xw = d_xw;
     bp.world = (uint32_t)h->world;
     bp.rank = (uint32_t)h->rank;
     bp.gwin = h->d_gwin;
@@ -1467,6 +1569,33 @@ int ngs_assume(ngs_dealer* h, const uint32_t* idx, uint32_t n, const int32_t* pe
     return run_assume(h, MODE_ASSUME, idx, n, percent, n_containers, policy, load, feasible, reason, score, plan, n_emitted);
 }
 
+// DealerImpl.Assume + Score over rows [0, n) with the per-node outputs left in device memory
+// (no copies, no synchronisation): what a caller that keeps the arg-max on the GPU uses, and what
+// bench.py times for the scan kernel's own roofline.
+int ngs_assume_dev(ngs_dealer* h, uint32_t n, const int32_t* percent, int n_containers, int policy, const ngs_load_ctx* load,
+                   uint8_t* d_feasible, int32_t* d_score) {
+    if (!h) return NGS_ERR_INVALID;
+    PodDemand pd;
+    LoadParams lp;
+    int rc = make_demand(h, percent, n_containers, policy, &pd);
+    if (rc) return rc;
+    rc = make_load(h, load, &lp);
+    if (rc) return rc;
+    if (n > h->T.n) return fail(h, NGS_ERR_INVALID, "n=%u exceeds the %u rows of this shard", n, h->T.n);
+    if (n == 0) return NGS_OK;
+    CU(h, cudaSetDevice(h->device));
+    const uint32_t gen = demand_generation(h, pd);
+    const int block = 256;
+    int grid = (int)((n + block - 1) / block);
+    const int max_grid = h->num_sms * 8;
+    if (grid > max_grid) grid = max_grid;
+    k_assume<false><<<grid, block, 0, h->stream>>>(h->T, nullptr, n, pd, lp, MODE_ASSUME, gen, d_feasible, nullptr, d_score, nullptr, nullptr);
+    CU(h, cudaGetLastError());
+    h->stats.kernel_launches++;
+    h->stats.node_evals += n;
+    return NGS_OK;
+}
+
 int ngs_score(ngs_dealer* h, const uint32_t* idx, uint32_t n, const int32_t* percent, int n_containers, int policy,
               const ngs_load_ctx* load, int32_t* score) {
     if (!score) return NGS_ERR_INVALID;
@@ -1622,7 +1751,7 @@ namespace {
 
 constexpr size_t NA_DEM_BYTES = sizeof(SortedDemand) * NGS_NOALLOC_MAX_PODS;                                      // sorted demands
 constexpr size_t NA_KEYS_BYTES = sizeof(unsigned long long) * (size_t)NGS_NOALLOC_MAX_PODS * NGS_NOALLOC_MAX_CTAS;  // per-CTA slots
-constexpr size_t NA_MX_BYTES = sizeof(unsigned long long) * NGS_NOALLOC_MAX_PODS;                                  // arg-max words
+constexpr size_t NA_MX_BYTES = sizeof(ulonglong2) * NGS_NOALLOC_MAX_PODS;                                          // arg-max exchange words
 constexpr size_t NA_DONE_BYTES = sizeof(uint32_t) * NGS_NOALLOC_MAX_PODS;                                          // arrival counters
 constexpr size_t NA_DEM_OFF = 0;
 constexpr size_t NA_KEYS_OFF = NA_DEM_OFF + NA_DEM_BYTES;
@@ -1697,22 +1826,21 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     if (grid > (uint32_t)dv->num_sms) grid = (uint32_t)dv->num_sms;
     if (grid > NGS_NOALLOC_MAX_CTAS) return NGS_ERR_NOALLOC_LIMIT;  // the per-CTA slots would not fit
     const uint32_t rpb = (N + grid - 1) / grid;
-    uint32_t block = ((rpb + 31) / 32) * 32;
-    if (block < 64) block = 64;
+    uint32_t block = ((rpb + 31) / 32) * 32 + 64;
     if (block > 1024) block = 1024;
-    const size_t smem = (size_t)rpb * 28 + (size_t)((rpb + 31) / 32) * 4 + 16;
+    const size_t smem = (size_t)rpb * 28 + (size_t)((rpb + 31) / 32) * 8 + 16;
     if (smem > (size_t)dv->smem_optin) return NGS_ERR_UNSUPPORTED;
 
     unsigned char* sc = dv->scratch;
     SortedDemand* dem = reinterpret_cast<SortedDemand*>(sc + NA_DEM_OFF);
     unsigned long long* keys = reinterpret_cast<unsigned long long*>(sc + NA_KEYS_OFF);
-    unsigned long long* mx = reinterpret_cast<unsigned long long*>(sc + NA_MX_OFF);
+    ulonglong2* mx = reinterpret_cast<ulonglong2*>(sc + NA_MX_OFF);
     uint32_t* done = reinterpret_cast<uint32_t*>(sc + NA_DONE_OFF);
     int32_t* err = reinterpret_cast<int32_t*>(sc + NA_ERR_OFF);
     // the array still holds the previous call's words: everything the kernel expects to find at
     // zero is cleared here, in stream order, before the launch
     if (cudaMemsetAsync(keys, 0, sizeof(unsigned long long) * (size_t)n_pods * grid, st) != cudaSuccess ||
-        cudaMemsetAsync(mx, 0, sizeof(unsigned long long) * (size_t)n_pods, st) != cudaSuccess ||
+        cudaMemsetAsync(mx, 0, sizeof(ulonglong2) * (size_t)n_pods, st) != cudaSuccess ||
         cudaMemsetAsync(done, 0, sizeof(uint32_t) * (size_t)n_pods, st) != cudaSuccess ||
         cudaMemsetAsync(err, 0, sizeof(int32_t), st) != cudaSuccess)
         return NGS_ERR_CUDA;
@@ -1741,7 +1869,7 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     bp.max_c = max_c;
     bp.keys = keys;
     bp.done = done;
-    bp.mx = mx;
+    bp.xw = mx;
     bp.world = 1;
     bp.rank = 0;
     bp.gwin = nullptr;

@@ -149,6 +149,12 @@ class GpuDealer:
             res["n_emitted"] = nem[:n]
         return res
 
+    def assume_dev(self, percent, policy, d_feasible, d_score, load=None, n=None):
+        """filter + score rows 0..n-1, outputs to raw device addresses, no synchronisation"""
+        d = np.ascontiguousarray(percent, dtype=np.int32)
+        self._check(self._lib.ngs_assume_dev(self._h, self.n if n is None else n, _p(d), len(d), policy, _ref(load),
+                                             d_feasible, d_score))
+
     def score(self, percent, policy, idx=None, load=None, n=None):
         d = np.ascontiguousarray(percent, dtype=np.int32)
         if idx is None:
