@@ -43,6 +43,8 @@ struct Tables {
     uint32_t* ts;
     uint32_t* tag;
     int32_t* cscore;
+    const int16_t* blut;  // Binpack.Rate percent table [9][801] (nullptr: compute in fp64)
+    uint32_t rl_zero;     // the rl table is known to hold only zeros (no load-aware pass ran yet): skip reading it
     uint32_t n;      // rows in this shard
     uint32_t first;  // global node index of row 0
 };
@@ -56,50 +58,82 @@ struct RowEval {
 };
 
 __device__ __forceinline__ int4 ld_row4(const int32_t* p) { return __ldcg(reinterpret_cast<const int4*>(p)); }
+// one 256-bit load per 32-byte row (LDG.E.256 on sm_100a): every sector a warp touches is fully used
+__device__ __forceinline__ void ld_row8(const void* p, uint32_t (&v)[8]) {
+    asm volatile("ld.global.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                 : "l"(p));
+}
+// exact plan search kept out of line: the scan's common path (shortcuts decide) stays small
+// (arguments by value — four words of u16 pairs and the 3-bit RemainLoad codes — so that the caller's
+// row stays in registers)
+__device__ __noinline__ bool choose_sorted_slow(uint32_t p0, uint32_t p1, uint32_t p2, uint32_t p3, uint32_t rlmeta, int G, bool spread,
+                                                const SortedDemand* dem) {
+    const uint32_t pk[4] = {p0, p1, p2, p3};
+    uint32_t w[8];
+#pragma unroll
+    for (int g = 0; g < 8; g++) {
+        const int fr = (int)((pk[g >> 1] >> (16 * (g & 1))) & 0xFFFFu);
+        w[g] = g < G ? pack_cell(fr, (int)((rlmeta >> (3 * g)) & 7u), g) : W_PAD;
+    }
+    return choose_sorted<false>(w, G, spread, (rlmeta & 0xFFFFFFu) == RL0_META, dem, nullptr, nullptr);
+}
+__global__ void k_build_rate_lut(int16_t* lut) {
+    const int G = blockIdx.x;  // 0..8
+    for (int used = threadIdx.x; used < RATE_LUT_STRIDE; used += blockDim.x)
+        lut[G * RATE_LUT_STRIDE + used] = (G > 0 && used <= 100 * G) ? (int16_t)binpack_percent_fp64(used, G) : (int16_t)0;
+}
 
 // One full GPUs.Choose (allocate.go:92-100) on a row read from the global tables.
 // do_rate=false is the plan-cache hit of NodeInfo.Bind (node.go:72-78): the plan is re-derived
 // from the RemainLoad the filter pass left behind, without running Rate / LoadUsage again.
 template <bool PLAN>
 __device__ __forceinline__ RowEval eval_row_global(const Tables& T, uint32_t row, const SortedDemand* dem, const LoadParams& lp,
-                                                   bool do_rate) {
+                                                   bool do_rate, const double* pair = nullptr) {
     RowEval ev;
     ev.known = false;
     ev.feasible = false;
     ev.score = NGS_SCORE_MIN;
     ev.emit = 0;
     ev.n_emit = 0;
-    const int G = T.gcount[row];
-    if (G == 0) return ev;
-    ev.known = true;
+    // every load of the row is issued before the first use, so that they are all in flight together
     const int policy = dem->policy;
-    int f[8];
-    {
-        const int4 a = ld_row4(T.free + (size_t)row * 8), b = ld_row4(T.free + (size_t)row * 8 + 4);
-        f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w;
-        f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
-    }
-    int rlc[8];
-    int load_int = 0;
-    if (lp.enabled && do_rate && policy != NGS_POLICY_RANDOM) {
-        // rater.go:62-66 / 116-120: LoadUsage per GPU, which also rewrites RemainLoad
-        uint8_t tenths[2][8];
-        uint32_t ts[2][8];
+    const bool load_path = lp.enabled && do_rate && policy != NGS_POLICY_RANDOM;
+    const int G = T.gcount[row];
+    uint32_t v[8];
+    ld_row8(T.free + (size_t)row * 8, v);
+    uint32_t ts[2][8];
+    uint2 t8[2];
+    uint2 r8 = make_uint2(0u, 0u);
+    if (load_path) {
 #pragma unroll
         for (int m = 0; m < 2; m++) {
             const size_t off = ((size_t)m * T.n + row) * 8;
-            const uint2 t8 = __ldcg(reinterpret_cast<const uint2*>(T.tenths + off));
-            const uint4 t0 = __ldcg(reinterpret_cast<const uint4*>(T.ts + off));
-            const uint4 t1 = __ldcg(reinterpret_cast<const uint4*>(T.ts + off + 4));
+            t8[m] = __ldcg(reinterpret_cast<const uint2*>(T.tenths + off));
+            ld_row8(T.ts + off, ts[m]);
+        }
+    } else if (!T.rl_zero) {
+        r8 = __ldcg(reinterpret_cast<const uint2*>(T.rl + (size_t)row * 8));
+    }
+    if (G == 0) return ev;
+    ev.known = true;
+    int f[8];
+#pragma unroll
+    for (int g = 0; g < 8; g++) f[g] = (int)v[g];
+    int rlc[8];
+    int load_int = 0;
+    if (load_path) {
+        // rater.go:62-66 / 116-120: LoadUsage per GPU, which also rewrites RemainLoad
+        uint8_t tenths[2][8];
+#pragma unroll
+        for (int m = 0; m < 2; m++) {
 #pragma unroll
             for (int g = 0; g < 4; g++) {
-                tenths[m][g] = (uint8_t)(t8.x >> (8 * g));
-                tenths[m][g + 4] = (uint8_t)(t8.y >> (8 * g));
+                tenths[m][g] = (uint8_t)(t8[m].x >> (8 * g));
+                tenths[m][g + 4] = (uint8_t)(t8[m].y >> (8 * g));
             }
-            ts[m][0] = t0.x; ts[m][1] = t0.y; ts[m][2] = t0.z; ts[m][3] = t0.w;
-            ts[m][4] = t1.x; ts[m][5] = t1.y; ts[m][6] = t1.z; ts[m][7] = t1.w;
         }
-        load_usage_row(tenths, ts, lp, G, rlc, &load_int);
+        load_usage_row(tenths, ts, lp, G, rlc, &load_int, pair);
         uint2 out;
         out.x = out.y = 0;
 #pragma unroll
@@ -108,19 +142,27 @@ __device__ __forceinline__ RowEval eval_row_global(const Tables& T, uint32_t row
             out.y |= (uint32_t)(uint8_t)(int8_t)(g + 4 < G ? rlc[g + 4] - 2 : 0) << (8 * g);
         }
         *reinterpret_cast<uint2*>(T.rl + (size_t)row * 8) = out;
-    } else {
-        const uint2 r8 = __ldcg(reinterpret_cast<const uint2*>(T.rl + (size_t)row * 8));
+    } else {  // (r8 is all zeros when the table is known to be)
 #pragma unroll
         for (int g = 0; g < 4; g++) {
             rlc[g] = (int)(int8_t)(r8.x >> (8 * g)) + 2;
             rlc[g + 4] = (int)(int8_t)(r8.y >> (8 * g)) + 2;
         }
     }
-    if (do_rate) ev.score = rate_policy(policy, f, G, load_int);
+    if (do_rate) ev.score = rate_policy(policy, f, G, load_int, T.blut);
     if (!PLAN) {
         const int cls = classify_row(f, dem, policy != NGS_POLICY_RANDOM);
         if (cls != FEAS_UNDECIDED) {
             ev.feasible = cls == FEAS_YES;
+            return ev;
+        }
+        if (policy != NGS_POLICY_RANDOM) {
+            uint32_t rlmeta = 0;
+#pragma unroll
+            for (int g = 0; g < 8; g++) rlmeta |= (uint32_t)(g < G ? rlc[g] : 2) << (3 * g);
+            ev.feasible = choose_sorted_slow((uint32_t)f[0] | ((uint32_t)f[1] << 16), (uint32_t)f[2] | ((uint32_t)f[3] << 16),
+                                             (uint32_t)f[4] | ((uint32_t)f[5] << 16), (uint32_t)f[6] | ((uint32_t)f[7] << 16), rlmeta, G,
+                                             policy == NGS_POLICY_SPREAD, dem);
             return ev;
         }
     }
@@ -145,13 +187,18 @@ enum { MODE_ASSUME = 0, MODE_SCORE = 1 };
 // per candidate.  MODE_ASSUME recomputes every candidate (cleanPlan + Assume, dealer.go:123-124);
 // MODE_SCORE serves NodeInfo.Score (node.go:59-68) from the per-node cache when it holds a
 // plan for this demand generation.
+#ifndef NGS_K1_BLOCKS
+#define NGS_K1_BLOCKS 4  // resident 256-thread blocks per SM for the feasibility/score scan
+#endif
 template <bool PLAN>
-__global__ void __launch_bounds__(256) k_assume(Tables T, const uint32_t* __restrict__ idx, uint32_t n, PodDemand pd, LoadParams lp,
+__global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables T, const uint32_t* __restrict__ idx, uint32_t n, PodDemand pd, LoadParams lp,
                                                 int mode, uint32_t gen, uint8_t* __restrict__ feasible,
                                                 int8_t* __restrict__ reason, int32_t* __restrict__ score,
                                                 int32_t* __restrict__ plan, int32_t* __restrict__ n_emitted) {
     __shared__ SortedDemand dem;
+    __shared__ double s_pair[121];
     if (threadIdx.x == 0) sort_demand(pd.percent, pd.n, pd.policy, &dem);
+    if (lp.enabled) fill_usage_pair_table(s_pair, threadIdx.x, blockDim.x);
     __syncthreads();
     const int C = pd.n;
     for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
@@ -169,11 +216,14 @@ __global__ void __launch_bounds__(256) k_assume(Tables T, const uint32_t* __rest
                 ev.known = ev.feasible = cached = true;
                 ev.score = T.cscore[row];
             } else {
-                ev = eval_row_global<PLAN>(T, row, &dem, lp, true);
+                ev = eval_row_global<PLAN>(T, row, &dem, lp, true, s_pair);
             }
         }
         const bool ok = ev.known && ev.feasible;
-        if (ev.known && !cached) {
+        // The per-node plan cache only matters when load scheduling is on (the usage tables may move
+        // between filter and prioritize); without it a later Score / Bind re-derives the same values
+        // from the unchanged row, so the scan does not spend 8 bytes per node on the cache.
+        if (ev.known && !cached && lp.enabled) {
             if (ok) {  // node.go:55
                 T.tag[row] = gen;
                 T.cscore[row] = ev.score;
@@ -427,8 +477,10 @@ __device__ __forceinline__ void publish_group(const BatchParams& bp, const SmemR
     const int sumf = __reduce_add_sync(0xFFu, fr);
     const int cnt100 = __popc(__ballot_sync(0xFFu, valid && fr == 100));
     if (g == 0) {
-        const double usage = __ddiv_rn((double)(100 * G - sumf), (double)(100 * G));       // allocate.go:164-171
-        S.scB[r] = __double2int_rz(__dmul_rn(usage, 100.0)) + load_int * 50 - G;           // rater.go:69
+        const int used = 100 * G - sumf;                                                   // allocate.go:164-171
+        const int pct = (bp.T.blut != nullptr && used >= 0 && used <= 100 * G) ? (int)__ldg(bp.T.blut + G * RATE_LUT_STRIDE + used)
+                                                                                : binpack_percent_fp64(used, G);
+        S.scB[r] = pct + load_int * 50 - G;                                                // rater.go:69
         S.scS[r] = 100 * cnt100 + sumf / 10 - G - load_int;                                // rater.go:122
         bp.T.tag[row] = 0;  // node.go:82
         bp.node_out[p] = (int32_t)(bp.T.first + row);
@@ -461,7 +513,7 @@ __device__ __forceinline__ void publish_sample(const BatchParams& bp, const Smem
     b.x = (uint32_t)f[4] | ((uint32_t)f[5] << 16); b.y = (uint32_t)f[6] | ((uint32_t)f[7] << 16);
     S.fA[r] = a;
     S.fB[r] = b;
-    S.scB[r] = rate_binpack(f, G, load_int);
+    S.scB[r] = rate_binpack(f, G, load_int, bp.T.blut);
     S.scS[r] = rate_spread(f, G, load_int);
     int4* gp = reinterpret_cast<int4*>(bp.T.free + (size_t)row * 8);
     gp[0] = make_int4(f[0], f[1], f[2], f[3]);
@@ -741,7 +793,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
         S.fA[r] = pa;
         S.fB[r] = pb;
         S.meta[r] = meta;
-        S.scB[r] = G ? rate_binpack(f, G, load_int) : 0;
+        S.scB[r] = G ? rate_binpack(f, G, load_int, T.blut) : 0;
         S.scS[r] = G ? rate_spread(f, G, load_int) : 0;
     }
     for (uint32_t i = tid; i < 2 * sizeof(SortedDemand) / 4; i += blockDim.x)
@@ -1142,12 +1194,18 @@ int make_load(ngs_dealer* h, const ngs_load_ctx* L, LoadParams* lp) {
         else if (min_ts > 0xFFFFFFFFLL) lp->never[e] = 1;
         else lp->min_ts[e] = (uint32_t)min_ts;
     }
+    lp->canonical = lp->n_periods == 2 && lp->metric[0] == NGS_METRIC_CORE && lp->metric[1] == NGS_METRIC_MEMORY && !lp->never[0] &&
+                    !lp->never[1];
     return NGS_OK;
 }
 
 // Demand.Hash keyed plan cache (node.go:45-47): a new demand opens a new generation
-uint32_t demand_generation(ngs_dealer* h, const PodDemand& pd) {
+uint32_t demand_generation(ngs_dealer* h, const PodDemand& pd, bool load_on) {
     std::vector<int32_t> d(pd.percent, pd.percent + pd.n);
+    d.push_back(load_on ? 1 : 0);  // a switch of isLoadSchedule also starts a new generation
+    if (load_on) {
+        h->T.rl_zero = 0;  // a load-aware Rate writes RemainLoad (allocate.go:193)
+    }
     if (d != h->cur_demand) {
         h->cur_demand.swap(d);
         h->gen++;
@@ -1217,6 +1275,7 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     CU(h, cudaMemsetAsync(h->d_keys, 0, sizeof(unsigned long long) * (size_t)P * grid, h->stream));
     CU(h, cudaMemsetAsync(d_xw, 0, sizeof(ulonglong2) * (size_t)P, h->stream));
     CU(h, cudaMemsetAsync(d_done, 0, sizeof(uint32_t) * (size_t)P, h->stream));
+    if (lp.enabled) h->T.rl_zero = 0;  // the batch's load-aware Rate writes RemainLoad
     BatchParams bp;
     bp.T = h->T;
     bp.dem = h->d_dem;
@@ -1321,6 +1380,7 @@ int ngs_create(ngs_dealer** out, int device, uint32_t max_nodes, uint32_t first_
     const size_t N = max_nodes;
     h->T.n = max_nodes;
     h->T.first = first_node;
+    h->T.rl_zero = 1;
     CU(h, cudaMalloc(&h->T.free, N * 8 * 4));
     CU(h, cudaMalloc(&h->T.gcount, N));
     CU(h, cudaMalloc(&h->T.rl, N * 8));
@@ -1328,6 +1388,13 @@ int ngs_create(ngs_dealer** out, int device, uint32_t max_nodes, uint32_t first_
     CU(h, cudaMalloc(&h->T.ts, 2 * N * 8 * 4));
     CU(h, cudaMalloc(&h->T.tag, N * 4));
     CU(h, cudaMalloc(&h->T.cscore, N * 4));
+    {
+        int16_t* lut = nullptr;
+        CU(h, cudaMalloc(&lut, sizeof(int16_t) * 9 * RATE_LUT_STRIDE));
+        k_build_rate_lut<<<9, 256, 0, h->stream>>>(lut);
+        CU(h, cudaGetLastError());
+        h->T.blut = lut;
+    }
     CU(h, cudaMemsetAsync(h->T.free, 0, N * 8 * 4, h->stream));
     CU(h, cudaMemsetAsync(h->T.gcount, 0, N, h->stream));
     CU(h, cudaMemsetAsync(h->T.rl, 0, N * 8, h->stream));
@@ -1352,7 +1419,7 @@ int ngs_destroy(ngs_dealer* h) {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     cudaFree(h->T.free); cudaFree(h->T.gcount); cudaFree(h->T.rl); cudaFree(h->T.tenths); cudaFree(h->T.ts);
-    cudaFree(h->T.tag); cudaFree(h->T.cscore);
+    cudaFree(h->T.tag); cudaFree(h->T.cscore); cudaFree(const_cast<int16_t*>(h->T.blut));
     cudaFree(h->d_idx); cudaFree(h->d_feas); cudaFree(h->d_reason); cudaFree(h->d_score); cudaFree(h->d_plan); cudaFree(h->d_nem);
     cudaFree(h->d_bind); cudaFreeHost(h->h_bind); cudaFree(h->d_small); cudaFreeHost(h->h_small);
     cudaFree(h->d_dem); cudaFree(h->d_keys); cudaFree(h->d_pod_in); cudaFree(h->d_pod_out);
@@ -1427,6 +1494,7 @@ int ngs_snapshot_load(ngs_dealer* h, uint32_t first, uint32_t n, const uint8_t* 
     }
     CU(h, cudaSetDevice(h->device));
     CU(h, cudaMemcpyAsync(h->T.free + (size_t)r0 * 8, fr.data(), fr.size() * 4, cudaMemcpyHostToDevice, h->stream));
+    if (remain_load) h->T.rl_zero = 0;
     CU(h, cudaMemcpyAsync(h->T.rl + (size_t)r0 * 8, rl.data(), rl.size(), cudaMemcpyHostToDevice, h->stream));
     CU(h, cudaMemcpyAsync(h->T.gcount + r0, gpu_count, n, cudaMemcpyHostToDevice, h->stream));
     CU(h, cudaMemsetAsync(h->T.tag + r0, 0, (size_t)n * 4, h->stream));
@@ -1534,14 +1602,14 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
     const bool want_plan = plan || n_emitted;
     rc = ensure_verb_scratch(h, n, want_plan ? (size_t)n * (n_containers > 0 ? n_containers : 1) : 0);
     if (rc) return rc;
-    const uint32_t gen = demand_generation(h, pd);
+    const uint32_t gen = demand_generation(h, pd, lp.enabled != 0);
     if (idx) {
         CU(h, cudaMemcpyAsync(h->d_idx, idx, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
         h->stats.h2d_bytes += (size_t)n * 4;
     }
     const int block = 256;
     int grid = (int)((n + block - 1) / block);
-    const int max_grid = h->num_sms * 8;
+    const int max_grid = h->num_sms * (want_plan ? 2 : NGS_K1_BLOCKS);  // exactly the resident blocks: measured best
     if (grid > max_grid) grid = max_grid;
     if (want_plan)
         k_assume<true><<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, feasible ? h->d_feas : nullptr,
@@ -1584,10 +1652,10 @@ int ngs_assume_dev(ngs_dealer* h, uint32_t n, const int32_t* percent, int n_cont
     if (n > h->T.n) return fail(h, NGS_ERR_INVALID, "n=%u exceeds the %u rows of this shard", n, h->T.n);
     if (n == 0) return NGS_OK;
     CU(h, cudaSetDevice(h->device));
-    const uint32_t gen = demand_generation(h, pd);
+    const uint32_t gen = demand_generation(h, pd, lp.enabled != 0);
     const int block = 256;
     int grid = (int)((n + block - 1) / block);
-    const int max_grid = h->num_sms * 8;
+    const int max_grid = h->num_sms * NGS_K1_BLOCKS;  // exactly the resident blocks: measured best
     if (grid > max_grid) grid = max_grid;
     k_assume<false><<<grid, block, 0, h->stream>>>(h->T, nullptr, n, pd, lp, MODE_ASSUME, gen, d_feasible, nullptr, d_score, nullptr, nullptr);
     CU(h, cudaGetLastError());
@@ -1612,7 +1680,7 @@ int ngs_bind(ngs_dealer* h, uint32_t idx, const int32_t* percent, int n_containe
     rc = make_load(h, load, &lp);
     if (rc) return rc;
     CU(h, cudaSetDevice(h->device));
-    const uint32_t gen = demand_generation(h, pd);
+    const uint32_t gen = demand_generation(h, pd, lp.enabled != 0);
     k_bind<<<1, 32, 0, h->stream>>>(h->T, idx, pd, lp, gen, h->d_bind);
     CU(h, cudaGetLastError());
     CU(h, cudaMemcpyAsync(h->h_bind, h->d_bind, sizeof(BindResult), cudaMemcpyDeviceToHost, h->stream));
@@ -1857,6 +1925,8 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     bp.T.ts = snap->ts;
     bp.T.tag = snap->plan_tag;
     bp.T.cscore = snap->plan_score;
+    bp.T.blut = nullptr;  // no table to borrow without a handle: Binpack.Rate runs in fp64
+    bp.T.rl_zero = 0;     // caller-owned table: always read
     bp.T.n = snap->n_nodes;
     bp.T.first = snap->first_node;
     bp.dem = dem;

@@ -72,6 +72,7 @@ struct LoadParams {
     int32_t metric[NGS_MAX_PERIODS];
     uint32_t min_ts[NGS_MAX_PERIODS];
     uint32_t never[NGS_MAX_PERIODS];  // window lies beyond the representable range: nothing valid
+    int32_t canonical;                // entries are exactly (core, memory), both usable: unrolled fast path
 };
 
 // sort.Sort(sortableDemand) (rater.go:81,134) with the Go 1.16 small-slice rule, then the
@@ -368,12 +369,21 @@ __device__ inline void write_plan(int32_t* out, const SortedDemand* dem, bool so
 // Binpack.Rate (rater.go:59-70) with GPUs.Usage (allocate.go:164-171): the fp64 division and
 // multiplication are done in IEEE round-to-nearest with explicit intrinsics (no contraction),
 // then truncated toward zero like Go's int(float64).
-__device__ __forceinline__ int rate_binpack(const int (&f)[8], int G, int load_int) {
+__device__ __forceinline__ int binpack_percent_fp64(int used, int G) {
+    const double usage = __ddiv_rn((double)used, (double)(100 * G));  // allocate.go:170
+    return __double2int_rz(__dmul_rn(usage, 100.0));                  // rater.go:69
+}
+// The table is filled on the device by the very same fp64 sequence (k_build_rate_lut), one entry
+// per (G, used) with 0 <= used <= 100*G; anything outside (a cell above 100 after a stray
+// Release) takes the fp64 path.  lut == nullptr: always fp64.
+constexpr int RATE_LUT_STRIDE = 801;
+__device__ __forceinline__ int rate_binpack(const int (&f)[8], int G, int load_int, const int16_t* __restrict__ lut = nullptr) {
     int used = 0;
 #pragma unroll
     for (int i = 0; i < 8; i++) used += i < G ? 100 - f[i] : 0;
-    const double usage = __ddiv_rn((double)used, (double)(100 * G));
-    return __double2int_rz(__dmul_rn(usage, 100.0)) + load_int * 50 - G;
+    const int pct = (lut != nullptr && used >= 0 && used <= 100 * G) ? (int)__ldg(lut + G * RATE_LUT_STRIDE + used)
+                                                                      : binpack_percent_fp64(used, G);
+    return pct + load_int * 50 - G;
 }
 // Spread.Rate (rater.go:113-123) with PercentAvailableAndFreeGpuCount (allocate.go:205-213)
 __device__ __forceinline__ int rate_spread(const int (&f)[8], int G, int load_int) {
@@ -385,20 +395,61 @@ __device__ __forceinline__ int rate_spread(const int (&f)[8], int G, int load_in
     }
     return 100 * cnt + avail / 10 - G - load_int;
 }
-__device__ __forceinline__ int rate_policy(int policy, const int (&f)[8], int G, int load_int) {
-    if (policy == NGS_POLICY_BINPACK) return rate_binpack(f, G, load_int);
+__device__ __forceinline__ int rate_policy(int policy, const int (&f)[8], int G, int load_int, const int16_t* __restrict__ lut = nullptr) {
+    if (policy == NGS_POLICY_BINPACK) return rate_binpack(f, G, load_int, lut);
     if (policy == NGS_POLICY_SPREAD) return rate_spread(f, G, load_int);
     return 100;  // SampleRater.Rate -> ScoreMax (rater.go:24-26)
 }
+
+// ceil(10*usage)/10 for ceil(10*usage) = 0..10: the literal k/10 and the fp64 quotient k/10.0 are the
+// same double (both correctly rounded), so the table replaces a division per usage sample
+__device__ __constant__ double c_tenth[11] = {0.0, 0.1, 0.2, 0.3, 0.4, 0.5, 0.6, 0.7, 0.8, 0.9, 1.0};
 
 // GPUResource.LoadUsage for the 8 cells of one row.  tenths[m] holds ceil(10*usage) per card
 // (255 = the reference would skip this entry: node or card missing, unparsable or stale
 // timestamp, unparsable or out-of-range value), ts[m] the update time in unix seconds.
 // Per card the SyncPeriod entries are summed in order, the node sum runs in GPU-index order
 // (rater.go:63-65), both in fp64 exactly as the reference does.  rlc[] = RemainLoad + 2.
+// pair[a*11+b] = fl(a/10 + b/10) for a, b in 0..10 — a 121-entry table the caller keeps in shared
+// memory (fill_usage_pair_table); nullptr = add the two table values with __dadd_rn instead.
+__device__ __forceinline__ void fill_usage_pair_table(double* pair, int tid, int nthreads) {
+    for (int i = tid; i < 121; i += nthreads) pair[i] = __dadd_rn(c_tenth[i / 11], c_tenth[i % 11]);
+}
 __device__ __forceinline__ void load_usage_row(const uint8_t (&tenths)[2][8], const uint32_t (&ts)[2][8], const LoadParams& lp,
-                                               int G, int (&rlc)[8], int* load_int) {
+                                               int G, int (&rlc)[8], int* load_int, const double* pair = nullptr) {
     double lu = 0.0;
+    if (lp.canonical && pair != nullptr) {
+        // as below, with the per-card sum looked up: one shared-memory load instead of two divergent
+        // constant loads and an add.  A skipped entry contributes index 0 (= 0.0).
+        const uint32_t min0 = lp.min_ts[0], min1 = lp.min_ts[1];
+#pragma unroll
+        for (int g = 0; g < 8; g++) {
+            const uint32_t a = tenths[0][g], b = tenths[1][g];
+            const uint32_t ia = (a <= 10u && ts[0][g] >= min0) ? a : 0u;
+            const uint32_t ib = (b <= 10u && ts[1][g] >= min1) ? b : 0u;
+            const double u = pair[ia * 11u + ib];
+            rlc[g] = g < G ? 4 - __double2int_rz(u) : 2;
+            if (g < G) lu = __dadd_rn(lu, u);
+        }
+        *load_int = __double2int_rz(lu) / G;
+        return;
+    }
+    if (lp.canonical) {
+        // the deployed policy (deploy/dynamic-scheduler-node-annotator-cm.yaml:11-16): core then memory.
+        // A skipped entry adds nothing, which for these non-negative values is the same as adding 0.0.
+        const uint32_t min0 = lp.min_ts[0], min1 = lp.min_ts[1];
+#pragma unroll
+        for (int g = 0; g < 8; g++) {
+            const uint32_t a = tenths[0][g], b = tenths[1][g];
+            const double xa = (a != 255u && ts[0][g] >= min0) ? c_tenth[a <= 10u ? a : 10u] : 0.0;
+            const double xb = (b != 255u && ts[1][g] >= min1) ? c_tenth[b <= 10u ? b : 10u] : 0.0;
+            const double u = __dadd_rn(xa, xb);
+            rlc[g] = g < G ? 4 - __double2int_rz(u) : 2;  // RemainLoad + 2 = (2 - int(usage)) + 2, allocate.go:193
+            if (g < G) lu = __dadd_rn(lu, u);
+        }
+        *load_int = __double2int_rz(lu) / G;  // rater.go:68,121
+        return;
+    }
 #pragma unroll
     for (int g = 0; g < 8; g++) {
         double u = 0.0;
@@ -407,7 +458,7 @@ __device__ __forceinline__ void load_usage_row(const uint8_t (&tenths)[2][8], co
             const uint32_t t10 = m ? tenths[1][g] : tenths[0][g];
             const uint32_t t = m ? ts[1][g] : ts[0][g];
             if (t10 == 255u || lp.never[e] || t < lp.min_ts[e]) continue;
-            u = __dadd_rn(u, __ddiv_rn((double)t10, 10.0));  // ceil(10*u)/10, allocate.go:190-191
+            u = __dadd_rn(u, c_tenth[t10 <= 10u ? t10 : 10u]);  // ceil(10*u)/10, allocate.go:190-191
         }
         const int rl = 2 - __double2int_rz(u);  // allocate.go:193 (LoadTotal = 2)
         rlc[g] = g < G ? rl + 2 : 2;

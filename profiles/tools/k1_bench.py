@@ -32,7 +32,7 @@ score = torch.empty(n, dtype=torch.int32, device="cuda")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 out = []
 with torch.cuda.stream(stream):
-    for name, demand, policy, ld, bpe in (("load off, C=1, binpack", [30], 0, None, 37 + 8), ("load off, C=3, spread", [40, 30, 20], 1, None, 37 + 8),
+    for name, demand, policy, ld, bpe in (("load off, C=1, binpack", [30], 0, None, 37), ("load off, C=3, spread", [40, 30, 20], 1, None, 37),
                                           ("load on, C=3, binpack", [40, 30, 20], 0, load, 125)):
         for _ in range(3):
             d.assume_dev(demand, policy, feas.data_ptr(), score.data_ptr(), load=ld)
