@@ -31,6 +31,31 @@ def is_stale() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+HOST_DIR = os.path.join(HERE, "host")
+HOST_LIB = os.path.join(HERE, "libngs_dealer_host.so")
+HOST_TEST = os.path.join(HERE, "host", "test_dealer_host")
+
+
+def build_host(force: bool = False) -> str:
+    """C++ mirror of the reference's Dealer interface (host/dealer_host.cpp) and its test program"""
+    src = os.path.join(HOST_DIR, "dealer_host.cpp")
+    hdr = os.path.join(HOST_DIR, "dealer_host.h")
+    test_src = os.path.join(HERE, "..", "tests", "host", "test_dealer_host.cpp")
+    deps = [src, hdr, test_src, LIB]
+    if force or not os.path.exists(HOST_TEST) or any(os.path.getmtime(d) > os.path.getmtime(HOST_TEST) for d in deps):
+        cxx = shutil.which("g++") or "g++"
+        common = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-I", os.path.join(HERE, "..", "include")]
+        res = subprocess.run([cxx, *common, "-shared", "-o", HOST_LIB, src, "-L", HERE, "-lngs_dealer", "-Wl,-rpath,$ORIGIN"],
+                             capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError("g++ (host mirror) failed:\n" + res.stdout + res.stderr)
+        res = subprocess.run([cxx, *common, "-o", HOST_TEST, test_src, src, "-L", HERE, "-lngs_dealer", "-Wl,-rpath,$ORIGIN/.."],
+                             capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError("g++ (host test) failed:\n" + res.stdout + res.stderr)
+    return HOST_TEST
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not is_stale():
         return LIB
