@@ -397,6 +397,8 @@ struct BatchParams {
     uint32_t world, rank;
     unsigned long long* xslots[NGS_MAX_RANKS];  // [rank r] -> r's slot array [P][NGS_MAX_RANKS] (this batch's parity half)
     unsigned long long* gwin;                   // [P] this rank's copy of the global result, zero before launch
+    uint32_t keys_stride, done_stride, xw_stride;  // distance between consecutive pods, in elements of each array
+    int32_t* status_out;       // optional host-visible copy of the error word, written when the kernel ends
     int32_t* err;              // device error word (0 = ok)
     uint32_t rows_per_block;
 #ifdef NGS_PHASE_TIMING
@@ -872,8 +874,8 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
           if (cw == 0) {
             // ---- control, random policy: counts -> seeded pick -> bind ----
             bool dead = false;
-            unsigned long long* krow = bp.keys + (size_t)p * gridDim.x;
-            uint32_t* done = bp.done + p;
+            unsigned long long* krow = bp.keys + (size_t)p * bp.keys_stride;
+            uint32_t* done = bp.done + (size_t)p * bp.done_stride;
             const uint32_t* fb = S.feasbits + (p & 1) * fwords;
             uint64_t v = lane < NW ? s_red[p & 1][lane] : 0;
             if (lane == 0) s_dirty = -1;
@@ -997,7 +999,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                 // word; the arrival counter is bumped only after that atomic has returned (data
                 // dependence), so a full counter implies every CTA's key is in the word
                 bool dead = false;
-                ulonglong2* xw = bp.xw + p;
+                ulonglong2* xw = bp.xw + (size_t)p * bp.xw_stride;
                 if (lane == 0) {
                     const unsigned long long old = atomicMax(&xw->x, (unsigned long long)v);
                     const unsigned long long one = 1ull + (old >> 63);  // bit 63 is never set: always 1
@@ -1077,6 +1079,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
         __syncthreads();
         PHASE_AFTER_BARRIER(3);
     }
+    if (blockIdx.x == 0 && tid == 0 && bp.status_out) *bp.status_out = *reinterpret_cast<volatile int32_t*>(bp.err);
 #ifdef NGS_PHASE_TIMING
     if (tid == NW * 32 && bp.dbg)
         for (int i = 0; i < 8; i++) bp.dbg[blockIdx.x * 16 + i] = (unsigned long long)ph[i];
@@ -1117,9 +1120,11 @@ struct ngs_dealer {
     // batch
     uint32_t batch_cap = 0;  // pods per launch chunk
     SortedDemand* d_dem = nullptr;
-    unsigned long long* d_keys = nullptr;
-    int32_t* d_pod_in = nullptr;   // percent [cap][12] | ncont [cap] | policy [cap]
-    int32_t* d_pod_out = nullptr;  // node [cap] | score [cap] | gpu_idx [cap][12]
+    unsigned long long* d_keys = nullptr;  // per-pod exchange records: {xw 16 B, done 4 B, pad, keys[num_sms]}
+    size_t pod_rec_bytes = 0;
+    int32_t* d_pod_in_dev = nullptr;       // device aliases of the mapped staging buffers
+    int32_t* d_pod_out_dev = nullptr;
+    int max_smem_set = 0;                  // largest dynamic shared memory size set on k_schedule so far
     int32_t* h_pod_in = nullptr;   // pinned mirrors
     int32_t* h_pod_out = nullptr;
     int32_t* d_err = nullptr;
@@ -1242,20 +1247,24 @@ int ensure_batch(ngs_dealer* h) {
     const uint32_t cap = BATCH_CHUNK;
     const size_t in_words = (size_t)cap * (NGS_MAX_CONTAINERS + 2), out_words = (size_t)cap * (NGS_MAX_CONTAINERS + 2);
     CU(h, cudaMalloc(&h->d_dem, sizeof(SortedDemand) * cap));
-    // key slots [cap][num_sms] followed by the arrival counters [cap]
-    // + one 16-byte arg-max exchange word per pod [cap] + the random-policy counters [cap]
-    CU(h, cudaMalloc(&h->d_keys, sizeof(unsigned long long) * cap * h->num_sms + sizeof(ulonglong2) * cap + sizeof(uint32_t) * cap));
-    CU(h, cudaMalloc(&h->d_pod_in, in_words * 4));
-    CU(h, cudaMalloc(&h->d_pod_out, out_words * 4));
-    CU(h, cudaMallocHost(&h->h_pod_in, in_words * 4));
-    CU(h, cudaMallocHost(&h->h_pod_out, out_words * 4));
+    // one exchange record per pod, pod-major, so that a batch of P pods clears ONE contiguous range:
+    //   [0,16) arg-max word {key, counter}   [16,20) random-policy arrival counter   [32, 32+8*SMs) per-CTA slots
+    h->pod_rec_bytes = (32 + sizeof(unsigned long long) * (size_t)h->num_sms + 31) / 32 * 32;
+    CU(h, cudaMalloc(&h->d_keys, h->pod_rec_bytes * cap));
+    // host-API staging lives in mapped pinned memory: the kernels read the pods and write the
+    // decisions straight through PCIe, so a call needs no copy commands at all
+    CU(h, cudaHostAlloc(&h->h_pod_in, (in_words + 8) * 4, cudaHostAllocMapped));
+    CU(h, cudaHostAlloc(&h->h_pod_out, (out_words + 8) * 4, cudaHostAllocMapped));
+    CU(h, cudaHostGetDevicePointer(&h->d_pod_in_dev, h->h_pod_in, 0));
+    CU(h, cudaHostGetDevicePointer(&h->d_pod_out_dev, h->h_pod_out, 0));
     h->batch_cap = cap;
     return NGS_OK;
 }
 
 // launch K6 for one chunk of <= BATCH_CHUNK pods whose inputs are in device memory
 int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const int32_t* d_ncont, int max_c, const int32_t* d_policy,
-                    const LoadParams& lp, uint64_t seed_seq, int32_t* d_node, int32_t* d_score, int32_t* d_gidx) {
+                    const LoadParams& lp, uint64_t seed_seq, int32_t* d_node, int32_t* d_score, int32_t* d_gidx,
+                    int32_t* status_out = nullptr) {
     if (!h->coop) return fail(h, NGS_ERR_CUDA, "device lacks cooperative launch");
     const uint32_t N = h->T.n;
     uint32_t grid = (N + 63) / 64;
@@ -1267,14 +1276,16 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     const size_t smem = (size_t)rpb * 28 + (size_t)((rpb + 31) / 32) * 8 + 16;  // rows + two feasbits buffers
     if (smem > (size_t)h->smem_optin)
         return fail(h, NGS_ERR_UNSUPPORTED, "%u rows per SM need %zu B shared memory (> %d): shard the cluster over more GPUs", rpb, smem, h->smem_optin);
-    CU(h, cudaFuncSetAttribute(k_schedule, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if ((int)smem > h->max_smem_set) {  // the attribute is an upper bound: raise it only when needed
+        CU(h, cudaFuncSetAttribute(k_schedule, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        h->max_smem_set = (int)smem;
+    }
     k_prep_demands<<<(P + 127) / 128, 128, 0, h->stream>>>(d_percent, d_ncont, max_c, d_policy, P, h->d_dem, h->d_err);
     CU(h, cudaGetLastError());
-    ulonglong2* d_xw = reinterpret_cast<ulonglong2*>(h->d_keys + (size_t)h->batch_cap * h->num_sms);  // 16 B aligned
-    uint32_t* d_done = reinterpret_cast<uint32_t*>(d_xw + h->batch_cap);
-    CU(h, cudaMemsetAsync(h->d_keys, 0, sizeof(unsigned long long) * (size_t)P * grid, h->stream));
-    CU(h, cudaMemsetAsync(d_xw, 0, sizeof(ulonglong2) * (size_t)P, h->stream));
-    CU(h, cudaMemsetAsync(d_done, 0, sizeof(uint32_t) * (size_t)P, h->stream));
+    unsigned char* rec = reinterpret_cast<unsigned char*>(h->d_keys);
+    ulonglong2* d_xw = reinterpret_cast<ulonglong2*>(rec);
+    uint32_t* d_done = reinterpret_cast<uint32_t*>(rec + 16);
+    CU(h, cudaMemsetAsync(rec, 0, h->pod_rec_bytes * (size_t)P, h->stream));
     if (lp.enabled) h->T.rl_zero = 0;  // the batch's load-aware Rate writes RemainLoad
     BatchParams bp;
     bp.T = h->T;
@@ -1286,9 +1297,13 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     bp.score_out = d_score;
     bp.gpu_idx_out = d_gidx;
     bp.max_c = max_c;
-    bp.keys = h->d_keys;
+    bp.keys = reinterpret_cast<unsigned long long*>(rec + 32);
     bp.done = d_done;
     bp.xw = d_xw;
+    bp.keys_stride = (uint32_t)(h->pod_rec_bytes / 8);
+    bp.done_stride = (uint32_t)(h->pod_rec_bytes / 4);
+    bp.xw_stride = (uint32_t)(h->pod_rec_bytes / 16);
+    bp.status_out = status_out;
     bp.world = (uint32_t)h->world;
     bp.rank = (uint32_t)h->rank;
     bp.gwin = h->d_gwin;
@@ -1422,7 +1437,7 @@ int ngs_destroy(ngs_dealer* h) {
     cudaFree(h->T.tag); cudaFree(h->T.cscore); cudaFree(const_cast<int16_t*>(h->T.blut));
     cudaFree(h->d_idx); cudaFree(h->d_feas); cudaFree(h->d_reason); cudaFree(h->d_score); cudaFree(h->d_plan); cudaFree(h->d_nem);
     cudaFree(h->d_bind); cudaFreeHost(h->h_bind); cudaFree(h->d_small); cudaFreeHost(h->h_small);
-    cudaFree(h->d_dem); cudaFree(h->d_keys); cudaFree(h->d_pod_in); cudaFree(h->d_pod_out);
+    cudaFree(h->d_dem); cudaFree(h->d_keys);
     cudaFreeHost(h->h_pod_in); cudaFreeHost(h->h_pod_out);
     cudaFree(h->d_err); cudaFreeHost(h->h_err);
     for (int r = 0; r < NGS_MAX_RANKS; r++)
@@ -1740,28 +1755,30 @@ int ngs_schedule_batch(ngs_dealer* h, uint32_t n_pods, const int32_t* percent, c
     if (rc) return rc;
     for (uint32_t p0 = 0; p0 < n_pods; p0 += BATCH_CHUNK) {
         const uint32_t P = n_pods - p0 < BATCH_CHUNK ? n_pods - p0 : BATCH_CHUNK;
-        // pinned staging: percent [P][max_c] | ncont [P] | policy [P]
+        // mapped pinned staging: percent [P][max_c] | ncont [P] | policy [P]; outputs: status | node | score | gpu_idx
         int32_t* hin = h->h_pod_in;
         memcpy(hin, percent + (size_t)p0 * max_c, (size_t)P * max_c * 4);
         memcpy(hin + (size_t)P * max_c, n_containers + p0, (size_t)P * 4);
         memcpy(hin + (size_t)P * max_c + P, policy + p0, (size_t)P * 4);
         const size_t in_bytes = ((size_t)P * max_c + 2 * (size_t)P) * 4;
-        CU(h, cudaMemcpyAsync(h->d_pod_in, hin, in_bytes, cudaMemcpyHostToDevice, h->stream));
-        int32_t* d_node = h->d_pod_out;
+        const int32_t* din = h->d_pod_in_dev;
+        int32_t* d_status = h->d_pod_out_dev;  // word 0..7: status (padded so that the arrays stay 32-byte aligned)
+        int32_t* d_node = h->d_pod_out_dev + 8;
         int32_t* d_score = d_node + P;
         int32_t* d_gidx = d_score + P;
-        rc = launch_schedule(h, P, h->d_pod_in, h->d_pod_in + (size_t)P * max_c, max_c, h->d_pod_in + (size_t)P * max_c + P, lp,
-                             seed + seq0 + p0, d_node, d_score, d_gidx);
+        h->h_pod_out[0] = NGS_ERR_CUDA;  // overwritten by the kernel's last act
+        rc = launch_schedule(h, P, din, din + (size_t)P * max_c, max_c, din + (size_t)P * max_c + P, lp, seed + seq0 + p0, d_node,
+                             d_score, d_gidx, d_status);
         if (rc) return rc;
         const size_t out_bytes = (2 * (size_t)P + (size_t)P * max_c) * 4;
-        CU(h, cudaMemcpyAsync(h->h_pod_out, h->d_pod_out, out_bytes, cudaMemcpyDeviceToHost, h->stream));
-        CU(h, cudaMemcpyAsync(h->h_err, h->d_err, 4, cudaMemcpyDeviceToHost, h->stream));
         CU(h, cudaStreamSynchronize(h->stream));
+        *h->h_err = h->h_pod_out[0];
         rc = check_dev_err(h);
         if (rc) return rc;
-        memcpy(node_out + p0, h->h_pod_out, (size_t)P * 4);
-        memcpy(score_out + p0, h->h_pod_out + P, (size_t)P * 4);
-        memcpy(gpu_idx_out + (size_t)p0 * max_c, h->h_pod_out + 2 * (size_t)P, (size_t)P * max_c * 4);
+        const int32_t* hout = h->h_pod_out + 8;
+        memcpy(node_out + p0, hout, (size_t)P * 4);
+        memcpy(score_out + p0, hout + P, (size_t)P * 4);
+        memcpy(gpu_idx_out + (size_t)p0 * max_c, hout + 2 * (size_t)P, (size_t)P * max_c * 4);
         h->stats.h2d_bytes += in_bytes;
         h->stats.d2h_bytes += out_bytes;
     }
@@ -1940,6 +1957,10 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     bp.keys = keys;
     bp.done = done;
     bp.xw = mx;
+    bp.keys_stride = grid;
+    bp.done_stride = 1;
+    bp.xw_stride = 1;
+    bp.status_out = nullptr;
     bp.world = 1;
     bp.rank = 0;
     bp.gwin = nullptr;
