@@ -539,3 +539,26 @@ def test_full_size_million_nodes(ngs):
             assert cur[best, gidx[p, 0]] == cur[best][cur[best] >= dem].min()
             cur[best, gidx[p, 0]] -= dem
         assert np.array_equal(d.snapshot_read()[1], cur)
+
+
+def test_assume_dev_outputs_stay_on_device(ngs):
+    """ngs_assume_dev: same decisions as ngs_assume, outputs left in device memory (torch tensors)"""
+    import torch
+
+    n = 50_000
+    oc, d, _, _ = make_pair(ngs, n, 0.5, 0xDE7)
+    with d:
+        fill_load_tables(oc, d, n, 0xDE7)
+        gl, ol = load_ctx_pair(ngs)
+        feas = torch.zeros(n, dtype=torch.uint8, device="cuda")
+        score = torch.zeros(n, dtype=torch.int32, device="cuda")
+        for pol, load_g, load_o, demand in ((0, None, None, [30]), (1, None, None, [40, 30, 20]), (0, gl, ol, [40, 30, 20])):
+            d.assume_dev(demand, pol, feas.data_ptr(), score.data_ptr(), load=load_g)
+            d.sync()
+            want = oc.assume(demand, pol, load=load_o)
+            assert np.array_equal(feas.cpu().numpy(), want["feasible"])
+            got = score.cpu().numpy()
+            assert np.array_equal(got[want["feasible"] == 1], want["score"][want["feasible"] == 1])
+        # load scheduling off: the scan leaves the plan cache alone, so Score evaluates afresh and agrees
+        d.assume_dev([30], 0, feas.data_ptr(), score.data_ptr())
+        assert np.array_equal(d.score([30], 0), oc.assume([30], 0)["score"])
