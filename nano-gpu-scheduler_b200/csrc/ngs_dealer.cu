@@ -432,6 +432,7 @@ struct SmemRows {
     uint32_t* meta;
     int32_t* scB;  // Binpack.Rate of the row's current state
     int32_t* scS;  // Spread.Rate
+    uint32_t* top4;  // the row's four largest free values, one byte each (classify_top4)
     uint32_t* feasbits;
 };
 
@@ -478,6 +479,15 @@ __device__ __forceinline__ void publish_group(const BatchParams& bp, const SmemR
     // both rates of the new state (Rate is a function of the row only, allocate.go:96)
     const int sumf = __reduce_add_sync(0xFFu, fr);
     const int cnt100 = __popc(__ballot_sync(0xFFu, valid && fr == 100));
+    {
+        // the four largest cells: each lane ranks its own (descending, ties by index)
+        const uint32_t c = ((uint32_t)fr << 3) | (uint32_t)(7 - g);
+        int rank = 0;
+#pragma unroll
+        for (int sft = 1; sft < 8; sft++) rank += __shfl_xor_sync(0xFFu, c, sft) > c ? 1 : 0;
+        const uint32_t t4 = __reduce_or_sync(0xFFu, rank < 4 ? (uint32_t)min(fr, 255) << (8 * rank) : 0u);
+        if (g == 0) S.top4[r] = t4;
+    }
     if (g == 0) {
         const int used = 100 * G - sumf;                                                   // allocate.go:164-171
         const int pct = (bp.T.blut != nullptr && used >= 0 && used <= 100 * G) ? (int)__ldg(bp.T.blut + G * RATE_LUT_STRIDE + used)
@@ -517,6 +527,7 @@ __device__ __forceinline__ void publish_sample(const BatchParams& bp, const Smem
     S.fB[r] = b;
     S.scB[r] = rate_binpack(f, G, load_int, bp.T.blut);
     S.scS[r] = rate_spread(f, G, load_int);
+    S.top4[r] = top4_of(f);
     int4* gp = reinterpret_cast<int4*>(bp.T.free + (size_t)row * 8);
     gp[0] = make_int4(f[0], f[1], f[2], f[3]);
     gp[1] = make_int4(f[4], f[5], f[6], f[7]);
@@ -667,11 +678,15 @@ __device__ __forceinline__ void filter_pass(const SmemRows& S, const SortedDeman
         const uint32_t r = it * WT + wt;
         int cls = FEAS_NO;
         if (mine && r < my_rows) {
-            const uint32_t meta = S.meta[r];
-            if (((meta >> 24) & 15) != 0) {
-                int f[8];
-                unpack_free(S.fA[r], S.fB[r], f);
-                cls = classify_row(f, dem, true);
+            cls = classify_top4(S.top4[r], dem, true);  // unknown nodes hold all zeros: FEAS_NO (or YES for an empty demand,
+            if (cls == FEAS_FALLBACK || dem->nz == 0) {  //  which the full-row path below sorts out)
+                cls = FEAS_NO;
+                const uint32_t meta = S.meta[r];
+                if (((meta >> 24) & 15) != 0) {
+                    int f[8];
+                    unpack_free(S.fA[r], S.fB[r], f);
+                    cls = classify_row(f, dem, true);
+                }
             }
         }
         // rows the shortcuts leave open are searched exactly right away, 8 lanes per row, 4 rows a time;
@@ -736,7 +751,8 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     S.meta = reinterpret_cast<uint32_t*>(S.fB + rpb);
     S.scB = reinterpret_cast<int32_t*>(S.meta + rpb);
     S.scS = S.scB + rpb;
-    S.feasbits = reinterpret_cast<uint32_t*>(S.scS + rpb);  // two buffers of fwords words (pod parity)
+    S.top4 = reinterpret_cast<uint32_t*>(S.scS + rpb);
+    S.feasbits = S.top4 + rpb;  // two buffers of fwords words (pod parity)
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
     // the two control warps are the LAST two: the SM's issue arbiter favours high warp ids, and the
@@ -797,6 +813,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
         S.meta[r] = meta;
         S.scB[r] = G ? rate_binpack(f, G, load_int, T.blut) : 0;
         S.scS[r] = G ? rate_spread(f, G, load_int) : 0;
+        S.top4[r] = top4_of(f);  // cells beyond G hold 0
     }
     for (uint32_t i = tid; i < 2 * sizeof(SortedDemand) / 4; i += blockDim.x)
         if (i / (sizeof(SortedDemand) / 4) < bp.P) reinterpret_cast<uint32_t*>(&s_dem[0])[i] = reinterpret_cast<const uint32_t*>(&bp.dem[0])[i];
@@ -1273,7 +1290,7 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     const uint32_t rpb = (N + grid - 1) / grid;
     uint32_t block = ((rpb + 31) / 32) * 32 + 64;  // one worker thread per row (up to 960) + two control warps
     if (block > 1024) block = 1024;
-    const size_t smem = (size_t)rpb * 28 + (size_t)((rpb + 31) / 32) * 8 + 16;  // rows + two feasbits buffers
+    const size_t smem = (size_t)rpb * 32 + (size_t)((rpb + 31) / 32) * 8 + 16;  // rows + two feasbits buffers
     if (smem > (size_t)h->smem_optin)
         return fail(h, NGS_ERR_UNSUPPORTED, "%u rows per SM need %zu B shared memory (> %d): shard the cluster over more GPUs", rpb, smem, h->smem_optin);
     if ((int)smem > h->max_smem_set) {  // the attribute is an upper bound: raise it only when needed
@@ -1913,7 +1930,7 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     const uint32_t rpb = (N + grid - 1) / grid;
     uint32_t block = ((rpb + 31) / 32) * 32 + 64;
     if (block > 1024) block = 1024;
-    const size_t smem = (size_t)rpb * 28 + (size_t)((rpb + 31) / 32) * 8 + 16;
+    const size_t smem = (size_t)rpb * 32 + (size_t)((rpb + 31) / 32) * 8 + 16;
     if (smem > (size_t)dv->smem_optin) return NGS_ERR_UNSUPPORTED;
 
     unsigned char* sc = dv->scratch;

@@ -182,6 +182,42 @@ __device__ __forceinline__ int classify_row(const int (&f)[8], const SortedDeman
     return FEAS_UNDECIDED;
 }
 
+// The same three statements read off the row's four LARGEST free values, kept beside the row as
+// one word (byte k = k-th largest, saturated at 255; refreshed whenever the row changes):
+// "at least nz cells hold d1" is "the nz-th largest holds d1", "no cell holds d1" is "the largest
+// does not".  Needs nz <= 4 and d1 <= 255, and a non-saturated maximum for the nz == 2 case;
+// FEAS_FALLBACK asks the caller to classify from the full row instead.
+constexpr int FEAS_FALLBACK = 3;
+__device__ __forceinline__ uint32_t top4_of(const int (&f)[8]) {
+    int a[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) a[i] = f[i];
+#define NGS_CEX_DESC(i, j) { const int hi_ = max(a[i], a[j]), lo_ = min(a[i], a[j]); a[i] = hi_; a[j] = lo_; }
+    NGS_CEX_DESC(0, 2) NGS_CEX_DESC(1, 3) NGS_CEX_DESC(4, 6) NGS_CEX_DESC(5, 7)
+    NGS_CEX_DESC(0, 4) NGS_CEX_DESC(1, 5) NGS_CEX_DESC(2, 6) NGS_CEX_DESC(3, 7)
+    NGS_CEX_DESC(0, 1) NGS_CEX_DESC(2, 3) NGS_CEX_DESC(4, 5) NGS_CEX_DESC(6, 7)
+    NGS_CEX_DESC(2, 4) NGS_CEX_DESC(3, 5)
+    NGS_CEX_DESC(1, 4) NGS_CEX_DESC(3, 6)
+    NGS_CEX_DESC(1, 2) NGS_CEX_DESC(3, 4) NGS_CEX_DESC(5, 6)
+#undef NGS_CEX_DESC
+    return (uint32_t)min(a[0], 255) | ((uint32_t)min(a[1], 255) << 8) | ((uint32_t)min(a[2], 255) << 16) | ((uint32_t)min(a[3], 255) << 24);
+}
+__device__ __forceinline__ int classify_top4(uint32_t top4, const SortedDemand* dem, bool sorted_policy) {
+    const int nz = dem->nz;
+    if (nz == 0) return FEAS_YES;
+    const int d1 = dem->d[0];
+    if (nz > 4 || d1 > 255) return FEAS_FALLBACK;
+    const int t0 = (int)(top4 & 0xFFu);
+    if (t0 < d1) return FEAS_NO;  // (a saturated 255 is >= d1, which is what the true value is, too)
+    if ((int)((top4 >> (8 * (nz - 1))) & 0xFFu) >= d1) return FEAS_YES;
+    if (sorted_policy && nz == 2) {  // exactly one cell holds d1: it is the row maximum
+        if (t0 == 255) return FEAS_FALLBACK;
+        const int d2 = dem->d[1];
+        return ((int)((top4 >> 8) & 0xFFu) >= d2 || t0 - d1 >= d2) ? FEAS_YES : FEAS_NO;
+    }
+    return FEAS_UNDECIDED;
+}
+
 // Binpack.Choose / Spread.Choose on the packed row.  Returns feasibility (rater.go:98-100).
 // PLAN: `emit` receives the `indexes` slice in emission order, 4 bits per entry (0xF = -1),
 // and n_emit its length; the greedy loop then runs to the end even after a miss, exactly as
