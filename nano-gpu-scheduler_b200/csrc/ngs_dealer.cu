@@ -45,6 +45,7 @@ struct Tables {
     int32_t* cscore;
     const int16_t* blut;  // Binpack.Rate percent table [9][801] (nullptr: compute in fp64)
     uint32_t rl_zero;     // the rl table is known to hold only zeros (no load-aware pass ran yet): skip reading it
+    uint32_t nstride;  // rows per metric plane of tenths / ts (>= n; padded so that every plane is 256-row aligned)
     uint32_t n;      // rows in this shard
     uint32_t first;  // global node index of row 0
 };
@@ -87,34 +88,31 @@ __global__ void k_build_rate_lut(int16_t* lut) {
 // One full GPUs.Choose (allocate.go:92-100) on a row read from the global tables.
 // do_rate=false is the plan-cache hit of NodeInfo.Bind (node.go:72-78): the plan is re-derived
 // from the RemainLoad the filter pass left behind, without running Rate / LoadUsage again.
+// everything one evaluation reads of its row, as it arrives from memory
+struct RowIn {
+    int G;
+    uint32_t v[8];      // free
+    uint2 t8[2];        // tenths per metric (load-aware pass only)
+    uint32_t ts[2][8];  // update times per metric (load-aware pass only)
+    uint2 r8;           // RemainLoad (other passes; zeros when the table is known to hold only zeros)
+};
+
 template <bool PLAN>
-__device__ __forceinline__ RowEval eval_row_global(const Tables& T, uint32_t row, const SortedDemand* dem, const LoadParams& lp,
-                                                   bool do_rate, const double* pair = nullptr) {
+__device__ __forceinline__ RowEval eval_row_values(const Tables& T, uint32_t row, const RowIn& in, const SortedDemand* dem,
+                                                   const LoadParams& lp, bool do_rate, const double* pair) {
     RowEval ev;
     ev.known = false;
     ev.feasible = false;
     ev.score = NGS_SCORE_MIN;
     ev.emit = 0;
     ev.n_emit = 0;
-    // every load of the row is issued before the first use, so that they are all in flight together
     const int policy = dem->policy;
     const bool load_path = lp.enabled && do_rate && policy != NGS_POLICY_RANDOM;
-    const int G = T.gcount[row];
-    uint32_t v[8];
-    ld_row8(T.free + (size_t)row * 8, v);
-    uint32_t ts[2][8];
-    uint2 t8[2];
-    uint2 r8 = make_uint2(0u, 0u);
-    if (load_path) {
-#pragma unroll
-        for (int m = 0; m < 2; m++) {
-            const size_t off = ((size_t)m * T.n + row) * 8;
-            t8[m] = __ldcg(reinterpret_cast<const uint2*>(T.tenths + off));
-            ld_row8(T.ts + off, ts[m]);
-        }
-    } else if (!T.rl_zero) {
-        r8 = __ldcg(reinterpret_cast<const uint2*>(T.rl + (size_t)row * 8));
-    }
+    const int G = in.G;
+    const uint32_t (&v)[8] = in.v;
+    const uint2 (&t8)[2] = in.t8;
+    const uint32_t (&ts)[2][8] = in.ts;
+    const uint2 r8 = in.r8;
     if (G == 0) return ev;
     ev.known = true;
     int f[8];
@@ -181,6 +179,31 @@ __device__ __forceinline__ RowEval eval_row_global(const Tables& T, uint32_t row
     return ev;
 }
 
+// One full GPUs.Choose (allocate.go:92-100) on a row read from the global tables.
+// do_rate=false is the plan-cache hit of NodeInfo.Bind (node.go:72-78): the plan is re-derived
+// from the RemainLoad the filter pass left behind, without running Rate / LoadUsage again.
+template <bool PLAN>
+__device__ __forceinline__ RowEval eval_row_global(const Tables& T, uint32_t row, const SortedDemand* dem, const LoadParams& lp,
+                                                   bool do_rate, const double* pair = nullptr) {
+    // every load of the row is issued before the first use, so that they are all in flight together
+    const bool load_path = lp.enabled && do_rate && dem->policy != NGS_POLICY_RANDOM;
+    RowIn in;
+    in.G = T.gcount[row];
+    ld_row8(T.free + (size_t)row * 8, in.v);
+    in.r8 = make_uint2(0u, 0u);
+    if (load_path) {
+#pragma unroll
+        for (int m = 0; m < 2; m++) {
+            const size_t off = ((size_t)m * T.nstride + row) * 8;
+            in.t8[m] = __ldcg(reinterpret_cast<const uint2*>(T.tenths + off));
+            ld_row8(T.ts + off, in.ts[m]);
+        }
+    } else if (!T.rl_zero) {
+        in.r8 = __ldcg(reinterpret_cast<const uint2*>(T.rl + (size_t)row * 8));
+    }
+    return eval_row_values<PLAN>(T, row, in, dem, lp, do_rate, pair);
+}
+
 enum { MODE_ASSUME = 0, MODE_SCORE = 1 };
 
 // K1.  DealerImpl.Assume / DealerImpl.Score fan-out (dealer.go:109-134, 138-153): one thread
@@ -241,6 +264,156 @@ __global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables
                 else for (int j = 0; j < C; j++) out[j] = INT32_MIN;
             }
             if (n_emitted) n_emitted[k] = ev.known ? ev.n_emit : 0;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1, streaming form: the same evaluation as k_assume for "all rows, no per-node plans", with the
+// row data staged through shared memory by the TMA engine (1-D bulk copies, cp.async.bulk +
+// mbarrier transaction counts) in a 2- or 3-stage ring of 256-row tiles, so that several tiles of every
+// table are in flight per CTA while the threads evaluate the tile that has landed.
+// ---------------------------------------------------------------------------------------------
+constexpr int SCAN_TILE = 256;
+#ifndef NGS_SCAN_STAGES_LOAD
+#define NGS_SCAN_STAGES_LOAD 2
+#endif
+#ifndef NGS_SCAN_STAGES_PLAIN
+#define NGS_SCAN_STAGES_PLAIN 3
+#endif
+#ifndef NGS_SCAN_BLOCKS_LOAD
+#define NGS_SCAN_BLOCKS_LOAD 3
+#endif
+constexpr uint32_t SCAN_FREE_BYTES = SCAN_TILE * 8 * 4;    // 8 KB
+constexpr uint32_t SCAN_GC_BYTES = SCAN_TILE;              // 256 B
+constexpr uint32_t SCAN_RL_BYTES = SCAN_TILE * 8;          // 2 KB   (pass without load scheduling)
+constexpr uint32_t SCAN_TENTHS_BYTES = SCAN_TILE * 8;      // 2 KB per metric (load-aware pass)
+constexpr uint32_t SCAN_TS_BYTES = SCAN_TILE * 8 * 4;      // 8 KB per metric (load-aware pass)
+template <bool LOAD>
+__host__ __device__ constexpr uint32_t scan_stage_bytes() {
+    return SCAN_FREE_BYTES + SCAN_GC_BYTES + (LOAD ? 2 * SCAN_TENTHS_BYTES + 2 * SCAN_TS_BYTES : SCAN_RL_BYTES);
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAIT_DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// TMA 1-D bulk copy global -> shared, completion counted in bytes on the mbarrier
+__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+template <bool LOAD>
+__global__ void __launch_bounds__(SCAN_TILE, LOAD ? NGS_SCAN_BLOCKS_LOAD : 4) k_scan_tma(Tables T, uint32_t n, PodDemand pd, LoadParams lp, uint32_t gen,
+                                                                        uint8_t* __restrict__ feasible, int8_t* __restrict__ reason,
+                                                                        int32_t* __restrict__ score) {
+    extern __shared__ __align__(128) unsigned char tiles[];
+    __shared__ SortedDemand dem;
+    __shared__ double s_pair[121];
+    constexpr int SCAN_STAGES = LOAD ? NGS_SCAN_STAGES_LOAD : NGS_SCAN_STAGES_PLAIN;
+    __shared__ __align__(8) uint64_t bars[SCAN_STAGES];
+    constexpr uint32_t STAGE = scan_stage_bytes<LOAD>();
+    const uint32_t tid = threadIdx.x;
+    const uint32_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    const bool want_rl = !LOAD && !T.rl_zero;
+
+    // one thread issues the copies of a tile: every table's 256-row slice is one contiguous range
+    auto issue = [&](uint32_t tile, uint32_t stage) {
+        unsigned char* base = tiles + (size_t)stage * STAGE;
+        const size_t row = (size_t)tile * SCAN_TILE;
+        uint32_t bytes = SCAN_FREE_BYTES + SCAN_GC_BYTES;
+        if (LOAD) bytes += 2 * SCAN_TENTHS_BYTES + 2 * SCAN_TS_BYTES;
+        else if (want_rl) bytes += SCAN_RL_BYTES;
+        mbar_expect_tx(&bars[stage], bytes);
+        tma_load_1d(base, T.free + row * 8, SCAN_FREE_BYTES, &bars[stage]);
+        tma_load_1d(base + SCAN_FREE_BYTES, T.gcount + row, SCAN_GC_BYTES, &bars[stage]);
+        unsigned char* q = base + SCAN_FREE_BYTES + SCAN_GC_BYTES;
+        if (LOAD) {
+#pragma unroll
+            for (int m = 0; m < 2; m++) {
+                const size_t off = ((size_t)m * T.nstride + row) * 8;
+                tma_load_1d(q + m * SCAN_TENTHS_BYTES, T.tenths + off, SCAN_TENTHS_BYTES, &bars[stage]);
+                tma_load_1d(q + 2 * SCAN_TENTHS_BYTES + m * SCAN_TS_BYTES, T.ts + off, SCAN_TS_BYTES, &bars[stage]);
+            }
+        } else if (want_rl) {
+            tma_load_1d(q, T.rl + row * 8, SCAN_RL_BYTES, &bars[stage]);
+        }
+    };
+
+    if (tid == 0) {
+        for (int st = 0; st < SCAN_STAGES; st++) mbar_init(&bars[st], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        sort_demand(pd.percent, pd.n, pd.policy, &dem);
+    }
+    if (LOAD) fill_usage_pair_table(s_pair, tid, blockDim.x);
+    __syncthreads();
+    if (tid == 0)
+        for (uint32_t i = 0; i < SCAN_STAGES; i++) {
+            const uint32_t tile = blockIdx.x + i * gridDim.x;
+            if (tile < ntiles) issue(tile, i);
+        }
+
+    uint32_t it = 0;
+    for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+        const uint32_t stage = it % SCAN_STAGES, parity = (it / SCAN_STAGES) & 1u;
+        mbar_wait(&bars[stage], parity);
+        const unsigned char* base = tiles + (size_t)stage * STAGE;
+        const uint32_t row = tile * SCAN_TILE + tid;
+        RowIn in;
+        {
+            const uint4 a = *reinterpret_cast<const uint4*>(base + (size_t)tid * 32);
+            const uint4 b = *reinterpret_cast<const uint4*>(base + (size_t)tid * 32 + 16);
+            in.v[0] = a.x; in.v[1] = a.y; in.v[2] = a.z; in.v[3] = a.w;
+            in.v[4] = b.x; in.v[5] = b.y; in.v[6] = b.z; in.v[7] = b.w;
+        }
+        in.G = base[SCAN_FREE_BYTES + tid];
+        in.r8 = make_uint2(0u, 0u);
+        const unsigned char* q = base + SCAN_FREE_BYTES + SCAN_GC_BYTES;
+        if (LOAD) {
+#pragma unroll
+            for (int m = 0; m < 2; m++) {
+                in.t8[m] = *reinterpret_cast<const uint2*>(q + m * SCAN_TENTHS_BYTES + (size_t)tid * 8);
+                const unsigned char* tsp = q + 2 * SCAN_TENTHS_BYTES + m * SCAN_TS_BYTES + (size_t)tid * 32;
+                const uint4 a = *reinterpret_cast<const uint4*>(tsp), b = *reinterpret_cast<const uint4*>(tsp + 16);
+                in.ts[m][0] = a.x; in.ts[m][1] = a.y; in.ts[m][2] = a.z; in.ts[m][3] = a.w;
+                in.ts[m][4] = b.x; in.ts[m][5] = b.y; in.ts[m][6] = b.z; in.ts[m][7] = b.w;
+            }
+        } else if (want_rl) {
+            in.r8 = *reinterpret_cast<const uint2*>(q + (size_t)tid * 8);
+        }
+        __syncthreads();  // the stage has been read by everyone: refill it with the tile 3 steps ahead
+        if (tid == 0) {
+            const uint32_t next = tile + SCAN_STAGES * gridDim.x;
+            if (next < ntiles) issue(next, stage);
+        }
+        if (row < n) {
+            const RowEval ev = eval_row_values<false>(T, row, in, &dem, lp, true, s_pair);
+            const bool ok = ev.known && ev.feasible;
+            if (ev.known && LOAD) {  // plan cache, as in k_assume (MODE_ASSUME)
+                T.tag[row] = ok ? gen : 0u;
+                if (ok) T.cscore[row] = ev.score;
+            }
+            if (feasible) feasible[row] = ok ? 1 : 0;
+            if (reason) reason[row] = !ev.known ? NGS_REASON_UNKNOWN_NODE : (ok ? NGS_REASON_OK : NGS_REASON_INFEASIBLE);
+            if (score) score[row] = ok ? ev.score : NGS_SCORE_MIN;
         }
     }
 }
@@ -341,12 +514,12 @@ __global__ void k_upsert(Tables T, uint32_t row, int G) {
 // K4.  Update{Core,Memory}Usage (nodeusage.go:70-80) on one cell / Add*Usage (nodeusage.go:58-68)
 __global__ void k_load_update(Tables T, uint32_t row, int metric, int card, uint8_t tenths, uint32_t ts) {
     if (threadIdx.x != 0) return;
-    const size_t off = ((size_t)metric * T.n + row) * 8 + card;
+    const size_t off = ((size_t)metric * T.nstride + row) * 8 + card;
     T.tenths[off] = tenths;
     T.ts[off] = ts;
 }
 __global__ void k_load_add_node(Tables T, uint32_t row, int metric) {
-    const size_t off = ((size_t)metric * T.n + row) * 8 + threadIdx.x;
+    const size_t off = ((size_t)metric * T.nstride + row) * 8 + threadIdx.x;
     if (threadIdx.x < 8) {
         T.tenths[off] = 255;
         T.ts[off] = 0;
@@ -781,7 +954,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
             uint32_t ts[2][8];
 #pragma unroll
             for (int m = 0; m < 2; m++) {
-                const size_t off = ((size_t)m * T.n + row) * 8;
+                const size_t off = ((size_t)m * T.nstride + row) * 8;
                 const uint2 t8 = __ldcg(reinterpret_cast<const uint2*>(T.tenths + off));
                 const uint4 t0 = __ldcg(reinterpret_cast<const uint4*>(T.ts + off));
                 const uint4 t1 = __ldcg(reinterpret_cast<const uint4*>(T.ts + off + 4));
@@ -1410,16 +1583,25 @@ int ngs_create(ngs_dealer** out, int device, uint32_t max_nodes, uint32_t first_
         h->own_stream = true;
     }
     const size_t N = max_nodes;
+    const size_t NP = (N + 255) / 256 * 256;  // tables are padded to whole 256-row tiles (the scan stages tiles with bulk copies)
     h->T.n = max_nodes;
+    h->T.nstride = (uint32_t)NP;
     h->T.first = first_node;
     h->T.rl_zero = 1;
-    CU(h, cudaMalloc(&h->T.free, N * 8 * 4));
-    CU(h, cudaMalloc(&h->T.gcount, N));
-    CU(h, cudaMalloc(&h->T.rl, N * 8));
-    CU(h, cudaMalloc(&h->T.tenths, 2 * N * 8));
-    CU(h, cudaMalloc(&h->T.ts, 2 * N * 8 * 4));
-    CU(h, cudaMalloc(&h->T.tag, N * 4));
-    CU(h, cudaMalloc(&h->T.cscore, N * 4));
+    CU(h, cudaMalloc(&h->T.free, NP * 8 * 4));
+    CU(h, cudaMalloc(&h->T.gcount, NP));
+    CU(h, cudaMalloc(&h->T.rl, NP * 8));
+    CU(h, cudaMalloc(&h->T.tenths, 2 * NP * 8));
+    CU(h, cudaMalloc(&h->T.ts, 2 * NP * 8 * 4));
+    CU(h, cudaMalloc(&h->T.tag, NP * 4));
+    CU(h, cudaMalloc(&h->T.cscore, NP * 4));
+    CU(h, cudaMemsetAsync(h->T.free, 0, NP * 8 * 4, h->stream));
+    CU(h, cudaMemsetAsync(h->T.gcount, 0, NP, h->stream));
+    CU(h, cudaMemsetAsync(h->T.rl, 0, NP * 8, h->stream));
+    CU(h, cudaMemsetAsync(h->T.tenths, 0xFF, 2 * NP * 8, h->stream));
+    CU(h, cudaMemsetAsync(h->T.ts, 0, 2 * NP * 8 * 4, h->stream));
+    CU(h, cudaMemsetAsync(h->T.tag, 0, NP * 4, h->stream));
+    CU(h, cudaMemsetAsync(h->T.cscore, 0, NP * 4, h->stream));
     {
         int16_t* lut = nullptr;
         CU(h, cudaMalloc(&lut, sizeof(int16_t) * 9 * RATE_LUT_STRIDE));
@@ -1610,12 +1792,33 @@ int ngs_load_update_bulk(ngs_dealer* h, int metric, uint32_t first, uint32_t n, 
         t10[i] = encode_tenths(value[i], value_ok ? value_ok[i] : 1, ts_sec[i], ts_ok ? ts_ok[i] : 1);
         ts[i] = t10[i] == 255 ? 0u : (uint32_t)ts_sec[i];
     }
-    const size_t off = ((size_t)metric * h->T.n + (first - h->T.first)) * 8;
+    const size_t off = ((size_t)metric * h->T.nstride + (first - h->T.first)) * 8;
     CU(h, cudaSetDevice(h->device));
     CU(h, cudaMemcpyAsync(h->T.tenths + off, t10.data(), cells, cudaMemcpyHostToDevice, h->stream));
     CU(h, cudaMemcpyAsync(h->T.ts + off, ts.data(), cells * 4, cudaMemcpyHostToDevice, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
     h->stats.h2d_bytes += cells * 5;
+    return NGS_OK;
+}
+
+// launch the streaming scan over rows [0, n): TMA-staged tiles, feasibility / reason / score only
+static int launch_scan(ngs_dealer* h, uint32_t n, const PodDemand& pd, const LoadParams& lp, uint32_t gen, uint8_t* d_feas, int8_t* d_reason,
+                       int32_t* d_score) {
+    const uint32_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    if (lp.enabled) {
+        // load-aware pass: instruction-heavier per row; measured best with direct 256-bit loads at full
+        // occupancy (k_assume, 73 % of HBM peak) rather than TMA staging at 2-3 CTAs per SM (66-69 %)
+        int grid = (int)((n + 255) / 256);
+        const int max_grid = h->num_sms * NGS_K1_BLOCKS;
+        if (grid > max_grid) grid = max_grid;
+        k_assume<false><<<grid, 256, 0, h->stream>>>(h->T, nullptr, n, pd, lp, MODE_ASSUME, gen, d_feas, d_reason, d_score, nullptr, nullptr);
+    } else {
+        const size_t smem = (size_t)NGS_SCAN_STAGES_PLAIN * scan_stage_bytes<false>();
+        uint32_t grid = (uint32_t)h->num_sms * 4;
+        if (grid > ntiles) grid = ntiles;
+        k_scan_tma<false><<<grid, SCAN_TILE, smem, h->stream>>>(h->T, n, pd, lp, gen, d_feas, d_reason, d_score);
+    }
+    CU(h, cudaGetLastError());
     return NGS_OK;
 }
 
@@ -1643,7 +1846,10 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
     int grid = (int)((n + block - 1) / block);
     const int max_grid = h->num_sms * (want_plan ? 2 : NGS_K1_BLOCKS);  // exactly the resident blocks: measured best
     if (grid > max_grid) grid = max_grid;
-    if (want_plan)
+    if (!idx && mode == MODE_ASSUME && !want_plan) {
+        rc = launch_scan(h, n, pd, lp, gen, feasible ? h->d_feas : nullptr, reason ? h->d_reason : nullptr, score ? h->d_score : nullptr);
+        if (rc) return rc;
+    } else if (want_plan)
         k_assume<true><<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, feasible ? h->d_feas : nullptr,
                                                      reason ? h->d_reason : nullptr, score ? h->d_score : nullptr,
                                                      plan ? h->d_plan : nullptr, n_emitted ? h->d_nem : nullptr);
@@ -1685,12 +1891,8 @@ int ngs_assume_dev(ngs_dealer* h, uint32_t n, const int32_t* percent, int n_cont
     if (n == 0) return NGS_OK;
     CU(h, cudaSetDevice(h->device));
     const uint32_t gen = demand_generation(h, pd, lp.enabled != 0);
-    const int block = 256;
-    int grid = (int)((n + block - 1) / block);
-    const int max_grid = h->num_sms * NGS_K1_BLOCKS;  // exactly the resident blocks: measured best
-    if (grid > max_grid) grid = max_grid;
-    k_assume<false><<<grid, block, 0, h->stream>>>(h->T, nullptr, n, pd, lp, MODE_ASSUME, gen, d_feasible, nullptr, d_score, nullptr, nullptr);
-    CU(h, cudaGetLastError());
+    rc = launch_scan(h, n, pd, lp, gen, d_feasible, nullptr, d_score);
+    if (rc) return rc;
     h->stats.kernel_launches++;
     h->stats.node_evals += n;
     return NGS_OK;
@@ -1962,6 +2164,7 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     bp.T.blut = nullptr;  // no table to borrow without a handle: Binpack.Rate runs in fp64
     bp.T.rl_zero = 0;     // caller-owned table: always read
     bp.T.n = snap->n_nodes;
+    bp.T.nstride = snap->n_nodes;  // caller-owned tables: planes are exactly n_nodes rows apart
     bp.T.first = snap->first_node;
     bp.dem = dem;
     bp.P = n_pods;
