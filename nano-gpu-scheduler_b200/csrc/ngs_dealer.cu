@@ -814,29 +814,20 @@ __device__ __forceinline__ unsigned long long read_slot(const unsigned long long
     return v & ~KEY_VALID;
 }
 
-// filter (and rate) this worker warp's rows for one pod.  Argmax policies: every thread keeps the
-// best key of its rows in spec_key.  Random policy: one feasibility bit per row in spec_ok and in
-// the pod's feasbits words, the warp's count in cnt (lane 0).  FIXUP re-does only the thread that
-// owns row `dirty` (the row the previous pod was just bound to); the other lanes keep their
-// results and merely take part in the warp-wide votes.  Must be called by all 32 lanes.
-template <bool FIXUP>
+// filter (and rate) this worker warp's rows for one pod, on the rows as they stand.  Argmax
+// policies: every thread keeps the best two keys of its rows (k1 >= k2).  Random policy: one
+// feasibility bit per row in the pod's feasbits words, the warp's count in cnt (lane 0).
+// Must be called by all 32 lanes.
 __device__ __forceinline__ void filter_pass(const SmemRows& S, const SortedDemand* dem, uint32_t wt, uint32_t WT, uint32_t n_iter,
-                                            uint32_t my_rows, uint32_t node0, uint32_t lane, int g, int gbase, int dirty,
-                                            uint32_t* fb, uint64_t& spec_key, uint64_t& spec_ok, uint32_t& cnt) {
+                                            uint32_t my_rows, uint32_t node0, uint32_t lane, int g, int gbase, uint32_t* fb,
+                                            uint64_t& k1, uint64_t& k2, uint32_t& cnt) {
     const int policy = dem->policy;
     const bool spread = policy == NGS_POLICY_SPREAD;
-    const bool mine = !FIXUP || ((uint32_t)dirty % WT == wt);
     if (policy == NGS_POLICY_RANDOM) {
         uint32_t c = 0;
         for (uint32_t it = 0; it < n_iter; it++) {
             const uint32_t r = it * WT + wt;
-            bool ok;
-            if (mine) {
-                ok = r < my_rows && eval_row_sample(S, r, dem);
-                spec_ok = (spec_ok & ~(1ull << it)) | ((uint64_t)ok << it);
-            } else {
-                ok = (spec_ok >> it) & 1ull;
-            }
+            const bool ok = r < my_rows && eval_row_sample(S, r, dem);
             const uint32_t bal = __ballot_sync(0xFFFFFFFFu, ok);
             if (lane == 0 && r < my_rows) {
                 fb[r >> 5] = bal;
@@ -846,11 +837,12 @@ __device__ __forceinline__ void filter_pass(const SmemRows& S, const SortedDeman
         cnt = c;
         return;
     }
-    if (mine) spec_key = 0;
+    k1 = 0;
+    k2 = 0;
     for (uint32_t it = 0; it < n_iter; it++) {
         const uint32_t r = it * WT + wt;
         int cls = FEAS_NO;
-        if (mine && r < my_rows) {
+        if (r < my_rows) {
             cls = classify_top4(S.top4[r], dem, true);  // unknown nodes hold all zeros: FEAS_NO (or YES for an empty demand,
             if (cls == FEAS_FALLBACK || dem->nz == 0) {  //  which the full-row path below sorts out)
                 cls = FEAS_NO;
@@ -886,9 +878,50 @@ __device__ __forceinline__ void filter_pass(const SmemRows& S, const SortedDeman
         }
         if (cls == FEAS_YES) {
             const uint64_t key = make_key(spread ? S.scS[r] : S.scB[r], node0 + r);
-            spec_key = key > spec_key ? key : spec_key;
+            if (key > k1) {
+                k2 = k1;
+                k1 = key;
+            } else if (key > k2) {
+                k2 = key;
+            }
         }
     }
+}
+
+// the warp's best two keys from every lane's best two: m1 = max of the k1; m2 = the best of what is
+// left (the holder of m1 offers its k2, everyone else their k1).  Keys are distinct (one per row).
+__device__ __forceinline__ void warp_top2(uint64_t k1, uint64_t k2, uint64_t& m1, uint64_t& m2) {
+    m1 = warp_max_u64(k1);
+    m2 = warp_max_u64(k1 == m1 ? k2 : k1);
+}
+
+// feasibility and key of ONE row for one pod, computed by a full warp (control warp 0 right after it
+// has bound the previous pod to that row): shortcuts first, the exact 8-lane search if they do not
+// decide.  All 32 lanes get the same answer.
+__device__ __forceinline__ uint64_t fresh_key_of_row(const SmemRows& S, uint32_t r, uint32_t node, const SortedDemand* dem, int g,
+                                                     int gbase, bool* feasible) {
+    const int policy = dem->policy;
+    if (policy == NGS_POLICY_RANDOM) {
+        *feasible = eval_row_sample(S, r, dem);
+        return 0;
+    }
+    const bool spread = policy == NGS_POLICY_SPREAD;
+    int cls = classify_top4(S.top4[r], dem, true);
+    if (cls == FEAS_FALLBACK || dem->nz == 0) {
+        int f[8];
+        unpack_free(S.fA[r], S.fB[r], f);
+        cls = classify_row(f, dem, true);
+    }
+    if (cls == FEAS_UNDECIDED) {  // warp-uniform: every lane looked at the same row
+        const uint32_t meta = S.meta[r];
+        const int G = (meta >> 24) & 15;
+        cls = choose_group8<false>(g, gbase, smem_cell(S, r, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem, nullptr, nullptr,
+                                   nullptr)
+                  ? FEAS_YES
+                  : FEAS_NO;
+    }
+    *feasible = cls == FEAS_YES;
+    return cls == FEAS_YES ? make_key(spread ? S.scS[r] : S.scB[r], node) : 0ull;
 }
 
 // K6.  One CTA per SM (cooperative launch, so every CTA is resident), each owning a contiguous
@@ -908,14 +941,18 @@ __device__ __forceinline__ void filter_pass(const SmemRows& S, const SortedDeman
 __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ SortedDemand s_dem[4];
-    __shared__ uint64_t s_red[2][32];
-    __shared__ uint64_t s_win;  // the pod's winning key, handed from the exchange warp to the plan warp
-    __shared__ int s_dirty;     // row of this CTA the pod was bound to, -1 if none
+    __shared__ uint64_t s_red[2][32][2];  // per pod parity, per worker warp: best two keys (or {count, -})
+    __shared__ uint64_t s_win;     // the pod's winning key, handed from the exchange warp to the plan warp
+    __shared__ int s_dirty;        // row of this CTA the last pod was bound to, -1 if none
+    __shared__ uint64_t s_fresh;   // that row's key for the NEXT pod, evaluated after the bind (0 = not feasible)
+    __shared__ int s_fresh_ok;     // ... and its feasibility (what the random policy needs)
     __shared__ int s_abort;
     const uint32_t rpb = bp.rows_per_block;
     if (threadIdx.x == 0) {
         s_abort = 0;
         s_dirty = -1;
+        s_fresh = 0;
+        s_fresh_ok = 0;
     }
     const uint32_t fwords = (rpb + 31) / 32;
     SmemRows S;
@@ -1005,7 +1042,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
 #endif
     const uint32_t n_iter = (my_rows + WT - 1) / WT;
     bool rl_pending = bp.lp.enabled != 0;  // RemainLoad write-back of the first load-aware Rate
-    uint64_t spec_key = 0, spec_ok = 0;    // this worker's results for the pod being filtered
+    uint64_t k1 = 0, k2 = 0;  // this worker's best two keys for the pod being filtered
     uint32_t cnt = 0;
 
     // allocate.go:193: LoadUsage leaves RemainLoad in the live node state.  SampleRater.Rate never
@@ -1026,6 +1063,19 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
         }
     };
 
+    auto publish_filter = [&](uint32_t buf, int policy) {  // hand the warp's result for a pod to the control warps
+        if (policy != NGS_POLICY_RANDOM) {
+            uint64_t m1, m2;
+            warp_top2(k1, k2, m1, m2);
+            if (lane == 0) {
+                s_red[buf][ww][0] = m1;
+                s_red[buf][ww][1] = m2;
+            }
+        } else if (lane == 0) {
+            s_red[buf][ww][0] = cnt;
+        }
+    };
+
     // pod 0 is filtered before the loop; inside the loop the workers are always one pod ahead
     if (bp.P > 0) {
         if (rl_pending && s_dem[0].policy != NGS_POLICY_RANDOM) {
@@ -1033,17 +1083,17 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
             write_back_rl();
         }
         if (is_worker) {
-            filter_pass<false>(S, &s_dem[0], wt, WT, n_iter, my_rows, T.first + row0, lane, g, gbase, -1, S.feasbits, spec_key, spec_ok, cnt);
-            if (s_dem[0].policy != NGS_POLICY_RANDOM) {
-                const uint64_t b = warp_max_u64(spec_key);
-                if (lane == 0) s_red[0][ww] = b;
-            } else if (lane == 0) {
-                s_red[0][ww] = cnt;
-            }
+            filter_pass(S, &s_dem[0], wt, WT, n_iter, my_rows, T.first + row0, lane, g, gbase, S.feasbits, k1, k2, cnt);
+            publish_filter(0, s_dem[0].policy);
         }
     }
     __syncthreads();
 
+    // ONE CTA-wide barrier per pod.  In iteration p the workers filter pod p+1 on the rows as they stand
+    // and leave each warp's best TWO keys; the control warps settle pod p, and if this CTA binds it, the
+    // row it was bound to is evaluated once more for pod p+1 by the binding warp itself.  At the start of
+    // iteration p+1 the control warps put the two together: a warp whose best key belongs to the changed
+    // row contributes its second best, and the changed row competes with its fresh key.
     for (uint32_t p = 0; p < bp.P; p++) {
         const SortedDemand* dem = &s_dem[p & 3];
         const int policy = dem->policy;
@@ -1055,24 +1105,48 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
             write_back_rl();
         }
         if (is_worker) {
-            // ---- workers: filter pod p+1 on the rows as they stand (pod p's bind is still in flight) ----
-            if (more)
-                filter_pass<false>(S, dem_next, wt, WT, n_iter, my_rows, T.first + row0, lane, g, gbase, -1,
-                                   S.feasbits + ((p + 1) & 1) * fwords, spec_key, spec_ok, cnt);
+            // ---- workers: filter pod p+1 (pod p's bind may still be in flight: its row is dealt with above) ----
+            if (more) {
+                filter_pass(S, dem_next, wt, WT, n_iter, my_rows, T.first + row0, lane, g, gbase, S.feasbits + ((p + 1) & 1) * fwords, k1,
+                            k2, cnt);
+                publish_filter((p + 1) & 1, dem_next->policy);
+            }
             PHASE(0);
-        } else if (policy == NGS_POLICY_RANDOM) {
-          if (cw == 0) {
-            // ---- control, random policy: counts -> seeded pick -> bind ----
-            bool dead = false;
-            unsigned long long* krow = bp.keys + (size_t)p * bp.keys_stride;
-            uint32_t* done = bp.done + (size_t)p * bp.done_stride;
-            const uint32_t* fb = S.feasbits + (p & 1) * fwords;
-            uint64_t v = lane < NW ? s_red[p & 1][lane] : 0;
-            if (lane == 0) s_dirty = -1;
-            if (p + 2 < bp.P)  // stage the demand the workers will need next
-                for (uint32_t i = lane; i < sizeof(SortedDemand) / 4; i += 32)
-                    reinterpret_cast<uint32_t*>(&s_dem[(p + 2) & 3])[i] = reinterpret_cast<const uint32_t*>(&bp.dem[p + 2])[i];
-            {
+        } else {
+            // what the previous iteration left: the row pod p-1 was bound to (if it is ours) and its fresh verdict
+            const int dirty = s_dirty;
+            const uint64_t fresh = s_fresh;
+            const int fresh_ok = s_fresh_ok;
+            const uint32_t dirty_node = dirty >= 0 ? T.first + row0 + (uint32_t)dirty : 0xFFFFFFFFu;
+            asm volatile("bar.sync 2, 64;" ::: "memory");  // both control warps have read them: they may be rewritten
+            if (policy == NGS_POLICY_RANDOM) {
+              if (cw == 0) {
+                // ---- control, random policy: counts -> seeded pick -> bind ----
+                bool dead = false;
+                unsigned long long* krow = bp.keys + (size_t)p * bp.keys_stride;
+                uint32_t* done = bp.done + (size_t)p * bp.done_stride;
+                uint32_t* fb = S.feasbits + (p & 1) * fwords;
+                uint64_t v = lane < NW ? s_red[p & 1][lane][0] : 0;
+                if (dirty >= 0) {  // the changed row: replace its (possibly stale) bit by the fresh verdict
+                    const uint32_t wi = (uint32_t)dirty >> 5, bit = 1u << (dirty & 31);
+                    const uint32_t old = fb[wi];
+                    __syncwarp();
+                    if (lane == 0) {
+                        fb[wi] = fresh_ok ? (old | bit) : (old & ~bit);
+                        v += (uint64_t)(fresh_ok ? 1 : 0) - (uint64_t)((old & bit) ? 1 : 0);  // lane 0 holds warp 0's count
+                    }
+                    __syncwarp();
+                }
+                if (lane == 0) {
+                    s_dirty = -1;
+                    s_fresh = 0;
+                    s_fresh_ok = 0;
+                }
+                if (p + 2 < bp.P)  // stage the demand the workers will need next
+                    for (uint32_t i = lane; i < sizeof(SortedDemand) / 4; i += 32)
+                        reinterpret_cast<uint32_t*>(&s_dem[(p + 2) & 3])[i] = reinterpret_cast<const uint32_t*>(&bp.dem[p + 2])[i];
+                int bound_row = -1;
+                {
                 uint32_t c = (uint32_t)v;
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, o);
@@ -1162,7 +1236,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                                     for (uint32_t q = 0; q < need; q++) bits &= bits - 1;
                                     const uint32_t r = wi * 32 + (__ffs(bits) - 1);
                                     publish_sample(bp, S, r, row0 + r, dem, p);
-                                    s_dirty = (int)r;
+                                    bound_row = (int)r;
                                     break;
                                 }
                                 need -= pc;
@@ -1170,104 +1244,121 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                         }
                     }
                 }
-            }
-            if (dead && lane == 0) s_abort = 1;
-          }
-        } else {
-            // ---- control, arg-max policies: warp 1 runs the exchange while warp 0 works out the exact
-            // plan of this CTA's best row (published only if that row is the global winner) ----
-            uint64_t v = lane < NW ? s_red[p & 1][lane] : 0;
-            v = warp_max_u64(v);
-            const bool have = (v & KEY_FEASIBLE) != 0;
-            const uint32_t my_r = have ? key_node(v) - T.first - row0 : 0u;
-            GroupCommit cm;
-            cm.fr = 0;
-            cm.emit = 0;
-            cm.n_emit = 0;
-            if (cw == 1) {
-                // exchange (fastest variant of profiles/tools/xchg_bench.cu): atomicMax into the pod's
-                // word; the arrival counter is bumped only after that atomic has returned (data
-                // dependence), so a full counter implies every CTA's key is in the word
-                bool dead = false;
-                ulonglong2* xw = bp.xw + (size_t)p * bp.xw_stride;
-                if (lane == 0) {
-                    const unsigned long long old = atomicMax(&xw->x, (unsigned long long)v);
-                    const unsigned long long one = 1ull + (old >> 63);  // bit 63 is never set: always 1
-                    asm volatile("red.relaxed.gpu.global.add.u64 [%0], %1;" ::"l"(&xw->y), "l"(one) : "memory");
                 }
-                if (bp.world == 1) {
+                // if this CTA bound the pod, evaluate that row for the next pod right away
+                const uint32_t bmask = __ballot_sync(0xFFFFFFFFu, bound_row >= 0);
+                if (bmask && more) {
+                    const int br = __shfl_sync(0xFFFFFFFFu, bound_row, __ffs(bmask) - 1);
+                    bool ok = false;
+                    const uint64_t fk = fresh_key_of_row(S, (uint32_t)br, T.first + row0 + (uint32_t)br, dem_next, g, gbase, &ok);
                     if (lane == 0) {
-                        unsigned long long m;
-                        dead = !wait_exchange(xw, gridDim.x, bp.err, &m);
-                        s_win = m;
+                        s_dirty = br;
+                        s_fresh = fk;
+                        s_fresh_ok = ok ? 1 : 0;
                     }
-                } else if (blockIdx.x == 0) {
-                    // K5: this rank's best key goes to every peer; the best over all ranks comes back
-                    unsigned long long mloc = 0;
-                    if (lane == 0) dead = !wait_exchange(xw, gridDim.x, bp.err, &mloc);
-                    mloc = __shfl_sync(0xFFFFFFFFu, mloc, 0);
-                    dead = __any_sync(0xFFFFFFFFu, dead);
-                    const uint64_t mg = warp_max_u64(cross_rank_exchange(bp, p, mloc, lane, dead));
-                    if (lane == 0) {
-                        st_relaxed_u64(bp.gwin + p, mg | KEY_VALID);
-                        s_win = mg;
-                    }
-                } else if (lane == 0) {
-                    s_win = wait_valid(bp.gwin + p, bp.err, dead);
                 }
                 if (dead && lane == 0) s_abort = 1;
+              }
             } else {
-                if (lane == 0) s_dirty = -1;
-                if (p + 2 < bp.P)  // stage the demand the workers will need next
-                    for (uint32_t i = lane; i < sizeof(SortedDemand) / 4; i += 32)
-                        reinterpret_cast<uint32_t*>(&s_dem[(p + 2) & 3])[i] = reinterpret_cast<const uint32_t*>(&bp.dem[p + 2])[i];
-                if (have) {
-                    const uint32_t meta = S.meta[my_r];
-                    const int G = (meta >> 24) & 15;
-                    choose_group8<true>(g, gbase, smem_cell(S, my_r, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem, &cm.emit,
-                                        &cm.n_emit, &cm.fr);
+                // ---- control, arg-max policies: warp 1 runs the exchange while warp 0 works out the exact
+                // plan of this CTA's best row (published only if that row is the global winner) ----
+                uint64_t v = 0;
+                if (lane < NW) {
+                    const uint64_t m1 = s_red[p & 1][lane][0], m2 = s_red[p & 1][lane][1];
+                    v = ((m1 & KEY_FEASIBLE) && key_node(m1) == dirty_node) ? m2 : m1;  // drop the changed row's old key
                 }
-            }
-            PHASE(4);
-            asm volatile("bar.sync 1, 64;" ::: "memory");  // the two control warps only
-            PHASE_AFTER_BARRIER(5);
-            if (cw == 0) {
-                const uint64_t m = s_win;
-                if (!(m & KEY_FEASIBLE)) {
-                    if (blockIdx.x == 0 && lane == 0) publish_none(bp, p);
-                } else if (blockIdx.x == 0 && lane == 0 && key_node(m) - T.first >= T.n) {
-                    // the winner lives on another rank: node and score are known from the key, the
-                    // plan is filled in by the owner (merged on the host side by an allreduce-max)
-                    publish_none(bp, p);
-                    bp.node_out[p] = (int32_t)key_node(m);
-                    bp.score_out[p] = key_score(m);
-                } else if (have && m == v && lane < 8) {
-                    // ---- bind on the owner ----
-                    publish_group(bp, S, my_r, row0 + my_r, dem, p, key_score(m), cm, g);
-                    if (lane == 0) s_dirty = (int)my_r;
+                v = warp_max_u64(v);
+                v = fresh > v ? fresh : v;  // ... and let it compete with its fresh one
+                const bool have = (v & KEY_FEASIBLE) != 0;
+                const uint32_t my_r = have ? key_node(v) - T.first - row0 : 0u;
+                GroupCommit cm;
+                cm.fr = 0;
+                cm.emit = 0;
+                cm.n_emit = 0;
+                if (cw == 1) {
+                    // exchange (fastest variant of profiles/tools/xchg_bench.cu): atomicMax into the pod's
+                    // word; the arrival counter is bumped only after that atomic has returned (data
+                    // dependence), so a full counter implies every CTA's key is in the word
+                    bool dead = false;
+                    ulonglong2* xw = bp.xw + (size_t)p * bp.xw_stride;
+                    if (lane == 0) {
+                        const unsigned long long old = atomicMax(&xw->x, (unsigned long long)v);
+                        const unsigned long long one = 1ull + (old >> 63);  // bit 63 is never set: always 1
+                        asm volatile("red.relaxed.gpu.global.add.u64 [%0], %1;" ::"l"(&xw->y), "l"(one) : "memory");
+                    }
+                    PHASE(2);
+                    if (bp.world == 1) {
+                        if (lane == 0) {
+                            unsigned long long m;
+                            dead = !wait_exchange(xw, gridDim.x, bp.err, &m);
+                            s_win = m;
+                        }
+                    } else if (blockIdx.x == 0) {
+                        // K5: this rank's best key goes to every peer; the best over all ranks comes back
+                        unsigned long long mloc = 0;
+                        if (lane == 0) dead = !wait_exchange(xw, gridDim.x, bp.err, &mloc);
+                        mloc = __shfl_sync(0xFFFFFFFFu, mloc, 0);
+                        dead = __any_sync(0xFFFFFFFFu, dead);
+                        const uint64_t mg = warp_max_u64(cross_rank_exchange(bp, p, mloc, lane, dead));
+                        if (lane == 0) {
+                            st_relaxed_u64(bp.gwin + p, mg | KEY_VALID);
+                            s_win = mg;
+                        }
+                    } else if (lane == 0) {
+                        s_win = wait_valid(bp.gwin + p, bp.err, dead);
+                    }
+                    if (dead && lane == 0) s_abort = 1;
+                } else {
+                    if (lane == 0) {
+                        s_dirty = -1;
+                        s_fresh = 0;
+                        s_fresh_ok = 0;
+                    }
+                    if (p + 2 < bp.P)  // stage the demand the workers will need next
+                        for (uint32_t i = lane; i < sizeof(SortedDemand) / 4; i += 32)
+                            reinterpret_cast<uint32_t*>(&s_dem[(p + 2) & 3])[i] = reinterpret_cast<const uint32_t*>(&bp.dem[p + 2])[i];
+                    if (have) {
+                        const uint32_t meta = S.meta[my_r];
+                        const int G = (meta >> 24) & 15;
+                        choose_group8<true>(g, gbase, smem_cell(S, my_r, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem, &cm.emit,
+                                            &cm.n_emit, &cm.fr);
+                    }
                 }
-                PHASE(6);
+                PHASE(4);
+                asm volatile("bar.sync 1, 64;" ::: "memory");  // the two control warps only
+                PHASE_AFTER_BARRIER(5);
+                if (cw == 0) {
+                    const uint64_t m = s_win;
+                    if (!(m & KEY_FEASIBLE)) {
+                        if (blockIdx.x == 0 && lane == 0) publish_none(bp, p);
+                    } else if (blockIdx.x == 0 && lane == 0 && key_node(m) - T.first >= T.n) {
+                        // the winner lives on another rank: node and score are known from the key, the
+                        // plan is filled in by the owner (merged on the host side by an allreduce-max)
+                        publish_none(bp, p);
+                        bp.node_out[p] = (int32_t)key_node(m);
+                        bp.score_out[p] = key_score(m);
+                    }
+                    if (have && m == v) {  // warp-uniform
+                        // ---- bind on the owner, then look at the changed row once more for the next pod ----
+                        if (lane < 8) publish_group(bp, S, my_r, row0 + my_r, dem, p, key_score(m), cm, g);
+                        __syncwarp();
+                        if (more) {
+                            bool ok = false;
+                            const uint64_t fk = fresh_key_of_row(S, my_r, T.first + row0 + my_r, dem_next, g, gbase, &ok);
+                            if (lane == 0) {
+                                s_dirty = (int)my_r;
+                                s_fresh = fk;
+                                s_fresh_ok = ok ? 1 : 0;
+                            }
+                        }
+                    }
+                    PHASE(6);
+                }
             }
         }
-        __syncthreads();  // pod p is bound; the workers' results for pod p+1 are in registers
+        __syncthreads();  // pod p is settled; the workers' results for pod p+1 are in s_red / feasbits
         PHASE_AFTER_BARRIER(1);
         if (s_abort) break;  // a peer never posted: give up instead of hanging the GPU
-        if (is_worker && more) {
-            // ---- fix-up: only the row pod p was bound to can have changed ----
-            const int dirty = s_dirty;
-            if (dirty >= 0 && ((uint32_t)dirty % WT) / 32 == ww)
-                filter_pass<true>(S, dem_next, wt, WT, n_iter, my_rows, T.first + row0, lane, g, gbase, dirty,
-                                  S.feasbits + ((p + 1) & 1) * fwords, spec_key, spec_ok, cnt);
-            if (dem_next->policy != NGS_POLICY_RANDOM) {
-                const uint64_t b = warp_max_u64(spec_key);
-                if (lane == 0) s_red[(p + 1) & 1][ww] = b;
-            } else if (lane == 0) {
-                s_red[(p + 1) & 1][ww] = cnt;
-            }
-            PHASE(2);
-        }
-        __syncthreads();
-        PHASE_AFTER_BARRIER(3);
     }
     if (blockIdx.x == 0 && tid == 0 && bp.status_out) *bp.status_out = *reinterpret_cast<volatile int32_t*>(bp.err);
 #ifdef NGS_PHASE_TIMING

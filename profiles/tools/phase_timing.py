@@ -46,9 +46,9 @@ grid = C.c_uint32(0)
 assert lib.ngs_debug_phases(d._h, buf.ctypes.data_as(C.c_void_p), C.byref(grid)) == 0
 g = grid.value
 a = buf[: 16 * g].reshape(g, 16).astype(np.float64) / P
-names = ["filter p+1 (workers)", "barrier S1 (pod p bound)", "fix-up + reduce (workers)", "barrier S2", "plan (w0)", "wait for exchange (w1)", "publish", "-"]
+names = ["filter p+1 (workers)", "barrier (pod p settled)", "cw1: combine + atomicMax + bump", "-", "plan (cw0) / exchange (cw1)", "pair barrier", "publish + fresh look at the row", "-"]
 print(f"{name}: {cfg['nodes']} nodes, {P} pods, grid {g}; cycles per pod (min / median / max over CTAs)")
-for who, off in (("control warp 0 (plan, bind)", 0), ("control warp 1 (exchange): 0 reduce, 2 atomicMax+bump, 6 all arrived, 4 read, 5 pair barrier, 1 S1, 3 S2", 8)):
+for who, off in (("control warp 0 (plan, bind)", 0), ("control warp 1 (exchange)", 8)):
     print(who)
     for i in range(8):
         col = a[:, off + i]

@@ -61,8 +61,9 @@ __global__ void k(unsigned long long* slots, uint32_t* cnt, unsigned long long* 
     }
     if (threadIdx.x == 0) { out[blockIdx.x * 2] = clock64() - t0; out[blockIdx.x * 2 + 1] = acc; }
 }
-template <int MODE> void run(const char* name, int work) {
+template <int MODE> void run(const char* name, int work, int grid_override = 0) {
     int dev = 0, sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (grid_override) sms = grid_override;
     const int rounds = 2000;
     unsigned long long *slots, *mx, *out; uint32_t* cnt;
     cudaMalloc(&slots, 8ull * rounds * sms); cudaMalloc(&mx, 8ull * rounds); cudaMalloc(&cnt, 4ull * rounds); cudaMalloc(&out, 16ull * sms);
@@ -75,7 +76,7 @@ template <int MODE> void run(const char* name, int work) {
     }
     unsigned long long h[512]; cudaMemcpy(h, out, 16ull * sms, cudaMemcpyDeviceToHost);
     double s = 0; for (int i = 0; i < sms; i++) s += h[2 * i];
-    printf("%-44s work=%4d : %8.0f cycles per round\n", name, work, s / sms / rounds);
+    printf("%-44s work=%4d grid=%3d : %8.0f cycles per round\n", name, work, sms, s / sms / rounds);
     cudaFree(slots); cudaFree(mx); cudaFree(cnt); cudaFree(out);
 }
 int main() {
@@ -86,5 +87,6 @@ int main() {
         run<3>("3 = 1 with nanosleep(40)", work);
         run<4>("4 = 0 with nanosleep(20) backoff", work);
     }
+    for (int g : {16, 37, 74, 148}) run<2>("2 atomicMax word + counter", 0, g);
     return 0;
 }
