@@ -630,55 +630,94 @@ __device__ __forceinline__ bool eval_row_sample(const SmemRows& S, uint32_t r, c
     return choose_sample<false>(f, G, dem, nullptr, nullptr);
 }
 
-// The decision for one row, spread over the 8 lanes that searched its plan (lane = GPU cell)
-// and held in registers until the row is known to be the global winner.
+// The decision for one row, worked out by a full warp (lane = GPU cell, the four 8-lane groups hold
+// identical copies) while the pod's exchange is still in flight, and held in registers until the
+// row is known to be the global winner: the plan, the row as GPUs.Allocate leaves it, its new
+// rates and top-4, and already the row's verdict for the NEXT pod.
 struct GroupCommit {
-    int32_t fr;      // this lane's cell after GPUs.Allocate
-    uint64_t emit;   // emission list (same in all 8 lanes)
+    int32_t fr;      // this lane's cell after GPUs.Allocate (0 beyond the GPU count)
+    uint64_t emit;   // emission list
     int32_t n_emit;
+    uint32_t top4;
+    int32_t scB, scS;
+    uint64_t fresh;  // key of the changed row for the next pod (0 = not feasible)
+    int32_t fresh_ok;
 };
 
-// publish a winning decision (called by lanes 0..7 of warp 0): shared row, cached rates, the
-// global table and the pod's outputs
-__device__ __forceinline__ void publish_group(const BatchParams& bp, const SmemRows& S, uint32_t r, uint32_t row,
-                                              const SortedDemand* dem, uint32_t p, int score, const GroupCommit& cm, int g) {
+__device__ __forceinline__ void plan_group(const BatchParams& bp, const SmemRows& S, uint32_t r, uint32_t node, const SortedDemand* dem,
+                                           const SortedDemand* dem_next, int g, int gbase, GroupCommit& cm) {
     const uint32_t meta = S.meta[r];
     const int G = (meta >> 24) & 15;
     const int load_int = (int)(meta >> 28);
+    const int rlc = (int)((meta >> (3 * g)) & 7);
     const bool valid = g < G;
+    choose_group8<true>(g, gbase, smem_cell(S, r, g), rlc, valid, dem->policy == NGS_POLICY_SPREAD, dem, &cm.emit, &cm.n_emit, &cm.fr);
     const int fr = valid ? cm.fr : 0;
-    reinterpret_cast<uint16_t*>(g < 4 ? &S.fA[r] : &S.fB[r])[g & 3] = (uint16_t)fr;
-    bp.T.free[(size_t)row * 8 + g] = fr;  // 8 lanes: one 32 B row store
-    // both rates of the new state (Rate is a function of the row only, allocate.go:96)
-    const int sumf = __reduce_add_sync(0xFFu, fr);
-    const int cnt100 = __popc(__ballot_sync(0xFFu, valid && fr == 100));
-    {
-        // the four largest cells: each lane ranks its own (descending, ties by index)
-        const uint32_t c = ((uint32_t)fr << 3) | (uint32_t)(7 - g);
-        int rank = 0;
+    cm.fr = fr;
+    // the row after the bind: sum, fully free cells, four largest (each lane ranks its own cell:
+    // descending, ties by index), both rates (Rate is a function of the row only, allocate.go:96)
+    int sumf = fr;
+    sumf += __shfl_xor_sync(FULL, sumf, 1);
+    sumf += __shfl_xor_sync(FULL, sumf, 2);
+    sumf += __shfl_xor_sync(FULL, sumf, 4);
+    const int cnt100 = __popc((__ballot_sync(FULL, valid && fr == 100) >> gbase) & 0xFFu);
+    const uint32_t c = ((uint32_t)fr << 3) | (uint32_t)(7 - g);
+    int rank = 0;
 #pragma unroll
-        for (int sft = 1; sft < 8; sft++) rank += __shfl_xor_sync(0xFFu, c, sft) > c ? 1 : 0;
-        const uint32_t t4 = __reduce_or_sync(0xFFu, rank < 4 ? (uint32_t)min(fr, 255) << (8 * rank) : 0u);
-        if (g == 0) S.top4[r] = t4;
+    for (int sft = 1; sft < 8; sft++) rank += __shfl_xor_sync(FULL, c, sft) > c ? 1 : 0;
+    uint32_t t4 = rank < 4 ? (uint32_t)min(fr, 255) << (8 * rank) : 0u;
+    t4 |= __shfl_xor_sync(FULL, t4, 1);
+    t4 |= __shfl_xor_sync(FULL, t4, 2);
+    t4 |= __shfl_xor_sync(FULL, t4, 4);
+    const int used = 100 * G - sumf;  // allocate.go:164-171
+    const int pct = (bp.T.blut != nullptr && used >= 0 && used <= 100 * G) ? (int)__ldg(bp.T.blut + G * RATE_LUT_STRIDE + used)
+                                                                            : binpack_percent_fp64(used, G);
+    cm.top4 = t4;
+    cm.scB = pct + load_int * 50 - G;                    // rater.go:69
+    cm.scS = 100 * cnt100 + sumf / 10 - G - load_int;    // rater.go:122
+    cm.fresh = 0;
+    cm.fresh_ok = 0;
+    if (dem_next == nullptr) return;
+    // the next pod on the row as it will stand after this bind
+    const int pol2 = dem_next->policy;
+    int cls = pol2 == NGS_POLICY_RANDOM ? FEAS_FALLBACK : classify_top4(t4, dem_next, true);
+    if (cls == FEAS_FALLBACK || dem_next->nz == 0) {  // (warp-uniform: all groups look at the same row)
+        int f[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) f[i] = __shfl_sync(FULL, fr, gbase + i);
+        cls = classify_row(f, dem_next, pol2 != NGS_POLICY_RANDOM);
+        if (cls == FEAS_UNDECIDED && pol2 == NGS_POLICY_RANDOM) cls = choose_sample<false>(f, G, dem_next, nullptr, nullptr) ? FEAS_YES : FEAS_NO;
     }
-    if (g == 0) {
-        const int used = 100 * G - sumf;                                                   // allocate.go:164-171
-        const int pct = (bp.T.blut != nullptr && used >= 0 && used <= 100 * G) ? (int)__ldg(bp.T.blut + G * RATE_LUT_STRIDE + used)
-                                                                                : binpack_percent_fp64(used, G);
-        S.scB[r] = pct + load_int * 50 - G;                                                // rater.go:69
-        S.scS[r] = 100 * cnt100 + sumf / 10 - G - load_int;                                // rater.go:122
+    if (cls == FEAS_UNDECIDED)
+        cls = choose_group8<false>(g, gbase, fr, rlc, valid, pol2 == NGS_POLICY_SPREAD, dem_next, nullptr, nullptr, nullptr) ? FEAS_YES
+                                                                                                                               : FEAS_NO;
+    cm.fresh_ok = cls == FEAS_YES;
+    if (cls == FEAS_YES && pol2 != NGS_POLICY_RANDOM) cm.fresh = make_key(pol2 == NGS_POLICY_SPREAD ? cm.scS : cm.scB, node);
+}
+
+// publish a winning decision (all 32 lanes of control warp 0): shared row, cached rates, the global
+// table and the pod's outputs -- stores only, everything was computed by plan_group
+__device__ __forceinline__ void publish_group(const BatchParams& bp, const SmemRows& S, uint32_t r, uint32_t row,
+                                              const SortedDemand* dem, uint32_t p, int score, const GroupCommit& cm, uint32_t lane) {
+    if (lane < 8) {
+        reinterpret_cast<uint16_t*>(lane < 4 ? &S.fA[r] : &S.fB[r])[lane & 3] = (uint16_t)cm.fr;
+        bp.T.free[(size_t)row * 8 + lane] = cm.fr;  // 8 lanes: one 32 B row store
+        int32_t* out = bp.gpu_idx_out + (size_t)p * bp.max_c;
+        const int C = dem->C;
+        for (int k = (int)lane; k < bp.max_c; k += 8)
+            if (k >= C) out[k] = INT32_MIN;
+        for (int k = (int)lane; k < C; k += 8) {  // rater.go:102-105: un-permute the emission order
+            const int e = (int)((cm.emit >> (4 * k)) & 0xF);
+            out[dem->order[k]] = e == 0xF ? NGS_NOT_NEED_GPU : e;
+        }
+    }
+    if (lane == 0) {
+        S.scB[r] = cm.scB;
+        S.scS[r] = cm.scS;
+        S.top4[r] = cm.top4;
         bp.T.tag[row] = 0;  // node.go:82
         bp.node_out[p] = (int32_t)(bp.T.first + row);
         bp.score_out[p] = score;
-    }
-    int32_t* out = bp.gpu_idx_out + (size_t)p * bp.max_c;
-    const int C = dem->C;
-    for (int k = g; k < bp.max_c; k += 8) {
-        if (k >= C) out[k] = INT32_MIN;
-    }
-    for (int k = g; k < C; k += 8) {  // rater.go:102-105: un-permute the emission order
-        const int e = (int)((cm.emit >> (4 * k)) & 0xF);
-        out[dem->order[k]] = e == 0xF ? NGS_NOT_NEED_GPU : e;
     }
 }
 
@@ -1275,6 +1314,10 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                 cm.fr = 0;
                 cm.emit = 0;
                 cm.n_emit = 0;
+                cm.top4 = 0;
+                cm.scB = cm.scS = 0;
+                cm.fresh = 0;
+                cm.fresh_ok = 0;
                 if (cw == 1) {
                     // exchange (fastest variant of profiles/tools/xchg_bench.cu): atomicMax into the pod's
                     // word; the arrival counter is bumped only after that atomic has returned (data
@@ -1285,6 +1328,11 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                         const unsigned long long old = atomicMax(&xw->x, (unsigned long long)v);
                         const unsigned long long one = 1ull + (old >> 63);  // bit 63 is never set: always 1
                         asm volatile("red.relaxed.gpu.global.add.u64 [%0], %1;" ::"l"(&xw->y), "l"(one) : "memory");
+                    } else if (p + 2 < bp.P) {
+                        // the idle lanes stage the demand the workers will need next (its global-load latency
+                        // hides behind this warp's wait for the exchange)
+                        for (uint32_t i = lane - 1; i < sizeof(SortedDemand) / 4; i += 31)
+                            reinterpret_cast<uint32_t*>(&s_dem[(p + 2) & 3])[i] = reinterpret_cast<const uint32_t*>(&bp.dem[p + 2])[i];
                     }
                     PHASE(2);
                     if (bp.world == 1) {
@@ -1314,15 +1362,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                         s_fresh = 0;
                         s_fresh_ok = 0;
                     }
-                    if (p + 2 < bp.P)  // stage the demand the workers will need next
-                        for (uint32_t i = lane; i < sizeof(SortedDemand) / 4; i += 32)
-                            reinterpret_cast<uint32_t*>(&s_dem[(p + 2) & 3])[i] = reinterpret_cast<const uint32_t*>(&bp.dem[p + 2])[i];
-                    if (have) {
-                        const uint32_t meta = S.meta[my_r];
-                        const int G = (meta >> 24) & 15;
-                        choose_group8<true>(g, gbase, smem_cell(S, my_r, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem, &cm.emit,
-                                            &cm.n_emit, &cm.fr);
-                    }
+                    if (have) plan_group(bp, S, my_r, T.first + row0 + my_r, dem, more ? dem_next : nullptr, g, gbase, cm);
                 }
                 PHASE(4);
                 asm volatile("bar.sync 1, 64;" ::: "memory");  // the two control warps only
@@ -1339,17 +1379,12 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                         bp.score_out[p] = key_score(m);
                     }
                     if (have && m == v) {  // warp-uniform
-                        // ---- bind on the owner, then look at the changed row once more for the next pod ----
-                        if (lane < 8) publish_group(bp, S, my_r, row0 + my_r, dem, p, key_score(m), cm, g);
-                        __syncwarp();
-                        if (more) {
-                            bool ok = false;
-                            const uint64_t fk = fresh_key_of_row(S, my_r, T.first + row0 + my_r, dem_next, g, gbase, &ok);
-                            if (lane == 0) {
-                                s_dirty = (int)my_r;
-                                s_fresh = fk;
-                                s_fresh_ok = ok ? 1 : 0;
-                            }
+                        // ---- bind on the owner: stores only, everything was worked out during the exchange ----
+                        publish_group(bp, S, my_r, row0 + my_r, dem, p, key_score(m), cm, lane);
+                        if (lane == 0) {
+                            s_dirty = (int)my_r;
+                            s_fresh = cm.fresh;
+                            s_fresh_ok = cm.fresh_ok;
                         }
                     }
                     PHASE(6);
