@@ -645,7 +645,7 @@ struct GroupCommit {
 };
 
 __device__ __forceinline__ void plan_group(const BatchParams& bp, const SmemRows& S, uint32_t r, uint32_t node, const SortedDemand* dem,
-                                           const SortedDemand* dem_next, int g, int gbase, GroupCommit& cm) {
+                                           const SortedDemand* dem_next, int g, int gbase, GroupCommit& cm, long long* stamps = nullptr) {
     const uint32_t meta = S.meta[r];
     const int G = (meta >> 24) & 15;
     const int load_int = (int)(meta >> 28);
@@ -654,6 +654,9 @@ __device__ __forceinline__ void plan_group(const BatchParams& bp, const SmemRows
     choose_group8<true>(g, gbase, smem_cell(S, r, g), rlc, valid, dem->policy == NGS_POLICY_SPREAD, dem, &cm.emit, &cm.n_emit, &cm.fr);
     const int fr = valid ? cm.fr : 0;
     cm.fr = fr;
+#ifdef NGS_PHASE_TIMING
+    if (stamps) stamps[0] = clock64() + (fr == -12345);
+#endif
     // the row after the bind: sum, fully free cells, four largest (each lane ranks its own cell:
     // descending, ties by index), both rates (Rate is a function of the row only, allocate.go:96)
     int sumf = fr;
@@ -677,6 +680,9 @@ __device__ __forceinline__ void plan_group(const BatchParams& bp, const SmemRows
     cm.scS = 100 * cnt100 + sumf / 10 - G - load_int;    // rater.go:122
     cm.fresh = 0;
     cm.fresh_ok = 0;
+#ifdef NGS_PHASE_TIMING
+    if (stamps) stamps[1] = clock64() + (cm.scB == -12345678);
+#endif
     if (dem_next == nullptr) return;
     // the next pod on the row as it will stand after this bind
     const int pol2 = dem_next->policy;
@@ -1362,7 +1368,18 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                         s_fresh = 0;
                         s_fresh_ok = 0;
                     }
+#ifdef NGS_PHASE_TIMING
+                    long long st[2] = {0, 0};
+                    const long long t_in = clock64();
+                    if (have) plan_group(bp, S, my_r, T.first + row0 + my_r, dem, more ? dem_next : nullptr, g, gbase, cm, st);
+                    if (have && cm.fresh != 12345) {
+                        ph[0] += st[0] - t_in;   // exact plan (choose_group8<PLAN>)
+                        ph[2] += st[1] - st[0];  // post-bind statistics and rates
+                        ph[6] -= 0;
+                    }
+#else
                     if (have) plan_group(bp, S, my_r, T.first + row0 + my_r, dem, more ? dem_next : nullptr, g, gbase, cm);
+#endif
                 }
                 PHASE(4);
                 asm volatile("bar.sync 1, 64;" ::: "memory");  // the two control warps only

@@ -46,12 +46,12 @@ grid = C.c_uint32(0)
 assert lib.ngs_debug_phases(d._h, buf.ctypes.data_as(C.c_void_p), C.byref(grid)) == 0
 g = grid.value
 a = buf[: 16 * g].reshape(g, 16).astype(np.float64) / P
-names = ["filter p+1 (workers)", "barrier (pod p settled)", "cw1: combine + atomicMax + bump", "-", "plan (cw0) / exchange (cw1)", "pair barrier", "publish + fresh look at the row", "-"]
+names = ["cw0: exact plan only / workers: filter", "barrier (pod p settled)", "cw0: post-bind stats / cw1: combine+atomicMax+bump", "-", "cw0: whole plan_group (incl. the two above) / cw1: exchange wait", "pair barrier", "publish", "-"]
 print(f"{name}: {cfg['nodes']} nodes, {P} pods, grid {g}; cycles per pod (min / median / max over CTAs)")
 for who, off in (("control warp 0 (plan, bind)", 0), ("control warp 1 (exchange)", 8)):
     print(who)
     for i in range(8):
         col = a[:, off + i]
-        print(f"  {names[i]:26s} {col.min():8.0f} {np.median(col):8.0f} {col.max():8.0f}")
+        print(f"  {names[i]:84s} {col.min():8.0f} {np.median(col):8.0f} {col.max():8.0f}")
     print(f"  {'total':14s} {a[:, off:off + 8].sum(axis=1).mean():8.0f}")
 
