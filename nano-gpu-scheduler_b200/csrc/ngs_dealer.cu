@@ -988,16 +988,17 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     __shared__ SortedDemand s_dem[4];
     __shared__ uint64_t s_red[2][32][2];  // per pod parity, per worker warp: best two keys (or {count, -})
     __shared__ uint64_t s_win;     // the pod's winning key, handed from the exchange warp to the plan warp
-    __shared__ int s_dirty;        // row of this CTA the last pod was bound to, -1 if none
-    __shared__ uint64_t s_fresh;   // that row's key for the NEXT pod, evaluated after the bind (0 = not feasible)
-    __shared__ int s_fresh_ok;     // ... and its feasibility (what the random policy needs)
+    // what binding pod p-1 leaves for pod p, indexed by p & 1 (written during iteration p-1, read in p):
+    __shared__ int s_dirty[2];        // row of this CTA pod p-1 was bound to, -1 if none
+    __shared__ uint64_t s_fresh[2];   // that row's key for pod p, evaluated on the row after the bind (0 = not feasible)
+    __shared__ int s_fresh_ok[2];     // ... and its feasibility (what the random policy needs)
     __shared__ int s_abort;
     const uint32_t rpb = bp.rows_per_block;
     if (threadIdx.x == 0) {
         s_abort = 0;
-        s_dirty = -1;
-        s_fresh = 0;
-        s_fresh_ok = 0;
+        s_dirty[0] = s_dirty[1] = -1;
+        s_fresh[0] = s_fresh[1] = 0;
+        s_fresh_ok[0] = s_fresh_ok[1] = 0;
     }
     const uint32_t fwords = (rpb + 31) / 32;
     SmemRows S;
@@ -1012,10 +1013,19 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
     // the two control warps are the LAST two: the SM's issue arbiter favours high warp ids, and the
     // control path (exchange, plan) is the latency-critical one
-    const uint32_t NW = nwarps - 2, WT = blockDim.x - 64;  // worker warps / threads
-    const uint32_t wt = tid, ww = warp;                    // worker ids (meaningful for warp < NW)
-    const bool is_worker = warp < NW;
-    const uint32_t cw = warp - NW;                         // control warp 0 (plan, bind) / 1 (exchange)
+    // Warps map to the SM's four schedulers by warp id % 4.  Control warp 0 runs the latency-critical plan
+    // search; the worker warps that would share its scheduler stay idle (they own no rows), so that its
+    // instructions never queue behind the filter's.
+    const uint32_t NWARP = nwarps - 2;                     // warps below the control warps
+    const uint32_t csm = NWARP & 3u;                       // scheduler of control warp 0
+    const uint32_t idle_below = (warp + 3u - csm) >> 2;    // idle warps among [0, warp)
+    const uint32_t NW = NWARP - ((NWARP + 3u - csm) >> 2); // worker warps that own rows
+    const uint32_t WT = NW * 32u;
+    const bool is_worker = warp < NWARP && (warp & 3u) != csm;
+    const bool is_control = warp >= NWARP;
+    const uint32_t ww = warp - idle_below;                 // worker index (meaningful for workers)
+    const uint32_t wt = ww * 32u + lane;
+    const uint32_t cw = warp - NWARP;                      // control warp 0 (plan, bind) / 1 (exchange)
     const uint32_t row0 = blockIdx.x * rpb;
     const uint32_t my_rows = row0 < bp.T.n ? min(rpb, bp.T.n - row0) : 0u;
     const Tables& T = bp.T;
@@ -1157,13 +1167,14 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                 publish_filter((p + 1) & 1, dem_next->policy);
             }
             PHASE(0);
-        } else {
+        } else if (is_control) {
             // what the previous iteration left: the row pod p-1 was bound to (if it is ours) and its fresh verdict
-            const int dirty = s_dirty;
-            const uint64_t fresh = s_fresh;
-            const int fresh_ok = s_fresh_ok;
+            const int dirty = s_dirty[p & 1];
+            const uint64_t fresh = s_fresh[p & 1];
+            const int fresh_ok = s_fresh_ok[p & 1];
             const uint32_t dirty_node = dirty >= 0 ? T.first + row0 + (uint32_t)dirty : 0xFFFFFFFFu;
-            asm volatile("bar.sync 2, 64;" ::: "memory");  // both control warps have read them: they may be rewritten
+            const uint32_t nx = (p + 1) & 1;  // slot control warp 0 fills for the next pod
+            PHASE(3);  // (profiling) control warps: start of iteration
             if (policy == NGS_POLICY_RANDOM) {
               if (cw == 0) {
                 // ---- control, random policy: counts -> seeded pick -> bind ----
@@ -1183,9 +1194,9 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                     __syncwarp();
                 }
                 if (lane == 0) {
-                    s_dirty = -1;
-                    s_fresh = 0;
-                    s_fresh_ok = 0;
+                    s_dirty[nx] = -1;
+                    s_fresh[nx] = 0;
+                    s_fresh_ok[nx] = 0;
                 }
                 if (p + 2 < bp.P)  // stage the demand the workers will need next
                     for (uint32_t i = lane; i < sizeof(SortedDemand) / 4; i += 32)
@@ -1297,9 +1308,9 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                     bool ok = false;
                     const uint64_t fk = fresh_key_of_row(S, (uint32_t)br, T.first + row0 + (uint32_t)br, dem_next, g, gbase, &ok);
                     if (lane == 0) {
-                        s_dirty = br;
-                        s_fresh = fk;
-                        s_fresh_ok = ok ? 1 : 0;
+                        s_dirty[nx] = br;
+                        s_fresh[nx] = fk;
+                        s_fresh_ok[nx] = ok ? 1 : 0;
                     }
                 }
                 if (dead && lane == 0) s_abort = 1;
@@ -1314,6 +1325,10 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                 }
                 v = warp_max_u64(v);
                 v = fresh > v ? fresh : v;  // ... and let it compete with its fresh one
+#ifdef NGS_PHASE_TIMING
+                if (v == 12345) ph[5]++;
+                PHASE(7);  // (profiling) combine: per-warp best two -> this CTA's key
+#endif
                 const bool have = (v & KEY_FEASIBLE) != 0;
                 const uint32_t my_r = have ? key_node(v) - T.first - row0 : 0u;
                 GroupCommit cm;
@@ -1330,15 +1345,19 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                     // dependence), so a full counter implies every CTA's key is in the word
                     bool dead = false;
                     ulonglong2* xw = bp.xw + (size_t)p * bp.xw_stride;
+                    // the demand the workers will need next is fetched into registers now and stored to shared
+                    // memory after the exchange, so that its global-load latency hides behind the wait
+                    uint32_t stg0 = 0, stg1 = 0;
+                    const bool stage = p + 2 < bp.P;
+                    if (stage) {
+                        const uint32_t* src = reinterpret_cast<const uint32_t*>(&bp.dem[p + 2]);
+                        stg0 = __ldcg(src + lane);
+                        if (lane + 32 < sizeof(SortedDemand) / 4) stg1 = __ldcg(src + lane + 32);
+                    }
                     if (lane == 0) {
                         const unsigned long long old = atomicMax(&xw->x, (unsigned long long)v);
                         const unsigned long long one = 1ull + (old >> 63);  // bit 63 is never set: always 1
                         asm volatile("red.relaxed.gpu.global.add.u64 [%0], %1;" ::"l"(&xw->y), "l"(one) : "memory");
-                    } else if (p + 2 < bp.P) {
-                        // the idle lanes stage the demand the workers will need next (its global-load latency
-                        // hides behind this warp's wait for the exchange)
-                        for (uint32_t i = lane - 1; i < sizeof(SortedDemand) / 4; i += 31)
-                            reinterpret_cast<uint32_t*>(&s_dem[(p + 2) & 3])[i] = reinterpret_cast<const uint32_t*>(&bp.dem[p + 2])[i];
                     }
                     PHASE(2);
                     if (bp.world == 1) {
@@ -1362,11 +1381,16 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                         s_win = wait_valid(bp.gwin + p, bp.err, dead);
                     }
                     if (dead && lane == 0) s_abort = 1;
+                    if (stage) {
+                        uint32_t* dst = reinterpret_cast<uint32_t*>(&s_dem[(p + 2) & 3]);
+                        dst[lane] = stg0;
+                        if (lane + 32 < sizeof(SortedDemand) / 4) dst[lane + 32] = stg1;
+                    }
                 } else {
                     if (lane == 0) {
-                        s_dirty = -1;
-                        s_fresh = 0;
-                        s_fresh_ok = 0;
+                        s_dirty[nx] = -1;
+                        s_fresh[nx] = 0;
+                        s_fresh_ok[nx] = 0;
                     }
 #ifdef NGS_PHASE_TIMING
                     long long st[2] = {0, 0};
@@ -1399,9 +1423,9 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                         // ---- bind on the owner: stores only, everything was worked out during the exchange ----
                         publish_group(bp, S, my_r, row0 + my_r, dem, p, key_score(m), cm, lane);
                         if (lane == 0) {
-                            s_dirty = (int)my_r;
-                            s_fresh = cm.fresh;
-                            s_fresh_ok = cm.fresh_ok;
+                            s_dirty[nx] = (int)my_r;
+                            s_fresh[nx] = cm.fresh;
+                            s_fresh_ok[nx] = cm.fresh_ok;
                         }
                     }
                     PHASE(6);
@@ -1414,9 +1438,9 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     }
     if (blockIdx.x == 0 && tid == 0 && bp.status_out) *bp.status_out = *reinterpret_cast<volatile int32_t*>(bp.err);
 #ifdef NGS_PHASE_TIMING
-    if (tid == NW * 32 && bp.dbg)
+    if (tid == NWARP * 32 && bp.dbg)
         for (int i = 0; i < 8; i++) bp.dbg[blockIdx.x * 16 + i] = (unsigned long long)ph[i];
-    if (tid == NW * 32 + 32 && bp.dbg)
+    if (tid == NWARP * 32 + 32 && bp.dbg)
         for (int i = 0; i < 8; i++) bp.dbg[blockIdx.x * 16 + 8 + i] = (unsigned long long)ph[i];
 #endif
 }
@@ -1594,6 +1618,18 @@ int ensure_batch(ngs_dealer* h) {
     return NGS_OK;
 }
 
+// Block size of k_schedule: two control warps on top of enough warps that, after leaving idle the
+// ones sharing control warp 0's scheduler, one worker thread per row remains (at most 32 warps).
+uint32_t schedule_block_size(uint32_t rpb) {
+    const uint32_t need = (rpb + 31) / 32;  // worker warps wanted
+    for (uint32_t nw = 1; nw <= 30; nw++) {
+        const uint32_t csm = nw & 3u;
+        const uint32_t workers = nw - ((nw + 3u - csm) >> 2);
+        if (workers >= need) return (nw + 2) * 32;
+    }
+    return 1024;
+}
+
 // launch K6 for one chunk of <= BATCH_CHUNK pods whose inputs are in device memory
 int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const int32_t* d_ncont, int max_c, const int32_t* d_policy,
                     const LoadParams& lp, uint64_t seed_seq, int32_t* d_node, int32_t* d_score, int32_t* d_gidx,
@@ -1604,8 +1640,7 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     if (grid < 1) grid = 1;
     if (grid > (uint32_t)h->num_sms) grid = (uint32_t)h->num_sms;
     const uint32_t rpb = (N + grid - 1) / grid;
-    uint32_t block = ((rpb + 31) / 32) * 32 + 64;  // one worker thread per row (up to 960) + two control warps
-    if (block > 1024) block = 1024;
+    const uint32_t block = schedule_block_size(rpb);
     const size_t smem = (size_t)rpb * 32 + (size_t)((rpb + 31) / 32) * 8 + 16;  // rows + two feasbits buffers
     if (smem > (size_t)h->smem_optin)
         return fail(h, NGS_ERR_UNSUPPORTED, "%u rows per SM need %zu B shared memory (> %d): shard the cluster over more GPUs", rpb, smem, h->smem_optin);
@@ -2273,8 +2308,7 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     if (grid > (uint32_t)dv->num_sms) grid = (uint32_t)dv->num_sms;
     if (grid > NGS_NOALLOC_MAX_CTAS) return NGS_ERR_NOALLOC_LIMIT;  // the per-CTA slots would not fit
     const uint32_t rpb = (N + grid - 1) / grid;
-    uint32_t block = ((rpb + 31) / 32) * 32 + 64;
-    if (block > 1024) block = 1024;
+    const uint32_t block = schedule_block_size(rpb);
     const size_t smem = (size_t)rpb * 32 + (size_t)((rpb + 31) / 32) * 8 + 16;
     if (smem > (size_t)dv->smem_optin) return NGS_ERR_UNSUPPORTED;
 

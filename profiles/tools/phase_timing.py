@@ -46,7 +46,7 @@ grid = C.c_uint32(0)
 assert lib.ngs_debug_phases(d._h, buf.ctypes.data_as(C.c_void_p), C.byref(grid)) == 0
 g = grid.value
 a = buf[: 16 * g].reshape(g, 16).astype(np.float64) / P
-names = ["cw0: exact plan only / workers: filter", "barrier (pod p settled)", "cw0: post-bind stats / cw1: combine+atomicMax+bump", "-", "cw0: whole plan_group (incl. the two above) / cw1: exchange wait", "pair barrier", "publish", "-"]
+names = ["cw0: exact plan only", "barrier (pod p settled)", "cw0: post-bind stats / cw1: atomicMax+bump", "control: iteration start -> pair barrier #2", "cw0: plan_group total / cw1: exchange wait", "pair barrier #1", "publish", "control: combine (best two per warp -> key)"]
 print(f"{name}: {cfg['nodes']} nodes, {P} pods, grid {g}; cycles per pod (min / median / max over CTAs)")
 for who, off in (("control warp 0 (plan, bind)", 0), ("control warp 1 (exchange)", 8)):
     print(who)
