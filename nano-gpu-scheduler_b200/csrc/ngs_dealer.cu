@@ -1481,7 +1481,6 @@ struct ngs_dealer {
     size_t pod_rec_bytes = 0;
     int32_t* d_pod_in_dev = nullptr;       // device aliases of the mapped staging buffers
     int32_t* d_pod_out_dev = nullptr;
-    int max_smem_set = 0;                  // largest dynamic shared memory size set on k_schedule so far
     int32_t* h_pod_in = nullptr;   // pinned mirrors
     int32_t* h_pod_out = nullptr;
     int32_t* d_err = nullptr;
@@ -1642,11 +1641,24 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     const uint32_t rpb = (N + grid - 1) / grid;
     const uint32_t block = schedule_block_size(rpb);
     const size_t smem = (size_t)rpb * 32 + (size_t)((rpb + 31) / 32) * 8 + 16;  // rows + two feasbits buffers
-    if (smem > (size_t)h->smem_optin)
+    if (smem + 2048 > (size_t)h->smem_optin)  // (2 KB: the kernel's static shared memory)
         return fail(h, NGS_ERR_UNSUPPORTED, "%u rows per SM need %zu B shared memory (> %d): shard the cluster over more GPUs", rpb, smem, h->smem_optin);
-    if ((int)smem > h->max_smem_set) {  // the attribute is an upper bound: raise it only when needed
-        CU(h, cudaFuncSetAttribute(k_schedule, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        h->max_smem_set = (int)smem;
+    {
+        // the attribute is a per-device upper bound shared by every handle: allow the device maximum, once
+        static bool s_done[64] = {false};
+        static pthread_mutex_t s_mu = PTHREAD_MUTEX_INITIALIZER;
+        const int dev = h->device & 63;
+        pthread_mutex_lock(&s_mu);
+        cudaError_t e = cudaSuccess;
+        if (!s_done[dev]) {
+            cudaFuncAttributes fa;
+            e = cudaFuncGetAttributes(&fa, k_schedule);  // the opt-in limit covers static + dynamic shared memory
+            if (e == cudaSuccess)
+                e = cudaFuncSetAttribute(k_schedule, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem_optin - (int)fa.sharedSizeBytes);
+            s_done[dev] = e == cudaSuccess;
+        }
+        pthread_mutex_unlock(&s_mu);
+        CU(h, e);
     }
     k_prep_demands<<<(P + 127) / 128, 128, 0, h->stream>>>(d_percent, d_ncont, max_c, d_policy, P, h->d_dem, h->d_err);
     CU(h, cudaGetLastError());
@@ -2310,7 +2322,7 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     const uint32_t rpb = (N + grid - 1) / grid;
     const uint32_t block = schedule_block_size(rpb);
     const size_t smem = (size_t)rpb * 32 + (size_t)((rpb + 31) / 32) * 8 + 16;
-    if (smem > (size_t)dv->smem_optin) return NGS_ERR_UNSUPPORTED;
+    if (smem + 2048 > (size_t)dv->smem_optin) return NGS_ERR_UNSUPPORTED;
 
     unsigned char* sc = dv->scratch;
     SortedDemand* dem = reinterpret_cast<SortedDemand*>(sc + NA_DEM_OFF);
@@ -2325,7 +2337,13 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
         cudaMemsetAsync(done, 0, sizeof(uint32_t) * (size_t)n_pods, st) != cudaSuccess ||
         cudaMemsetAsync(err, 0, sizeof(int32_t), st) != cudaSuccess)
         return NGS_ERR_CUDA;
-    if (cudaFuncSetAttribute(k_schedule, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return NGS_ERR_CUDA;
+    // (an upper bound per device: asking for the device maximum once keeps it valid for every later launch, also of handles)
+    {
+        cudaFuncAttributes fa;
+        if (cudaFuncGetAttributes(&fa, k_schedule) != cudaSuccess ||
+            cudaFuncSetAttribute(k_schedule, cudaFuncAttributeMaxDynamicSharedMemorySize, dv->smem_optin - (int)fa.sharedSizeBytes) != cudaSuccess)
+            return NGS_ERR_CUDA;
+    }
     k_prep_demands<<<(n_pods + 127) / 128, 128, 0, st>>>(d_percent, d_n_containers, max_c, d_policy, n_pods, dem, err);
     if (cudaGetLastError() != cudaSuccess) return NGS_ERR_CUDA;
 

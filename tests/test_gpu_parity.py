@@ -562,3 +562,24 @@ def test_assume_dev_outputs_stay_on_device(ngs):
         # load scheduling off: the scan leaves the plan cache alone, so Score evaluates afresh and agrees
         d.assume_dev([30], 0, feas.data_ptr(), score.data_ptr())
         assert np.array_equal(d.score([30], 0), oc.assume([30], 0)["score"])
+
+
+def test_two_handles_of_different_size_share_the_device(ngs):
+    """a small handle must not shrink what a big one is allowed (the kernel's shared-memory limit is per device)"""
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    big_n, small_n = 400_000, 300
+    gc_b, fr_b = wl.make_cluster(big_n, 0.5, 71)
+    gc_s, fr_s = wl.make_cluster(small_n, 0.5, 72)
+    pc, nc = wl.make_pods(40, 1, 3, 0, 12, 73)
+    with ngs.GpuDealer(big_n, device=0) as big, ngs.GpuDealer(small_n, device=0) as small:
+        big.snapshot_load(gc_b, fr_b)
+        small.snapshot_load(gc_s, fr_s)
+        n1, _, _ = big.schedule_batch(pc, nc, 0)
+        oc = o.OracleCluster(small_n)
+        oc.load_snapshot(gc_s, fr_s)
+        n2, s2, g2 = small.schedule_batch(pc, nc, 1)
+        on, os_, og = oc.schedule_batch(pc, nc, 1)
+        assert np.array_equal(n2, on) and np.array_equal(s2, os_) and np.array_equal(g2, og)
+        n3, _, _ = big.schedule_batch(pc, nc, 0)  # still launches with its large shared-memory footprint
+        assert (n1 >= 0).all() and (n3 >= 0).all()
