@@ -43,7 +43,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="C3", choices=["C2", "C3", "C4"])
+    ap.add_argument("--workload", default="C3", choices=["C2", "C3", "C4", "C5"])
     ap.add_argument("--pods-per-step", type=int, default=2048)
     ap.add_argument("--nodes", type=int, default=0, help="override nodes per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -410,10 +410,88 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+def run_c5(args):
+    """BASELINE configs[4]: mixed-policy churn on 50k nodes through the host API — every step schedules
+    60 % of its 2048 operations (policy cycling random / binpack / spread per pod, seeded replay), releases
+    35 % (random live pods, one ngs_release_batch call) and forgets 5 % (host bookkeeping only,
+    dealer.go:311-319).  node-evals = scheduled pods x nodes; everything is timed end to end on the host."""
+    import torch
+
+    import nano_gpu_scheduler_b200 as ngs
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device")
+    cfg = workload_spec("C5", args.nodes)
+    n, ops = cfg["nodes"], args.pods_per_step
+    n_sched, n_rel = int(ops * 0.60), int(ops * 0.35)
+    steps_total = args.warmup + args.steps
+    gcount, free = wl.make_cluster(n, cfg["p_used"], cfg["seed"])
+    pc, nc = wl.make_pods(steps_total * n_sched, cfg["c"][0], cfg["c"][1], cfg["pct"][0], cfg["pct"][1], cfg["seed"], max_c=MAX_C)
+    policy = ((np.arange(len(pc)) % 3 + 2) % 3).astype(np.int32)  # random, binpack, spread, ...
+    rng = np.random.default_rng(cfg["seed"])
+    d = ngs.GpuDealer(n, device=0)
+    d.snapshot_load(gcount, free)
+    live_node, live_gidx, live_pc, live_nc = [], [], [], []
+    sampler = ClockSampler(0)
+    times, launches0 = [], 0
+    for s in range(steps_total):
+        if s == args.warmup:
+            launches0 = d.stats()["kernel_launches"]
+            sampler.start()
+        lo = s * n_sched
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        node, score, gidx = d.schedule_batch(pc[lo:lo + n_sched], nc[lo:lo + n_sched], policy[lo:lo + n_sched], seed=cfg["seed"], seq0=lo)
+        ok = node >= 0
+        live_node.extend(node[ok].tolist())
+        live_gidx.extend(gidx[ok])
+        live_pc.extend(pc[lo:lo + n_sched][ok])
+        live_nc.extend(nc[lo:lo + n_sched][ok].tolist())
+        k = min(n_rel, len(live_node))
+        if k:
+            pick = rng.choice(len(live_node), size=k, replace=False)
+            rc, st = d.release_batch(np.array([live_node[i] for i in pick], dtype=np.uint32), np.stack([live_gidx[i] for i in pick]),
+                                     np.stack([live_pc[i] for i in pick]), np.array([live_nc[i] for i in pick], dtype=np.int32))
+            assert rc == 0, rc
+            keep = np.ones(len(live_node), dtype=bool)
+            keep[pick] = False
+            live_node = [x for x, m in zip(live_node, keep) if m]
+            live_gidx = [x for x, m in zip(live_gidx, keep) if m]
+            live_pc = [x for x, m in zip(live_pc, keep) if m]
+            live_nc = [x for x, m in zip(live_nc, keep) if m]
+        dt = time.perf_counter() - t0
+        if s >= args.warmup:
+            times.append(dt)
+    sampler.stop()
+    launches = d.stats()["kernel_launches"] - launches0
+    value = n_sched * n * len(times) / sum(times)
+    peak, peak_src = measured_peak()
+    achieved = value * BYTES_PER_EVAL[False] / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "int32+f64", "data": "synthetic",
+        "config": {"workload": f"C5: {n}-node x 8-GPU cluster, mixed-policy churn (random/binpack/spread per pod), {n_sched} schedules + "
+                               f"{n_rel} releases + {ops - n_sched - n_rel} forgets per step, host API end to end (Python bookkeeping included)",
+                   "nodes_per_gpu": n, "pods_per_step": n_sched},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": int(n_sched * (MAX_C + 2) * 4 + n_rel * (2 * MAX_C + 2) * 4),
+                "d2h_bytes_per_step": int(n_sched * (MAX_C + 2) * 4 + n_rel * 4)},
+        "gpu_launches": int(launches), "clocks": sampler.summary(),
+        "roofline": {"bound": "hbm", "kernel": "k_schedule", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "peak_source": peak_src, "algorithmic_bytes_per_eval": BYTES_PER_EVAL[False], "traffic": None,
+                     "note": "host-timed end to end, not a kernel-only figure"},
+    }
+    d.close()
+    print(json.dumps(line), flush=True)
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "C5":
+        run_c5(args)
     else:
         run_b200(args)
 

@@ -112,6 +112,14 @@ int ngs_snapshot_read(ngs_dealer *h, uint32_t first, uint32_t n, uint8_t *gpu_co
  * allocate.go:120-131) via NodeInfo.Allocate/Release (node.go:86-94).  Drops the node's cached plan. */
 int ngs_node_apply(ngs_dealer *h, uint32_t idx, const int32_t *gpu_idx, const int32_t *percent, int n_containers, int sign);
 
+/* DealerImpl.Release for n finished pods in one call (dealer.go:230-255 -> node.go:91-94 ->
+ * allocate.go:120-131; the informer path pkg/controller/controller.go:210-243 handles them one by
+ * one).  node[n], gpu_idx[n][max_c], percent[n][max_c], n_containers[n]; status_out[n] (nullable)
+ * receives each pod's status.  Releases only add and additions commute, so the resulting snapshot
+ * equals releasing the pods one after the other.  Returns the first non-OK pod status, if any. */
+int ngs_release_batch(ngs_dealer *h, uint32_t n, const uint32_t *node, const int32_t *gpu_idx, const int32_t *percent,
+                      const int32_t *n_containers, int max_c, int32_t *status_out);
+
 /* ---- load-usage tables ---- */
 /* AddCoreUsage / AddMemoryUsage (nodeusage.go:58-68): fresh empty per-card map for the node */
 int ngs_load_add_node(ngs_dealer *h, uint32_t idx, int metric);

@@ -24,7 +24,7 @@ METRIC_CORE, METRIC_MEMORY = 0, 1
 # every symbol include/ngs_dealer.h declares (tests check the library exports each one)
 SYMBOLS = [
     "ngs_abi_version", "ngs_strerror", "ngs_last_error", "ngs_create", "ngs_destroy", "ngs_stream", "ngs_sync",
-    "ngs_stats", "ngs_node_upsert", "ngs_snapshot_load", "ngs_snapshot_read", "ngs_node_apply", "ngs_load_add_node",
+    "ngs_stats", "ngs_node_upsert", "ngs_snapshot_load", "ngs_snapshot_read", "ngs_node_apply", "ngs_release_batch", "ngs_load_add_node",
     "ngs_load_update", "ngs_load_update_bulk", "ngs_parse_usage", "ngs_parse_update_time", "ngs_assume", "ngs_assume_dev", "ngs_score",
     "ngs_bind", "ngs_schedule_batch", "ngs_schedule_batch_dev", "ngs_xchg_export", "ngs_xchg_attach",
     "ngs_schedule_batch_noalloc",
@@ -95,6 +95,7 @@ def load():
     L.ngs_snapshot_load.argtypes = [vp, u32, u32, vp, vp, vp]
     L.ngs_snapshot_read.argtypes = [vp, u32, u32, vp, vp, vp]
     L.ngs_node_apply.argtypes = [vp, u32, vp, vp, ci, ci]
+    L.ngs_release_batch.argtypes = [vp, u32, vp, vp, vp, vp, ci, vp]
     L.ngs_load_add_node.argtypes = [vp, u32, ci]
     L.ngs_load_update.argtypes = [vp, u32, ci, ci, dbl, ci, i64, ci]
     L.ngs_load_update_bulk.argtypes = [vp, ci, u32, u32, vp, vp, vp, vp]

@@ -500,6 +500,46 @@ __global__ void k_apply(Tables T, uint32_t gidx, PodDemand pd, const int32_t* __
     *status = rc;
 }
 
+// K3, batched: GPUs.Release (allocate.go:120-131) for many finished pods at once (the informer's
+// completion path, pkg/controller/controller.go:210-243 -> dealer.go:230-255).  Releases only add,
+// and additions commute, so one thread per pod with atomic adds gives the same table as releasing
+// the pods one after the other.  Per pod: stops at the first GPU index >= G, as the reference does
+// (earlier containers stay released), and reports NGS_ERR_APPLY; unknown node: NGS_ERR_UNKNOWN_NODE.
+__global__ void k_release_batch(Tables T, uint32_t n, const uint32_t* __restrict__ node, const int32_t* __restrict__ gpu_idx,
+                                const int32_t* __restrict__ percent, const int32_t* __restrict__ ncont, int max_c,
+                                int32_t* __restrict__ status) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t gidx = node[i], row = gidx - T.first;
+    int rc = NGS_OK;
+    if (gidx < T.first || row >= T.n || T.gcount[row] == 0) {
+        rc = NGS_ERR_UNKNOWN_NODE;
+    } else {
+        const int G = T.gcount[row];
+        T.tag[row] = 0;  // node.go:92: cleanPlan
+        const int C = min(max(ncont[i], 0), max_c);
+        for (int k = 0; k < C; k++) {
+            const int gi = gpu_idx[(size_t)i * max_c + k], pc = percent[(size_t)i * max_c + k];
+            if (gi < 0) continue;
+            if (gi >= G) {
+                rc = NGS_ERR_APPLY;
+                break;
+            }
+            if (pc < 0 || pc > NGS_MAX_FREE) {
+                rc = NGS_ERR_INVALID;
+                break;
+            }
+            const int old = atomicAdd(&T.free[(size_t)row * 8 + gi], pc);
+            if (old + pc > NGS_MAX_FREE) {  // keep cells inside what the kernels can hold
+                atomicSub(&T.free[(size_t)row * 8 + gi], pc);
+                rc = NGS_ERR_RANGE;
+                break;
+            }
+        }
+    }
+    if (status) status[i] = rc;
+}
+
 // NewNodeInfo (node.go:25-42)
 __global__ void k_upsert(Tables T, uint32_t row, int G) {
     if (threadIdx.x != 0) return;
@@ -1485,6 +1525,8 @@ struct ngs_dealer {
     int32_t* h_pod_out = nullptr;
     int32_t* d_err = nullptr;
     int32_t* h_err = nullptr;
+    int32_t* d_rel = nullptr;  // scratch of ngs_release_batch
+    size_t rel_cap = 0;
     // cross-GPU exchange (K5)
     int world = 1, rank = 0;
     unsigned long long* d_xslots = nullptr;               // own buffer: [2 parities][BATCH_CHUNK][NGS_MAX_RANKS]
@@ -1831,7 +1873,7 @@ int ngs_destroy(ngs_dealer* h) {
     cudaFree(h->d_err); cudaFreeHost(h->h_err);
     for (int r = 0; r < NGS_MAX_RANKS; r++)
         if (h->peer_xslots[r] && r != h->rank) cudaIpcCloseMemHandle(h->peer_xslots[r]);
-    cudaFree(h->d_xslots); cudaFree(h->d_gwin);
+    cudaFree(h->d_xslots); cudaFree(h->d_gwin); cudaFree(h->d_rel);
     cudaFree(h->d_dbg);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -1937,6 +1979,47 @@ int ngs_node_apply(ngs_dealer* h, uint32_t idx, const int32_t* gpu_idx, const in
     h->stats.kernel_launches++;
     rc = h->h_small[32];
     if (rc) return fail(h, rc, "apply on node %u: %s", idx, ngs_strerror(rc));
+    return NGS_OK;
+}
+
+int ngs_release_batch(ngs_dealer* h, uint32_t n, const uint32_t* node, const int32_t* gpu_idx, const int32_t* percent,
+                      const int32_t* n_containers, int max_c, int32_t* status_out) {
+    if (!h || (n > 0 && (!node || !gpu_idx || !percent || !n_containers))) return NGS_ERR_INVALID;
+    if (max_c < 1 || max_c > NGS_MAX_CONTAINERS) return fail(h, NGS_ERR_UNSUPPORTED, "max_c %d outside [1, NGS_MAX_CONTAINERS]", max_c);
+    if (n == 0) return NGS_OK;
+    CU(h, cudaSetDevice(h->device));
+    const size_t cells = (size_t)n * max_c;
+    const size_t words = 3 * (size_t)n + 2 * cells;  // node | ncont | status | gpu_idx | percent
+    if (words > h->rel_cap) {
+        cudaFree(h->d_rel);
+        h->d_rel = nullptr;
+        h->rel_cap = 0;
+        CU(h, cudaMalloc(&h->d_rel, words * 4));
+        h->rel_cap = words;
+    }
+    uint32_t* d_node = reinterpret_cast<uint32_t*>(h->d_rel);
+    int32_t* d_nc = h->d_rel + n;
+    int32_t* d_st = h->d_rel + 2 * (size_t)n;
+    int32_t* d_gi = h->d_rel + 3 * (size_t)n;
+    int32_t* d_pc = d_gi + cells;
+    CU(h, cudaMemcpyAsync(d_node, node, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(d_nc, n_containers, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(d_gi, gpu_idx, cells * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(d_pc, percent, cells * 4, cudaMemcpyHostToDevice, h->stream));
+    k_release_batch<<<(n + 127) / 128, 128, 0, h->stream>>>(h->T, n, d_node, d_gi, d_pc, d_nc, max_c, d_st);
+    CU(h, cudaGetLastError());
+    std::vector<int32_t> st(n);
+    CU(h, cudaMemcpyAsync(st.data(), d_st, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    h->stats.kernel_launches++;
+    h->stats.h2d_bytes += (2 * (size_t)n + 2 * cells) * 4;
+    h->stats.d2h_bytes += (size_t)n * 4;
+    int first_bad = NGS_OK;
+    for (uint32_t i = 0; i < n; i++) {
+        if (status_out) status_out[i] = st[i];
+        if (st[i] != NGS_OK && first_bad == NGS_OK) first_bad = st[i];
+    }
+    if (first_bad != NGS_OK) return fail(h, first_bad, "release batch: at least one pod failed (%s); see the per-pod status", ngs_strerror(first_bad));
     return NGS_OK;
 }
 

@@ -112,6 +112,18 @@ class GpuDealer:
         pc = np.ascontiguousarray(percent, dtype=np.int32)
         return self._lib.ngs_node_apply(self._h, idx, _p(gi), _p(pc), len(pc), sign)
 
+    def release_batch(self, node, gpu_idx, percent, n_containers):
+        """GPUs.Release for many pods at once -> (status of the call, per-pod status)"""
+        nd = np.ascontiguousarray(node, dtype=np.uint32)
+        gi = np.ascontiguousarray(gpu_idx, dtype=np.int32)
+        pc = np.ascontiguousarray(percent, dtype=np.int32)
+        nc = np.ascontiguousarray(n_containers, dtype=np.int32)
+        n = len(nd)
+        max_c = gi.shape[1] if gi.ndim == 2 else 1
+        st = np.zeros(max(n, 1), dtype=np.int32)
+        rc = self._lib.ngs_release_batch(self._h, n, _p(nd), _p(gi), _p(pc), _p(nc), max_c, _p(st))
+        return rc, st[:n]
+
     # -- load tables ------------------------------------------------------------------------
     def load_add_node(self, idx, metric):
         self._check(self._lib.ngs_load_add_node(self._h, idx, metric))

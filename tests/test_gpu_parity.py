@@ -583,3 +583,33 @@ def test_two_handles_of_different_size_share_the_device(ngs):
         assert np.array_equal(n2, on) and np.array_equal(s2, os_) and np.array_equal(g2, og)
         n3, _, _ = big.schedule_batch(pc, nc, 0)  # still launches with its large shared-memory footprint
         assert (n1 >= 0).all() and (n3 >= 0).all()
+
+
+def test_release_batch_equals_one_by_one(ngs):
+    """configs[4] shape at scale: schedule a mixed-policy stream, then give a random half back in ONE call"""
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    n, P = 20_000, 3000
+    oc, d, _, free0 = make_pair(ngs, n, 0.5, 0xC5)
+    pc, nc = wl.make_pods(P, 1, 3, 1, 12, 0xC5)
+    pol = (np.arange(P) % 3).astype(np.int32)
+    rng = np.random.default_rng(0xC5)
+    with d:
+        node, score, gidx = d.schedule_batch(pc, nc, pol, seed=5)
+        onode, oscore, ogidx = oc.schedule_batch(pc, nc, pol, seed=5)
+        assert np.array_equal(node, onode) and np.array_equal(gidx, ogidx)
+        placed = np.flatnonzero(node >= 0)
+        pick = rng.permutation(placed)[: len(placed) // 2]
+        rc, st = d.release_batch(node[pick].astype(np.uint32), gidx[pick], pc[pick], nc[pick])
+        assert rc == ngs.OK and (st == 0).all()
+        for p in pick:
+            assert oc.node_apply(int(node[p]), gidx[p, : nc[p]], pc[p, : nc[p]], -1) == 0
+        assert_same_snapshot(oc, d)
+        # per-pod error reporting: an index beyond the GPU count, an unknown node
+        bad_node = np.array([3, 3, n + 7], dtype=np.uint32)
+        bad_idx = np.array([[0, 9], [1, -1], [0, 0]], dtype=np.int32)
+        bad_pc = np.array([[5, 5], [5, 0], [5, 5]], dtype=np.int32)
+        rc, st = d.release_batch(bad_node, bad_idx, bad_pc, [2, 2, 2])
+        assert rc != ngs.OK and st.tolist() == [ngs.ERR_APPLY, ngs.OK, ngs.ERR_UNKNOWN_NODE]
+        assert oc.node_apply(3, [0, 9], [5, 5], -1) != 0 and oc.node_apply(3, [1, -1], [5, 0], -1) == 0
+        assert_same_snapshot(oc, d)  # the first pod's container 0 stays released, as in the reference
