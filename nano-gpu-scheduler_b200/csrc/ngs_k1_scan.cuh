@@ -1,0 +1,218 @@
+// ngs_k1_scan.cuh — K1, the filter / prioritize scans: k_assume (one thread per candidate, direct
+// 256-bit loads) and k_scan_tma (all rows, tiles staged by TMA bulk copies).
+// Included by ngs_dealer.cu inside its anonymous namespace, after ngs_rows.cuh.
+#pragma once
+
+enum { MODE_ASSUME = 0, MODE_SCORE = 1 };
+
+// K1.  DealerImpl.Assume / DealerImpl.Score fan-out (dealer.go:109-134, 138-153): one thread
+// per candidate.  MODE_ASSUME recomputes every candidate (cleanPlan + Assume, dealer.go:123-124);
+// MODE_SCORE serves NodeInfo.Score (node.go:59-68) from the per-node cache when it holds a
+// plan for this demand generation.
+#ifndef NGS_K1_BLOCKS
+#define NGS_K1_BLOCKS 4  // resident 256-thread blocks per SM for the feasibility/score scan
+#endif
+template <bool PLAN>
+__global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables T, const uint32_t* __restrict__ idx, uint32_t n, PodDemand pd, LoadParams lp,
+                                                int mode, uint32_t gen, uint8_t* __restrict__ feasible,
+                                                int8_t* __restrict__ reason, int32_t* __restrict__ score,
+                                                int32_t* __restrict__ plan, int32_t* __restrict__ n_emitted) {
+    __shared__ SortedDemand dem;
+    __shared__ double s_pair[121];
+    if (threadIdx.x == 0) sort_demand(pd.percent, pd.n, pd.policy, &dem);
+    if (lp.enabled) fill_usage_pair_table(s_pair, threadIdx.x, blockDim.x);
+    __syncthreads();
+    const int C = pd.n;
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        const uint32_t gidx = idx ? idx[k] : T.first + k;
+        const uint32_t row = gidx - T.first;
+        RowEval ev;
+        ev.known = false;
+        ev.feasible = false;
+        ev.score = NGS_SCORE_MIN;
+        ev.emit = 0;
+        ev.n_emit = 0;
+        bool cached = false;
+        if (gidx >= T.first && row < T.n) {
+            if (mode == MODE_SCORE && T.tag[row] == gen && T.gcount[row] != 0) {
+                ev.known = ev.feasible = cached = true;
+                ev.score = T.cscore[row];
+            } else {
+                ev = eval_row_global<PLAN>(T, row, &dem, lp, true, s_pair);
+            }
+        }
+        const bool ok = ev.known && ev.feasible;
+        // The per-node plan cache only matters when load scheduling is on (the usage tables may move
+        // between filter and prioritize); without it a later Score / Bind re-derives the same values
+        // from the unchanged row, so the scan does not spend 8 bytes per node on the cache.
+        if (ev.known && !cached && lp.enabled) {
+            if (ok) {  // node.go:55
+                T.tag[row] = gen;
+                T.cscore[row] = ev.score;
+            } else if (mode == MODE_ASSUME) {
+                T.tag[row] = 0;  // dealer.go:123 cleared it, the failed Assume caches nothing
+            }
+        }
+        if (feasible) feasible[k] = ok ? 1 : 0;
+        if (reason) reason[k] = !ev.known ? NGS_REASON_UNKNOWN_NODE : (ok ? NGS_REASON_OK : NGS_REASON_INFEASIBLE);
+        if (score) score[k] = ok ? ev.score : NGS_SCORE_MIN;
+        if (PLAN) {
+            if (plan) {
+                int32_t* out = plan + (size_t)k * C;
+                if (ev.known) write_plan(out, &dem, dem.policy != NGS_POLICY_RANDOM, ok, ev.emit, ev.n_emit);
+                else for (int j = 0; j < C; j++) out[j] = INT32_MIN;
+            }
+            if (n_emitted) n_emitted[k] = ev.known ? ev.n_emit : 0;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1, streaming form: the same evaluation as k_assume for "all rows, no per-node plans", with the
+// row data staged through shared memory by the TMA engine (1-D bulk copies, cp.async.bulk +
+// mbarrier transaction counts) in a 2- or 3-stage ring of 256-row tiles, so that several tiles of every
+// table are in flight per CTA while the threads evaluate the tile that has landed.
+// ---------------------------------------------------------------------------------------------
+constexpr int SCAN_TILE = 256;
+#ifndef NGS_SCAN_STAGES_LOAD
+#define NGS_SCAN_STAGES_LOAD 2
+#endif
+#ifndef NGS_SCAN_STAGES_PLAIN
+#define NGS_SCAN_STAGES_PLAIN 3
+#endif
+#ifndef NGS_SCAN_BLOCKS_LOAD
+#define NGS_SCAN_BLOCKS_LOAD 3
+#endif
+constexpr uint32_t SCAN_FREE_BYTES = SCAN_TILE * 8 * 4;    // 8 KB
+constexpr uint32_t SCAN_GC_BYTES = SCAN_TILE;              // 256 B
+constexpr uint32_t SCAN_RL_BYTES = SCAN_TILE * 8;          // 2 KB   (pass without load scheduling)
+constexpr uint32_t SCAN_TENTHS_BYTES = SCAN_TILE * 8;      // 2 KB per metric (load-aware pass)
+constexpr uint32_t SCAN_TS_BYTES = SCAN_TILE * 8 * 4;      // 8 KB per metric (load-aware pass)
+template <bool LOAD>
+__host__ __device__ constexpr uint32_t scan_stage_bytes() {
+    return SCAN_FREE_BYTES + SCAN_GC_BYTES + (LOAD ? 2 * SCAN_TENTHS_BYTES + 2 * SCAN_TS_BYTES : SCAN_RL_BYTES);
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAIT_DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// TMA 1-D bulk copy global -> shared, completion counted in bytes on the mbarrier
+__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+template <bool LOAD>
+__global__ void __launch_bounds__(SCAN_TILE, LOAD ? NGS_SCAN_BLOCKS_LOAD : 4) k_scan_tma(Tables T, uint32_t n, PodDemand pd, LoadParams lp, uint32_t gen,
+                                                                        uint8_t* __restrict__ feasible, int8_t* __restrict__ reason,
+                                                                        int32_t* __restrict__ score) {
+    extern __shared__ __align__(128) unsigned char tiles[];
+    __shared__ SortedDemand dem;
+    __shared__ double s_pair[121];
+    constexpr int SCAN_STAGES = LOAD ? NGS_SCAN_STAGES_LOAD : NGS_SCAN_STAGES_PLAIN;
+    __shared__ __align__(8) uint64_t bars[SCAN_STAGES];
+    constexpr uint32_t STAGE = scan_stage_bytes<LOAD>();
+    const uint32_t tid = threadIdx.x;
+    const uint32_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    const bool want_rl = !LOAD && !T.rl_zero;
+
+    // one thread issues the copies of a tile: every table's 256-row slice is one contiguous range
+    auto issue = [&](uint32_t tile, uint32_t stage) {
+        unsigned char* base = tiles + (size_t)stage * STAGE;
+        const size_t row = (size_t)tile * SCAN_TILE;
+        uint32_t bytes = SCAN_FREE_BYTES + SCAN_GC_BYTES;
+        if (LOAD) bytes += 2 * SCAN_TENTHS_BYTES + 2 * SCAN_TS_BYTES;
+        else if (want_rl) bytes += SCAN_RL_BYTES;
+        mbar_expect_tx(&bars[stage], bytes);
+        tma_load_1d(base, T.free + row * 8, SCAN_FREE_BYTES, &bars[stage]);
+        tma_load_1d(base + SCAN_FREE_BYTES, T.gcount + row, SCAN_GC_BYTES, &bars[stage]);
+        unsigned char* q = base + SCAN_FREE_BYTES + SCAN_GC_BYTES;
+        if (LOAD) {
+#pragma unroll
+            for (int m = 0; m < 2; m++) {
+                const size_t off = ((size_t)m * T.nstride + row) * 8;
+                tma_load_1d(q + m * SCAN_TENTHS_BYTES, T.tenths + off, SCAN_TENTHS_BYTES, &bars[stage]);
+                tma_load_1d(q + 2 * SCAN_TENTHS_BYTES + m * SCAN_TS_BYTES, T.ts + off, SCAN_TS_BYTES, &bars[stage]);
+            }
+        } else if (want_rl) {
+            tma_load_1d(q, T.rl + row * 8, SCAN_RL_BYTES, &bars[stage]);
+        }
+    };
+
+    if (tid == 0) {
+        for (int st = 0; st < SCAN_STAGES; st++) mbar_init(&bars[st], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        sort_demand(pd.percent, pd.n, pd.policy, &dem);
+    }
+    if (LOAD) fill_usage_pair_table(s_pair, tid, blockDim.x);
+    __syncthreads();
+    if (tid == 0)
+        for (uint32_t i = 0; i < SCAN_STAGES; i++) {
+            const uint32_t tile = blockIdx.x + i * gridDim.x;
+            if (tile < ntiles) issue(tile, i);
+        }
+
+    uint32_t it = 0;
+    for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+        const uint32_t stage = it % SCAN_STAGES, parity = (it / SCAN_STAGES) & 1u;
+        mbar_wait(&bars[stage], parity);
+        const unsigned char* base = tiles + (size_t)stage * STAGE;
+        const uint32_t row = tile * SCAN_TILE + tid;
+        RowIn in;
+        {
+            const uint4 a = *reinterpret_cast<const uint4*>(base + (size_t)tid * 32);
+            const uint4 b = *reinterpret_cast<const uint4*>(base + (size_t)tid * 32 + 16);
+            in.v[0] = a.x; in.v[1] = a.y; in.v[2] = a.z; in.v[3] = a.w;
+            in.v[4] = b.x; in.v[5] = b.y; in.v[6] = b.z; in.v[7] = b.w;
+        }
+        in.G = base[SCAN_FREE_BYTES + tid];
+        in.r8 = make_uint2(0u, 0u);
+        const unsigned char* q = base + SCAN_FREE_BYTES + SCAN_GC_BYTES;
+        if (LOAD) {
+#pragma unroll
+            for (int m = 0; m < 2; m++) {
+                in.t8[m] = *reinterpret_cast<const uint2*>(q + m * SCAN_TENTHS_BYTES + (size_t)tid * 8);
+                const unsigned char* tsp = q + 2 * SCAN_TENTHS_BYTES + m * SCAN_TS_BYTES + (size_t)tid * 32;
+                const uint4 a = *reinterpret_cast<const uint4*>(tsp), b = *reinterpret_cast<const uint4*>(tsp + 16);
+                in.ts[m][0] = a.x; in.ts[m][1] = a.y; in.ts[m][2] = a.z; in.ts[m][3] = a.w;
+                in.ts[m][4] = b.x; in.ts[m][5] = b.y; in.ts[m][6] = b.z; in.ts[m][7] = b.w;
+            }
+        } else if (want_rl) {
+            in.r8 = *reinterpret_cast<const uint2*>(q + (size_t)tid * 8);
+        }
+        __syncthreads();  // the stage has been read by everyone: refill it with the tile 3 steps ahead
+        if (tid == 0) {
+            const uint32_t next = tile + SCAN_STAGES * gridDim.x;
+            if (next < ntiles) issue(next, stage);
+        }
+        if (row < n) {
+            const RowEval ev = eval_row_values<false>(T, row, in, &dem, lp, true, s_pair);
+            const bool ok = ev.known && ev.feasible;
+            if (ev.known && LOAD) {  // plan cache, as in k_assume (MODE_ASSUME)
+                T.tag[row] = ok ? gen : 0u;
+                if (ok) T.cscore[row] = ev.score;
+            }
+            if (feasible) feasible[row] = ok ? 1 : 0;
+            if (reason) reason[row] = !ev.known ? NGS_REASON_UNKNOWN_NODE : (ok ? NGS_REASON_OK : NGS_REASON_INFEASIBLE);
+            if (score) score[row] = ok ? ev.score : NGS_SCORE_MIN;
+        }
+    }
+}

@@ -1,0 +1,151 @@
+// ngs_k3_rows.cuh — K3 / K4, the single-row kernels: bind, apply, batched release, node upsert,
+// usage-table updates.  Included by ngs_dealer.cu inside its anonymous namespace.
+#pragma once
+
+struct BindResult {
+    int32_t status;
+    int32_t score;
+    int32_t gpu_idx[NGS_MAX_CONTAINERS];
+};
+
+// K3.  NodeInfo.Bind (node.go:70-84) for one row: cached or fresh plan, GPUs.Allocate, cleanPlan.
+__global__ void k_bind(Tables T, uint32_t gidx, PodDemand pd, LoadParams lp, uint32_t gen, BindResult* res) {
+    __shared__ SortedDemand dem;
+    if (threadIdx.x != 0) return;
+    sort_demand(pd.percent, pd.n, pd.policy, &dem);
+    const uint32_t row = gidx - T.first;
+    for (int j = 0; j < NGS_MAX_CONTAINERS; j++) res->gpu_idx[j] = INT32_MIN;
+    res->score = NGS_SCORE_MIN;
+    if (gidx < T.first || row >= T.n || T.gcount[row] == 0) {
+        res->status = NGS_ERR_UNKNOWN_NODE;
+        return;
+    }
+    const bool hit = T.tag[row] == gen;
+    RowEval ev = eval_row_global<true>(T, row, &dem, lp, !hit);
+    if (!ev.feasible) {  // node.go:74-76
+        res->status = NGS_ERR_INFEASIBLE;
+        return;
+    }
+    int32_t planv[NGS_MAX_CONTAINERS];
+    write_plan(planv, &dem, dem.policy != NGS_POLICY_RANDOM, true, ev.emit, ev.n_emit);
+    int32_t* f = T.free + (size_t)row * 8;
+    for (int k = 0; k < pd.n; k++) {  // GPUs.Allocate (allocate.go:102-118); the plan fits by construction
+        res->gpu_idx[k] = planv[k];
+        if (planv[k] >= 0) f[planv[k]] -= pd.percent[k];
+    }
+    res->score = hit ? T.cscore[row] : ev.score;
+    T.tag[row] = 0;  // node.go:82
+    res->status = NGS_OK;
+}
+
+// K3.  GPUs.Allocate (sign>0, all-or-nothing) / GPUs.Release (sign<0) with a caller-given plan.
+__global__ void k_apply(Tables T, uint32_t gidx, PodDemand pd, const int32_t* __restrict__ gpu_idx_in, int sign, int32_t* status) {
+    if (threadIdx.x != 0) return;
+    const uint32_t row = gidx - T.first;
+    if (gidx < T.first || row >= T.n || T.gcount[row] == 0) {
+        *status = NGS_ERR_UNKNOWN_NODE;
+        return;
+    }
+    const int G = T.gcount[row];
+    int32_t* fp = T.free + (size_t)row * 8;
+    int f[8];
+    for (int g = 0; g < 8; g++) f[g] = fp[g];
+    T.tag[row] = 0;  // node.go:87,92: cleanPlan runs before the apply, whatever its outcome
+    int rc = NGS_OK;
+    if (sign > 0) {
+        for (int k = 0; k < pd.n; k++) {
+            const int gi = gpu_idx_in[k];
+            if (gi < 0) continue;  // allocate.go:105-107
+            if (gi >= G || f[gi] < pd.percent[k]) {  // allocate.go:108 (an index >= G panics in Go)
+                rc = NGS_ERR_APPLY;
+                break;
+            }
+            f[gi] -= pd.percent[k];
+        }
+        if (rc == NGS_OK)
+            for (int g = 0; g < 8; g++) fp[g] = f[g];
+    } else {
+        for (int k = 0; k < pd.n; k++) {
+            const int gi = gpu_idx_in[k];
+            if (gi < 0) continue;
+            if (gi >= G) {  // allocate.go:125-127: earlier containers stay released
+                rc = NGS_ERR_APPLY;
+                break;
+            }
+            if (f[gi] + pd.percent[k] > NGS_MAX_FREE) {
+                rc = NGS_ERR_RANGE;
+                break;
+            }
+            f[gi] += pd.percent[k];
+        }
+        if (rc != NGS_ERR_RANGE)
+            for (int g = 0; g < 8; g++) fp[g] = f[g];
+    }
+    *status = rc;
+}
+
+// K3, batched: GPUs.Release (allocate.go:120-131) for many finished pods at once (the informer's
+// completion path, pkg/controller/controller.go:210-243 -> dealer.go:230-255).  Releases only add,
+// and additions commute, so one thread per pod with atomic adds gives the same table as releasing
+// the pods one after the other.  Per pod: stops at the first GPU index >= G, as the reference does
+// (earlier containers stay released), and reports NGS_ERR_APPLY; unknown node: NGS_ERR_UNKNOWN_NODE.
+__global__ void k_release_batch(Tables T, uint32_t n, const uint32_t* __restrict__ node, const int32_t* __restrict__ gpu_idx,
+                                const int32_t* __restrict__ percent, const int32_t* __restrict__ ncont, int max_c,
+                                int32_t* __restrict__ status) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t gidx = node[i], row = gidx - T.first;
+    int rc = NGS_OK;
+    if (gidx < T.first || row >= T.n || T.gcount[row] == 0) {
+        rc = NGS_ERR_UNKNOWN_NODE;
+    } else {
+        const int G = T.gcount[row];
+        T.tag[row] = 0;  // node.go:92: cleanPlan
+        const int C = min(max(ncont[i], 0), max_c);
+        for (int k = 0; k < C; k++) {
+            const int gi = gpu_idx[(size_t)i * max_c + k], pc = percent[(size_t)i * max_c + k];
+            if (gi < 0) continue;
+            if (gi >= G) {
+                rc = NGS_ERR_APPLY;
+                break;
+            }
+            if (pc < 0 || pc > NGS_MAX_FREE) {
+                rc = NGS_ERR_INVALID;
+                break;
+            }
+            const int old = atomicAdd(&T.free[(size_t)row * 8 + gi], pc);
+            if (old + pc > NGS_MAX_FREE) {  // keep cells inside what the kernels can hold
+                atomicSub(&T.free[(size_t)row * 8 + gi], pc);
+                rc = NGS_ERR_RANGE;
+                break;
+            }
+        }
+    }
+    if (status) status[i] = rc;
+}
+
+// NewNodeInfo (node.go:25-42)
+__global__ void k_upsert(Tables T, uint32_t row, int G) {
+    if (threadIdx.x != 0) return;
+    T.gcount[row] = (uint8_t)G;
+    for (int g = 0; g < 8; g++) {
+        T.free[(size_t)row * 8 + g] = g < G ? 100 : 0;
+        T.rl[(size_t)row * 8 + g] = 0;
+    }
+    T.tag[row] = 0;
+}
+
+// K4.  Update{Core,Memory}Usage (nodeusage.go:70-80) on one cell / Add*Usage (nodeusage.go:58-68)
+__global__ void k_load_update(Tables T, uint32_t row, int metric, int card, uint8_t tenths, uint32_t ts) {
+    if (threadIdx.x != 0) return;
+    const size_t off = ((size_t)metric * T.nstride + row) * 8 + card;
+    T.tenths[off] = tenths;
+    T.ts[off] = ts;
+}
+__global__ void k_load_add_node(Tables T, uint32_t row, int metric) {
+    const size_t off = ((size_t)metric * T.nstride + row) * 8 + threadIdx.x;
+    if (threadIdx.x < 8) {
+        T.tenths[off] = 255;
+        T.ts[off] = 0;
+    }
+}
