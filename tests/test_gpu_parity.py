@@ -613,3 +613,47 @@ def test_release_batch_equals_one_by_one(ngs):
         assert rc != ngs.OK and st.tolist() == [ngs.ERR_APPLY, ngs.OK, ngs.ERR_UNKNOWN_NODE]
         assert oc.node_apply(3, [0, 9], [5, 5], -1) != 0 and oc.node_apply(3, [1, -1], [5, 0], -1) == 0
         assert_same_snapshot(oc, d)  # the first pod's container 0 stays released, as in the reference
+
+
+def test_random_policy_seeded_replay(ngs):
+    """the random policy (SURVEY a9'): same snapshot + same seed and sequence numbers -> the same picks; another
+    seed -> other picks; every pick is a node the SampleRater plan search accepts (feasibility-set membership)"""
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    n, P = 4000, 300
+    gcount, free = wl.make_cluster(n, 0.6, 0x5EED)
+    pc, nc = wl.make_pods(P, 1, 3, 1, 14, 0x5EED)
+    runs = []
+    for seed in (1234, 1234, 99):
+        with ngs.GpuDealer(n, device=0) as d:
+            d.snapshot_load(gcount, free)
+            runs.append(d.schedule_batch(pc, nc, ngs.POLICY_RANDOM, seed=seed, seq0=17))
+    assert all(np.array_equal(a, b) for a, b in zip(runs[0], runs[1]))
+    assert not np.array_equal(runs[0][0], runs[2][0])
+    # membership: replay the first picks on the oracle and check each against the feasible set of its moment
+    oc = o.OracleCluster(n)
+    oc.load_snapshot(gcount, free)
+    node, score, gidx = runs[0]
+    for p in range(40):
+        feas = oc.assume(pc[p, : nc[p]], o.POLICY_RANDOM)["feasible"]
+        if node[p] < 0:
+            assert feas.sum() == 0
+            continue
+        assert feas[node[p]] == 1 and score[p] == 100
+        want = o.splitmix64(1234 + 17 + p) % int(feas.sum())
+        assert node[p] == np.flatnonzero(feas)[want]
+        rc, gi, _ = oc.bind(int(node[p]), pc[p, : nc[p]], o.POLICY_RANDOM)
+        assert rc == 0 and np.array_equal(gi, gidx[p, : nc[p]])
+
+
+def test_stats_counters(ngs):
+    with ngs.GpuDealer(1000, device=0) as d:
+        d.snapshot_load(np.full(1000, 8, dtype=np.uint8))
+        s0 = d.stats()
+        d.assume([10], 0)
+        d.schedule_batch(np.full((5, 1), 10, dtype=np.int32), [1] * 5, 0)
+        s1 = d.stats()
+        assert s1["node_evals"] - s0["node_evals"] == 1000 + 5 * 1000
+        assert s1["pods_scheduled"] - s0["pods_scheduled"] == 5
+        assert s1["kernel_launches"] - s0["kernel_launches"] == 3
+        assert s1["d2h_bytes"] > s0["d2h_bytes"] and s1["h2d_bytes"] > s0["h2d_bytes"]
