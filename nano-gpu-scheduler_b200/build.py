@@ -38,19 +38,20 @@ HOST_TEST = os.path.join(HERE, "host", "test_dealer_host")
 
 
 def build_host(force: bool = False) -> str:
-    """C++ mirror of the reference's Dealer interface (host/dealer_host.cpp) and its test program"""
-    src = os.path.join(HOST_DIR, "dealer_host.cpp")
-    hdr = os.path.join(HOST_DIR, "dealer_host.h")
+    """C++ mirror of the reference's Dealer interface (host/dealer_host.cpp), the extender wire codec
+    (host/extender_codec.cpp) and their test program"""
+    srcs = [os.path.join(HOST_DIR, f) for f in ("dealer_host.cpp", "extender_codec.cpp", "extender_codec_c.cpp")]
+    hdrs = [os.path.join(HOST_DIR, f) for f in ("dealer_host.h", "extender_codec.h")]
     test_src = os.path.join(HERE, "..", "tests", "host", "test_dealer_host.cpp")
-    deps = [src, hdr, test_src, LIB]
+    deps = [*srcs, *hdrs, test_src, LIB]
     if force or not os.path.exists(HOST_TEST) or any(os.path.getmtime(d) > os.path.getmtime(HOST_TEST) for d in deps):
         cxx = shutil.which("g++") or "g++"
         common = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-I", os.path.join(HERE, "..", "include")]
-        res = subprocess.run([cxx, *common, "-shared", "-o", HOST_LIB, src, "-L", HERE, "-lngs_dealer", "-Wl,-rpath,$ORIGIN"],
+        res = subprocess.run([cxx, *common, "-shared", "-o", HOST_LIB, *srcs, "-L", HERE, "-lngs_dealer", "-Wl,-rpath,$ORIGIN"],
                              capture_output=True, text=True)
         if res.returncode != 0:
             raise RuntimeError("g++ (host mirror) failed:\n" + res.stdout + res.stderr)
-        res = subprocess.run([cxx, *common, "-o", HOST_TEST, test_src, src, "-L", HERE, "-lngs_dealer", "-Wl,-rpath,$ORIGIN/.."],
+        res = subprocess.run([cxx, *common, "-o", HOST_TEST, test_src, *srcs[:2], "-L", HERE, "-lngs_dealer", "-Wl,-rpath,$ORIGIN/.."],
                              capture_output=True, text=True)
         if res.returncode != 0:
             raise RuntimeError("g++ (host test) failed:\n" + res.stdout + res.stderr)

@@ -2,10 +2,13 @@
 // top of the C ABI; paths below are relative to /root/reference/pkg/dealer/.
 #include "dealer_host.h"
 
+#include <algorithm>
 #include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
+#include <unordered_map>
 
 namespace ngs_host {
 
@@ -86,6 +89,106 @@ Error getActiveDuration(const std::vector<Period>& list, const std::string& name
     return "error get activeDuration";
 }
 
+// NodeIndex
+uint64_t HashName(std::string_view s) {
+    // 8 bytes at a time, multiply-xorshift mixing (node names are short and share long prefixes)
+    const uint64_t k = 0x9E3779B97F4A7C15ull;
+    uint64_t h = 0xB2005EEDull ^ (s.size() * k);
+    const char* p = s.data();
+    size_t n = s.size();
+    while (n >= 8) {
+        uint64_t w;
+        memcpy(&w, p, 8);
+        h = (h ^ w) * k;
+        h ^= h >> 29;
+        p += 8;
+        n -= 8;
+    }
+    if (n) {
+        uint64_t w = 0;
+        memcpy(&w, p, n);
+        h = (h ^ w) * k;
+        h ^= h >> 29;
+    }
+    h *= 0xBF58476D1CE4E5B9ull;
+    h ^= h >> 32;
+    return h;
+}
+
+NodeIndex::NodeIndex() {
+    slots_.assign(1024, Slot{0, 0, 0, 0, 0});
+    mask_ = 1023;
+}
+
+void NodeIndex::grow() {
+    std::vector<Slot> old;
+    old.swap(slots_);
+    const size_t cap = old.size() * 2;
+    slots_.assign(cap, Slot{0, 0, 0, 0, 0});
+    mask_ = cap - 1;
+    for (const Slot& o : old) {
+        if (!o.used) continue;
+        size_t j = o.hash & mask_;
+        while (slots_[j].used) j = (j + 1) & mask_;
+        slots_[j] = o;
+    }
+}
+
+const uint32_t* NodeIndex::Find(std::string_view name) const {
+    const uint64_t h = HashName(name);
+    for (size_t j = h & mask_;; j = (j + 1) & mask_) {
+        const Slot& s = slots_[j];
+        if (!s.used) return nullptr;
+        if (s.hash == h && s.len == name.size() && memcmp(arena_.data() + s.off, name.data(), name.size()) == 0)
+            return s.row == 0xFFFFFFFFu ? nullptr : &s.row;  // 0xFFFFFFFF: a name whose row was withdrawn
+    }
+}
+
+void NodeIndex::FindMany(const std::string_view* names, size_t n, uint32_t* rows) const {
+    constexpr size_t B = 32;
+    uint64_t h[B];
+    for (size_t base = 0; base < n; base += B) {
+        const size_t m = n - base < B ? n - base : B;
+        for (size_t k = 0; k < m; k++) {
+            h[k] = HashName(names[base + k]);
+            __builtin_prefetch(&slots_[h[k] & mask_]);
+        }
+        for (size_t k = 0; k < m; k++) {  // the home slot almost always decides: fetch its name bytes too
+            const Slot& s = slots_[h[k] & mask_];
+            if (s.used && s.hash == h[k]) __builtin_prefetch(arena_.data() + s.off);
+        }
+        for (size_t k = 0; k < m; k++) {
+            const std::string_view name = names[base + k];
+            uint32_t row = 0xFFFFFFFFu;
+            for (size_t j = h[k] & mask_;; j = (j + 1) & mask_) {
+                const Slot& s = slots_[j];
+                if (!s.used) break;
+                if (s.hash == h[k] && s.len == name.size() && memcmp(arena_.data() + s.off, name.data(), name.size()) == 0) {
+                    row = s.row;
+                    break;
+                }
+            }
+            rows[base + k] = row;
+        }
+    }
+}
+
+void NodeIndex::Insert(std::string_view name, uint32_t row) {
+    if ((count_ + 1) * 2 > slots_.size()) grow();
+    const uint64_t h = HashName(name);
+    size_t j = h & mask_;
+    for (; slots_[j].used; j = (j + 1) & mask_) {
+        Slot& s = slots_[j];
+        if (s.hash == h && s.len == name.size() && memcmp(arena_.data() + s.off, name.data(), name.size()) == 0) {
+            s.row = row;
+            return;
+        }
+    }
+    slots_[j] = Slot{h, row, (uint32_t)name.size(), (uint32_t)arena_.size(), 1};
+    arena_.append(name.data(), name.size());
+    count_++;
+}
+
 // ---- Dealer -----------------------------------------------------------------------------------
 Dealer::Dealer(ClusterSource* src, RaterKind rater, uint32_t max_nodes, int device) : src_(src), rater_(rater) {
     int rc = ngs_create(&h_, device, max_nodes, 0, nullptr);
@@ -94,6 +197,27 @@ Dealer::Dealer(ClusterSource* src, RaterKind rater, uint32_t max_nodes, int devi
         if (init_error_.empty()) init_error_ = ngs_strerror(rc);
         if (h_) ngs_destroy(h_);
         h_ = nullptr;
+        return;
+    }
+    if (src_) {  // dealer.go:58-72: every node that already runs an assumed pod is built up front
+        // One list call serves every node here (the reference lists again per node, dealer.go:279): the
+        // pods are grouped by node and replay_assumed_pods reads the groups instead of asking the source.
+        const std::vector<Pod> pods = src_->ListAllAssumedPods();
+        std::unordered_map<std::string, std::vector<const Pod*>> by_node;
+        std::vector<const std::string*> nodes;
+        for (const Pod& p : pods) {
+            if (p.node_name.empty()) continue;
+            auto ins = by_node.try_emplace(p.node_name);
+            if (ins.second) nodes.push_back(&ins.first->first);
+            ins.first->second.push_back(&p);
+        }
+        if (!nodes.empty()) {
+            CandidateSet cs;
+            for (const std::string* s : nodes) cs.names.push_back(*s);
+            listed_ = &by_node;
+            Resolve(&cs);  // failures are only logged by the reference (dealer.go:68)
+            listed_ = nullptr;
+        }
     }
 }
 Dealer::~Dealer() {
@@ -124,28 +248,53 @@ bool Dealer::load_ctx(const PolicySpec& spec, bool isLoad, ngs_load_ctx* out) co
 }
 
 Error Dealer::getNodeInfo(const std::string& name, uint32_t* row) {  // dealer.go:271-301
-    auto it = index_.find(name);
-    if (it != index_.end()) {
-        *row = it->second;
+    if (const uint32_t* known = index_.Find(name)) {
+        *row = *known;
         return "";
     }
-    Node node;
-    if (!src_ || !src_->GetNode(name, &node)) return fmt("node \"%s\" not found", name.c_str());
-    const int G = GetGPUDeviceCountOfNode(node);
-    if (G <= 0) return fmt("node \"%s\" has no nano-gpu/gpu-percent capacity", name.c_str());  // the reference would divide by zero in Rate
-    const uint32_t r = (uint32_t)names_.size();
-    int rc = ngs_node_upsert(h_, r, G);  // NewNodeInfo (node.go:25-42)
-    if (rc != NGS_OK) return ngs_last_error(h_);
-    index_[name] = r;
-    names_.push_back(name);
-    gpu_count_.push_back(G);
-    for (const Pod& pod : src_->ListAssumedPods(name)) {  // dealer.go:287-299: replay the assumed pods
+    CandidateSet one;  // same path as a whole candidate list, so a node is built one way only
+    one.names.push_back(name);
+    Resolve(&one);
+    if (one.n_missing) return one.lookup_err.begin()->second;
+    *row = one.rows[0];
+    return "";
+}
+
+// dealer.go:287-299 on the host copy of a new row: Allocate each assumed pod's plan (all or nothing,
+// DESIGN.md "deviations"), remember the pods that fitted.
+void Dealer::replay_assumed_pods(const std::string& name, int G, int32_t* fr) {
+    std::vector<Pod> fetched;
+    std::vector<const Pod*> local;
+    const std::vector<const Pod*>* pods = &local;
+    if (listed_) {
+        auto it = listed_->find(name);
+        if (it != listed_->end()) pods = &it->second;
+    } else {
+        fetched = src_->ListAssumedPods(name);
+        for (const Pod& p : fetched) local.push_back(&p);
+    }
+    for (const Pod* pp : *pods) {
+        const Pod& pod = *pp;
         std::vector<int32_t> demand, idx;
         if (!NewPlanFromPod(pod, &demand, &idx).empty()) continue;
-        if (ngs_node_apply(h_, r, idx.data(), demand.data(), (int)demand.size(), +1) != NGS_OK) continue;
+        if (demand.size() > NGS_MAX_CONTAINERS) continue;
+        int32_t f[NGS_MAX_GPUS];
+        for (int g = 0; g < NGS_MAX_GPUS; g++) f[g] = fr[g];
+        bool ok = true;
+        for (size_t k = 0; k < demand.size() && ok; k++) {
+            const int gi = idx[k];
+            if (gi < 0) continue;  // allocate.go:105-107
+            if (demand[k] < 0 || gi >= G || f[gi] < demand[k]) ok = false;  // allocate.go:108
+            else f[gi] -= demand[k];
+        }
+        if (!ok) continue;
+        for (int g = 0; g < NGS_MAX_GPUS; g++) fr[g] = f[g];
         pod_maps_[pod.uid] = pod;
     }
-    // usage samples that arrived before the node was materialised
+}
+
+// usage samples that arrived before the node was materialised
+void Dealer::replay_usage(const std::string& name, uint32_t r) {
     for (int m = 0; m < 2; m++) {
         if (m == 0 ? !core_usage_.count(name) : !memory_usage_.count(name)) continue;
         ngs_load_add_node(h_, r, m);
@@ -165,71 +314,192 @@ Error Dealer::getNodeInfo(const std::string& name, uint32_t* row) {  // dealer.g
             }
         }
     }
-    *row = r;
-    return "";
+}
+
+void Dealer::Resolve(CandidateSet* cs) {  // dealer.go:97-106 for a whole list
+    const size_t n = cs->names.size();
+    const bool fresh = cs->rows.size() != n;
+    if (fresh) {
+        cs->rows.resize(n);
+        cs->lookup_err.clear();
+        index_.FindMany(cs->names.data(), n, cs->rows.data());  // the known names, which is nearly all of them
+    }
+    // pass 1: known names; unknown ones are fetched from the lister and queued for one bulk upload
+    const uint32_t first_new = (uint32_t)names_.size();
+    std::vector<uint8_t> new_g;
+    std::vector<int32_t> new_free;
+    for (size_t i = 0; i < n; i++) {
+        if (cs->rows[i] != 0xFFFFFFFFu) continue;
+        const std::string_view nm = cs->names[i];
+        if (const uint32_t* known = index_.Find(nm)) {
+            cs->rows[i] = *known;
+            cs->lookup_err.erase((uint32_t)i);
+            continue;
+        }
+        const std::string name(nm);
+        Node node;
+        Error e;
+        int G = 0;
+        if (!src_ || !src_->GetNode(name, &node)) e = fmt("node \"%s\" not found", name.c_str());
+        else if ((G = GetGPUDeviceCountOfNode(node)) <= 0) e = fmt("node \"%s\" has no nano-gpu/gpu-percent capacity", name.c_str());
+        else if (G > NGS_MAX_GPUS) e = fmt("node \"%s\": %d GPUs, more than NGS_MAX_GPUS", name.c_str(), G);
+        if (!e.empty()) {
+            cs->lookup_err[(uint32_t)i] = e;
+            continue;
+        }
+        const uint32_t r = (uint32_t)names_.size();
+        index_.Insert(nm, r);
+        names_.push_back(name);
+        gpu_count_.push_back(G);
+        new_g.push_back((uint8_t)G);
+        new_free.resize(new_free.size() + NGS_MAX_GPUS, 0);
+        int32_t* fr = new_free.data() + new_free.size() - NGS_MAX_GPUS;
+        for (int g = 0; g < G; g++) fr[g] = 100;  // NewNodeInfo (node.go:25-42)
+        replay_assumed_pods(name, G, fr);
+        cs->rows[i] = r;
+        cs->lookup_err.erase((uint32_t)i);
+    }
+    if (!new_g.empty()) {
+        // all new rows go up in one H2D copy instead of one launch per node and per replayed pod
+        if (ngs_snapshot_load(h_, first_new, (uint32_t)new_g.size(), new_g.data(), new_free.data(), nullptr) != NGS_OK) {
+            const Error e = ngs_last_error(h_);
+            for (size_t i = 0; i < n; i++)
+                if (cs->rows[i] != 0xFFFFFFFFu && cs->rows[i] >= first_new) cs->rows[i] = 0xFFFFFFFFu, cs->lookup_err[(uint32_t)i] = e;
+            // the rows were never built: forget them again
+            for (uint32_t r = first_new; r < names_.size(); r++) index_.Insert(names_[r], 0xFFFFFFFFu);
+            names_.resize(first_new);
+            gpu_count_.resize(first_new);
+        } else {
+            for (uint32_t r = first_new; r < names_.size(); r++) replay_usage(names_[r], r);
+        }
+    }
+    cs->n_missing = cs->lookup_err.size();
+    cs->all_rows = cs->n_missing == 0 && n == names_.size() && n > 0;
+    for (size_t i = 0; cs->all_rows && i < n; i++) cs->all_rows = cs->rows[i] == i;
+}
+
+AssumeResult Dealer::AssumeSet(const CandidateSet& cs, const Pod& pod, const PolicySpec& spec, bool isLoadSchedule) {  // dealer.go:89-136
+    AssumeResult r;
+    r.demand = NewDemandFromPod(pod);
+    r.demand_text = DemandString(r.demand);
+    const size_t n = cs.names.size();
+    r.ok.assign(n, 0);
+    r.reason.assign(n, NGS_REASON_UNKNOWN_NODE);
+    if (n == 0) return r;
+    ngs_load_ctx L;
+    const bool has_load = load_ctx(spec, isLoadSchedule, &L);
+    const int C = (int)r.demand.size();
+    r.plan.resize(n * (size_t)(C > 0 ? C : 1));
+    r.n_emitted.resize(n);
+    const int rc = ngs_assume(h_, cs.all_rows ? nullptr : cs.rows.data(), (uint32_t)n, r.demand.data(), C, policy(), has_load ? &L : nullptr,
+                              r.ok.data(), r.reason.data(), nullptr, r.plan.data(), r.n_emitted.data());
+    if (rc != NGS_OK) {
+        r.call_err = ngs_last_error(h_);
+        std::fill(r.ok.begin(), r.ok.end(), 0);
+        return r;
+    }
+    // one ranged read-back covers every row a failure message will quote
+    uint32_t lo = 0xFFFFFFFFu, hi = 0;
+    for (size_t i = 0; i < n; i++)
+        if (r.reason[i] == NGS_REASON_INFEASIBLE) {
+            lo = std::min(lo, cs.rows[i]);
+            hi = std::max(hi, cs.rows[i]);
+        }
+    if (lo <= hi) {
+        r.free_first = lo;
+        r.free.resize((size_t)(hi - lo + 1) * 8);
+        ngs_snapshot_read(h_, lo, hi - lo + 1, nullptr, r.free.data(), nullptr);
+    }
+    return r;
+}
+
+Error Dealer::FailureText(const CandidateSet& cs, const AssumeResult& r, size_t i) const {
+    auto it = cs.lookup_err.find((uint32_t)i);
+    if (it != cs.lookup_err.end()) return "nano gpu scheduler get node failed: " + it->second;  // dealer.go:102
+    if (!r.call_err.empty()) return r.call_err;
+    if (r.reason[i] != NGS_REASON_INFEASIBLE) return "";
+    const uint32_t row = cs.rows[i];
+    const int32_t* fr = r.free.data() + (size_t)(row - r.free_first) * 8;
+    std::vector<int> gp(fr, fr + gpu_count_[row]);
+    if (rater_ == RaterKind::Sample)  // rater.go:47
+        return fmt("unexpected failure of allocation  %s on %s", DemandString(r.demand).c_str(), GPUsString(gp).c_str());
+    const size_t C = r.demand.size();  // rater.go:99,152
+    std::vector<int32_t> partial(r.plan.begin() + i * C, r.plan.begin() + i * C + r.n_emitted[i]);
+    return fmt("can't allocate   %s on %s: indexes=%s", DemandString(r.demand).c_str(), GPUsString(gp).c_str(), IntsString(partial).c_str());
+}
+
+char* Dealer::PutFailureText(char* p, const CandidateSet& cs, const AssumeResult& r, size_t i) const {
+    auto lit = [&](const char* s) {
+        const size_t n = strlen(s);
+        memcpy(p, s, n);
+        p += n;
+    };
+    auto num = [&](int64_t v) {
+        char tmp[24];
+        int n = 0;
+        uint64_t u = v < 0 ? (uint64_t)0 - (uint64_t)v : (uint64_t)v;
+        do tmp[n++] = (char)('0' + u % 10); while (u /= 10);
+        if (v < 0) *p++ = '-';
+        while (n) *p++ = tmp[--n];
+    };
+    const uint32_t row = cs.rows[i];
+    const int32_t* fr = r.free.data() + (size_t)(row - r.free_first) * 8;
+    lit(rater_ == RaterKind::Sample ? "unexpected failure of allocation  " : "can't allocate   ");  // rater.go:47 / 99,152
+    memcpy(p, r.demand_text.data(), r.demand_text.size());
+    p += r.demand_text.size();
+    lit(" on ");
+    for (int g = 0; g < gpu_count_[row]; g++) {  // GPUs.String() (allocate.go:133-139)
+        *p++ = '(';
+        num(fr[g]);
+        *p++ = ')';
+    }
+    if (rater_ != RaterKind::Sample) {
+        lit(": indexes=[");
+        const size_t C = r.demand.size();
+        for (int k = 0; k < r.n_emitted[i]; k++) {
+            if (k) *p++ = ' ';
+            num(r.plan[i * C + (size_t)k]);
+        }
+        *p++ = ']';
+    }
+    return p;
+}
+
+std::vector<int> Dealer::ScoreSet(const CandidateSet& cs, const Pod& pod, const PolicySpec& spec, bool isLoadSchedule) {  // dealer.go:138-153
+    const std::vector<int32_t> demand = NewDemandFromPod(pod);
+    const size_t n = cs.names.size();
+    std::vector<int> scores(n, NGS_SCORE_MIN);  // a missing node scores ScoreMin (dealer.go:145-148)
+    if (n == 0) return scores;
+    ngs_load_ctx L;
+    const bool has_load = load_ctx(spec, isLoadSchedule, &L);
+    static_assert(sizeof(int) == sizeof(int32_t), "scores are read straight into the result");
+    if (ngs_score(h_, cs.all_rows ? nullptr : cs.rows.data(), (uint32_t)n, demand.data(), (int)demand.size(), policy(), has_load ? &L : nullptr,
+                  scores.data()) != NGS_OK)
+        std::fill(scores.begin(), scores.end(), NGS_SCORE_MIN);
+    return scores;
 }
 
 std::pair<std::vector<bool>, std::vector<Error>> Dealer::Assume(const std::vector<std::string>& nodes, const Pod& pod,
                                                                 const PolicySpec& spec, bool isLoadSchedule) {  // dealer.go:89-136
-    const std::vector<int32_t> demand = NewDemandFromPod(pod);
+    CandidateSet cs;
+    cs.names.assign(nodes.begin(), nodes.end());
+    Resolve(&cs);
+    const AssumeResult r = AssumeSet(cs, pod, spec, isLoadSchedule);
     const size_t n = nodes.size();
     std::vector<bool> ans(n, false);
     std::vector<Error> res(n);
-    std::vector<uint32_t> idx(n, 0xFFFFFFFFu);
     for (size_t i = 0; i < n; i++) {
-        uint32_t row;
-        Error e = getNodeInfo(nodes[i], &row);
-        if (!e.empty()) res[i] = "nano gpu scheduler get node failed: " + e;  // dealer.go:102
-        else idx[i] = row;
-    }
-    if (n == 0) return {ans, res};
-    ngs_load_ctx L;
-    const bool has_load = load_ctx(spec, isLoadSchedule, &L);
-    const int C = (int)demand.size();
-    std::vector<uint8_t> feas(n);
-    std::vector<int8_t> reason(n);
-    std::vector<int32_t> plan(n * (size_t)(C > 0 ? C : 1)), nem(n);
-    int rc = ngs_assume(h_, idx.data(), (uint32_t)n, demand.data(), C, policy(), has_load ? &L : nullptr, feas.data(), reason.data(),
-                        nullptr, plan.data(), nem.data());
-    for (size_t i = 0; i < n; i++) {
-        if (!res[i].empty()) continue;  // node lookup already failed
-        if (rc != NGS_OK) {
-            res[i] = ngs_last_error(h_);
-            continue;
-        }
-        ans[i] = feas[i] != 0;
-        if (reason[i] == NGS_REASON_INFEASIBLE) {
-            std::vector<int32_t> fr(8);
-            ngs_snapshot_read(h_, idx[i], 1, nullptr, fr.data(), nullptr);
-            std::vector<int> gp(fr.begin(), fr.begin() + gpu_count_[idx[i]]);
-            if (rater_ == RaterKind::Sample) {  // rater.go:47
-                res[i] = fmt("unexpected failure of allocation  %s on %s", DemandString(demand).c_str(), GPUsString(gp).c_str());
-            } else {  // rater.go:99,152
-                std::vector<int32_t> partial(plan.begin() + i * C, plan.begin() + i * C + nem[i]);
-                res[i] = fmt("can't allocate   %s on %s: indexes=%s", DemandString(demand).c_str(), GPUsString(gp).c_str(),
-                             IntsString(partial).c_str());
-            }
-        }
+        ans[i] = r.ok[i] != 0;
+        if (!ans[i]) res[i] = FailureText(cs, r, i);
     }
     return {ans, res};
 }
 
 std::vector<int> Dealer::Score(const std::vector<std::string>& nodes, const Pod& pod, const PolicySpec& spec, bool isLoadSchedule) {
-    const std::vector<int32_t> demand = NewDemandFromPod(pod);  // dealer.go:138-153
-    const size_t n = nodes.size();
-    std::vector<int> scores(n, NGS_SCORE_MIN);
-    if (n == 0) return scores;
-    std::vector<uint32_t> idx(n, 0xFFFFFFFFu);
-    for (size_t i = 0; i < n; i++) {
-        uint32_t row;
-        if (getNodeInfo(nodes[i], &row).empty()) idx[i] = row;  // a missing node scores ScoreMin (dealer.go:145-148)
-    }
-    ngs_load_ctx L;
-    const bool has_load = load_ctx(spec, isLoadSchedule, &L);
-    std::vector<int32_t> sc(n);
-    if (ngs_score(h_, idx.data(), (uint32_t)n, demand.data(), (int)demand.size(), policy(), has_load ? &L : nullptr, sc.data()) == NGS_OK)
-        for (size_t i = 0; i < n; i++) scores[i] = sc[i];
-    return scores;
+    CandidateSet cs;
+    cs.names.assign(nodes.begin(), nodes.end());
+    Resolve(&cs);
+    return ScoreSet(cs, pod, spec, isLoadSchedule);
 }
 
 Error Dealer::Bind(const std::string& node, Pod* pod, const PolicySpec& spec, bool isLoadSchedule) {  // dealer.go:155-203
@@ -331,31 +601,29 @@ std::pair<std::map<int, GPUMemoryUsage>, bool> Dealer::GetMemoryUsage(const std:
 }
 void Dealer::AddCoreUsage(const std::string& node) {  // nodeusage.go:58-62
     core_usage_[node] = {};
-    auto it = index_.find(node);
-    if (it != index_.end()) ngs_load_add_node(h_, it->second, NGS_METRIC_CORE);
+    if (const uint32_t* row = index_.Find(node)) ngs_load_add_node(h_, *row, NGS_METRIC_CORE);
 }
 void Dealer::AddMemoryUsage(const std::string& node) {  // nodeusage.go:64-68
     memory_usage_[node] = {};
-    auto it = index_.find(node);
-    if (it != index_.end()) ngs_load_add_node(h_, it->second, NGS_METRIC_MEMORY);
+    if (const uint32_t* row = index_.Find(node)) ngs_load_add_node(h_, *row, NGS_METRIC_MEMORY);
 }
 void Dealer::UpdateCoreUsage(const std::string& node, const std::string& coreUsage, const std::string& updateTime, int cardNum) {
     core_usage_[node][cardNum] = GPUCoreUsage{coreUsage, updateTime};  // nodeusage.go:70-74
-    auto it = index_.find(node);
-    if (it == index_.end()) return;  // replayed when the node is materialised (getNodeInfo)
+    const uint32_t* row = index_.Find(node);
+    if (!row) return;  // replayed when the node is materialised (getNodeInfo)
     double v = 0;
     int64_t ts = 0;
     int vok = ngs_parse_usage(coreUsage.c_str(), &v), tok = ngs_parse_update_time(updateTime.c_str(), &ts);
-    ngs_load_update(h_, it->second, NGS_METRIC_CORE, cardNum, v, vok, ts, tok);
+    ngs_load_update(h_, *row, NGS_METRIC_CORE, cardNum, v, vok, ts, tok);
 }
 void Dealer::UpdateMemoryUsage(const std::string& node, const std::string& memoryUsage, const std::string& updateTime, int cardNum) {
     memory_usage_[node][cardNum] = GPUMemoryUsage{memoryUsage, updateTime};  // nodeusage.go:76-80
-    auto it = index_.find(node);
-    if (it == index_.end()) return;
+    const uint32_t* row = index_.Find(node);
+    if (!row) return;
     double v = 0;
     int64_t ts = 0;
     int vok = ngs_parse_usage(memoryUsage.c_str(), &v), tok = ngs_parse_update_time(updateTime.c_str(), &ts);
-    ngs_load_update(h_, it->second, NGS_METRIC_MEMORY, cardNum, v, vok, ts, tok);
+    ngs_load_update(h_, *row, NGS_METRIC_MEMORY, cardNum, v, vok, ts, tok);
 }
 
 Dealer::Usage Dealer::GetUsage(const std::string& node, const std::string& key, int card, int64_t activeDuration_ns) {  // nodeusage.go:82-111

@@ -13,6 +13,8 @@
 #include <map>
 #include <set>
 #include <string>
+#include <string_view>
+#include <unordered_map>
 #include <utility>
 #include <vector>
 
@@ -52,6 +54,55 @@ class ClusterSource {
     virtual ~ClusterSource() {}
     virtual bool GetNode(const std::string& name, Node* out) = 0;                             // false: `node "x" not found`
     virtual std::vector<Pod> ListAssumedPods(const std::string& node_name) { return {}; }    // label nano-gpu/assume=true
+    virtual std::vector<Pod> ListAllAssumedPods() { return {}; }                              // the same label over all nodes (dealer.go:58)
+};
+
+// An error is a string; "" is Go's nil.
+using Error = std::string;
+
+// name -> row, open addressing over a name arena; replaces the Go map lookups of dealer.go:272
+class NodeIndex {
+  public:
+    NodeIndex();
+    const uint32_t* Find(std::string_view name) const;
+    // rows[i] = the row of names[i], 0xFFFFFFFF when absent.  Looks the names up in blocks with the table
+    // and arena lines prefetched, so a 100k-name list does not pay one cache miss after the other.
+    void FindMany(const std::string_view* names, size_t n, uint32_t* rows) const;
+    void Insert(std::string_view name, uint32_t row);
+    size_t size() const { return count_; }
+
+  private:
+    struct Slot {
+        uint64_t hash;
+        uint32_t row, len;
+        uint32_t off, used;  // used == 0: empty
+    };
+    std::vector<Slot> slots_;
+    std::string arena_;
+    size_t count_ = 0, mask_ = 0;
+    void grow();
+};
+uint64_t HashName(std::string_view s);
+
+
+// A candidate list after name resolution (dealer.go:97-106 done once per list instead of once per
+// goroutine): rows[i] = the dense row of names[i], 0xFFFFFFFF when getNodeInfo failed.
+struct CandidateSet {
+    std::vector<std::string_view> names;     // caller-owned storage
+    std::vector<uint32_t> rows;
+    std::map<uint32_t, Error> lookup_err;    // i -> getNodeInfo's error, only for the failed ones
+    size_t n_missing = 0;
+    bool all_rows = false;                   // names are exactly rows 0..n-1 in order: the C ABI's idx == NULL form
+};
+// what one Assume over a CandidateSet brings back from the device
+struct AssumeResult {
+    std::vector<uint8_t> ok;                 // Assume's []bool
+    std::vector<int8_t> reason;              // NGS_REASON_*
+    std::vector<int32_t> demand, plan, n_emitted;
+    std::string demand_text;                 // DemandString(demand), shared by every failure message
+    std::vector<int32_t> free;               // rows [free_first, free_first + free.size()/8) read back once, for the messages
+    uint32_t free_first = 0;
+    Error call_err;                          // the C ABI call itself failed: every node reports it
 };
 
 enum class RaterKind { Binpack, Spread, Sample };  // controller.Rater (pkg/controller/controller.go:38)
@@ -63,8 +114,6 @@ struct GPUMemoryUsage {
     std::string MemoryUsage, UpdateTime;
 };  // nodeusage.go:15-18
 
-// An error is a string; "" is Go's nil.
-using Error = std::string;
 
 class Dealer {
   public:
@@ -102,6 +151,19 @@ class Dealer {
     };
     Usage GetUsage(const std::string& node, const std::string& key, int card, int64_t activeDuration_ns);
 
+    // The same Assume / Score over a pre-resolved candidate list (extender_codec.h keeps one per
+    // distinct NodeNames array): no per-name strings, one ranged read-back for the failure texts.
+    void Resolve(CandidateSet* cs);  // getNodeInfo for every name not resolved yet; new nodes go up in one bulk load
+    AssumeResult AssumeSet(const CandidateSet& cs, const Pod& pod, const PolicySpec& spec, bool isLoadSchedule);
+    Error FailureText(const CandidateSet& cs, const AssumeResult& r, size_t i) const;  // res[i] of Assume for a node with !ok[i]
+    // FailureText for the common case (the rater said no) written at p without temporaries; FailureIsPlain
+    // tells whether entry i is that case.  The text is ASCII without quotes or backslashes.
+    bool FailureIsPlain(const CandidateSet& cs, const AssumeResult& r, size_t i) const {
+        return r.call_err.empty() && r.reason[i] == NGS_REASON_INFEASIBLE && (cs.n_missing == 0 || !cs.lookup_err.count((uint32_t)i));
+    }
+    char* PutFailureText(char* p, const CandidateSet& cs, const AssumeResult& r, size_t i) const;
+    std::vector<int> ScoreSet(const CandidateSet& cs, const Pod& pod, const PolicySpec& spec, bool isLoadSchedule);
+
     // time.Now() of the next calls (tests freeze it); 0 = wall clock
     void SetNow(int64_t unix_ns) { now_ns_ = unix_ns; }
 
@@ -111,7 +173,7 @@ class Dealer {
     ngs_dealer* h_ = nullptr;
     std::string init_error_;
     int64_t now_ns_ = 0;
-    std::map<std::string, uint32_t> index_;      // NodeMaps keys -> dense row
+    NodeIndex index_;                            // NodeMaps keys -> dense row
     std::vector<std::string> names_;             // row -> name
     std::vector<int> gpu_count_;                 // row -> G
     std::map<std::string, Pod> pod_maps_;        // PodMaps (dealer.go:82)
@@ -119,8 +181,12 @@ class Dealer {
     std::map<std::string, std::map<int, GPUCoreUsage>> core_usage_;      // dealer.go:84
     std::map<std::string, std::map<int, GPUMemoryUsage>> memory_usage_;  // dealer.go:85
 
+    const std::unordered_map<std::string, std::vector<const Pod*>>* listed_ = nullptr;  // NewDealer's one list, grouped by node
+
     int policy() const;
     Error getNodeInfo(const std::string& name, uint32_t* row);  // dealer.go:271-301
+    void replay_assumed_pods(const std::string& name, int G, int32_t* row_free);  // dealer.go:287-299 on the host copy of a new row
+    void replay_usage(const std::string& name, uint32_t row);                     // usage samples that arrived before the node existed
     bool load_ctx(const PolicySpec& spec, bool isLoad, ngs_load_ctx* out) const;
     int64_t now() const;
 };

@@ -1,0 +1,211 @@
+"""The filter / prioritize routes end to end on the GPU: JSON body in -> C++ codec ->
+name resolution -> ngs_assume / ngs_score on the device -> JSON body out, compared byte for byte with
+what the reference would marshal for the ORACLE's verdicts on the same cluster (pkg/routes/routes.go:40-123,
+pkg/scheduler/predicate.go:21-38, priority.go:30-37, failure texts of pkg/dealer/rater.go:47,99,152 and
+dealer.go:102)."""
+import ctypes as C
+import json
+import time
+
+import numpy as np
+import pytest
+
+import oracle as o
+from tests import extender_util as x
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _built(built):
+    import nano_gpu_scheduler_b200.build as b
+
+    b.build_host()
+
+
+def node_name(i):
+    return "node-%06d" % i
+
+
+class Routes:
+    def __init__(self, gcount, rater, assumed=(), load=False):
+        self.L = x.lib()
+        g = np.ascontiguousarray(gcount, dtype=np.uint8)
+        self.h = C.c_void_p(self.L.ngsx_routes_new(len(g), g.ctypes.data_as(C.c_void_p)))
+        for node, uid, percent, gpu_idx in assumed:
+            pc = (C.c_int32 * len(percent))(*percent)
+            gi = (C.c_int32 * len(percent))(*gpu_idx)
+            self.L.ngsx_routes_add_assumed(self.h, node, uid.encode(), pc, gi, len(percent))
+        err = C.c_char_p()
+        t0 = time.perf_counter()
+        rc = self.L.ngsx_routes_start(self.h, rater, len(g) + 8, 0, int(load), C.byref(err))
+        self.start_ms = (time.perf_counter() - t0) * 1e3  # NewDealer: list the assumed pods, rebuild their nodes
+        assert rc == 0, err.value
+
+    def close(self):
+        self.L.ngsx_routes_destroy(self.h)
+
+    def predicate(self, body):
+        body = body if isinstance(body, bytes) else body.encode()
+        n = C.c_size_t()
+        return x._take(self.L.ngsx_routes_predicate(self.h, body, C.c_size_t(len(body)), C.byref(n)), n)
+
+    def prioritize(self, body):
+        body = body if isinstance(body, bytes) else body.encode()
+        n = C.c_size_t()
+        p = C.c_int()
+        out = x._take(self.L.ngsx_routes_prioritize(self.h, body, C.c_size_t(len(body)), C.byref(n), C.byref(p)), n)
+        return out, bool(p.value)
+
+    def counters(self):
+        c = (C.c_uint64 * 7)()
+        self.L.ngsx_routes_counters(self.h, c)
+        return dict(requests=c[0], cache_hits=c[1], all_rows=c[2], ns_decode=c[3], ns_resolve=c[4], ns_dealer=c[5], ns_encode=c[6])
+
+    def bind(self, node, uid, percent):
+        pc = (C.c_int32 * len(percent))(*percent)
+        out = (C.c_int32 * len(percent))()
+        err = C.c_char_p()
+        rc = self.L.ngsx_routes_bind(self.h, node.encode(), uid.encode(), pc, len(percent), out, C.byref(err))
+        return rc, list(out), err.value
+
+
+def demand_str(d):
+    return "[" + " ".join("(%d)" % v for v in d) + "]"
+
+
+def expected_filter(oc, gcount, policy, demand, names):
+    """what predicate.go builds from the oracle's Assume over `names` (unknown names -> the lister's error)"""
+    ids = []
+    for nm in names:
+        ok = nm.startswith("node-") and len(nm) == 11 and nm[5:].isdigit() and int(nm[5:]) < len(gcount)
+        ids.append(int(nm[5:]) if ok else -1)
+    known = [i for i in ids if i >= 0]
+    res = oc.assume(demand, policy, idx=np.array(known, dtype=np.uint32), want_plan=True) if known else None
+    can, failed, k = [], {}, 0
+    for nm, i in zip(names, ids):
+        if i < 0:
+            failed[nm] = 'nano gpu scheduler get node failed: node "%s" not found' % nm
+            continue
+        if res["feasible"][k]:
+            can.append(nm)
+        else:
+            free = oc.node_get(i)[1][: gcount[i]]
+            gpus = "".join("(%d)" % v for v in free)
+            if policy == o.POLICY_RANDOM:
+                failed[nm] = "unexpected failure of allocation  %s on %s" % (demand_str(demand), gpus)
+            else:
+                part = res["plan"][k][: res["n_emitted"][k]]
+                failed[nm] = "can't allocate   %s on %s: indexes=[%s]" % (demand_str(demand), gpus, " ".join(str(int(v)) for v in part))
+        k += 1
+    return can, failed
+
+
+def make_assumed(gcount, rng, frac):
+    """random valid assumed pods; returns [(node, uid, percent, gpu_idx)]"""
+    out = []
+    for i in np.flatnonzero(rng.random(len(gcount)) < frac):
+        free = [100] * int(gcount[i])
+        for j in range(int(rng.integers(1, 4))):
+            c = int(rng.integers(1, 4))
+            pc, gi = [], []
+            for _ in range(c):
+                g = int(rng.integers(0, gcount[i]))
+                p = int(5 * rng.integers(1, 13))
+                if free[g] < p:
+                    p = 0
+                free[g] -= p
+                pc.append(p)
+                gi.append(g if p else -1)
+            out.append((int(i), "pod-%d-%d" % (i, j), pc, gi))
+    return out
+
+
+@pytest.mark.parametrize("rater,policy", [(0, o.POLICY_BINPACK), (1, o.POLICY_SPREAD), (2, o.POLICY_RANDOM)])
+def test_routes_match_the_oracle_byte_for_byte(rater, policy):
+    rng = np.random.default_rng(100 + rater)
+    n = 3000
+    gcount = rng.integers(1, 9, size=n).astype(np.uint8)
+    assumed = make_assumed(gcount, rng, 0.5)
+    oc = o.OracleCluster(n)
+    oc.load_snapshot(gcount, np.where(np.arange(8)[None, :] < gcount[:, None], 100, 0).astype(np.int32))
+    for node, _, pc, gi in assumed:
+        assert oc.node_apply(node, gi, pc, +1) == 0
+    r = Routes(gcount, rater, assumed)
+    try:
+        names = [node_name(i) for i in range(n)]
+        for demand in ([20, 40], [0, 100, 5], [60, 60, 60], [100] * 9):
+            pod = x.pod_json(demand)
+            body = json.dumps({"Pod": pod, "Nodes": None, "NodeNames": names})
+            can, failed = expected_filter(oc, gcount, policy, demand, names)
+            assert r.predicate(body) == x.go_filter_result(can, failed), demand
+            out, panicked = r.prioritize(body)
+            sc = oc.assume(demand, policy)["score"]
+            assert not panicked and out == x.go_priorities(names, [int(v) for v in sc])
+        c = r.counters()
+        assert c["requests"] == 8 and c["cache_hits"] == 7  # one tokenise + resolve for eight requests over the same list
+        # kube-scheduler's rotating start index, a subset, unknown names and a duplicate
+        sub = names[1700:] + names[:400] + ["bogus", "node-999999", names[5], names[5], "node-<&>"]
+        demand = [50, 50]
+        body = json.dumps({"Pod": x.pod_json(demand), "NodeNames": sub})
+        can, failed = expected_filter(oc, gcount, policy, demand, sub)
+        got = r.predicate(body)
+        assert got == x.go_filter_result(can, failed)
+        back = json.loads(got)
+        assert back["FailedNodes"]["bogus"] == 'nano gpu scheduler get node failed: node "bogus" not found'
+        assert list(back["FailedNodes"]) == sorted(back["FailedNodes"], key=lambda s: s.encode())
+        out, _ = r.prioritize(body)
+        want = []
+        for nm in sub:
+            known = nm[5:].isdigit() and int(nm[5:]) < n
+            want.append(int(oc.assume(demand, policy, idx=np.array([int(nm[5:])], dtype=np.uint32))["score"][0]) if known else 0)
+        assert out == x.go_priorities(sub, want)
+    finally:
+        r.close()
+        oc.close()
+
+
+def test_routes_all_rows_fast_path_and_state_changes():
+    n = 2048
+    gcount = np.full(n, 8, dtype=np.uint8)
+    oc = o.OracleCluster(n)
+    oc.load_snapshot(gcount, np.full((n, 8), 100, dtype=np.int32))
+    r = Routes(gcount, 0)
+    try:
+        names = [node_name(i) for i in range(n)]
+        demand = [70, 40]
+        body = json.dumps({"Pod": x.pod_json(demand), "NodeNames": names})
+        # the first request materialises every node in list order -> the list IS rows 0..n-1
+        assert r.predicate(body) == x.go_filter_result(names, {})
+        assert r.counters()["all_rows"] == 1
+        rng = np.random.default_rng(3)
+        for k in range(80):  # fill some nodes through Dealer.Bind, mirrored on the oracle
+            node = int(rng.integers(0, 4))
+            rc, gi, err = r.bind(node_name(node), "b%d" % k, demand)
+            orc, ogi, _ = oc.bind(node, demand, o.POLICY_BINPACK)
+            assert (rc == 0) == (orc == 0), err
+            if rc == 0:
+                assert gi == [int(v) for v in ogi]
+        can, failed = expected_filter(oc, gcount, o.POLICY_BINPACK, demand, names)
+        assert len(failed) > 0
+        assert r.predicate(body) == x.go_filter_result(can, failed)  # cached candidate set, fresh verdicts
+        c = r.counters()
+        assert c["cache_hits"] == 1 and c["all_rows"] == 2
+    finally:
+        r.close()
+        oc.close()
+
+
+def test_route_error_shapes():
+    r = Routes(np.full(4, 8, dtype=np.uint8), 0)
+    try:
+        assert r.predicate(b"{") == x.go_filter_error("unexpected EOF")  # routes.go:54-60
+        assert r.predicate(json.dumps({"Pod": x.pod_json([10]), "Nodes": {"items": []}})) == x.go_filter_error(
+            "nano-gpu-scheduler extender must be configured with nodeCacheCapable=true")  # routes.go:62-68
+        assert r.predicate(json.dumps({"Pod": x.pod_json([10]), "NodeNames": []})) == b'{"Nodes":null,"NodeNames":[],"FailedNodes":{},"Error":""}'
+        out, panicked = r.prioritize(b"not json")
+        assert panicked and out == b""  # routes.go:103: the reference panics here
+        out, panicked = r.prioritize(json.dumps({"Pod": x.pod_json([10]), "NodeNames": []}))
+        assert not panicked and out == b"[]"
+    finally:
+        r.close()
