@@ -78,7 +78,7 @@ constexpr int SCAN_TILE = 256;
 #define NGS_SCAN_STAGES_LOAD 2
 #endif
 #ifndef NGS_SCAN_STAGES_PLAIN
-#define NGS_SCAN_STAGES_PLAIN 3
+#define NGS_SCAN_STAGES_PLAIN 2
 #endif
 #ifndef NGS_SCAN_BLOCKS_LOAD
 #define NGS_SCAN_BLOCKS_LOAD 3
@@ -120,8 +120,11 @@ __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem
                  : "memory");
 }
 
+#ifndef NGS_SCAN_BLOCKS_PLAIN
+#define NGS_SCAN_BLOCKS_PLAIN 6
+#endif
 template <bool LOAD>
-__global__ void __launch_bounds__(SCAN_TILE, LOAD ? NGS_SCAN_BLOCKS_LOAD : 4) k_scan_tma(Tables T, uint32_t n, PodDemand pd, LoadParams lp, uint32_t gen,
+__global__ void __launch_bounds__(SCAN_TILE, LOAD ? NGS_SCAN_BLOCKS_LOAD : NGS_SCAN_BLOCKS_PLAIN) k_scan_tma(Tables T, uint32_t n, PodDemand pd, LoadParams lp_in, uint32_t gen,
                                                                         uint8_t* __restrict__ feasible, int8_t* __restrict__ reason,
                                                                         int32_t* __restrict__ score) {
     extern __shared__ __align__(128) unsigned char tiles[];
@@ -133,6 +136,8 @@ __global__ void __launch_bounds__(SCAN_TILE, LOAD ? NGS_SCAN_BLOCKS_LOAD : 4) k_
     const uint32_t tid = threadIdx.x;
     const uint32_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     const bool want_rl = !LOAD && !T.rl_zero;
+    LoadParams lp = lp_in;
+    if (!LOAD) lp.enabled = 0;  // a compile-time fact for this instantiation: the LoadUsage code drops out
 
     // one thread issues the copies of a tile: every table's 256-row slice is one contiguous range
     auto issue = [&](uint32_t tile, uint32_t stage) {
@@ -157,18 +162,19 @@ __global__ void __launch_bounds__(SCAN_TILE, LOAD ? NGS_SCAN_BLOCKS_LOAD : 4) k_
         }
     };
 
+    // thread 0 gets the first tiles moving before anything else happens; the demand is sorted by another
+    // warp meanwhile, so the prologue costs no memory time
     if (tid == 0) {
         for (int st = 0; st < SCAN_STAGES; st++) mbar_init(&bars[st], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        sort_demand(pd.percent, pd.n, pd.policy, &dem);
-    }
-    if (LOAD) fill_usage_pair_table(s_pair, tid, blockDim.x);
-    __syncthreads();
-    if (tid == 0)
         for (uint32_t i = 0; i < SCAN_STAGES; i++) {
             const uint32_t tile = blockIdx.x + i * gridDim.x;
             if (tile < ntiles) issue(tile, i);
         }
+    }
+    if (tid == 32) sort_demand(pd.percent, pd.n, pd.policy, &dem);
+    if (LOAD) fill_usage_pair_table(s_pair, tid, blockDim.x);
+    __syncthreads();
 
     uint32_t it = 0;
     for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {

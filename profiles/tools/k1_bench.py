@@ -15,7 +15,7 @@ import bench  # noqa: E402
 import nano_gpu_scheduler_b200 as ngs  # noqa: E402
 from nano_gpu_scheduler_b200 import workloads as wl  # noqa: E402
 
-n = int(sys.argv[1]) if len(sys.argv) > 1 else 4_000_000
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 16_000_000
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 20
 peak, src = bench.measured_peak()
 gcount, free = wl.make_cluster(n, 0.5, 0xB2000004)
