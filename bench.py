@@ -346,10 +346,13 @@ def run_b200(args):
             o_node, o_score, o_gidx = (np.zeros(1, dtype=np.int32), np.zeros(1, dtype=np.int32), np.zeros(MAX_C, dtype=np.int32))
             vp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
             lref = None if load is None else C.c_void_p(C.addressof(load))
-            for s in range(n_lat):
-                a_pc, a_nc, a_pol = pc[lo + s:lo + s + 1], nc[lo + s:lo + s + 1], policy[lo + s:lo + s + 1]
+            p_out = (vp(o_node), vp(o_score), vp(o_gidx))
+            p_in = [(C.c_void_p(pc.ctypes.data + (lo + s) * MAX_C * 4), C.c_void_p(nc.ctypes.data + (lo + s) * 4),
+                     C.c_void_p(policy.ctypes.data + (lo + s) * 4), C.c_uint64(s)) for s in range(n_lat)]
+            fn, hd, one, mc, sd1 = lib.ngs_schedule_batch, d._h, C.c_uint32(1), C.c_int(MAX_C), C.c_uint64(1)
+            for a_pc, a_nc, a_pol, seq in p_in:
                 t0 = time.perf_counter()
-                rc = lib.ngs_schedule_batch(d._h, 1, vp(a_pc), vp(a_nc), MAX_C, vp(a_pol), lref, 1, s, vp(o_node), vp(o_score), vp(o_gidx))
+                rc = fn(hd, one, a_pc, a_nc, mc, a_pol, lref, sd1, seq, p_out[0], p_out[1], p_out[2])
                 lat.append(time.perf_counter() - t0)
                 assert rc == 0
         else:

@@ -24,6 +24,7 @@
 #include <pthread.h>
 
 #include <cmath>
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -42,6 +43,7 @@ namespace {
 #include "ngs_k1_scan.cuh"
 #include "ngs_k3_rows.cuh"
 #include "ngs_k6_batch.cuh"
+#include "ngs_k7_one.cuh"
 
 // ---------------------------------------------------------------------------------------------
 // host side
@@ -75,6 +77,7 @@ struct ngs_dealer {
     // batch
     uint32_t batch_cap = 0;  // pods per launch chunk
     SortedDemand* d_dem = nullptr;
+    OneRec* d_one = nullptr;               // K7's arg-max word and ticket counter (zero between calls)
     unsigned long long* d_keys = nullptr;  // per-pod exchange records: {xw 16 B, done 4 B, pad, keys[num_sms]}
     size_t pod_rec_bytes = 0;
     int32_t* d_pod_in_dev = nullptr;       // device aliases of the mapped staging buffers
@@ -207,6 +210,8 @@ int ensure_batch(ngs_dealer* h) {
     //   [0,16) arg-max word {key, counter}   [16,20) random-policy arrival counter   [32, 32+8*SMs) per-CTA slots
     h->pod_rec_bytes = (32 + sizeof(unsigned long long) * (size_t)h->num_sms + 31) / 32 * 32;
     CU(h, cudaMalloc(&h->d_keys, h->pod_rec_bytes * cap));
+    CU(h, cudaMalloc(&h->d_one, sizeof(OneRec)));
+    CU(h, cudaMemsetAsync(h->d_one, 0, sizeof(OneRec), h->stream));
     // host-API staging lives in mapped pinned memory: the kernels read the pods and write the
     // decisions straight through PCIe, so a call needs no copy commands at all
     CU(h, cudaHostAlloc(&h->h_pod_in, (in_words + 8) * 4, cudaHostAllocMapped));
@@ -426,7 +431,7 @@ int ngs_destroy(ngs_dealer* h) {
     cudaFree(h->T.tag); cudaFree(h->T.cscore); cudaFree(const_cast<int16_t*>(h->T.blut));
     cudaFree(h->d_idx); cudaFree(h->d_feas); cudaFree(h->d_reason); cudaFree(h->d_score); cudaFree(h->d_plan); cudaFree(h->d_nem);
     cudaFree(h->d_bind); cudaFreeHost(h->h_bind); cudaFree(h->d_small); cudaFreeHost(h->h_small);
-    cudaFree(h->d_dem); cudaFree(h->d_keys);
+    cudaFree(h->d_dem); cudaFree(h->d_keys); cudaFree(h->d_one);
     cudaFreeHost(h->h_pod_in); cudaFreeHost(h->h_pod_out);
     cudaFree(h->d_err); cudaFreeHost(h->h_err);
     for (int r = 0; r < NGS_MAX_RANKS; r++)
@@ -803,6 +808,39 @@ int ngs_schedule_batch(ngs_dealer* h, uint32_t n_pods, const int32_t* percent, c
     CU(h, cudaSetDevice(h->device));
     rc = ensure_batch(h);
     if (rc) return rc;
+    if (n_pods == 1 && h->world <= 1 && policy[0] != NGS_POLICY_RANDOM) {
+        // one pod: K7, a single ordinary launch; the answer arrives in mapped host memory and the
+        // status word behind it is polled, so the call returns without a stream synchronisation
+        PodDemand pd;
+        rc = make_demand(h, percent, n_containers[0], policy[0], &pd);
+        if (rc) return rc;
+        if (lp.enabled) h->T.rl_zero = 0;  // the load-aware Rate writes RemainLoad
+        volatile int32_t* hout = h->h_pod_out;
+        hout[0] = ONE_PENDING;
+        uint32_t grid = (h->T.n + 255) / 256;
+        if (grid > (uint32_t)h->num_sms * 4) grid = (uint32_t)h->num_sms * 4;
+        if (grid < 1) grid = 1;
+        k_schedule_one<<<grid, 256, 0, h->stream>>>(h->T, pd, lp, h->d_one, h->d_pod_out_dev, max_c);
+        CU(h, cudaGetLastError());
+        for (uint32_t spins = 1; hout[0] == ONE_PENDING; spins++) {
+            if ((spins & 0xFFFu) == 0) {  // now and then make sure the kernel is still alive
+                const cudaError_t q = cudaStreamQuery(h->stream);
+                if (q == cudaSuccess) break;
+                if (q != cudaErrorNotReady) return fail(h, NGS_ERR_CUDA, "k_schedule_one: %s", cudaGetErrorString(q));
+            }
+        }
+        std::atomic_thread_fence(std::memory_order_acquire);
+        if (hout[0] != NGS_OK) return fail(h, NGS_ERR_CUDA, "k_schedule_one ended without an answer");
+        node_out[0] = hout[8];
+        score_out[0] = hout[9];
+        for (int k = 0; k < max_c; k++) gpu_idx_out[k] = hout[10 + k];
+        h->stats.kernel_launches += 1;
+        h->stats.node_evals += h->T.n;
+        h->stats.pods_scheduled += 1;
+        h->stats.h2d_bytes += sizeof(PodDemand);
+        h->stats.d2h_bytes += (size_t)(3 + max_c) * 4;
+        return NGS_OK;
+    }
     for (uint32_t p0 = 0; p0 < n_pods; p0 += BATCH_CHUNK) {
         const uint32_t P = n_pods - p0 < BATCH_CHUNK ? n_pods - p0 : BATCH_CHUNK;
         // mapped pinned staging: percent [P][max_c] | ncont [P] | policy [P]; outputs: status | node | score | gpu_idx

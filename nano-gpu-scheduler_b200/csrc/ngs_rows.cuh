@@ -150,12 +150,8 @@ __device__ __forceinline__ RowEval eval_row_values(const Tables& T, uint32_t row
 // One full GPUs.Choose (allocate.go:92-100) on a row read from the global tables.
 // do_rate=false is the plan-cache hit of NodeInfo.Bind (node.go:72-78): the plan is re-derived
 // from the RemainLoad the filter pass left behind, without running Rate / LoadUsage again.
-template <bool PLAN>
-__device__ __forceinline__ RowEval eval_row_global(const Tables& T, uint32_t row, const SortedDemand* dem, const LoadParams& lp,
-                                                   bool do_rate, const double* pair = nullptr) {
-    // every load of the row is issued before the first use, so that they are all in flight together
-    const bool load_path = lp.enabled && do_rate && dem->policy != NGS_POLICY_RANDOM;
-    RowIn in;
+// every load of a row issued before the first use, so that they are all in flight together
+__device__ __forceinline__ void load_row(const Tables& T, uint32_t row, bool load_path, RowIn& in) {
     in.G = T.gcount[row];
     ld_row8(T.free + (size_t)row * 8, in.v);
     in.r8 = make_uint2(0u, 0u);
@@ -169,5 +165,12 @@ __device__ __forceinline__ RowEval eval_row_global(const Tables& T, uint32_t row
     } else if (!T.rl_zero) {
         in.r8 = __ldcg(reinterpret_cast<const uint2*>(T.rl + (size_t)row * 8));
     }
+}
+
+template <bool PLAN>
+__device__ __forceinline__ RowEval eval_row_global(const Tables& T, uint32_t row, const SortedDemand* dem, const LoadParams& lp,
+                                                   bool do_rate, const double* pair = nullptr) {
+    RowIn in;
+    load_row(T, row, lp.enabled && do_rate && dem->policy != NGS_POLICY_RANDOM, in);
     return eval_row_values<PLAN>(T, row, in, dem, lp, do_rate, pair);
 }

@@ -657,3 +657,51 @@ def test_stats_counters(ngs):
         assert s1["pods_scheduled"] - s0["pods_scheduled"] == 5
         assert s1["kernel_launches"] - s0["kernel_launches"] == 3
         assert s1["d2h_bytes"] > s0["d2h_bytes"] and s1["h2d_bytes"] > s0["h2d_bytes"]
+
+
+@pytest.mark.parametrize("policy,load,hetero", [(0, False, False), (1, False, True), (0, True, True), (1, True, False)])
+def test_single_pod_kernel_matches_oracle_and_batch_kernel(ngs, policy, load, hetero):
+    """a one-pod call takes K7 (one ordinary launch, polled answer): pod by pod it must give what the oracle
+    gives and what the batch kernel K6 gives for the same pods in one call, and leave the same snapshot"""
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    n, P, seed = 3000, 160, 0x0E + policy + 2 * load
+    oc, d, gcount, free = make_pair(ngs, n, 0.55, seed, hetero=hetero)
+    pc, nc = wl.make_pods(P, 1, 4, 0, 14, seed)
+    with d, ngs.GpuDealer(n, device=0) as d6:
+        d6.snapshot_load(gcount, free)
+        gl = ol = None
+        if load:
+            fill_load_tables(oc, d, n, seed)
+            fill_load_tables(o.OracleCluster(n), d6, n, seed)
+            gl, ol = load_ctx_pair(ngs)
+        node6, score6, gidx6 = d6.schedule_batch(pc, nc, policy, load=gl)
+        launches0 = d.stats()["kernel_launches"]
+        for p in range(P):
+            node, score, gidx = d.schedule_batch(pc[p : p + 1], nc[p : p + 1], policy, load=gl)
+            onode, oscore, ogidx = oc.schedule_batch(pc[p : p + 1], nc[p : p + 1], policy, load=ol)
+            assert node[0] == onode[0] == node6[p], p
+            assert score[0] == oscore[0] == score6[p], p
+            assert np.array_equal(gidx[0], ogidx[0]) and np.array_equal(gidx[0], gidx6[p]), p
+        assert d.stats()["kernel_launches"] - launches0 == P  # one launch per pod: the K7 path was the one that ran
+        assert (node6 >= 0).any()
+        assert_same_snapshot(oc, d)
+        assert_same_snapshot(oc, d6)
+
+
+def test_single_pod_kernel_edge_cases(ngs):
+    with ngs.GpuDealer(64, device=0) as d:
+        d.snapshot_load(np.full(64, 2, dtype=np.uint8))
+        # nothing fits: node -1, ScoreMin, no indexes; the exchange record must be clean for the next call
+        node, score, gidx = d.schedule_batch(np.array([[100, 100, 100]], dtype=np.int32), [3], 0)
+        assert node[0] == -1 and score[0] == 0 and (gidx[0] == np.iinfo(np.int32).min).all()
+        # zero-percent containers get -1, unused slots INT32_MIN
+        node, score, gidx = d.schedule_batch(np.array([[0, 30, 0, 0]], dtype=np.int32), [3], 0)
+        assert node[0] == 0 and list(gidx[0]) == [-1, 0, -1, np.iinfo(np.int32).min]
+        # a pod without containers binds to the best-rated node with an empty plan
+        node, score, gidx = d.schedule_batch(np.zeros((1, 2), dtype=np.int32), [0], 0)
+        assert node[0] >= 0 and (gidx[0] == np.iinfo(np.int32).min).all()
+        # many calls in a row reuse the record
+        for _ in range(50):
+            node, _, _ = d.schedule_batch(np.array([[100]], dtype=np.int32), [1], 0)
+        assert node[0] >= 0
