@@ -210,8 +210,8 @@ int ensure_batch(ngs_dealer* h) {
     //   [0,16) arg-max word {key, counter}   [16,20) random-policy arrival counter   [32, 32+8*SMs) per-CTA slots
     h->pod_rec_bytes = (32 + sizeof(unsigned long long) * (size_t)h->num_sms + 31) / 32 * 32;
     CU(h, cudaMalloc(&h->d_keys, h->pod_rec_bytes * cap));
-    CU(h, cudaMalloc(&h->d_one, sizeof(OneRec)));
-    CU(h, cudaMemsetAsync(h->d_one, 0, sizeof(OneRec), h->stream));
+    CU(h, cudaMalloc(&h->d_one, sizeof(OneRec) + sizeof(uint32_t) * ONE_MAX_CTAS));  // record, then K7's per-CTA counts
+    CU(h, cudaMemsetAsync(h->d_one, 0, sizeof(OneRec) + sizeof(uint32_t) * ONE_MAX_CTAS, h->stream));
     // host-API staging lives in mapped pinned memory: the kernels read the pods and write the
     // decisions straight through PCIe, so a call needs no copy commands at all
     CU(h, cudaHostAlloc(&h->h_pod_in, (in_words + 8) * 4, cudaHostAllocMapped));
@@ -808,19 +808,23 @@ int ngs_schedule_batch(ngs_dealer* h, uint32_t n_pods, const int32_t* percent, c
     CU(h, cudaSetDevice(h->device));
     rc = ensure_batch(h);
     if (rc) return rc;
-    if (n_pods == 1 && h->world <= 1 && policy[0] != NGS_POLICY_RANDOM) {
+    if (n_pods == 1 && h->world <= 1) {
         // one pod: K7, a single ordinary launch; the answer arrives in mapped host memory and the
         // status word behind it is polled, so the call returns without a stream synchronisation
         PodDemand pd;
         rc = make_demand(h, percent, n_containers[0], policy[0], &pd);
         if (rc) return rc;
-        if (lp.enabled) h->T.rl_zero = 0;  // the load-aware Rate writes RemainLoad
+        if (lp.enabled && policy[0] != NGS_POLICY_RANDOM) h->T.rl_zero = 0;  // the load-aware Rate writes RemainLoad
         volatile int32_t* hout = h->h_pod_out;
         hout[0] = ONE_PENDING;
         uint32_t grid = (h->T.n + 255) / 256;
         if (grid > (uint32_t)h->num_sms * 4) grid = (uint32_t)h->num_sms * 4;
         if (grid < 1) grid = 1;
-        k_schedule_one<<<grid, 256, 0, h->stream>>>(h->T, pd, lp, h->d_one, h->d_pod_out_dev, max_c);
+        if (policy[0] == NGS_POLICY_RANDOM)
+            k_schedule_one_random<<<grid, 256, 0, h->stream>>>(h->T, pd, seed + seq0, h->d_one, reinterpret_cast<uint32_t*>(h->d_one + 1),
+                                                               h->d_pod_out_dev, max_c);
+        else
+            k_schedule_one<<<grid, 256, 0, h->stream>>>(h->T, pd, lp, h->d_one, h->d_pod_out_dev, max_c);
         CU(h, cudaGetLastError());
         for (uint32_t spins = 1; hout[0] == ONE_PENDING; spins++) {
             if ((spins & 0xFFFu) == 0) {  // now and then make sure the kernel is still alive

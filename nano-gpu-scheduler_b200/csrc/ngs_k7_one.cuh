@@ -4,8 +4,10 @@
 // single pod none of that pays, so this kernel scans the tables where they lie (K1's row
 // evaluation), folds the keys with one atomicMax per CTA, and the CTA that arrives last — it can
 // tell from a ticket counter, nobody waits for anybody — binds the winner and leaves the exchange
-// record zeroed for the next call.  Binpack / spread only; the random policy and node-range
-// sharding stay with K6.  Same results as K6 with P = 1 (tests/test_gpu_parity.py).
+// record zeroed for the next call.  The random policy goes the same way with counts instead of keys:
+// every CTA owns a contiguous node range and leaves the number of feasible nodes in it; the last CTA
+// to arrive finds the range holding the seeded k-th feasible node and evaluates that range once more.
+// Node-range sharding stays with K6.  Same results as K6 with P = 1 (tests/test_gpu_parity.py).
 // Included by ngs_dealer.cu inside its anonymous namespace, after ngs_k6_batch.cuh.
 #pragma once
 
@@ -16,6 +18,150 @@ struct OneRec {
 };
 
 constexpr int32_t ONE_PENDING = 0x7FFFFFFF;  // status word while the kernel has not answered yet
+constexpr uint32_t ONE_MAX_CTAS = 1024;      // entries of the random policy's per-CTA count array
+
+// exclusive prefix of v over the 256 threads of the block (in thread order) and the block total
+__device__ __forceinline__ uint32_t block_scan_256(uint32_t v, uint32_t* s_warp /*[8]*/, uint32_t* total) {
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t up = __shfl_up_sync(FULL, inc, d);
+        if (lane >= (uint32_t)d) inc += up;
+    }
+    __syncthreads();  // (s_warp may still be read from a previous scan)
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    uint32_t base = 0, tot = 0;
+#pragma unroll
+    for (uint32_t w = 0; w < 8; w++) {
+        const uint32_t x = s_warp[w];
+        if (w < warp) base += x;
+        tot += x;
+    }
+    *total = tot;
+    return base + inc - v;
+}
+
+// SampleRater on one row: feasibility only
+__device__ __forceinline__ bool sample_row_feasible(const Tables& T, uint32_t row, const SortedDemand* dem) {
+    const int G = T.gcount[row];
+    if (G == 0) return false;
+    uint32_t v[8];
+    ld_row8(T.free + (size_t)row * 8, v);
+    int f[8];
+#pragma unroll
+    for (int g = 0; g < 8; g++) f[g] = (int)v[g];
+    return choose_sample<false>(f, G, dem, nullptr, nullptr);
+}
+
+// K7, random policy (see the file header).  cnt: [gridDim.x] feasible nodes per CTA range.
+__global__ void __launch_bounds__(256, 4) k_schedule_one_random(Tables T, PodDemand pd, uint64_t seed_seq, OneRec* rec, uint32_t* cnt, int32_t* out,
+                                                                int max_c) {
+    __shared__ SortedDemand dem;
+    __shared__ uint32_t s_warp[8];
+    __shared__ int s_last;
+    __shared__ uint32_t s_pick_cta, s_pick_off;
+    const uint32_t tid = threadIdx.x;
+    if (tid == 0) sort_demand(pd.percent, pd.n, pd.policy, &dem);
+    __syncthreads();
+    // CTA b owns rows [b * per_cta, (b+1) * per_cta), thread t the rpt consecutive rows from b * per_cta + t * rpt
+    const uint32_t rpt = (T.n + gridDim.x * 256u - 1) / (gridDim.x * 256u);
+    const uint32_t per_cta = rpt * 256u;
+    auto count_range = [&](uint32_t cta) {
+        uint32_t c = 0;
+        const uint32_t r0 = cta * per_cta + tid * rpt;
+        for (uint32_t j = 0; j < rpt; j++)
+            if (r0 + j < T.n && sample_row_feasible(T, r0 + j, &dem)) c++;
+        return c;
+    };
+    uint32_t total;
+    const uint32_t mine = count_range(blockIdx.x);
+    block_scan_256(mine, s_warp, &total);
+    if (tid == 0) {
+        cnt[blockIdx.x] = total;
+        __threadfence();
+        s_last = atomicAdd(&rec->arrived, 1u) == gridDim.x - 1 ? 1 : 0;
+    }
+    __syncthreads();
+    if (!s_last) return;
+
+    // ---- the last CTA to arrive ----
+    __threadfence();
+    if (tid == 0) rec->arrived = 0;
+    const uint32_t gpt = (gridDim.x + 255u) / 256u;  // count entries per thread
+    uint32_t part = 0;
+    for (uint32_t j = 0; j < gpt; j++) {
+        const uint32_t b = tid * gpt + j;
+        if (b < gridDim.x) part += __ldcg(cnt + b);
+    }
+    uint32_t feasible;
+    const uint32_t before = block_scan_256(part, s_warp, &feasible);
+    int32_t* gout = out + 10;
+    for (int k = (int)tid; k < max_c; k += 256) gout[k] = INT32_MIN;
+    if (feasible == 0) {
+        if (tid == 0) {
+            out[8] = -1;
+            out[9] = NGS_SCORE_MIN;
+        }
+    } else {
+        const uint32_t pick = (uint32_t)(splitmix64(seed_seq) % feasible);  // the pick-th feasible node in index order
+        if (pick >= before && pick < before + part) {
+            uint32_t acc = before;
+            for (uint32_t j = 0; j < gpt; j++) {
+                const uint32_t b = tid * gpt + j;
+                if (b >= gridDim.x) break;
+                const uint32_t c = __ldcg(cnt + b);
+                if (pick < acc + c) {
+                    s_pick_cta = b;
+                    s_pick_off = pick - acc;
+                    break;
+                }
+                acc += c;
+            }
+        }
+        __syncthreads();
+        const uint32_t cta = s_pick_cta, off = s_pick_off;
+        const uint32_t c2 = count_range(cta);
+        uint32_t tot2;
+        const uint32_t before2 = block_scan_256(c2, s_warp, &tot2);
+        if (off >= before2 && off < before2 + c2) {  // exactly one thread: the node is among its rows
+            uint32_t left = off - before2;
+            const uint32_t r0 = cta * per_cta + tid * rpt;
+            for (uint32_t j = 0; j < rpt; j++) {
+                const uint32_t row = r0 + j;
+                if (row >= T.n || !sample_row_feasible(T, row, &dem)) continue;
+                if (left-- != 0) continue;
+                // NodeInfo.Bind (node.go:70-84) with SampleRater.Choose (rater.go:28-50)
+                const int G = T.gcount[row];
+                uint32_t v[8];
+                ld_row8(T.free + (size_t)row * 8, v);
+                int f[8];
+#pragma unroll
+                for (int g = 0; g < 8; g++) f[g] = (int)v[g];
+                uint64_t emit = 0;
+                int n_emit = 0;
+                choose_sample<true>(f, G, &dem, &emit, &n_emit);  // places on f
+                int4* gp = reinterpret_cast<int4*>(T.free + (size_t)row * 8);
+                gp[0] = make_int4(f[0], f[1], f[2], f[3]);
+                gp[1] = make_int4(f[4], f[5], f[6], f[7]);
+                T.tag[row] = 0;
+                for (int k = 0; k < dem.C; k++) {
+                    const int e = (int)((emit >> (4 * k)) & 0xF);
+                    gout[k] = e == 0xF ? NGS_NOT_NEED_GPU : e;
+                }
+                out[8] = (int32_t)(T.first + row);
+                out[9] = 100;  // SampleRater.Rate (rater.go:24-26)
+                break;
+            }
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence_system();
+        *reinterpret_cast<volatile int32_t*>(out) = NGS_OK;
+    }
+}
 
 // out (mapped host memory): [0] status, [8] node, [9] score, [10 .. 10+max_c) gpu indexes
 __global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd, LoadParams lp, OneRec* rec, int32_t* out, int max_c) {

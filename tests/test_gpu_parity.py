@@ -659,7 +659,7 @@ def test_stats_counters(ngs):
         assert s1["d2h_bytes"] > s0["d2h_bytes"] and s1["h2d_bytes"] > s0["h2d_bytes"]
 
 
-@pytest.mark.parametrize("policy,load,hetero", [(0, False, False), (1, False, True), (0, True, True), (1, True, False)])
+@pytest.mark.parametrize("policy,load,hetero", [(0, False, False), (1, False, True), (0, True, True), (1, True, False), (2, False, True), (2, True, False)])
 def test_single_pod_kernel_matches_oracle_and_batch_kernel(ngs, policy, load, hetero):
     """a one-pod call takes K7 (one ordinary launch, polled answer): pod by pod it must give what the oracle
     gives and what the batch kernel K6 gives for the same pods in one call, and leave the same snapshot"""
@@ -675,11 +675,11 @@ def test_single_pod_kernel_matches_oracle_and_batch_kernel(ngs, policy, load, he
             fill_load_tables(oc, d, n, seed)
             fill_load_tables(o.OracleCluster(n), d6, n, seed)
             gl, ol = load_ctx_pair(ngs)
-        node6, score6, gidx6 = d6.schedule_batch(pc, nc, policy, load=gl)
+        node6, score6, gidx6 = d6.schedule_batch(pc, nc, policy, load=gl, seed=77, seq0=0)
         launches0 = d.stats()["kernel_launches"]
         for p in range(P):
-            node, score, gidx = d.schedule_batch(pc[p : p + 1], nc[p : p + 1], policy, load=gl)
-            onode, oscore, ogidx = oc.schedule_batch(pc[p : p + 1], nc[p : p + 1], policy, load=ol)
+            node, score, gidx = d.schedule_batch(pc[p : p + 1], nc[p : p + 1], policy, load=gl, seed=77, seq0=p)
+            onode, oscore, ogidx = oc.schedule_batch(pc[p : p + 1], nc[p : p + 1], policy, load=ol, seed=77, seq0=p)
             assert node[0] == onode[0] == node6[p], p
             assert score[0] == oscore[0] == score6[p], p
             assert np.array_equal(gidx[0], ogidx[0]) and np.array_equal(gidx[0], gidx6[p]), p
@@ -701,7 +701,23 @@ def test_single_pod_kernel_edge_cases(ngs):
         # a pod without containers binds to the best-rated node with an empty plan
         node, score, gidx = d.schedule_batch(np.zeros((1, 2), dtype=np.int32), [0], 0)
         assert node[0] >= 0 and (gidx[0] == np.iinfo(np.int32).min).all()
-        # many calls in a row reuse the record
-        for _ in range(50):
-            node, _, _ = d.schedule_batch(np.array([[100]], dtype=np.int32), [1], 0)
+        # many calls in a row reuse the record; the random policy shares it
+        for i in range(60):
+            node, _, _ = d.schedule_batch(np.array([[100]], dtype=np.int32), [1], i % 3, seed=5, seq0=i)
         assert node[0] >= 0
+        # random policy with nothing feasible, and on a cluster far larger than one row per thread
+        node, score, gidx = d.schedule_batch(np.array([[100, 100, 100]], dtype=np.int32), [3], 2)
+        assert node[0] == -1 and score[0] == 0
+    n = 400_000
+    from nano_gpu_scheduler_b200 import workloads as wl
+    gcount, free = wl.make_cluster(n, 0.7, 31)
+    oc = o.OracleCluster(n)
+    oc.load_snapshot(gcount, free)
+    with ngs.GpuDealer(n, device=0) as d:
+        d.snapshot_load(gcount, free)
+        for i in range(12):
+            dem = np.array([[60, 45]], dtype=np.int32)
+            got = d.schedule_batch(dem, [2], 2, seed=9, seq0=i)
+            want = oc.schedule_batch(dem, [2], 2, seed=9, seq0=i)
+            assert all(np.array_equal(a, b) for a, b in zip(got, want)), i
+        assert_same_snapshot(oc, d)
