@@ -299,7 +299,6 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
         // that half once it has finished batch i, which needs this rank's batch-i posts first.
         const size_t cur = (size_t)(h->xbatch & 1), nxt = cur ^ 1;
         CU(h, cudaMemsetAsync(h->d_xslots + nxt * XSLOT_HALF, 0, sizeof(unsigned long long) * XSLOT_HALF, h->stream));
-        CU(h, cudaMemsetAsync(h->d_gwin, 0, sizeof(unsigned long long) * (size_t)P, h->stream));
         for (int r = 0; r < h->world; r++) bp.xslots[r] = h->peer_xslots[r] + cur * XSLOT_HALF;
         h->xbatch++;
     }

@@ -42,10 +42,10 @@ struct BatchParams {
     ulonglong2* xw;            // [P] arg-max exchange words {x: atomicMax key, y: arrival counter}, zero before launch
     // node-range sharding over the GPUs of one box: every rank runs this same kernel on
     // its own rows; CTA 0 of each rank trades the rank's result with the peers through
-    // peer-mapped memory (plain 8-byte stores over NVLink), then tells its own CTAs
+    // peer-mapped memory (plain 8-byte stores over NVLink); every CTA reads the ranks' words from there
     uint32_t world, rank;
     unsigned long long* xslots[NGS_MAX_RANKS];  // [rank r] -> r's slot array [P][NGS_MAX_RANKS] (this batch's parity half)
-    unsigned long long* gwin;                   // [P] this rank's copy of the global result, zero before launch
+    unsigned long long* gwin;                   // (unused since every CTA reads the slot array itself)
     uint32_t keys_stride, done_stride, xw_stride;  // distance between consecutive pods, in elements of each array
     int32_t* status_out;       // optional host-visible copy of the error word, written when the kernel ends
     int32_t* err;              // device error word (0 = ok)
@@ -302,6 +302,15 @@ __device__ __forceinline__ unsigned long long cross_rank_exchange(const BatchPar
         st_relaxed_sys_u64(bp.xslots[lane] + (size_t)p * NGS_MAX_RANKS + bp.rank, mine | KEY_VALID);
         got = wait_valid(bp.xslots[bp.rank] + (size_t)p * NGS_MAX_RANKS + lane, bp.err, dead);
     }
+    dead = __any_sync(0xFFFFFFFFu, dead);
+    return got;
+}
+
+// every other CTA: the ranks' words straight from this rank's slot array (CTA 0 posts our own word there,
+// too), so the result needs no relay through a second location.  Same return convention.
+__device__ __forceinline__ unsigned long long collect_ranks(const BatchParams& bp, uint32_t p, uint32_t lane, bool& dead) {
+    unsigned long long got = 0;
+    if (lane < bp.world) got = wait_valid(bp.xslots[bp.rank] + (size_t)p * NGS_MAX_RANKS + lane, bp.err, dead);
     dead = __any_sync(0xFFFFFFFFu, dead);
     return got;
 }
@@ -703,26 +712,15 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                 uint64_t total = ltotal, before_rank = 0;
                 if (bp.world > 1) {
                     // K5: ranks trade their totals; rank r's feasible rows follow those of ranks < r
-                    unsigned long long packed = 0;
-                    if (blockIdx.x == 0) {
-                        const unsigned long long cj = cross_rank_exchange(bp, p, ltotal, lane, dead);
-                        unsigned long long inc2 = cj;
+                    const unsigned long long cj = blockIdx.x == 0 ? cross_rank_exchange(bp, p, ltotal, lane, dead) : collect_ranks(bp, p, lane, dead);
+                    unsigned long long inc2 = cj;
 #pragma unroll
-                        for (int o = 1; o < 32; o <<= 1) {
-                            const unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, inc2, o);
-                            if (lane >= (uint32_t)o) inc2 += t;
-                        }
-                        const unsigned long long gt = __shfl_sync(0xFFFFFFFFu, inc2, 31);
-                        const unsigned long long bf = __shfl_sync(0xFFFFFFFFu, inc2 - cj, bp.rank);
-                        packed = (gt << 31) | bf;
-                        if (lane == 0) st_relaxed_u64(bp.gwin + p, packed | KEY_VALID);
-                    } else {
-                        if (lane == 0) packed = wait_valid(bp.gwin + p, bp.err, dead);
-                        packed = __shfl_sync(0xFFFFFFFFu, packed, 0);
-                        dead = __any_sync(0xFFFFFFFFu, dead);
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, inc2, o);
+                        if (lane >= (uint32_t)o) inc2 += t;
                     }
-                    total = packed >> 31;
-                    before_rank = packed & 0x7FFFFFFFull;
+                    total = __shfl_sync(0xFFFFFFFFu, inc2, 31);
+                    before_rank = __shfl_sync(0xFFFFFFFFu, inc2 - cj, bp.rank);
                 }
                 if (total == 0) {
                     if (blockIdx.x == 0 && lane == 0) publish_none(bp, p);
@@ -849,12 +847,10 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                         mloc = __shfl_sync(0xFFFFFFFFu, mloc, 0);
                         dead = __any_sync(0xFFFFFFFFu, dead);
                         const uint64_t mg = warp_max_u64(cross_rank_exchange(bp, p, mloc, lane, dead));
-                        if (lane == 0) {
-                            st_relaxed_u64(bp.gwin + p, mg | KEY_VALID);
-                            s_win = mg;
-                        }
-                    } else if (lane == 0) {
-                        s_win = wait_valid(bp.gwin + p, bp.err, dead);
+                        if (lane == 0) s_win = mg;
+                    } else {
+                        const uint64_t mg = warp_max_u64(collect_ranks(bp, p, lane, dead));
+                        if (lane == 0) s_win = mg;
                     }
                     if (dead && lane == 0) s_abort = 1;
                     if (stage) {
