@@ -828,13 +828,16 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                         stg0 = __ldcg(src + lane);
                         if (lane + 32 < sizeof(SortedDemand) / 4) stg1 = __ldcg(src + lane + 32);
                     }
-                    if (lane == 0) {
+                    const bool solo = gridDim.x == 1 && bp.world == 1;  // one CTA holds every row: nothing to trade
+                    if (lane == 0 && !solo) {
                         const unsigned long long old = atomicMax(&xw->x, (unsigned long long)v);
                         const unsigned long long one = 1ull + (old >> 63);  // bit 63 is never set: always 1
                         asm volatile("red.relaxed.gpu.global.add.u64 [%0], %1;" ::"l"(&xw->y), "l"(one) : "memory");
                     }
                     PHASE(2);
-                    if (bp.world == 1) {
+                    if (solo) {
+                        if (lane == 0) s_win = v;
+                    } else if (bp.world == 1) {
                         if (lane == 0) {
                             unsigned long long m;
                             dead = !wait_exchange(xw, gridDim.x, bp.err, &m);
