@@ -92,7 +92,6 @@ struct ngs_dealer {
     int world = 1, rank = 0;
     unsigned long long* d_xslots = nullptr;               // own buffer: [2 parities][BATCH_CHUNK][NGS_MAX_RANKS]
     unsigned long long* peer_xslots[NGS_MAX_RANKS] = {};  // peer-mapped bases (own entry = d_xslots)
-    unsigned long long* d_gwin = nullptr;                 // [BATCH_CHUNK]
     uint64_t xbatch = 0;                                  // launches so far: selects the parity half
     ngs_stats_t stats{};
     unsigned long long* d_dbg = nullptr;  // profiling builds only
@@ -291,7 +290,6 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     bp.status_out = status_out;
     bp.world = (uint32_t)h->world;
     bp.rank = (uint32_t)h->rank;
-    bp.gwin = h->d_gwin;
     for (int r = 0; r < NGS_MAX_RANKS; r++) bp.xslots[r] = nullptr;
     if (h->world > 1) {
         // Parity halves instead of a cross-rank barrier per batch: batch i uses half i&1 on every
@@ -435,7 +433,7 @@ int ngs_destroy(ngs_dealer* h) {
     cudaFree(h->d_err); cudaFreeHost(h->h_err);
     for (int r = 0; r < NGS_MAX_RANKS; r++)
         if (h->peer_xslots[r] && r != h->rank) cudaIpcCloseMemHandle(h->peer_xslots[r]);
-    cudaFree(h->d_xslots); cudaFree(h->d_gwin); cudaFree(h->d_rel);
+    cudaFree(h->d_xslots); cudaFree(h->d_rel);
     cudaFree(h->d_dbg);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -826,6 +824,9 @@ int ngs_schedule_batch(ngs_dealer* h, uint32_t n_pods, const int32_t* percent, c
             k_schedule_one<<<grid, 256, 0, h->stream>>>(h->T, pd, lp, h->d_one, h->d_pod_out_dev, max_c);
         CU(h, cudaGetLastError());
         for (uint32_t spins = 1; hout[0] == ONE_PENDING; spins++) {
+#if defined(__x86_64__) || defined(__i386__)
+            __builtin_ia32_pause();
+#endif
             if ((spins & 0xFFFu) == 0) {  // now and then make sure the kernel is still alive
                 const cudaError_t q = cudaStreamQuery(h->stream);
                 if (q == cudaSuccess) break;
@@ -882,9 +883,7 @@ int ngs_xchg_export(ngs_dealer* h, void* handle_out) {
     CU(h, cudaSetDevice(h->device));
     if (!h->d_xslots) {
         CU(h, cudaMalloc(&h->d_xslots, sizeof(unsigned long long) * 2 * XSLOT_HALF));
-        CU(h, cudaMalloc(&h->d_gwin, sizeof(unsigned long long) * BATCH_CHUNK));
         CU(h, cudaMemset(h->d_xslots, 0, sizeof(unsigned long long) * 2 * XSLOT_HALF));
-        CU(h, cudaMemset(h->d_gwin, 0, sizeof(unsigned long long) * BATCH_CHUNK));
         CU(h, cudaDeviceSynchronize());  // cleared before any peer can learn the handle
     }
     cudaIpcMemHandle_t mh;
@@ -1060,7 +1059,6 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     bp.status_out = nullptr;
     bp.world = 1;
     bp.rank = 0;
-    bp.gwin = nullptr;
     bp.err = err;
     bp.rows_per_block = rpb;
     void* args[] = {&bp};

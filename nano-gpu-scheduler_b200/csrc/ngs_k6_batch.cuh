@@ -45,7 +45,6 @@ struct BatchParams {
     // peer-mapped memory (plain 8-byte stores over NVLink); every CTA reads the ranks' words from there
     uint32_t world, rank;
     unsigned long long* xslots[NGS_MAX_RANKS];  // [rank r] -> r's slot array [P][NGS_MAX_RANKS] (this batch's parity half)
-    unsigned long long* gwin;                   // (unused since every CTA reads the slot array itself)
     uint32_t keys_stride, done_stride, xw_stride;  // distance between consecutive pods, in elements of each array
     int32_t* status_out;       // optional host-visible copy of the error word, written when the kernel ends
     int32_t* err;              // device error word (0 = ok)

@@ -162,7 +162,7 @@ struct Scanner {
 
     // skip any value (unknown keys, ignored sub-trees); *kind gets the Go name of what was there
     bool skip(const char** kind = nullptr, int depth = 0) {
-        if (depth > 10000) { err = "exceeded max depth"; return false; }
+        if (depth > 1000) { err = "exceeded max depth"; return false; }  // (Go allows 10000: its stacks grow, this one does not)
         const char c = peek("looking for beginning of value");
         if (!c) return false;
         const char* k = "";
