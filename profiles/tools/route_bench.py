@@ -11,7 +11,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 from tests import extender_util as x  # noqa: E402
-from tests.test_gpu_routes import Routes, node_name  # noqa: E402
+from nano_gpu_scheduler_b200.routes import Routes, node_name  # noqa: E402
 
 
 def main():

@@ -1,98 +1,11 @@
-"""ctypes access to the extender wire codec (nano-gpu-scheduler_b200/host/extender_codec_c.cpp) and a
-Python restatement of Go 1.16 encoding/json's output rules — the checker the C++ encoder is compared
-with byte for byte.  Go itself is not in this image, so this pins the codec against the published
-rules (encode.go: escapeHTML on, \\u00xx for control bytes, \\ufffd for invalid UTF-8, U+2028/9
-escaped, map keys sorted), not against a Go run."""
-import ctypes as C
-import json
-import os
-
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-HOST_LIB = os.path.join(ROOT, "nano-gpu-scheduler_b200", "libngs_dealer_host.so")
-
-_lib = None
-
-
-def lib():
-    global _lib
-    if _lib is None:
-        L = C.CDLL(HOST_LIB)
-        for name in ("ngsx_decode_args", "ngsx_decode_binding", "ngsx_json_string", "ngsx_encode_filter", "ngsx_encode_filter_error",
-                     "ngsx_encode_binding_result", "ngsx_encode_priorities", "ngsx_routes_predicate", "ngsx_routes_prioritize"):
-            getattr(L, name).restype = C.c_void_p
-        L.ngsx_routes_new.restype = C.c_void_p
-        L.ngsx_free.argtypes = [C.c_void_p]
-        _lib = L
-    return _lib
-
-
-def _take(ptr, n):
-    out = C.string_at(ptr, n.value)
-    lib().ngsx_free(ptr)
-    return out
-
-
-def _b(s):
-    return s if isinstance(s, bytes) else s.encode("utf-8", "surrogatepass")
-
-
-def decode_args(body):
-    body = _b(body)
-    n = C.c_size_t()
-    return json.loads(_take(lib().ngsx_decode_args(body, C.c_size_t(len(body)), C.byref(n)), n))
-
-
-def decode_binding(body):
-    body = _b(body)
-    n = C.c_size_t()
-    return json.loads(_take(lib().ngsx_decode_binding(body, C.c_size_t(len(body)), C.byref(n)), n))
-
-
-def json_string(s):
-    s = _b(s)
-    n = C.c_size_t()
-    return _take(lib().ngsx_json_string(s, C.c_size_t(len(s)), C.byref(n)), n)
-
-
-def quantity(s):
-    s = _b(s)
-    v = C.c_int64()
-    ok = lib().ngsx_quantity(s, C.c_size_t(len(s)), C.byref(v))
-    return v.value if ok else None
-
-
-def _blob(strings):
-    bs = [_b(s) for s in strings]
-    lens = (C.c_uint32 * max(len(bs), 1))(*[len(x) for x in bs])
-    return b"".join(bs), lens
-
-
-def encode_filter(can, failed):
-    flat = list(can)
-    for k, m in failed:
-        flat += [k, m]
-    blob, lens = _blob(flat)
-    n = C.c_size_t()
-    return _take(lib().ngsx_encode_filter(blob, lens, len(can), len(failed), C.byref(n)), n)
-
-
-def encode_filter_error(msg):
-    msg = _b(msg)
-    n = C.c_size_t()
-    return _take(lib().ngsx_encode_filter_error(msg, C.c_size_t(len(msg)), C.byref(n)), n)
-
-
-def encode_binding_result(msg):
-    msg = _b(msg)
-    n = C.c_size_t()
-    return _take(lib().ngsx_encode_binding_result(msg, C.c_size_t(len(msg)), C.byref(n)), n)
-
-
-def encode_priorities(hosts, scores):
-    blob, lens = _blob(hosts)
-    sc = (C.c_int32 * max(len(scores), 1))(*scores)
-    n = C.c_size_t()
-    return _take(lib().ngsx_encode_priorities(blob, lens, sc, len(hosts), C.byref(n)), n)
+"""A Python restatement of Go 1.16 encoding/json's output rules — the checker the C++ encoder
+(nano-gpu-scheduler_b200/host/extender_codec.cpp, bound by nano_gpu_scheduler_b200.routes) is compared with byte
+for byte.  Go itself is not in this image, so this pins the codec against the published rules (encode.go:
+escapeHTML on, \\u00xx for control bytes, \\ufffd for invalid UTF-8, U+2028/9 escaped, map keys sorted), not
+against a Go run."""
+from nano_gpu_scheduler_b200.routes import (HOST_LIB, Routes, _b, _take, decode_args, decode_binding, encode_binding_result,  # noqa: F401
+                                            encode_filter, encode_filter_error, encode_priorities, json_string, lib, node_name,
+                                            quantity)
 
 
 # ---- Go 1.16 encoding/json, restated --------------------------------------------------------------

@@ -3,14 +3,13 @@ name resolution -> ngs_assume / ngs_score on the device -> JSON body out, compar
 what the reference would marshal for the ORACLE's verdicts on the same cluster (pkg/routes/routes.go:40-123,
 pkg/scheduler/predicate.go:21-38, priority.go:30-37, failure texts of pkg/dealer/rater.go:47,99,152 and
 dealer.go:102)."""
-import ctypes as C
 import json
-import time
 
 import numpy as np
 import pytest
 
 import oracle as o
+from nano_gpu_scheduler_b200.routes import Routes, node_name
 from tests import extender_util as x
 
 pytestmark = pytest.mark.gpu
@@ -21,53 +20,6 @@ def _built(built):
     import nano_gpu_scheduler_b200.build as b
 
     b.build_host()
-
-
-def node_name(i):
-    return "node-%06d" % i
-
-
-class Routes:
-    def __init__(self, gcount, rater, assumed=(), load=False):
-        self.L = x.lib()
-        g = np.ascontiguousarray(gcount, dtype=np.uint8)
-        self.h = C.c_void_p(self.L.ngsx_routes_new(len(g), g.ctypes.data_as(C.c_void_p)))
-        for node, uid, percent, gpu_idx in assumed:
-            pc = (C.c_int32 * len(percent))(*percent)
-            gi = (C.c_int32 * len(percent))(*gpu_idx)
-            self.L.ngsx_routes_add_assumed(self.h, node, uid.encode(), pc, gi, len(percent))
-        err = C.c_char_p()
-        t0 = time.perf_counter()
-        rc = self.L.ngsx_routes_start(self.h, rater, len(g) + 8, 0, int(load), C.byref(err))
-        self.start_ms = (time.perf_counter() - t0) * 1e3  # NewDealer: list the assumed pods, rebuild their nodes
-        assert rc == 0, err.value
-
-    def close(self):
-        self.L.ngsx_routes_destroy(self.h)
-
-    def predicate(self, body):
-        body = body if isinstance(body, bytes) else body.encode()
-        n = C.c_size_t()
-        return x._take(self.L.ngsx_routes_predicate(self.h, body, C.c_size_t(len(body)), C.byref(n)), n)
-
-    def prioritize(self, body):
-        body = body if isinstance(body, bytes) else body.encode()
-        n = C.c_size_t()
-        p = C.c_int()
-        out = x._take(self.L.ngsx_routes_prioritize(self.h, body, C.c_size_t(len(body)), C.byref(n), C.byref(p)), n)
-        return out, bool(p.value)
-
-    def counters(self):
-        c = (C.c_uint64 * 7)()
-        self.L.ngsx_routes_counters(self.h, c)
-        return dict(requests=c[0], cache_hits=c[1], all_rows=c[2], ns_decode=c[3], ns_resolve=c[4], ns_dealer=c[5], ns_encode=c[6])
-
-    def bind(self, node, uid, percent):
-        pc = (C.c_int32 * len(percent))(*percent)
-        out = (C.c_int32 * len(percent))()
-        err = C.c_char_p()
-        rc = self.L.ngsx_routes_bind(self.h, node.encode(), uid.encode(), pc, len(percent), out, C.byref(err))
-        return rc, list(out), err.value
 
 
 def demand_str(d):
