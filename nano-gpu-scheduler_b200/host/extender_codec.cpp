@@ -49,7 +49,7 @@ struct Scanner {
     // after ws(): the next byte, or 0 at the end (with the EOF error set)
     char peek(const char* context) {
         ws();
-        if (p >= end) {
+        if (p >= end || *p == 0) {  // (a NUL byte is an invalid character wherever a token is expected)
             syntax(context);
             return 0;
         }

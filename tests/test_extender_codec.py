@@ -115,6 +115,7 @@ GO_ERRORS = [
     (b'{"NodeNames": ["a"', "unexpected EOF"),
     (b'{"NodeNames": ["a', "unexpected EOF"),
     (b"x", "invalid character 'x' looking for beginning of value"),
+    (b'{"a":\x00}', "invalid character '\\x00' looking for beginning of value"),
     (b'{"a" 1}', "invalid character '1' after object key"),
     (b'{"a":1 "b":2}', "invalid character '\"' after object key:value pair"),
     (b'{"NodeNames":["a" "b"]}', "invalid character '\"' after array element"),
@@ -180,3 +181,63 @@ def test_routes_fail_loudly_without_a_gpu():
     err = C.c_char_p()
     assert L.ngsx_routes_start(h, 0, 16, 0, 0, C.byref(err)) == 1 and b"CUDA" in err.value  # no CPU fallback behind the routes
     L.ngsx_routes_destroy(h)
+
+
+def test_decode_fuzz_against_python_json():
+    """random well-formed bodies (any unicode, either escaping style, any indentation, extra members) read the same
+    as Python's json reads them; random byte damage to such bodies never crashes the scanner"""
+    from hypothesis import given, settings
+    from hypothesis import strategies as st
+
+    names = st.lists(st.text(max_size=24), max_size=40)
+    junk = st.recursive(st.none() | st.booleans() | st.integers(-10**6, 10**6) | st.floats(allow_nan=False, allow_infinity=False) | st.text(max_size=8),
+                        lambda ch: st.lists(ch, max_size=4) | st.dictionaries(st.text(max_size=6), ch, max_size=4), max_leaves=12)
+
+    @settings(max_examples=150, deadline=None)
+    @given(names, st.lists(st.one_of(st.none(), st.integers(0, 400)), max_size=6), st.dictionaries(st.text(max_size=10), st.text(max_size=10), max_size=5),
+           junk, st.booleans(), st.sampled_from([None, 0, 3]))
+    def run(node_names, percents, annotations, extra, ascii_only, indent):
+        pod = x.pod_json(percents, name="pé", uid="uid-日")
+        pod["metadata"]["annotations"] = annotations
+        body = json.dumps({"zz": extra, "Pod": pod, "NodeNames": node_names, "aa": [extra]}, ensure_ascii=ascii_only, indent=indent)
+        d = x.decode_args(body.encode("utf-8", "surrogatepass"))
+        want_names = [s.encode("utf-8", "surrogatepass").decode("utf-8", "replace") if not ascii_only else s for s in node_names]
+        if ascii_only:  # lone surrogates arrive as \\udXXX escapes: Go makes them U+FFFD
+            want_names = ["".join("�" if 0xD800 <= ord(c) < 0xE000 else c for c in s) for s in node_names]
+        assert d["err"] == ""
+        if not ascii_only and any(0xD800 <= ord(c) < 0xE000 for s in node_names for c in s):
+            return  # raw surrogate bytes are invalid UTF-8: one U+FFFD per bad byte, not per character
+        assert d["node_names"] == want_names
+        assert [c["percent"] for c in d["pod"]["containers"]] == [p or 0 for p in percents]
+        assert [c["has"] for c in d["pod"]["containers"]] == [p is not None for p in percents]
+        if all(not (0xD800 <= ord(c) < 0xE000) for k, v in annotations.items() for c in k + v):
+            assert d["pod"]["annotations"] == annotations
+
+    run()
+
+    rng = random.Random(11)
+    base = json.dumps({"Pod": x.pod_json([20, 40]), "NodeNames": ["node-%06d" % i for i in range(50)]}).encode()
+    for _ in range(3000):
+        b = bytearray(base)
+        for _ in range(rng.randrange(1, 4)):
+            i = rng.randrange(len(b))
+            op = rng.randrange(3)
+            if op == 0:
+                b[i] = rng.randrange(256)
+            elif op == 1:
+                del b[i:i + rng.randrange(1, 20)]
+            else:
+                b[i:i] = bytes(rng.randrange(256) for _ in range(rng.randrange(1, 6)))
+        d = x.decode_args(bytes(b))  # must come back (error text or not)
+        assert isinstance(d["err"], str)
+        try:
+            ok = json.loads(bytes(b).decode("utf-8"))
+        except Exception:
+            ok = None
+        if d["err"] == "" and ok is None:
+            # the scanner accepted something Python rejects: only allowed for invalid UTF-8 (Go substitutes U+FFFD),
+            # trailing bytes after the first value (json.Decoder reads one value) or lone-surrogate escapes
+            try:
+                json.loads(bytes(b).decode("utf-8", "replace"))
+            except json.JSONDecodeError as e:
+                assert "Extra data" in str(e), bytes(b)
