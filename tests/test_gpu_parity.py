@@ -721,3 +721,70 @@ def test_single_pod_kernel_edge_cases(ngs):
             want = oc.schedule_batch(dem, [2], 2, seed=9, seq0=i)
             assert all(np.array_equal(a, b) for a, b in zip(got, want)), i
         assert_same_snapshot(oc, d)
+
+
+def _overfull_cluster(n, seed):
+    """free percents as stray Releases can leave them (GPUs.Release adds without an upper bound, allocate.go:120-131):
+    most cells in 0..100, some in 101..300, a few up to NGS_MAX_FREE"""
+    rng = np.random.default_rng(seed)
+    gcount = rng.integers(1, 9, size=n).astype(np.uint8)
+    kind = rng.random((n, 8))
+    free = np.where(kind < 0.7, rng.integers(0, 101, (n, 8)), np.where(kind < 0.9, rng.integers(101, 301, (n, 8)), rng.integers(1000, 65536, (n, 8))))
+    free = np.where(np.arange(8)[None, :] < gcount[:, None], free, 0).astype(np.int32)
+    return gcount, free
+
+
+DEMAND_VALUES = np.array([0, 5, 50, 100, 101, 150, 254, 255, 256, 300, 999, 40000, 65535], dtype=np.int32)
+
+
+@pytest.mark.parametrize("policy", ["binpack", "spread", "random"])
+def test_free_percent_beyond_100(ngs, policy):
+    """rows above 100 % free: negative 'used' in Binpack.Rate (fp64 path, no table), large Spread rates, demands
+    beyond one byte (the top-4 shortcut saturates at 255 and must fall back), u16 rows in the batch kernel"""
+    n = 3000
+    gcount, free = _overfull_cluster(n, 77)
+    oc = o.OracleCluster(n)
+    oc.load_snapshot(gcount, free)
+    rng = np.random.default_rng(5)
+    with ngs.GpuDealer(n, device=0) as d:
+        d.snapshot_load(gcount, free)
+        for trial in range(20):
+            demand = rng.choice(DEMAND_VALUES, size=int(rng.integers(1, 5)))
+            a = d.assume(demand, POL[policy], want_plan=True)
+            b = oc.assume(demand, POL[policy], want_plan=True)
+            for k in ("feasible", "reason", "score", "n_emitted", "plan"):
+                assert np.array_equal(a[k], b[k]), (policy, trial, k, demand)
+            a2 = d.assume(demand, POL[policy])  # the streaming scan
+            assert np.array_equal(a2["feasible"], b["feasible"]) and np.array_equal(a2["score"], b["score"])
+        P = 150
+        pc = rng.choice(DEMAND_VALUES, size=(P, 4)).astype(np.int32)
+        nc = rng.integers(1, 5, size=P).astype(np.int32)
+        got = d.schedule_batch(pc, nc, POL[policy], seed=3)
+        want = oc.schedule_batch(pc, nc, POL[policy], seed=3)
+        assert all(np.array_equal(x, y) for x, y in zip(got, want))
+        assert (got[0] >= 0).any()
+        for p in range(40):  # and pod by pod through the single-pod kernel
+            got = d.schedule_batch(pc[p : p + 1], nc[p : p + 1], POL[policy], seed=8, seq0=p)
+            want = oc.schedule_batch(pc[p : p + 1], nc[p : p + 1], POL[policy], seed=8, seq0=p)
+            assert all(np.array_equal(x, y) for x, y in zip(got, want)), p
+        assert_same_snapshot(oc, d)
+
+
+@pytest.mark.parametrize("policy", ["binpack", "spread", "random"])
+def test_batch_with_up_to_twelve_containers(ngs, policy):
+    """NGS_MAX_CONTAINERS-wide pods through K6 and K7 (Go's sort.Sort switches from insertion sort to quicksort
+    above 12 elements, so 12 is the widest demand the reference sorts the simple way)"""
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    n, P = 1500, 120
+    oc, d, _, _ = make_pair(ngs, n, 0.35, 0xC12, hetero=True)
+    pc, nc = wl.make_pods(P, 6, 12, 0, 8, 0xC12, max_c=12)
+    with d:
+        got = d.schedule_batch(pc[:80], nc[:80], POL[policy], seed=1)
+        want = oc.schedule_batch(pc[:80], nc[:80], POL[policy], seed=1)
+        assert all(np.array_equal(x, y) for x, y in zip(got, want))
+        for p in range(80, P):
+            got = d.schedule_batch(pc[p : p + 1], nc[p : p + 1], POL[policy], seed=1, seq0=p)
+            want = oc.schedule_batch(pc[p : p + 1], nc[p : p + 1], POL[policy], seed=1, seq0=p)
+            assert all(np.array_equal(x, y) for x, y in zip(got, want)), p
+        assert_same_snapshot(oc, d)
