@@ -788,3 +788,45 @@ def test_batch_with_up_to_twelve_containers(ngs, policy):
             want = oc.schedule_batch(pc[p : p + 1], nc[p : p + 1], POL[policy], seed=1, seq0=p)
             assert all(np.array_equal(x, y) for x, y in zip(got, want)), p
         assert_same_snapshot(oc, d)
+
+
+PERIOD_LISTS = [
+    [(1, 320 * 10**9), (0, 320 * 10**9)],                                      # memory before core
+    [(0, 320 * 10**9)],                                                        # core only
+    [(1, 50 * 10**9)],                                                         # memory only, a window most samples miss
+    [(0, 320 * 10**9), (0, 60 * 10**9), (1, 320 * 10**9), (1, 10**9)],          # NGS_MAX_PERIODS entries, metrics repeated
+    [],                                                                        # load scheduling on, empty SyncPeriod
+    [(0, 10**18), (1, -(10**12))],                                             # a window that always / never holds
+]
+
+
+@pytest.mark.parametrize("periods", PERIOD_LISTS, ids=lambda p: "periods%d" % len(p))
+def test_load_mode_with_other_period_lists(ngs, periods):
+    """PolicySpec.SyncPeriod lists other than the deployed (core, memory) pair take the general LoadUsage path
+    (allocate.go:173-195 loops over whatever the list holds, in its order)"""
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    n = 2500
+    oc, d, _, _ = make_pair(ngs, n, 0.5, 0x9E, hetero=True)
+    with d:
+        fill_load_tables(oc, d, n, 0x9E, stale_frac=0.15, absent_frac=0.05)
+        gl, ol = load_ctx_pair(ngs, periods=periods)
+        for policy in (0, 1):
+            for demand in ([30], [20, 40, 0], [100, 100]):
+                a = d.assume(demand, policy, load=gl, want_plan=True)
+                b = oc.assume(demand, policy, load=ol, want_plan=True)
+                for k in ("feasible", "score", "n_emitted", "plan"):
+                    assert np.array_equal(a[k], b[k]), (policy, demand, k)
+                a2 = d.assume(demand, policy, load=gl)
+                assert np.array_equal(a2["score"], b["score"])
+                assert_same_snapshot(oc, d)
+        pc, nc = wl.make_pods(90, 1, 3, 1, 12, 0x9E)
+        for policy in (0, 1, 2):
+            got = d.schedule_batch(pc[:60], nc[:60], policy, load=gl, seed=2)
+            want = oc.schedule_batch(pc[:60], nc[:60], policy, load=ol, seed=2)
+            assert all(np.array_equal(x, y) for x, y in zip(got, want)), policy
+            for p in range(60, 90):
+                got = d.schedule_batch(pc[p : p + 1], nc[p : p + 1], policy, load=gl, seed=2, seq0=p)
+                want = oc.schedule_batch(pc[p : p + 1], nc[p : p + 1], policy, load=ol, seed=2, seq0=p)
+                assert all(np.array_equal(x, y) for x, y in zip(got, want)), (policy, p)
+            assert_same_snapshot(oc, d)
