@@ -646,10 +646,10 @@ static int launch_scan(ngs_dealer* h, uint32_t n, const PodDemand& pd, const Loa
         if (grid > max_grid) grid = max_grid;
         k_assume<false><<<grid, 256, 0, h->stream>>>(h->T, nullptr, n, pd, lp, MODE_ASSUME, gen, d_feas, d_reason, d_score, nullptr, nullptr);
     } else {
-        const size_t smem = (size_t)NGS_SCAN_STAGES_PLAIN * scan_stage_bytes<false>();
-        uint32_t grid = (uint32_t)h->num_sms * NGS_SCAN_BLOCKS_PLAIN;
+        const size_t smem = (size_t)NGS_SCAN_STAGES * SCAN_STAGE_BYTES;
+        uint32_t grid = (uint32_t)h->num_sms * NGS_SCAN_BLOCKS;
         if (grid > ntiles) grid = ntiles;
-        k_scan_tma<false><<<grid, SCAN_TILE, smem, h->stream>>>(h->T, n, pd, lp, gen, d_feas, d_reason, d_score);
+        k_scan_tma<<<grid, SCAN_TILE, smem, h->stream>>>(h->T, n, pd, lp, d_feas, d_reason, d_score);
     }
     CU(h, cudaGetLastError());
     return NGS_OK;

@@ -68,30 +68,24 @@ __global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables
 }
 
 // ---------------------------------------------------------------------------------------------
-// K1, streaming form: the same evaluation as k_assume for "all rows, no per-node plans", with the
-// row data staged through shared memory by the TMA engine (1-D bulk copies, cp.async.bulk +
-// mbarrier transaction counts) in a 2- or 3-stage ring of 256-row tiles, so that several tiles of every
-// table are in flight per CTA while the threads evaluate the tile that has landed.
+// K1, streaming form: the same evaluation as k_assume for "all rows, no per-node plans, load
+// scheduling off", with the row data staged through shared memory by the TMA engine (1-D bulk
+// copies, cp.async.bulk + mbarrier transaction counts) in a ring of 256-row tiles, so that several
+// tiles of every table are in flight per CTA while the threads evaluate the tile that has landed.
+// (The load-aware pass does more arithmetic per row and measured faster with k_assume's direct
+// 256-bit loads at full occupancy than with this staging at 2-3 CTAs per SM: DESIGN.md, K1.)
 // ---------------------------------------------------------------------------------------------
 constexpr int SCAN_TILE = 256;
-#ifndef NGS_SCAN_STAGES_LOAD
-#define NGS_SCAN_STAGES_LOAD 2
+#ifndef NGS_SCAN_STAGES
+#define NGS_SCAN_STAGES 2
 #endif
-#ifndef NGS_SCAN_STAGES_PLAIN
-#define NGS_SCAN_STAGES_PLAIN 2
+#ifndef NGS_SCAN_BLOCKS
+#define NGS_SCAN_BLOCKS 6  // resident CTAs per SM
 #endif
-#ifndef NGS_SCAN_BLOCKS_LOAD
-#define NGS_SCAN_BLOCKS_LOAD 3
-#endif
-constexpr uint32_t SCAN_FREE_BYTES = SCAN_TILE * 8 * 4;    // 8 KB
-constexpr uint32_t SCAN_GC_BYTES = SCAN_TILE;              // 256 B
-constexpr uint32_t SCAN_RL_BYTES = SCAN_TILE * 8;          // 2 KB   (pass without load scheduling)
-constexpr uint32_t SCAN_TENTHS_BYTES = SCAN_TILE * 8;      // 2 KB per metric (load-aware pass)
-constexpr uint32_t SCAN_TS_BYTES = SCAN_TILE * 8 * 4;      // 8 KB per metric (load-aware pass)
-template <bool LOAD>
-__host__ __device__ constexpr uint32_t scan_stage_bytes() {
-    return SCAN_FREE_BYTES + SCAN_GC_BYTES + (LOAD ? 2 * SCAN_TENTHS_BYTES + 2 * SCAN_TS_BYTES : SCAN_RL_BYTES);
-}
+constexpr uint32_t SCAN_FREE_BYTES = SCAN_TILE * 8 * 4;  // 8 KB
+constexpr uint32_t SCAN_GC_BYTES = SCAN_TILE;            // 256 B
+constexpr uint32_t SCAN_RL_BYTES = SCAN_TILE * 8;        // 2 KB
+constexpr uint32_t SCAN_STAGE_BYTES = SCAN_FREE_BYTES + SCAN_GC_BYTES + SCAN_RL_BYTES;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -120,67 +114,46 @@ __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem
                  : "memory");
 }
 
-#ifndef NGS_SCAN_BLOCKS_PLAIN
-#define NGS_SCAN_BLOCKS_PLAIN 6
-#endif
-template <bool LOAD>
-__global__ void __launch_bounds__(SCAN_TILE, LOAD ? NGS_SCAN_BLOCKS_LOAD : NGS_SCAN_BLOCKS_PLAIN) k_scan_tma(Tables T, uint32_t n, PodDemand pd, LoadParams lp_in, uint32_t gen,
-                                                                        uint8_t* __restrict__ feasible, int8_t* __restrict__ reason,
-                                                                        int32_t* __restrict__ score) {
+__global__ void __launch_bounds__(SCAN_TILE, NGS_SCAN_BLOCKS) k_scan_tma(Tables T, uint32_t n, PodDemand pd, LoadParams lp_in,
+                                                                       uint8_t* __restrict__ feasible, int8_t* __restrict__ reason,
+                                                                       int32_t* __restrict__ score) {
     extern __shared__ __align__(128) unsigned char tiles[];
     __shared__ SortedDemand dem;
-    __shared__ double s_pair[121];
-    constexpr int SCAN_STAGES = LOAD ? NGS_SCAN_STAGES_LOAD : NGS_SCAN_STAGES_PLAIN;
-    __shared__ __align__(8) uint64_t bars[SCAN_STAGES];
-    constexpr uint32_t STAGE = scan_stage_bytes<LOAD>();
+    __shared__ __align__(8) uint64_t bars[NGS_SCAN_STAGES];
     const uint32_t tid = threadIdx.x;
     const uint32_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
-    const bool want_rl = !LOAD && !T.rl_zero;
+    const bool want_rl = !T.rl_zero;
     LoadParams lp = lp_in;
-    if (!LOAD) lp.enabled = 0;  // a compile-time fact for this instantiation: the LoadUsage code drops out
+    lp.enabled = 0;  // a compile-time fact for this kernel: the LoadUsage code drops out of the row evaluation
 
     // one thread issues the copies of a tile: every table's 256-row slice is one contiguous range
     auto issue = [&](uint32_t tile, uint32_t stage) {
-        unsigned char* base = tiles + (size_t)stage * STAGE;
+        unsigned char* base = tiles + (size_t)stage * SCAN_STAGE_BYTES;
         const size_t row = (size_t)tile * SCAN_TILE;
-        uint32_t bytes = SCAN_FREE_BYTES + SCAN_GC_BYTES;
-        if (LOAD) bytes += 2 * SCAN_TENTHS_BYTES + 2 * SCAN_TS_BYTES;
-        else if (want_rl) bytes += SCAN_RL_BYTES;
-        mbar_expect_tx(&bars[stage], bytes);
+        mbar_expect_tx(&bars[stage], SCAN_FREE_BYTES + SCAN_GC_BYTES + (want_rl ? SCAN_RL_BYTES : 0u));
         tma_load_1d(base, T.free + row * 8, SCAN_FREE_BYTES, &bars[stage]);
         tma_load_1d(base + SCAN_FREE_BYTES, T.gcount + row, SCAN_GC_BYTES, &bars[stage]);
-        unsigned char* q = base + SCAN_FREE_BYTES + SCAN_GC_BYTES;
-        if (LOAD) {
-#pragma unroll
-            for (int m = 0; m < 2; m++) {
-                const size_t off = ((size_t)m * T.nstride + row) * 8;
-                tma_load_1d(q + m * SCAN_TENTHS_BYTES, T.tenths + off, SCAN_TENTHS_BYTES, &bars[stage]);
-                tma_load_1d(q + 2 * SCAN_TENTHS_BYTES + m * SCAN_TS_BYTES, T.ts + off, SCAN_TS_BYTES, &bars[stage]);
-            }
-        } else if (want_rl) {
-            tma_load_1d(q, T.rl + row * 8, SCAN_RL_BYTES, &bars[stage]);
-        }
+        if (want_rl) tma_load_1d(base + SCAN_FREE_BYTES + SCAN_GC_BYTES, T.rl + row * 8, SCAN_RL_BYTES, &bars[stage]);
     };
 
     // thread 0 gets the first tiles moving before anything else happens; the demand is sorted by another
     // warp meanwhile, so the prologue costs no memory time
     if (tid == 0) {
-        for (int st = 0; st < SCAN_STAGES; st++) mbar_init(&bars[st], 1);
+        for (int st = 0; st < NGS_SCAN_STAGES; st++) mbar_init(&bars[st], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        for (uint32_t i = 0; i < SCAN_STAGES; i++) {
+        for (uint32_t i = 0; i < NGS_SCAN_STAGES; i++) {
             const uint32_t tile = blockIdx.x + i * gridDim.x;
             if (tile < ntiles) issue(tile, i);
         }
     }
     if (tid == 32) sort_demand(pd.percent, pd.n, pd.policy, &dem);
-    if (LOAD) fill_usage_pair_table(s_pair, tid, blockDim.x);
     __syncthreads();
 
     uint32_t it = 0;
     for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
-        const uint32_t stage = it % SCAN_STAGES, parity = (it / SCAN_STAGES) & 1u;
+        const uint32_t stage = it % NGS_SCAN_STAGES, parity = (it / NGS_SCAN_STAGES) & 1u;
         mbar_wait(&bars[stage], parity);
-        const unsigned char* base = tiles + (size_t)stage * STAGE;
+        const unsigned char* base = tiles + (size_t)stage * SCAN_STAGE_BYTES;
         const uint32_t row = tile * SCAN_TILE + tid;
         RowIn in;
         {
@@ -191,31 +164,15 @@ __global__ void __launch_bounds__(SCAN_TILE, LOAD ? NGS_SCAN_BLOCKS_LOAD : NGS_S
         }
         in.G = base[SCAN_FREE_BYTES + tid];
         in.r8 = make_uint2(0u, 0u);
-        const unsigned char* q = base + SCAN_FREE_BYTES + SCAN_GC_BYTES;
-        if (LOAD) {
-#pragma unroll
-            for (int m = 0; m < 2; m++) {
-                in.t8[m] = *reinterpret_cast<const uint2*>(q + m * SCAN_TENTHS_BYTES + (size_t)tid * 8);
-                const unsigned char* tsp = q + 2 * SCAN_TENTHS_BYTES + m * SCAN_TS_BYTES + (size_t)tid * 32;
-                const uint4 a = *reinterpret_cast<const uint4*>(tsp), b = *reinterpret_cast<const uint4*>(tsp + 16);
-                in.ts[m][0] = a.x; in.ts[m][1] = a.y; in.ts[m][2] = a.z; in.ts[m][3] = a.w;
-                in.ts[m][4] = b.x; in.ts[m][5] = b.y; in.ts[m][6] = b.z; in.ts[m][7] = b.w;
-            }
-        } else if (want_rl) {
-            in.r8 = *reinterpret_cast<const uint2*>(q + (size_t)tid * 8);
-        }
-        __syncthreads();  // the stage has been read by everyone: refill it with the tile 3 steps ahead
+        if (want_rl) in.r8 = *reinterpret_cast<const uint2*>(base + SCAN_FREE_BYTES + SCAN_GC_BYTES + (size_t)tid * 8);
+        __syncthreads();  // the stage has been read by everyone: refill it with the tile NGS_SCAN_STAGES steps ahead
         if (tid == 0) {
-            const uint32_t next = tile + SCAN_STAGES * gridDim.x;
+            const uint32_t next = tile + NGS_SCAN_STAGES * gridDim.x;
             if (next < ntiles) issue(next, stage);
         }
         if (row < n) {
-            const RowEval ev = eval_row_values<false>(T, row, in, &dem, lp, true, s_pair);
+            const RowEval ev = eval_row_values<false>(T, row, in, &dem, lp, true, nullptr);
             const bool ok = ev.known && ev.feasible;
-            if (ev.known && LOAD) {  // plan cache, as in k_assume (MODE_ASSUME)
-                T.tag[row] = ok ? gen : 0u;
-                if (ok) T.cscore[row] = ev.score;
-            }
             if (feasible) feasible[row] = ok ? 1 : 0;
             if (reason) reason[row] = !ev.known ? NGS_REASON_UNKNOWN_NODE : (ok ? NGS_REASON_OK : NGS_REASON_INFEASIBLE);
             if (score) score[row] = ok ? ev.score : NGS_SCORE_MIN;
