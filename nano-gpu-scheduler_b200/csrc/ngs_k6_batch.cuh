@@ -63,7 +63,8 @@ __device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long
     return v;
 }
 
-constexpr long long SPIN_TIMEOUT_CYCLES = 2000000000LL;  // ~1 s
+constexpr long long SPIN_TIMEOUT_CYCLES = 2000000000LL;   // ~1 s: waits on CTAs of the same (cooperative, fully resident) launch
+constexpr long long PEER_TIMEOUT_CYCLES = 16000000000LL;  // ~8 s: waits on another GPU, whose host may launch its kernel later
 
 __device__ __forceinline__ uint64_t warp_max_u64(uint64_t v) {
     const uint32_t hi = (uint32_t)(v >> 32);
@@ -283,7 +284,7 @@ __device__ __forceinline__ unsigned long long wait_valid(const unsigned long lon
     uint32_t spins = 0;
     while (!((v = ld_relaxed_sys_u64(p)) & KEY_VALID)) {
         if ((++spins & 255u) == 0) {
-            if (*reinterpret_cast<volatile int32_t*>(err) != 0 || clock64() - t0 > SPIN_TIMEOUT_CYCLES) {
+            if (*reinterpret_cast<volatile int32_t*>(err) != 0 || clock64() - t0 > PEER_TIMEOUT_CYCLES) {
                 atomicCAS(err, 0, NGS_ERR_TIMEOUT);
                 dead = true;
                 return 0;
