@@ -339,7 +339,8 @@ def run_b200(args):
         lat = []
         lo = base
         n_lat = 60 if args.skip_e2e else 400
-        if sd is None:
+        if sd is None or int(policy[0]) != ngs.POLICY_RANDOM:
+            # (sharded handles too: a one-pod call trades keys and the plan between the ranks' kernels itself)
             import ctypes as C
 
             lib = ngs._abi.load()
@@ -349,7 +350,7 @@ def run_b200(args):
             p_out = (vp(o_node), vp(o_score), vp(o_gidx))
             p_in = [(C.c_void_p(pc.ctypes.data + (lo + s) * MAX_C * 4), C.c_void_p(nc.ctypes.data + (lo + s) * 4),
                      C.c_void_p(policy.ctypes.data + (lo + s) * 4), C.c_uint64(s)) for s in range(n_lat)]
-            fn, hd, one, mc, sd1 = lib.ngs_schedule_batch, d._h, C.c_uint32(1), C.c_int(MAX_C), C.c_uint64(1)
+            fn, hd, one, mc, sd1 = lib.ngs_schedule_batch, (d if sd is None else sd.local)._h, C.c_uint32(1), C.c_int(MAX_C), C.c_uint64(1)
             for a_pc, a_nc, a_pol, seq in p_in:
                 t0 = time.perf_counter()
                 rc = fn(hd, one, a_pc, a_nc, mc, a_pol, lref, sd1, seq, p_out[0], p_out[1], p_out[2])

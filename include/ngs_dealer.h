@@ -158,8 +158,9 @@ int ngs_bind(ngs_dealer *h, uint32_t idx, const int32_t *percent, int n_containe
  * ties -> lowest node index; NGS_POLICY_RANDOM: splitmix64(seed+seq0+p) mod |feasible|), bind.
  * Equivalent to P x (Assume, Score, pick, Bind) on the reference dealer.  percent is
  * [P][max_c]; node_out[p] = global node index or -1; gpu_idx_out [P][max_c] padded with INT32_MIN.
- * A call with ONE pod on an unsharded handle is the low-latency form: a single
- * ordinary launch over the tables in place, the answer polled from mapped host memory. */
+ * A call with ONE pod is the low-latency form: a single ordinary launch over the tables in place,
+ * the answer polled from mapped host memory (sharded handles: every rank makes the same call and
+ * gets the whole decision; the random policy on a sharded handle takes the batch path). */
 int ngs_schedule_batch(ngs_dealer *h, uint32_t n_pods, const int32_t *percent, const int32_t *n_containers, int max_c,
                        const int32_t *policy, const ngs_load_ctx *load, uint64_t seed, uint64_t seq0, int32_t *node_out,
                        int32_t *score_out, int32_t *gpu_idx_out);

@@ -102,7 +102,8 @@ struct ngs_dealer {
 namespace {
 
 constexpr uint32_t BATCH_CHUNK = 4096;
-constexpr size_t XSLOT_HALF = (size_t)BATCH_CHUNK * NGS_MAX_RANKS;  // u64 words per parity half
+constexpr size_t XSLOT_HALF = (size_t)BATCH_CHUNK * NGS_MAX_RANKS + XMAIL_WORDS;  // u64 words per parity half: pod slots, then K7's plan mailbox
+static_assert(XMAIL_OFFSET == (size_t)BATCH_CHUNK * NGS_MAX_RANKS, "K7's mailbox sits right behind the pod slots");
 
 int fail(ngs_dealer* h, int code, const char* fmt, ...) {
     if (h) {
@@ -805,7 +806,7 @@ int ngs_schedule_batch(ngs_dealer* h, uint32_t n_pods, const int32_t* percent, c
     CU(h, cudaSetDevice(h->device));
     rc = ensure_batch(h);
     if (rc) return rc;
-    if (n_pods == 1 && h->world <= 1) {
+    if (n_pods == 1 && (h->world <= 1 || policy[0] != NGS_POLICY_RANDOM)) {
         // one pod: K7, a single ordinary launch; the answer arrives in mapped host memory and the
         // status word behind it is polled, so the call returns without a stream synchronisation
         PodDemand pd;
@@ -817,11 +818,22 @@ int ngs_schedule_batch(ngs_dealer* h, uint32_t n_pods, const int32_t* percent, c
         uint32_t grid = (h->T.n + 255) / 256;
         if (grid > (uint32_t)h->num_sms * 4) grid = (uint32_t)h->num_sms * 4;
         if (grid < 1) grid = 1;
+        OneShard sh;
+        memset(&sh, 0, sizeof(sh));
+        sh.world = (uint32_t)h->world;
+        sh.rank = (uint32_t)h->rank;
+        sh.err = h->d_err;
+        if (h->world > 1) {  // same parity discipline as K6 (launch_schedule): this call uses one half, the other is cleared now
+            const size_t cur = (size_t)(h->xbatch & 1), nxt = cur ^ 1;
+            CU(h, cudaMemsetAsync(h->d_xslots + nxt * XSLOT_HALF, 0, sizeof(unsigned long long) * XSLOT_HALF, h->stream));
+            for (int r = 0; r < h->world; r++) sh.xs[r] = h->peer_xslots[r] + cur * XSLOT_HALF;
+            h->xbatch++;
+        }
         if (policy[0] == NGS_POLICY_RANDOM)
             k_schedule_one_random<<<grid, 256, 0, h->stream>>>(h->T, pd, seed + seq0, h->d_one, reinterpret_cast<uint32_t*>(h->d_one + 1),
                                                                h->d_pod_out_dev, max_c);
         else
-            k_schedule_one<<<grid, 256, 0, h->stream>>>(h->T, pd, lp, h->d_one, h->d_pod_out_dev, max_c);
+            k_schedule_one<<<grid, 256, 0, h->stream>>>(h->T, pd, lp, h->d_one, h->d_pod_out_dev, max_c, sh);
         CU(h, cudaGetLastError());
         for (uint32_t spins = 1; hout[0] == ONE_PENDING; spins++) {
 #if defined(__x86_64__) || defined(__i386__)
@@ -834,6 +846,10 @@ int ngs_schedule_batch(ngs_dealer* h, uint32_t n_pods, const int32_t* percent, c
             }
         }
         std::atomic_thread_fence(std::memory_order_acquire);
+        if (hout[0] == NGS_ERR_TIMEOUT) {
+            cudaMemsetAsync(h->d_err, 0, 4, h->stream);
+            return fail(h, NGS_ERR_TIMEOUT, "single-pod kernel gave up waiting for a peer GPU");
+        }
         if (hout[0] != NGS_OK) return fail(h, NGS_ERR_CUDA, "k_schedule_one ended without an answer");
         node_out[0] = hout[8];
         score_out[0] = hout[9];

@@ -7,7 +7,10 @@
 // record zeroed for the next call.  The random policy goes the same way with counts instead of keys:
 // every CTA owns a contiguous node range and leaves the number of feasible nodes in it; the last CTA
 // to arrive finds the range holding the seeded k-th feasible node and evaluates that range once more.
-// Node-range sharding stays with K6.  Same results as K6 with P = 1 (tests/test_gpu_parity.py).
+// On a sharded handle (binpack / spread) the last CTA of every rank trades the rank's best key with the
+// peers through the same peer-mapped slot arrays K6 uses; the rank that owns the winner binds it and
+// drops the plan into every peer's mailbox, so all ranks return the full decision without a collective.
+// Same results as K6 with P = 1 (tests/test_gpu_parity.py, tests/sharded_worker.py).
 // Included by ngs_dealer.cu inside its anonymous namespace, after ngs_k6_batch.cuh.
 #pragma once
 
@@ -16,6 +19,16 @@ struct OneRec {
     unsigned int arrived;    // CTAs that have folded their key in
     unsigned int pad;
 };
+
+// node-range sharding: this call's parity half of every rank's exchange buffer (K6's layout: pod-major
+// slots [BATCH_CHUNK][NGS_MAX_RANKS], then XMAIL_WORDS words of mailbox for the owner's plan)
+struct OneShard {
+    uint32_t world, rank;
+    unsigned long long* xs[NGS_MAX_RANKS];
+    int32_t* err;  // the handle's device error word (bounded waits raise it)
+};
+constexpr size_t XMAIL_WORDS = 16;
+constexpr size_t XMAIL_OFFSET = (size_t)4096 * NGS_MAX_RANKS;  // == BATCH_CHUNK * NGS_MAX_RANKS (static_assert in ngs_dealer.cu)
 
 constexpr int32_t ONE_PENDING = 0x7FFFFFFF;  // status word while the kernel has not answered yet
 constexpr uint32_t ONE_MAX_CTAS = 1024;      // entries of the random policy's per-CTA count array
@@ -164,11 +177,12 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one_random(Tables T, PodDem
 }
 
 // out (mapped host memory): [0] status, [8] node, [9] score, [10 .. 10+max_c) gpu indexes
-__global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd, LoadParams lp, OneRec* rec, int32_t* out, int max_c) {
+__global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd, LoadParams lp, OneRec* rec, int32_t* out, int max_c, OneShard sh) {
     __shared__ SortedDemand dem;
     __shared__ double s_pair[121];
     __shared__ uint64_t s_wmax[8];
     __shared__ int s_last;
+    __shared__ int32_t s_plan[NGS_MAX_CONTAINERS];  // the winner's plan in container order (last CTA only)
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     // the first row of every thread is requested before the demand is sorted: the loads do not depend on it
     const bool load_path = lp.enabled != 0;  // (binpack / spread only)
@@ -212,14 +226,30 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd,
     }
     key = __shfl_sync(FULL, key, 0);
     int32_t* gout = out + 10;
-    for (int k = (int)lane; k < max_c; k += 32) gout[k] = INT32_MIN;
+    if (lane < NGS_MAX_CONTAINERS) s_plan[lane] = INT32_MIN;
     __syncwarp();
-    if (key == 0) {  // no node takes the pod
+    int32_t status = NGS_OK;
+    bool mine = key != 0;  // the winner is one of this rank's rows
+    if (sh.world > 1) {
+        // K5 for one pod: this rank's best key to every rank (its own array included), all ranks' keys back
+        bool dead = false;
+        unsigned long long got = 0;
+        if (lane < sh.world) {
+            st_relaxed_sys_u64(sh.xs[lane] + sh.rank, key | KEY_VALID);
+            got = wait_valid(sh.xs[sh.rank] + lane, sh.err, dead);
+        }
+        dead = __any_sync(FULL, dead);
+        const unsigned long long gmax = warp_max_u64(got);
+        if (dead) status = NGS_ERR_TIMEOUT;
+        mine = !dead && gmax != 0 && gmax == key;
+        key = dead ? 0ull : gmax;
+    }
+    if (key == 0) {  // no node takes the pod (or the exchange gave up)
         if (lane == 0) {
             out[8] = -1;
             out[9] = NGS_SCORE_MIN;
         }
-    } else {
+    } else if (mine) {
         // NodeInfo.Bind (node.go:70-84) on the winner, eight lanes on the row's eight cells (the four
         // groups of the warp hold identical copies): the plan from the RemainLoad the scan left behind
         const uint32_t wrow = key_node(key) - T.first;
@@ -234,18 +264,54 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd,
             if (g < G) T.free[(size_t)wrow * 8 + lane] = fr;  // GPUs.Allocate (allocate.go:102-118)
             for (int k = (int)lane; k < dem.C; k += 8) {      // rater.go:102-105: un-permute the emission order
                 const int e = (int)((emit >> (4 * k)) & 0xF);
-                gout[dem.order[k]] = e == 0xF ? NGS_NOT_NEED_GPU : e;
+                s_plan[dem.order[k]] = e == 0xF ? NGS_NOT_NEED_GPU : e;
             }
         }
+        __syncwarp();
         if (lane == 0) {
             T.tag[wrow] = 0;  // node.go:82
             out[8] = (int32_t)(T.first + wrow);
             out[9] = key_score(key);
         }
+        if (sh.world > 1) {
+            // the plan goes into every peer's mailbox: 6 words of indexes, then (after a fence) the word that says so
+            if (lane < sh.world && lane != sh.rank) {
+                unsigned long long* mail = sh.xs[lane] + XMAIL_OFFSET;
+                for (int w = 0; w < NGS_MAX_CONTAINERS / 2; w++)
+                    st_relaxed_sys_u64(mail + 1 + w, ((unsigned long long)(uint32_t)s_plan[2 * w + 1] << 32) | (uint32_t)s_plan[2 * w]);
+                __threadfence_system();
+                st_relaxed_sys_u64(mail, KEY_VALID | 1ull);
+            }
+        }
+    } else {
+        // another rank owns the winner: node and score are in the key, the plan arrives in the mailbox
+        bool dead = false;
+        const unsigned long long* mail = sh.xs[sh.rank] + XMAIL_OFFSET;
+        if (lane == 0) wait_valid(mail, sh.err, dead);
+        dead = __any_sync(FULL, dead);
+        if (dead) {
+            status = NGS_ERR_TIMEOUT;
+            if (lane == 0) {
+                out[8] = -1;
+                out[9] = NGS_SCORE_MIN;
+            }
+        } else {
+            __threadfence_system();
+            if (lane < NGS_MAX_CONTAINERS) {
+                const unsigned long long w = ld_relaxed_sys_u64(mail + 1 + lane / 2);
+                s_plan[lane] = (int32_t)(uint32_t)((lane & 1u) ? (w >> 32) : w);
+            }
+            if (lane == 0) {
+                out[8] = (int32_t)key_node(key);
+                out[9] = key_score(key);
+            }
+        }
     }
+    __syncwarp();
+    if ((int)lane < max_c) gout[lane] = lane < NGS_MAX_CONTAINERS ? s_plan[lane] : INT32_MIN;
     __syncwarp();
     if (lane == 0) {
         __threadfence_system();  // the answer is in host memory before the status word says so
-        *reinterpret_cast<volatile int32_t*>(out) = NGS_OK;
+        *reinterpret_cast<volatile int32_t*>(out) = status;
     }
 }

@@ -54,6 +54,34 @@ def main():
                 bad = np.flatnonzero((node != onode) | (score != oscore))
                 print(f"round {rnd} policy {policy} load {load_on}: MISMATCH at pods {bad[:8]}", flush=True)
         seq += P
+    # single pods: the low-latency path (K7 with the cross-GPU trade and the plan mailbox), every rank gets the whole decision
+    for rnd, (policy, load_on) in enumerate([(0, False), (1, True), (0, True), (2, False)]):
+        pc, nc = wl.make_pods(60, 1, 4, 0, 12, 0x99 + rnd, max_c=4)
+        gl = ngs.make_load_ctx(wl.DEFAULT_PERIODS, NOW_NS) if load_on else None
+        ol = o.make_load_ctx(wl.DEFAULT_PERIODS, NOW_NS) if load_on else None
+        launches0 = sd.local.stats()["kernel_launches"]
+        for p in range(60):
+            node, score, gidx = sd.schedule_batch(pc[p:p + 1], nc[p:p + 1], policy, load=gl, seed=42, seq0=seq)
+            want = None
+            if rank == 0:
+                want = oc.schedule_batch(pc[p:p + 1], nc[p:p + 1], policy, load=ol, seed=42, seq0=seq)
+                if not (np.array_equal(node, want[0]) and np.array_equal(score, want[1]) and np.array_equal(gidx, want[2])):
+                    failures += 1
+                    print(f"single pod {p} policy {policy} load {load_on}: MISMATCH {node} {score} {gidx} vs {want}", flush=True)
+            # every rank must hold the same full answer: compare with rank 0's
+            mine = torch.from_numpy(np.concatenate([node, score, gidx.ravel()]).astype(np.int32)).cuda()
+            ref = mine.clone()
+            dist.broadcast(ref, 0)
+            if not torch.equal(mine, ref):
+                failures += 1
+                print(f"rank {rank}: single pod {p} differs from rank 0", flush=True)
+            seq += 1
+        if policy != 2 and sd.local.stats()["kernel_launches"] - launches0 != 60:
+            failures += 1
+            print(f"rank {rank}: the single-pod kernel did not run (policy {policy})", flush=True)
+    fl = torch.tensor([failures], device="cuda")
+    dist.all_reduce(fl)
+    failures = int(fl.item())
     # the shards together hold exactly the oracle's snapshot
     _, fr, rl = sd.local.snapshot_read(first=lo, n=n)
     t = torch.from_numpy(fr.astype(np.int32)).cuda()
