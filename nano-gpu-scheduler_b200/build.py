@@ -46,7 +46,7 @@ def build_host(force: bool = False) -> str:
     deps = [*srcs, *hdrs, test_src, LIB]
     if force or not os.path.exists(HOST_TEST) or any(os.path.getmtime(d) > os.path.getmtime(HOST_TEST) for d in deps):
         cxx = shutil.which("g++") or "g++"
-        common = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-I", os.path.join(HERE, "..", "include")]
+        common = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-pthread", "-I", os.path.join(HERE, "..", "include")]
         res = subprocess.run([cxx, *common, "-shared", "-o", HOST_LIB, *srcs, "-L", HERE, "-lngs_dealer", "-Wl,-rpath,$ORIGIN"],
                              capture_output=True, text=True)
         if res.returncode != 0:

@@ -317,6 +317,7 @@ void Dealer::replay_usage(const std::string& name, uint32_t r) {
 }
 
 void Dealer::Resolve(CandidateSet* cs) {  // dealer.go:97-106 for a whole list
+    std::lock_guard<std::recursive_mutex> lock(mu_);
     const size_t n = cs->names.size();
     const bool fresh = cs->rows.size() != n;
     if (fresh) {
@@ -379,6 +380,7 @@ void Dealer::Resolve(CandidateSet* cs) {  // dealer.go:97-106 for a whole list
 }
 
 AssumeResult Dealer::AssumeSet(const CandidateSet& cs, const Pod& pod, const PolicySpec& spec, bool isLoadSchedule) {  // dealer.go:89-136
+    std::lock_guard<std::recursive_mutex> lock(mu_);
     AssumeResult r;
     r.demand = NewDemandFromPod(pod);
     r.demand_text = DemandString(r.demand);
@@ -466,6 +468,7 @@ char* Dealer::PutFailureText(char* p, const CandidateSet& cs, const AssumeResult
 }
 
 std::vector<int> Dealer::ScoreSet(const CandidateSet& cs, const Pod& pod, const PolicySpec& spec, bool isLoadSchedule) {  // dealer.go:138-153
+    std::lock_guard<std::recursive_mutex> lock(mu_);
     const std::vector<int32_t> demand = NewDemandFromPod(pod);
     const size_t n = cs.names.size();
     std::vector<int> scores(n, NGS_SCORE_MIN);  // a missing node scores ScoreMin (dealer.go:145-148)
@@ -481,6 +484,7 @@ std::vector<int> Dealer::ScoreSet(const CandidateSet& cs, const Pod& pod, const 
 
 std::pair<std::vector<bool>, std::vector<Error>> Dealer::Assume(const std::vector<std::string>& nodes, const Pod& pod,
                                                                 const PolicySpec& spec, bool isLoadSchedule) {  // dealer.go:89-136
+    std::lock_guard<std::recursive_mutex> lock(mu_);
     CandidateSet cs;
     cs.names.assign(nodes.begin(), nodes.end());
     Resolve(&cs);
@@ -496,6 +500,7 @@ std::pair<std::vector<bool>, std::vector<Error>> Dealer::Assume(const std::vecto
 }
 
 std::vector<int> Dealer::Score(const std::vector<std::string>& nodes, const Pod& pod, const PolicySpec& spec, bool isLoadSchedule) {
+    std::lock_guard<std::recursive_mutex> lock(mu_);
     CandidateSet cs;
     cs.names.assign(nodes.begin(), nodes.end());
     Resolve(&cs);
@@ -503,6 +508,7 @@ std::vector<int> Dealer::Score(const std::vector<std::string>& nodes, const Pod&
 }
 
 Error Dealer::Bind(const std::string& node, Pod* pod, const PolicySpec& spec, bool isLoadSchedule) {  // dealer.go:155-203
+    std::lock_guard<std::recursive_mutex> lock(mu_);
     uint32_t row;
     Error e = getNodeInfo(node, &row);
     if (!e.empty()) return e;
@@ -527,6 +533,7 @@ Error Dealer::Bind(const std::string& node, Pod* pod, const PolicySpec& spec, bo
 }
 
 Error Dealer::Allocate(const Pod& pod) {  // dealer.go:205-228
+    std::lock_guard<std::recursive_mutex> lock(mu_);
     if (pod.node_name.empty()) return fmt("pod %s/%s nodename is empty", pod.ns.c_str(), pod.name.c_str());
     uint32_t row;
     Error e = getNodeInfo(pod.node_name, &row);
@@ -547,6 +554,7 @@ Error Dealer::Allocate(const Pod& pod) {  // dealer.go:205-228
 }
 
 Error Dealer::Release(const Pod& pod) {  // dealer.go:230-255
+    std::lock_guard<std::recursive_mutex> lock(mu_);
     uint32_t row;
     Error e = getNodeInfo(pod.node_name, &row);
     if (!e.empty()) return e;
@@ -566,14 +574,22 @@ Error Dealer::Release(const Pod& pod) {  // dealer.go:230-255
 }
 
 Error Dealer::Forget(const Pod& pod) {  // dealer.go:311-319: bookkeeping only, no capacity returns
+    std::lock_guard<std::recursive_mutex> lock(mu_);
     released_.erase(pod.uid);
     pod_maps_.erase(pod.uid);
     return "";
 }
-bool Dealer::KnownPod(const Pod& pod) { return pod_maps_.count(pod.uid) != 0; }     // dealer.go:257-262
-bool Dealer::PodReleased(const Pod& pod) { return released_.count(pod.uid) != 0; }  // dealer.go:264-269
+bool Dealer::KnownPod(const Pod& pod) {  // dealer.go:257-262
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    return pod_maps_.count(pod.uid) != 0;
+}
+bool Dealer::PodReleased(const Pod& pod) {  // dealer.go:264-269
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    return released_.count(pod.uid) != 0;
+}
 
 std::map<std::string, std::vector<int>> Dealer::Status() {  // dealer.go:321-323 (NodeMaps), via one read-back
+    std::lock_guard<std::recursive_mutex> lock(mu_);
     std::map<std::string, std::vector<int>> out;
     const uint32_t n = (uint32_t)names_.size();
     if (n == 0) return out;
@@ -600,14 +616,17 @@ std::pair<std::map<int, GPUMemoryUsage>, bool> Dealer::GetMemoryUsage(const std:
     return {it->second, true};
 }
 void Dealer::AddCoreUsage(const std::string& node) {  // nodeusage.go:58-62
+    std::lock_guard<std::recursive_mutex> lock(mu_);
     core_usage_[node] = {};
     if (const uint32_t* row = index_.Find(node)) ngs_load_add_node(h_, *row, NGS_METRIC_CORE);
 }
 void Dealer::AddMemoryUsage(const std::string& node) {  // nodeusage.go:64-68
+    std::lock_guard<std::recursive_mutex> lock(mu_);
     memory_usage_[node] = {};
     if (const uint32_t* row = index_.Find(node)) ngs_load_add_node(h_, *row, NGS_METRIC_MEMORY);
 }
 void Dealer::UpdateCoreUsage(const std::string& node, const std::string& coreUsage, const std::string& updateTime, int cardNum) {
+    std::lock_guard<std::recursive_mutex> lock(mu_);
     core_usage_[node][cardNum] = GPUCoreUsage{coreUsage, updateTime};  // nodeusage.go:70-74
     const uint32_t* row = index_.Find(node);
     if (!row) return;  // replayed when the node is materialised (getNodeInfo)
@@ -617,6 +636,7 @@ void Dealer::UpdateCoreUsage(const std::string& node, const std::string& coreUsa
     ngs_load_update(h_, *row, NGS_METRIC_CORE, cardNum, v, vok, ts, tok);
 }
 void Dealer::UpdateMemoryUsage(const std::string& node, const std::string& memoryUsage, const std::string& updateTime, int cardNum) {
+    std::lock_guard<std::recursive_mutex> lock(mu_);
     memory_usage_[node][cardNum] = GPUMemoryUsage{memoryUsage, updateTime};  // nodeusage.go:76-80
     const uint32_t* row = index_.Find(node);
     if (!row) return;

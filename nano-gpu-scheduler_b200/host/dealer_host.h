@@ -11,6 +11,7 @@
 #pragma once
 #include <cstdint>
 #include <map>
+#include <mutex>
 #include <set>
 #include <string>
 #include <string_view>
@@ -137,8 +138,14 @@ class Dealer {
     std::map<std::string, std::vector<int>> Status();                    // node -> free percent per GPU
     std::pair<std::map<int, GPUCoreUsage>, bool> GetCoreUsage(const std::string& node);
     std::pair<std::map<int, GPUMemoryUsage>, bool> GetMemoryUsage(const std::string& node);
-    std::pair<std::map<int, GPUMemoryUsage>, bool> GetMemoryUsageLock(const std::string& node) { return GetMemoryUsage(node); }
-    std::pair<std::map<int, GPUCoreUsage>, bool> GetCoreUsageLock(const std::string& node) { return GetCoreUsage(node); }
+    std::pair<std::map<int, GPUMemoryUsage>, bool> GetMemoryUsageLock(const std::string& node) {  // nodeusage.go:41-46
+        std::lock_guard<std::recursive_mutex> lock(mu_);
+        return GetMemoryUsage(node);
+    }
+    std::pair<std::map<int, GPUCoreUsage>, bool> GetCoreUsageLock(const std::string& node) {  // nodeusage.go:34-39
+        std::lock_guard<std::recursive_mutex> lock(mu_);
+        return GetCoreUsage(node);
+    }
     void AddCoreUsage(const std::string& node);
     void AddMemoryUsage(const std::string& node);
     void UpdateCoreUsage(const std::string& node, const std::string& coreUsage, const std::string& updateTime, int cardNum);
@@ -168,6 +175,10 @@ class Dealer {
     void SetNow(int64_t unix_ns) { now_ns_ = unix_ns; }
 
   private:
+    // DealerImpl.Lock (dealer.go:81): every method the reference locks takes it here, too, which also gives the
+    // "one call at a time per handle" the C library asks for.  Recursive because Assume / Score go through the
+    // *Set forms, which lock on their own for callers such as ExtenderRoutes.
+    std::recursive_mutex mu_;
     ClusterSource* src_;
     RaterKind rater_;
     ngs_dealer* h_ = nullptr;

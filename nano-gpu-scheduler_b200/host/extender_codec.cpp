@@ -866,6 +866,7 @@ inline char* put_int(char* p, int64_t v) {
 }  // namespace
 
 std::string ExtenderRoutes::Predicate(std::string_view body) {
+    std::lock_guard<std::mutex> lock(mu_);
     const uint64_t t0 = now_ns();
     ExtenderArgs a;
     Error e = DecodeExtenderArgs(body, &a, valid_ ? &raw_ : nullptr);
@@ -943,6 +944,7 @@ std::string ExtenderRoutes::Predicate(std::string_view body) {
 }
 
 std::string ExtenderRoutes::Prioritize(std::string_view body, bool* panicked) {
+    std::lock_guard<std::mutex> lock(mu_);
     if (panicked) *panicked = false;
     const uint64_t t0 = now_ns();
     ExtenderArgs a;

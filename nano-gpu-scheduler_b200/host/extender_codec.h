@@ -84,6 +84,7 @@ class ExtenderRoutes {
     const Counters& counters() const { return c_; }
 
   private:
+    std::mutex mu_;  // the candidate-set cache is shared state: requests are served one at a time
     Dealer* d_;
     PolicySpec spec_;
     bool load_;

@@ -6,7 +6,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <map>
+#include <atomic>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../nano-gpu-scheduler_b200/host/dealer_host.h"
@@ -287,6 +289,55 @@ static void TestLoadAwareScoring() {
     CHECK(sc[0] == 48 && sc[1] == -2);
 }
 
+// DealerImpl serves the extender's HTTP handlers concurrently behind d.Lock (dealer.go:81): four
+// threads filter, score, bind and release against one Dealer; afterwards no capacity is lost or made up.
+static void TestConcurrentCallers() {
+    FakeCluster fc;
+    std::vector<std::string> names;
+    for (int i = 0; i < 24; i++) {
+        fc.add("node-" + std::to_string(i), 4);
+        names.push_back("node-" + std::to_string(i));
+    }
+    Dealer d(&fc, RaterKind::Spread, 64);
+    std::atomic<int> bound_total{0}, released_total{0}, errors{0};
+    auto worker = [&](int t) {
+        std::vector<Pod> mine;
+        for (int k = 0; k < 60; k++) {
+            Pod pod = MockPodWithDemand({20 + 5 * (k % 3), 10}, "t" + std::to_string(t) + "-" + std::to_string(k));
+            auto r = d.Assume(names, pod, PolicySpec{}, false);
+            std::vector<int> sc = d.Score(names, pod, PolicySpec{}, false);
+            int best = -1;
+            for (size_t i = 0; i < names.size(); i++)
+                if (r.first[i] && (best < 0 || sc[i] > sc[best])) best = (int)i;
+            if (best < 0) continue;
+            pod.node_name = names[best];
+            // another thread may have taken the capacity between Assume and Bind: an error here is legal, corruption is not
+            if (d.Bind(names[best], &pod, PolicySpec{}, false).empty()) {
+                mine.push_back(pod);
+                bound_total++;
+            }
+            if (k % 4 == 3 && !mine.empty()) {
+                if (!d.Release(mine.back()).empty()) errors++;
+                mine.pop_back();
+                released_total++;
+            }
+        }
+        for (Pod& p : mine) {
+            if (!d.Release(p).empty()) errors++;
+            released_total++;
+        }
+    };
+    std::vector<std::thread> th;
+    for (int t = 0; t < 4; t++) th.emplace_back(worker, t);
+    for (auto& x : th) x.join();
+    CHECK(errors == 0);
+    CHECK(bound_total > 100 && bound_total == released_total);
+    auto st = d.Status();
+    CHECK(st.size() == names.size());
+    for (auto& kv : st)
+        for (int f : kv.second) CHECK(f == 100);  // everything that was bound came back, cell by cell
+}
+
 int main() {
     {
         FakeCluster fc;
@@ -306,6 +357,7 @@ int main() {
     TestScheduleCycleAndRelease();
     TestAllocateFromAnnotationsAndRebuild();
     TestLoadAwareScoring();
+    TestConcurrentCallers();
     printf("%s: %d checks, %d failed\n", g_fail ? "HOST TESTS FAILED" : "HOST TESTS OK", g_checks, g_fail);
     return g_fail ? 1 : 0;
 }
