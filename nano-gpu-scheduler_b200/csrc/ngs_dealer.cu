@@ -402,13 +402,6 @@ int ngs_create(ngs_dealer** out, int device, uint32_t max_nodes, uint32_t first_
         CU(h, cudaGetLastError());
         h->T.blut = lut;
     }
-    CU(h, cudaMemsetAsync(h->T.free, 0, N * 8 * 4, h->stream));
-    CU(h, cudaMemsetAsync(h->T.gcount, 0, N, h->stream));
-    CU(h, cudaMemsetAsync(h->T.rl, 0, N * 8, h->stream));
-    CU(h, cudaMemsetAsync(h->T.tenths, 0xFF, 2 * N * 8, h->stream));
-    CU(h, cudaMemsetAsync(h->T.ts, 0, 2 * N * 8 * 4, h->stream));
-    CU(h, cudaMemsetAsync(h->T.tag, 0, N * 4, h->stream));
-    CU(h, cudaMemsetAsync(h->T.cscore, 0, N * 4, h->stream));
     CU(h, cudaMalloc(&h->d_bind, sizeof(BindResult)));
     CU(h, cudaMallocHost(&h->h_bind, sizeof(BindResult)));
     CU(h, cudaMalloc(&h->d_small, 64 * 4));
