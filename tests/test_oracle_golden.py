@@ -145,3 +145,62 @@ def test_go119_rule_differs_sometimes():
         assert a[0] == b[0]  # feasibility never depends on the tie order when RemainLoad is 0
         differ += a[1] != b[1]
     assert differ > 100
+
+
+def _load_usage_py(values, ts, present, periods, now_ns, g):
+    """GPUResource.LoadUsage (allocate.go:173-195) with GetUsage (nodeusage.go:82-111) and inUpdateTimePeriod
+    (stats.go:30-55) folded in, restated independently of the C oracle.  values/ts/present: per metric."""
+    import math
+
+    usage = 0.0
+    for metric, window_ns in periods:  # getActiveDuration already applied by the caller (stats.go:57-66)
+        if window_ns == 0 or not present[metric]:  # activeDuration == 0 / node has no usage map: skipped
+            continue
+        if not (now_ns < int(ts[metric][g]) * 10**9 + window_ns):  # now.Before(updatetime)
+            continue
+        v = float(values[metric][g])
+        if v < 0 or v > 1:
+            continue
+        usage += math.ceil(10 * v) / 10
+    return usage, 2 - int(usage)
+
+
+@pytest.mark.parametrize("periods", [
+    [(0, 320 * 10**9), (1, 320 * 10**9)], [(1, 320 * 10**9), (0, 320 * 10**9)], [(0, 320 * 10**9)], [(1, 40 * 10**9), (1, 320 * 10**9), (0, 90 * 10**9)], []])
+def test_load_aware_rates_match_python_restatement(periods):
+    """the load-aware half of Binpack.Rate / Spread.Rate (rater.go:59-70,113-123) and the RemainLoad it leaves
+    (allocate.go:193), oracle vs a second restatement in plain Python floats: same summation order, so sums that
+    land just below an integer (0.1 * 10 = 0.9999999999999999) truncate the same way"""
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    now_s = 1_790_000_000
+    now_ns = now_s * 10**9 + 987_654_321
+    n = 400
+    gcount, free = wl.make_cluster(n, 0.5, 0xFACE, hetero=True)
+    tables = wl.make_load_tables(n, 0xFACE, now_s, stale_frac=0.2, absent_frac=0.1)
+    oc = o.OracleCluster(n)
+    oc.load_snapshot(gcount, free)
+    for m, (value, ts, absent) in enumerate(tables):
+        oc.load_update_bulk(m, value, ts, ok=np.repeat(~absent[:, None], 8, axis=1).astype(np.uint8))
+    L = o.make_load_ctx(periods, now_ns)
+    for policy in (o.POLICY_BINPACK, o.POLICY_SPREAD):
+        got = oc.assume([0], policy, load=L)  # an empty-handed pod fits everywhere: the score is Rate alone
+        _, _, rl = oc.snapshot()
+        for i in range(n):
+            G = int(gcount[i])
+            values = [tables[0][0][i], tables[1][0][i]]
+            tss = [tables[0][1][i], tables[1][1][i]]
+            present = [not tables[0][2][i], not tables[1][2][i]]
+            load, remain = 0.0, []
+            for g in range(G):
+                u, r = _load_usage_py(values, tss, present, periods, now_ns, g)
+                load += u
+                remain.append(r)
+            fr = [int(v) for v in free[i][:G]]
+            if policy == o.POLICY_BINPACK:
+                want = int(float(100 * G - sum(fr)) / float(100 * G) * 100) + (int(load) // G) * 50 - G
+            else:
+                want = 100 * sum(1 for v in fr if v == 100) + sum(fr) // 10 - G - int(load) // G
+            assert got["score"][i] == want, (policy, i)
+            assert rl[i][:G].tolist() == remain, (policy, i)
+    oc.close()
