@@ -599,6 +599,33 @@ std::map<std::string, std::vector<int>> Dealer::Status() {  // dealer.go:321-323
     return out;
 }
 
+std::string Dealer::StatusJSON() {  // routes.go:212-240
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    const uint32_t n = (uint32_t)names_.size();
+    std::vector<int32_t> fr((size_t)n * 8);
+    std::vector<int8_t> rl((size_t)n * 8);
+    if (n && ngs_snapshot_read(h_, 0, n, nullptr, fr.data(), rl.data()) != NGS_OK) return "{}";
+    std::vector<uint32_t> order(n);
+    for (uint32_t r = 0; r < n; r++) order[r] = r;
+    std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return names_[a] < names_[b]; });  // Go sorts map keys
+    std::string out = "{";
+    for (uint32_t k = 0; k < n; k++) {
+        const uint32_t r = order[k];
+        if (k) out += ",";
+        AppendJSONString(&out, names_[r]);
+        out += ":{\"Rater\":{},\"Name\":";
+        AppendJSONString(&out, names_[r]);
+        out += ",\"GPUs\":[";
+        for (int g = 0; g < gpu_count_[r]; g++) {
+            if (g) out += ",";
+            out += "{\"Percent\":" + std::to_string(fr[(size_t)r * 8 + g]) + ",\"PercentTotal\":100,\"RemainLoad\":" +
+                   std::to_string((int)rl[(size_t)r * 8 + g]) + "}";
+        }
+        out += "],\"PlanCache\":{}}";
+    }
+    return out + "}";
+}
+
 std::string Dealer::PrintStatus(const Pod& pod, const std::string& action) {  // dealer.go:303-309
     std::string s = fmt("------resource status after %s for %s/%s------\n", action.c_str(), pod.ns.c_str(), pod.name.c_str());
     for (auto& kv : Status()) s += fmt("node %s: %s\n", kv.first.c_str(), GPUsString(kv.second).c_str());

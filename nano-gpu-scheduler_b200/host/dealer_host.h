@@ -136,6 +136,11 @@ class Dealer {
     bool PodReleased(const Pod& pod);
     std::string PrintStatus(const Pod& pod, const std::string& action);  // returns what the reference logs
     std::map<std::string, std::vector<int>> Status();                    // node -> free percent per GPU
+    // what StatusRoute writes (pkg/routes/routes.go:212-240): json.Marshal(map[string]*NodeInfo) with NodeInfo =
+    // {Rater, Name, GPUs []{Percent, PercentTotal, RemainLoad}, PlanCache} (node.go:18-23, allocate.go:141-145).
+    // PlanCache is written as {}: the per-node plan cache is not kept as objects here (Score / Bind re-derive the
+    // plan from the row), so the cached entry the reference would show for the last filtered demand is absent.
+    std::string StatusJSON();
     std::pair<std::map<int, GPUCoreUsage>, bool> GetCoreUsage(const std::string& node);
     std::pair<std::map<int, GPUMemoryUsage>, bool> GetMemoryUsage(const std::string& node);
     std::pair<std::map<int, GPUMemoryUsage>, bool> GetMemoryUsageLock(const std::string& node) {  // nodeusage.go:41-46
@@ -201,6 +206,9 @@ class Dealer {
     bool load_ctx(const PolicySpec& spec, bool isLoad, ngs_load_ctx* out) const;
     int64_t now() const;
 };
+
+// encoding/json's string encoder (defined in extender_codec.cpp, declared again in extender_codec.h)
+void AppendJSONString(std::string* out, std::string_view s);
 
 // helpers mirrored from the reference (used by the tests, too)
 std::vector<int32_t> NewDemandFromPod(const Pod& pod);                                   // allocate.go:54-62

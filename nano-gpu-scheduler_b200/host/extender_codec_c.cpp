@@ -254,6 +254,8 @@ void ngsx_routes_counters(void* h, uint64_t out[7]) {
     out[5] = c.ns_dealer;
     out[6] = c.ns_encode;
 }
+// StatusRoute's body (routes.go:212-240)
+char* ngsx_routes_status(void* h, size_t* out_n) { return dup_out(((Routes*)h)->dealer->StatusJSON(), out_n); }
 // Dealer.Bind through the mirror (what the bind route calls after fetching the pod): 0 = nil error
 int ngsx_routes_bind(void* h, const char* node, const char* uid, const int32_t* percent, int n_containers, int32_t* gpu_idx_out, char** err) {
     Routes* r = (Routes*)h;

@@ -21,7 +21,8 @@ def lib():
     if _lib is None:
         L = C.CDLL(HOST_LIB)
         for name in ("ngsx_decode_args", "ngsx_decode_binding", "ngsx_json_string", "ngsx_encode_filter", "ngsx_encode_filter_error",
-                     "ngsx_encode_binding_result", "ngsx_encode_priorities", "ngsx_routes_predicate", "ngsx_routes_prioritize"):
+                     "ngsx_encode_binding_result", "ngsx_encode_priorities", "ngsx_routes_predicate", "ngsx_routes_prioritize",
+                     "ngsx_routes_status"):
             getattr(L, name).restype = C.c_void_p
         L.ngsx_routes_new.restype = C.c_void_p
         L.ngsx_free.argtypes = [C.c_void_p]
@@ -146,6 +147,11 @@ class Routes:
         p = C.c_int()
         out = _take(self.L.ngsx_routes_prioritize(self.h, body, C.c_size_t(len(body)), C.byref(n), C.byref(p)), n)
         return out, bool(p.value)
+
+    def status(self):
+        """the /status body: every node the dealer has built, its GPUs' free percent and RemainLoad"""
+        n = C.c_size_t()
+        return _take(self.L.ngsx_routes_status(self.h, C.byref(n)), n)
 
     def counters(self):
         c = (C.c_uint64 * 7)()

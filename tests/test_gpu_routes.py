@@ -161,3 +161,35 @@ def test_route_error_shapes():
         assert not panicked and out == b"[]"
     finally:
         r.close()
+
+
+def test_status_route_body():
+    """StatusRoute (routes.go:212-240) marshals map[string]*NodeInfo: node names in key order, each GPU's Percent /
+    PercentTotal / RemainLoad; only nodes the dealer has built appear; PlanCache is written empty"""
+    n = 40
+    gcount = np.array([1 + i % 8 for i in range(n)], dtype=np.uint8)
+    assumed = [(3, "a", [30, 20], [0, 2]), (17, "b", [100], [1])]
+    oc = o.OracleCluster(n)
+    oc.load_snapshot(gcount, np.where(np.arange(8)[None, :] < gcount[:, None], 100, 0).astype(np.int32))
+    for node, _, pc, gi in assumed:
+        assert oc.node_apply(node, gi, pc, +1) == 0
+    with Routes(gcount, 1, assumed) as r:
+        def want(nodes):
+            items = []
+            for i in sorted(nodes, key=node_name):
+                _, free, rl = oc.node_get(i)
+                gpus = ",".join('{"Percent":%d,"PercentTotal":100,"RemainLoad":%d}' % (free[g], rl[g]) for g in range(gcount[i]))
+                items.append('"%s":{"Rater":{},"Name":"%s","GPUs":[%s],"PlanCache":{}}' % (node_name(i), node_name(i), gpus))
+            return ("{" + ",".join(items) + "}").encode()
+
+        assert r.status() == want([3, 17])  # NewDealer built the nodes that run assumed pods, nothing else
+        names = [node_name(i) for i in (30, 5, 17, 8)]
+        r.predicate(json.dumps({"Pod": x.pod_json([10]), "NodeNames": names}))
+        assert r.status() == want([3, 17, 30, 5, 8])  # the filter call built the nodes it was asked about
+        rc, gi, _ = r.bind(node_name(5), "c", [40, 40])
+        orc, ogi, _ = oc.bind(5, [40, 40], o.POLICY_SPREAD)
+        assert rc == 0 and orc == 0 and gi == [int(v) for v in ogi]
+        got = r.status()
+        assert got == want([3, 17, 30, 5, 8])
+        assert json.loads(got)[node_name(5)]["GPUs"][0]["Percent"] in (60, 100)
+    oc.close()
