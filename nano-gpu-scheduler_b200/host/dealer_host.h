@@ -33,6 +33,7 @@ struct Pod {
     std::string ns, name, uid, node_name;  // node_name = Spec.NodeName
     std::vector<Container> containers;
     std::map<std::string, std::string> annotations, labels;
+    bool completed = false;  // utils.IsCompletedPod: DeletionTimestamp set, or phase Succeeded / Failed
 };
 struct Node {
     std::string name;
@@ -55,6 +56,7 @@ class ClusterSource {
     virtual ~ClusterSource() {}
     virtual bool GetNode(const std::string& name, Node* out) = 0;                             // false: `node "x" not found`
     virtual std::vector<Pod> ListAssumedPods(const std::string& node_name) { return {}; }    // label nano-gpu/assume=true
+    virtual bool GetPod(const std::string& ns, const std::string& name, Pod* out) { return false; }  // clientset Pods(ns).Get; false: `pods "x" not found`
     virtual std::vector<Pod> ListAllAssumedPods() { return {}; }                              // the same label over all nodes (dealer.go:58)
 };
 
@@ -122,6 +124,7 @@ class Dealer {
     Dealer(ClusterSource* src, RaterKind rater, uint32_t max_nodes, int device = 0);
     ~Dealer();
     bool ok() const { return h_ != nullptr; }
+    ClusterSource* source() const { return src_; }  // the lister / apiserver stand-in the routes fetch pods from
     const std::string& init_error() const { return init_error_; }
 
     // the 19 methods of dealer.Dealer, same order as dealer.go:23-43

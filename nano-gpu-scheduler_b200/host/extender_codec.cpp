@@ -981,4 +981,33 @@ std::string ExtenderRoutes::Prioritize(std::string_view body, bool* panicked) {
     return out;
 }
 
+std::string ExtenderRoutes::Bind(std::string_view body, int* http_status) {
+    std::lock_guard<std::mutex> lock(mu_);
+    BindingArgs a;
+    Error err = DecodeBindingArgs(body, &a);  // routes.go:136-140
+    if (err.empty()) {
+        Pod pod;
+        ClusterSource* src = d_->source();
+        // getPod (scheduler/bind.go:61-84): a second Get when the uid differs, then give up
+        bool found = src && src->GetPod(a.PodNamespace, a.PodName, &pod);
+        if (found && pod.uid != a.PodUID) found = src->GetPod(a.PodNamespace, a.PodName, &pod);
+        char buf[1024];
+        if (!found) {
+            snprintf(buf, sizeof buf, "pods \"%s\" not found", a.PodName.c_str());
+            err = buf;
+        } else if (pod.uid != a.PodUID) {
+            snprintf(buf, sizeof buf, "pod %s in ns %s's uid is %s, and it's not equal with expected %s", a.PodName.c_str(), a.PodNamespace.c_str(),
+                     pod.uid.c_str(), a.PodUID.c_str());
+            err = buf;
+        } else if (pod.completed) {  // bind.go:46-50
+            snprintf(buf, sizeof buf, "pod %s/%s already deleted or completed", a.PodName.c_str(), a.PodNamespace.c_str());
+            err = buf;
+        } else {
+            err = d_->Bind(a.Node, &pod, spec_, load_);  // bind.go:52
+        }
+    }
+    if (http_status) *http_status = err.empty() ? 200 : 500;  // routes.go:147-166
+    return EncodeBindingResult(err);
+}
+
 }  // namespace ngs_host

@@ -7,7 +7,8 @@
 //   scheduler/predicate.go:21-38  split names into canSchedule / canNotSchedule -> ExtenderRoutes::Predicate
 //   routes/routes.go:75-87    json.Marshal(extenderFilterResult)               -> EncodeFilterResult
 //   scheduler/priority.go:30-37 + routes.go:113-119  HostPriorityList + Marshal -> ExtenderRoutes::Prioritize
-//   routes/routes.go:139-150  ExtenderBindingArgs / ExtenderBindingResult       -> DecodeBindingArgs / EncodeBindingResult
+//   routes/routes.go:125-169 + scheduler/bind.go:25-84  bind verb: args, pod fetch, Dealer.Bind, result -> ExtenderRoutes::Bind
+//   routes/routes.go:212-240  json.Marshal(nodeMaps) of the status route        -> Dealer::StatusJSON
 //
 // The structs are those of k8s.io/kube-scheduler v0.18.0 (go.mod:19), extender/v1/types.go, which
 // is NOT vendored under /root/reference: ExtenderArgs{Pod, Nodes, NodeNames}, ExtenderFilterResult
@@ -77,6 +78,9 @@ class ExtenderRoutes {
     ExtenderRoutes(Dealer* d, PolicySpec spec, bool isLoadSchedule) : d_(d), spec_(std::move(spec)), load_(isLoadSchedule) {}
     std::string Predicate(std::string_view body);                     // always a 200 body (routes.go:75-87)
     std::string Prioritize(std::string_view body, bool* panicked);    // *panicked: the reference panics (routes.go:103,110)
+    // BindRoute + Bind.Handler + NewNanoGPUBind (routes.go:125-169, scheduler/bind.go:25-59): the pod is fetched from
+    // the ClusterSource, checked (uid, not completed) and bound through Dealer.Bind; *http_status = 200 or 500
+    std::string Bind(std::string_view body, int* http_status);
     struct Counters {
         uint64_t requests = 0, cache_hits = 0, all_rows = 0;
         uint64_t ns_decode = 0, ns_resolve = 0, ns_dealer = 0, ns_encode = 0;  // where the wall time of the routes went

@@ -45,6 +45,13 @@ class RangeSource : public ClusterSource {
         auto it = assumed.find(node);
         return it == assumed.end() ? std::vector<Pod>() : it->second;
     }
+    std::map<std::string, Pod> pods;  // pending pods by "ns/name"
+    bool GetPod(const std::string& ns, const std::string& name, Pod* out) override {
+        auto it = pods.find(ns + "/" + name);
+        if (it == pods.end()) return false;
+        *out = it->second;
+        return true;
+    }
     std::vector<Pod> ListAllAssumedPods() override {
         std::vector<Pod> all;
         for (auto& kv : assumed) all.insert(all.end(), kv.second.begin(), kv.second.end());
@@ -253,6 +260,26 @@ void ngsx_routes_counters(void* h, uint64_t out[7]) {
     out[4] = c.ns_resolve;
     out[5] = c.ns_dealer;
     out[6] = c.ns_encode;
+}
+// a pending pod the bind route can fetch (what the apiserver would return for Pods(ns).Get(name))
+void ngsx_routes_add_pod(void* h, const char* ns, const char* name, const char* uid, const int32_t* percent, int n_containers, int completed) {
+    Routes* r = (Routes*)h;
+    Pod p;
+    p.ns = ns;
+    p.name = name;
+    p.uid = uid;
+    p.completed = completed != 0;
+    for (int k = 0; k < n_containers; k++) {
+        Container c;
+        c.name = "c" + std::to_string(k);
+        c.has_gpu_limit = true;
+        c.gpu_percent = percent[k];
+        p.containers.push_back(c);
+    }
+    r->src.pods[p.ns + "/" + p.name] = p;
+}
+char* ngsx_routes_bind_route(void* h, const char* body, size_t n, size_t* out_n, int* http_status) {
+    return dup_out(((Routes*)h)->routes->Bind(std::string_view(body, n), http_status), out_n);
 }
 // StatusRoute's body (routes.go:212-240)
 char* ngsx_routes_status(void* h, size_t* out_n) { return dup_out(((Routes*)h)->dealer->StatusJSON(), out_n); }

@@ -22,7 +22,7 @@ def lib():
         L = C.CDLL(HOST_LIB)
         for name in ("ngsx_decode_args", "ngsx_decode_binding", "ngsx_json_string", "ngsx_encode_filter", "ngsx_encode_filter_error",
                      "ngsx_encode_binding_result", "ngsx_encode_priorities", "ngsx_routes_predicate", "ngsx_routes_prioritize",
-                     "ngsx_routes_status"):
+                     "ngsx_routes_status", "ngsx_routes_bind_route"):
             getattr(L, name).restype = C.c_void_p
         L.ngsx_routes_new.restype = C.c_void_p
         L.ngsx_free.argtypes = [C.c_void_p]
@@ -147,6 +147,18 @@ class Routes:
         p = C.c_int()
         out = _take(self.L.ngsx_routes_prioritize(self.h, body, C.c_size_t(len(body)), C.byref(n), C.byref(p)), n)
         return out, bool(p.value)
+
+    def add_pod(self, ns, name, uid, percent, completed=False):
+        """a pending pod the bind route will find (stands in for the apiserver's answer to Pods(ns).Get(name))"""
+        pc = (C.c_int32 * max(len(percent), 1))(*percent)
+        self.L.ngsx_routes_add_pod(self.h, ns.encode(), name.encode(), uid.encode(), pc, len(percent), int(completed))
+
+    def bind_route(self, body):
+        """BindRoute: ExtenderBindingArgs JSON in -> (ExtenderBindingResult JSON, HTTP status)"""
+        body = body if isinstance(body, bytes) else body.encode()
+        n = C.c_size_t()
+        st = C.c_int()
+        return _take(self.L.ngsx_routes_bind_route(self.h, body, C.c_size_t(len(body)), C.byref(n), C.byref(st)), n), st.value
 
     def status(self):
         """the /status body: every node the dealer has built, its GPUs' free percent and RemainLoad"""

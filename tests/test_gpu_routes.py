@@ -193,3 +193,34 @@ def test_status_route_body():
         assert got == want([3, 17, 30, 5, 8])
         assert json.loads(got)[node_name(5)]["GPUs"][0]["Percent"] in (60, 100)
     oc.close()
+
+
+def test_bind_route_bodies():
+    """BindRoute (routes.go:125-169) with NewNanoGPUBind (scheduler/bind.go:38-59): args in, {"Error": ...} out, 200 / 500"""
+    n = 16
+    gcount = np.full(n, 4, dtype=np.uint8)
+    oc = o.OracleCluster(n)
+    oc.load_snapshot(gcount, np.where(np.arange(8)[None, :] < 4, 100, 0).astype(np.int32).repeat(n, 0).reshape(n, 8))
+    with Routes(gcount, 0) as r:
+        r.add_pod("default", "p1", "uid-1", [60, 30])
+        r.add_pod("default", "gone", "uid-2", [10], completed=True)
+        r.add_pod("default", "big", "uid-3", [100, 100, 100, 100, 100])
+        args = lambda name, uid, node: json.dumps({"PodName": name, "PodNamespace": "default", "PodUID": uid, "Node": node})  # noqa: E731
+        body, st = r.bind_route(args("p1", "uid-1", node_name(2)))
+        assert (body, st) == (b'{"Error":""}', 200)
+        assert oc.bind(2, [60, 30], o.POLICY_BINPACK)[0] == 0
+        got = json.loads(r.status())[node_name(2)]["GPUs"]
+        assert [g["Percent"] for g in got] == [int(v) for v in oc.node_get(2)[1]]
+        body, st = r.bind_route(args("nobody", "uid-9", node_name(2)))
+        assert st == 500 and json.loads(body) == {"Error": 'pods "nobody" not found'}
+        body, st = r.bind_route(args("p1", "other-uid", node_name(2)))
+        assert st == 500 and json.loads(body) == {"Error": "pod p1 in ns default's uid is uid-1, and it's not equal with expected other-uid"}
+        body, st = r.bind_route(args("gone", "uid-2", node_name(2)))
+        assert st == 500 and json.loads(body) == {"Error": "pod gone/default already deleted or completed"}
+        body, st = r.bind_route(args("big", "uid-3", node_name(3)))  # five full GPUs on a four-GPU node (node.go:75)
+        assert st == 500 and json.loads(body) == {"Error": "assume [(100) (100) (100) (100) (100)] on (100)(100)(100)(100) failed"}
+        body, st = r.bind_route(args("p1", "uid-1", "node-nowhere"))
+        assert st == 500 and json.loads(body) == {"Error": 'node "node-nowhere" not found'}
+        body, st = r.bind_route(b"{")
+        assert st == 500 and body == b'{"Error":"unexpected EOF"}'
+    oc.close()
