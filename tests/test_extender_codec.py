@@ -23,7 +23,8 @@ def test_c_surface_exports():
     for name in ("ngsx_decode_args", "ngsx_decode_binding", "ngsx_json_string", "ngsx_quantity", "ngsx_encode_filter",
                  "ngsx_encode_filter_error", "ngsx_encode_binding_result", "ngsx_encode_priorities", "ngsx_node_index_check",
                  "ngsx_routes_new", "ngsx_routes_add_assumed", "ngsx_routes_start", "ngsx_routes_predicate", "ngsx_routes_prioritize",
-                 "ngsx_routes_counters", "ngsx_routes_bind", "ngsx_routes_destroy", "ngsx_free"):
+                 "ngsx_routes_counters", "ngsx_routes_bind", "ngsx_routes_destroy", "ngsx_free", "ngsx_routes_status", "ngsx_routes_add_pod",
+                 "ngsx_routes_bind_route"):
         assert hasattr(L, name), name
 
 
