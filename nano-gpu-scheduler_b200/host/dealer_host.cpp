@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <unordered_map>
 
 namespace ngs_host {
@@ -78,6 +79,23 @@ std::string IntsString(const std::vector<int32_t>& v) {  // fmt %v of []int
 int GetGPUDeviceCountOfNode(const Node& node) {  // pkg/utils/node.go:8-14
     if (!node.has_capacity) return 0;
     return (int)(node.gpu_percent_capacity / 100);
+}
+std::string FormatLocalTime(int64_t unix_ns) {
+    // the zone has been UTC+8 without daylight saving since 1991, and the parser (stats.go:35-38) falls back to a fixed +8 too
+    int64_t sec = unix_ns / 1000000000LL;
+    if (unix_ns % 1000000000LL < 0) sec--;
+    const time_t t = (time_t)(sec + 8 * 3600);
+    struct tm tmv;
+    gmtime_r(&t, &tmv);
+    char buf[32];
+    strftime(buf, sizeof buf, "%Y-%m-%dT%H:%M:%SZ", &tmv);
+    return buf;
+}
+std::string FormatMetricValue(double v) {
+    if (v < 0 || v != v) v = 0;
+    char buf[64];
+    snprintf(buf, sizeof buf, "%.5f", v);
+    return buf;
 }
 Error getActiveDuration(const std::vector<Period>& list, const std::string& name, int64_t* out_ns) {  // stats.go:57-66
     for (const Period& p : list)
@@ -671,6 +689,23 @@ void Dealer::UpdateMemoryUsage(const std::string& node, const std::string& memor
     int64_t ts = 0;
     int vok = ngs_parse_usage(memoryUsage.c_str(), &v), tok = ngs_parse_update_time(updateTime.c_str(), &ts);
     ngs_load_update(h_, *row, NGS_METRIC_MEMORY, cardNum, v, vok, ts, tok);
+}
+
+Error Dealer::AnnotatorNode(const std::string& node, const std::string& key, const std::string& cardNum, const std::string& value) {
+    if (value.empty())  // controller/node.go:113-116
+        return fmt("QueryLasterData %s for node %s return value: %s , error: <nil>", key.c_str(), node.c_str(), value.c_str());
+    char* end = nullptr;
+    const long card = strtol(cardNum.c_str(), &end, 10);  // strconv.Atoi
+    if (cardNum.empty() || *end != '\0') return fmt("strconv.Atoi: parsing \"%s\": invalid syntax", cardNum.c_str());
+    const std::string stamp = FormatLocalTime(now());
+    if (key == kCoreUsagePriority) {
+        if (!GetCoreUsageLock(node).second) AddCoreUsage(node);
+        UpdateCoreUsage(node, value, stamp, (int)card);
+    } else {
+        if (!GetMemoryUsageLock(node).second) AddMemoryUsage(node);
+        UpdateMemoryUsage(node, value, stamp, (int)card);
+    }
+    return "";
 }
 
 Dealer::Usage Dealer::GetUsage(const std::string& node, const std::string& key, int card, int64_t activeDuration_ns) {  // nodeusage.go:82-111

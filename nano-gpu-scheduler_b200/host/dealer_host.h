@@ -179,6 +179,11 @@ class Dealer {
     char* PutFailureText(char* p, const CandidateSet& cs, const AssumeResult& r, size_t i) const;
     std::vector<int> ScoreSet(const CandidateSet& cs, const Pod& pod, const PolicySpec& spec, bool isLoadSchedule);
 
+    // Controller.annotatorNode (pkg/controller/node.go:111-135): one Prometheus sample for (node, metric key, card)
+    // becomes Add*Usage (first sample of the node) + Update*Usage stamped with the controller's local time.
+    // `value` is the string QueryLasterData returned (FormatMetricValue); empty -> the reference's error.
+    Error AnnotatorNode(const std::string& node, const std::string& key, const std::string& cardNum, const std::string& value);
+
     // time.Now() of the next calls (tests freeze it); 0 = wall clock
     void SetNow(int64_t unix_ns) { now_ns_ = unix_ns; }
 
@@ -220,6 +225,8 @@ std::string DemandString(const std::vector<int32_t>& d);   // how fmt renders a 
 std::string GPUsString(const std::vector<int>& free);      // GPUs.String() (allocate.go:133-139): "(10)(50)"
 std::string IntsString(const std::vector<int32_t>& v);     // fmt %v of []int: "[1 0]"
 int GetGPUDeviceCountOfNode(const Node& node);              // pkg/utils/node.go:8-14
+std::string FormatLocalTime(int64_t unix_ns);               // Controller.getLocalTime (controller/node.go:137-141): Asia/Shanghai wall clock as "2006-01-02T15:04:05Z"
+std::string FormatMetricValue(double v);                    // prometheus.go:57-62: negative or NaN -> 0, then FormatFloat(v, 'f', 5, 64)
 bool IsAssumed(const Pod& pod);                             // pkg/utils/pod.go:81-83
 Error getActiveDuration(const std::vector<Period>& list, const std::string& name, int64_t* out_ns);  // stats.go:57-66
 

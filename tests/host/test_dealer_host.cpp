@@ -289,6 +289,47 @@ static void TestLoadAwareScoring() {
     CHECK(sc[0] == 48 && sc[1] == -2);
 }
 
+// the controller's metric sync (controller/node.go:111-135, prometheus.go:57-62) feeding the same tables
+static void TestAnnotatorNodeIngestion() {
+    CHECK_EQ_STR(FormatLocalTime(1709265610LL * 1000000000LL), "2024-03-01T12:00:10Z");  // 04:00:10 UTC shown as Shanghai wall clock
+    CHECK_EQ_STR(FormatLocalTime(1709251200LL * 1000000000LL + 999999999LL), "2024-03-01T08:00:00Z");
+    CHECK_EQ_STR(FormatMetricValue(0.949996), "0.95000");
+    CHECK_EQ_STR(FormatMetricValue(-0.3), "0.00000");
+    CHECK_EQ_STR(FormatMetricValue(0.0 / 0.0), "0.00000");
+    int64_t back = 0;
+    CHECK(ngs_parse_update_time(FormatLocalTime(1709265610LL * 1000000000LL).c_str(), &back) == 1 && back == 1709265610LL);
+    FakeCluster fc;
+    fc.add("busy", 2);
+    fc.add("idle", 2);
+    Dealer d(&fc, RaterKind::Binpack, 16), ref(&fc, RaterKind::Binpack, 16);
+    PolicySpec spec;
+    spec.sync_period = {{"gpu_core_usage_avg", 15LL * 1000000000LL}, {"gpu_memory_usage_avg", 15LL * 1000000000LL}};
+    d.SetNow(1709265600LL * 1000000000LL);
+    ref.SetNow(1709265600LL * 1000000000LL);
+    for (int card = 0; card < 2; card++) {
+        CHECK(d.AnnotatorNode("busy", "gpu_core_usage_avg", std::to_string(card), FormatMetricValue(0.95)).empty());
+        CHECK(d.AnnotatorNode("busy", "gpu_memory_usage_avg", std::to_string(card), FormatMetricValue(0.85)).empty());
+    }
+    CHECK(d.GetCoreUsageLock("busy").second && d.GetCoreUsage("busy").first.size() == 2);  // the map was created once, both cards kept
+    CHECK_EQ_STR(d.GetCoreUsage("busy").first[1].UpdateTime, "2024-03-01T12:00:00Z");
+    CHECK_EQ_STR(d.AnnotatorNode("busy", "gpu_core_usage_avg", "0", ""),
+                 "QueryLasterData gpu_core_usage_avg for node busy return value:  , error: <nil>");
+    CHECK(!d.AnnotatorNode("busy", "gpu_core_usage_avg", "x", "0.5").empty());
+    ref.AddCoreUsage("busy");
+    ref.AddMemoryUsage("busy");
+    for (int card = 0; card < 2; card++) {
+        ref.UpdateCoreUsage("busy", "0.95000", "2024-03-01T12:00:00Z", card);
+        ref.UpdateMemoryUsage("busy", "0.85000", "2024-03-01T12:00:00Z", card);
+    }
+    d.SetNow(1709265610LL * 1000000000LL);  // ten seconds later the filter runs
+    ref.SetNow(1709265610LL * 1000000000LL);
+    Pod pod = MockPodWithDemand({31});
+    CHECK(d.Assume({"busy", "idle"}, pod, spec, true).first[0]);
+    CHECK(ref.Assume({"busy", "idle"}, pod, spec, true).first[0]);
+    CHECK(d.Score({"busy", "idle"}, pod, spec, true) == ref.Score({"busy", "idle"}, pod, spec, true));
+    CHECK(d.Score({"busy", "idle"}, pod, spec, true)[0] == 48);
+}
+
 // DealerImpl serves the extender's HTTP handlers concurrently behind d.Lock (dealer.go:81): four
 // threads filter, score, bind and release against one Dealer; afterwards no capacity is lost or made up.
 static void TestConcurrentCallers() {
@@ -357,6 +398,7 @@ int main() {
     TestScheduleCycleAndRelease();
     TestAllocateFromAnnotationsAndRebuild();
     TestLoadAwareScoring();
+    TestAnnotatorNodeIngestion();
     TestConcurrentCallers();
     printf("%s: %d checks, %d failed\n", g_fail ? "HOST TESTS FAILED" : "HOST TESTS OK", g_checks, g_fail);
     return g_fail ? 1 : 0;
