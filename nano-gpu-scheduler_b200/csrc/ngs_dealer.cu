@@ -234,6 +234,23 @@ uint32_t schedule_block_size(uint32_t rpb) {
     return 1024;
 }
 
+// which instantiation of K6 serves CTAs of `rpb` rows, and its block size
+const void* schedule_kernel(uint32_t rpb) {
+    return rpb > K6_EXCLUSIVE_ROWS ? (const void*)k_schedule<true> : (const void*)k_schedule<false>;
+}
+uint32_t schedule_block(uint32_t rpb) { return rpb > K6_EXCLUSIVE_ROWS ? 1024u : schedule_block_size(rpb); }
+// the dynamic shared memory limit is a per-device upper bound shared by every launch: allow the device maximum for both instantiations
+cudaError_t schedule_allow_max_smem(int smem_optin) {
+    const void* fns[2] = {(const void*)k_schedule<false>, (const void*)k_schedule<true>};
+    for (const void* fn : fns) {
+        cudaFuncAttributes fa;
+        cudaError_t e = cudaFuncGetAttributes(&fa, fn);  // the opt-in limit covers static + dynamic shared memory
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - (int)fa.sharedSizeBytes);
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
 // launch K6 for one chunk of <= BATCH_CHUNK pods whose inputs are in device memory
 int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const int32_t* d_ncont, int max_c, const int32_t* d_policy,
                     const LoadParams& lp, uint64_t seed_seq, int32_t* d_node, int32_t* d_score, int32_t* d_gidx,
@@ -244,7 +261,7 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     if (grid < 1) grid = 1;
     if (grid > (uint32_t)h->num_sms) grid = (uint32_t)h->num_sms;
     const uint32_t rpb = (N + grid - 1) / grid;
-    const uint32_t block = schedule_block_size(rpb);
+    const uint32_t block = schedule_block(rpb);
     const size_t smem = (size_t)rpb * 32 + (size_t)((rpb + 31) / 32) * 8 + 16;  // rows + two feasbits buffers
     if (smem + 2048 > (size_t)h->smem_optin)  // (2 KB: the kernel's static shared memory)
         return fail(h, NGS_ERR_UNSUPPORTED, "%u rows per SM need %zu B shared memory (> %d): shard the cluster over more GPUs", rpb, smem, h->smem_optin);
@@ -256,10 +273,7 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
         pthread_mutex_lock(&s_mu);
         cudaError_t e = cudaSuccess;
         if (!s_done[dev]) {
-            cudaFuncAttributes fa;
-            e = cudaFuncGetAttributes(&fa, k_schedule);  // the opt-in limit covers static + dynamic shared memory
-            if (e == cudaSuccess)
-                e = cudaFuncSetAttribute(k_schedule, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem_optin - (int)fa.sharedSizeBytes);
+            e = schedule_allow_max_smem(h->smem_optin);
             s_done[dev] = e == cudaSuccess;
         }
         pthread_mutex_unlock(&s_mu);
@@ -310,7 +324,7 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     h->dbg_grid = grid;
 #endif
     void* args[] = {&bp};
-    CU(h, cudaLaunchCooperativeKernel((void*)k_schedule, dim3(grid), dim3(block), args, smem, h->stream));
+    CU(h, cudaLaunchCooperativeKernel(schedule_kernel(rpb), dim3(grid), dim3(block), args, smem, h->stream));
     h->stats.kernel_launches += 2;
     h->stats.node_evals += (uint64_t)P * N;
     h->stats.pods_scheduled += P;
@@ -1010,7 +1024,7 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     if (grid > (uint32_t)dv->num_sms) grid = (uint32_t)dv->num_sms;
     if (grid > NGS_NOALLOC_MAX_CTAS) return NGS_ERR_NOALLOC_LIMIT;  // the per-CTA slots would not fit
     const uint32_t rpb = (N + grid - 1) / grid;
-    const uint32_t block = schedule_block_size(rpb);
+    const uint32_t block = schedule_block(rpb);
     const size_t smem = (size_t)rpb * 32 + (size_t)((rpb + 31) / 32) * 8 + 16;
     if (smem + 2048 > (size_t)dv->smem_optin) return NGS_ERR_UNSUPPORTED;
 
@@ -1028,12 +1042,7 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
         cudaMemsetAsync(err, 0, sizeof(int32_t), st) != cudaSuccess)
         return NGS_ERR_CUDA;
     // (an upper bound per device: asking for the device maximum once keeps it valid for every later launch, also of handles)
-    {
-        cudaFuncAttributes fa;
-        if (cudaFuncGetAttributes(&fa, k_schedule) != cudaSuccess ||
-            cudaFuncSetAttribute(k_schedule, cudaFuncAttributeMaxDynamicSharedMemorySize, dv->smem_optin - (int)fa.sharedSizeBytes) != cudaSuccess)
-            return NGS_ERR_CUDA;
-    }
+    if (schedule_allow_max_smem(dv->smem_optin) != cudaSuccess) return NGS_ERR_CUDA;
     k_prep_demands<<<(n_pods + 127) / 128, 128, 0, st>>>(d_percent, d_n_containers, max_c, d_policy, n_pods, dem, err);
     if (cudaGetLastError() != cudaSuccess) return NGS_ERR_CUDA;
 
@@ -1071,7 +1080,7 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     bp.err = err;
     bp.rows_per_block = rpb;
     void* args[] = {&bp};
-    if (cudaLaunchCooperativeKernel((void*)k_schedule, dim3(grid), dim3(block), args, smem, st) != cudaSuccess) return NGS_ERR_CUDA;
+    if (cudaLaunchCooperativeKernel(schedule_kernel(rpb), dim3(grid), dim3(block), args, smem, st) != cudaSuccess) return NGS_ERR_CUDA;
     int32_t dev_status = NGS_OK;  // device-side validation / timeout word of this batch
     if (cudaMemcpyAsync(&dev_status, err, sizeof(dev_status), cudaMemcpyDeviceToHost, st) != cudaSuccess) return NGS_ERR_CUDA;
     if (cudaStreamSynchronize(st) != cudaSuccess) return NGS_ERR_CUDA;

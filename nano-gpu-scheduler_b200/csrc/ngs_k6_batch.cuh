@@ -63,6 +63,11 @@ __device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long
     return v;
 }
 
+#ifndef NGS_K6_EXCLUSIVE_ROWS
+#define NGS_K6_EXCLUSIVE_ROWS 2048
+#endif
+constexpr uint32_t K6_EXCLUSIVE_ROWS = NGS_K6_EXCLUSIVE_ROWS;
+constexpr uint32_t K6_ROW_PER_THREAD_ITERS = 2;  // up to this many rows per worker thread the simple filter loop is the faster one  // up to this many rows per CTA control warp 0 keeps a scheduler to itself
 constexpr long long SPIN_TIMEOUT_CYCLES = 2000000000LL;   // ~1 s: waits on CTAs of the same (cooperative, fully resident) launch
 constexpr long long PEER_TIMEOUT_CYCLES = 16000000000LL;  // ~8 s: waits on another GPU, whose host may launch its kernel later
 
@@ -367,14 +372,40 @@ __device__ __forceinline__ void filter_pass(const SmemRows& S, const SortedDeman
         cnt = c;
         return;
     }
-    k1 = 0;
-    k2 = 0;
+    // Everything the loop needs of the demand sits in registers (the shared-memory stores of the random
+    // branch would otherwise make the compiler reload it per row), and a lane tracks its best two rows by
+    // score alone: it visits its rows in ascending order, so among equal scores the earlier row is the one
+    // the key order (higher score, then lower node index) prefers, and strict comparisons keep it.
+    const int nz = dem->nz, d1 = dem->d[0], d2 = dem->d[1];
+    const bool generic = nz == 0 || nz > 4 || d1 > 255;  // the top-4 word cannot decide (classify_top4's FEAS_FALLBACK cases)
+    const bool may_stay_open = nz >= 3;                   // one or two containers are always settled by the shortcuts
+    const uint32_t sh = nz >= 1 ? 8u * (uint32_t)(nz - 1) : 0u;
+    const int32_t* __restrict__ rate = spread ? S.scS : S.scB;
+    constexpr int NONE = INT32_MIN;
+    int s1 = NONE, s2 = NONE;
+    uint32_t r1 = 0, r2 = 0;
     for (uint32_t it = 0; it < n_iter; it++) {
         const uint32_t r = it * WT + wt;
+        const bool in = r < my_rows;
         int cls = FEAS_NO;
-        if (r < my_rows) {
-            cls = classify_top4(S.top4[r], dem, true);  // unknown nodes hold all zeros: FEAS_NO (or YES for an empty demand,
-            if (cls == FEAS_FALLBACK || dem->nz == 0) {  //  which the full-row path below sorts out)
+        bool full = in && generic;
+        if (!generic) {
+            // classify_top4 with the demand in registers, written without branches: this is the path nearly every
+            // row takes, and nested divergent branches cost more than the arithmetic they skip
+            const uint32_t t4 = in ? S.top4[r] : 0u;  // rows beyond the range and unknown nodes read as all zeros: infeasible
+            const int t0 = (int)(t4 & 0xFFu);
+            const bool yes = (int)((t4 >> sh) & 0xFFu) >= d1;  // the nz-th largest cell holds d1
+            const bool no = t0 < d1;                            // not even the largest does
+            cls = yes ? FEAS_YES : (no ? FEAS_NO : FEAS_UNDECIDED);
+            if (nz == 2) {  // (warp-uniform) exactly one cell holds d1: it is the row maximum
+                const bool mid = !yes && !no;
+                full = mid && t0 == 255;  // saturated: the true maximum is unknown, look at the whole row
+                const bool fits = (int)((t4 >> 8) & 0xFFu) >= d2 || t0 - d1 >= d2;
+                cls = mid ? (fits ? FEAS_YES : FEAS_NO) : cls;
+            }
+        }
+        if (__any_sync(0xFFFFFFFFu, full)) {  // rare (or the generic case): classify from the full row
+            if (full) {
                 cls = FEAS_NO;
                 const uint32_t meta = S.meta[r];
                 if (((meta >> 24) & 15) != 0) {
@@ -384,38 +415,40 @@ __device__ __forceinline__ void filter_pass(const SmemRows& S, const SortedDeman
                 }
             }
         }
-        // rows the shortcuts leave open are searched exactly right away, 8 lanes per row, 4 rows a time;
-        // the verdict goes back to the lane that owns the row
-        uint32_t und = __ballot_sync(0xFFFFFFFFu, cls == FEAS_UNDECIDED);
-        while (und) {  // warp-uniform
-            uint32_t t = und;
-            for (uint32_t q = 0; q < (lane >> 3); q++) t &= t - 1;  // group j takes the j-th open row
-            const bool has = t != 0;
-            const uint32_t rr = __shfl_sync(0xFFFFFFFFu, r, has ? __ffs(t) - 1 : 0);
-            const uint32_t meta = S.meta[rr];
-            const int G = has ? (int)((meta >> 24) & 15) : 0;
-            const bool ok = choose_group8<false>(g, gbase, smem_cell(S, rr, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem,
-                                                 nullptr, nullptr, nullptr);
-            const uint32_t okb = __ballot_sync(0xFFFFFFFFu, has && ok && g == 0);  // group j's verdict at bit 8j
-            if ((und >> lane) & 1u) {
-                const uint32_t j = __popc(und & ((1u << lane) - 1u));
-                if (j < 4) cls = ((okb >> (8 * j)) & 1u) ? FEAS_YES : FEAS_NO;
-            }
-            und &= und - 1;
-            und &= und - 1;
-            und &= und - 1;
-            und &= und - 1;
-        }
-        if (cls == FEAS_YES) {
-            const uint64_t key = make_key(spread ? S.scS[r] : S.scB[r], node0 + r);
-            if (key > k1) {
-                k2 = k1;
-                k1 = key;
-            } else if (key > k2) {
-                k2 = key;
+        if (may_stay_open) {  // (warp-uniform)
+            // rows the shortcuts leave open are searched exactly right away, 8 lanes per row, 4 rows a time;
+            // the verdict goes back to the lane that owns the row
+            uint32_t und = __ballot_sync(0xFFFFFFFFu, cls == FEAS_UNDECIDED);
+            while (und) {  // warp-uniform
+                uint32_t t = und;
+                for (uint32_t q = 0; q < (lane >> 3); q++) t &= t - 1;  // group j takes the j-th open row
+                const bool has = t != 0;
+                const uint32_t rr = __shfl_sync(0xFFFFFFFFu, r, has ? __ffs(t) - 1 : 0);
+                const uint32_t meta = S.meta[rr];
+                const int G = has ? (int)((meta >> 24) & 15) : 0;
+                const bool ok = choose_group8<false>(g, gbase, smem_cell(S, rr, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem,
+                                                     nullptr, nullptr, nullptr);
+                const uint32_t okb = __ballot_sync(0xFFFFFFFFu, has && ok && g == 0);  // group j's verdict at bit 8j
+                if ((und >> lane) & 1u) {
+                    const uint32_t j = __popc(und & ((1u << lane) - 1u));
+                    if (j < 4) cls = ((okb >> (8 * j)) & 1u) ? FEAS_YES : FEAS_NO;
+                }
+                und &= und - 1;
+                und &= und - 1;
+                und &= und - 1;
+                und &= und - 1;
             }
         }
+        // best two by score, branch-free: an infeasible row enters as NONE and changes nothing
+        const int sc = cls == FEAS_YES ? rate[r] : NONE;
+        const bool gt1 = sc > s1, gt2 = sc > s2;
+        s2 = gt1 ? s1 : (gt2 ? sc : s2);
+        r2 = gt1 ? r1 : (gt2 ? r : r2);
+        s1 = gt1 ? sc : s1;
+        r1 = gt1 ? r : r1;
     }
+    k1 = s1 != NONE ? make_key(s1, node0 + r1) : 0;
+    k2 = s2 != NONE ? make_key(s2, node0 + r2) : 0;
 }
 
 // the warp's best two keys from every lane's best two: m1 = max of the k1; m2 = the best of what is
@@ -468,6 +501,10 @@ __device__ __forceinline__ uint64_t fresh_key_of_row(const SmemRows& S, uint32_t
 //      exact plan of this CTA's best row, 8 lanes per row.
 //      (random policy: slots carry feasible counts; seeded k-th pick over the feasible set)
 //   bind (warp 0 of the CTA that owns the winner): publish the plan, update the row.
+// ALL_WORK (chosen by the host from the rows per CTA, schedule_kernel()): every warp below the control warps
+// filters; otherwise the warps that share control warp 0's scheduler stay idle.  A compile-time choice: as a
+// run-time flag it cost the small-CTA case 1.8 %.
+template <bool ALL_WORK>
 __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ SortedDemand s_dem[4];
@@ -501,12 +538,15 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     // Warps map to the SM's four schedulers by warp id % 4.  Control warp 0 runs the latency-critical plan
     // search; the worker warps that would share its scheduler stay idle (they own no rows), so that its
     // instructions never queue behind the filter's.
+    // When a CTA holds so many rows that the filter, not the exchange, sets the pace (several rows per worker
+    // thread), that scheduler is worth more filtering: then every warp below the control warps owns rows.
     const uint32_t NWARP = nwarps - 2;                     // warps below the control warps
+    constexpr bool all_work = ALL_WORK;
     const uint32_t csm = NWARP & 3u;                       // scheduler of control warp 0
-    const uint32_t idle_below = (warp + 3u - csm) >> 2;    // idle warps among [0, warp)
-    const uint32_t NW = NWARP - ((NWARP + 3u - csm) >> 2); // worker warps that own rows
+    const uint32_t idle_below = all_work ? 0u : (warp + 3u - csm) >> 2;    // idle warps among [0, warp)
+    const uint32_t NW = all_work ? NWARP : NWARP - ((NWARP + 3u - csm) >> 2); // worker warps that own rows
     const uint32_t WT = NW * 32u;
-    const bool is_worker = warp < NWARP && (warp & 3u) != csm;
+    const bool is_worker = warp < NWARP && (all_work || (warp & 3u) != csm);
     const bool is_control = warp >= NWARP;
     const uint32_t ww = warp - idle_below;                 // worker index (meaningful for workers)
     const uint32_t wt = ww * 32u + lane;
@@ -646,6 +686,9 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
         }
         if (is_worker) {
             // ---- workers: filter pod p+1 (pod p's bind may still be in flight: its row is dealt with above) ----
+#ifdef NGS_PHASE_TIMING
+            tq = clock64();  // (profiling) the filter alone, without the wait at the barrier before it
+#endif
             if (more) {
                 filter_pass(S, dem_next, wt, WT, n_iter, my_rows, T.first + row0, lane, g, gbase, S.feasbits + ((p + 1) & 1) * fwords, k1,
                             k2, cnt);
@@ -917,5 +960,6 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
         for (int i = 0; i < 8; i++) bp.dbg[blockIdx.x * 16 + i] = (unsigned long long)ph[i];
     if (tid == NWARP * 32 + 32 && bp.dbg)
         for (int i = 0; i < 8; i++) bp.dbg[blockIdx.x * 16 + 8 + i] = (unsigned long long)ph[i];
+    if (is_worker && lane == 0 && bp.dbg) bp.dbg[4096 + blockIdx.x * 32 + ww] = (unsigned long long)ph[0];  // filter time of every worker warp
 #endif
 }

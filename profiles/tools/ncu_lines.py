@@ -26,7 +26,8 @@ def sass_lines(so, kernel):
         for ln in dis.splitlines():
             m = re.match(r"\s*\.section\s+\.text\.(\S+?),", ln)
             if m:
-                active = kernel in m.group(1)
+                # the mangled name carries the identifier's length: "10k_schedule" must not match "14k_schedule_one"
+                active = ("%d%s" % (len(kernel), kernel)) in m.group(1) or kernel == m.group(1)
                 cur_line = None
                 continue
             if not active:
@@ -46,7 +47,7 @@ def sass_lines(so, kernel):
 def main():
     rep, so, kernel = sys.argv[1], sys.argv[2], sys.argv[3]
     top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "-k", "regex:" + kernel], capture_output=True, text=True).stdout
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "-k", "regex:" + kernel + "$"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
     hi = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
     hdr = rows[hi]

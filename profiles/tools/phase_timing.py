@@ -55,3 +55,11 @@ for who, off in (("control warp 0 (plan, bind)", 0), ("control warp 1 (exchange)
         print(f"  {names[i]:84s} {col.min():8.0f} {np.median(col):8.0f} {col.max():8.0f}")
     print(f"  {'total':14s} {a[:, off:off + 8].sum(axis=1).mean():8.0f}")
 
+
+w = buf[4096: 4096 + 32 * g].reshape(g, 32).astype(np.float64) / P
+nw = int((w[0] > 0).sum())
+per_cta = w[:, :nw].max(axis=1)
+print(f"workers: filter of the NEXT pod, cycles per pod, slowest warp of each CTA ({nw} worker warps): min {per_cta.min():.0f} median {np.median(per_cta):.0f} "
+      f"max {per_cta.max():.0f} (CTA {int(per_cta.argmax())}); within the slowest CTA: fastest warp {w[int(per_cta.argmax()), :nw].min():.0f}")
+order = np.argsort(-per_cta)[:6]
+print("slowest CTAs:", [(int(c), int(per_cta[c])) for c in order])
