@@ -26,8 +26,11 @@ def sass_lines(so, kernel):
         for ln in dis.splitlines():
             m = re.match(r"\s*\.section\s+\.text\.(\S+?),", ln)
             if m:
-                # the mangled name carries the identifier's length: "10k_schedule" must not match "14k_schedule_one"
-                active = ("%d%s" % (len(kernel), kernel)) in m.group(1) or kernel == m.group(1)
+                # the mangled name carries the identifier's length: "10k_schedule" must not match "14k_schedule_one";
+                # "k_schedule<0>" selects the instantiation with a bool argument ("10k_scheduleILb0EE")
+                base, _, targ = kernel.partition("<")
+                want = "%d%s" % (len(base), base) + ("ILb%sEE" % targ.rstrip(">") if targ else "")
+                active = want in m.group(1) or kernel == m.group(1)
                 cur_line = None
                 continue
             if not active:
@@ -47,7 +50,7 @@ def sass_lines(so, kernel):
 def main():
     rep, so, kernel = sys.argv[1], sys.argv[2], sys.argv[3]
     top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "-k", "regex:" + kernel + "$"], capture_output=True, text=True).stdout
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "-k", "regex:" + kernel.partition("<")[0] + "$"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
     hi = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
     hdr = rows[hi]
