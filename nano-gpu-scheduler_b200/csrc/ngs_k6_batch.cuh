@@ -384,15 +384,18 @@ __device__ __forceinline__ void filter_pass(const SmemRows& S, const SortedDeman
     constexpr int NONE = INT32_MIN;
     int s1 = NONE, s2 = NONE;
     uint32_t r1 = 0, r2 = 0;
-    for (uint32_t it = 0; it < n_iter; it++) {
-        const uint32_t r = it * WT + wt;
+    const bool may_need_row = generic || nz == 2;  // (warp-uniform) only then can a lane ask for the full row
+    const uint32_t* top4p = S.top4 + wt;           // this lane's entries, WT apart: pointers advance, no index arithmetic per row
+    const int32_t* ratep = rate + wt;
+    uint32_t r = wt;
+    for (uint32_t it = 0; it < n_iter; it++, r += WT, top4p += WT, ratep += WT) {
         const bool in = r < my_rows;
         int cls = FEAS_NO;
         bool full = in && generic;
         if (!generic) {
             // classify_top4 with the demand in registers, written without branches: this is the path nearly every
             // row takes, and nested divergent branches cost more than the arithmetic they skip
-            const uint32_t t4 = in ? S.top4[r] : 0u;  // rows beyond the range and unknown nodes read as all zeros: infeasible
+            const uint32_t t4 = in ? *top4p : 0u;  // rows beyond the range and unknown nodes read as all zeros: infeasible
             const int t0 = (int)(t4 & 0xFFu);
             const bool yes = (int)((t4 >> sh) & 0xFFu) >= d1;  // the nz-th largest cell holds d1
             const bool no = t0 < d1;                            // not even the largest does
@@ -404,7 +407,7 @@ __device__ __forceinline__ void filter_pass(const SmemRows& S, const SortedDeman
                 cls = mid ? (fits ? FEAS_YES : FEAS_NO) : cls;
             }
         }
-        if (__any_sync(0xFFFFFFFFu, full)) {  // rare (or the generic case): classify from the full row
+        if (may_need_row && __any_sync(0xFFFFFFFFu, full)) {  // rare (or the generic case): classify from the full row
             if (full) {
                 cls = FEAS_NO;
                 const uint32_t meta = S.meta[r];
@@ -440,7 +443,7 @@ __device__ __forceinline__ void filter_pass(const SmemRows& S, const SortedDeman
             }
         }
         // best two by score, branch-free: an infeasible row enters as NONE and changes nothing
-        const int sc = cls == FEAS_YES ? rate[r] : NONE;
+        const int sc = cls == FEAS_YES ? *ratep : NONE;
         const bool gt1 = sc > s1, gt2 = sc > s2;
         s2 = gt1 ? s1 : (gt2 ? sc : s2);
         r2 = gt1 ? r1 : (gt2 ? r : r2);
