@@ -405,6 +405,12 @@ def run_b200(args):
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": f"{pods} pods x {n} nodes in {dt:.1f} s, oracle/ C restatement of the Go dealer "
                                               "(omits the reference's per-node SHA-256, map allocation and klog, so it is faster than the Go binary)"}
+            # also one thread and the reference's own fan-out of four goroutines (dealer.go:113), on short samples
+            by_threads = {str(threads): v}
+            for t in (1, 4):
+                if t < threads:
+                    by_threads[str(t)] = time_oracle(cfg, gcount, free, tables, pc, nc, t, min(2.0, args.cpu_seconds))[0]
+            line["cpu_baseline"]["by_threads"] = by_threads
         except Exception as e:  # the baseline must never take the GPU number down with it
             line["cpu_baseline"] = {"error": repr(e)}
     d.close()
