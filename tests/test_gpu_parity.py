@@ -830,3 +830,26 @@ def test_load_mode_with_other_period_lists(ngs, periods):
                 want = oc.schedule_batch(pc[p : p + 1], nc[p : p + 1], policy, load=ol, seed=2, seq0=p)
                 assert all(np.array_equal(x, y) for x, y in zip(got, want)), (policy, p)
             assert_same_snapshot(oc, d)
+
+
+@pytest.mark.parametrize("load", [False, True])
+def test_many_rows_per_cta_all_policies(ngs, load):
+    """clusters beyond 2048 rows per CTA run the batch kernel's all-warps-filter instantiation (k_schedule<true>):
+    mixed policies, multi-container pods, zero-percent containers and load-aware scoring against the oracle"""
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    n, P = 330_000, 96  # 148 SMs -> 2230 rows per CTA
+    oc, d, _, _ = make_pair(ngs, n, 0.6, 0xA77, hetero=True)
+    pc, nc = wl.make_pods(P, 1, 4, 0, 14, 0xA77, max_c=4)
+    pol = (np.arange(P) % 3).astype(np.int32)
+    with d:
+        gl = ol = None
+        if load:
+            fill_load_tables(oc, d, n, 0xA77)
+            gl, ol = load_ctx_pair(ngs)
+        got = d.schedule_batch(pc, nc, pol, load=gl, seed=11, seq0=3)
+        want = oc.schedule_batch(pc, nc, pol, load=ol, seed=11, seq0=3, n_threads=8)
+        for a, b, what in zip(got, want, ("node", "score", "gpu_idx")):
+            assert np.array_equal(a, b), (what, np.flatnonzero((np.asarray(a) != np.asarray(b)).reshape(P, -1).any(axis=1))[:8])
+        assert (got[0] >= 0).sum() > P // 2
+        assert_same_snapshot(oc, d)
