@@ -207,6 +207,27 @@ void NodeIndex::Insert(std::string_view name, uint32_t row) {
     count_++;
 }
 
+// ---- the controller's pod event handlers -------------------------------------------------------
+SyncResult SyncPod(Dealer& d, const Pod* pod) {  // controller.go:210-245
+    if (!pod) return {true, ""};                 // "has been deleted": logged only
+    if (pod->completed) {                        // utils.IsCompletedPod
+        d.Release(*pod);                         // an error is logged, not returned (:228-230)
+        d.PrintStatus(*pod, "release");
+        return {true, ""};
+    }
+    if (pod->node_name.empty()) return {true, ""};
+    const Error e = d.Allocate(*pod);
+    d.PrintStatus(*pod, "allocate");
+    if (!e.empty()) return {false, e};
+    return {true, ""};
+}
+bool NeedUpdate(Dealer& d, const Pod& oldPod, const Pod& newPod) {  // controller.go:303-310
+    if (d.KnownPod(oldPod) && newPod.completed) return true;       // 1. turned complete or failed
+    if (!d.KnownPod(oldPod) && !d.PodReleased(oldPod) && IsAssumed(newPod)) return true;  // 2. unknown, unreleased, GPU annotation set
+    return false;
+}
+void DeletePodFromCache(Dealer& d, const Pod& pod) { d.Forget(pod); }  // controller.go:356
+
 // ---- Dealer -----------------------------------------------------------------------------------
 Dealer::Dealer(ClusterSource* src, RaterKind rater, uint32_t max_nodes, int device) : src_(src), rater_(rater) {
     int rc = ngs_create(&h_, device, max_nodes, 0, nullptr);

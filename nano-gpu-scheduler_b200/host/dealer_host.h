@@ -218,6 +218,16 @@ class Dealer {
 // encoding/json's string encoder (defined in extender_codec.cpp, declared again in extender_codec.h)
 void AppendJSONString(std::string* out, std::string_view s);
 
+// The controller's pod event handlers, the callers of Allocate / Release / Forget (pkg/controller/controller.go).
+// SyncPod: Controller.syncPod (:210-245) for the pod the lister returned (nullptr = NotFound: nothing to do).
+struct SyncResult {
+    bool forget;  // the work-queue item is done
+    Error err;
+};
+SyncResult SyncPod(Dealer& d, const Pod* pod);
+bool NeedUpdate(Dealer& d, const Pod& oldPod, const Pod& newPod);  // updatePodInCache (:289-335): does the update go on the queue?
+void DeletePodFromCache(Dealer& d, const Pod& pod);                // deletePodFromCache (:337-357)
+
 // helpers mirrored from the reference (used by the tests, too)
 std::vector<int32_t> NewDemandFromPod(const Pod& pod);                                   // allocate.go:54-62
 Error NewPlanFromPod(const Pod& pod, std::vector<int32_t>* demand, std::vector<int32_t>* gpu_idx);  // allocate.go:29-50

@@ -330,6 +330,34 @@ static void TestAnnotatorNodeIngestion() {
     CHECK(d.Score({"busy", "idle"}, pod, spec, true)[0] == 48);
 }
 
+// the informer side: syncPod / updatePodInCache / deletePodFromCache (controller.go:210-357) drive Allocate, Release, Forget
+static void TestControllerPodEvents() {
+    FakeCluster fc;
+    fc.add("n", 2);
+    Dealer d(&fc, RaterKind::Binpack, 8);
+    Pod pending = MockPodWithDemand({60, 30}, "p1");
+    CHECK(SyncPod(d, nullptr).forget);                                    // deleted before the worker got to it
+    CHECK(SyncPod(d, &pending).forget && d.Status().empty());             // not scheduled yet: nothing to account
+    Pod running = MockPodWithPlan({60, 30}, {1, 1}, "n", "p1");           // the scheduler bound it; the informer sees the update
+    CHECK(NeedUpdate(d, pending, running));                               // unknown, unreleased, annotation set
+    SyncResult r = SyncPod(d, &running);
+    CHECK(r.forget && r.err.empty() && d.KnownPod(running));
+    CHECK((d.Status()["n"] == std::vector<int>{100, 10}));
+    CHECK(!NeedUpdate(d, running, running));                              // known and still running: no work
+    Pod bad = MockPodWithPlan({60}, {1}, "n", "p2");                      // a plan that no longer fits
+    r = SyncPod(d, &bad);
+    CHECK(!r.forget && !r.err.empty());                                   // re-queued with the Allocate error (:238-240)
+    Pod done = running;
+    done.completed = true;
+    CHECK(NeedUpdate(d, running, done));                                  // known pod turned complete
+    CHECK(SyncPod(d, &done).forget && d.PodReleased(done) && !d.KnownPod(done));
+    CHECK((d.Status()["n"] == std::vector<int>{100, 100}));
+    CHECK(!NeedUpdate(d, done, done));                                    // released: later updates are ignored
+    DeletePodFromCache(d, done);
+    CHECK(!d.PodReleased(done));                                          // Forget drops the bookkeeping, no capacity moves
+    CHECK((d.Status()["n"] == std::vector<int>{100, 100}));
+}
+
 // DealerImpl serves the extender's HTTP handlers concurrently behind d.Lock (dealer.go:81): four
 // threads filter, score, bind and release against one Dealer; afterwards no capacity is lost or made up.
 static void TestConcurrentCallers() {
@@ -399,6 +427,7 @@ int main() {
     TestAllocateFromAnnotationsAndRebuild();
     TestLoadAwareScoring();
     TestAnnotatorNodeIngestion();
+    TestControllerPodEvents();
     TestConcurrentCallers();
     printf("%s: %d checks, %d failed\n", g_fail ? "HOST TESTS FAILED" : "HOST TESTS OK", g_checks, g_fail);
     return g_fail ? 1 : 0;
