@@ -207,6 +207,135 @@ void NodeIndex::Insert(std::string_view name, uint32_t row) {
     count_++;
 }
 
+// ---- policy file --------------------------------------------------------------------------------
+bool ParseGoDuration(const std::string& str, int64_t* out_ns) {  // time.ParseDuration: [-+]?([0-9]*(\.[0-9]*)?[a-zµ]+)+
+    size_t i = 0;
+    const size_t n = str.size();
+    if (n == 0) return false;
+    bool neg = false;
+    if (str[i] == '+' || str[i] == '-') neg = str[i++] == '-';
+    if (i == n) return false;
+    if (str.compare(i, std::string::npos, "0") == 0) {
+        *out_ns = 0;
+        return true;
+    }
+    long double total = 0;
+    while (i < n) {
+        long double v = 0, scale = 1;
+        bool digits = false;
+        while (i < n && str[i] >= '0' && str[i] <= '9') v = v * 10 + (str[i++] - '0'), digits = true;
+        if (i < n && str[i] == '.') {
+            i++;
+            while (i < n && str[i] >= '0' && str[i] <= '9') scale /= 10, v += (str[i++] - '0') * scale, digits = true;
+        }
+        if (!digits) return false;
+        size_t u = i;
+        while (i < n && str[i] != '.' && !(str[i] >= '0' && str[i] <= '9')) i++;
+        const std::string unit = str.substr(u, i - u);
+        long double mult;
+        if (unit == "ns") mult = 1;
+        else if (unit == "us" || unit == "\xc2\xb5s" || unit == "\xce\xbcs") mult = 1e3L;  // us, µs (U+00B5), μs (U+03BC)
+        else if (unit == "ms") mult = 1e6L;
+        else if (unit == "s") mult = 1e9L;
+        else if (unit == "m") mult = 60e9L;
+        else if (unit == "h") mult = 3600e9L;
+        else return false;
+        total += v * mult;
+    }
+    if (total > 9.2e18L) return false;
+    *out_ns = (int64_t)(neg ? -total : total);
+    return true;
+}
+
+PolicySpec ParsePolicyConfig(const std::string& text, Error* err) {
+    PolicySpec spec;
+    if (err) err->clear();
+    // lines -> (indent, content without comment); the only structure needed: spec: / syncPeriod: / "- name:" / "period:"
+    struct Line {
+        int indent;
+        std::string body;
+    };
+    std::vector<Line> lines;
+    size_t pos = 0;
+    while (pos <= text.size()) {
+        size_t e = text.find('\n', pos);
+        if (e == std::string::npos) e = text.size();
+        std::string ln = text.substr(pos, e - pos);
+        pos = e + 1;
+        bool in_s = false, in_d = false;
+        for (size_t k = 0; k < ln.size(); k++) {  // a comment starts at an unquoted '#' that begins the line or follows a blank
+            if (ln[k] == '\'' && !in_d) in_s = !in_s;
+            else if (ln[k] == '"' && !in_s) in_d = !in_d;
+            else if (ln[k] == '#' && !in_s && !in_d && (k == 0 || ln[k - 1] == ' ' || ln[k - 1] == '\t')) {
+                ln.erase(k);
+                break;
+            }
+        }
+        while (!ln.empty() && (ln.back() == ' ' || ln.back() == '\t' || ln.back() == '\r')) ln.pop_back();
+        size_t ind = 0;
+        while (ind < ln.size() && ln[ind] == ' ') ind++;
+        if (ind < ln.size() && ln[ind] == '\t') {
+            if (err) *err = "yaml: found character that cannot start any token";
+            return PolicySpec();
+        }
+        if (ind == ln.size()) continue;
+        lines.push_back({(int)ind, ln.substr(ind)});
+    }
+    auto scalar = [](std::string v) {
+        while (!v.empty() && v.front() == ' ') v.erase(0, 1);
+        if (v.size() >= 2 && ((v.front() == '"' && v.back() == '"') || (v.front() == '\'' && v.back() == '\''))) v = v.substr(1, v.size() - 2);
+        return v;
+    };
+    int spec_ind = -1, sp_ind = -1, item_ind = -1;
+    bool in_spec = false, in_sp = false;
+    for (const Line& L : lines) {
+        if (in_sp && L.indent <= sp_ind && L.body.compare(0, 1, "-") != 0) in_sp = false;  // left the sequence
+        if (in_sp && L.indent < sp_ind) in_sp = false;
+        if (in_spec && L.indent <= spec_ind) in_spec = in_sp = false;
+        if (!in_spec) {
+            if (L.indent == 0 && (L.body == "spec:" || L.body.compare(0, 5, "spec:") == 0)) {
+                in_spec = true;
+                spec_ind = L.indent;
+            }
+            continue;
+        }
+        if (!in_sp) {
+            if (L.body == "syncPeriod:") {
+                in_sp = true;
+                sp_ind = L.indent;
+                item_ind = -1;
+            }
+            continue;
+        }
+        std::string body = L.body;
+        int ind = L.indent;
+        if (body[0] == '-') {  // a new sequence entry: "- name: x"
+            spec.sync_period.emplace_back();
+            size_t k = 1;
+            while (k < body.size() && body[k] == ' ') k++;
+            ind += (int)k;
+            body = body.substr(k);
+            item_ind = ind;
+            if (body.empty()) continue;
+        } else if (spec.sync_period.empty() || ind != item_ind) {
+            continue;  // deeper or foreign structure: not part of a Period
+        }
+        const size_t c = body.find(':');
+        if (c == std::string::npos) continue;
+        const std::string key = body.substr(0, c), val = scalar(body.substr(c + 1));
+        if (key == "name") spec.sync_period.back().name = val;
+        else if (key == "period") {
+            int64_t ns = 0;
+            if (!ParseGoDuration(val, &ns)) {  // yaml.v2: cannot unmarshal into time.Duration -> the whole Unmarshal reports an error
+                if (err) *err = "yaml: unmarshal errors:\n  cannot unmarshal !!str `" + val + "` into time.Duration";
+                return PolicySpec();
+            }
+            spec.sync_period.back().period_ns = ns;
+        }
+    }
+    return spec;
+}
+
 // ---- the controller's pod event handlers -------------------------------------------------------
 SyncResult SyncPod(Dealer& d, const Pod* pod) {  // controller.go:210-245
     if (!pod) return {true, ""};                 // "has been deleted": logged only

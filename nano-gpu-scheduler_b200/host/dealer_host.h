@@ -228,6 +228,13 @@ SyncResult SyncPod(Dealer& d, const Pod* pod);
 bool NeedUpdate(Dealer& d, const Pod& oldPod, const Pod& newPod);  // updatePodInCache (:289-335): does the update go on the queue?
 void DeletePodFromCache(Dealer& d, const Pod& pod);                // deletePodFromCache (:337-357)
 
+// getSyncPeriodFormPolicyConfig (pkg/controller/controller.go:359-371): spec.syncPeriod of the policy file
+// (deploy/dynamic-scheduler-node-annotator-cm.yaml:7-16) -> PolicySpec.  The file is YAML; this reads the subset
+// the policy uses (block mappings and sequences, scalars, comments) and Go duration strings ("15s", "1m30s",
+// "500ms").  Like the reference, a file that does not parse yields an empty list (the error is only logged).
+PolicySpec ParsePolicyConfig(const std::string& yaml_text, Error* err = nullptr);
+bool ParseGoDuration(const std::string& s, int64_t* out_ns);  // time.ParseDuration
+
 // helpers mirrored from the reference (used by the tests, too)
 std::vector<int32_t> NewDemandFromPod(const Pod& pod);                                   // allocate.go:54-62
 Error NewPlanFromPod(const Pod& pod, std::vector<int32_t>* demand, std::vector<int32_t>* gpu_idx);  // allocate.go:29-50

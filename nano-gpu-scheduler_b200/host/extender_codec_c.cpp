@@ -179,6 +179,17 @@ char* ngsx_encode_priorities(const char* blob, const uint32_t* lens, const int32
     return dup_out(EncodeHostPriorityList(hosts, sc), out_n);
 }
 
+// the policy file -> "name=period_ns;name=period_ns" (or "!error text")
+char* ngsx_parse_policy(const char* text, size_t n, size_t* out_n) {
+    Error e;
+    const PolicySpec spec = ParsePolicyConfig(std::string(text, n), &e);
+    std::string o;
+    if (!e.empty()) o = "!" + e;
+    for (const Period& p : spec.sync_period) o += (o.empty() ? "" : ";") + p.name + "=" + std::to_string(p.period_ns);
+    return dup_out(o, out_n);
+}
+int ngsx_parse_duration(const char* s, size_t n, int64_t* out) { return ParseGoDuration(std::string(s, n), out) ? 1 : 0; }
+
 // NodeIndex self-check: insert n generated names, look all of them (and n absent ones) up; 0 = ok
 int ngsx_node_index_check(uint32_t n) {
     NodeIndex ix;

@@ -22,7 +22,7 @@ def lib():
         L = C.CDLL(HOST_LIB)
         for name in ("ngsx_decode_args", "ngsx_decode_binding", "ngsx_json_string", "ngsx_encode_filter", "ngsx_encode_filter_error",
                      "ngsx_encode_binding_result", "ngsx_encode_priorities", "ngsx_routes_predicate", "ngsx_routes_prioritize",
-                     "ngsx_routes_status", "ngsx_routes_bind_route"):
+                     "ngsx_routes_status", "ngsx_routes_bind_route", "ngsx_parse_policy"):
             getattr(L, name).restype = C.c_void_p
         L.ngsx_routes_new.restype = C.c_void_p
         L.ngsx_free.argtypes = [C.c_void_p]
@@ -96,6 +96,22 @@ def encode_priorities(hosts, scores):
     sc = (C.c_int32 * max(len(scores), 1))(*scores)
     n = C.c_size_t()
     return _take(lib().ngsx_encode_priorities(blob, lens, sc, len(hosts), C.byref(n)), n)
+
+
+def parse_policy(text):
+    """spec.syncPeriod of a policy file -> [(name, period_ns)]; raises ValueError with the decoder's message"""
+    b = _b(text)
+    n = C.c_size_t()
+    out = _take(lib().ngsx_parse_policy(b, C.c_size_t(len(b)), C.byref(n)), n).decode()
+    if out.startswith("!"):
+        raise ValueError(out[1:])
+    return [(kv.rsplit("=", 1)[0], int(kv.rsplit("=", 1)[1])) for kv in out.split(";")] if out else []
+
+
+def parse_duration(s):
+    b = _b(s)
+    v = C.c_int64()
+    return v.value if lib().ngsx_parse_duration(b, C.c_size_t(len(b)), C.byref(v)) else None
 
 
 def node_name(i):

@@ -24,7 +24,7 @@ def test_c_surface_exports():
                  "ngsx_encode_filter_error", "ngsx_encode_binding_result", "ngsx_encode_priorities", "ngsx_node_index_check",
                  "ngsx_routes_new", "ngsx_routes_add_assumed", "ngsx_routes_start", "ngsx_routes_predicate", "ngsx_routes_prioritize",
                  "ngsx_routes_counters", "ngsx_routes_bind", "ngsx_routes_destroy", "ngsx_free", "ngsx_routes_status", "ngsx_routes_add_pod",
-                 "ngsx_routes_bind_route"):
+                 "ngsx_routes_bind_route", "ngsx_parse_policy", "ngsx_parse_duration"):
         assert hasattr(L, name), name
 
 
@@ -242,3 +242,45 @@ def test_decode_fuzz_against_python_json():
                 json.loads(bytes(b).decode("utf-8", "replace"))
             except json.JSONDecodeError as e:
                 assert "Extra data" in str(e), bytes(b)
+
+
+def test_policy_file_and_go_durations():
+    """getSyncPeriodFormPolicyConfig (controller.go:359-371) on the policy the reference deploys
+    (deploy/dynamic-scheduler-node-annotator-cm.yaml:7-16, the text below is that ConfigMap's policy.yaml) and
+    time.ParseDuration for the period strings"""
+    from nano_gpu_scheduler_b200.routes import parse_duration, parse_policy
+
+    deployed = """apiVersion: v1
+kind: public-dynamic-scheduler
+spec:
+  syncPeriod:
+    ##gpu usage
+    - name: gpu_core_usage_avg
+      period: 15s
+    - name: gpu_memory_usage_avg
+      period: 15s
+"""
+    assert parse_policy(deployed) == [("gpu_core_usage_avg", 15 * 10**9), ("gpu_memory_usage_avg", 15 * 10**9)]
+    other = """
+spec:
+  priority:            # never read by the dealer (SURVEY a14)
+    - name: gpu_core_usage_avg
+      weight: 0.7
+  syncPeriod:
+  - name: "gpu_memory_usage_avg"   # quoted scalar, sequence at the parent's indent
+    period: 1m30s
+  - period: 500ms
+    name: gpu_core_usage_avg
+  - name: idle
+status: {}
+"""
+    assert parse_policy(other) == [("gpu_memory_usage_avg", 90 * 10**9), ("gpu_core_usage_avg", 500 * 10**6), ("idle", 0)]
+    assert parse_policy("kind: x\n") == [] and parse_policy("") == []
+    with pytest.raises(ValueError):
+        parse_policy("spec:\n  syncPeriod:\n    - name: a\n      period: soon\n")
+    table = {"15s": 15 * 10**9, "1m30s": 90 * 10**9, "1.5h": 5400 * 10**9, "500ms": 5 * 10**8, "2us": 2000, "3µs": 3000, "7ns": 7, "0": 0,
+             "-1m": -60 * 10**9, "+2s": 2 * 10**9, ".5s": 5 * 10**8, "1h2m3s4ms": 3723004 * 10**6}
+    for s, want in table.items():
+        assert parse_duration(s) == want, s
+    for bad in ("", "15", "s", "1d", "1 s", "--1s", "1s2"):
+        assert parse_duration(bad) is None, bad
