@@ -42,6 +42,14 @@ bool IsAssumed(const Pod& pod) {
     return it != pod.annotations.end() && it->second == "true";
 }
 
+uint64_t GetGPUPercentFromPodResource(const Pod& pod) {
+    uint64_t sum = 0;
+    for (const Container& c : pod.containers)
+        if (c.has_gpu_limit) sum += (uint64_t)c.gpu_percent;  // uint(val.Value())
+    return sum;
+}
+bool IsGPUSharingPod(const Pod& pod) { return GetGPUPercentFromPodResource(pod) > 0; }
+
 Error NewPlanFromPod(const Pod& pod, std::vector<int32_t>* demand, std::vector<int32_t>* gpu_idx) {  // allocate.go:29-50
     if (!IsAssumed(pod)) return fmt("pod %s/%s is not assumed", pod.ns.c_str(), pod.name.c_str());
     *demand = NewDemandFromPod(pod);

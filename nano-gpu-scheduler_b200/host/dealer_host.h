@@ -245,6 +245,8 @@ int GetGPUDeviceCountOfNode(const Node& node);              // pkg/utils/node.go
 std::string FormatLocalTime(int64_t unix_ns);               // Controller.getLocalTime (controller/node.go:137-141): Asia/Shanghai wall clock as "2006-01-02T15:04:05Z"
 std::string FormatMetricValue(double v);                    // prometheus.go:57-62: negative or NaN -> 0, then FormatFloat(v, 'f', 5, 64)
 bool IsAssumed(const Pod& pod);                             // pkg/utils/pod.go:81-83
+uint64_t GetGPUPercentFromPodResource(const Pod& pod);      // pkg/utils/pod.go:50-58: sum of the containers' gpu-percent limits
+bool IsGPUSharingPod(const Pod& pod);                       // pkg/utils/pod.go:27-29: the informer's filter for pods this dealer tracks
 Error getActiveDuration(const std::vector<Period>& list, const std::string& name, int64_t* out_ns);  // stats.go:57-66
 
 }  // namespace ngs_host

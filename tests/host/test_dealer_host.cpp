@@ -177,6 +177,8 @@ static void TestNewDemandAndPlanFromPod() {  // allocate_test.go:124-158
     CHECK(NewPlanFromPod(p, &d, &idx).empty());
     CHECK((d == std::vector<int32_t>{20, 40, 0}) && (idx == std::vector<int32_t>{1, 0, -1}));
     CHECK((NewDemandFromPod(MockPodWithDemand({5, 10})) == std::vector<int32_t>{5, 10}));
+    CHECK(GetGPUPercentFromPodResource(MockPodWithDemand({5, 10})) == 15 && IsGPUSharingPod(MockPodWithDemand({5, 10})));
+    CHECK(!IsGPUSharingPod(MockPodWithDemand({0, 0})) && !IsGPUSharingPod(MockPodWithDemand({})));  // pkg/utils/pod.go:27-29
     Pod q = MockPodWithDemand({20});
     CHECK_EQ_STR(NewPlanFromPod(q, &d, &idx), "pod default/pod-uid is not assumed");
 }
