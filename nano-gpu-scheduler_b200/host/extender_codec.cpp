@@ -664,22 +664,43 @@ bool ParseQuantityValue(std::string_view s, int64_t* out) {
         exp10 += eneg ? -ev : ev;
     } else return false;
 
+    // value = mant * 2^exp2 * 10^exp10, rounded up, saturated at int64.  With k = -exp10 > 0 it is split as
+    // mant = q * 10^k + r, value = q * 2^exp2 + ceil(r * 2^exp2 / 10^k), the last term with the common powers of
+    // two cancelled so that everything stays inside 128 bits (k is held to 28 digits; more fractional digits
+    // than that only keep a "something was there" flag, which is all a ceiling needs for them).
     const unsigned __int128 kMax = (unsigned __int128)INT64_MAX;
-    unsigned __int128 v = mant;
-    bool inexact = false;
-    if (mant == 0) {
+    if (mant == 0 && !overflow) {
         *out = 0;
         return true;
     }
-    if (overflow) v = kMax + 1;
-    for (int k = 0; k < exp2 && v <= kMax; k++) v *= 2;
-    for (; exp10 > 0 && v <= kMax; exp10--) v *= 10;
-    for (; exp10 < 0 && v != 0; exp10++) {
-        if (v % 10) inexact = true;
-        v /= 10;
+    unsigned __int128 v;
+    bool sticky = false;
+    if (overflow) {
+        v = kMax + 1;
+    } else if (exp10 >= 0) {
+        v = mant;
+        for (int k = 0; k < exp2 && v <= kMax; k++) v *= 2;
+        for (; exp10 > 0 && v <= kMax; exp10--) v *= 10;
+    } else {
+        int k = -exp10;
+        for (; k > 28; k--) {
+            if (mant % 10) sticky = true;
+            mant /= 10;
+        }
+        unsigned __int128 D = 1;
+        for (int i = 0; i < k; i++) D *= 10;
+        const unsigned __int128 q = mant / D, r = mant % D;
+        v = q;
+        for (int i = 0; i < exp2 && v <= kMax; i++) v *= 2;
+        const int c = exp2 < k ? exp2 : k;  // twos shared by 2^exp2 and 10^k
+        unsigned __int128 Dr = D, num = r;
+        for (int i = 0; i < c; i++) Dr /= 2;
+        for (int i = 0; i < exp2 - c; i++) num *= 2;  // r < 10^k, so num < 5^k * 2^exp2 <= 5^28 * 2^60 < 2^126
+        unsigned __int128 frac = num / Dr;
+        if (num % Dr) sticky = true;
+        if (v <= kMax) v += frac;
     }
-    if (exp10 < 0 && v == 0) inexact = true;  // a non-zero value scaled away entirely
-    if (inexact && !neg) v += 1;              // Value() = ScaledValue(0) rounds up
+    if (sticky && !neg && v <= kMax) v += 1;  // Value() = ScaledValue(0) rounds up
     if (v > kMax) v = kMax;                   // Value() saturates
     *out = neg ? -(int64_t)v : (int64_t)v;
     return true;

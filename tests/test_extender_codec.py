@@ -284,3 +284,41 @@ status: {}
         assert parse_duration(s) == want, s
     for bad in ("", "15", "s", "1d", "1 s", "--1s", "1s2"):
         assert parse_duration(bad) is None, bad
+
+
+def test_quantity_fuzz_against_fractions():
+    """ParseQuantityValue against exact rational arithmetic: <digits>[.<digits>]<suffix>, rounded up, saturated at int64"""
+    from fractions import Fraction
+    import math
+
+    rng = random.Random(23)
+    dec = {"n": Fraction(1, 10**9), "u": Fraction(1, 10**6), "m": Fraction(1, 1000), "": Fraction(1), "k": Fraction(10**3), "M": Fraction(10**6),
+           "G": Fraction(10**9), "T": Fraction(10**12), "P": Fraction(10**15), "E": Fraction(10**18)}
+    bina = {"Ki": 2**10, "Mi": 2**20, "Gi": 2**30, "Ti": 2**40, "Pi": 2**50, "Ei": 2**60}
+    for _ in range(4000):
+        ip = str(rng.randrange(0, 10 ** rng.randrange(1, 8)))
+        fp = "".join(rng.choice("0123456789") for _ in range(rng.randrange(0, 5)))
+        num = ip + ("." + fp if fp or rng.random() < 0.1 else "")
+        kind = rng.randrange(3)
+        if kind == 0:
+            suf = rng.choice(list(dec))
+            mult = dec[suf]
+        elif kind == 1:
+            suf = rng.choice(list(bina))
+            mult = Fraction(bina[suf])
+        else:
+            e = rng.randrange(-6, 7)
+            suf = rng.choice("eE") + (rng.choice(["", "+"]) if e >= 0 else "") + str(e)
+            mult = Fraction(10) ** e
+        value = Fraction(num if not num.endswith(".") else num[:-1]) * mult
+        want = min(math.ceil(value), 2**63 - 1)
+        assert x.quantity(num + suf) == want, num + suf
+
+
+def test_node_index_odd_names():
+    """names of any length and content resolve to themselves (the route decoder hands over raw bytes)"""
+    names = ["", "a", "a" * 7, "a" * 8, "a" * 9, "a" * 255, "node\x00with-nul", "ünï", "x" * 4096, "A", "a ", " a"]
+    names += ["n%d" % i for i in range(5000)] + ["n%d." % i for i in range(5000)]
+    body = json.dumps({"Pod": x.pod_json([10]), "NodeNames": names})
+    d = x.decode_args(body)
+    assert d["err"] == "" and d["node_names"] == names
