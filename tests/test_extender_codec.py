@@ -322,3 +322,40 @@ def test_node_index_odd_names():
     body = json.dumps({"Pod": x.pod_json([10]), "NodeNames": names})
     d = x.decode_args(body)
     assert d["err"] == "" and d["node_names"] == names
+
+
+def test_policy_parser_against_pyyaml():
+    """generated policy files (entry order, indentation, comments, quoting, extra keys) read like PyYAML reads them"""
+    import yaml
+
+    from nano_gpu_scheduler_b200.routes import parse_duration, parse_policy
+
+    rng = random.Random(5)
+    units = ["ns", "us", "ms", "s", "m", "h"]
+    for _ in range(300):
+        ind = " " * rng.choice([2, 4])
+        seq_ind = rng.choice(["", ind])  # a block sequence may sit at its parent's indent
+        lines = ["apiVersion: v1", "kind: public-dynamic-scheduler  # trailing comment", "spec:"]
+        if rng.random() < 0.5:
+            lines += [ind + "priority:", ind + seq_ind + "- name: gpu_core_usage_avg", ind + seq_ind + "  weight: 0.5"]
+        lines.append(ind + "syncPeriod:")
+        want = []
+        for _k in range(rng.randrange(0, 5)):
+            name = rng.choice(["gpu_core_usage_avg", "gpu_memory_usage_avg", "x_%d" % rng.randrange(100)])
+            dur = "".join("%d%s" % (rng.randrange(1, 90), u) for u in rng.sample(units, rng.randrange(1, 3)))
+            q = rng.choice(['', '"', "'"])
+            fields = ["name: %s%s%s" % (q, name, q), "period: %s" % dur]
+            if rng.random() < 0.3:
+                fields.append("note: ignored")
+            rng.shuffle(fields)
+            if rng.random() < 0.3:
+                lines.append(ind + seq_ind + "# a comment between entries")
+            lines.append(ind + seq_ind + "- " + fields[0])
+            lines += [ind + seq_ind + "  " + f for f in fields[1:]]
+            want.append((name, parse_duration(dur)))
+        if rng.random() < 0.5:
+            lines += ["status:", ind + "phase: x"]
+        text = "\n".join(lines) + "\n"
+        ref = yaml.safe_load(text)["spec"]["syncPeriod"] or []
+        assert [(e["name"], parse_duration(str(e["period"]))) for e in ref] == want  # the generator and PyYAML agree
+        assert parse_policy(text) == want, text
