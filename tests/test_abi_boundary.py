@@ -94,3 +94,31 @@ def test_load_ctx_layout_matches_header(built):
 
     assert C.sizeof(ngs._abi.LoadCtx) == 4 + 4 * 4 + 4 + 8 * 4 + 8  # int32, int32[4], pad, int64[4], int64
     assert C.sizeof(ngs._abi.Stats) == 40
+
+
+def test_parse_fuzz_against_python(built):
+    """random well-formed update times (any second from 1992 to 2100, the years Asia/Shanghai is plainly UTC+8) and
+    usage strings as the metric sync writes them ('%.5f'), plus damaged variants of both"""
+    import calendar
+    import random
+
+    import nano_gpu_scheduler_b200 as ngs
+
+    rng = random.Random(99)
+    lo, hi = calendar.timegm((1992, 1, 1, 0, 0, 0)), calendar.timegm((2100, 1, 1, 0, 0, 0))
+    for _ in range(3000):
+        t = rng.randrange(lo, hi)
+        y, mo, d, h, mi, s = __import__("time").gmtime(t + 8 * 3600)[:6]
+        text = "%04d-%02d-%02dT%02d:%02d:%02dZ" % (y, mo, d, h, mi, s)
+        assert ngs.parse_update_time(text) == (True, t), text
+        i = rng.randrange(len(text))
+        broken = text[:i] + rng.choice("x :-/T") + text[i + 1:]
+        if broken != text:
+            ok, _ = ngs.parse_update_time(broken)
+            assert ok is False, broken
+    for _ in range(3000):
+        v = rng.random() * rng.choice([1.0, 1.0, 2.0])
+        text = "%.5f" % v
+        assert ngs.parse_usage(text) == (True, float(text)), text
+        text2 = repr(rng.uniform(-3, 3))
+        assert ngs.parse_usage(text2) == (True, float(text2)), text2
