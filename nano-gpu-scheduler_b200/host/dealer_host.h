@@ -55,8 +55,8 @@ class ClusterSource {
   public:
     virtual ~ClusterSource() {}
     virtual bool GetNode(const std::string& name, Node* out) = 0;                             // false: `node "x" not found`
-    virtual std::vector<Pod> ListAssumedPods(const std::string& node_name) { return {}; }    // label nano-gpu/assume=true
-    virtual bool GetPod(const std::string& ns, const std::string& name, Pod* out) { return false; }  // clientset Pods(ns).Get; false: `pods "x" not found`
+    virtual std::vector<Pod> ListAssumedPods(const std::string& /*node_name*/) { return {}; }    // label nano-gpu/assume=true
+    virtual bool GetPod(const std::string& /*ns*/, const std::string& /*name*/, Pod* /*out*/) { return false; }  // clientset Pods(ns).Get; false: `pods "x" not found`
     virtual std::vector<Pod> ListAllAssumedPods() { return {}; }                              // the same label over all nodes (dealer.go:58)
 };
 

@@ -688,14 +688,14 @@ bool ParseQuantityValue(std::string_view s, int64_t* out) {
             mant /= 10;
         }
         unsigned __int128 D = 1;
-        for (int i = 0; i < k; i++) D *= 10;
+        for (int t = 0; t < k; t++) D *= 10;
         const unsigned __int128 q = mant / D, r = mant % D;
         v = q;
-        for (int i = 0; i < exp2 && v <= kMax; i++) v *= 2;
+        for (int t = 0; t < exp2 && v <= kMax; t++) v *= 2;
         const int c = exp2 < k ? exp2 : k;  // twos shared by 2^exp2 and 10^k
         unsigned __int128 Dr = D, num = r;
-        for (int i = 0; i < c; i++) Dr /= 2;
-        for (int i = 0; i < exp2 - c; i++) num *= 2;  // r < 10^k, so num < 5^k * 2^exp2 <= 5^28 * 2^60 < 2^126
+        for (int t = 0; t < c; t++) Dr /= 2;
+        for (int t = 0; t < exp2 - c; t++) num *= 2;  // r < 10^k, so num < 5^k * 2^exp2 <= 5^28 * 2^60 < 2^126
         unsigned __int128 frac = num / Dr;
         if (num % Dr) sticky = true;
         if (v <= kMax) v += frac;
