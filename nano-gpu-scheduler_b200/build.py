@@ -13,7 +13,7 @@ HEADERS = [os.path.join(CSRC, f) for f in ("ngs_device.cuh", "ngs_rows.cuh", "ng
     os.path.join(HERE, "..", "include", "ngs_dealer.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-    "-shared", "-Xcompiler", "-fPIC", "-diag-suppress", "177",
+    "-shared", "-Xcompiler", "-fPIC",
 ]
 
 

@@ -680,7 +680,6 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     for (uint32_t p = 0; p < bp.P; p++) {
         const SortedDemand* dem = &s_dem[p & 3];
         const int policy = dem->policy;
-        const bool spread = policy == NGS_POLICY_SPREAD;
         const bool more = p + 1 < bp.P;
         const SortedDemand* dem_next = &s_dem[(p + 1) & 3];
         if (more && rl_pending && dem_next->policy != NGS_POLICY_RANDOM) {
