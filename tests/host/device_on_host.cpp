@@ -2,8 +2,10 @@
 // nano-gpu-scheduler_b200/csrc/ngs_device.cuh (the very source the kernels include) with g++, with
 // the handful of CUDA intrinsics they use spelled out in plain C++, so that the CPU test suite can
 // compare them with the oracle on millions of rows without a GPU (tests/test_device_source_on_host.py).
-// The warp-cooperative pieces (choose_group8 and everything in the .cu files) only run on the GPU
-// and are covered by the -m gpu tests.  Nothing in the package links or loads this file.
+// The 8-lanes-per-row plan search (choose_group8) runs on a small lockstep warp simulator (32 coroutines,
+// ballots and shuffles resolved when every lane has arrived), which also reports what would hang a real
+// warp: lanes meeting different sync ops, or returning while others wait.  The kernels themselves (.cu)
+// only run on the GPU and are covered by the -m gpu tests.  Nothing in the package links or loads this file.
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
@@ -23,13 +25,105 @@ static inline int min(int a, int b) { return a < b ? a : b; }  // CUDA's global-
 static inline int max(int a, int b) { return a > b ? a : b; }
 static inline uint32_t min(uint32_t a, uint32_t b) { return a < b ? a : b; }
 static inline uint32_t max(uint32_t a, uint32_t b) { return a > b ? a : b; }
-[[noreturn]] static inline void warp_only() {
-    fprintf(stderr, "device_on_host: a warp-cooperative function was called on the host\n");
-    abort();
+
+// ---- a lockstep warp, single-threaded: 32 coroutines (ucontext), one per lane.  A lane runs until it reaches a
+// warp-synchronous op, posts its operand and yields; once every lane has posted, the results are handed out and
+// the lanes run on.  Lanes that reach DIFFERENT ops, or a lane that returns while others wait at an op, would
+// hang a real warp (full-mask ops): the simulator reports that instead (warp_sim_error).
+#include <ucontext.h>
+namespace warpsim {
+enum Op { NONE = 0, BALLOT, SHFL, SHFL_XOR, DONE };
+struct Lane {
+    ucontext_t ctx;
+    Op op = NONE;
+    uint64_t val = 0;   // operand
+    int arg = 0;        // source lane / xor mask
+    uint64_t res = 0;   // result
+    char* stack = nullptr;
+};
+static Lane g_lane[32];
+static ucontext_t g_sched;
+static int g_cur = -1;          // lane being run (-1: not inside a simulated warp)
+static const char* g_error = nullptr;
+static void (*g_body)(int lane, void* arg);
+static void* g_body_arg;
+
+static void trampoline() {
+    g_body(g_cur, g_body_arg);
+    g_lane[g_cur].op = DONE;
+    swapcontext(&g_lane[g_cur].ctx, &g_sched);
 }
-static inline unsigned __ballot_sync(unsigned, bool) { warp_only(); }
-template <class T> static inline T __shfl_sync(unsigned, T, int) { warp_only(); }
-template <class T> static inline T __shfl_xor_sync(unsigned, T, int) { warp_only(); }
+static uint64_t post(Op op, uint64_t v, int arg) {
+    if (g_cur < 0) {
+        fprintf(stderr, "device_on_host: warp-synchronous op outside a simulated warp\n");
+        abort();
+    }
+    Lane& L = g_lane[g_cur];
+    L.op = op;
+    L.val = v;
+    L.arg = arg;
+    swapcontext(&L.ctx, &g_sched);  // back when the op has been resolved
+    return L.res;
+}
+// run body(lane, arg) on 32 lanes in lockstep; nullptr on success, else what went wrong
+static const char* run_warp(void (*body)(int, void*), void* arg) {
+    constexpr size_t STACK = 256 * 1024;
+    g_body = body;
+    g_body_arg = arg;
+    g_error = nullptr;
+    for (int l = 0; l < 32; l++) {
+        Lane& L = g_lane[l];
+        if (!L.stack) L.stack = (char*)malloc(STACK);
+        getcontext(&L.ctx);
+        L.ctx.uc_stack.ss_sp = L.stack;
+        L.ctx.uc_stack.ss_size = STACK;
+        L.ctx.uc_link = &g_sched;
+        L.op = NONE;
+        makecontext(&L.ctx, trampoline, 0);
+    }
+    for (;;) {
+        for (int l = 0; l < 32; l++) {  // let every live lane run to its next op
+            if (g_lane[l].op == DONE) continue;
+            g_cur = l;
+            swapcontext(&g_sched, &g_lane[l].ctx);
+        }
+        g_cur = -1;
+        int done = 0;
+        for (int l = 0; l < 32; l++) done += g_lane[l].op == DONE;
+        if (done == 32) return nullptr;
+        const Op op = g_lane[0].op;
+        for (int l = 0; l < 32; l++)
+            if (g_lane[l].op != op) {
+                g_error = done ? "a lane returned while others wait at a full-mask warp op (a real warp would hang)"
+                               : "lanes reached different warp-synchronous ops (divergent control flow around a sync op)";
+                return g_error;  // (the abandoned coroutines are simply dropped: their stacks are reused by the next run)
+            }
+        if (op == BALLOT) {
+            uint32_t m = 0;
+            for (int l = 0; l < 32; l++) m |= (g_lane[l].val ? 1u : 0u) << l;
+            for (int l = 0; l < 32; l++) g_lane[l].res = m;
+        } else if (op == SHFL) {
+            for (int l = 0; l < 32; l++) g_lane[l].res = g_lane[g_lane[l].arg & 31].val;
+        } else {  // SHFL_XOR
+            for (int l = 0; l < 32; l++) g_lane[l].res = g_lane[(l ^ g_lane[l].arg) & 31].val;
+        }
+    }
+}
+template <class T> static inline uint64_t bits(T v) {
+    static_assert(sizeof(T) <= 8, "shuffle operand");
+    uint64_t b = 0;
+    memcpy(&b, &v, sizeof(T));
+    return b;
+}
+template <class T> static inline T from(uint64_t b) {
+    T v;
+    memcpy(&v, &b, sizeof(T));
+    return v;
+}
+}  // namespace warpsim
+static inline unsigned __ballot_sync(unsigned, bool pred) { return (unsigned)warpsim::post(warpsim::BALLOT, pred ? 1 : 0, 0); }
+template <class T> static inline T __shfl_sync(unsigned, T v, int src) { return warpsim::from<T>(warpsim::post(warpsim::SHFL, warpsim::bits(v), src)); }
+template <class T> static inline T __shfl_xor_sync(unsigned, T v, int m) { return warpsim::from<T>(warpsim::post(warpsim::SHFL_XOR, warpsim::bits(v), m)); }
 
 #include "../../nano-gpu-scheduler_b200/csrc/ngs_device.cuh"
 
@@ -122,6 +216,85 @@ int doh_load_usage(const uint8_t* tenths /*[2][8]*/, const uint32_t* ts /*[2][8]
     load_usage_row(t10, tt, lp, G, rlc, &load_int, mode == 2 ? pair : nullptr);
     for (int g = 0; g < 8; g++) rl_out[g] = rlc[g] - 2;
     return load_int;
+}
+
+// Binpack / Spread.Choose with eight lanes per row (choose_group8), four rows per simulated warp.
+//   free[4][8], G[4], rl[4][8] (RemainLoad); one demand for all four rows.
+//   ok[4]; with plan != 0 also emit[4] (4 bits per entry), n_emit[4], fr_out[4][8] (cells after GPUs.Allocate)
+// Returns 0, or 1 when the simulator saw what would hang a warp (message via doh_warp_error).
+struct G8Args {
+    const int32_t* free;
+    const int32_t* G;
+    const int8_t* rl;
+    SortedDemand dem;
+    bool spread, plan;
+    int32_t* ok;
+    uint64_t* emit;
+    int32_t* n_emit;
+    int32_t* fr_out;
+};
+static void g8_body(int lane, void* p) {
+    G8Args& a = *(G8Args*)p;
+    const int g = lane & 7, gbase = lane & 24, row = lane >> 3;
+    const int G = a.G[row];
+    const int fr = a.free[row * 8 + g], rlc = a.rl[row * 8 + g] + 2;
+    uint64_t emit = 0;
+    int n_emit = 0, fr_after = 0;
+    bool ok;
+    if (a.plan) ok = choose_group8<true>(g, gbase, fr, rlc, g < G, a.spread, &a.dem, &emit, &n_emit, &fr_after);
+    else ok = choose_group8<false>(g, gbase, fr, rlc, g < G, a.spread, &a.dem, nullptr, nullptr, nullptr);
+    if (g == 0) {
+        a.ok[row] = ok ? 1 : 0;
+        if (a.plan) {
+            a.emit[row] = emit;
+            a.n_emit[row] = n_emit;
+        }
+    }
+    if (a.plan) a.fr_out[row * 8 + g] = g < G ? fr_after : 0;
+}
+static const char* g_warp_error = "";
+const char* doh_warp_error() { return g_warp_error; }
+int doh_choose_group8(const int32_t* free, const int32_t* G, const int8_t* rl, const int32_t* percent, int C, int spread, int plan, int32_t* ok,
+                      uint64_t* emit, int32_t* n_emit, int32_t* fr_out) {
+    G8Args a;
+    a.free = free;
+    a.G = G;
+    a.rl = rl;
+    sort_demand(percent, C, spread ? NGS_POLICY_SPREAD : NGS_POLICY_BINPACK, &a.dem);
+    a.spread = spread != 0;
+    a.plan = plan != 0;
+    a.ok = ok;
+    a.emit = emit;
+    a.n_emit = n_emit;
+    a.fr_out = fr_out;
+    const char* e = warpsim::run_warp(g8_body, &a);
+    g_warp_error = e ? e : "";
+    return e ? 1 : 0;
+}
+// the emission list of choose_group8 in container order, as the kernels publish it (rater.go:102-105)
+void doh_unpermute(const int32_t* percent, int C, int spread, uint64_t emit, int32_t* plan) {
+    SortedDemand dem;
+    sort_demand(percent, C, spread ? NGS_POLICY_SPREAD : NGS_POLICY_BINPACK, &dem);
+    for (int k = 0; k < C; k++) {
+        const int e = (int)((emit >> (4 * k)) & 0xF);
+        plan[dem.order[k]] = e == 0xF ? NGS_NOT_NEED_GPU : e;
+    }
+}
+
+// two deliberately wrong warp programs: the simulator must report both (they are the bug classes that hang a GPU)
+static void bad_short_circuit(int lane, void*) {
+    bool ok = (lane & 8) == 0;                                      // lanes disagree ...
+    ok = ok && (__ballot_sync(0xFFFFFFFFu, lane < 4) != 0u);        // ... so only some of them reach the ballot
+    if (__shfl_xor_sync(0xFFFFFFFFu, ok ? 1 : 0, 1) == 12345) abort();
+}
+static void bad_early_return(int lane, void*) {
+    if (lane == 7) return;
+    if (__ballot_sync(0xFFFFFFFFu, true) == 0u) abort();
+}
+int doh_selftest_detects_hangs() {
+    const char* e1 = warpsim::run_warp(bad_short_circuit, nullptr);
+    const char* e2 = warpsim::run_warp(bad_early_return, nullptr);
+    return (e1 != nullptr ? 1 : 0) | (e2 != nullptr ? 2 : 0);
 }
 
 uint64_t doh_splitmix64(uint64_t x) { return splitmix64(x); }

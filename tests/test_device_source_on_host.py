@@ -3,8 +3,9 @@
 tests/host/device_on_host.cpp includes nano-gpu-scheduler_b200/csrc/ngs_device.cuh (the source the CUDA kernels
 include) and spells the few intrinsics it uses in plain C++, so the thread-serial logic — demand sort, packed-cell
 plan search (choose_sorted), SampleRater, both Rate functions, the exact feasibility shortcuts, LoadUsage — can be
-compared with the oracle on hundreds of thousands of rows without a GPU.  This is a test harness only: the product
-never loads it, and the warp-cooperative code (choose_group8, the kernels) is covered by the -m gpu tests."""
+compared with the oracle on hundreds of thousands of rows without a GPU; choose_group8 (eight lanes per row) runs on
+a lockstep warp simulator that also flags sync ops under divergent control flow.  This is a test harness only: the
+product never loads it, and the kernels themselves are covered by the -m gpu tests."""
 import ctypes as C
 import os
 import shutil
@@ -194,3 +195,58 @@ def test_keys_and_prng(doh):
     keys.sort()
     for (k0, s0, n0), (k1, s1, n1) in zip(keys, keys[1:]):
         assert (s0, -n0) <= (s1, -n1)
+
+
+def test_warp_simulator_reports_what_would_hang_a_warp(doh):
+    """lanes that meet different sync ops (a ballot behind `ok &&`), or return while the others wait at one"""
+    assert doh.doh_selftest_detects_hangs() == 3
+
+
+@pytest.mark.parametrize("spread", [False, True])
+@pytest.mark.parametrize("wide", [False, True])
+def test_eight_lane_plan_search_matches_oracle(doh, spread, wide):
+    """choose_group8 — the plan search of the batch kernel, one GPU cell per lane, four rows per warp — on a lockstep
+    warp simulator: feasibility, emission order, the row as GPUs.Allocate leaves it, and no sync op under divergence"""
+    doh.doh_warp_error.restype = C.c_char_p
+    policy = o.POLICY_SPREAD if spread else o.POLICY_BINPACK
+    rng = np.random.default_rng(77 + 2 * spread + wide)
+    for trial in range(1500):
+        if wide:
+            demand = rng.choice([0, 5, 50, 100, 101, 255, 256, 300, 65535], size=int(rng.integers(0, 13))).astype(np.int32)
+        else:
+            demand = (rng.integers(0, 15, int(rng.integers(1, 7))) * 5).astype(np.int32)
+        free = np.zeros((4, 8), dtype=np.int32)
+        rl = np.zeros((4, 8), dtype=np.int8)
+        G = rng.integers(0, 9, 4).astype(np.int32)  # G = 0: an unknown node in one of the four groups
+        for r in range(4):
+            vals = rng.choice([0, 5, 20, 50, 99, 100, 101, 254, 255, 256, 300, 4000, 65535], size=8) if wide else rng.integers(0, 21, 8) * 5
+            free[r, : G[r]] = vals[: G[r]]
+            if rng.random() < 0.5:
+                rl[r, : G[r]] = rng.integers(-2, 3, G[r])
+        C_ = len(demand)
+        dptr = _p(demand) if C_ else None
+        for plan in (1, 0):
+            ok = np.zeros(4, dtype=np.int32)
+            emit = np.zeros(4, dtype=np.uint64)
+            ne = np.zeros(4, dtype=np.int32)
+            fr = np.zeros((4, 8), dtype=np.int32)
+            rc = doh.doh_choose_group8(_p(free), _p(G), _p(rl), dptr, C_, int(spread), plan, _p(ok), _p(emit), _p(ne), _p(fr))
+            assert rc == 0, doh.doh_warp_error()
+            for r in range(4):
+                g = int(G[r])
+                if g == 0:
+                    # no cells: feasible only if nothing is demanded
+                    assert bool(ok[r]) == (not (demand != 0).any()), (trial, r)
+                    continue
+                want_ok, idx, want_ne = o.choose(policy, free[r, :g].astype(np.int64), demand, rl=rl[r, :g].astype(np.int64))
+                assert bool(ok[r]) == want_ok, (trial, r, free[r, :g], rl[r, :g], demand)
+                if not plan or not want_ok:
+                    continue
+                got = np.full(max(C_, 1), INT32_MIN, dtype=np.int32)
+                doh.doh_unpermute(dptr, C_, int(spread), C.c_uint64(int(emit[r])), _p(got))
+                assert got[:C_].tolist() == idx and ne[r] == C_, (trial, r, free[r, :g], rl[r, :g], demand)
+                after = free[r].astype(np.int64).copy()
+                for c, gi in enumerate(idx):
+                    if gi >= 0:
+                        after[gi] -= int(demand[c])
+                assert fr[r, :g].tolist() == after[:g].tolist(), (trial, r)
