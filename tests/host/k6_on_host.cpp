@@ -147,6 +147,61 @@ int k6h_plan(const int32_t* free, const int32_t* G, const int8_t* rl, const int3
     *same = s;
     return 0;
 }
+// eval_row_values (ngs_rows.cuh): the whole GPUs.Choose of the per-verb kernels for n rows, one after the other —
+// Rate (with LoadUsage and the RemainLoad write-back when load != 0), shortcuts, exact search.
+//   tenths / ts: [2][n][8] as the device tables hold them; min_ts[2]: the (core, memory) thresholds of make_load
+//   plan != 0: PLAN instantiation (plans / partial emission lists), else the feasibility-only one
+void k6h_eval_rows(const int32_t* free, const int32_t* G, int8_t* rl, const uint8_t* tenths, const uint32_t* ts, uint32_t n,
+                   const int32_t* percent, int C, int policy, int load, const uint32_t* min_ts, int use_pair, int plan, int32_t* feasible,
+                   int32_t* score, int32_t* plan_out, int32_t* n_emit) {
+    SortedDemand dem;
+    sort_demand(percent, C, policy, &dem);
+    LoadParams lp;
+    memset(&lp, 0, sizeof lp);
+    if (load) {
+        lp.enabled = 1;
+        lp.n_periods = 2;
+        lp.metric[0] = NGS_METRIC_CORE;
+        lp.metric[1] = NGS_METRIC_MEMORY;
+        lp.min_ts[0] = min_ts[0];
+        lp.min_ts[1] = min_ts[1];
+        lp.canonical = 1;
+    }
+    double pair[121];
+    for (int i = 0; i < 121; i++) fill_usage_pair_table(pair, i, 121 + i);
+    Tables T;
+    memset(&T, 0, sizeof T);
+    T.rl = rl;
+    T.n = n;
+    T.nstride = n;
+    for (uint32_t r = 0; r < n; r++) {
+        RowIn in;
+        memset(&in, 0, sizeof in);
+        in.G = G[r];
+        for (int g = 0; g < 8; g++) in.v[g] = (uint32_t)free[r * 8 + g];
+        for (int m = 0; m < 2; m++) {
+            const uint8_t* t = tenths + ((size_t)m * n + r) * 8;
+            in.t8[m].x = t[0] | (t[1] << 8) | (t[2] << 16) | ((uint32_t)t[3] << 24);
+            in.t8[m].y = t[4] | (t[5] << 8) | (t[6] << 16) | ((uint32_t)t[7] << 24);
+            for (int g = 0; g < 8; g++) in.ts[m][g] = ts[((size_t)m * n + r) * 8 + g];
+        }
+        const int8_t* rr = rl + (size_t)r * 8;
+        in.r8.x = (uint8_t)rr[0] | ((uint8_t)rr[1] << 8) | ((uint8_t)rr[2] << 16) | ((uint32_t)(uint8_t)rr[3] << 24);
+        in.r8.y = (uint8_t)rr[4] | ((uint8_t)rr[5] << 8) | ((uint8_t)rr[6] << 16) | ((uint32_t)(uint8_t)rr[7] << 24);
+        RowEval ev = plan ? eval_row_values<true>(T, r, in, &dem, lp, true, use_pair ? pair : nullptr)
+                          : eval_row_values<false>(T, r, in, &dem, lp, true, use_pair ? pair : nullptr);
+        const bool ok = ev.known && ev.feasible;
+        feasible[r] = ok ? 1 : 0;
+        score[r] = ok ? ev.score : NGS_SCORE_MIN;
+        if (plan) {
+            int32_t* out = plan_out + (size_t)r * (C > 0 ? C : 1);
+            if (ev.known) write_plan(out, &dem, dem.policy != NGS_POLICY_RANDOM, ok, ev.emit, ev.n_emit);
+            else for (int j = 0; j < C; j++) out[j] = INT32_MIN;
+            n_emit[r] = ev.known ? ev.n_emit : 0;
+        }
+    }
+}
+
 // the emission list in container order, as publish_group writes it (rater.go:102-105)
 void k6h_unpermute(const int32_t* percent, int C, int policy, uint64_t emit, int32_t* plan) {
     SortedDemand dem;

@@ -167,3 +167,59 @@ def test_plan_group_and_fresh_key(k6, policy, wide):
         else:
             assert fresh.value == 0 and fresh_ok.value == 0
     assert done > 500
+
+
+@pytest.mark.parametrize("policy", [o.POLICY_BINPACK, o.POLICY_SPREAD, o.POLICY_RANDOM])
+@pytest.mark.parametrize("load", [False, True])
+def test_row_evaluation_of_the_verb_kernels(k6, policy, load):
+    """eval_row_values (ngs_rows.cuh) — what one thread of k_assume / k_scan_tma / K7 does with its row — against
+    OracleCluster.assume on whole small clusters: feasibility, Plan.Score, plans and partial emission lists, and in
+    load-aware mode the RemainLoad it writes back; both instantiations, with and without the usage-pair table"""
+    import math
+
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    now_s = 1_790_000_000
+    now_ns = now_s * 10**9 + 555_555_555
+    rng = np.random.default_rng(40 + 3 * policy + load)
+    n = 600
+    gcount, free = wl.make_cluster(n, 0.55, 0xE7 + policy, hetero=True)
+    gcount = gcount.copy()
+    gcount[rng.integers(0, n, 12)] = 0  # a few unknown nodes
+    free = np.where(np.arange(8)[None, :] < gcount[:, None], free, 0).astype(np.int32)
+    tables = wl.make_load_tables(n, 0xE7, now_s, stale_frac=0.2, absent_frac=0.1)
+    oc = o.OracleCluster(n)
+    oc.load_snapshot(gcount, free)
+    tenths = np.full((2, n, 8), 255, dtype=np.uint8)
+    ts = np.zeros((2, n, 8), dtype=np.uint32)
+    for m, (value, t, absent) in enumerate(tables):
+        ok = np.repeat(~absent[:, None], 8, axis=1)
+        oc.load_update_bulk(m, value, t, ok=ok.astype(np.uint8))
+        good = ok & (value >= 0) & (value <= 1)
+        tenths[m] = np.where(good, np.ceil(10 * value), 255).astype(np.uint8)
+        ts[m] = t.astype(np.uint32)
+    periods = wl.DEFAULT_PERIODS
+    L = o.make_load_ctx(periods, now_ns) if load else None
+    min_ts = np.array([max(0, math.floor((now_ns - w) / 10**9) + 1) for _, w in periods], dtype=np.uint32)
+    G32 = gcount.astype(np.int32)
+    rl = np.zeros((n, 8), dtype=np.int8)
+    for trial in range(10):
+        demand = (rng.integers(0, 13, int(rng.integers(1, 5))) * 5).astype(np.int32)
+        want = oc.assume(demand, policy, load=L, want_plan=True)
+        _, _, orl = oc.snapshot()
+        for plan in (1, 0):
+            for use_pair in (1, 0):
+                feas = np.zeros(n, dtype=np.int32)
+                score = np.zeros(n, dtype=np.int32)
+                plans = np.full((n, len(demand)), INT32_MIN, dtype=np.int32)
+                nem = np.zeros(n, dtype=np.int32)
+                rl_run = rl.copy()
+                k6.k6h_eval_rows(_p(free), _p(G32), _p(rl_run), _p(tenths), _p(ts), n, _p(demand), len(demand), policy, int(load), _p(min_ts),
+                                 use_pair, plan, _p(feas), _p(score), _p(plans), _p(nem))
+                assert np.array_equal(feas, want["feasible"]), (trial, plan, use_pair)
+                assert np.array_equal(score, want["score"]), (trial, plan, use_pair)
+                assert np.array_equal(rl_run, orl.astype(np.int8)), (trial, plan, use_pair)
+                if plan:
+                    assert np.array_equal(nem, want["n_emitted"]) and np.array_equal(plans, want["plan"]), (trial, use_pair)
+        rl = orl.astype(np.int8)  # the next evaluation starts from what this one left behind
+    oc.close()
