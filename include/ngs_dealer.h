@@ -24,11 +24,11 @@
 extern "C" {
 #endif
 
-#define NGS_ABI_VERSION 1u
+#define NGS_ABI_VERSION 2u /* 2: ngs_load_ctx holds 8 periods; NGS_NODE_INVALID_POD */
 
 #define NGS_MAX_GPUS 8         /* GPUs per node handled by the kernels (row = 8 x int32 = 2 x int4) */
 #define NGS_MAX_CONTAINERS 12  /* containers per pod (Go sort.Sort's <=12-element regime) */
-#define NGS_MAX_PERIODS 4      /* usable PolicySpec.SyncPeriod entries */
+#define NGS_MAX_PERIODS 8      /* usable PolicySpec.SyncPeriod entries (the deployed policy has 2; more than 8 -> NGS_ERR_UNSUPPORTED) */
 #define NGS_MAX_FREE 65535     /* upper bound of a cell's free percent kept in the snapshot */
 #define NGS_MAX_BATCH 65536    /* pods per ngs_schedule_batch call */
 #define NGS_MAX_RANKS 8        /* GPUs of one box a cluster can be sharded over */
@@ -63,6 +63,8 @@ enum {
 enum { NGS_METRIC_CORE = 0, NGS_METRIC_MEMORY = 1 };
 
 #define NGS_NOT_NEED_GPU (-1) /* allocate.go:15 */
+#define NGS_NODE_NONE (-1)         /* node_out: no node takes the pod */
+#define NGS_NODE_INVALID_POD (-2)  /* node_out: the pod itself was malformed (device-resident batches only, see below) */
 #define NGS_SCORE_MIN 0       /* rater.go:12 */
 
 /* isLoadSchedule=true context: PolicySpec.SyncPeriod (type.go:16-27) after the host resolved
@@ -160,12 +162,29 @@ int ngs_bind(ngs_dealer *h, uint32_t idx, const int32_t *percent, int n_containe
  * [P][max_c]; node_out[p] = global node index or -1; gpu_idx_out [P][max_c] padded with INT32_MIN.
  * A call with ONE pod is the low-latency form: a single ordinary launch over the tables in place,
  * the answer polled from mapped host memory (sharded handles: every rank makes the same call and
- * gets the whole decision; the random policy on a sharded handle takes the batch path). */
+ * gets the whole decision; the random policy on a sharded handle takes the batch path).
+ * Two things a caller has to know about a batch:
+ *  - load-aware mode: `load->now_ns` and the usage tables are read ONCE, when the launch starts
+ *    (LoadUsage of every row is evaluated in the kernel's prologue).  The whole batch - up to
+ *    NGS_MAX_BATCH pods, in chunks of 4096 per launch - is one "pod cycle" in the sense of
+ *    SURVEY hard part 6: an ngs_load_update between two pods of one batch is not seen, and no pod
+ *    of the batch crosses an update-window edge.  Callers that need a fresher clock cut the batch.
+ *  - size: the batch kernel keeps every row of the shard in shared memory (32 B per row, one CTA
+ *    per SM), which holds about 1.04 M rows on a B200 (148 SMs x 227 KB).  A larger shard gets
+ *    NGS_ERR_UNSUPPORTED from this call - there is no streaming fallback; split the cluster over
+ *    more handles / GPUs (node-range sharding below).  The verb calls have no such limit.
+ * The host-buffer form validates every pod before anything is launched (NGS_ERR_INVALID, nothing
+ * scheduled). */
 int ngs_schedule_batch(ngs_dealer *h, uint32_t n_pods, const int32_t *percent, const int32_t *n_containers, int max_c,
                        const int32_t *policy, const ngs_load_ctx *load, uint64_t seed, uint64_t seq0, int32_t *node_out,
                        int32_t *score_out, int32_t *gpu_idx_out);
 /* same, with every array already resident in device memory and no synchronisation:
- * results are valid after ngs_sync() or once work queued later on ngs_stream() runs. */
+ * results are valid after ngs_sync() or once work queued later on ngs_stream() runs.
+ * The pods cannot be checked on the host here, so the device does it: a pod with a bad container
+ * count (< 0, > max_c), percent (< 0, > NGS_MAX_FREE) or policy is left unscheduled with
+ * node_out = NGS_NODE_INVALID_POD, score NGS_SCORE_MIN and gpu_idx INT32_MIN; every other pod of the
+ * batch is scheduled exactly as if the bad one were not there, and the next ngs_sync() returns
+ * NGS_ERR_INVALID once to say that some batch since the last sync held such a pod. */
 int ngs_schedule_batch_dev(ngs_dealer *h, uint32_t n_pods, const int32_t *d_percent, const int32_t *d_n_containers,
                            int max_c, const int32_t *d_policy, const ngs_load_ctx *load, uint64_t seed, uint64_t seq0,
                            int32_t *d_node_out, int32_t *d_score_out, int32_t *d_gpu_idx_out);
@@ -195,14 +214,21 @@ int ngs_xchg_attach(ngs_dealer *h, int rank, int world, const void *handles);
  * the caller owns the snapshot tables (described by ngs_snapshot_view, laid out exactly as the
  * handle keeps them) and passes the pods and the outputs as device pointers; the scratch the batch
  * kernel needs (sorted demands, per-pod exchange words, error word) lives in a fixed array inside
- * the library's device image, about 372 KB that every GPU loading the library keeps until exit.
+ * the library's device image, 374 016 bytes (about 365 KiB) that every GPU loading the library keeps
+ * until exit.
  *
  * Limits: at most NGS_NOALLOC_MAX_PODS pods per call and a launch of at most
  * NGS_NOALLOC_MAX_CTAS CTAs (one per SM); anything larger is refused with NGS_ERR_NOALLOC_LIMIT
  * and nothing is launched.  One GPU only (no node-range sharding).
  * The call clears the part of the scratch that has to start at zero, queues the work on `stream`
- * (NULL = the default stream), waits for it and returns the batch's status.  It calls no
- * cudaMalloc, cudaFree, stream / event creation or any other allocating routine.
+ * (NULL = the default stream), waits for it with cudaStreamSynchronize - every call does, not only
+ * the first - and returns the batch's status (NGS_ERR_INVALID if a pod was malformed: see
+ * NGS_NODE_INVALID_POD above).  It calls no cudaMalloc, cudaFree, stream / event creation or any
+ * other allocating routine.
+ * Alignment: the kernels read whole rows with vector loads, so `free` and `ts` must be 32-byte
+ * aligned, `tenths` and `remain_load` 8-byte aligned, `plan_tag` / `plan_score` 4-byte aligned
+ * (anything cudaMalloc returns is; a sub-allocation at an odd offset may not be).  A view that is
+ * not gets NGS_ERR_INVALID and nothing is launched.
  * The first call on each device looks up the scratch array's device address
  * (cudaGetSymbolAddress); make that first call outside of any stream capture.
  * All calls on a device share the one scratch array, which keeps the previous call's contents:

@@ -11,7 +11,7 @@ LIB_PATH = os.environ.get("NGS_DEALER_LIB") or os.path.join(HERE, "libngs_dealer
 
 MAX_GPUS = 8
 MAX_CONTAINERS = 12
-MAX_PERIODS = 4
+MAX_PERIODS = 8
 MAX_FREE = 65535
 MAX_BATCH = 65536
 INT32_MIN = -(2**31)
@@ -32,6 +32,7 @@ SYMBOLS = [
 NOALLOC_MAX_PODS = 256
 NOALLOC_MAX_CTAS = 160
 ERR_NOALLOC_LIMIT = 9
+NODE_NONE, NODE_INVALID_POD = -1, -2
 MAX_RANKS = 8
 IPC_HANDLE_BYTES = 64
 

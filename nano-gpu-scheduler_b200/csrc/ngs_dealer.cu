@@ -279,6 +279,9 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
         pthread_mutex_unlock(&s_mu);
         CU(h, e);
     }
+    // the abort flag belongs to one launch (a batch that timed out must not make the next one give up); the status word
+    // beside it stays until ngs_sync() has reported it
+    CU(h, cudaMemsetAsync(h->d_err + 1, 0, 4, h->stream));
     k_prep_demands<<<(P + 127) / 128, 128, 0, h->stream>>>(d_percent, d_ncont, max_c, d_policy, P, h->d_dem, h->d_err);
     CU(h, cudaGetLastError());
     unsigned char* rec = reinterpret_cast<unsigned char*>(h->d_keys);
@@ -335,9 +338,10 @@ int check_dev_err(ngs_dealer* h) {
     if (*h->h_err != NGS_OK) {
         int e = *h->h_err;
         *h->h_err = NGS_OK;
-        cudaMemsetAsync(h->d_err, 0, 4, h->stream);
+        cudaMemsetAsync(h->d_err, 0, 8, h->stream);
         if (e == NGS_ERR_TIMEOUT) return fail(h, e, "batch kernel gave up waiting for a peer CTA (results of this batch are incomplete)");
-        return fail(h, e, "device-side validation failed (bad container count, percent or policy in a batch)");
+        return fail(h, e, "a batch held a pod with a bad container count, percent or policy: that pod was left unscheduled "
+                          "(node_out = NGS_NODE_INVALID_POD), every other pod was scheduled as usual");
     }
     return NGS_OK;
 }
@@ -420,10 +424,10 @@ int ngs_create(ngs_dealer** out, int device, uint32_t max_nodes, uint32_t first_
     CU(h, cudaMallocHost(&h->h_bind, sizeof(BindResult)));
     CU(h, cudaMalloc(&h->d_small, 64 * 4));
     CU(h, cudaMallocHost(&h->h_small, 64 * 4));
-    CU(h, cudaMalloc(&h->d_err, 4));
+    CU(h, cudaMalloc(&h->d_err, 8));  // [0] status, [1] abort flag
     CU(h, cudaMallocHost(&h->h_err, 4));
     *h->h_err = 0;
-    CU(h, cudaMemsetAsync(h->d_err, 0, 4, h->stream));
+    CU(h, cudaMemsetAsync(h->d_err, 0, 8, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
     return NGS_OK;
 }
@@ -854,7 +858,7 @@ int ngs_schedule_batch(ngs_dealer* h, uint32_t n_pods, const int32_t* percent, c
         }
         std::atomic_thread_fence(std::memory_order_acquire);
         if (hout[0] == NGS_ERR_TIMEOUT) {
-            cudaMemsetAsync(h->d_err, 0, 4, h->stream);
+            cudaMemsetAsync(h->d_err, 0, 8, h->stream);
             return fail(h, NGS_ERR_TIMEOUT, "single-pod kernel gave up waiting for a peer GPU");
         }
         if (hout[0] != NGS_OK) return fail(h, NGS_ERR_CUDA, "k_schedule_one ended without an answer");
@@ -971,7 +975,8 @@ struct NoAllocDevice {
 NoAllocDevice g_na_dev[64];
 pthread_mutex_t g_na_mu = PTHREAD_MUTEX_INITIALIZER;
 
-// once per device, with that device current: resolve the scratch array's address there
+// once per device, with that device current: resolve the scratch array's address there and opt the batch kernels in to
+// the device's full shared memory (driver calls that do not belong on the per-call path)
 int noalloc_setup(int device, NoAllocDevice** out) {
     if (device < 0 || device >= 64) return NGS_ERR_INVALID;
     NoAllocDevice* d = &g_na_dev[device];
@@ -982,7 +987,9 @@ int noalloc_setup(int device, NoAllocDevice** out) {
         if (cudaGetSymbolAddress(&ptr, g_noalloc_scratch) != cudaSuccess || ptr == nullptr ||
             cudaDeviceGetAttribute(&d->num_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess ||
             cudaDeviceGetAttribute(&d->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device) != cudaSuccess ||
-            cudaDeviceGetAttribute(&d->coop, cudaDevAttrCooperativeLaunch, device) != cudaSuccess) {
+            cudaDeviceGetAttribute(&d->coop, cudaDevAttrCooperativeLaunch, device) != cudaSuccess ||
+            // (an upper bound per device: asking for the device maximum once keeps it valid for every later launch, also of handles)
+            schedule_allow_max_smem(d->smem_optin) != cudaSuccess) {
             rc = NGS_ERR_CUDA;
         } else {
             d->scratch = static_cast<unsigned char*>(ptr);
@@ -1004,6 +1011,14 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
         !snap->plan_score || snap->n_nodes == 0)
         return NGS_ERR_INVALID;
     if (!d_percent || !d_n_containers || !d_policy || !d_node_out || !d_score_out || !d_gpu_idx_out) return NGS_ERR_INVALID;
+    {
+        // whole rows are read with vector loads: a table at an odd offset would fault inside the kernel
+        auto misaligned = [](const void* p, uintptr_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) != 0; };
+        if (misaligned(snap->free, 32) || misaligned(snap->ts, 32) || misaligned(snap->tenths, 8) || misaligned(snap->remain_load, 8) ||
+            misaligned(snap->plan_tag, 4) || misaligned(snap->plan_score, 4) || misaligned(d_percent, 4) || misaligned(d_n_containers, 4) ||
+            misaligned(d_policy, 4) || misaligned(d_node_out, 4) || misaligned(d_score_out, 4) || misaligned(d_gpu_idx_out, 4))
+            return NGS_ERR_INVALID;
+    }
     if (max_c < 1 || max_c > NGS_MAX_CONTAINERS) return NGS_ERR_UNSUPPORTED;
     if (n_pods > NGS_NOALLOC_MAX_PODS) return NGS_ERR_NOALLOC_LIMIT;  // the sorted demands would not fit
     if (n_pods == 0) return NGS_OK;
@@ -1039,10 +1054,8 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     if (cudaMemsetAsync(keys, 0, sizeof(unsigned long long) * (size_t)n_pods * grid, st) != cudaSuccess ||
         cudaMemsetAsync(mx, 0, sizeof(ulonglong2) * (size_t)n_pods, st) != cudaSuccess ||
         cudaMemsetAsync(done, 0, sizeof(uint32_t) * (size_t)n_pods, st) != cudaSuccess ||
-        cudaMemsetAsync(err, 0, sizeof(int32_t), st) != cudaSuccess)
+        cudaMemsetAsync(err, 0, 2 * sizeof(int32_t), st) != cudaSuccess)
         return NGS_ERR_CUDA;
-    // (an upper bound per device: asking for the device maximum once keeps it valid for every later launch, also of handles)
-    if (schedule_allow_max_smem(dv->smem_optin) != cudaSuccess) return NGS_ERR_CUDA;
     k_prep_demands<<<(n_pods + 127) / 128, 128, 0, st>>>(d_percent, d_n_containers, max_c, d_policy, n_pods, dem, err);
     if (cudaGetLastError() != cudaSuccess) return NGS_ERR_CUDA;
 

@@ -19,12 +19,17 @@ __global__ void k_prep_demands(const int32_t* __restrict__ percent, const int32_
         if (pc[k] < 0 || pc[k] > NGS_MAX_FREE) bad = true;
     }
     if (bad) {
-        atomicExch(err, NGS_ERR_INVALID);
+        // A pod the kernels cannot take is not allowed to stop the batch: it is scheduled as a pod that fits
+        // nowhere (one container larger than any cell can be) and reported as NGS_NODE_INVALID_POD in node_out;
+        // the call's status word remembers that there was one.  The waits below never look at that word.
+        atomicMax(err, NGS_ERR_INVALID);
         for (int k = 0; k < NGS_MAX_CONTAINERS; k++) pc[k] = 0;
-        C = 0;
+        pc[0] = INT32_MAX;
+        C = 1;
         pol = NGS_POLICY_BINPACK;
     }
     sort_demand(pc, C, pol, &out[p]);
+    out[p].pad_ = bad ? 1 : 0;
 }
 
 struct BatchParams {
@@ -47,7 +52,7 @@ struct BatchParams {
     unsigned long long* xslots[NGS_MAX_RANKS];  // [rank r] -> r's slot array [P][NGS_MAX_RANKS] (this batch's parity half)
     uint32_t keys_stride, done_stride, xw_stride;  // distance between consecutive pods, in elements of each array
     int32_t* status_out;       // optional host-visible copy of the error word, written when the kernel ends
-    int32_t* err;              // device error word (0 = ok)
+    int32_t* err;              // device status words: [0] sticky status of the batch (0 = ok), [1] abort flag (set by a wait that timed out)
     uint32_t rows_per_block;
 #ifdef NGS_PHASE_TIMING
     unsigned long long* dbg;   // [gridDim.x][8] accumulated cycles per phase (profiling builds only)
@@ -70,6 +75,14 @@ constexpr uint32_t K6_EXCLUSIVE_ROWS = NGS_K6_EXCLUSIVE_ROWS;
 constexpr uint32_t K6_ROW_PER_THREAD_ITERS = 2;  // up to this many rows per worker thread the simple filter loop is the faster one  // up to this many rows per CTA control warp 0 keeps a scheduler to itself
 constexpr long long SPIN_TIMEOUT_CYCLES = 2000000000LL;   // ~1 s: waits on CTAs of the same (cooperative, fully resident) launch
 constexpr long long PEER_TIMEOUT_CYCLES = 16000000000LL;  // ~8 s: waits on another GPU, whose host may launch its kernel later
+
+// The status word err[0] is sticky (invalid pod, time-out) and is what the host reads; err[1] is the abort flag the
+// bounded waits look at: only a wait that has timed out raises it, so a bad pod cannot make other waits give up.
+__device__ __forceinline__ bool abort_raised(const int32_t* err) { return *reinterpret_cast<const volatile int32_t*>(err + 1) != 0; }
+__device__ __forceinline__ void raise_timeout(int32_t* err) {
+    atomicExch(err + 1, 1);
+    atomicMax(err, NGS_ERR_TIMEOUT);  // (outranks NGS_ERR_INVALID)
+}
 
 __device__ __forceinline__ uint64_t warp_max_u64(uint64_t v) {
     const uint32_t hi = (uint32_t)(v >> 32);
@@ -240,8 +253,8 @@ __device__ __forceinline__ void publish_sample(const BatchParams& bp, const Smem
     }
 }
 
-__device__ __forceinline__ void publish_none(const BatchParams& bp, uint32_t p) {
-    bp.node_out[p] = -1;
+__device__ __forceinline__ void publish_none(const BatchParams& bp, uint32_t p, const SortedDemand* dem) {
+    bp.node_out[p] = dem->pad_ ? NGS_NODE_INVALID_POD : -1;  // (pad_: the pod failed validation, k_prep_demands)
     bp.score_out[p] = NGS_SCORE_MIN;
     for (int k = 0; k < bp.max_c; k++) bp.gpu_idx_out[(size_t)p * bp.max_c + k] = INT32_MIN;
 }
@@ -265,8 +278,8 @@ __device__ __forceinline__ bool wait_done(const uint32_t* done, uint32_t target,
         asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(done) : "memory");
         if (v >= target) return true;
         if ((++spins & 255u) == 0) {
-            if (*reinterpret_cast<volatile int32_t*>(err) != 0 || clock64() - t0 > SPIN_TIMEOUT_CYCLES) {
-                atomicCAS(err, 0, NGS_ERR_TIMEOUT);
+            if (abort_raised(err) || clock64() - t0 > SPIN_TIMEOUT_CYCLES) {
+                raise_timeout(err);
                 return false;
             }
         }
@@ -289,8 +302,8 @@ __device__ __forceinline__ unsigned long long wait_valid(const unsigned long lon
     uint32_t spins = 0;
     while (!((v = ld_relaxed_sys_u64(p)) & KEY_VALID)) {
         if ((++spins & 255u) == 0) {
-            if (*reinterpret_cast<volatile int32_t*>(err) != 0 || clock64() - t0 > PEER_TIMEOUT_CYCLES) {
-                atomicCAS(err, 0, NGS_ERR_TIMEOUT);
+            if (abort_raised(err) || clock64() - t0 > PEER_TIMEOUT_CYCLES) {
+                raise_timeout(err);
                 dead = true;
                 return 0;
             }
@@ -334,8 +347,8 @@ __device__ __forceinline__ bool wait_exchange(const ulonglong2* w, uint32_t targ
             return true;
         }
         if ((++spins & 255u) == 0) {
-            if (*reinterpret_cast<volatile int32_t*>(err) != 0 || clock64() - t0 > SPIN_TIMEOUT_CYCLES) {
-                atomicCAS(err, 0, NGS_ERR_TIMEOUT);
+            if (abort_raised(err) || clock64() - t0 > SPIN_TIMEOUT_CYCLES) {
+                raise_timeout(err);
                 *key = 0;
                 return false;
             }
@@ -768,12 +781,12 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                     before_rank = __shfl_sync(0xFFFFFFFFu, inc2 - cj, bp.rank);
                 }
                 if (total == 0) {
-                    if (blockIdx.x == 0 && lane == 0) publish_none(bp, p);
+                    if (blockIdx.x == 0 && lane == 0) publish_none(bp, p, dem);
                 } else {
                     const uint64_t gpick = splitmix64(bp.seed_seq + p) % total;
                     const bool mine = gpick >= before_rank && gpick < before_rank + ltotal;
                     if (!mine && blockIdx.x == 0 && lane == 0) {
-                        publish_none(bp, p);  // another rank owns the pick; it reports node and plan
+                        publish_none(bp, p, dem);  // another rank owns the pick; it reports node and plan
                         bp.score_out[p] = 100;
                     }
                     const uint64_t pick = mine ? gpick - before_rank : ~0ull;  // ~0: matches no CTA
@@ -931,11 +944,11 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                 if (cw == 0) {
                     const uint64_t m = s_win;
                     if (!(m & KEY_FEASIBLE)) {
-                        if (blockIdx.x == 0 && lane == 0) publish_none(bp, p);
+                        if (blockIdx.x == 0 && lane == 0) publish_none(bp, p, dem);
                     } else if (blockIdx.x == 0 && lane == 0 && key_node(m) - T.first >= T.n) {
                         // the winner lives on another rank: node and score are known from the key, the
                         // plan is filled in by the owner (merged on the host side by an allreduce-max)
-                        publish_none(bp, p);
+                        publish_none(bp, p, dem);
                         bp.node_out[p] = (int32_t)key_node(m);
                         bp.score_out[p] = key_score(m);
                     }

@@ -414,7 +414,12 @@ bool Dealer::load_ctx(const PolicySpec& spec, bool isLoad, ngs_load_ctx* out) co
     for (const Period& p : spec.sync_period) {  // allocate.go:175-180
         int64_t dur = 0;
         if (!getActiveDuration(spec.sync_period, p.name, &dur).empty() || dur == 0) continue;
-        if (out->n_periods >= NGS_MAX_PERIODS) break;
+        if (out->n_periods >= NGS_MAX_PERIODS) {
+            // allocate.go:175-195 sums every entry; the kernels hold NGS_MAX_PERIODS of them.  Never truncate silently:
+            // an over-long list travels on as n_periods > NGS_MAX_PERIODS, which every C-ABI call refuses (NGS_ERR_UNSUPPORTED)
+            out->n_periods = NGS_MAX_PERIODS + 1;
+            break;
+        }
         out->metric[out->n_periods] = p.name == kCoreUsagePriority ? NGS_METRIC_CORE : NGS_METRIC_MEMORY;  // nodeusage.go:84
         out->window_ns[out->n_periods] = dur;
         out->n_periods++;
@@ -683,7 +688,7 @@ std::vector<int> Dealer::Score(const std::vector<std::string>& nodes, const Pod&
     return ScoreSet(cs, pod, spec, isLoadSchedule);
 }
 
-Error Dealer::Bind(const std::string& node, Pod* pod, const PolicySpec& spec, bool isLoadSchedule) {  // dealer.go:155-203
+Error Dealer::Bind(const std::string& node, Pod* pod, const PolicySpec& spec, bool isLoadSchedule, const CommitFn& commit) {  // dealer.go:155-203
     std::lock_guard<std::recursive_mutex> lock(mu_);
     uint32_t row;
     Error e = getNodeInfo(node, &row);
@@ -704,6 +709,10 @@ Error Dealer::Bind(const std::string& node, Pod* pod, const PolicySpec& spec, bo
     for (size_t i = 0; i < pod->containers.size(); i++) pod->annotations[std::string(kContainerOn) + pod->containers[i].name] = std::to_string(gpu[i]);
     pod->annotations[kGPUAssume] = "true";
     pod->labels[kGPUAssume] = "true";
+    if (commit) {  // dealer.go:177-199: a failed apiserver Update / Bind returns before PodMaps is written; nothing is rolled back
+        Error ce = commit(*pod);
+        if (!ce.empty()) return ce;
+    }
     pod_maps_[pod->uid] = *pod;  // dealer.go:200
     return "";
 }

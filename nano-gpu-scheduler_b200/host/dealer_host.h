@@ -10,6 +10,7 @@
 // Citations are relative to /root/reference/pkg/dealer/ unless stated.
 #pragma once
 #include <cstdint>
+#include <functional>
 #include <map>
 #include <mutex>
 #include <set>
@@ -131,7 +132,12 @@ class Dealer {
     std::pair<std::vector<bool>, std::vector<Error>> Assume(const std::vector<std::string>& nodes, const Pod& pod, const PolicySpec& spec,
                                                             bool isLoadSchedule);
     std::vector<int> Score(const std::vector<std::string>& nodes, const Pod& pod, const PolicySpec& spec, bool isLoadSchedule);
-    Error Bind(const std::string& node, Pod* pod, const PolicySpec& spec, bool isLoadSchedule);  // pod gets the annotations of pkg/utils/pod.go:65-79
+    // pod gets the annotations of pkg/utils/pod.go:65-79.  `commit` stands where the reference talks to the apiserver
+    // (Pods().Update, one retry on the optimistic-lock message, then Pods().Bind: dealer.go:177-199): it is called with
+    // the annotated pod after the capacity has been taken; if it returns an error, Bind returns it and - as in the
+    // reference - the capacity stays taken while the pod does NOT enter PodMaps (dealer.go:200 is never reached).
+    using CommitFn = std::function<Error(const Pod&)>;
+    Error Bind(const std::string& node, Pod* pod, const PolicySpec& spec, bool isLoadSchedule, const CommitFn& commit = nullptr);
     Error Allocate(const Pod& pod);
     Error Release(const Pod& pod);
     Error Forget(const Pod& pod);

@@ -198,6 +198,35 @@ static void TestAssumeErrorTexts() {
     CHECK_EQ_STR(d.Bind("full", &p, PolicySpec{}, false), "assume [(20) (40)] on (10)(50) failed");  // node.go:75
 }
 
+// dealer.go:177-200: when the apiserver Update / Bind fails the capacity stays taken and the pod stays out of PodMaps
+static void TestBindCommitFailureLeavesPodUnknown() {
+    FakeCluster fc;
+    setup_node(fc, "n", {100, 100});
+    Dealer d(&fc, RaterKind::Binpack, 16);
+    Pod p = MockPodWithDemand({20, 40}, "commit-fails");
+    p.node_name = "n";
+    int calls = 0;
+    Error e = d.Bind("n", &p, PolicySpec{}, false, [&](const Pod& annotated) {
+        calls++;
+        CHECK(annotated.annotations.count("nano-gpu/assume") == 1);  // the host sees the annotated copy it has to write
+        return Error("Operation cannot be fulfilled on pods");
+    });
+    CHECK_EQ_STR(e, "Operation cannot be fulfilled on pods");
+    CHECK(calls == 1);
+    CHECK(!d.KnownPod(p));                    // never reached dealer.go:200
+    auto st = d.Status();
+    CHECK(st["n"][0] == 40 && st["n"][1] == 100);  // ... but the capacity is gone (no rollback in the reference)
+    CHECK(d.Release(p).empty());              // "no such pod": Release of an unknown pod changes nothing (dealer.go:240-243)
+    st = d.Status();
+    CHECK(st["n"][0] == 40);
+    // five usable SyncPeriod entries are within the library's limit of eight; nine are refused loudly, not truncated
+    PolicySpec many;
+    for (int i = 0; i < 9; i++) many.sync_period.push_back(Period{i % 2 ? "gpu_core_usage_avg" : "gpu_memory_usage_avg", 15LL * 1000000000LL});
+    auto r = d.Assume({"n"}, MockPodWithDemand({10}), many, true);
+    CHECK(!r.first[0]);
+    CHECK(r.second[0].find("periods") != std::string::npos);
+}
+
 static void TestScheduleCycleAndRelease() {
     FakeCluster fc;
     for (int i = 0; i < 6; i++) fc.add("node-" + std::to_string(i), 8);
@@ -425,6 +454,7 @@ int main() {
     TestSpreadRate();
     TestNewDemandAndPlanFromPod();
     TestAssumeErrorTexts();
+    TestBindCommitFailureLeavesPodUnknown();
     TestScheduleCycleAndRelease();
     TestAllocateFromAnnotationsAndRebuild();
     TestLoadAwareScoring();

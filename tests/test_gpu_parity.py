@@ -375,9 +375,9 @@ def test_batch_small_clusters(ngs, policy):
         run_batch_pair(ngs, n, 0.5, 150, (1, 3), (0, 12), policy, 100 + n)
 
 
-def test_batch_config_c2_scaled(ngs):
-    """configs[1] shape (spread, single container) at a size the oracle finishes in seconds"""
-    run_batch_pair(ngs, 5000, 0.3, 1500, (1, 1), (1, 20), 1, 0xB2000002)
+def test_batch_config_c2_full(ngs):
+    """BASELINE configs[1] at its full size: 5k nodes, 10k pending pods, spread, single container (50 M oracle evaluations)"""
+    run_batch_pair(ngs, 5000, 0.3, 10000, (1, 1), (1, 20), 1, 0xB2000002)
 
 
 def test_batch_config_c3_scaled(ngs):
@@ -453,6 +453,53 @@ def test_batch_rejects_bad_pods(ngs):
         assert len(node) == 0
 
 
+def test_device_batch_with_one_bad_pod_schedules_the_rest(ngs):
+    """device-resident batches are validated on the device: a malformed pod is reported as NGS_NODE_INVALID_POD and
+    skipped, every other pod gets exactly the decision it would get in a batch without the bad one, the snapshot
+    shows the good pods only, and the call's status says NGS_ERR_INVALID once"""
+    import torch
+
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    n, P, max_c = 3000, 300, 4
+    for bad_at, what in ((137, "percent"), (0, "ncont"), (299, "policy")):
+        oc, d, _, _ = make_pair(ngs, n, 0.5, 0xBAD + bad_at)
+        pc, nc = wl.make_pods(P, 1, 4, 0, 12, 0xBAD, max_c=max_c)
+        pol = (np.arange(P) % 3).astype(np.int32)
+        good = np.ones(P, dtype=bool)
+        good[bad_at] = False
+        bpc, bnc, bpol = pc.copy(), nc.copy(), pol.copy()
+        if what == "percent":
+            bpc[bad_at, 0] = -5
+        elif what == "ncont":
+            bnc[bad_at] = max_c + 1
+        else:
+            bpol[bad_at] = 7
+        dev = torch.device("cuda", 0)
+        with d:
+            t_pc, t_nc, t_pol = (torch.from_numpy(a).to(dev) for a in (bpc, bnc, bpol))
+            out = torch.full(((2 + max_c) * P,), 777, dtype=torch.int32, device=dev)
+            b = out.data_ptr()
+            d.schedule_batch_dev(P, t_pc.data_ptr(), t_nc.data_ptr(), max_c, t_pol.data_ptr(), b, b + 4 * P, b + 8 * P, seed=4, seq0=0)
+            with pytest.raises(ngs.NgsError) as ei:
+                d.sync()
+            assert ei.value.status == ngs.ERR_INVALID
+            d.sync()  # reported once
+            o_ = out.cpu().numpy()
+            node, score, gidx = o_[:P], o_[P:2 * P], o_[2 * P:].reshape(P, max_c)
+            assert node[bad_at] == ngs._abi.NODE_INVALID_POD and score[bad_at] == 0 and (gidx[bad_at] == ngs.INT32_MIN).all()
+            # the oracle schedules the good pods with the sequence numbers they had in the batch (the random policy's pick
+            # is seeded per pod position): run it pod by pod
+            for p_ in np.flatnonzero(good):
+                on, os_, og = oc.schedule_batch(pc[p_:p_ + 1], nc[p_:p_ + 1], pol[p_:p_ + 1], seed=4, seq0=int(p_))
+                assert node[p_] == on[0] and score[p_] == os_[0] and np.array_equal(gidx[p_], og[0]), (what, p_)
+            assert_same_snapshot(oc, d)
+            # a later batch on the same handle is not disturbed
+            node2, _, _ = d.schedule_batch(pc[:50], nc[:50], pol[:50], seed=5)
+            on2, _, _ = oc.schedule_batch(pc[:50], nc[:50], pol[:50], seed=5)
+            assert np.array_equal(node2, on2)
+
+
 def test_batch_chunking_across_launches(ngs):
     """more pods than one launch holds (4096): chunks continue the same sequence"""
     run_batch_pair(ngs, 400, 0.2, 5000, (1, 2), (1, 6), 2, 0xC4)
@@ -460,14 +507,16 @@ def test_batch_chunking_across_launches(ngs):
 
 
 # ---- full-size, size-independent properties ----------------------------------------------------
-def test_full_size_c3_properties(ngs):
-    """100k nodes, load-aware binpack (BASELINE configs[2]): the oracle is too slow for every pod,
-    so check (a) the oracle on a prefix of pods, (b) conservation: capacity removed from the
-    snapshot == sum of placed demands, (c) every placed container fits where it was put,
-    (d) schedule -> release of everything restores the snapshot bit for bit."""
+def test_full_size_c3_whole_bench_step(ngs):
+    """100k nodes, load-aware binpack, 2..4 containers (BASELINE configs[2], the configuration the headline number is
+    quoted on): ONE WHOLE bench step - 2048 pods in order - against the oracle, every decision and the snapshot bit for
+    bit (205 M oracle evaluations, all host threads); then the size-independent properties on a longer run:
+    (b) conservation, (c) every placed container fits where it was put, (d) schedule -> release restores the snapshot."""
+    import os
+
     from nano_gpu_scheduler_b200 import workloads as wl
 
-    n, P = 100_000, 3000
+    n, P, K = 100_000, 3000, 2048
     gcount, free = wl.make_cluster(n, 0.5, 0xB2000003)
     pc, nc = wl.make_pods(P, 2, 4, 0, 12, 0xB2000003, max_c=4)
     with ngs.GpuDealer(n, device=0) as d:
@@ -477,7 +526,19 @@ def test_full_size_c3_properties(ngs):
             ok = np.repeat(~absent[:, None], 8, axis=1).astype(np.uint8)
             d.load_update_bulk(m, value, ts, value_ok=ok, ts_ok=ok)
         gl, ol = load_ctx_pair(ngs)
-        node, score, gidx = d.schedule_batch(pc, nc, 0, load=gl)
+        node, score, gidx = d.schedule_batch(pc[:K], nc[:K], 0, load=gl)
+        # (a) the oracle on the whole step
+        oc = o.OracleCluster(n)
+        oc.load_snapshot(gcount, free)
+        for m, (value, ts, absent) in enumerate(tables):
+            oc.load_update_bulk(m, value, ts, ok=np.repeat(~absent[:, None], 8, axis=1).astype(np.uint8))
+        onode, oscore, ogidx = oc.schedule_batch(pc[:K], nc[:K], 0, load=ol, n_threads=os.cpu_count() or 4)
+        assert np.array_equal(node, onode) and np.array_equal(score, oscore) and np.array_equal(gidx, ogidx)
+        assert_same_snapshot(oc, d)
+        oc.close()
+        # the rest of the run continues on the same snapshot
+        node2, score2, gidx2 = d.schedule_batch(pc[K:], nc[K:], 0, load=gl, seq0=K)
+        node, gidx = np.concatenate([node, node2]), np.concatenate([gidx, gidx2])
         _, after, _ = d.snapshot_read()
         placed = node >= 0
         assert placed.sum() > P // 2
@@ -495,18 +556,56 @@ def test_full_size_c3_properties(ngs):
                     assert 0 <= g < 8 and cur[node[p], g] >= pc[p, k]
                     cur[node[p], g] -= pc[p, k]
         assert np.array_equal(cur, after)
-        # (a) oracle on a prefix
-        K = 12
-        oc = o.OracleCluster(n)
-        oc.load_snapshot(gcount, free)
-        for m, (value, ts, absent) in enumerate(tables):
-            oc.load_update_bulk(m, value, ts, ok=np.repeat(~absent[:, None], 8, axis=1).astype(np.uint8))
-        onode, oscore, ogidx = oc.schedule_batch(pc[:K], nc[:K], 0, load=ol, n_threads=4)
-        assert np.array_equal(node[:K], onode) and np.array_equal(score[:K], oscore) and np.array_equal(gidx[:K], ogidx)
         # (d) round trip
         for p in np.flatnonzero(placed):
             assert d.node_apply(int(node[p]), gidx[p, : nc[p]], pc[p, : nc[p]], -1) == 0
         assert np.array_equal(d.snapshot_read()[1], free)
+
+
+def test_full_size_c5_churn_slice(ngs):
+    """BASELINE configs[4] at its full cluster size: 50k nodes, 6000 interleaved operations - schedule (policy cycling
+    random / binpack / spread per pod, seeded replay) 60 %, release of a random live pod 35 %, forget 5 % (bookkeeping
+    only, dealer.go:311-319) - every decision and the final snapshot against the oracle"""
+    import os
+
+    from nano_gpu_scheduler_b200 import workloads as wl
+
+    n = 50_000
+    oc, d, _, _ = make_pair(ngs, n, 0.5, 0xB2000005)
+    rng = np.random.default_rng(0xC5)
+    threads = os.cpu_count() or 4
+    live, seq, ops = [], 0, 0
+    with d:
+        for rnd in range(10):
+            P = 360  # 60 % of a 600-operation round
+            pc, nc = wl.make_pods(P, 1, 3, 1, 12, 0xB2000005 + rnd, max_c=4)
+            pol = ((np.arange(P) + seq) % 3 + 2) % 3  # random, binpack, spread, ...
+            node, score, gidx = d.schedule_batch(pc, nc, pol, seed=0xB2000005, seq0=seq)
+            onode, oscore, ogidx = oc.schedule_batch(pc, nc, pol, seed=0xB2000005, seq0=seq, n_threads=threads)
+            assert np.array_equal(node, onode) and np.array_equal(score, oscore) and np.array_equal(gidx, ogidx), rnd
+            seq += P
+            for p in range(P):
+                if node[p] >= 0:
+                    live.append((int(node[p]), pc[p, : nc[p]].copy(), gidx[p, : nc[p]].copy()))
+            k = min(210, len(live))  # 35 %: one batched Release call on the GPU, one by one on the oracle
+            picks = sorted(rng.choice(len(live), size=k, replace=False).tolist(), reverse=True)
+            rel = [live.pop(i) for i in picks]
+            r_node = np.array([r[0] for r in rel], dtype=np.uint32)
+            r_gi = np.full((k, 4), -1, dtype=np.int32)
+            r_pc = np.zeros((k, 4), dtype=np.int32)
+            r_nc = np.array([len(r[1]) for r in rel], dtype=np.int32)
+            for i, r in enumerate(rel):
+                r_pc[i, : len(r[1])] = r[1]
+                r_gi[i, : len(r[2])] = r[2]
+                assert oc.node_apply(r[0], r[2], r[1], -1) == 0
+            rc, st = d.release_batch(r_node, r_gi, r_pc, r_nc)
+            assert rc == 0 and not st.any()
+            for _ in range(30):  # 5 %: Forget changes no capacity
+                if live:
+                    live.pop(int(rng.integers(0, len(live))))
+            ops += P + k + 30
+        assert ops >= 5000
+        assert_same_snapshot(oc, d)
 
 
 def test_full_size_million_nodes(ngs):
@@ -526,6 +625,14 @@ def test_full_size_million_nodes(ngs):
         assert np.array_equal(r["score"][r["feasible"] == 1], want[r["feasible"] == 1])
         pc, nc = wl.make_pods(64, 1, 1, 1, 20, 0xB2000004)
         node, score, gidx = d.schedule_batch(pc, nc, 0)
+        # the oracle on the same 64 pods over all 1M nodes (and below an independent numpy restatement)
+        import os
+
+        oc = o.OracleCluster(n)
+        oc.load_snapshot(gcount, free)
+        onode, oscore, ogidx = oc.schedule_batch(pc, nc, 0, n_threads=os.cpu_count() or 4)
+        assert np.array_equal(node, onode) and np.array_equal(score, oscore) and np.array_equal(gidx, ogidx)
+        oc.close()
         cur = free.copy()
         for p in range(64):
             dem = pc[p, 0]

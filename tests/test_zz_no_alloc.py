@@ -6,7 +6,9 @@ and outputs are the caller's (here: torch tensors).
 
 Checked through the C ABI against the existing handle-based entry point (ngs_schedule_batch_dev)
 on the same snapshot and pods, bit for bit, on two calls in a row — the second call finds the
-scratch array full of the first call's words.  This file sorts last on purpose."""
+scratch array full of the first call's words — and, so that the comparison does not rest on the
+handle path alone, the first call's decisions also against the CPU oracle.  This file sorts last
+on purpose."""
 import numpy as np
 import pytest
 
@@ -83,6 +85,21 @@ def test_noalloc_matches_handle_path_twice(built, load_on):
                                             got.data_ptr() + 4 * P, got.data_ptr() + 8 * P, load=load, seed=9, seq0=call * P)
             assert rc == ngs.OK, rc
             assert torch.equal(got, want), f"call {call}: decisions differ"
+            if call == 0:  # the oracle itself on the first call (the snapshot is still the generated one)
+                import oracle as o
+
+                oc = o.OracleCluster(n)
+                oc.load_snapshot(gcount, free)
+                ol = None
+                if load_on:
+                    for m, (value, stamp, absent) in enumerate(load_tables):
+                        oc.load_update_bulk(m, value, stamp, ok=np.repeat(~absent[:, None], 8, axis=1).astype(np.uint8))
+                    ol = o.make_load_ctx(wl.DEFAULT_PERIODS, NOW_NS)
+                onode, oscore, ogidx = oc.schedule_batch(pc, nc, pol, load=ol, seed=9, seq0=0)
+                g = got.cpu().numpy()
+                assert np.array_equal(g[:P], onode) and np.array_equal(g[P:2 * P], oscore)
+                assert np.array_equal(g[2 * P:].reshape(P, max_c), ogidx)
+                oc.close()
             assert (want[:P] >= 0).sum().item() > P // 2
             _, fr, rl = ref.snapshot_read()
             assert np.array_equal(t["free"].cpu().numpy(), fr), f"call {call}: snapshots differ"
@@ -115,10 +132,17 @@ def test_noalloc_limits_and_arguments(built):
     rc = ngs.schedule_batch_noalloc(view, P, pc.data_ptr(), nc.data_ptr(), max_c, pol.data_ptr(), out.data_ptr(),
                                     out.data_ptr() + 4 * P, out.data_ptr() + 8 * P)
     assert rc == ngs.OK and (out[:P] >= 0).all()
-    # bad pods are reported by the batch's status word
+    # a bad pod is reported by the batch's status word and by its own node_out; the others are scheduled
     pc[3, 0] = -7
     rc = ngs.schedule_batch_noalloc(view, P, pc.data_ptr(), nc.data_ptr(), max_c, pol.data_ptr(), out.data_ptr(),
                                     out.data_ptr() + 4 * P, out.data_ptr() + 8 * P)
+    assert rc == ngs.ERR_INVALID
+    assert out[3].item() == ngs._abi.NODE_INVALID_POD and (out[:3] >= 0).all() and (out[4:P] >= 0).all()
+    # a table at an address the vector loads cannot take is refused before anything is launched
+    odd = torch.zeros(n * 8 + 1, dtype=torch.int32, device=dev)
+    bad_view = _view(ngs, dict(t, free=odd[1:]), n)
+    rc = ngs.schedule_batch_noalloc(bad_view, 4, pc.data_ptr(), nc.data_ptr(), max_c, pol.data_ptr(), out.data_ptr(),
+                                    out.data_ptr() + 16, out.data_ptr() + 32)
     assert rc == ngs.ERR_INVALID
     assert ngs.schedule_batch_noalloc(view, 1, 0, nc.data_ptr(), max_c, pol.data_ptr(), out.data_ptr(), out.data_ptr(),
                                       out.data_ptr()) == ngs.ERR_INVALID
