@@ -92,7 +92,7 @@ def test_parse_update_time_like_go_layout(built):  # stats.go:30-44, type.go:12
 def test_load_ctx_layout_matches_header(built):
     import nano_gpu_scheduler_b200 as ngs
 
-    assert C.sizeof(ngs._abi.LoadCtx) == 4 + 4 * 4 + 4 + 8 * 4 + 8  # int32, int32[4], pad, int64[4], int64
+    assert C.sizeof(ngs._abi.LoadCtx) == 4 + 4 * 8 + 4 + 8 * 8 + 8  # int32, int32[8], pad, int64[8], int64
     assert C.sizeof(ngs._abi.Stats) == 40
 
 
