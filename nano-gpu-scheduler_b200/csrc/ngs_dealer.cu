@@ -102,8 +102,8 @@ struct ngs_dealer {
 namespace {
 
 constexpr uint32_t BATCH_CHUNK = 4096;
-constexpr size_t XSLOT_HALF = (size_t)BATCH_CHUNK * NGS_MAX_RANKS + XMAIL_WORDS;  // u64 words per parity half: pod slots, then K7's plan mailbox
-static_assert(XMAIL_OFFSET == (size_t)BATCH_CHUNK * NGS_MAX_RANKS, "K7's mailbox sits right behind the pod slots");
+constexpr size_t XSLOT_HALF = (size_t)BATCH_CHUNK * NGS_MAX_RANKS * 2 + XMAIL_WORDS;  // u64 words per parity half: pod slots [pod][rank][2], then K7's plan mailbox
+static_assert(XMAIL_OFFSET == (size_t)BATCH_CHUNK * NGS_MAX_RANKS * 2, "K7's mailbox sits right behind the pod slots");
 
 int fail(ngs_dealer* h, int code, const char* fmt, ...) {
     if (h) {
@@ -207,8 +207,8 @@ int ensure_batch(ngs_dealer* h) {
     const size_t in_words = (size_t)cap * (NGS_MAX_CONTAINERS + 2), out_words = (size_t)cap * (NGS_MAX_CONTAINERS + 2);
     CU(h, cudaMalloc(&h->d_dem, sizeof(SortedDemand) * cap));
     // one exchange record per pod, pod-major, so that a batch of P pods clears ONE contiguous range:
-    //   [0,16) arg-max word {key, counter}   [16,20) random-policy arrival counter   [32, 32+8*SMs) per-CTA slots
-    h->pod_rec_bytes = (32 + sizeof(unsigned long long) * (size_t)h->num_sms + 31) / 32 * 32;
+    //   [0,32) arg-max round record {xa, x1, x2, arrivals}   [32,36) random-policy arrival counter   [64, 64+8*SMs) per-CTA slots
+    h->pod_rec_bytes = (64 + sizeof(unsigned long long) * (size_t)h->num_sms + 31) / 32 * 32;
     CU(h, cudaMalloc(&h->d_keys, h->pod_rec_bytes * cap));
     CU(h, cudaMalloc(&h->d_one, sizeof(OneRec) + sizeof(uint32_t) * ONE_MAX_CTAS));  // record, then K7's per-CTA counts
     CU(h, cudaMemsetAsync(h->d_one, 0, sizeof(OneRec) + sizeof(uint32_t) * ONE_MAX_CTAS, h->stream));
@@ -234,6 +234,10 @@ uint32_t schedule_block_size(uint32_t rpb) {
     return 1024;
 }
 
+// dynamic shared memory of K6: 32 bytes per row plus four feasibility-bit buffers (one per pod in flight); its static part
+// (staged demands, per-warp keys, round state) stays below K6_STATIC_SMEM
+size_t schedule_smem_bytes(uint32_t rpb) { return (size_t)rpb * 32 + (size_t)((rpb + 31) / 32) * 16 + 16; }
+constexpr size_t K6_STATIC_SMEM = 4096;
 // which instantiation of K6 serves CTAs of `rpb` rows, and its block size
 const void* schedule_kernel(uint32_t rpb) {
     return rpb > K6_EXCLUSIVE_ROWS ? (const void*)k_schedule<true> : (const void*)k_schedule<false>;
@@ -262,9 +266,12 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     if (grid > (uint32_t)h->num_sms) grid = (uint32_t)h->num_sms;
     const uint32_t rpb = (N + grid - 1) / grid;
     const uint32_t block = schedule_block(rpb);
-    const size_t smem = (size_t)rpb * 32 + (size_t)((rpb + 31) / 32) * 8 + 16;  // rows + two feasbits buffers
-    if (smem + 2048 > (size_t)h->smem_optin)  // (2 KB: the kernel's static shared memory)
+    const size_t smem = schedule_smem_bytes(rpb);
+    if (smem + K6_STATIC_SMEM > (size_t)h->smem_optin)
         return fail(h, NGS_ERR_UNSUPPORTED, "%u rows per SM need %zu B shared memory (> %d): shard the cluster over more GPUs", rpb, smem, h->smem_optin);
+    if ((uint64_t)h->T.first + N > (uint64_t)PK_NODE_MAX + 1)
+        return fail(h, NGS_ERR_UNSUPPORTED, "the batch kernel packs node indices into 26 bits: first_node + nodes = %llu > 2^26",
+                    (unsigned long long)h->T.first + N);
     {
         // the attribute is a per-device upper bound shared by every handle: allow the device maximum, once
         static bool s_done[64] = {false};
@@ -285,8 +292,7 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     k_prep_demands<<<(P + 127) / 128, 128, 0, h->stream>>>(d_percent, d_ncont, max_c, d_policy, P, h->d_dem, h->d_err);
     CU(h, cudaGetLastError());
     unsigned char* rec = reinterpret_cast<unsigned char*>(h->d_keys);
-    ulonglong2* d_xw = reinterpret_cast<ulonglong2*>(rec);
-    uint32_t* d_done = reinterpret_cast<uint32_t*>(rec + 16);
+    uint32_t* d_done = reinterpret_cast<uint32_t*>(rec + 32);
     CU(h, cudaMemsetAsync(rec, 0, h->pod_rec_bytes * (size_t)P, h->stream));
     if (lp.enabled) h->T.rl_zero = 0;  // the batch's load-aware Rate writes RemainLoad
     BatchParams bp;
@@ -299,12 +305,12 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     bp.score_out = d_score;
     bp.gpu_idx_out = d_gidx;
     bp.max_c = max_c;
-    bp.keys = reinterpret_cast<unsigned long long*>(rec + 32);
+    bp.keys = reinterpret_cast<unsigned long long*>(rec + 64);
     bp.done = d_done;
-    bp.xw = d_xw;
+    bp.rr = reinterpret_cast<unsigned long long*>(rec);
     bp.keys_stride = (uint32_t)(h->pod_rec_bytes / 8);
     bp.done_stride = (uint32_t)(h->pod_rec_bytes / 4);
-    bp.xw_stride = (uint32_t)(h->pod_rec_bytes / 16);
+    bp.rr_stride = (uint32_t)(h->pod_rec_bytes / 8);
     bp.status_out = status_out;
     bp.world = (uint32_t)h->world;
     bp.rank = (uint32_t)h->rank;
@@ -953,7 +959,7 @@ namespace {
 
 constexpr size_t NA_DEM_BYTES = sizeof(SortedDemand) * NGS_NOALLOC_MAX_PODS;                                      // sorted demands
 constexpr size_t NA_KEYS_BYTES = sizeof(unsigned long long) * (size_t)NGS_NOALLOC_MAX_PODS * NGS_NOALLOC_MAX_CTAS;  // per-CTA slots
-constexpr size_t NA_MX_BYTES = sizeof(ulonglong2) * NGS_NOALLOC_MAX_PODS;                                          // arg-max exchange words
+constexpr size_t NA_MX_BYTES = 32 * (size_t)NGS_NOALLOC_MAX_PODS;                                                   // arg-max round records
 constexpr size_t NA_DONE_BYTES = sizeof(uint32_t) * NGS_NOALLOC_MAX_PODS;                                          // arrival counters
 constexpr size_t NA_DEM_OFF = 0;
 constexpr size_t NA_KEYS_OFF = NA_DEM_OFF + NA_DEM_BYTES;
@@ -1040,19 +1046,20 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     if (grid > NGS_NOALLOC_MAX_CTAS) return NGS_ERR_NOALLOC_LIMIT;  // the per-CTA slots would not fit
     const uint32_t rpb = (N + grid - 1) / grid;
     const uint32_t block = schedule_block(rpb);
-    const size_t smem = (size_t)rpb * 32 + (size_t)((rpb + 31) / 32) * 8 + 16;
-    if (smem + 2048 > (size_t)dv->smem_optin) return NGS_ERR_UNSUPPORTED;
+    const size_t smem = schedule_smem_bytes(rpb);
+    if (smem + K6_STATIC_SMEM > (size_t)dv->smem_optin) return NGS_ERR_UNSUPPORTED;
+    if ((uint64_t)snap->first_node + N > (uint64_t)PK_NODE_MAX + 1) return NGS_ERR_UNSUPPORTED;  // node indices are packed into 26 bits
 
     unsigned char* sc = dv->scratch;
     SortedDemand* dem = reinterpret_cast<SortedDemand*>(sc + NA_DEM_OFF);
     unsigned long long* keys = reinterpret_cast<unsigned long long*>(sc + NA_KEYS_OFF);
-    ulonglong2* mx = reinterpret_cast<ulonglong2*>(sc + NA_MX_OFF);
+    unsigned long long* mx = reinterpret_cast<unsigned long long*>(sc + NA_MX_OFF);
     uint32_t* done = reinterpret_cast<uint32_t*>(sc + NA_DONE_OFF);
     int32_t* err = reinterpret_cast<int32_t*>(sc + NA_ERR_OFF);
     // the array still holds the previous call's words: everything the kernel expects to find at
     // zero is cleared here, in stream order, before the launch
     if (cudaMemsetAsync(keys, 0, sizeof(unsigned long long) * (size_t)n_pods * grid, st) != cudaSuccess ||
-        cudaMemsetAsync(mx, 0, sizeof(ulonglong2) * (size_t)n_pods, st) != cudaSuccess ||
+        cudaMemsetAsync(mx, 0, 32 * (size_t)n_pods, st) != cudaSuccess ||
         cudaMemsetAsync(done, 0, sizeof(uint32_t) * (size_t)n_pods, st) != cudaSuccess ||
         cudaMemsetAsync(err, 0, 2 * sizeof(int32_t), st) != cudaSuccess)
         return NGS_ERR_CUDA;
@@ -1083,10 +1090,10 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     bp.max_c = max_c;
     bp.keys = keys;
     bp.done = done;
-    bp.xw = mx;
+    bp.rr = mx;
     bp.keys_stride = grid;
     bp.done_stride = 1;
-    bp.xw_stride = 1;
+    bp.rr_stride = 4;
     bp.status_out = nullptr;
     bp.world = 1;
     bp.rank = 0;

@@ -21,14 +21,15 @@ struct OneRec {
 };
 
 // node-range sharding: this call's parity half of every rank's exchange buffer (K6's layout: pod-major
-// slots [BATCH_CHUNK][NGS_MAX_RANKS], then XMAIL_WORDS words of mailbox for the owner's plan)
+// slots [BATCH_CHUNK][NGS_MAX_RANKS][2] - this kernel uses the first NGS_MAX_RANKS words as one word per rank - then
+// XMAIL_WORDS words of mailbox for the owner's plan)
 struct OneShard {
     uint32_t world, rank;
     unsigned long long* xs[NGS_MAX_RANKS];
     int32_t* err;  // the handle's device error word (bounded waits raise it)
 };
 constexpr size_t XMAIL_WORDS = 16;
-constexpr size_t XMAIL_OFFSET = (size_t)4096 * NGS_MAX_RANKS;  // == BATCH_CHUNK * NGS_MAX_RANKS (static_assert in ngs_dealer.cu)
+constexpr size_t XMAIL_OFFSET = (size_t)4096 * NGS_MAX_RANKS * 2;  // == BATCH_CHUNK * NGS_MAX_RANKS * 2 (static_assert in ngs_dealer.cu)
 
 constexpr int32_t ONE_PENDING = 0x7FFFFFFF;  // status word while the kernel has not answered yet
 constexpr uint32_t ONE_MAX_CTAS = 1024;      // entries of the random policy's per-CTA count array

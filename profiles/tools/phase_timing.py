@@ -45,21 +45,24 @@ buf = np.zeros(4096 + 256 * 256 * 4, dtype=np.uint64)
 grid = C.c_uint32(0)
 assert lib.ngs_debug_phases(d._h, buf.ctypes.data_as(C.c_void_p), C.byref(grid)) == 0
 g = grid.value
-a = buf[: 16 * g].reshape(g, 16).astype(np.float64) / P
-names = ["cw0: exact plan only", "barrier (pod p settled)", "cw0: post-bind stats / cw1: atomicMax+bump", "control: iteration start -> pair barrier #2", "cw0: plan_group total / cw1: exchange wait", "pair barrier #1", "publish", "control: combine (best two per warp -> key)"]
-print(f"{name}: {cfg['nodes']} nodes, {P} pods, grid {g}; cycles per pod (min / median / max over CTAs)")
-for who, off in (("control warp 0 (plan, bind)", 0), ("control warp 1 (exchange)", 8)):
+R = P / 2.0  # rounds: two arg-max pods per grid exchange (bench workloads hold no random-policy pods)
+a = buf[: 16 * g].reshape(g, 16).astype(np.float64) / R
+names = ["-", "dirty-row fix-ups (bits, one warp's keys recomputed)", "combine + exact plan (cw0: pod a + F; cw1: first atomicMax issued, plan of pod b's row)",
+         "post (cw0: atomicMax xa + counter; cw1: second atomicMax + counter)", "cw1: poll the round record + resolve", "pair barrier (cw0 waits for the resolution)",
+         "bind + the changed row's verdicts for the next round", "CTA barrier at the end of the previous round -> start of this one"]
+print(f"{name}: {cfg['nodes']} nodes, {P} pods, grid {g}; cycles per ROUND of two pods (min / median / max over CTAs)")
+for who, off in (("control warp 0 (pod a: plan, post, bind)", 0), ("control warp 1 (pod b: top two, poll, bind)", 8)):
     print(who)
-    for i in range(8):
+    for i in (7, 1, 2, 3, 4, 5, 6):
         col = a[:, off + i]
-        print(f"  {names[i]:84s} {col.min():8.0f} {np.median(col):8.0f} {col.max():8.0f}")
+        print(f"  {names[i]:100s} {col.min():8.0f} {np.median(col):8.0f} {col.max():8.0f}")
     print(f"  {'total':14s} {a[:, off:off + 8].sum(axis=1).mean():8.0f}")
 
 
-w = buf[4096: 4096 + 32 * g].reshape(g, 32).astype(np.float64) / P
+w = buf[4096: 4096 + 32 * g].reshape(g, 32).astype(np.float64) / R
 nw = int((w[0] > 0).sum())
 per_cta = w[:, :nw].max(axis=1)
-print(f"workers: filter of the NEXT pod, cycles per pod, slowest warp of each CTA ({nw} worker warps): min {per_cta.min():.0f} median {np.median(per_cta):.0f} "
+print(f"workers: filter of the NEXT round's pods, cycles per round, slowest warp of each CTA ({nw} worker warps): min {per_cta.min():.0f} median {np.median(per_cta):.0f} "
       f"max {per_cta.max():.0f} (CTA {int(per_cta.argmax())}); within the slowest CTA: fastest warp {w[int(per_cta.argmax()), :nw].min():.0f}")
 order = np.argsort(-per_cta)[:6]
 print("slowest CTAs:", [(int(c), int(per_cta[c])) for c in order])
