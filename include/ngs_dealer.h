@@ -214,7 +214,7 @@ int ngs_xchg_attach(ngs_dealer *h, int rank, int world, const void *handles);
  * the caller owns the snapshot tables (described by ngs_snapshot_view, laid out exactly as the
  * handle keeps them) and passes the pods and the outputs as device pointers; the scratch the batch
  * kernel needs (sorted demands, per-pod exchange words, error word) lives in a fixed array inside
- * the library's device image, 378 112 bytes (about 369 KiB) that every GPU loading the library keeps
+ * the library's device image, 386 304 bytes (about 377 KiB) that every GPU loading the library keeps
  * until exit.
  *
  * Limits: at most NGS_NOALLOC_MAX_PODS pods per call and a launch of at most

@@ -70,8 +70,29 @@ struct ngs_dealer {
     int32_t* d_nem = nullptr;
     size_t verb_cap = 0;   // candidates the verb scratch holds
     size_t plan_cap = 0;   // int32 entries d_plan holds
-    BindResult* d_bind = nullptr;
-    BindResult* h_bind = nullptr;  // pinned
+    BindResult* d_bind = nullptr;  // device alias of h_bind
+    BindResult* h_bind = nullptr;  // mapped pinned: k_bind writes its answer here, the host polls the status word
+    // verb staging in mapped pinned memory: the scan kernels write feasible / reason / score straight into host memory
+    // and raise a flag; a call needs no copy command and no stream synchronisation
+    uint8_t* h_vfeas = nullptr;
+    int8_t* h_vreason = nullptr;
+    int32_t* h_vscore = nullptr;
+    int32_t* h_vflag = nullptr;
+    uint8_t* d_vfeas = nullptr;  // device aliases
+    int8_t* d_vreason = nullptr;
+    int32_t* d_vscore = nullptr;
+    int32_t* d_vflag = nullptr;
+    uint32_t* d_vticket = nullptr;
+    size_t vstage_cap = 0;
+    int32_t vseq = 0;
+    // NodeInfo.Score after NodeInfo.Assume (node.go:59-68: the cached Plan.Score of the filter call): the scores of the last
+    // ngs_assume stay in the staging area; an ngs_score for the same demand and candidates, with no row changed in between, is a copy
+    bool sc_valid = false;
+    uint32_t sc_gen = 0, sc_n = 0;
+    uint64_t sc_sig = 0, sc_epoch = 0;
+    uint64_t epoch = 1;       // bumped by every call that changes a row
+    uint64_t idx_sig = 0;     // signature of the candidate list resident in d_idx (0: none)
+    uint32_t idx_n = 0;
     int32_t* d_small = nullptr;    // gpu_idx in / status out for k_apply
     int32_t* h_small = nullptr;    // pinned
     // batch
@@ -178,12 +199,61 @@ uint32_t demand_generation(ngs_dealer* h, const PodDemand& pd, bool load_on) {
     return h->gen;
 }
 
+// FNV-1a over the candidate list, eight bytes a step: the same list (kube-scheduler sends one list for filter and
+// prioritize, and mostly the same from pod to pod) is not uploaded again
+uint64_t idx_signature(const uint32_t* idx, uint32_t n) {
+    uint64_t hsh = 0xcbf29ce484222325ULL ^ n;
+    const uint64_t* p8 = reinterpret_cast<const uint64_t*>(idx);
+    uint32_t i = 0;
+    if ((reinterpret_cast<uintptr_t>(idx) & 7u) == 0)
+        for (; i + 2 <= n; i += 2) hsh = (hsh ^ p8[i >> 1]) * 0x100000001b3ULL;
+    for (; i < n; i++) hsh = (hsh ^ idx[i]) * 0x100000001b3ULL;
+    return hsh | 1ull;  // never 0
+}
+
+int ensure_verb_stage(ngs_dealer* h, size_t n) {
+    if (n <= h->vstage_cap) return NGS_OK;
+    const size_t cap = n < 4096 ? 4096 : n;
+    cudaFreeHost(h->h_vfeas); cudaFreeHost(h->h_vreason); cudaFreeHost(h->h_vscore);
+    h->h_vfeas = nullptr; h->h_vreason = nullptr; h->h_vscore = nullptr;
+    h->vstage_cap = 0;
+    h->sc_valid = false;
+    CU(h, cudaHostAlloc(&h->h_vfeas, cap, cudaHostAllocMapped));
+    CU(h, cudaHostAlloc(&h->h_vreason, cap, cudaHostAllocMapped));
+    CU(h, cudaHostAlloc(&h->h_vscore, cap * 4, cudaHostAllocMapped));
+    CU(h, cudaHostGetDevicePointer(&h->d_vfeas, h->h_vfeas, 0));
+    CU(h, cudaHostGetDevicePointer(&h->d_vreason, h->h_vreason, 0));
+    CU(h, cudaHostGetDevicePointer(&h->d_vscore, h->h_vscore, 0));
+    h->vstage_cap = cap;
+    return NGS_OK;
+}
+
+// wait for a verb kernel's flag in mapped host memory (no stream synchronisation); keeps an eye on the stream
+int wait_flag(ngs_dealer* h, volatile int32_t* flag, int32_t want, const char* what) {
+    for (uint32_t spins = 1; *flag != want; spins++) {
+#if defined(__x86_64__) || defined(__i386__)
+        __builtin_ia32_pause();
+#endif
+        if ((spins & 0xFFFu) == 0) {
+            const cudaError_t q = cudaStreamQuery(h->stream);
+            if (q == cudaSuccess) {
+                if (*flag == want) break;
+                return fail(h, NGS_ERR_CUDA, "%s ended without raising its flag", what);
+            }
+            if (q != cudaErrorNotReady) return fail(h, NGS_ERR_CUDA, "%s: %s", what, cudaGetErrorString(q));
+        }
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);
+    return NGS_OK;
+}
+
 int ensure_verb_scratch(ngs_dealer* h, size_t n, size_t plan_entries) {
     if (n > h->verb_cap) {
         size_t cap = n < 1024 ? 1024 : n;
         cudaFree(h->d_idx); cudaFree(h->d_feas); cudaFree(h->d_reason); cudaFree(h->d_score); cudaFree(h->d_nem);
         h->d_idx = nullptr; h->d_feas = nullptr; h->d_reason = nullptr; h->d_score = nullptr; h->d_nem = nullptr;
         h->verb_cap = 0;
+        h->idx_sig = 0;
         CU(h, cudaMalloc(&h->d_idx, cap * 4));
         CU(h, cudaMalloc(&h->d_feas, cap));
         CU(h, cudaMalloc(&h->d_reason, cap));
@@ -260,6 +330,7 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
                     const LoadParams& lp, uint64_t seed_seq, int32_t* d_node, int32_t* d_score, int32_t* d_gidx,
                     int32_t* status_out = nullptr) {
     if (!h->coop) return fail(h, NGS_ERR_CUDA, "device lacks cooperative launch");
+    h->epoch++;  // the batch binds pods
     const uint32_t N = h->T.n;
     uint32_t grid = (N + 63) / 64;
     if (grid < 1) grid = 1;
@@ -270,7 +341,7 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     if (smem + K6_STATIC_SMEM > (size_t)h->smem_optin)
         return fail(h, NGS_ERR_UNSUPPORTED, "%u rows per SM need %zu B shared memory (> %d): shard the cluster over more GPUs", rpb, smem, h->smem_optin);
     if ((uint64_t)h->T.first + N > (uint64_t)PK_NODE_MAX + 1)
-        return fail(h, NGS_ERR_UNSUPPORTED, "the batch kernel packs node indices into 26 bits: first_node + nodes = %llu > 2^26",
+        return fail(h, NGS_ERR_UNSUPPORTED, "the batch kernel packs node indices into 25 bits: first_node + nodes = %llu > 2^25",
                     (unsigned long long)h->T.first + N);
     {
         // the attribute is a per-device upper bound shared by every handle: allow the device maximum, once
@@ -327,8 +398,8 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     bp.err = h->d_err;
     bp.rows_per_block = rpb;
 #ifdef NGS_PHASE_TIMING
-    if (!h->d_dbg) CU(h, cudaMalloc(&h->d_dbg, sizeof(unsigned long long) * (4096 + 256 * 256 * 4)));
-    CU(h, cudaMemsetAsync(h->d_dbg, 0, sizeof(unsigned long long) * (4096 + 256 * 256 * 4), h->stream));
+    if (!h->d_dbg) CU(h, cudaMalloc(&h->d_dbg, sizeof(unsigned long long) * (4096 + 256 * 256 * 8)));
+    CU(h, cudaMemsetAsync(h->d_dbg, 0, sizeof(unsigned long long) * (4096 + 256 * 256 * 8), h->stream));
     bp.dbg = h->d_dbg;
     h->dbg_grid = grid;
 #endif
@@ -426,8 +497,13 @@ int ngs_create(ngs_dealer** out, int device, uint32_t max_nodes, uint32_t first_
         CU(h, cudaGetLastError());
         h->T.blut = lut;
     }
-    CU(h, cudaMalloc(&h->d_bind, sizeof(BindResult)));
-    CU(h, cudaMallocHost(&h->h_bind, sizeof(BindResult)));
+    CU(h, cudaHostAlloc(&h->h_bind, sizeof(BindResult), cudaHostAllocMapped));
+    CU(h, cudaHostGetDevicePointer(&h->d_bind, h->h_bind, 0));
+    CU(h, cudaHostAlloc(&h->h_vflag, 64, cudaHostAllocMapped));
+    CU(h, cudaHostGetDevicePointer(&h->d_vflag, h->h_vflag, 0));
+    *h->h_vflag = 0;
+    CU(h, cudaMalloc(&h->d_vticket, 64));
+    CU(h, cudaMemsetAsync(h->d_vticket, 0, 64, h->stream));
     CU(h, cudaMalloc(&h->d_small, 64 * 4));
     CU(h, cudaMallocHost(&h->h_small, 64 * 4));
     CU(h, cudaMalloc(&h->d_err, 8));  // [0] status, [1] abort flag
@@ -445,7 +521,8 @@ int ngs_destroy(ngs_dealer* h) {
     cudaFree(h->T.free); cudaFree(h->T.gcount); cudaFree(h->T.rl); cudaFree(h->T.tenths); cudaFree(h->T.ts);
     cudaFree(h->T.tag); cudaFree(h->T.cscore); cudaFree(const_cast<int16_t*>(h->T.blut));
     cudaFree(h->d_idx); cudaFree(h->d_feas); cudaFree(h->d_reason); cudaFree(h->d_score); cudaFree(h->d_plan); cudaFree(h->d_nem);
-    cudaFree(h->d_bind); cudaFreeHost(h->h_bind); cudaFree(h->d_small); cudaFreeHost(h->h_small);
+    cudaFreeHost(h->h_bind); cudaFree(h->d_small); cudaFreeHost(h->h_small);
+    cudaFreeHost(h->h_vfeas); cudaFreeHost(h->h_vreason); cudaFreeHost(h->h_vscore); cudaFreeHost(h->h_vflag); cudaFree(h->d_vticket);
     cudaFree(h->d_dem); cudaFree(h->d_keys); cudaFree(h->d_one);
     cudaFreeHost(h->h_pod_in); cudaFreeHost(h->h_pod_out);
     cudaFree(h->d_err); cudaFreeHost(h->h_err);
@@ -472,7 +549,7 @@ int ngs_sync(ngs_dealer* h) {
 // profiling builds only: per-CTA cycles per phase of the last k_schedule launch ([grid][16])
 int ngs_debug_phases(ngs_dealer* h, unsigned long long* out, uint32_t* grid) {
     if (!h || !h->d_dbg) return NGS_ERR_INVALID;
-    CU(h, cudaMemcpyAsync(out, h->d_dbg, sizeof(unsigned long long) * (4096 + 256 * 256 * 4), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaMemcpyAsync(out, h->d_dbg, sizeof(unsigned long long) * (4096 + 256 * 256 * 8), cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
     *grid = h->dbg_grid;
     return NGS_OK;
@@ -491,6 +568,7 @@ int ngs_node_upsert(ngs_dealer* h, uint32_t idx, int gpu_count) {
     if (gpu_count < 0) return fail(h, NGS_ERR_INVALID, "gpu_count %d", gpu_count);
     if (gpu_count > NGS_MAX_GPUS) return fail(h, NGS_ERR_UNSUPPORTED, "gpu_count %d > NGS_MAX_GPUS", gpu_count);
     CU(h, cudaSetDevice(h->device));
+    h->epoch++;
     k_upsert<<<1, 32, 0, h->stream>>>(h->T, idx - h->T.first, gpu_count);
     CU(h, cudaGetLastError());
     h->stats.kernel_launches++;
@@ -517,6 +595,7 @@ int ngs_snapshot_load(ngs_dealer* h, uint32_t first, uint32_t n, const uint8_t* 
         }
     }
     CU(h, cudaSetDevice(h->device));
+    h->epoch++;
     CU(h, cudaMemcpyAsync(h->T.free + (size_t)r0 * 8, fr.data(), fr.size() * 4, cudaMemcpyHostToDevice, h->stream));
     if (remain_load) h->T.rl_zero = 0;
     CU(h, cudaMemcpyAsync(h->T.rl + (size_t)r0 * 8, rl.data(), rl.size(), cudaMemcpyHostToDevice, h->stream));
@@ -550,6 +629,7 @@ int ngs_node_apply(ngs_dealer* h, uint32_t idx, const int32_t* gpu_idx, const in
     CU(h, cudaSetDevice(h->device));
     for (int i = 0; i < n_containers; i++) h->h_small[i] = gpu_idx[i];
     CU(h, cudaMemcpyAsync(h->d_small, h->h_small, NGS_MAX_CONTAINERS * 4, cudaMemcpyHostToDevice, h->stream));
+    h->epoch++;
     k_apply<<<1, 32, 0, h->stream>>>(h->T, idx, pd, h->d_small, sign, h->d_small + 32);
     CU(h, cudaGetLastError());
     CU(h, cudaMemcpyAsync(h->h_small + 32, h->d_small + 32, 4, cudaMemcpyDeviceToHost, h->stream));
@@ -584,6 +664,7 @@ int ngs_release_batch(ngs_dealer* h, uint32_t n, const uint32_t* node, const int
     CU(h, cudaMemcpyAsync(d_nc, n_containers, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
     CU(h, cudaMemcpyAsync(d_gi, gpu_idx, cells * 4, cudaMemcpyHostToDevice, h->stream));
     CU(h, cudaMemcpyAsync(d_pc, percent, cells * 4, cudaMemcpyHostToDevice, h->stream));
+    h->epoch++;
     k_release_batch<<<(n + 127) / 128, 128, 0, h->stream>>>(h->T, n, d_node, d_gi, d_pc, d_nc, max_c, d_st);
     CU(h, cudaGetLastError());
     std::vector<int32_t> st(n);
@@ -654,7 +735,7 @@ int ngs_load_update_bulk(ngs_dealer* h, int metric, uint32_t first, uint32_t n, 
 
 // launch the streaming scan over rows [0, n): TMA-staged tiles, feasibility / reason / score only
 static int launch_scan(ngs_dealer* h, uint32_t n, const PodDemand& pd, const LoadParams& lp, uint32_t gen, uint8_t* d_feas, int8_t* d_reason,
-                       int32_t* d_score) {
+                       int32_t* d_score, const VerbDone& vd) {
     const uint32_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     if (lp.enabled) {
         // load-aware pass: instruction-heavier per row; measured best with direct 256-bit loads at full
@@ -662,12 +743,12 @@ static int launch_scan(ngs_dealer* h, uint32_t n, const PodDemand& pd, const Loa
         int grid = (int)((n + 255) / 256);
         const int max_grid = h->num_sms * NGS_K1_BLOCKS;
         if (grid > max_grid) grid = max_grid;
-        k_assume<false><<<grid, 256, 0, h->stream>>>(h->T, nullptr, n, pd, lp, MODE_ASSUME, gen, d_feas, d_reason, d_score, nullptr, nullptr);
+        k_assume<false><<<grid, 256, 0, h->stream>>>(h->T, nullptr, n, pd, lp, MODE_ASSUME, gen, d_feas, d_reason, d_score, nullptr, nullptr, vd);
     } else {
         const size_t smem = (size_t)NGS_SCAN_STAGES * SCAN_STAGE_BYTES;
         uint32_t grid = (uint32_t)h->num_sms * NGS_SCAN_BLOCKS;
         if (grid > ntiles) grid = ntiles;
-        k_scan_tma<<<grid, SCAN_TILE, smem, h->stream>>>(h->T, n, pd, lp, d_feas, d_reason, d_score);
+        k_scan_tma<<<grid, SCAN_TILE, smem, h->stream>>>(h->T, n, pd, lp, d_feas, d_reason, d_score, vd);
     }
     CU(h, cudaGetLastError());
     return NGS_OK;
@@ -688,35 +769,68 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
     const bool want_plan = plan || n_emitted;
     rc = ensure_verb_scratch(h, n, want_plan ? (size_t)n * (n_containers > 0 ? n_containers : 1) : 0);
     if (rc) return rc;
+    rc = ensure_verb_stage(h, n);
+    if (rc) return rc;
     const uint32_t gen = demand_generation(h, pd, lp.enabled != 0);
+    uint64_t sig = 0;
     if (idx) {
-        CU(h, cudaMemcpyAsync(h->d_idx, idx, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
-        h->stats.h2d_bytes += (size_t)n * 4;
+        sig = idx_signature(idx, n);
+        if (sig != h->idx_sig || n != h->idx_n) {  // a list the device does not hold yet
+            CU(h, cudaMemcpyAsync(h->d_idx, idx, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+            h->stats.h2d_bytes += (size_t)n * 4;
+            h->idx_sig = sig;
+            h->idx_n = n;
+        }
     }
+    // NodeInfo.Score right after NodeInfo.Assume: the filter call's scores are still in the staging area
+    if (mode == MODE_SCORE && h->sc_valid && h->sc_gen == gen && h->sc_n == n && h->sc_sig == sig && h->sc_epoch == h->epoch) {
+        memcpy(score, h->h_vscore, (size_t)n * 4);
+        h->stats.node_evals += n;
+        return NGS_OK;
+    }
+    h->sc_valid = false;
     const int block = 256;
     int grid = (int)((n + block - 1) / block);
     const int max_grid = h->num_sms * (want_plan ? 2 : NGS_K1_BLOCKS);  // exactly the resident blocks: measured best
     if (grid > max_grid) grid = max_grid;
+    // per-node outputs go straight into mapped host memory; the scores are always produced (an ngs_score usually follows)
+    VerbDone vd;
+    vd.ticket = h->d_vticket;
+    vd.flag = h->d_vflag;
+    vd.seq = ++h->vseq;
+    uint8_t* o_feas = feasible ? h->d_vfeas : nullptr;
+    int8_t* o_reason = reason ? h->d_vreason : nullptr;
+    int32_t* o_score = h->d_vscore;
     if (!idx && mode == MODE_ASSUME && !want_plan) {
-        rc = launch_scan(h, n, pd, lp, gen, feasible ? h->d_feas : nullptr, reason ? h->d_reason : nullptr, score ? h->d_score : nullptr);
+        rc = launch_scan(h, n, pd, lp, gen, o_feas, o_reason, o_score, vd);
         if (rc) return rc;
     } else if (want_plan)
-        k_assume<true><<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, feasible ? h->d_feas : nullptr,
-                                                     reason ? h->d_reason : nullptr, score ? h->d_score : nullptr,
-                                                     plan ? h->d_plan : nullptr, n_emitted ? h->d_nem : nullptr);
+        k_assume<true><<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, o_feas, o_reason, o_score,
+                                                     plan ? h->d_plan : nullptr, n_emitted ? h->d_nem : nullptr, vd);
     else
-        k_assume<false><<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, feasible ? h->d_feas : nullptr,
-                                                      reason ? h->d_reason : nullptr, score ? h->d_score : nullptr, nullptr, nullptr);
+        k_assume<false><<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, o_feas, o_reason, o_score, nullptr,
+                                                      nullptr, vd);
     CU(h, cudaGetLastError());
-    if (feasible) CU(h, cudaMemcpyAsync(feasible, h->d_feas, n, cudaMemcpyDeviceToHost, h->stream));
-    if (reason) CU(h, cudaMemcpyAsync(reason, h->d_reason, n, cudaMemcpyDeviceToHost, h->stream));
-    if (score) CU(h, cudaMemcpyAsync(score, h->d_score, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
-    if (plan && n_containers > 0) CU(h, cudaMemcpyAsync(plan, h->d_plan, (size_t)n * n_containers * 4, cudaMemcpyDeviceToHost, h->stream));
-    if (n_emitted) CU(h, cudaMemcpyAsync(n_emitted, h->d_nem, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
-    CU(h, cudaStreamSynchronize(h->stream));
+    if (want_plan) {  // plans (the FailedNodes texts of the host mirror) still travel by copy commands
+        if (plan && n_containers > 0) CU(h, cudaMemcpyAsync(plan, h->d_plan, (size_t)n * n_containers * 4, cudaMemcpyDeviceToHost, h->stream));
+        if (n_emitted) CU(h, cudaMemcpyAsync(n_emitted, h->d_nem, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
+        CU(h, cudaStreamSynchronize(h->stream));
+    }
+    rc = wait_flag(h, h->h_vflag, vd.seq, "scan kernel");
+    if (rc) return rc;
+    if (feasible) memcpy(feasible, h->h_vfeas, n);
+    if (reason) memcpy(reason, h->h_vreason, n);
+    if (score) memcpy(score, h->h_vscore, (size_t)n * 4);
+    if (mode == MODE_ASSUME) {  // (a Score pass serves cached values per node: not a filter call's result)
+        h->sc_valid = true;
+        h->sc_gen = gen;
+        h->sc_n = n;
+        h->sc_sig = sig;
+        h->sc_epoch = h->epoch;
+    }
     h->stats.kernel_launches++;
     h->stats.node_evals += n;
-    h->stats.d2h_bytes += (feasible ? n : 0) + (reason ? n : 0) + (score ? (size_t)n * 4 : 0) +
+    h->stats.d2h_bytes += (feasible ? n : 0) + (reason ? n : 0) + (size_t)n * 4 +
                           (plan ? (size_t)n * n_containers * 4 : 0) + (n_emitted ? (size_t)n * 4 : 0);
     return NGS_OK;
 }
@@ -742,7 +856,12 @@ int ngs_assume_dev(ngs_dealer* h, uint32_t n, const int32_t* percent, int n_cont
     if (n == 0) return NGS_OK;
     CU(h, cudaSetDevice(h->device));
     const uint32_t gen = demand_generation(h, pd, lp.enabled != 0);
-    rc = launch_scan(h, n, pd, lp, gen, d_feasible, nullptr, d_score);
+    VerbDone none;
+    none.ticket = nullptr;
+    none.flag = nullptr;
+    none.seq = 0;
+    h->sc_valid = false;  // (a load-aware scan rewrites the per-node plan cache)
+    rc = launch_scan(h, n, pd, lp, gen, d_feasible, nullptr, d_score, none);
     if (rc) return rc;
     h->stats.kernel_launches++;
     h->stats.node_evals += n;
@@ -766,10 +885,26 @@ int ngs_bind(ngs_dealer* h, uint32_t idx, const int32_t* percent, int n_containe
     if (rc) return rc;
     CU(h, cudaSetDevice(h->device));
     const uint32_t gen = demand_generation(h, pd, lp.enabled != 0);
+    constexpr int32_t BIND_PENDING = 0x7FFFFFFE;
+    *reinterpret_cast<volatile int32_t*>(&h->h_bind->status) = BIND_PENDING;
+    h->epoch++;  // a row changes: scores kept from the last filter call are no longer the cache's
     k_bind<<<1, 32, 0, h->stream>>>(h->T, idx, pd, lp, gen, h->d_bind);
     CU(h, cudaGetLastError());
-    CU(h, cudaMemcpyAsync(h->h_bind, h->d_bind, sizeof(BindResult), cudaMemcpyDeviceToHost, h->stream));
-    CU(h, cudaStreamSynchronize(h->stream));
+    {   // the answer arrives in mapped host memory, status word last
+        volatile int32_t* st = &h->h_bind->status;
+        for (uint32_t spins = 1; *st == BIND_PENDING; spins++) {
+#if defined(__x86_64__) || defined(__i386__)
+            __builtin_ia32_pause();
+#endif
+            if ((spins & 0xFFFu) == 0) {
+                const cudaError_t q = cudaStreamQuery(h->stream);
+                if (q == cudaSuccess) break;
+                if (q != cudaErrorNotReady) return fail(h, NGS_ERR_CUDA, "k_bind: %s", cudaGetErrorString(q));
+            }
+        }
+        std::atomic_thread_fence(std::memory_order_acquire);
+        if (*st == BIND_PENDING) return fail(h, NGS_ERR_CUDA, "k_bind ended without an answer");
+    }
     h->stats.kernel_launches++;
     h->stats.node_evals++;
     h->stats.d2h_bytes += sizeof(BindResult);
@@ -832,6 +967,7 @@ int ngs_schedule_batch(ngs_dealer* h, uint32_t n_pods, const int32_t* percent, c
         if (lp.enabled && policy[0] != NGS_POLICY_RANDOM) h->T.rl_zero = 0;  // the load-aware Rate writes RemainLoad
         volatile int32_t* hout = h->h_pod_out;
         hout[0] = ONE_PENDING;
+        h->epoch++;  // the call binds the pod
         uint32_t grid = (h->T.n + 255) / 256;
         if (grid > (uint32_t)h->num_sms * 4) grid = (uint32_t)h->num_sms * 4;
         if (grid < 1) grid = 1;
@@ -959,7 +1095,7 @@ namespace {
 
 constexpr size_t NA_DEM_BYTES = sizeof(SortedDemand) * NGS_NOALLOC_MAX_PODS;                                      // sorted demands
 constexpr size_t NA_KEYS_BYTES = sizeof(unsigned long long) * (size_t)NGS_NOALLOC_MAX_PODS * NGS_NOALLOC_MAX_CTAS;  // per-CTA slots
-constexpr size_t NA_MX_BYTES = 32 * (size_t)NGS_NOALLOC_MAX_PODS;                                                   // arg-max round records
+constexpr size_t NA_MX_BYTES = 64 * (size_t)NGS_NOALLOC_MAX_PODS;                                                   // arg-max round records
 constexpr size_t NA_DONE_BYTES = sizeof(uint32_t) * NGS_NOALLOC_MAX_PODS;                                          // arrival counters
 constexpr size_t NA_DEM_OFF = 0;
 constexpr size_t NA_KEYS_OFF = NA_DEM_OFF + NA_DEM_BYTES;
@@ -1048,7 +1184,7 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     const uint32_t block = schedule_block(rpb);
     const size_t smem = schedule_smem_bytes(rpb);
     if (smem + K6_STATIC_SMEM > (size_t)dv->smem_optin) return NGS_ERR_UNSUPPORTED;
-    if ((uint64_t)snap->first_node + N > (uint64_t)PK_NODE_MAX + 1) return NGS_ERR_UNSUPPORTED;  // node indices are packed into 26 bits
+    if ((uint64_t)snap->first_node + N > (uint64_t)PK_NODE_MAX + 1) return NGS_ERR_UNSUPPORTED;  // node indices are packed into 25 bits
 
     unsigned char* sc = dv->scratch;
     SortedDemand* dem = reinterpret_cast<SortedDemand*>(sc + NA_DEM_OFF);
@@ -1059,7 +1195,7 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     // the array still holds the previous call's words: everything the kernel expects to find at
     // zero is cleared here, in stream order, before the launch
     if (cudaMemsetAsync(keys, 0, sizeof(unsigned long long) * (size_t)n_pods * grid, st) != cudaSuccess ||
-        cudaMemsetAsync(mx, 0, 32 * (size_t)n_pods, st) != cudaSuccess ||
+        cudaMemsetAsync(mx, 0, 64 * (size_t)n_pods, st) != cudaSuccess ||
         cudaMemsetAsync(done, 0, sizeof(uint32_t) * (size_t)n_pods, st) != cudaSuccess ||
         cudaMemsetAsync(err, 0, 2 * sizeof(int32_t), st) != cudaSuccess)
         return NGS_ERR_CUDA;
@@ -1093,7 +1229,7 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     bp.rr = mx;
     bp.keys_stride = grid;
     bp.done_stride = 1;
-    bp.rr_stride = 4;
+    bp.rr_stride = 8;
     bp.status_out = nullptr;
     bp.world = 1;
     bp.rank = 0;

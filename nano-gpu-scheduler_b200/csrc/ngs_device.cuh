@@ -50,7 +50,7 @@ struct SortedDemand {
     int32_t C;       // containers
     int32_t nz;      // containers with percent != 0
     int32_t policy;  // NGS_POLICY_*
-    int32_t pad_;
+    int32_t flags;   // bit 0: the pod failed validation (k_prep_demands); bits 1..: sum of the percents
     int32_t raw[NGS_MAX_CONTAINERS];    // container order (SampleRater walks this)
     int32_t d[NGS_MAX_CONTAINERS];      // processing order, non-zero entries first
     int32_t order[NGS_MAX_CONTAINERS];  // container index of each processed entry
@@ -95,16 +95,18 @@ __device__ inline void sort_demand(const int32_t* percent, int C, int policy, So
         }
     out->C = C;
     out->policy = policy;
-    out->pad_ = 0;
+    uint32_t sum = 0;
     int nz = 0;
     for (int k = 0; k < NGS_MAX_CONTAINERS; k++) {
         int j = C - 1 - k;  // rater.go:82: j runs from the largest demand down
         out->raw[k] = k < C ? percent[k] : 0;
+        sum += (uint32_t)key[k];  // (entries beyond C are 0)
         out->d[k] = j >= 0 ? key[j] : 0;
         out->order[k] = j >= 0 ? idx[j] : 0;
         if (j >= 0 && key[j] != 0) nz++;
     }
     out->nz = nz;  // percents are >= 0 (checked at the boundary), so non-zeros come first
+    out->flags = (int32_t)(sum << 1);
 }
 
 __device__ __forceinline__ void cex(uint32_t& a, uint32_t& b) {
@@ -351,6 +353,61 @@ __device__ __forceinline__ bool choose_group8(int g, int gbase, int fr, int rlc,
         *emit = em;
         *n_emit = ne;
         *fr_out = fr;
+    }
+    return ok;
+}
+
+// The same search, feasibility only, for FOUR (row, pod) pairs at once: every 8-lane group brings its own row and its
+// own demand (dem == nullptr: the group has nothing to ask and gets false).  Policies may differ between the groups.
+// The loop runs to the largest container count among the groups; a group that is through keeps executing the
+// warp-synchronous ops with a demand of zero, which places nothing.  One call costs what one search costs, so the
+// verdicts a bind owes to several waiting pods come at the price of one.  All 32 lanes must call this together.
+__device__ __forceinline__ bool choose_group8_multi(int g, int gbase, int fr, int rlc, bool valid, const SortedDemand* dem) {
+    uint32_t key = valid ? (uint32_t)(fr + 50 * rlc + 28) : 0x0FFFFFFFu;  // biased key; padding sorts last
+    if (!valid) fr = -1;                                                   // and never fits
+    int pos = g;
+    const int nz = dem != nullptr ? dem->nz : 0;
+    const bool spread = dem != nullptr && dem->policy == NGS_POLICY_SPREAD;
+    const int nzmax = (int)__reduce_max_sync(FULL, (unsigned)nz);
+    bool ok = dem != nullptr;
+    for (int k = 0; k < nzmax; k++) {
+        const bool active = k < nz;
+        const int d = active ? dem->d[k] : 0;
+        // (this group's last container only has to fit somewhere: what the vote below answers)
+        const uint32_t anyfit = (__ballot_sync(FULL, fr >= d) >> gbase) & 0xFFu;
+        if (active && k == nz - 1) ok = ok && anyfit != 0u;
+        const bool place = active && k < nz - 1;  // earlier containers are really placed: sort, first fit, subtract
+        const uint32_t b0 = (__ballot_sync(FULL, pos == 0) >> gbase) & 0xFFu;
+        const uint32_t b1 = (__ballot_sync(FULL, pos == 1) >> gbase) & 0xFFu;
+        const uint32_t b6 = (__ballot_sync(FULL, pos == 6) >> gbase) & 0xFFu;
+        const uint32_t b7 = (__ballot_sync(FULL, pos == 7) >> gbase) & 0xFFu;
+        const uint32_t k0 = __shfl_sync(FULL, key, gbase + __ffs(b0) - 1);
+        const uint32_t k1 = __shfl_sync(FULL, key, gbase + __ffs(b1) - 1);
+        const uint32_t k6 = __shfl_sync(FULL, key, gbase + __ffs(b6) - 1);
+        const uint32_t k7 = __shfl_sync(FULL, key, gbase + __ffs(b7) - 1);
+        const bool s06 = k6 < k0, s17 = k7 < k1;
+        int np = pos;
+        np = (s06 && pos == 0) ? 6 : np;
+        np = (s06 && pos == 6) ? 0 : np;
+        np = (s17 && pos == 1) ? 7 : np;
+        np = (s17 && pos == 7) ? 1 : np;
+        const uint32_t c = (key << 3) | (uint32_t)np;
+        int rank = 0;
+#pragma unroll
+        for (int sft = 1; sft < 8; sft++) rank += __shfl_xor_sync(FULL, c, sft) < c ? 1 : 0;
+        const bool fit = fr >= d;
+        int v = fit ? (spread ? rank : 7 - rank) : -1;  // larger is better in both cases
+        v = max(v, __shfl_xor_sync(FULL, v, 1));
+        v = max(v, __shfl_xor_sync(FULL, v, 2));
+        v = max(v, __shfl_xor_sync(FULL, v, 4));
+        const int sel = spread ? v : 7 - v;  // 8 / -1 when nothing fits: matches no position
+        const bool chosen = place && fit && rank == sel;
+        if (place) {
+            pos = rank;
+            ok = ok && v >= 0;
+        }
+        fr -= chosen ? d : 0;
+        key -= chosen ? (uint32_t)d : 0u;
     }
     return ok;
 }

@@ -5,6 +5,27 @@
 
 enum { MODE_ASSUME = 0, MODE_SCORE = 1 };
 
+// How a verb kernel tells the host that its outputs are complete when they go straight into mapped host memory (no copy
+// command, no stream synchronisation): every thread makes its stores visible system-wide, the CTA that draws the last
+// ticket writes the call's sequence number into the host's flag word.  flag == nullptr: the caller synchronises the stream.
+struct VerbDone {
+    uint32_t* ticket;  // device counter, zero between calls
+    int32_t* flag;     // mapped host word
+    int32_t seq;
+};
+__device__ __forceinline__ void verb_done(const VerbDone& vd) {
+    if (vd.flag == nullptr) return;
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (atomicAdd(vd.ticket, 1u) == gridDim.x - 1) {
+            *vd.ticket = 0;  // ready for the next call (ordered by the kernel boundary)
+            __threadfence_system();
+            *reinterpret_cast<volatile int32_t*>(vd.flag) = vd.seq;
+        }
+    }
+}
+
 // K1.  DealerImpl.Assume / DealerImpl.Score fan-out (dealer.go:109-134, 138-153): one thread
 // per candidate.  MODE_ASSUME recomputes every candidate (cleanPlan + Assume, dealer.go:123-124);
 // MODE_SCORE serves NodeInfo.Score (node.go:59-68) from the per-node cache when it holds a
@@ -16,7 +37,7 @@ template <bool PLAN>
 __global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables T, const uint32_t* __restrict__ idx, uint32_t n, PodDemand pd, LoadParams lp,
                                                 int mode, uint32_t gen, uint8_t* __restrict__ feasible,
                                                 int8_t* __restrict__ reason, int32_t* __restrict__ score,
-                                                int32_t* __restrict__ plan, int32_t* __restrict__ n_emitted) {
+                                                int32_t* __restrict__ plan, int32_t* __restrict__ n_emitted, VerbDone vd) {
     __shared__ SortedDemand dem;
     __shared__ double s_pair[121];
     if (threadIdx.x == 0) sort_demand(pd.percent, pd.n, pd.policy, &dem);
@@ -65,6 +86,7 @@ __global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables
             if (n_emitted) n_emitted[k] = ev.known ? ev.n_emit : 0;
         }
     }
+    verb_done(vd);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -116,7 +138,7 @@ __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem
 
 __global__ void __launch_bounds__(SCAN_TILE, NGS_SCAN_BLOCKS) k_scan_tma(Tables T, uint32_t n, PodDemand pd, LoadParams lp_in,
                                                                        uint8_t* __restrict__ feasible, int8_t* __restrict__ reason,
-                                                                       int32_t* __restrict__ score) {
+                                                                       int32_t* __restrict__ score, VerbDone vd) {
     extern __shared__ __align__(128) unsigned char tiles[];
     __shared__ SortedDemand dem;
     __shared__ __align__(8) uint64_t bars[NGS_SCAN_STAGES];
@@ -178,4 +200,5 @@ __global__ void __launch_bounds__(SCAN_TILE, NGS_SCAN_BLOCKS) k_scan_tma(Tables 
             if (score) score[row] = ok ? ev.score : NGS_SCORE_MIN;
         }
     }
+    verb_done(vd);
 }

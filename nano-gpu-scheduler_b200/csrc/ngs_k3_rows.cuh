@@ -9,9 +9,22 @@ struct BindResult {
 };
 
 // K3.  NodeInfo.Bind (node.go:70-84) for one row: cached or fresh plan, GPUs.Allocate, cleanPlan.
-__global__ void k_bind(Tables T, uint32_t gidx, PodDemand pd, LoadParams lp, uint32_t gen, BindResult* res) {
+// res may be mapped host memory: the status word is written last, behind a system-wide fence, and the host polls it
+__global__ void k_bind(Tables T, uint32_t gidx, PodDemand pd, LoadParams lp, uint32_t gen, BindResult* res_out) {
     __shared__ SortedDemand dem;
+    __shared__ BindResult s_res;
     if (threadIdx.x != 0) return;
+    BindResult* res = &s_res;
+    struct Publish {  // whatever way the body returns: copy the result out, status last
+        BindResult* from;
+        BindResult* to;
+        __device__ ~Publish() {
+            for (int j = 0; j < NGS_MAX_CONTAINERS; j++) to->gpu_idx[j] = from->gpu_idx[j];
+            to->score = from->score;
+            __threadfence_system();
+            *reinterpret_cast<volatile int32_t*>(&to->status) = from->status;
+        }
+    } publish{res, res_out};
     sort_demand(pd.percent, pd.n, pd.policy, &dem);
     const uint32_t row = gidx - T.first;
     for (int j = 0; j < NGS_MAX_CONTAINERS; j++) res->gpu_idx[j] = INT32_MIN;

@@ -154,6 +154,37 @@ int doh_choose_group8(const int32_t* free, const int32_t* G, const int8_t* rl, c
     g_warp_error = e ? e : "";
     return e ? 1 : 0;
 }
+// choose_group8_multi: four (row, pod) pairs per simulated warp, each group with its own demand and policy
+// (C[j] < 0: the group has nothing to ask).  percent is [4][12].
+struct G8MultiArgs {
+    const int32_t* free;
+    const int32_t* G;
+    const int8_t* rl;
+    SortedDemand dem[4];
+    bool has[4];
+    int32_t* ok;
+};
+static void g8m_body(int lane, void* p) {
+    G8MultiArgs& a = *(G8MultiArgs*)p;
+    const int g = lane & 7, gbase = lane & 24, row = lane >> 3;
+    const bool ok = choose_group8_multi(g, gbase, a.free[row * 8 + g], a.rl[row * 8 + g] + 2, g < a.G[row], a.has[row] ? &a.dem[row] : nullptr);
+    if (g == 0) a.ok[row] = ok ? 1 : 0;
+}
+int doh_choose_group8_multi(const int32_t* free, const int32_t* G, const int8_t* rl, const int32_t* percent, const int32_t* C, const int32_t* spread,
+                            int32_t* ok) {
+    G8MultiArgs a;
+    a.free = free;
+    a.G = G;
+    a.rl = rl;
+    a.ok = ok;
+    for (int j = 0; j < 4; j++) {
+        a.has[j] = C[j] >= 0;
+        if (a.has[j]) sort_demand(percent + 12 * j, C[j], spread[j] ? NGS_POLICY_SPREAD : NGS_POLICY_BINPACK, &a.dem[j]);
+    }
+    const char* e = warpsim::run_warp(g8m_body, &a);
+    g_warp_error = e ? e : "";
+    return e ? 1 : 0;
+}
 // the emission list of choose_group8 in container order, as the kernels publish it (rater.go:102-105)
 void doh_unpermute(const int32_t* percent, int C, int spread, uint64_t emit, int32_t* plan) {
     SortedDemand dem;

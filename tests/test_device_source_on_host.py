@@ -250,3 +250,46 @@ def test_eight_lane_plan_search_matches_oracle(doh, spread, wide):
                     if gi >= 0:
                         after[gi] -= int(demand[c])
                 assert fr[r, :g].tolist() == after[:g].tolist(), (trial, r)
+
+
+@pytest.mark.parametrize("wide", [False, True])
+def test_eight_lane_search_with_one_demand_per_group_matches_oracle(doh, wide):
+    """choose_group8_multi — feasibility of four (row, pod) pairs in one call: every 8-lane group has its own row, its own
+    demand (different container counts, so the groups finish at different iterations) and its own policy, or nothing at all"""
+    doh.doh_warp_error.restype = C.c_char_p
+    rng = np.random.default_rng(4242 + wide)
+    for trial in range(2500):
+        free = np.zeros((4, 8), dtype=np.int32)
+        rl = np.zeros((4, 8), dtype=np.int8)
+        G = rng.integers(0, 9, 4).astype(np.int32)
+        pct = np.zeros((4, 12), dtype=np.int32)
+        Cn = np.zeros(4, dtype=np.int32)
+        spread = rng.integers(0, 2, 4).astype(np.int32)
+        for r in range(4):
+            vals = rng.choice([0, 5, 20, 50, 99, 100, 101, 254, 255, 256, 300, 4000, 65535], size=8) if wide else rng.integers(0, 21, 8) * 5
+            free[r, : G[r]] = vals[: G[r]]
+            if rng.random() < 0.5:
+                rl[r, : G[r]] = rng.integers(-2, 3, G[r])
+            if rng.random() < 0.15:
+                Cn[r] = -1  # this group asks nothing
+                continue
+            Cn[r] = int(rng.integers(0, 13 if wide else 7))
+            if wide:
+                pct[r, : Cn[r]] = rng.choice([0, 5, 50, 100, 101, 255, 256, 300, 65535], size=Cn[r])
+            else:
+                pct[r, : Cn[r]] = rng.integers(0, 15, Cn[r]) * 5
+        ok = np.full(4, 7, dtype=np.int32)
+        rc = doh.doh_choose_group8_multi(_p(free), _p(G), _p(rl), _p(pct), _p(Cn), _p(spread), _p(ok))
+        assert rc == 0, doh.doh_warp_error()
+        for r in range(4):
+            if Cn[r] < 0:
+                assert ok[r] == 0, (trial, r)
+                continue
+            demand = pct[r, : Cn[r]]
+            g = int(G[r])
+            if g == 0:
+                assert bool(ok[r]) == (not (demand != 0).any()), (trial, r)
+                continue
+            policy = o.POLICY_SPREAD if spread[r] else o.POLICY_BINPACK
+            want_ok, _, _ = o.choose(policy, free[r, :g].astype(np.int64), demand, rl=rl[r, :g].astype(np.int64))
+            assert bool(ok[r]) == want_ok, (trial, r, free[r, :g], rl[r, :g], demand, spread[r])

@@ -204,3 +204,60 @@ def test_load_aware_rates_match_python_restatement(periods):
             assert got["score"][i] == want, (policy, i)
             assert rl[i][:G].tolist() == remain, (policy, i)
     oc.close()
+
+
+def test_go_vectors_when_present():
+    """tests/golden/go_vectors.json — outputs of the reference's own Go dealer (tests/golden/go_vectors/gen_go_vectors.go,
+    needs Go 1.16): tie order at 7..12 GPUs, Binpack.Rate over all totals, the load-aware mode.  Skipped while nobody with a
+    Go toolchain has generated the file."""
+    import json
+    import os
+
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "go_vectors.json")
+    if not os.path.exists(path):
+        pytest.skip("tests/golden/go_vectors.json has not been generated (needs Go 1.16 and the reference's module cache)")
+    with open(path) as f:
+        v = json.load(f)
+    for c in v["choose"]:
+        ok, idx, _ = o.choose(POL[c["policy"]], c["free"], c["demand"], rl=c["remain_load"])
+        assert ok == c["ok"], c
+        if ok:
+            assert idx == c["plan"], c
+    for c in v["binpack_rate"]:
+        G, used = c["gpus"], c["used"]
+        free, left = [], used
+        for _ in range(G):
+            take = min(left, 100)
+            free.append(100 - take)
+            left -= take
+        assert o.rate(o.POLICY_BINPACK, free) == c["score"], c
+    now_s = 1_790_000_000
+    for c in v["load"]:
+        G = len(c["free"])
+        oc = o.OracleCluster(1)
+        oc.node_set(0, c["free"])
+        for metric, table in ((o.METRIC_CORE, c["core"]), (o.METRIC_MEMORY, c["memory"])):
+            if table is None:
+                continue  # the node has no entry: GetUsage says "not exist" (nodeusage.go:85-88)
+            oc.load_add_node(0, metric)
+            for card, s in enumerate(table):
+                try:
+                    val, val_ok = float(s["value"]), True
+                except ValueError:
+                    val, val_ok = 0.0, False
+                oc.load_update(0, metric, card, val, now_s - s["age_s"], value_ok=val_ok, ts_ok=not s["bad_time"])
+        # getActiveDuration (stats.go:57-66) takes the FIRST entry with the name; window = period + 5 min (type.go:6)
+        first = {}
+        for m, p in c["periods"]:
+            first.setdefault(m, p)
+        periods = [(m, first[m] + 5 * 60 * 10**9) for m, _ in c["periods"]]
+        load = o.make_load_ctx(periods, now_s * 10**9 + 500_000_000)
+        r = oc.assume(c["demand"], POL[c["policy"]], load=load, want_plan=True)
+        assert bool(r["feasible"][0]) == c["ok"], c
+        # (Plan.Score is Rate's value whether or not Choose succeeds; the oracle reports 0 for an infeasible node as
+        # NodeInfo.Score does, node.go:59-68)
+        if c["ok"]:
+            assert r["score"][0] == c["score"], c
+            assert r["plan"][0].tolist() == c["plan"], c
+        _, _, rl = oc.node_get(0)
+        assert rl.tolist()[:G] == c["remain_load_after"], c
