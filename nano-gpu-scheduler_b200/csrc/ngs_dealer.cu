@@ -340,9 +340,6 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     const size_t smem = schedule_smem_bytes(rpb);
     if (smem + K6_STATIC_SMEM > (size_t)h->smem_optin)
         return fail(h, NGS_ERR_UNSUPPORTED, "%u rows per SM need %zu B shared memory (> %d): shard the cluster over more GPUs", rpb, smem, h->smem_optin);
-    if ((uint64_t)h->T.first + N > (uint64_t)PK_NODE_MAX + 1)
-        return fail(h, NGS_ERR_UNSUPPORTED, "the batch kernel packs node indices into 25 bits: first_node + nodes = %llu > 2^25",
-                    (unsigned long long)h->T.first + N);
     {
         // the attribute is a per-device upper bound shared by every handle: allow the device maximum, once
         static bool s_done[64] = {false};
@@ -1184,7 +1181,6 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     const uint32_t block = schedule_block(rpb);
     const size_t smem = schedule_smem_bytes(rpb);
     if (smem + K6_STATIC_SMEM > (size_t)dv->smem_optin) return NGS_ERR_UNSUPPORTED;
-    if ((uint64_t)snap->first_node + N > (uint64_t)PK_NODE_MAX + 1) return NGS_ERR_UNSUPPORTED;  // node indices are packed into 25 bits
 
     unsigned char* sc = dv->scratch;
     SortedDemand* dem = reinterpret_cast<SortedDemand*>(sc + NA_DEM_OFF);

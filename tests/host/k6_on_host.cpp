@@ -83,11 +83,7 @@ void plan_body(int lane, void* p) {
     PlanArgs& a = *(PlanArgs*)p;
     GroupCommit cm;
     memset(&cm, 0, sizeof cm);
-    PlanTargets pt;
-    pt.t0 = a.has_next ? &a.dem_next : nullptr;
-    pt.t1 = pt.t2 = nullptr;
-    pt.n = a.has_next ? 1 : 0;
-    plan_group(a.bp, a.rows->S, a.r, a.node, &a.dem, pt, nullptr, lane & 7, lane & 24, cm);
+    plan_group(a.bp, a.rows->S, a.r, a.node, &a.dem, a.has_next ? &a.dem_next : nullptr, lane & 7, lane & 24, cm);
     a.cm[lane] = cm;
     bool ok = false;
     a.fresh_only[lane] = fresh_key_of_row(a.rows->S, a.r, a.node, &a.dem, lane & 7, lane & 24, &ok);  // the row as it stands, this pod
