@@ -357,6 +357,52 @@ __device__ __forceinline__ bool choose_group8(int g, int gbase, int fr, int rlc,
     return ok;
 }
 
+// ---------------------------------------------------------------------------------------------
+// The greedy search without positions: what it does to the row as a set of cells, and whether it
+// succeeds - not which GPU index each container gets.  The order Go's sort leaves among cells of
+// DIFFERENT keys is the key order (the sort is correct, only not stable), so "first fit from the low
+// end" is "the fitting cell of the smallest key" (spread: of the largest).  Among cells of equal key
+// the reference goes by position; if those cells also hold the same free percent (hence the same
+// RemainLoad) they are interchangeable and any of them leaves the same row-as-a-set, so the outcome
+// is still exact.  Only a tie between equal keys with DIFFERENT free percents (free 60 / RemainLoad 0
+// against free 10 / RemainLoad 1) needs the positions: then bit 1 of the result is set and the caller
+// has to run the positional search (choose_group8).  A third of the shuffles and votes of
+// choose_group8 per container, and that is what the control path of the batch kernel waits for.
+//   APPLY: every container is placed and fr holds the cell as GPUs.Allocate would leave it;
+//   otherwise feasibility only (the last container only has to fit somewhere).
+// Returns bit 0: every non-zero container found a cell; bit 1: ambiguous tie met (result void).
+// One row per 8-lane group, all 32 lanes together, as choose_group8.
+// ---------------------------------------------------------------------------------------------
+template <bool APPLY>
+__device__ __forceinline__ int greedy_group8(int g, int gbase, int& fr, int rlc, bool valid, bool spread, const SortedDemand* dem) {
+    const int nz = dem->nz;
+    bool ok = true, amb = false;
+    for (int k = 0; k < nz; k++) {
+        const int d = dem->d[k];
+        const bool fit = valid && fr >= d;
+        if (!APPLY && k == nz - 1) {
+            const uint32_t anyfit = (__ballot_sync(FULL, fit) >> gbase) & 0xFFu;
+            ok = ok && anyfit != 0u;
+            break;
+        }
+        const uint32_t key = (uint32_t)(fr + 50 * rlc);
+        const uint32_t mine = fit ? (spread ? key + 1u : 0x7FFFFFFFu - key) : 0u;  // larger is better; 0 = does not fit
+        uint32_t v = mine;
+        v = max(v, __shfl_xor_sync(FULL, v, 1));
+        v = max(v, __shfl_xor_sync(FULL, v, 2));
+        v = max(v, __shfl_xor_sync(FULL, v, 4));
+        const bool cand = fit && mine == v;
+        const uint32_t cb = (__ballot_sync(FULL, cand) >> gbase) & 0xFFu;
+        const int first = cb ? __ffs(cb) - 1 : 0;
+        const int f0 = __shfl_sync(FULL, fr, gbase + first);
+        const uint32_t differ = (__ballot_sync(FULL, cand && fr != f0) >> gbase) & 0xFFu;
+        amb = amb || differ != 0u;
+        ok = ok && cb != 0u;  // rater.go:88-95: nothing fits, nothing appended; later containers are still placed
+        if (cb != 0u && g == first) fr -= d;
+    }
+    return (ok ? 1 : 0) | (amb ? 2 : 0);
+}
+
 // The same search, feasibility only, for FOUR (row, pod) pairs at once: every 8-lane group brings its own row and its
 // own demand (dem == nullptr: the group has nothing to ask and gets false).  Policies may differ between the groups.
 // The loop runs to the largest container count among the groups; a group that is through keeps executing the

@@ -140,7 +140,9 @@ struct GroupCommit {
 };
 
 __device__ __forceinline__ void plan_group(const BatchParams& bp, const SmemRows& S, uint32_t r, uint32_t node, const SortedDemand* dem,
-                                           const SortedDemand* dem_next, int g, int gbase, GroupCommit& cm, long long* stamps = nullptr) {
+                                           const SortedDemand* dem_next, int g, int gbase, GroupCommit& cm, long long* stamps = nullptr,
+                                           const int16_t* lut = nullptr) {
+    (void)bp;  // lut: Binpack.Rate's percent table wherever the caller keeps it (shared memory, global; plain loads), nullptr = fp64
     const uint32_t meta = S.meta[r];
     const int G = (meta >> 24) & 15;
     const int load_int = (int)(meta >> 28);
@@ -168,8 +170,7 @@ __device__ __forceinline__ void plan_group(const BatchParams& bp, const SmemRows
     t4 |= __shfl_xor_sync(FULL, t4, 2);
     t4 |= __shfl_xor_sync(FULL, t4, 4);
     const int used = 100 * G - sumf;  // allocate.go:164-171
-    const int pct = (bp.T.blut != nullptr && used >= 0 && used <= 100 * G) ? (int)__ldg(bp.T.blut + G * RATE_LUT_STRIDE + used)
-                                                                            : binpack_percent_fp64(used, G);
+    const int pct = (lut != nullptr && used >= 0 && used <= 100 * G) ? (int)lut[G * RATE_LUT_STRIDE + used] : binpack_percent_fp64(used, G);
     cm.top4 = t4;
     cm.scB = pct + load_int * 50 - G;                    // rater.go:69
     cm.scS = 100 * cnt100 + sumf / 10 - G - load_int;    // rater.go:122
@@ -189,9 +190,16 @@ __device__ __forceinline__ void plan_group(const BatchParams& bp, const SmemRows
         cls = classify_row(f, dem_next, pol2 != NGS_POLICY_RANDOM);
         if (cls == FEAS_UNDECIDED && pol2 == NGS_POLICY_RANDOM) cls = choose_sample<false>(f, G, dem_next, nullptr, nullptr) ? FEAS_YES : FEAS_NO;
     }
-    if (cls == FEAS_UNDECIDED)
-        cls = choose_group8<false>(g, gbase, fr, rlc, valid, pol2 == NGS_POLICY_SPREAD, dem_next, nullptr, nullptr, nullptr) ? FEAS_YES
-                                                                                                                               : FEAS_NO;
+    // less capacity left on the row than the pod asks for in total: no placement exists, so the greedy one fails as well
+    if (cls == FEAS_UNDECIDED && sumf < (int)((uint32_t)dem_next->flags >> 1)) cls = FEAS_NO;
+    if (cls == FEAS_UNDECIDED) {  // (warp-uniform) the position-free search first; the positional one only on an ambiguous tie
+        int frx = fr;
+        const int st = greedy_group8<false>(g, gbase, frx, rlc, valid, pol2 == NGS_POLICY_SPREAD, dem_next);
+        if (st & 2)
+            cls = choose_group8<false>(g, gbase, fr, rlc, valid, pol2 == NGS_POLICY_SPREAD, dem_next, nullptr, nullptr, nullptr) ? FEAS_YES : FEAS_NO;
+        else
+            cls = (st & 1) ? FEAS_YES : FEAS_NO;
+    }
     cm.fresh_ok = cls == FEAS_YES;
     if (cls == FEAS_YES && pol2 != NGS_POLICY_RANDOM) cm.fresh = make_key(pol2 == NGS_POLICY_SPREAD ? cm.scS : cm.scB, node);
 }
@@ -443,8 +451,15 @@ __device__ __forceinline__ void filter_pass(const SmemRows& S, const SortedDeman
                 const uint32_t rr = __shfl_sync(0xFFFFFFFFu, r, has ? __ffs(t) - 1 : 0);
                 const uint32_t meta = S.meta[rr];
                 const int G = has ? (int)((meta >> 24) & 15) : 0;
-                const bool ok = choose_group8<false>(g, gbase, smem_cell(S, rr, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem,
-                                                     nullptr, nullptr, nullptr);
+                // the position-free search first (a third of the latency); the positional one only where it met an ambiguous tie
+                int frx = smem_cell(S, rr, g);
+                const int st = greedy_group8<false>(g, gbase, frx, (int)((meta >> (3 * g)) & 7), g < G, spread, dem);
+                bool ok = (st & 1) != 0;
+                if (__any_sync(0xFFFFFFFFu, has && (st & 2))) {  // (warp-uniform)
+                    const bool ok_exact = choose_group8<false>(g, gbase, smem_cell(S, rr, g), (int)((meta >> (3 * g)) & 7), g < G, spread, dem,
+                                                               nullptr, nullptr, nullptr);
+                    if (st & 2) ok = ok_exact;
+                }
                 const uint32_t okb = __ballot_sync(0xFFFFFFFFu, has && ok && g == 0);  // group j's verdict at bit 8j
                 if ((und >> lane) & 1u) {
                     const uint32_t j = __popc(und & ((1u << lane) - 1u));
@@ -532,6 +547,8 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     __shared__ uint64_t s_fresh[2];   // that row's key for pod p, evaluated on the row after the bind (0 = not feasible)
     __shared__ int s_fresh_ok[2];     // ... and its feasibility (what the random policy needs)
     __shared__ int s_abort;
+    // Binpack.Rate's percent table next to the rows when they leave room (an L2 trip on the plan's path otherwise)
+    __shared__ int16_t s_blut[ALL_WORK ? 2 : 9 * RATE_LUT_STRIDE];
     const uint32_t rpb = bp.rows_per_block;
     if (threadIdx.x == 0) {
         s_abort = 0;
@@ -621,6 +638,11 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
         S.scB[r] = G ? rate_binpack(f, G, load_int, T.blut) : 0;
         S.scS[r] = G ? rate_spread(f, G, load_int) : 0;
         S.top4[r] = top4_of(f);  // cells beyond G hold 0
+    }
+    const int16_t* lut = bp.T.blut;  // where the plan warp looks Binpack.Rate up (nullptr: fp64)
+    if (!ALL_WORK && bp.T.blut != nullptr) {
+        for (uint32_t i = tid; i < 9 * RATE_LUT_STRIDE; i += blockDim.x) s_blut[i] = __ldg(bp.T.blut + i);
+        lut = s_blut;
     }
     for (uint32_t i = tid; i < 2 * sizeof(SortedDemand) / 4; i += blockDim.x)
         if (i / (sizeof(SortedDemand) / 4) < bp.P) reinterpret_cast<uint32_t*>(&s_dem[0])[i] = reinterpret_cast<const uint32_t*>(&bp.dem[0])[i];
@@ -929,14 +951,14 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
 #ifdef NGS_PHASE_TIMING
                     long long st[2] = {0, 0};
                     const long long t_in = clock64();
-                    if (have) plan_group(bp, S, my_r, T.first + row0 + my_r, dem, more ? dem_next : nullptr, g, gbase, cm, st);
+                    if (have) plan_group(bp, S, my_r, T.first + row0 + my_r, dem, more ? dem_next : nullptr, g, gbase, cm, st, lut);
                     if (have && cm.fresh != 12345) {
                         ph[0] += st[0] - t_in;   // exact plan (choose_group8<PLAN>)
                         ph[2] += st[1] - st[0];  // post-bind statistics and rates
                         ph[6] -= 0;
                     }
 #else
-                    if (have) plan_group(bp, S, my_r, T.first + row0 + my_r, dem, more ? dem_next : nullptr, g, gbase, cm);
+                    if (have) plan_group(bp, S, my_r, T.first + row0 + my_r, dem, more ? dem_next : nullptr, g, gbase, cm, nullptr, lut);
 #endif
                 }
                 PHASE(4);

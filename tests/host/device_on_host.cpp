@@ -185,6 +185,42 @@ int doh_choose_group8_multi(const int32_t* free, const int32_t* G, const int8_t*
     g_warp_error = e ? e : "";
     return e ? 1 : 0;
 }
+// greedy_group8: the position-free greedy search, four rows per simulated warp, one demand for all.
+//   state[4]: bit 0 ok, bit 1 ambiguous;  fr_out[4][8]: the cells afterwards (apply != 0)
+struct GGArgs {
+    const int32_t* free;
+    const int32_t* G;
+    const int8_t* rl;
+    SortedDemand dem;
+    bool spread, apply;
+    int32_t* state;
+    int32_t* fr_out;
+};
+static void gg_body(int lane, void* p) {
+    GGArgs& a = *(GGArgs*)p;
+    const int g = lane & 7, gbase = lane & 24, row = lane >> 3;
+    int fr = a.free[row * 8 + g];
+    const int rlc = a.rl[row * 8 + g] + 2;
+    const int st = a.apply ? greedy_group8<true>(g, gbase, fr, rlc, g < a.G[row], a.spread, &a.dem)
+                           : greedy_group8<false>(g, gbase, fr, rlc, g < a.G[row], a.spread, &a.dem);
+    if (g == 0) a.state[row] = st;
+    a.fr_out[row * 8 + g] = fr;
+}
+int doh_greedy_group8(const int32_t* free, const int32_t* G, const int8_t* rl, const int32_t* percent, int C, int spread, int apply,
+                      int32_t* state, int32_t* fr_out) {
+    GGArgs a;
+    a.free = free;
+    a.G = G;
+    a.rl = rl;
+    sort_demand(percent, C, spread ? NGS_POLICY_SPREAD : NGS_POLICY_BINPACK, &a.dem);
+    a.spread = spread != 0;
+    a.apply = apply != 0;
+    a.state = state;
+    a.fr_out = fr_out;
+    const char* e = warpsim::run_warp(gg_body, &a);
+    g_warp_error = e ? e : "";
+    return e ? 1 : 0;
+}
 // the emission list of choose_group8 in container order, as the kernels publish it (rater.go:102-105)
 void doh_unpermute(const int32_t* percent, int C, int spread, uint64_t emit, int32_t* plan) {
     SortedDemand dem;

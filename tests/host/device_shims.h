@@ -140,6 +140,7 @@ static inline long long clock64() { return 0; }
 template <class T> static inline T __ldcg(const T* p) { return *p; }
 static inline void __threadfence() {}
 static inline void __threadfence_system() {}
+static inline void __threadfence_block() {}
 // atomics of a single-threaded simulation
 static inline int atomicExch(int* p, int v) { int o = *p; *p = v; return o; }
 static inline int atomicCAS(int* p, int c, int v) { int o = *p; if (o == c) *p = v; return o; }

@@ -293,3 +293,49 @@ def test_eight_lane_search_with_one_demand_per_group_matches_oracle(doh, wide):
             policy = o.POLICY_SPREAD if spread[r] else o.POLICY_BINPACK
             want_ok, _, _ = o.choose(policy, free[r, :g].astype(np.int64), demand, rl=rl[r, :g].astype(np.int64))
             assert bool(ok[r]) == want_ok, (trial, r, free[r, :g], rl[r, :g], demand, spread[r])
+
+
+@pytest.mark.parametrize("spread", [False, True])
+def test_position_free_greedy_search_matches_oracle(doh, spread):
+    """greedy_group8 — the search without positions: wherever it does not report an ambiguous tie, its verdict equals the
+    oracle's, and (APPLY) the row it leaves equals, as a multiset of (free, RemainLoad) cells, the row the oracle's plan
+    leaves; ties it reports must be real (two fitting cells of equal key and different free percent exist at some step)"""
+    doh.doh_warp_error.restype = C.c_char_p
+    policy = o.POLICY_SPREAD if spread else o.POLICY_BINPACK
+    rng = np.random.default_rng(909 + spread)
+    n_amb = n_tot = 0
+    for trial in range(2500):
+        demand = (rng.integers(0, 13, int(rng.integers(1, 6))) * 5).astype(np.int32)
+        free = np.zeros((4, 8), dtype=np.int32)
+        rl = np.zeros((4, 8), dtype=np.int8)
+        G = rng.integers(0, 9, 4).astype(np.int32)
+        for r in range(4):
+            free[r, : G[r]] = rng.integers(0, 21, G[r]) * 5
+            if rng.random() < 0.6:
+                rl[r, : G[r]] = rng.integers(0, 3, G[r])
+        for apply in (1, 0):
+            st = np.zeros(4, dtype=np.int32)
+            fr = np.zeros((4, 8), dtype=np.int32)
+            rc = doh.doh_greedy_group8(_p(free), _p(G), _p(rl), _p(demand), len(demand), int(spread), apply, _p(st), _p(fr))
+            assert rc == 0, doh.doh_warp_error()
+            for r in range(4):
+                g = int(G[r])
+                n_tot += 1
+                if st[r] & 2:
+                    n_amb += 1  # (a tie can also arise from the placements themselves; the caller then runs the positional search)
+                    assert (rl[r, :g] != rl[r, 0]).any(), (trial, r)  # ... but never on a row whose cells share one RemainLoad
+                    continue
+                if g == 0:
+                    assert bool(st[r] & 1) == (not (demand != 0).any())
+                    continue
+                want_ok, idx, _ = o.choose(policy, free[r, :g].astype(np.int64), demand, rl=rl[r, :g].astype(np.int64))
+                assert bool(st[r] & 1) == want_ok, (trial, r, free[r, :g], rl[r, :g], demand)
+                if apply and want_ok:
+                    after = free[r, :g].astype(np.int64).copy()
+                    for c, gi in enumerate(idx):
+                        if gi >= 0:
+                            after[gi] -= int(demand[c])
+                    got = sorted(zip(fr[r, :g].tolist(), rl[r, :g].tolist()))
+                    want = sorted(zip(after.tolist(), rl[r, :g].tolist()))
+                    assert got == want, (trial, r, free[r, :g], rl[r, :g], demand, idx)
+    assert n_amb < 0.2 * n_tot  # the fast path has to be the common one
