@@ -91,8 +91,10 @@ struct ngs_dealer {
     uint32_t sc_gen = 0, sc_n = 0;
     uint64_t sc_sig = 0, sc_epoch = 0;
     uint64_t epoch = 1;       // bumped by every call that changes a row
-    uint64_t idx_sig = 0;     // signature of the candidate list resident in d_idx (0: none)
-    uint32_t idx_n = 0;
+    // the candidate list resident in d_idx, kept on the host as well: the same list (kube-scheduler sends one list for
+    // filter and prioritize, and mostly the same from pod to pod) is recognised by one memcmp and not uploaded again
+    std::vector<uint32_t> idx_host;
+    uint64_t idx_sig = 0;     // serial number of that list (0: none); part of the score cache's key
     int32_t* d_small = nullptr;    // gpu_idx in / status out for k_apply
     int32_t* h_small = nullptr;    // pinned
     // batch
@@ -197,18 +199,6 @@ uint32_t demand_generation(ngs_dealer* h, const PodDemand& pd, bool load_on) {
         if (h->gen == 0) h->gen = 1;
     }
     return h->gen;
-}
-
-// FNV-1a over the candidate list, eight bytes a step: the same list (kube-scheduler sends one list for filter and
-// prioritize, and mostly the same from pod to pod) is not uploaded again
-uint64_t idx_signature(const uint32_t* idx, uint32_t n) {
-    uint64_t hsh = 0xcbf29ce484222325ULL ^ n;
-    const uint64_t* p8 = reinterpret_cast<const uint64_t*>(idx);
-    uint32_t i = 0;
-    if ((reinterpret_cast<uintptr_t>(idx) & 7u) == 0)
-        for (; i + 2 <= n; i += 2) hsh = (hsh ^ p8[i >> 1]) * 0x100000001b3ULL;
-    for (; i < n; i++) hsh = (hsh ^ idx[i]) * 0x100000001b3ULL;
-    return hsh | 1ull;  // never 0
 }
 
 int ensure_verb_stage(ngs_dealer* h, size_t n) {
@@ -771,13 +761,14 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
     const uint32_t gen = demand_generation(h, pd, lp.enabled != 0);
     uint64_t sig = 0;
     if (idx) {
-        sig = idx_signature(idx, n);
-        if (sig != h->idx_sig || n != h->idx_n) {  // a list the device does not hold yet
-            CU(h, cudaMemcpyAsync(h->d_idx, idx, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+        if (h->idx_sig == 0 || h->idx_host.size() != n || memcmp(h->idx_host.data(), idx, (size_t)n * 4) != 0) {
+            // a list the device does not hold yet
+            h->idx_host.assign(idx, idx + n);
+            CU(h, cudaMemcpyAsync(h->d_idx, h->idx_host.data(), (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
             h->stats.h2d_bytes += (size_t)n * 4;
-            h->idx_sig = sig;
-            h->idx_n = n;
+            h->idx_sig = h->idx_sig + 1 ? h->idx_sig + 1 : 1;
         }
+        sig = h->idx_sig;
     }
     // NodeInfo.Score right after NodeInfo.Assume: the filter call's scores are still in the staging area
     if (mode == MODE_SCORE && h->sc_valid && h->sc_gen == gen && h->sc_n == n && h->sc_sig == sig && h->sc_epoch == h->epoch) {

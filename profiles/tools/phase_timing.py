@@ -41,7 +41,7 @@ d.schedule_batch(pc[:P], nc[:P], pol[:P], load=load)
 d.schedule_batch(pc[P:], nc[P:], pol[P:], load=load)
 lib = ngs._abi.load()
 lib.ngs_debug_phases.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)]
-buf = np.zeros(4096 + 256 * 256 * 4, dtype=np.uint64)
+buf = np.zeros(4096 + 256 * 256 * 8, dtype=np.uint64)
 grid = C.c_uint32(0)
 assert lib.ngs_debug_phases(d._h, buf.ctypes.data_as(C.c_void_p), C.byref(grid)) == 0
 g = grid.value
