@@ -162,7 +162,7 @@ int ngs_bind(ngs_dealer *h, uint32_t idx, const int32_t *percent, int n_containe
  * [P][max_c]; node_out[p] = global node index or -1; gpu_idx_out [P][max_c] padded with INT32_MIN.
  * A call with ONE pod is the low-latency form: a single ordinary launch over the tables in place,
  * the answer polled from mapped host memory (sharded handles: every rank makes the same call and
- * gets the whole decision; the random policy on a sharded handle takes the batch path).
+ * gets the whole decision, every policy).
  * Two things a caller has to know about a batch:
  *  - load-aware mode: `load->now_ns` and the usage tables are read ONCE, when the launch starts
  *    (LoadUsage of every row is evaluated in the kernel's prologue).  The whole batch - up to

@@ -946,7 +946,7 @@ int ngs_schedule_batch(ngs_dealer* h, uint32_t n_pods, const int32_t* percent, c
     CU(h, cudaSetDevice(h->device));
     rc = ensure_batch(h);
     if (rc) return rc;
-    if (n_pods == 1 && (h->world <= 1 || policy[0] != NGS_POLICY_RANDOM)) {
+    if (n_pods == 1) {
         // one pod: K7, a single ordinary launch; the answer arrives in mapped host memory and the
         // status word behind it is polled, so the call returns without a stream synchronisation
         PodDemand pd;
@@ -972,7 +972,7 @@ int ngs_schedule_batch(ngs_dealer* h, uint32_t n_pods, const int32_t* percent, c
         }
         if (policy[0] == NGS_POLICY_RANDOM)
             k_schedule_one_random<<<grid, 256, 0, h->stream>>>(h->T, pd, seed + seq0, h->d_one, reinterpret_cast<uint32_t*>(h->d_one + 1),
-                                                               h->d_pod_out_dev, max_c);
+                                                               h->d_pod_out_dev, max_c, sh);
         else
             k_schedule_one<<<grid, 256, 0, h->stream>>>(h->T, pd, lp, h->d_one, h->d_pod_out_dev, max_c, sh);
         CU(h, cudaGetLastError());

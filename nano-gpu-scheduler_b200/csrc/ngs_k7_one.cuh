@@ -70,12 +70,17 @@ __device__ __forceinline__ bool sample_row_feasible(const Tables& T, uint32_t ro
 }
 
 // K7, random policy (see the file header).  cnt: [gridDim.x] feasible nodes per CTA range.
+// On a sharded handle the last CTA of every rank trades the rank's number of feasible nodes with the peers (the slot arrays
+// of K5); rank r's feasible nodes follow those of the ranks before it, so every rank knows which rank holds the seeded pick.
+// That rank binds it and drops node and plan into every peer's mailbox; the others wait for the mailbox.
 __global__ void __launch_bounds__(256, 4) k_schedule_one_random(Tables T, PodDemand pd, uint64_t seed_seq, OneRec* rec, uint32_t* cnt, int32_t* out,
-                                                                int max_c) {
+                                                                int max_c, OneShard sh) {
     __shared__ SortedDemand dem;
     __shared__ uint32_t s_warp[8];
     __shared__ int s_last;
     __shared__ uint32_t s_pick_cta, s_pick_off;
+    __shared__ unsigned long long s_total, s_before_rank;
+    __shared__ int s_status;
     const uint32_t tid = threadIdx.x;
     if (tid == 0) sort_demand(pd.percent, pd.n, pd.policy, &dem);
     __syncthreads();
@@ -113,13 +118,67 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one_random(Tables T, PodDem
     const uint32_t before = block_scan_256(part, s_warp, &feasible);
     int32_t* gout = out + 10;
     for (int k = (int)tid; k < max_c; k += 256) gout[k] = INT32_MIN;
-    if (feasible == 0) {
+    if (tid == 0) {
+        s_total = feasible;
+        s_before_rank = 0;
+        s_status = NGS_OK;
+    }
+    __syncthreads();
+    if (sh.world > 1) {
+        if (tid < 32) {  // warp 0: this rank's count to every rank (its own array included), all ranks' counts back
+            bool dead = false;
+            unsigned long long got = 0;
+            if (tid < sh.world) {
+                st_relaxed_sys_u64(sh.xs[tid] + sh.rank, (unsigned long long)feasible | KEY_VALID);
+                got = wait_valid(sh.xs[sh.rank] + tid, sh.err, dead);
+            }
+            dead = __any_sync(FULL, dead);
+            unsigned long long inc = got;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned long long t = __shfl_up_sync(FULL, inc, o);
+                if (tid >= (uint32_t)o) inc += t;
+            }
+            const unsigned long long tot = __shfl_sync(FULL, inc, 31);
+            const unsigned long long bef = __shfl_sync(FULL, inc - got, sh.rank);
+            if (tid == 0) {
+                s_total = dead ? 0ull : tot;
+                s_before_rank = bef;
+                if (dead) s_status = NGS_ERR_TIMEOUT;
+            }
+        }
+        __syncthreads();
+    }
+    const unsigned long long gtotal = s_total, before_rank = s_before_rank;
+    const unsigned long long gpick = gtotal ? splitmix64(seed_seq) % gtotal : 0ull;  // the gpick-th feasible node of the whole cluster
+    const bool pick_here = gtotal != 0 && gpick >= before_rank && gpick < before_rank + feasible;
+    if (gtotal == 0) {
         if (tid == 0) {
             out[8] = -1;
             out[9] = NGS_SCORE_MIN;
         }
+    } else if (!pick_here) {
+        // another rank holds the pick: node and plan arrive in the mailbox
+        if (tid == 0) {
+            bool dead = false;
+            const unsigned long long* mail = sh.xs[sh.rank] + XMAIL_OFFSET;
+            wait_valid(mail, sh.err, dead);
+            if (dead) {
+                s_status = NGS_ERR_TIMEOUT;
+                out[8] = -1;
+                out[9] = NGS_SCORE_MIN;
+            } else {
+                __threadfence_system();
+                for (int k = 0; k < max_c && k < NGS_MAX_CONTAINERS; k++) {
+                    const unsigned long long w = ld_relaxed_sys_u64(mail + 1 + k / 2);
+                    gout[k] = (int32_t)(uint32_t)((k & 1) ? (w >> 32) : w);
+                }
+                out[8] = (int32_t)(uint32_t)ld_relaxed_sys_u64(mail + 1 + NGS_MAX_CONTAINERS / 2);
+                out[9] = 100;
+            }
+        }
     } else {
-        const uint32_t pick = (uint32_t)(splitmix64(seed_seq) % feasible);  // the pick-th feasible node in index order
+        const uint32_t pick = (uint32_t)(gpick - before_rank);  // the pick-th feasible node of this rank, in index order
         if (pick >= before && pick < before + part) {
             uint32_t acc = before;
             for (uint32_t j = 0; j < gpt; j++) {
@@ -166,6 +225,23 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one_random(Tables T, PodDem
                 }
                 out[8] = (int32_t)(T.first + row);
                 out[9] = 100;  // SampleRater.Rate (rater.go:24-26)
+                if (sh.world > 1) {  // node and plan into every peer's mailbox, then (after a fence) the word that says so
+                    int32_t planv[NGS_MAX_CONTAINERS];
+                    for (int k = 0; k < NGS_MAX_CONTAINERS; k++) {
+                        const int e = (int)((emit >> (4 * k)) & 0xF);
+                        planv[k] = k < dem.C ? (e == 0xF ? NGS_NOT_NEED_GPU : e) : INT32_MIN;
+                    }
+                    for (uint32_t r = 0; r < sh.world; r++) {
+                        if (r == sh.rank) continue;
+                        unsigned long long* mail = sh.xs[r] + XMAIL_OFFSET;
+                        for (int w = 0; w < NGS_MAX_CONTAINERS / 2; w++)
+                            st_relaxed_sys_u64(mail + 1 + w, ((unsigned long long)(uint32_t)planv[2 * w + 1] << 32) | (uint32_t)planv[2 * w]);
+                        st_relaxed_sys_u64(mail + 1 + NGS_MAX_CONTAINERS / 2, (unsigned long long)(T.first + row));
+                    }
+                    __threadfence_system();
+                    for (uint32_t r = 0; r < sh.world; r++)
+                        if (r != sh.rank) st_relaxed_sys_u64(sh.xs[r] + XMAIL_OFFSET, KEY_VALID | 1ull);
+                }
                 break;
             }
         }
@@ -173,7 +249,7 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one_random(Tables T, PodDem
     __syncthreads();
     if (tid == 0) {
         __threadfence_system();
-        *reinterpret_cast<volatile int32_t*>(out) = NGS_OK;
+        *reinterpret_cast<volatile int32_t*>(out) = s_status;
     }
 }
 

@@ -53,9 +53,9 @@ class ShardedDealer:
         """every rank passes the same pods; returns the merged (node, score, gpu_idx) on every rank"""
         pc = np.ascontiguousarray(percent, dtype=np.int32)
         P, max_c = pc.shape
-        pol0 = int(np.asarray(policy).ravel()[0])
-        if P == 1 and pol0 != _abi.POLICY_RANDOM:
-            # one pod: the low-latency kernel trades keys and the plan across the ranks itself, no collective needed
+        if P == 1:
+            # one pod: the low-latency kernel trades keys (random policy: feasible counts) and the plan across the ranks
+            # itself, no collective needed
             return self.local.schedule_batch(pc, n_containers, policy, load=load, seed=seed, seq0=seq0)
         dev = torch.device("cuda", self.device)
         t_pc = torch.from_numpy(pc).to(dev)
