@@ -51,7 +51,7 @@ for r in rows:
 tot = sum(v[1] for v in agg.values())
 with open(os.path.join(OUT, "launch_list_summary.txt"), "w") as f:
     f.write("ncu --metrics gpu__time_duration.sum --clock-control none -c 200 : python bench.py --steps 2 --warmup 3 --pods-per-step 512 "
-            "--no-cpu-baseline --skip-e2e\n(cold-cache, serialised launches: compare shares, not absolutes)\n"
+            "--no-cpu-baseline --skip-e2e --skip-extras\n(cold-cache, serialised launches: compare shares, not absolutes)\n"
             "(a step = k_prep_demands + k_schedule; the k_schedule_one launches are the single-pod latency arm that runs after the timed steps,\n"
             " the fill kernels are the L2 flush between steps)\n")
     for k, v in sorted(agg.items(), key=lambda x: -x[1][1]):
