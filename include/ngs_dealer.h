@@ -24,9 +24,11 @@
 extern "C" {
 #endif
 
-#define NGS_ABI_VERSION 2u /* 2: ngs_load_ctx holds 8 periods; NGS_NODE_INVALID_POD */
+#define NGS_ABI_VERSION 3u /* 2: ngs_load_ctx holds 8 periods; NGS_NODE_INVALID_POD.  3: nodes of 9..12 GPUs (ngs_node_*_wide) */
 
-#define NGS_MAX_GPUS 8         /* GPUs per node handled by the kernels (row = 8 x int32 = 2 x int4) */
+#define NGS_MAX_GPUS 8         /* cells per row of the bulk arrays (row = 8 x int32 = 2 x int4): what a node usually has */
+#define NGS_MAX_GPUS_WIDE 12   /* most GPUs a node may have (Go sort.Sort's <=12-element regime, as for containers); cells
+                                * 8..11 travel through ngs_node_set_wide / ngs_node_get_wide */
 #define NGS_MAX_CONTAINERS 12  /* containers per pod (Go sort.Sort's <=12-element regime) */
 #define NGS_MAX_PERIODS 8      /* usable PolicySpec.SyncPeriod entries (the deployed policy has 2; more than 8 -> NGS_ERR_UNSUPPORTED) */
 #define NGS_MAX_FREE 65535     /* upper bound of a cell's free percent kept in the snapshot */
@@ -43,7 +45,7 @@ enum {
     NGS_ERR_INFEASIBLE = 4,   /* bind: "assume ... failed" (node.go:74-76) */
     NGS_ERR_APPLY = 5,        /* apply: "can't apply plan" (allocate.go:113) / index >= G (allocate.go:126) */
     NGS_ERR_RANGE = 6,        /* a cell would leave [0, NGS_MAX_FREE] */
-    NGS_ERR_UNSUPPORTED = 7,  /* gpu_count > NGS_MAX_GPUS, too many containers or periods */
+    NGS_ERR_UNSUPPORTED = 7,  /* gpu_count > NGS_MAX_GPUS_WIDE, too many containers or periods */
     NGS_ERR_TIMEOUT = 8,      /* the batch kernel gave up waiting for a peer (never expected) */
     NGS_ERR_NOALLOC_LIMIT = 9 /* ngs_schedule_batch_noalloc: batch or grid larger than its fixed scratch */
 };
@@ -104,6 +106,17 @@ int ngs_stats(ngs_dealer *h, ngs_stats_t *out);
 /* NewNodeInfo (node.go:25-42): gpu_count cells of (100,100,0); gpu_count from
  * capacity["nano-gpu/gpu-percent"]/100 (pkg/utils/node.go:8-14). */
 int ngs_node_upsert(ngs_dealer *h, uint32_t idx, int gpu_count);
+/* Nodes with 9..12 GPUs (the reference takes any count, pkg/utils/node.go:8-14; above 12 Go 1.16's sort.Sort leaves
+ * its insertion-sort regime and NGS_ERR_UNSUPPORTED comes back).  ngs_node_upsert registers them like any node;
+ * these two set / read one node of ANY width with all its cells: free[gpu_count] (NULL = all 100),
+ * remain_load[gpu_count] (NULL = 0) — the per-node form of ngs_snapshot_load / ngs_snapshot_read, whose
+ * [n][NGS_MAX_GPUS] arrays hold cells 0..7 only (ngs_snapshot_load refuses gpu_count > NGS_MAX_GPUS,
+ * ngs_snapshot_read returns such a node's gpu_count and its first eight cells).  Every verb (assume, score, bind,
+ * apply, release, load updates with card < 12) and the single-pod form of ngs_schedule_batch handle such nodes;
+ * the persistent batch kernel (n_pods > 1) keeps its rows 8 cells wide and answers NGS_ERR_UNSUPPORTED while the
+ * snapshot holds one. */
+int ngs_node_set_wide(ngs_dealer *h, uint32_t idx, int gpu_count, const int32_t *free, const int8_t *remain_load);
+int ngs_node_get_wide(ngs_dealer *h, uint32_t idx, int *gpu_count, int32_t *free, int8_t *remain_load); /* free / remain_load: [NGS_MAX_GPUS_WIDE] */
 /* bulk rebuild on start (dealer.go:58-72,279-299 replayed host-side, then one H2D copy).
  * free is [n][NGS_MAX_GPUS] (NULL = all 100), remain_load [n][NGS_MAX_GPUS] (NULL = 0). */
 int ngs_snapshot_load(ngs_dealer *h, uint32_t first, uint32_t n, const uint8_t *gpu_count, const int32_t *free,

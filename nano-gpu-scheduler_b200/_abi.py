@@ -10,6 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("NGS_DEALER_LIB") or os.path.join(HERE, "libngs_dealer.so")  # override: profiling builds
 
 MAX_GPUS = 8
+MAX_GPUS_WIDE = 12
 MAX_CONTAINERS = 12
 MAX_PERIODS = 8
 MAX_FREE = 65535
@@ -27,7 +28,7 @@ SYMBOLS = [
     "ngs_stats", "ngs_node_upsert", "ngs_snapshot_load", "ngs_snapshot_read", "ngs_node_apply", "ngs_release_batch", "ngs_load_add_node",
     "ngs_load_update", "ngs_load_update_bulk", "ngs_parse_usage", "ngs_parse_update_time", "ngs_assume", "ngs_assume_dev", "ngs_score",
     "ngs_bind", "ngs_schedule_batch", "ngs_schedule_batch_dev", "ngs_xchg_export", "ngs_xchg_attach",
-    "ngs_schedule_batch_noalloc",
+    "ngs_schedule_batch_noalloc", "ngs_node_set_wide", "ngs_node_get_wide",
 ]
 NOALLOC_MAX_PODS = 256
 NOALLOC_MAX_CTAS = 160
@@ -93,6 +94,8 @@ def load():
     L.ngs_sync.argtypes = [vp]
     L.ngs_stats.argtypes = [vp, C.POINTER(Stats)]
     L.ngs_node_upsert.argtypes = [vp, u32, ci]
+    L.ngs_node_set_wide.argtypes = [vp, u32, ci, vp, vp]
+    L.ngs_node_get_wide.argtypes = [vp, u32, C.POINTER(ci), vp, vp]
     L.ngs_snapshot_load.argtypes = [vp, u32, u32, vp, vp, vp]
     L.ngs_snapshot_read.argtypes = [vp, u32, u32, vp, vp, vp]
     L.ngs_node_apply.argtypes = [vp, u32, vp, vp, ci, ci]

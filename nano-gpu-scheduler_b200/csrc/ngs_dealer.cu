@@ -116,6 +116,9 @@ struct ngs_dealer {
     unsigned long long* d_xslots = nullptr;               // own buffer: [2 parities][BATCH_CHUNK][NGS_MAX_RANKS]
     unsigned long long* peer_xslots[NGS_MAX_RANKS] = {};  // peer-mapped bases (own entry = d_xslots)
     uint64_t xbatch = 0;                                  // launches so far: selects the parity half
+    // nodes with 9..12 GPUs (ngs_wide.cuh): which rows, so that the batch kernel can refuse them before it binds anything
+    std::vector<uint8_t> wide_row;
+    uint32_t n_wide = 0;
     ngs_stats_t stats{};
     unsigned long long* d_dbg = nullptr;  // profiling builds only
     uint32_t dbg_grid = 0;
@@ -320,6 +323,10 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
                     const LoadParams& lp, uint64_t seed_seq, int32_t* d_node, int32_t* d_score, int32_t* d_gidx,
                     int32_t* status_out = nullptr) {
     if (!h->coop) return fail(h, NGS_ERR_CUDA, "device lacks cooperative launch");
+    // (a sharded handle launches regardless — its peers are already waiting for it — and the kernel leaves such rows out)
+    if (h->n_wide && h->world == 1)
+        return fail(h, NGS_ERR_UNSUPPORTED, "the snapshot holds %u node(s) with more than NGS_MAX_GPUS GPUs: the batch kernel keeps 8 cells per row; "
+                                            "schedule through the verbs or one pod per call", h->n_wide);
     h->epoch++;  // the batch binds pods
     const uint32_t N = h->T.n;
     uint32_t grid = (N + 63) / 64;
@@ -398,12 +405,45 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     return NGS_OK;
 }
 
+// the second plane of the tables (cells 8..11), created when the first node with more than 8 GPUs arrives
+int ensure_wide(ngs_dealer* h) {
+    if (h->T.free_hi) return NGS_OK;
+    const size_t NP = h->T.nstride;
+    int32_t* fh = nullptr;
+    int8_t* rh = nullptr;
+    uint8_t* th = nullptr;
+    uint32_t* sh = nullptr;
+    if (cudaMalloc(&fh, NP * 4 * 4) != cudaSuccess || cudaMalloc(&rh, NP * 4) != cudaSuccess || cudaMalloc(&th, 2 * NP * 4) != cudaSuccess ||
+        cudaMalloc(&sh, 2 * NP * 4 * 4) != cudaSuccess) {
+        const cudaError_t e = cudaGetLastError();
+        cudaFree(fh); cudaFree(rh); cudaFree(th); cudaFree(sh);
+        return fail(h, NGS_ERR_CUDA, "tables for nodes of more than %d GPUs: %s", NGS_MAX_GPUS, cudaGetErrorString(e));
+    }
+    CU(h, cudaMemsetAsync(fh, 0, NP * 4 * 4, h->stream));
+    CU(h, cudaMemsetAsync(rh, 0, NP * 4, h->stream));
+    CU(h, cudaMemsetAsync(th, 0xFF, 2 * NP * 4, h->stream));
+    CU(h, cudaMemsetAsync(sh, 0, 2 * NP * 4 * 4, h->stream));
+    h->T.free_hi = fh;
+    h->T.rl_hi = rh;
+    h->T.tenths_hi = th;
+    h->T.ts_hi = sh;
+    h->wide_row.assign(h->T.n, 0);
+    return NGS_OK;
+}
+void mark_width(ngs_dealer* h, uint32_t row, int G) {
+    if (h->wide_row.empty()) return;
+    const uint8_t w = G > NGS_MAX_GPUS ? 1 : 0;
+    h->n_wide += (uint32_t)w - (uint32_t)h->wide_row[row];
+    h->wide_row[row] = w;
+}
+
 int check_dev_err(ngs_dealer* h) {
     if (*h->h_err != NGS_OK) {
         int e = *h->h_err;
         *h->h_err = NGS_OK;
         cudaMemsetAsync(h->d_err, 0, 8, h->stream);
         if (e == NGS_ERR_TIMEOUT) return fail(h, e, "batch kernel gave up waiting for a peer CTA (results of this batch are incomplete)");
+        if (e == NGS_ERR_UNSUPPORTED) return fail(h, e, "the batch kernel met a node with more than NGS_MAX_GPUS GPUs and left it out (schedule such snapshots through the verbs)");
         return fail(h, e, "a batch held a pod with a bad container count, percent or policy: that pod was left unscheduled "
                           "(node_out = NGS_NODE_INVALID_POD), every other pod was scheduled as usual");
     }
@@ -507,6 +547,7 @@ int ngs_destroy(ngs_dealer* h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     cudaFree(h->T.free); cudaFree(h->T.gcount); cudaFree(h->T.rl); cudaFree(h->T.tenths); cudaFree(h->T.ts);
     cudaFree(h->T.tag); cudaFree(h->T.cscore); cudaFree(const_cast<int16_t*>(h->T.blut));
+    cudaFree(h->T.free_hi); cudaFree(h->T.rl_hi); cudaFree(h->T.tenths_hi); cudaFree(h->T.ts_hi);
     cudaFree(h->d_idx); cudaFree(h->d_feas); cudaFree(h->d_reason); cudaFree(h->d_score); cudaFree(h->d_plan); cudaFree(h->d_nem);
     cudaFreeHost(h->h_bind); cudaFree(h->d_small); cudaFreeHost(h->h_small);
     cudaFreeHost(h->h_vfeas); cudaFreeHost(h->h_vreason); cudaFreeHost(h->h_vscore); cudaFreeHost(h->h_vflag); cudaFree(h->d_vticket);
@@ -553,12 +594,80 @@ int ngs_node_upsert(ngs_dealer* h, uint32_t idx, int gpu_count) {
     if (!h) return NGS_ERR_INVALID;
     if (idx < h->T.first || idx - h->T.first >= h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "node %u outside this shard", idx);
     if (gpu_count < 0) return fail(h, NGS_ERR_INVALID, "gpu_count %d", gpu_count);
-    if (gpu_count > NGS_MAX_GPUS) return fail(h, NGS_ERR_UNSUPPORTED, "gpu_count %d > NGS_MAX_GPUS", gpu_count);
+    if (gpu_count > NGS_MAX_GPUS_WIDE) return fail(h, NGS_ERR_UNSUPPORTED, "gpu_count %d > NGS_MAX_GPUS_WIDE", gpu_count);
     CU(h, cudaSetDevice(h->device));
+    if (gpu_count > NGS_MAX_GPUS) {
+        const int rc = ensure_wide(h);
+        if (rc) return rc;
+    }
+    mark_width(h, idx - h->T.first, gpu_count);
     h->epoch++;
     k_upsert<<<1, 32, 0, h->stream>>>(h->T, idx - h->T.first, gpu_count);
     CU(h, cudaGetLastError());
     h->stats.kernel_launches++;
+    return NGS_OK;
+}
+
+int ngs_node_set_wide(ngs_dealer* h, uint32_t idx, int gpu_count, const int32_t* free, const int8_t* remain_load) {
+    if (!h) return NGS_ERR_INVALID;
+    if (idx < h->T.first || idx - h->T.first >= h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "node %u outside this shard", idx);
+    if (gpu_count < 0) return fail(h, NGS_ERR_INVALID, "gpu_count %d", gpu_count);
+    if (gpu_count > NGS_MAX_GPUS_WIDE) return fail(h, NGS_ERR_UNSUPPORTED, "gpu_count %d > NGS_MAX_GPUS_WIDE", gpu_count);
+    int32_t fr[NGS_MAX_GPUS_WIDE];
+    int8_t rl[NGS_MAX_GPUS_WIDE];
+    for (int g = 0; g < NGS_MAX_GPUS_WIDE; g++) {
+        fr[g] = g < gpu_count ? (free ? free[g] : 100) : 0;
+        if (fr[g] < 0 || fr[g] > NGS_MAX_FREE) return fail(h, NGS_ERR_RANGE, "node %u cell %d: free %d out of range", idx, g, fr[g]);
+        const int r = (g < gpu_count && remain_load) ? remain_load[g] : 0;
+        if (r < -2 || r > 2) return fail(h, NGS_ERR_RANGE, "node %u cell %d: remain_load %d out of range", idx, g, r);
+        rl[g] = (int8_t)r;
+    }
+    CU(h, cudaSetDevice(h->device));
+    if (gpu_count > NGS_MAX_GPUS) {
+        const int rc = ensure_wide(h);
+        if (rc) return rc;
+    }
+    const uint32_t row = idx - h->T.first;
+    mark_width(h, row, gpu_count);
+    h->epoch++;
+    if (remain_load) h->T.rl_zero = 0;
+    const uint8_t G8 = (uint8_t)gpu_count;
+    // (pageable sources: the copies have left the host buffers when the calls return)
+    CU(h, cudaMemcpyAsync(h->T.free + (size_t)row * 8, fr, 32, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(h->T.rl + (size_t)row * 8, rl, 8, cudaMemcpyHostToDevice, h->stream));
+    if (h->T.free_hi) {
+        CU(h, cudaMemcpyAsync(h->T.free_hi + (size_t)row * 4, fr + 8, 16, cudaMemcpyHostToDevice, h->stream));
+        CU(h, cudaMemcpyAsync(h->T.rl_hi + (size_t)row * 4, rl + 8, 4, cudaMemcpyHostToDevice, h->stream));
+    }
+    CU(h, cudaMemcpyAsync(h->T.gcount + row, &G8, 1, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemsetAsync(h->T.tag + row, 0, 4, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    h->stats.h2d_bytes += 61;
+    return NGS_OK;
+}
+
+int ngs_node_get_wide(ngs_dealer* h, uint32_t idx, int* gpu_count, int32_t* free, int8_t* remain_load) {
+    if (!h) return NGS_ERR_INVALID;
+    if (idx < h->T.first || idx - h->T.first >= h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "node %u outside this shard", idx);
+    const uint32_t row = idx - h->T.first;
+    CU(h, cudaSetDevice(h->device));
+    uint8_t G8 = 0;
+    int32_t fr[NGS_MAX_GPUS_WIDE] = {0};
+    int8_t rl[NGS_MAX_GPUS_WIDE] = {0};
+    CU(h, cudaMemcpyAsync(&G8, h->T.gcount + row, 1, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaMemcpyAsync(fr, h->T.free + (size_t)row * 8, 32, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaMemcpyAsync(rl, h->T.rl + (size_t)row * 8, 8, cudaMemcpyDeviceToHost, h->stream));
+    if (h->T.free_hi) {
+        CU(h, cudaMemcpyAsync(fr + 8, h->T.free_hi + (size_t)row * 4, 16, cudaMemcpyDeviceToHost, h->stream));
+        CU(h, cudaMemcpyAsync(rl + 8, h->T.rl_hi + (size_t)row * 4, 4, cudaMemcpyDeviceToHost, h->stream));
+    }
+    CU(h, cudaStreamSynchronize(h->stream));
+    h->stats.d2h_bytes += 61;
+    if (gpu_count) *gpu_count = G8;
+    for (int g = 0; g < NGS_MAX_GPUS_WIDE; g++) {
+        if (free) free[g] = g < (int)G8 ? fr[g] : 0;
+        if (remain_load) remain_load[g] = g < (int)G8 ? rl[g] : 0;
+    }
     return NGS_OK;
 }
 
@@ -571,7 +680,7 @@ int ngs_snapshot_load(ngs_dealer* h, uint32_t first, uint32_t n, const uint8_t* 
     std::vector<int8_t> rl((size_t)n * 8, 0);
     for (uint32_t i = 0; i < n; i++) {
         const int G = gpu_count[i];
-        if (G > NGS_MAX_GPUS) return fail(h, NGS_ERR_UNSUPPORTED, "row %u: gpu_count %d > NGS_MAX_GPUS", first + i, G);
+        if (G > NGS_MAX_GPUS) return fail(h, NGS_ERR_UNSUPPORTED, "row %u: gpu_count %d > NGS_MAX_GPUS (a node that wide goes through ngs_node_set_wide)", first + i, G);
         for (int g = 0; g < 8; g++) {
             int32_t v = g < G ? (free ? free[(size_t)i * 8 + g] : 100) : 0;
             if (v < 0 || v > NGS_MAX_FREE) return fail(h, NGS_ERR_RANGE, "row %u cell %d: free %d out of range", first + i, g, v);
@@ -583,6 +692,7 @@ int ngs_snapshot_load(ngs_dealer* h, uint32_t first, uint32_t n, const uint8_t* 
     }
     CU(h, cudaSetDevice(h->device));
     h->epoch++;
+    for (uint32_t i = 0; i < n && h->n_wide; i++) mark_width(h, r0 + i, gpu_count[i]);
     CU(h, cudaMemcpyAsync(h->T.free + (size_t)r0 * 8, fr.data(), fr.size() * 4, cudaMemcpyHostToDevice, h->stream));
     if (remain_load) h->T.rl_zero = 0;
     CU(h, cudaMemcpyAsync(h->T.rl + (size_t)r0 * 8, rl.data(), rl.size(), cudaMemcpyHostToDevice, h->stream));
@@ -690,8 +800,12 @@ int ngs_load_update(ngs_dealer* h, uint32_t idx, int metric, int card, double va
     if (!h || metric < 0 || metric > 1) return NGS_ERR_INVALID;
     if (idx < h->T.first || idx - h->T.first >= h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "node %u outside this shard", idx);
     if (card < 0) return fail(h, NGS_ERR_INVALID, "card %d", card);
-    if (card >= NGS_MAX_GPUS) return NGS_OK;  // a card the kernels never look at (LoadUsage walks gpus only)
+    if (card >= NGS_MAX_GPUS_WIDE) return NGS_OK;  // a card the kernels never look at (LoadUsage walks gpus only)
     CU(h, cudaSetDevice(h->device));
+    if (card >= NGS_MAX_GPUS) {  // (an entry may arrive before its node does: nodeusage.go keeps them apart, too)
+        const int rc = ensure_wide(h);
+        if (rc) return rc;
+    }
     const uint8_t t10 = encode_tenths(value, value_ok, ts_sec, ts_ok);
     k_load_update<<<1, 32, 0, h->stream>>>(h->T, idx - h->T.first, metric, card, t10, t10 == 255 ? 0u : (uint32_t)ts_sec);
     CU(h, cudaGetLastError());

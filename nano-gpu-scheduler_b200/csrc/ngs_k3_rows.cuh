@@ -41,10 +41,9 @@ __global__ void k_bind(Tables T, uint32_t gidx, PodDemand pd, LoadParams lp, uin
     }
     int32_t planv[NGS_MAX_CONTAINERS];
     write_plan(planv, &dem, dem.policy != NGS_POLICY_RANDOM, true, ev.emit, ev.n_emit);
-    int32_t* f = T.free + (size_t)row * 8;
     for (int k = 0; k < pd.n; k++) {  // GPUs.Allocate (allocate.go:102-118); the plan fits by construction
         res->gpu_idx[k] = planv[k];
-        if (planv[k] >= 0) f[planv[k]] -= pd.percent[k];
+        if (planv[k] >= 0) *wide_free_cell(T, row, planv[k]) -= pd.percent[k];
     }
     res->score = hit ? T.cscore[row] : ev.score;
     T.tag[row] = 0;  // node.go:82
@@ -59,10 +58,9 @@ __global__ void k_apply(Tables T, uint32_t gidx, PodDemand pd, const int32_t* __
         *status = NGS_ERR_UNKNOWN_NODE;
         return;
     }
-    const int G = T.gcount[row];
-    int32_t* fp = T.free + (size_t)row * 8;
-    int f[8];
-    for (int g = 0; g < 8; g++) f[g] = fp[g];
+    const int G = min((int)T.gcount[row], WIDE_MAX);
+    int f[WIDE_MAX];
+    for (int g = 0; g < G; g++) f[g] = *wide_free_cell(T, row, g);
     T.tag[row] = 0;  // node.go:87,92: cleanPlan runs before the apply, whatever its outcome
     int rc = NGS_OK;
     if (sign > 0) {
@@ -76,7 +74,7 @@ __global__ void k_apply(Tables T, uint32_t gidx, PodDemand pd, const int32_t* __
             f[gi] -= pd.percent[k];
         }
         if (rc == NGS_OK)
-            for (int g = 0; g < 8; g++) fp[g] = f[g];
+            for (int g = 0; g < G; g++) *wide_free_cell(T, row, g) = f[g];
     } else {
         for (int k = 0; k < pd.n; k++) {
             const int gi = gpu_idx_in[k];
@@ -92,7 +90,7 @@ __global__ void k_apply(Tables T, uint32_t gidx, PodDemand pd, const int32_t* __
             f[gi] += pd.percent[k];
         }
         if (rc != NGS_ERR_RANGE)
-            for (int g = 0; g < 8; g++) fp[g] = f[g];
+            for (int g = 0; g < G; g++) *wide_free_cell(T, row, g) = f[g];
     }
     *status = rc;
 }
@@ -126,9 +124,10 @@ __global__ void k_release_batch(Tables T, uint32_t n, const uint32_t* __restrict
                 rc = NGS_ERR_INVALID;
                 break;
             }
-            const int old = atomicAdd(&T.free[(size_t)row * 8 + gi], pc);
+            int32_t* cell = wide_free_cell(T, row, gi);
+            const int old = atomicAdd(cell, pc);
             if (old + pc > NGS_MAX_FREE) {  // keep cells inside what the kernels can hold
-                atomicSub(&T.free[(size_t)row * 8 + gi], pc);
+                atomicSub(cell, pc);
                 rc = NGS_ERR_RANGE;
                 break;
             }
@@ -145,20 +144,30 @@ __global__ void k_upsert(Tables T, uint32_t row, int G) {
         T.free[(size_t)row * 8 + g] = g < G ? 100 : 0;
         T.rl[(size_t)row * 8 + g] = 0;
     }
+    if (T.free_hi)
+        for (int g = 8; g < WIDE_MAX; g++) {
+            T.free_hi[(size_t)row * 4 + g - 8] = g < G ? 100 : 0;
+            T.rl_hi[(size_t)row * 4 + g - 8] = 0;
+        }
     T.tag[row] = 0;
 }
 
 // K4.  Update{Core,Memory}Usage (nodeusage.go:70-80) on one cell / Add*Usage (nodeusage.go:58-68)
 __global__ void k_load_update(Tables T, uint32_t row, int metric, int card, uint8_t tenths, uint32_t ts) {
     if (threadIdx.x != 0) return;
-    const size_t off = ((size_t)metric * T.nstride + row) * 8 + card;
-    T.tenths[off] = tenths;
-    T.ts[off] = ts;
+    bool hi;
+    const size_t off = wide_usage_off(T, row, metric, card, &hi);
+    (hi ? T.tenths_hi : T.tenths)[off] = tenths;
+    (hi ? T.ts_hi : T.ts)[off] = ts;
 }
 __global__ void k_load_add_node(Tables T, uint32_t row, int metric) {
     const size_t off = ((size_t)metric * T.nstride + row) * 8 + threadIdx.x;
     if (threadIdx.x < 8) {
         T.tenths[off] = 255;
         T.ts[off] = 0;
+    } else if (threadIdx.x < WIDE_MAX && T.tenths_hi) {
+        const size_t off_hi = ((size_t)metric * T.nstride + row) * 4 + threadIdx.x - 8;
+        T.tenths_hi[off_hi] = 255;
+        T.ts_hi[off_hi] = 0;
     }
 }

@@ -593,7 +593,11 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     // ---- prologue: rows -> shared memory (and the load-aware quantities, frozen for the batch) ----
     for (uint32_t r = tid; r < my_rows; r += blockDim.x) {
         const uint32_t row = row0 + r;
-        const int G = T.gcount[row];
+        int G = T.gcount[row];
+        if (G > 8) {  // 9..12 GPUs (ngs_wide.cuh): the rows of this kernel are 8 cells wide.  The host refuses such
+            G = 0;    // snapshots before the launch; a caller-owned view gets the status and the node left out
+            atomicMax(bp.err, NGS_ERR_UNSUPPORTED);
+        }
         int f[8];
         const int4 a = ld_row4(T.free + (size_t)row * 8), b = ld_row4(T.free + (size_t)row * 8 + 4);
         f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w;

@@ -61,6 +61,13 @@ __device__ __forceinline__ uint32_t block_scan_256(uint32_t v, uint32_t* s_warp 
 __device__ __forceinline__ bool sample_row_feasible(const Tables& T, uint32_t row, const SortedDemand* dem) {
     const int G = T.gcount[row];
     if (G == 0) return false;
+    if (G > 8) {  // ngs_wide.cuh
+        LoadParams off;
+        off.enabled = 0;
+        RowEval ev;
+        eval_wide_row(T, row, dem, off, false, &ev, nullptr);
+        return ev.feasible;
+    }
     uint32_t v[8];
     ld_row8(T.free + (size_t)row * 8, v);
     int f[8];
@@ -207,17 +214,28 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one_random(Tables T, PodDem
                 if (left-- != 0) continue;
                 // NodeInfo.Bind (node.go:70-84) with SampleRater.Choose (rater.go:28-50)
                 const int G = T.gcount[row];
-                uint32_t v[8];
-                ld_row8(T.free + (size_t)row * 8, v);
-                int f[8];
-#pragma unroll
-                for (int g = 0; g < 8; g++) f[g] = (int)v[g];
                 uint64_t emit = 0;
                 int n_emit = 0;
-                choose_sample<true>(f, G, &dem, &emit, &n_emit);  // places on f
-                int4* gp = reinterpret_cast<int4*>(T.free + (size_t)row * 8);
-                gp[0] = make_int4(f[0], f[1], f[2], f[3]);
-                gp[1] = make_int4(f[4], f[5], f[6], f[7]);
+                if (G > 8) {  // ngs_wide.cuh
+                    LoadParams off;
+                    off.enabled = 0;
+                    RowEval ev;
+                    int placed[WIDE_MAX];
+                    eval_wide_row(T, row, &dem, off, false, &ev, placed);
+                    wide_store_free(T, row, placed);
+                    emit = ev.emit;
+                    n_emit = ev.n_emit;
+                } else {
+                    uint32_t v[8];
+                    ld_row8(T.free + (size_t)row * 8, v);
+                    int f[8];
+#pragma unroll
+                    for (int g = 0; g < 8; g++) f[g] = (int)v[g];
+                    choose_sample<true>(f, G, &dem, &emit, &n_emit);  // places on f
+                    int4* gp = reinterpret_cast<int4*>(T.free + (size_t)row * 8);
+                    gp[0] = make_int4(f[0], f[1], f[2], f[3]);
+                    gp[1] = make_int4(f[4], f[5], f[6], f[7]);
+                }
                 T.tag[row] = 0;
                 for (int k = 0; k < dem.C; k++) {
                     const int e = (int)((emit >> (4 * k)) & 0xF);
@@ -336,9 +354,22 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd,
         const int rlc = (int)__ldcg(T.rl + (size_t)wrow * 8 + g) + 2;
         uint64_t emit = 0;
         int n_emit = 0, fr = 0;
-        choose_group8<true>(g, gbase, cell, rlc, g < G, dem.policy == NGS_POLICY_SPREAD, &dem, &emit, &n_emit, &fr);
+        if (G > 8) {  // ngs_wide.cuh: lane 0 plans and places, the plan goes to the other lanes
+            if (lane == 0) {
+                LoadParams off;
+                off.enabled = 0;  // (the plan is derived from the RemainLoad the scan left behind, as below)
+                RowEval ev;
+                int placed[WIDE_MAX];
+                eval_wide_row(T, wrow, &dem, off, false, &ev, placed);
+                wide_store_free(T, wrow, placed);
+                emit = ev.emit;
+            }
+            emit = __shfl_sync(FULL, emit, 0);
+        } else {
+            choose_group8<true>(g, gbase, cell, rlc, g < G, dem.policy == NGS_POLICY_SPREAD, &dem, &emit, &n_emit, &fr);
+        }
         if (lane < 8) {
-            if (g < G) T.free[(size_t)wrow * 8 + lane] = fr;  // GPUs.Allocate (allocate.go:102-118)
+            if (g < G && G <= 8) T.free[(size_t)wrow * 8 + lane] = fr;  // GPUs.Allocate (allocate.go:102-118)
             for (int k = (int)lane; k < dem.C; k += 8) {      // rater.go:102-105: un-permute the emission order
                 const int e = (int)((emit >> (4 * k)) & 0xF);
                 s_plan[dem.order[k]] = e == 0xF ? NGS_NOT_NEED_GPU : e;

@@ -3,28 +3,8 @@
 // Included by ngs_dealer.cu inside its anonymous namespace.
 #pragma once
 
-struct Tables {
-    int32_t* free;
-    uint8_t* gcount;
-    int8_t* rl;
-    uint8_t* tenths;
-    uint32_t* ts;
-    uint32_t* tag;
-    int32_t* cscore;
-    const int16_t* blut;  // Binpack.Rate percent table [9][801] (nullptr: compute in fp64)
-    uint32_t rl_zero;     // the rl table is known to hold only zeros (no load-aware pass ran yet): skip reading it
-    uint32_t nstride;  // rows per metric plane of tenths / ts (>= n; padded so that every plane is 256-row aligned)
-    uint32_t n;      // rows in this shard
-    uint32_t first;  // global node index of row 0
-};
-
-struct RowEval {
-    bool known;
-    bool feasible;
-    int score;
-    uint64_t emit;
-    int n_emit;
-};
+#include "ngs_tables.cuh"
+#include "ngs_wide.cuh"
 
 __device__ __forceinline__ int4 ld_row4(const int32_t* p) { return __ldcg(reinterpret_cast<const int4*>(p)); }
 // one 256-bit load per 32-byte row (LDG.E.256 on sm_100a): every sector a warp touches is fully used
@@ -82,6 +62,10 @@ __device__ __forceinline__ RowEval eval_row_values(const Tables& T, uint32_t row
     const uint32_t (&ts)[2][8] = in.ts;
     const uint2 r8 = in.r8;
     if (G == 0) return ev;
+    if (G > 8) {  // 9..12 GPUs: the row's cells are not all in `in` (ngs_wide.cuh)
+        eval_wide_row(T, row, dem, lp, do_rate, &ev, nullptr);
+        return ev;
+    }
     ev.known = true;
     int f[8];
 #pragma unroll

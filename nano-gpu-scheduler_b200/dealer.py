@@ -7,7 +7,7 @@ import ctypes as C
 import numpy as np
 
 from . import _abi
-from ._abi import (INT32_MIN, MAX_CONTAINERS, MAX_GPUS, METRIC_CORE, METRIC_MEMORY, POLICY_BINPACK,  # noqa: F401
+from ._abi import (INT32_MIN, MAX_CONTAINERS, MAX_GPUS, MAX_GPUS_WIDE, METRIC_CORE, METRIC_MEMORY, POLICY_BINPACK,  # noqa: F401
                    POLICY_RANDOM, POLICY_SPREAD, LoadCtx, Stats)
 
 
@@ -90,6 +90,22 @@ class GpuDealer:
     # -- snapshot ---------------------------------------------------------------------------
     def node_upsert(self, idx, gpu_count):
         self._check(self._lib.ngs_node_upsert(self._h, idx, gpu_count))
+
+    def node_set_wide(self, idx, gpu_count, free=None, remain_load=None):
+        """one node of any width (up to MAX_GPUS_WIDE GPUs) with all its cells"""
+        fr = None if free is None else np.ascontiguousarray(free, dtype=np.int32)
+        rl = None if remain_load is None else np.ascontiguousarray(remain_load, dtype=np.int8)
+        for a in (fr, rl):
+            if a is not None and len(a) < gpu_count:
+                raise ValueError("node_set_wide: fewer cells than gpu_count")
+        self._check(self._lib.ngs_node_set_wide(self._h, idx, gpu_count, _p(fr), _p(rl)))
+
+    def node_get_wide(self, idx):
+        g = C.c_int(0)
+        fr = np.zeros(MAX_GPUS_WIDE, dtype=np.int32)
+        rl = np.zeros(MAX_GPUS_WIDE, dtype=np.int8)
+        self._check(self._lib.ngs_node_get_wide(self._h, idx, C.byref(g), _p(fr), _p(rl)))
+        return g.value, fr, rl
 
     def snapshot_load(self, gpu_count, free=None, remain_load=None, first=None):
         gc = np.ascontiguousarray(gpu_count, dtype=np.uint8)

@@ -12,6 +12,10 @@
 
 using namespace ngs;
 
+// the one-thread evaluation of nodes with 9..12 GPUs, as the kernels include it
+#include "../../nano-gpu-scheduler_b200/csrc/ngs_tables.cuh"
+#include "../../nano-gpu-scheduler_b200/csrc/ngs_wide.cuh"
+
 extern "C" {
 
 // GPUs.Choose for one row as the per-thread kernels evaluate it: Rate (fp64, no table), the exact plan search
@@ -47,6 +51,58 @@ void doh_eval_row(const int32_t* free, int G, const int8_t* rl, const int32_t* p
     out[0] = ok ? 1 : 0;
     out[2] = n_emit;
     write_plan(plan, &dem, policy != NGS_POLICY_RANDOM, ok, emit, n_emit);
+}
+
+// GPUs.Choose on one node of up to 12 GPUs through ngs_wide.cuh, on one-row tables built here.
+//   tenths / ts: [2][12] usage cells per metric (nullptr: load scheduling off); rl in: the RemainLoad the row holds
+//   out[0] feasible  out[1] score  out[2] n_emit; plan[C] as doh_eval_row; free_after[12] / rl_after[12]: the row after the call
+//   (free_after = the plan applied when feasible)
+void doh_eval_wide_row(const int32_t* free, int G, const int8_t* rl, const int32_t* percent, int C, int policy, const uint8_t* tenths,
+                       const uint32_t* ts, int n_periods, const int32_t* metric, const uint32_t* min_ts, const uint32_t* never, int do_rate,
+                       int32_t* out, int32_t* plan, int32_t* free_after, int8_t* rl_after) {
+    SortedDemand dem;
+    sort_demand(percent, C, policy, &dem);
+    int32_t f_lo[8] = {0}, f_hi[4] = {0};
+    int8_t r_lo[8] = {0}, r_hi[4] = {0};
+    uint8_t t_lo[2 * 8], t_hi[2 * 4];
+    uint32_t s_lo[2 * 8], s_hi[2 * 4];
+    for (int g = 0; g < G; g++) {
+        (g < 8 ? f_lo[g] : f_hi[g - 8]) = free[g];
+        (g < 8 ? r_lo[g] : r_hi[g - 8]) = rl ? rl[g] : 0;
+    }
+    for (int m = 0; m < 2; m++)
+        for (int g = 0; g < 12; g++) {
+            (g < 8 ? t_lo[m * 8 + g] : t_hi[m * 4 + g - 8]) = tenths ? tenths[m * 12 + g] : 255;
+            (g < 8 ? s_lo[m * 8 + g] : s_hi[m * 4 + g - 8]) = ts ? ts[m * 12 + g] : 0;
+        }
+    uint8_t gc = (uint8_t)G;
+    Tables T;
+    memset(&T, 0, sizeof(T));
+    T.free = f_lo; T.free_hi = f_hi; T.rl = r_lo; T.rl_hi = r_hi; T.tenths = t_lo; T.tenths_hi = t_hi; T.ts = s_lo; T.ts_hi = s_hi;
+    T.gcount = &gc;
+    T.nstride = 1;
+    T.n = 1;
+    LoadParams lp;
+    memset(&lp, 0, sizeof(lp));
+    lp.enabled = tenths != nullptr;
+    lp.n_periods = n_periods;
+    for (int e = 0; e < n_periods; e++) {
+        lp.metric[e] = metric[e];
+        lp.min_ts[e] = min_ts[e];
+        lp.never[e] = never[e];
+    }
+    RowEval ev;
+    int placed[WIDE_MAX] = {0};
+    eval_wide_row(T, 0, &dem, lp, do_rate != 0, &ev, placed);
+    if (ev.feasible) wide_store_free(T, 0, placed);
+    out[0] = ev.feasible;
+    out[1] = ev.score;
+    out[2] = ev.n_emit;
+    write_plan(plan, &dem, policy != NGS_POLICY_RANDOM, ev.feasible, ev.emit, ev.n_emit);
+    for (int g = 0; g < 12; g++) {
+        free_after[g] = g < 8 ? f_lo[g] : f_hi[g - 8];
+        rl_after[g] = g < 8 ? r_lo[g] : r_hi[g - 8];
+    }
 }
 
 // feasibility only, through the variant the streaming scan uses (no plan: early exit, no sort for the last container)

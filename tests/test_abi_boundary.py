@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol(built):
     for s in syms:
         assert hasattr(lib, s), s
     assert sorted(ngs._abi.SYMBOLS) == syms
-    assert lib.ngs_abi_version() == 2
+    assert lib.ngs_abi_version() == 3
 
 
 def test_no_torch_or_oracle_in_the_product_library(built):

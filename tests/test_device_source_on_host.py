@@ -19,7 +19,8 @@ import oracle as o
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "host", "device_on_host.cpp")
 LIB = os.path.join(HERE, "host", "libdevice_on_host.so")
-HDR = os.path.join(HERE, "..", "nano-gpu-scheduler_b200", "csrc", "ngs_device.cuh")
+CSRC = os.path.join(HERE, "..", "nano-gpu-scheduler_b200", "csrc")
+HDRS = [os.path.join(CSRC, f) for f in ("ngs_device.cuh", "ngs_tables.cuh", "ngs_wide.cuh")]
 INT32_MIN = -(2**31)
 FEAS_NO, FEAS_YES, FEAS_UNDECIDED, FEAS_FALLBACK = 0, 1, 2, 3
 
@@ -29,7 +30,7 @@ def doh():
     cuda_inc = "/usr/local/cuda/include"
     if not os.path.isdir(cuda_inc):
         pytest.skip("no CUDA headers")
-    if not os.path.exists(LIB) or max(os.path.getmtime(SRC), os.path.getmtime(HDR)) > os.path.getmtime(LIB):
+    if not os.path.exists(LIB) or max(os.path.getmtime(f) for f in [SRC] + HDRS) > os.path.getmtime(LIB):
         cxx = shutil.which("g++") or "g++"
         # -ffp-contract=off: the fp64 sequence must stay add / mul / div in IEEE round-to-nearest, as on the device
         res = subprocess.run([cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-I", cuda_inc, "-o", LIB, SRC],
@@ -339,3 +340,81 @@ def test_position_free_greedy_search_matches_oracle(doh, spread):
                     want = sorted(zip(after.tolist(), rl[r, :g].tolist()))
                     assert got == want, (trial, r, free[r, :g], rl[r, :g], demand, idx)
     assert n_amb < 0.2 * n_tot  # the fast path has to be the common one
+
+
+# ---- nodes with 9..12 GPUs: the one-thread evaluation of ngs_wide.cuh --------------------------------------------
+def eval_wide(L, free, rl, demand, policy, usage=None, periods=(), do_rate=True):
+    G = len(free)
+    f = np.ascontiguousarray(free, dtype=np.int32)
+    r = np.ascontiguousarray(rl, dtype=np.int8)
+    d = np.ascontiguousarray(demand, dtype=np.int32)
+    out = np.zeros(3, dtype=np.int32)
+    plan = np.full(max(len(d), 1), INT32_MIN, dtype=np.int32)
+    fa = np.zeros(12, dtype=np.int32)
+    ra = np.zeros(12, dtype=np.int8)
+    metric = np.array([p[0] for p in periods] + [0] * 8, dtype=np.int32)
+    min_ts = np.array([p[1] for p in periods] + [0] * 8, dtype=np.uint32)
+    never = np.array([p[2] for p in periods] + [0] * 8, dtype=np.uint32)
+    tenths, ts = (None, None) if usage is None else usage
+    L.doh_eval_wide_row(_p(f), G, _p(r), _p(d), len(d), policy, None if tenths is None else _p(tenths), None if ts is None else _p(ts),
+                        len(periods), _p(metric), _p(min_ts), _p(never), int(do_rate), _p(out), _p(plan), _p(fa), _p(ra))
+    return dict(ok=bool(out[0]), score=int(out[1]), ne=int(out[2]), plan=plan[: len(d)].tolist(), free_after=fa[:G].tolist(), rl_after=ra[:G].tolist())
+
+
+@pytest.mark.parametrize("policy", [o.POLICY_BINPACK, o.POLICY_SPREAD, o.POLICY_RANDOM])
+def test_wide_row_evaluation_matches_oracle(doh, policy):
+    """G = 1..12 (the function is written for any width; the kernels send it rows of 9..12)"""
+    rng = np.random.default_rng(4000 + policy)
+    for trial in range(20000):
+        G = int(rng.integers(1, 13)) if trial % 4 else int(rng.integers(9, 13))
+        if trial % 5 == 0:
+            free = rng.choice([0, 5, 20, 50, 99, 100, 101, 255, 300, 65535], size=G)
+            demand = rng.choice([0, 5, 50, 100, 101, 255, 300, 65535], size=int(rng.integers(0, 13)))
+        else:
+            free = rng.integers(0, 21, G) * 5
+            demand = rng.integers(0, 15, int(rng.integers(1, 13 if trial % 3 == 0 else 7))) * 5
+        rl = rng.integers(-2, 3, G) if rng.random() < 0.5 else np.zeros(G, dtype=np.int64)
+        got = eval_wide(doh, free, rl, demand, policy)
+        ok, idx, ne = o.choose(policy, free.astype(np.int64), demand.astype(np.int32), rl=rl.astype(np.int64))
+        assert got["ok"] == ok, (trial, free, rl, demand)
+        if ok:
+            assert got["plan"] == idx, (trial, free, rl, demand)
+            after = free.astype(np.int64).copy()
+            for k, gi in enumerate(idx):
+                if gi >= 0:
+                    after[gi] -= demand[k]
+            assert got["free_after"] == after.tolist()
+        elif policy != o.POLICY_RANDOM:
+            assert got["ne"] == ne and got["plan"][:ne] == idx[:ne], (trial, free, rl, demand)
+        assert got["score"] == o.rate(policy, free.astype(np.int64)), (trial, free)
+        assert got["rl_after"] == rl.tolist()  # no load-aware pass: RemainLoad untouched
+
+
+def test_wide_row_load_usage_matches_python_and_oracle_rate(doh):
+    rng = np.random.default_rng(77)
+    for trial in range(6000):
+        G = int(rng.integers(1, 13))
+        tenths = rng.choice(np.arange(0, 11).tolist() + [255], size=(2, 12)).astype(np.uint8)
+        ts = rng.integers(90, 111, size=(2, 12)).astype(np.uint32)
+        n = 2 if trial % 2 == 0 else int(rng.integers(0, 6))
+        periods = [(int(rng.integers(0, 2)), int(rng.integers(95, 106)), int(rng.random() < 0.1)) for _ in range(n)]
+        if trial % 2 == 0:
+            periods = [(0, periods[0][1], 0), (1, periods[1][1], 0)]  # the deployed pair
+        want_int, want_rl = _load_usage_py(tenths, ts, periods, G)
+        free = (rng.integers(0, 21, G) * 5).astype(np.int64)
+        total = 0.0
+        for g in range(G):  # the fp64 node sum the oracle's Rate takes (rater.go:63-65)
+            u = 0.0
+            for metric, min_ts, never in periods:
+                t10 = int(tenths[metric][g])
+                if t10 == 255 or never or int(ts[metric][g]) < min_ts:
+                    continue
+                u += min(t10, 10) / 10
+            total += u
+        for policy in (o.POLICY_BINPACK, o.POLICY_SPREAD):
+            got = eval_wide(doh, free, np.zeros(G), [10, 5], policy, usage=(tenths, ts), periods=periods)
+            assert got["rl_after"] == want_rl, (trial, G, periods)
+            assert got["score"] == o.rate(policy, free, total), (trial, free, total)
+            # the plan uses the RemainLoad this very pass computed
+            ok, idx, _ = o.choose(policy, free, np.array([10, 5], dtype=np.int32), rl=np.array(want_rl, dtype=np.int64))
+            assert got["ok"] == ok and (not ok or got["plan"] == idx)
