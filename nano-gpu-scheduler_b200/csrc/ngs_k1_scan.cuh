@@ -40,7 +40,9 @@ __global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables
                                                 int32_t* __restrict__ plan, int32_t* __restrict__ n_emitted, VerbDone vd) {
     __shared__ SortedDemand dem;
     __shared__ double s_pair[121];
+    __shared__ WideCtx s_wcx;
     if (threadIdx.x == 0) sort_demand(pd.percent, pd.n, pd.policy, &dem);
+    wide_ctx_fill(&s_wcx, T, lp, threadIdx.x == 32);
     if (lp.enabled) fill_usage_pair_table(s_pair, threadIdx.x, blockDim.x);
     __syncthreads();
     const int C = pd.n;
@@ -59,7 +61,7 @@ __global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables
                 ev.known = ev.feasible = cached = true;
                 ev.score = T.cscore[row];
             } else {
-                ev = eval_row_global<PLAN>(T, row, &dem, lp, true, s_pair);
+                ev = eval_row_global<PLAN>(T, row, &dem, lp, true, &s_wcx, s_pair);
             }
         }
         const bool ok = ev.known && ev.feasible;
@@ -142,6 +144,7 @@ __global__ void __launch_bounds__(SCAN_TILE, NGS_SCAN_BLOCKS) k_scan_tma(Tables 
     extern __shared__ __align__(128) unsigned char tiles[];
     __shared__ SortedDemand dem;
     __shared__ __align__(8) uint64_t bars[NGS_SCAN_STAGES];
+    __shared__ WideCtx s_wcx;
     const uint32_t tid = threadIdx.x;
     const uint32_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     const bool want_rl = !T.rl_zero;
@@ -169,6 +172,7 @@ __global__ void __launch_bounds__(SCAN_TILE, NGS_SCAN_BLOCKS) k_scan_tma(Tables 
         }
     }
     if (tid == 32) sort_demand(pd.percent, pd.n, pd.policy, &dem);
+    wide_ctx_fill(&s_wcx, T, lp, tid == 64);
     __syncthreads();
 
     uint32_t it = 0;
@@ -193,7 +197,7 @@ __global__ void __launch_bounds__(SCAN_TILE, NGS_SCAN_BLOCKS) k_scan_tma(Tables 
             if (next < ntiles) issue(next, stage);
         }
         if (row < n) {
-            const RowEval ev = eval_row_values<false>(T, row, in, &dem, lp, true, nullptr);
+            const RowEval ev = eval_row_values<false>(T, row, in, &dem, lp, true, nullptr, &s_wcx);
             const bool ok = ev.known && ev.feasible;
             if (feasible) feasible[row] = ok ? 1 : 0;
             if (reason) reason[row] = !ev.known ? NGS_REASON_UNKNOWN_NODE : (ok ? NGS_REASON_OK : NGS_REASON_INFEASIBLE);

@@ -13,7 +13,9 @@ struct BindResult {
 __global__ void k_bind(Tables T, uint32_t gidx, PodDemand pd, LoadParams lp, uint32_t gen, BindResult* res_out) {
     __shared__ SortedDemand dem;
     __shared__ BindResult s_res;
+    __shared__ WideCtx s_wcx;
     if (threadIdx.x != 0) return;
+    wide_ctx_fill(&s_wcx, T, lp, true);
     BindResult* res = &s_res;
     struct Publish {  // whatever way the body returns: copy the result out, status last
         BindResult* from;
@@ -34,7 +36,7 @@ __global__ void k_bind(Tables T, uint32_t gidx, PodDemand pd, LoadParams lp, uin
         return;
     }
     const bool hit = T.tag[row] == gen;
-    RowEval ev = eval_row_global<true>(T, row, &dem, lp, !hit);
+    RowEval ev = eval_row_global<true>(T, row, &dem, lp, !hit, &s_wcx);
     if (!ev.feasible) {  // node.go:74-76
         res->status = NGS_ERR_INFEASIBLE;
         return;

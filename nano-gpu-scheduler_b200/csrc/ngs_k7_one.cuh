@@ -58,16 +58,10 @@ __device__ __forceinline__ uint32_t block_scan_256(uint32_t v, uint32_t* s_warp 
 }
 
 // SampleRater on one row: feasibility only
-__device__ __forceinline__ bool sample_row_feasible(const Tables& T, uint32_t row, const SortedDemand* dem) {
+__device__ __forceinline__ bool sample_row_feasible(const Tables& T, uint32_t row, const SortedDemand* dem, const WideCtx* wcx) {
     const int G = T.gcount[row];
     if (G == 0) return false;
-    if (G > 8) {  // ngs_wide.cuh
-        LoadParams off;
-        off.enabled = 0;
-        RowEval ev;
-        eval_wide_row(T, row, dem, off, false, &ev, nullptr);
-        return ev.feasible;
-    }
+    if (G > 8) return (eval_wide_row(wcx, row, dem, 0u).x & 1u) != 0;  // ngs_wide.cuh
     uint32_t v[8];
     ld_row8(T.free + (size_t)row * 8, v);
     int f[8];
@@ -88,8 +82,14 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one_random(Tables T, PodDem
     __shared__ uint32_t s_pick_cta, s_pick_off;
     __shared__ unsigned long long s_total, s_before_rank;
     __shared__ int s_status;
+    __shared__ WideCtx s_wcx;
     const uint32_t tid = threadIdx.x;
     if (tid == 0) sort_demand(pd.percent, pd.n, pd.policy, &dem);
+    if (tid == 32) {
+        LoadParams off;
+        off.enabled = 0;  // SampleRater never looks at the load tables
+        wide_ctx_fill(&s_wcx, T, off, true);
+    }
     __syncthreads();
     // CTA b owns rows [b * per_cta, (b+1) * per_cta), thread t the rpt consecutive rows from b * per_cta + t * rpt
     const uint32_t rpt = (T.n + gridDim.x * 256u - 1) / (gridDim.x * 256u);
@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one_random(Tables T, PodDem
         uint32_t c = 0;
         const uint32_t r0 = cta * per_cta + tid * rpt;
         for (uint32_t j = 0; j < rpt; j++)
-            if (r0 + j < T.n && sample_row_feasible(T, r0 + j, &dem)) c++;
+            if (r0 + j < T.n && sample_row_feasible(T, r0 + j, &dem, &s_wcx)) c++;
         return c;
     };
     uint32_t total;
@@ -210,21 +210,16 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one_random(Tables T, PodDem
             const uint32_t r0 = cta * per_cta + tid * rpt;
             for (uint32_t j = 0; j < rpt; j++) {
                 const uint32_t row = r0 + j;
-                if (row >= T.n || !sample_row_feasible(T, row, &dem)) continue;
+                if (row >= T.n || !sample_row_feasible(T, row, &dem, &s_wcx)) continue;
                 if (left-- != 0) continue;
                 // NodeInfo.Bind (node.go:70-84) with SampleRater.Choose (rater.go:28-50)
                 const int G = T.gcount[row];
                 uint64_t emit = 0;
                 int n_emit = 0;
                 if (G > 8) {  // ngs_wide.cuh
-                    LoadParams off;
-                    off.enabled = 0;
-                    RowEval ev;
-                    int placed[WIDE_MAX];
-                    eval_wide_row(T, row, &dem, off, false, &ev, placed);
-                    wide_store_free(T, row, placed);
-                    emit = ev.emit;
-                    n_emit = ev.n_emit;
+                    const uint4 r = eval_wide_row(&s_wcx, row, &dem, WIDE_APPLY);
+                    emit = (uint64_t)r.z | ((uint64_t)r.w << 32);
+                    n_emit = (int)(r.x >> 8);
                 } else {
                     uint32_t v[8];
                     ld_row8(T.free + (size_t)row * 8, v);
@@ -278,6 +273,7 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd,
     __shared__ uint64_t s_wmax[8];
     __shared__ int s_last;
     __shared__ int32_t s_plan[NGS_MAX_CONTAINERS];  // the winner's plan in container order (last CTA only)
+    __shared__ WideCtx s_wcx;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     // the first row of every thread is requested before the demand is sorted: the loads do not depend on it
     const bool load_path = lp.enabled != 0;  // (binpack / spread only)
@@ -285,12 +281,13 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd,
     RowIn in;
     if (row < T.n) load_row(T, row, load_path, in);
     if (tid == 32) sort_demand(pd.percent, pd.n, pd.policy, &dem);
+    wide_ctx_fill(&s_wcx, T, lp, tid == 64);
     if (lp.enabled) fill_usage_pair_table(s_pair, tid, blockDim.x);
     __syncthreads();
     uint64_t best = 0;
     for (; row < T.n; row += gridDim.x * blockDim.x) {
         // Rate + Choose on the row as it stands; in load-aware mode this also leaves RemainLoad behind (allocate.go:193)
-        const RowEval ev = eval_row_values<false>(T, row, in, &dem, lp, true, s_pair);
+        const RowEval ev = eval_row_values<false>(T, row, in, &dem, lp, true, s_pair, &s_wcx);
         if (ev.known && ev.feasible) {
             const uint64_t k = make_key(ev.score, T.first + row);
             best = k > best ? k : best;
@@ -355,14 +352,9 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd,
         uint64_t emit = 0;
         int n_emit = 0, fr = 0;
         if (G > 8) {  // ngs_wide.cuh: lane 0 plans and places, the plan goes to the other lanes
-            if (lane == 0) {
-                LoadParams off;
-                off.enabled = 0;  // (the plan is derived from the RemainLoad the scan left behind, as below)
-                RowEval ev;
-                int placed[WIDE_MAX];
-                eval_wide_row(T, wrow, &dem, off, false, &ev, placed);
-                wide_store_free(T, wrow, placed);
-                emit = ev.emit;
+            if (lane == 0) {  // (no WIDE_LOAD: the plan is derived from the RemainLoad the scan left behind, as below)
+                const uint4 r = eval_wide_row(&s_wcx, wrow, &dem, WIDE_APPLY);
+                emit = (uint64_t)r.z | ((uint64_t)r.w << 32);
             }
             emit = __shfl_sync(FULL, emit, 0);
         } else {

@@ -45,9 +45,10 @@ struct RowIn {
     uint2 r8;           // RemainLoad (other passes; zeros when the table is known to hold only zeros)
 };
 
+// wcx: the CTA's context for rows of more than 8 GPUs (ngs_wide.cuh)
 template <bool PLAN>
 __device__ __forceinline__ RowEval eval_row_values(const Tables& T, uint32_t row, const RowIn& in, const SortedDemand* dem,
-                                                   const LoadParams& lp, bool do_rate, const double* pair) {
+                                                   const LoadParams& lp, bool do_rate, const double* pair, const WideCtx* wcx) {
     RowEval ev;
     ev.known = false;
     ev.feasible = false;
@@ -62,10 +63,8 @@ __device__ __forceinline__ RowEval eval_row_values(const Tables& T, uint32_t row
     const uint32_t (&ts)[2][8] = in.ts;
     const uint2 r8 = in.r8;
     if (G == 0) return ev;
-    if (G > 8) {  // 9..12 GPUs: the row's cells are not all in `in` (ngs_wide.cuh)
-        eval_wide_row(T, row, dem, lp, do_rate, &ev, nullptr);
-        return ev;
-    }
+    if (G > 8)  // 9..12 GPUs: the row's cells are not all in `in`
+        return wide_row_eval(wcx, row, dem, (do_rate ? WIDE_RATE : 0u) | (lp.enabled ? WIDE_LOAD : 0u));
     ev.known = true;
     int f[8];
 #pragma unroll
@@ -153,8 +152,8 @@ __device__ __forceinline__ void load_row(const Tables& T, uint32_t row, bool loa
 
 template <bool PLAN>
 __device__ __forceinline__ RowEval eval_row_global(const Tables& T, uint32_t row, const SortedDemand* dem, const LoadParams& lp,
-                                                   bool do_rate, const double* pair = nullptr) {
+                                                   bool do_rate, const WideCtx* wcx, const double* pair = nullptr) {
     RowIn in;
     load_row(T, row, lp.enabled && do_rate && dem->policy != NGS_POLICY_RANDOM, in);
-    return eval_row_values<PLAN>(T, row, in, dem, lp, do_rate, pair);
+    return eval_row_values<PLAN>(T, row, in, dem, lp, do_rate, pair, wcx);
 }

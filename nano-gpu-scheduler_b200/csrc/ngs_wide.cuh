@@ -40,20 +40,34 @@ __device__ inline void wide_go_sort(int* key, int* fr, int* ix, int n) {
         }
 }
 
-// GPUs.Choose (allocate.go:92-100) on one wide row.  do_rate / the load-aware pass / the emission list mean what
-// they mean in eval_row_values (ngs_rows.cuh); `placed`, when given, receives the row's free cells after GPUs.Allocate
-// of the plan (only meaningful when the result is feasible).
-__device__ __noinline__ void eval_wide_row(const Tables& T, uint32_t row, const SortedDemand* dem, const LoadParams& lp, bool do_rate,
-                                           RowEval* out, int* placed) {
-    RowEval ev;
-    ev.known = true;
-    ev.feasible = false;
-    ev.score = NGS_SCORE_MIN;
-    ev.emit = 0;
-    ev.n_emit = 0;
+// What the evaluation reads, staged once per CTA in shared memory (wide_ctx_fill) by the kernels that may meet such a
+// row: the out-of-line call then takes one pointer instead of two by-value structs, which would otherwise be copied
+// to every thread's stack whether or not a wide row ever shows up.
+struct WideCtx {
+    Tables T;
+    LoadParams lp;
+};
+// call before the kernel's first __syncthreads(); snapshots without wide nodes (free_hi == nullptr) skip the copy
+__device__ __forceinline__ void wide_ctx_fill(WideCtx* cx, const Tables& T, const LoadParams& lp, bool one_thread) {
+    if (T.free_hi != nullptr && one_thread) {
+        cx->T = T;
+        cx->lp = lp;
+    }
+}
+enum { WIDE_RATE = 1, WIDE_LOAD = 2, WIDE_APPLY = 4 };
+
+// GPUs.Choose (allocate.go:92-100) on one wide row.  flags: WIDE_RATE = run Rate (do_rate of eval_row_values),
+// WIDE_LOAD = the call is load-aware if the context says so (cx->lp.enabled), WIDE_APPLY = when the plan is feasible
+// store the cells as GPUs.Allocate leaves them (allocate.go:102-118).
+// Returns x: bit 0 feasible, bits 8.. n_emit; y: score; (z, w): the emission list, 4 bits per entry as elsewhere.
+__device__ __noinline__ uint4 eval_wide_row(const WideCtx* cx, uint32_t row, const SortedDemand* dem, uint32_t flags) {
+    const Tables& T = cx->T;
+    const LoadParams& lp = cx->lp;
+    const bool do_rate = (flags & WIDE_RATE) != 0;
+    int score = NGS_SCORE_MIN;
     const int policy = dem->policy;
     const int G = min((int)T.gcount[row], WIDE_MAX);
-    const bool load_path = lp.enabled && do_rate && policy != NGS_POLICY_RANDOM;
+    const bool load_path = (flags & WIDE_LOAD) && lp.enabled && do_rate && policy != NGS_POLICY_RANDOM;
     int f[WIDE_MAX], rl[WIDE_MAX];
     for (int g = 0; g < G; g++) f[g] = __ldcg(wide_free_cell(T, row, g));
     int load_int = 0;
@@ -82,16 +96,16 @@ __device__ __noinline__ void eval_wide_row(const Tables& T, uint32_t row, const 
         if (policy == NGS_POLICY_BINPACK) {  // rater.go:59-70
             int used = 0;
             for (int g = 0; g < G; g++) used += 100 - f[g];
-            ev.score = binpack_percent_fp64(used, G) + load_int * 50 - G;
+            score = binpack_percent_fp64(used, G) + load_int * 50 - G;
         } else if (policy == NGS_POLICY_SPREAD) {  // rater.go:113-123
             int avail = 0, cnt = 0;
             for (int g = 0; g < G; g++) {
                 avail += f[g];
                 cnt += f[g] == 100 ? 1 : 0;
             }
-            ev.score = 100 * cnt + avail / 10 - G - load_int;
+            score = 100 * cnt + avail / 10 - G - load_int;
         } else {
-            ev.score = 100;  // rater.go:24-26
+            score = 100;  // rater.go:24-26
         }
     }
     uint64_t em = 0;
@@ -144,16 +158,18 @@ __device__ __noinline__ void eval_wide_row(const Tables& T, uint32_t row, const 
         for (int k = dem->nz; k < dem->C; k++) em |= (uint64_t)0xF << (4 * ne++);
         for (int i = 0; i < G; i++) f[ix[i]] = fr[i];
     }
-    ev.feasible = ok;
-    ev.emit = em;
-    ev.n_emit = ne;
-    if (placed)
-        for (int g = 0; g < G; g++) placed[g] = f[g];
-    *out = ev;
+    if (ok && (flags & WIDE_APPLY))
+        for (int g = 0; g < G; g++) *wide_free_cell(T, row, g) = f[g];
+    return make_uint4((ok ? 1u : 0u) | ((uint32_t)ne << 8), (uint32_t)score, (uint32_t)em, (uint32_t)(em >> 32));
 }
-
-// GPUs.Allocate of a plan just chosen on a wide row: store the cells eval_wide_row left in `placed`
-__device__ inline void wide_store_free(const Tables& T, uint32_t row, const int* placed) {
-    const int G = min((int)T.gcount[row], WIDE_MAX);
-    for (int g = 0; g < G; g++) *wide_free_cell(T, row, g) = placed[g];
+// the same, unpacked into what the 8-cell paths return
+__device__ __forceinline__ RowEval wide_row_eval(const WideCtx* cx, uint32_t row, const SortedDemand* dem, uint32_t flags) {
+    const uint4 r = eval_wide_row(cx, row, dem, flags);
+    RowEval ev;
+    ev.known = true;
+    ev.feasible = (r.x & 1u) != 0;
+    ev.score = (int)r.y;
+    ev.emit = (uint64_t)r.z | ((uint64_t)r.w << 32);
+    ev.n_emit = (int)(r.x >> 8);
+    return ev;
 }

@@ -76,14 +76,14 @@ void doh_eval_wide_row(const int32_t* free, int G, const int8_t* rl, const int32
             (g < 8 ? s_lo[m * 8 + g] : s_hi[m * 4 + g - 8]) = ts ? ts[m * 12 + g] : 0;
         }
     uint8_t gc = (uint8_t)G;
-    Tables T;
-    memset(&T, 0, sizeof(T));
+    WideCtx cx;
+    memset(&cx, 0, sizeof(cx));
+    Tables& T = cx.T;
     T.free = f_lo; T.free_hi = f_hi; T.rl = r_lo; T.rl_hi = r_hi; T.tenths = t_lo; T.tenths_hi = t_hi; T.ts = s_lo; T.ts_hi = s_hi;
     T.gcount = &gc;
     T.nstride = 1;
     T.n = 1;
-    LoadParams lp;
-    memset(&lp, 0, sizeof(lp));
+    LoadParams& lp = cx.lp;
     lp.enabled = tenths != nullptr;
     lp.n_periods = n_periods;
     for (int e = 0; e < n_periods; e++) {
@@ -91,10 +91,7 @@ void doh_eval_wide_row(const int32_t* free, int G, const int8_t* rl, const int32
         lp.min_ts[e] = min_ts[e];
         lp.never[e] = never[e];
     }
-    RowEval ev;
-    int placed[WIDE_MAX] = {0};
-    eval_wide_row(T, 0, &dem, lp, do_rate != 0, &ev, placed);
-    if (ev.feasible) wide_store_free(T, 0, placed);
+    const RowEval ev = wide_row_eval(&cx, 0, &dem, (do_rate ? WIDE_RATE : 0u) | WIDE_LOAD | WIDE_APPLY);
     out[0] = ev.feasible;
     out[1] = ev.score;
     out[2] = ev.n_emit;
