@@ -112,9 +112,10 @@ int ngs_node_upsert(ngs_dealer *h, uint32_t idx, int gpu_count);
  * remain_load[gpu_count] (NULL = 0) — the per-node form of ngs_snapshot_load / ngs_snapshot_read, whose
  * [n][NGS_MAX_GPUS] arrays hold cells 0..7 only (ngs_snapshot_load refuses gpu_count > NGS_MAX_GPUS,
  * ngs_snapshot_read returns such a node's gpu_count and its first eight cells).  Every verb (assume, score, bind,
- * apply, release, load updates with card < 12) and the single-pod form of ngs_schedule_batch handle such nodes;
- * the persistent batch kernel (n_pods > 1) keeps its rows 8 cells wide and answers NGS_ERR_UNSUPPORTED while the
- * snapshot holds one. */
+ * apply, release, load updates with card < 12) and ngs_schedule_batch / _dev handle such nodes: their rows are
+ * evaluated by one thread each, from the global tables, so a snapshot full of them runs several times slower than
+ * one of 8-GPU nodes.  ngs_schedule_batch_noalloc takes caller-owned tables of 8 cells per row: a node with more
+ * GPUs is left out there and NGS_ERR_UNSUPPORTED comes back. */
 int ngs_node_set_wide(ngs_dealer *h, uint32_t idx, int gpu_count, const int32_t *free, const int8_t *remain_load);
 int ngs_node_get_wide(ngs_dealer *h, uint32_t idx, int *gpu_count, int32_t *free, int8_t *remain_load); /* free / remain_load: [NGS_MAX_GPUS_WIDE] */
 /* bulk rebuild on start (dealer.go:58-72,279-299 replayed host-side, then one H2D copy).

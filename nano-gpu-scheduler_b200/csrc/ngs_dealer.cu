@@ -302,13 +302,16 @@ uint32_t schedule_block_size(uint32_t rpb) {
 size_t schedule_smem_bytes(uint32_t rpb) { return (size_t)rpb * 32 + (size_t)((rpb + 31) / 32) * 16 + 16; }
 constexpr size_t K6_STATIC_SMEM = 4096;
 // which instantiation of K6 serves CTAs of `rpb` rows, and its block size
-const void* schedule_kernel(uint32_t rpb) {
-    return rpb > K6_EXCLUSIVE_ROWS ? (const void*)k_schedule<true> : (const void*)k_schedule<false>;
+// (wide: the snapshot holds nodes of more than NGS_MAX_GPUS GPUs)
+const void* schedule_kernel(uint32_t rpb, bool wide) {
+    if (wide) return rpb > K6_EXCLUSIVE_ROWS ? (const void*)k_schedule<true, true> : (const void*)k_schedule<false, true>;
+    return rpb > K6_EXCLUSIVE_ROWS ? (const void*)k_schedule<true, false> : (const void*)k_schedule<false, false>;
 }
 uint32_t schedule_block(uint32_t rpb) { return rpb > K6_EXCLUSIVE_ROWS ? 1024u : schedule_block_size(rpb); }
-// the dynamic shared memory limit is a per-device upper bound shared by every launch: allow the device maximum for both instantiations
+// the dynamic shared memory limit is a per-device upper bound shared by every launch: allow the device maximum for every instantiation
 cudaError_t schedule_allow_max_smem(int smem_optin) {
-    const void* fns[2] = {(const void*)k_schedule<false>, (const void*)k_schedule<true>};
+    const void* fns[4] = {(const void*)k_schedule<false, false>, (const void*)k_schedule<true, false>, (const void*)k_schedule<false, true>,
+                          (const void*)k_schedule<true, true>};
     for (const void* fn : fns) {
         cudaFuncAttributes fa;
         cudaError_t e = cudaFuncGetAttributes(&fa, fn);  // the opt-in limit covers static + dynamic shared memory
@@ -323,10 +326,6 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
                     const LoadParams& lp, uint64_t seed_seq, int32_t* d_node, int32_t* d_score, int32_t* d_gidx,
                     int32_t* status_out = nullptr) {
     if (!h->coop) return fail(h, NGS_ERR_CUDA, "device lacks cooperative launch");
-    // (a sharded handle launches regardless — its peers are already waiting for it — and the kernel leaves such rows out)
-    if (h->n_wide && h->world == 1)
-        return fail(h, NGS_ERR_UNSUPPORTED, "the snapshot holds %u node(s) with more than NGS_MAX_GPUS GPUs: the batch kernel keeps 8 cells per row; "
-                                            "schedule through the verbs or one pod per call", h->n_wide);
     h->epoch++;  // the batch binds pods
     const uint32_t N = h->T.n;
     uint32_t grid = (N + 63) / 64;
@@ -398,7 +397,7 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     h->dbg_grid = grid;
 #endif
     void* args[] = {&bp};
-    CU(h, cudaLaunchCooperativeKernel(schedule_kernel(rpb), dim3(grid), dim3(block), args, smem, h->stream));
+    CU(h, cudaLaunchCooperativeKernel(schedule_kernel(rpb, h->n_wide != 0), dim3(grid), dim3(block), args, smem, h->stream));
     h->stats.kernel_launches += 2;
     h->stats.node_evals += (uint64_t)P * N;
     h->stats.pods_scheduled += P;
@@ -1337,7 +1336,7 @@ extern "C" int ngs_schedule_batch_noalloc(int device, void* stream, const ngs_sn
     bp.err = err;
     bp.rows_per_block = rpb;
     void* args[] = {&bp};
-    if (cudaLaunchCooperativeKernel(schedule_kernel(rpb), dim3(grid), dim3(block), args, smem, st) != cudaSuccess) return NGS_ERR_CUDA;
+    if (cudaLaunchCooperativeKernel(schedule_kernel(rpb, false), dim3(grid), dim3(block), args, smem, st) != cudaSuccess) return NGS_ERR_CUDA;
     int32_t dev_status = NGS_OK;  // device-side validation / timeout word of this batch
     if (cudaMemcpyAsync(&dev_status, err, sizeof(dev_status), cudaMemcpyDeviceToHost, st) != cudaSuccess) return NGS_ERR_CUDA;
     if (cudaStreamSynchronize(st) != cudaSuccess) return NGS_ERR_CUDA;

@@ -375,16 +375,22 @@ __device__ __forceinline__ unsigned long long read_slot(const unsigned long long
 // policies: every thread keeps the best two keys of its rows (k1 >= k2).  Random policy: one
 // feasibility bit per row in the pod's feasbits words, the warp's count in cnt (lane 0).
 // Must be called by all 32 lanes.
+// WIDE: the snapshot holds nodes of 9..12 GPUs (ngs_wide.cuh).  Their shared-memory rows are empty (never feasible for
+// the code below); widebits marks them, and the lane that owns such a row evaluates it from the global tables instead —
+// in its turn, so that a lane still meets its rows in ascending order.  row0: first row of this CTA.
+template <bool WIDE>
 __device__ __forceinline__ void filter_pass(const SmemRows& S, const SortedDemand* dem, uint32_t wt, uint32_t WT, uint32_t n_iter,
                                             uint32_t my_rows, uint32_t node0, uint32_t lane, int g, int gbase, uint32_t* fb,
-                                            uint64_t& k1, uint64_t& k2, uint32_t& cnt) {
+                                            uint64_t& k1, uint64_t& k2, uint32_t& cnt, const WideCtx* wcx, const uint32_t* widebits,
+                                            uint32_t row0) {
     const int policy = dem->policy;
     const bool spread = policy == NGS_POLICY_SPREAD;
     if (policy == NGS_POLICY_RANDOM) {
         uint32_t c = 0;
         for (uint32_t it = 0; it < n_iter; it++) {
             const uint32_t r = it * WT + wt;
-            const bool ok = r < my_rows && eval_row_sample(S, r, dem);
+            bool ok = r < my_rows && eval_row_sample(S, r, dem);
+            if (WIDE && r < my_rows && ((widebits[r >> 5] >> (r & 31)) & 1u)) ok = (eval_wide_row(wcx, row0 + r, dem, 0u).x & 1u) != 0;
             const uint32_t bal = __ballot_sync(0xFFFFFFFFu, ok);
             if (lane == 0 && r < my_rows) {
                 fb[r >> 5] = bal;
@@ -472,7 +478,11 @@ __device__ __forceinline__ void filter_pass(const SmemRows& S, const SortedDeman
             }
         }
         // best two by score, branch-free: an infeasible row enters as NONE and changes nothing
-        const int sc = cls == FEAS_YES ? *ratep : NONE;
+        int sc = cls == FEAS_YES ? *ratep : NONE;
+        if (WIDE && in && ((widebits[r >> 5] >> (r & 31)) & 1u)) {  // Rate (load-aware if the batch is) and Choose, one thread
+            const uint4 w = eval_wide_row(wcx, row0 + r, dem, WIDE_RATE | WIDE_LOAD);
+            sc = (w.x & 1u) ? (int)w.y : NONE;
+        }
         const bool gt1 = sc > s1, gt2 = sc > s2;
         s2 = gt1 ? s1 : (gt2 ? sc : s2);
         r2 = gt1 ? r1 : (gt2 ? r : r2);
@@ -519,6 +529,26 @@ __device__ __forceinline__ uint64_t fresh_key_of_row(const SmemRows& S, uint32_t
     return cls == FEAS_YES ? make_key(spread ? S.scS[r] : S.scB[r], node) : 0ull;
 }
 
+// A pod bound to a node of 9..12 GPUs (one lane): the plan on the row as it stands in the global tables (RemainLoad as
+// the filter left it), GPUs.Allocate, the pod's outputs.
+__device__ __forceinline__ void publish_wide(const BatchParams& bp, const WideCtx* wcx, uint32_t row, const SortedDemand* dem, uint32_t p,
+                                             int score) {
+    const uint4 w = eval_wide_row(wcx, row, dem, WIDE_APPLY);
+    int32_t* out = bp.gpu_idx_out + (size_t)p * bp.max_c;
+    for (int k = dem->C; k < bp.max_c; k++) out[k] = INT32_MIN;
+    write_plan(out, dem, dem->policy != NGS_POLICY_RANDOM, true, (uint64_t)w.z | ((uint64_t)w.w << 32), (int)(w.x >> 8));
+    bp.T.tag[row] = 0;  // node.go:82
+    bp.node_out[p] = (int32_t)(bp.T.first + row);
+    bp.score_out[p] = score;
+}
+// ... and that row's verdict for the next pod, on the row as the bind left it
+__device__ __forceinline__ uint64_t fresh_key_of_wide_row(const WideCtx* wcx, uint32_t row, uint32_t node, const SortedDemand* dem_next,
+                                                          int* fresh_ok) {
+    const uint4 w = eval_wide_row(wcx, row, dem_next, WIDE_RATE | WIDE_LOAD);
+    *fresh_ok = (int)(w.x & 1u);
+    return ((w.x & 1u) && dem_next->policy != NGS_POLICY_RANDOM) ? make_key((int)w.y, node) : 0ull;
+}
+
 // K6.  One CTA per SM (cooperative launch, so every CTA is resident), each owning a contiguous
 // node range held in shared memory for the whole batch.  Warps 0 and 1 are control warps, the
 // others ("workers") own the rows.  Pods are decided strictly in order, but the work is pipelined:
@@ -536,7 +566,8 @@ __device__ __forceinline__ uint64_t fresh_key_of_row(const SmemRows& S, uint32_t
 // ALL_WORK (chosen by the host from the rows per CTA, schedule_kernel()): every warp below the control warps
 // filters; otherwise the warps that share control warp 0's scheduler stay idle.  A compile-time choice: as a
 // run-time flag it cost the small-CTA case 1.8 %.
-template <bool ALL_WORK>
+// WIDE: the snapshot holds nodes of 9..12 GPUs; see filter_pass.  The host picks it only then (no cost otherwise).
+template <bool ALL_WORK, bool WIDE>
 __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ SortedDemand s_dem[4];
@@ -549,6 +580,8 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     __shared__ int s_abort;
     // Binpack.Rate's percent table next to the rows when they leave room (an L2 trip on the plan's path otherwise)
     __shared__ int16_t s_blut[ALL_WORK ? 2 : 9 * RATE_LUT_STRIDE];
+    __shared__ WideCtx s_wcx;  // (referenced by the WIDE instantiations only)
+    const WideCtx* wcx = &s_wcx;
     const uint32_t rpb = bp.rows_per_block;
     if (threadIdx.x == 0) {
         s_abort = 0;
@@ -565,6 +598,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     S.scS = S.scB + rpb;
     S.top4 = reinterpret_cast<uint32_t*>(S.scS + rpb);
     S.feasbits = S.top4 + rpb;  // two buffers of fwords words (pod parity)
+    uint32_t* widebits = S.feasbits + 2 * fwords;  // WIDE: one bit per row, set for nodes of more than 8 GPUs (the allocation has room for four buffers)
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
     // the two control warps are the LAST two: the SM's issue arbiter favours high warp ids, and the
@@ -591,17 +625,28 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
     const int g = lane & 7, gbase = lane & 24;
 
     // ---- prologue: rows -> shared memory (and the load-aware quantities, frozen for the batch) ----
+    if (WIDE) {
+        if (tid == 0) {
+            s_wcx.T = bp.T;
+            s_wcx.lp = bp.lp;
+        }
+        for (uint32_t i = tid; i < fwords; i += blockDim.x) widebits[i] = 0;
+        __syncthreads();
+    }
     for (uint32_t r = tid; r < my_rows; r += blockDim.x) {
         const uint32_t row = row0 + r;
         int G = T.gcount[row];
-        if (G > 8) {  // 9..12 GPUs (ngs_wide.cuh): the rows of this kernel are 8 cells wide.  The host refuses such
-            G = 0;    // snapshots before the launch; a caller-owned view gets the status and the node left out
-            atomicMax(bp.err, NGS_ERR_UNSUPPORTED);
-        }
         int f[8];
         const int4 a = ld_row4(T.free + (size_t)row * 8), b = ld_row4(T.free + (size_t)row * 8 + 4);
         f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w;
         f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+        if (G > 8) {  // 9..12 GPUs (ngs_wide.cuh): the shared-memory row stays empty
+            if (WIDE) atomicOr(&widebits[r >> 5], 1u << (r & 31));
+            else atomicMax(bp.err, NGS_ERR_UNSUPPORTED);  // a caller-owned view (no second plane): the node is left out, the status says so
+            G = 0;
+#pragma unroll
+            for (int c = 0; c < 8; c++) f[c] = 0;
+        }
         int rlc[8];
         int load_int = 0;
         if (bp.lp.enabled && G > 0) {
@@ -706,7 +751,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
             write_back_rl();
         }
         if (is_worker) {
-            filter_pass(S, &s_dem[0], wt, WT, n_iter, my_rows, T.first + row0, lane, g, gbase, S.feasbits, k1, k2, cnt);
+            filter_pass<WIDE>(S, &s_dem[0], wt, WT, n_iter, my_rows, T.first + row0, lane, g, gbase, S.feasbits, k1, k2, cnt, wcx, widebits, row0);
             publish_filter(0, s_dem[0].policy);
         }
     }
@@ -732,8 +777,8 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
             tq = clock64();  // (profiling) the filter alone, without the wait at the barrier before it
 #endif
             if (more) {
-                filter_pass(S, dem_next, wt, WT, n_iter, my_rows, T.first + row0, lane, g, gbase, S.feasbits + ((p + 1) & 1) * fwords, k1,
-                            k2, cnt);
+                filter_pass<WIDE>(S, dem_next, wt, WT, n_iter, my_rows, T.first + row0, lane, g, gbase, S.feasbits + ((p + 1) & 1) * fwords, k1,
+                                  k2, cnt, wcx, widebits, row0);
                 publish_filter((p + 1) & 1, dem_next->policy);
             }
             PHASE(0);
@@ -850,7 +895,8 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                                 if (need < pc) {
                                     for (uint32_t q = 0; q < need; q++) bits &= bits - 1;
                                     const uint32_t r = wi * 32 + (__ffs(bits) - 1);
-                                    publish_sample(bp, S, r, row0 + r, dem, p);
+                                    if (WIDE && ((widebits[r >> 5] >> (r & 31)) & 1u)) publish_wide(bp, wcx, row0 + r, dem, p, 100);
+                                    else publish_sample(bp, S, r, row0 + r, dem, p);
                                     bound_row = (int)r;
                                     break;
                                 }
@@ -865,7 +911,17 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                 if (bmask && more) {
                     const int br = __shfl_sync(0xFFFFFFFFu, bound_row, __ffs(bmask) - 1);
                     bool ok = false;
-                    const uint64_t fk = fresh_key_of_row(S, (uint32_t)br, T.first + row0 + (uint32_t)br, dem_next, g, gbase, &ok);
+                    uint64_t fk = 0;
+                    if (WIDE && ((widebits[br >> 5] >> (br & 31)) & 1u)) {
+                        __syncwarp();  // (the lane that bound the pod has stored the row)
+                        if (lane == 0) {
+                            int fo = 0;
+                            fk = fresh_key_of_wide_row(wcx, row0 + (uint32_t)br, T.first + row0 + (uint32_t)br, dem_next, &fo);
+                            ok = fo != 0;
+                        }
+                    } else {
+                        fk = fresh_key_of_row(S, (uint32_t)br, T.first + row0 + (uint32_t)br, dem_next, g, gbase, &ok);
+                    }
                     if (lane == 0) {
                         s_dirty[nx] = br;
                         s_fresh[nx] = fk;
@@ -890,6 +946,7 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
 #endif
                 const bool have = (v & KEY_FEASIBLE) != 0;
                 const uint32_t my_r = have ? key_node(v) - T.first - row0 : 0u;
+                const bool my_wide = WIDE && have && ((widebits[my_r >> 5] >> (my_r & 31)) & 1u);  // planned only if it wins, below
                 GroupCommit cm;
                 cm.fr = 0;
                 cm.emit = 0;
@@ -955,14 +1012,14 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
 #ifdef NGS_PHASE_TIMING
                     long long st[2] = {0, 0};
                     const long long t_in = clock64();
-                    if (have) plan_group(bp, S, my_r, T.first + row0 + my_r, dem, more ? dem_next : nullptr, g, gbase, cm, st, lut);
+                    if (have && !my_wide) plan_group(bp, S, my_r, T.first + row0 + my_r, dem, more ? dem_next : nullptr, g, gbase, cm, st, lut);
                     if (have && cm.fresh != 12345) {
                         ph[0] += st[0] - t_in;   // exact plan (choose_group8<PLAN>)
                         ph[2] += st[1] - st[0];  // post-bind statistics and rates
                         ph[6] -= 0;
                     }
 #else
-                    if (have) plan_group(bp, S, my_r, T.first + row0 + my_r, dem, more ? dem_next : nullptr, g, gbase, cm, nullptr, lut);
+                    if (have && !my_wide) plan_group(bp, S, my_r, T.first + row0 + my_r, dem, more ? dem_next : nullptr, g, gbase, cm, nullptr, lut);
 #endif
                 }
                 PHASE(4);
@@ -980,8 +1037,15 @@ __global__ void __launch_bounds__(1024, 1) k_schedule(BatchParams bp) {
                         bp.score_out[p] = key_score(m);
                     }
                     if (have && m == v) {  // warp-uniform
-                        // ---- bind on the owner: stores only, everything was worked out during the exchange ----
-                        publish_group(bp, S, my_r, row0 + my_r, dem, p, key_score(m), cm, lane);
+                        if (my_wide) {
+                            if (lane == 0) {
+                                publish_wide(bp, wcx, row0 + my_r, dem, p, key_score(m));
+                                if (more) cm.fresh = fresh_key_of_wide_row(wcx, row0 + my_r, T.first + row0 + my_r, dem_next, &cm.fresh_ok);
+                            }
+                        } else {
+                            // ---- bind on the owner: stores only, everything was worked out during the exchange ----
+                            publish_group(bp, S, my_r, row0 + my_r, dem, p, key_score(m), cm, lane);
+                        }
                         if (lane == 0) {
                             s_dirty[nx] = (int)my_r;
                             s_fresh[nx] = cm.fresh;

@@ -441,6 +441,29 @@ Error Dealer::getNodeInfo(const std::string& name, uint32_t* row) {  // dealer.g
     return "";
 }
 
+// Rows [lo, lo + n) with all their cells, kRowCells per row (nodes of 9..12 GPUs keep cells 8..11 in a second table:
+// ngs_node_get_wide).  rl may be nullptr.
+bool Dealer::read_rows(uint32_t lo, uint32_t n, std::vector<int32_t>* fr, std::vector<int8_t>* rl) const {
+    fr->assign((size_t)n * kRowCells, 0);
+    if (rl) rl->assign((size_t)n * kRowCells, 0);
+    if (n == 0) return true;
+    std::vector<int32_t> f8((size_t)n * NGS_MAX_GPUS);
+    std::vector<int8_t> r8(rl ? (size_t)n * NGS_MAX_GPUS : 0);
+    if (ngs_snapshot_read(h_, lo, n, nullptr, f8.data(), rl ? r8.data() : nullptr) != NGS_OK) return false;
+    for (uint32_t i = 0; i < n; i++) {
+        if (gpu_count_[lo + i] > NGS_MAX_GPUS) {
+            if (ngs_node_get_wide(h_, lo + i, nullptr, fr->data() + (size_t)i * kRowCells, rl ? rl->data() + (size_t)i * kRowCells : nullptr) != NGS_OK)
+                return false;
+            continue;
+        }
+        for (int g = 0; g < NGS_MAX_GPUS; g++) {
+            (*fr)[(size_t)i * kRowCells + g] = f8[(size_t)i * NGS_MAX_GPUS + g];
+            if (rl) (*rl)[(size_t)i * kRowCells + g] = r8[(size_t)i * NGS_MAX_GPUS + g];
+        }
+    }
+    return true;
+}
+
 // dealer.go:287-299 on the host copy of a new row: Allocate each assumed pod's plan (all or nothing,
 // DESIGN.md "deviations"), remember the pods that fitted.
 void Dealer::replay_assumed_pods(const std::string& name, int G, int32_t* fr) {
@@ -459,8 +482,8 @@ void Dealer::replay_assumed_pods(const std::string& name, int G, int32_t* fr) {
         std::vector<int32_t> demand, idx;
         if (!NewPlanFromPod(pod, &demand, &idx).empty()) continue;
         if (demand.size() > NGS_MAX_CONTAINERS) continue;
-        int32_t f[NGS_MAX_GPUS];
-        for (int g = 0; g < NGS_MAX_GPUS; g++) f[g] = fr[g];
+        int32_t f[kRowCells];
+        for (int g = 0; g < kRowCells; g++) f[g] = fr[g];
         bool ok = true;
         for (size_t k = 0; k < demand.size() && ok; k++) {
             const int gi = idx[k];
@@ -469,7 +492,7 @@ void Dealer::replay_assumed_pods(const std::string& name, int G, int32_t* fr) {
             else f[gi] -= demand[k];
         }
         if (!ok) continue;
-        for (int g = 0; g < NGS_MAX_GPUS; g++) fr[g] = f[g];
+        for (int g = 0; g < kRowCells; g++) fr[g] = f[g];
         pod_maps_[pod.uid] = pod;
     }
 }
@@ -524,7 +547,7 @@ void Dealer::Resolve(CandidateSet* cs) {  // dealer.go:97-106 for a whole list
         int G = 0;
         if (!src_ || !src_->GetNode(name, &node)) e = fmt("node \"%s\" not found", name.c_str());
         else if ((G = GetGPUDeviceCountOfNode(node)) <= 0) e = fmt("node \"%s\" has no nano-gpu/gpu-percent capacity", name.c_str());
-        else if (G > NGS_MAX_GPUS) e = fmt("node \"%s\": %d GPUs, more than NGS_MAX_GPUS", name.c_str(), G);
+        else if (G > NGS_MAX_GPUS_WIDE) e = fmt("node \"%s\": %d GPUs, more than NGS_MAX_GPUS_WIDE", name.c_str(), G);
         if (!e.empty()) {
             cs->lookup_err[(uint32_t)i] = e;
             continue;
@@ -534,16 +557,28 @@ void Dealer::Resolve(CandidateSet* cs) {  // dealer.go:97-106 for a whole list
         names_.push_back(name);
         gpu_count_.push_back(G);
         new_g.push_back((uint8_t)G);
-        new_free.resize(new_free.size() + NGS_MAX_GPUS, 0);
-        int32_t* fr = new_free.data() + new_free.size() - NGS_MAX_GPUS;
+        new_free.resize(new_free.size() + kRowCells, 0);
+        int32_t* fr = new_free.data() + new_free.size() - kRowCells;
         for (int g = 0; g < G; g++) fr[g] = 100;  // NewNodeInfo (node.go:25-42)
         replay_assumed_pods(name, G, fr);
         cs->rows[i] = r;
         cs->lookup_err.erase((uint32_t)i);
     }
     if (!new_g.empty()) {
-        // all new rows go up in one H2D copy instead of one launch per node and per replayed pod
-        if (ngs_snapshot_load(h_, first_new, (uint32_t)new_g.size(), new_g.data(), new_free.data(), nullptr) != NGS_OK) {
+        // all new rows go up in one H2D copy instead of one launch per node and per replayed pod; the bulk arrays are
+        // NGS_MAX_GPUS cells wide, so a node with more GPUs than that travels as an empty row and is set on its own after
+        const size_t nn = new_g.size();
+        std::vector<uint8_t> g8(nn);
+        std::vector<int32_t> f8(nn * NGS_MAX_GPUS);
+        for (size_t k = 0; k < nn; k++) {
+            const bool wide = new_g[k] > NGS_MAX_GPUS;
+            g8[k] = wide ? 0 : new_g[k];
+            for (int g = 0; g < NGS_MAX_GPUS; g++) f8[k * NGS_MAX_GPUS + g] = wide ? 0 : new_free[k * kRowCells + g];
+        }
+        int rc = ngs_snapshot_load(h_, first_new, (uint32_t)nn, g8.data(), f8.data(), nullptr);
+        for (size_t k = 0; k < nn && rc == NGS_OK; k++)
+            if (new_g[k] > NGS_MAX_GPUS) rc = ngs_node_set_wide(h_, first_new + (uint32_t)k, new_g[k], new_free.data() + k * kRowCells, nullptr);
+        if (rc != NGS_OK) {
             const Error e = ngs_last_error(h_);
             for (size_t i = 0; i < n; i++)
                 if (cs->rows[i] != 0xFFFFFFFFu && cs->rows[i] >= first_new) cs->rows[i] = 0xFFFFFFFFu, cs->lookup_err[(uint32_t)i] = e;
@@ -590,8 +625,7 @@ AssumeResult Dealer::AssumeSet(const CandidateSet& cs, const Pod& pod, const Pol
         }
     if (lo <= hi) {
         r.free_first = lo;
-        r.free.resize((size_t)(hi - lo + 1) * 8);
-        ngs_snapshot_read(h_, lo, hi - lo + 1, nullptr, r.free.data(), nullptr);
+        read_rows(lo, hi - lo + 1, &r.free, nullptr);
     }
     return r;
 }
@@ -602,7 +636,7 @@ Error Dealer::FailureText(const CandidateSet& cs, const AssumeResult& r, size_t 
     if (!r.call_err.empty()) return r.call_err;
     if (r.reason[i] != NGS_REASON_INFEASIBLE) return "";
     const uint32_t row = cs.rows[i];
-    const int32_t* fr = r.free.data() + (size_t)(row - r.free_first) * 8;
+    const int32_t* fr = r.free.data() + (size_t)(row - r.free_first) * kRowCells;
     std::vector<int> gp(fr, fr + gpu_count_[row]);
     if (rater_ == RaterKind::Sample)  // rater.go:47
         return fmt("unexpected failure of allocation  %s on %s", DemandString(r.demand).c_str(), GPUsString(gp).c_str());
@@ -626,7 +660,7 @@ char* Dealer::PutFailureText(char* p, const CandidateSet& cs, const AssumeResult
         while (n) *p++ = tmp[--n];
     };
     const uint32_t row = cs.rows[i];
-    const int32_t* fr = r.free.data() + (size_t)(row - r.free_first) * 8;
+    const int32_t* fr = r.free.data() + (size_t)(row - r.free_first) * kRowCells;
     lit(rater_ == RaterKind::Sample ? "unexpected failure of allocation  " : "can't allocate   ");  // rater.go:47 / 99,152
     memcpy(p, r.demand_text.data(), r.demand_text.size());
     p += r.demand_text.size();
@@ -699,8 +733,8 @@ Error Dealer::Bind(const std::string& node, Pod* pod, const PolicySpec& spec, bo
     std::vector<int32_t> gpu(demand.size() ? demand.size() : 1);
     int rc = ngs_bind(h_, row, demand.data(), (int)demand.size(), policy(), has_load ? &L : nullptr, gpu.data(), nullptr);
     if (rc == NGS_ERR_INFEASIBLE) {  // node.go:75
-        std::vector<int32_t> fr(8);
-        ngs_snapshot_read(h_, row, 1, nullptr, fr.data(), nullptr);
+        std::vector<int32_t> fr;
+        read_rows(row, 1, &fr, nullptr);
         std::vector<int> gp(fr.begin(), fr.begin() + gpu_count_[row]);
         return fmt("assume %s on %s failed", DemandString(demand).c_str(), GPUsString(gp).c_str());
     }
@@ -729,8 +763,8 @@ Error Dealer::Allocate(const Pod& pod) {  // dealer.go:205-228
     if (!e.empty()) return e;
     int rc = ngs_node_apply(h_, row, idx.data(), demand.data(), (int)demand.size(), +1);
     if (rc != NGS_OK) {  // allocate.go:113: "can't apply plan %v on %s" with plan = &Plan{Demand, GPUIndexes, Score}
-        std::vector<int32_t> fr(8);
-        ngs_snapshot_read(h_, row, 1, nullptr, fr.data(), nullptr);
+        std::vector<int32_t> fr;
+        read_rows(row, 1, &fr, nullptr);
         std::vector<int> gp(fr.begin(), fr.begin() + gpu_count_[row]);
         return fmt("can't apply plan &{%s %s 0} on %s", DemandString(demand).c_str(), IntsString(idx).c_str(), GPUsString(gp).c_str());
     }
@@ -778,18 +812,18 @@ std::map<std::string, std::vector<int>> Dealer::Status() {  // dealer.go:321-323
     std::map<std::string, std::vector<int>> out;
     const uint32_t n = (uint32_t)names_.size();
     if (n == 0) return out;
-    std::vector<int32_t> fr((size_t)n * 8);
-    if (ngs_snapshot_read(h_, 0, n, nullptr, fr.data(), nullptr) != NGS_OK) return out;
-    for (uint32_t r = 0; r < n; r++) out[names_[r]] = std::vector<int>(fr.begin() + r * 8, fr.begin() + r * 8 + gpu_count_[r]);
+    std::vector<int32_t> fr;
+    if (!read_rows(0, n, &fr, nullptr)) return out;
+    for (uint32_t r = 0; r < n; r++) out[names_[r]] = std::vector<int>(fr.begin() + (size_t)r * kRowCells, fr.begin() + (size_t)r * kRowCells + gpu_count_[r]);
     return out;
 }
 
 std::string Dealer::StatusJSON() {  // routes.go:212-240
     std::lock_guard<std::recursive_mutex> lock(mu_);
     const uint32_t n = (uint32_t)names_.size();
-    std::vector<int32_t> fr((size_t)n * 8);
-    std::vector<int8_t> rl((size_t)n * 8);
-    if (n && ngs_snapshot_read(h_, 0, n, nullptr, fr.data(), rl.data()) != NGS_OK) return "{}";
+    std::vector<int32_t> fr;
+    std::vector<int8_t> rl;
+    if (!read_rows(0, n, &fr, &rl)) return "{}";
     std::vector<uint32_t> order(n);
     for (uint32_t r = 0; r < n; r++) order[r] = r;
     std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return names_[a] < names_[b]; });  // Go sorts map keys
@@ -803,8 +837,8 @@ std::string Dealer::StatusJSON() {  // routes.go:212-240
         out += ",\"GPUs\":[";
         for (int g = 0; g < gpu_count_[r]; g++) {
             if (g) out += ",";
-            out += "{\"Percent\":" + std::to_string(fr[(size_t)r * 8 + g]) + ",\"PercentTotal\":100,\"RemainLoad\":" +
-                   std::to_string((int)rl[(size_t)r * 8 + g]) + "}";
+            out += "{\"Percent\":" + std::to_string(fr[(size_t)r * kRowCells + g]) + ",\"PercentTotal\":100,\"RemainLoad\":" +
+                   std::to_string((int)rl[(size_t)r * kRowCells + g]) + "}";
         }
         out += "],\"PlanCache\":{}}";
     }

@@ -24,6 +24,8 @@
 
 namespace ngs_host {
 
+constexpr int kRowCells = NGS_MAX_GPUS_WIDE;  // cells per row in the host-side copies of snapshot rows
+
 // v1.Container / v1.Pod / v1.Node, reduced
 struct Container {
     std::string name;
@@ -104,7 +106,7 @@ struct AssumeResult {
     std::vector<int8_t> reason;              // NGS_REASON_*
     std::vector<int32_t> demand, plan, n_emitted;
     std::string demand_text;                 // DemandString(demand), shared by every failure message
-    std::vector<int32_t> free;               // rows [free_first, free_first + free.size()/8) read back once, for the messages
+    std::vector<int32_t> free;               // rows [free_first, free_first + free.size()/kRowCells) read back once, for the messages
     uint32_t free_first = 0;
     Error call_err;                          // the C ABI call itself failed: every node reports it
 };
@@ -215,6 +217,7 @@ class Dealer {
 
     int policy() const;
     Error getNodeInfo(const std::string& name, uint32_t* row);  // dealer.go:271-301
+    bool read_rows(uint32_t lo, uint32_t n, std::vector<int32_t>* fr, std::vector<int8_t>* rl) const;  // kRowCells per row
     void replay_assumed_pods(const std::string& name, int G, int32_t* row_free);  // dealer.go:287-299 on the host copy of a new row
     void replay_usage(const std::string& name, uint32_t row);                     // usage samples that arrived before the node existed
     bool load_ctx(const PolicySpec& spec, bool isLoad, ngs_load_ctx* out) const;

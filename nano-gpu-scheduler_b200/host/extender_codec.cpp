@@ -923,7 +923,7 @@ std::string ExtenderRoutes::Predicate(std::string_view body) {
                 slow.emplace_back((uint32_t)i, std::move(m));
             }
     }
-    const size_t per_msg = 64 + r.demand_text.size() + NGS_MAX_GPUS * 8 + NGS_MAX_CONTAINERS * 12;
+    const size_t per_msg = 64 + r.demand_text.size() + NGS_MAX_GPUS_WIDE * 8 + NGS_MAX_CONTAINERS * 12;
     std::string out;
     out.resize(96 + tok_bytes_ + n + n_fail * (per_msg + 2) + slow_bytes);
     char* p = &out[0];

@@ -59,7 +59,8 @@ void filter_body(int lane, void* p) {
     uint64_t k1 = 0, k2 = 0;
     uint32_t cnt = 0;
     const uint32_t WT = 32, n_iter = (a.n + WT - 1) / WT;
-    filter_pass(a.rows->S, &a.dem, (uint32_t)lane, WT, n_iter, a.n, a.node0, (uint32_t)lane, lane & 7, lane & 24, a.rows->S.feasbits, k1, k2, cnt);
+    filter_pass<false>(a.rows->S, &a.dem, (uint32_t)lane, WT, n_iter, a.n, a.node0, (uint32_t)lane, lane & 7, lane & 24, a.rows->S.feasbits, k1, k2, cnt,
+                       nullptr, nullptr, 0u);
     if (a.dem.policy != NGS_POLICY_RANDOM) {
         uint64_t m1, m2;
         warp_top2(k1, k2, m1, m2);
@@ -188,8 +189,8 @@ void k6h_eval_rows(const int32_t* free, const int32_t* G, int8_t* rl, const uint
         const int8_t* rr = rl + (size_t)r * 8;
         in.r8.x = (uint8_t)rr[0] | ((uint8_t)rr[1] << 8) | ((uint8_t)rr[2] << 16) | ((uint32_t)(uint8_t)rr[3] << 24);
         in.r8.y = (uint8_t)rr[4] | ((uint8_t)rr[5] << 8) | ((uint8_t)rr[6] << 16) | ((uint32_t)(uint8_t)rr[7] << 24);
-        RowEval ev = plan ? eval_row_values<true>(T, r, in, &dem, lp, true, use_pair ? pair : nullptr)
-                          : eval_row_values<false>(T, r, in, &dem, lp, true, use_pair ? pair : nullptr);
+        RowEval ev = plan ? eval_row_values<true>(T, r, in, &dem, lp, true, use_pair ? pair : nullptr, nullptr)
+                          : eval_row_values<false>(T, r, in, &dem, lp, true, use_pair ? pair : nullptr, nullptr);
         const bool ok = ev.known && ev.feasible;
         feasible[r] = ok ? 1 : 0;
         score[r] = ok ? ev.score : NGS_SCORE_MIN;

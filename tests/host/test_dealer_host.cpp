@@ -289,6 +289,48 @@ static void TestAllocateFromAnnotationsAndRebuild() {
                  "------resource status after allocate for default/pod-new------\nnode n: (10)(100)(50)(100)\n------------\n");
 }
 
+// a node with 12 GPUs (capacity 1200: pkg/utils/node.go:8-14); expected values from the oracle
+static void TestTwelveGpuNode() {
+    FakeCluster fc;
+    fc.add("wide", 12);
+    fc.add("small", 4);
+    fc.assumed["wide"].push_back(MockPodWithPlan({60, 100}, {10, 3}, "wide", "old"));  // replayed onto cards 10 and 3 (dealer.go:287-299)
+    Dealer d(&fc, RaterKind::Binpack, 16);
+    auto r = d.Assume({"wide", "small"}, MockPodWithDemand({50, 50, 30}), PolicySpec{}, false);
+    CHECK(r.first[0] && r.first[1]);
+    const std::vector<int> start{100, 100, 100, 0, 100, 100, 100, 100, 100, 100, 40, 100};
+    CHECK((d.Status()["wide"] == start));
+    std::vector<int> sc = d.Score({"wide", "small"}, MockPodWithDemand({50, 50, 30}), PolicySpec{}, false);
+    CHECK(sc[0] == 1 && sc[1] == -4);  // int(160/1200*100) - 12; 0 - 4
+    // eleven full cards asked, ten there: the message quotes all twelve cells and the ten indexes placed so far
+    std::vector<int> eleven(11, 100);
+    auto f = d.Assume({"wide"}, MockPodWithDemand(eleven), PolicySpec{}, false);
+    CHECK(!f.first[0]);
+    CHECK_EQ_STR(f.second[0],
+                 "can't allocate   [(100) (100) (100) (100) (100) (100) (100) (100) (100) (100) (100)] on "
+                 "(100)(100)(100)(0)(100)(100)(100)(100)(100)(100)(40)(100): indexes=[0 1 2 5 6 7 8 9 4 11]");
+    Pod p = MockPodWithDemand({50, 50, 30}, "p1");
+    p.node_name = "wide";
+    CHECK(d.Bind("wide", &p, PolicySpec{}, false).empty());
+    CHECK((plan_of(p) == std::vector<int>{0, 0, 10}));
+    std::vector<int> after = start;
+    after[0] = 0;
+    after[10] = 10;
+    CHECK((d.Status()["wide"] == after));
+    Pod big = MockPodWithPlan({20}, {10}, "wide", "big");
+    CHECK_EQ_STR(d.Allocate(big), "can't apply plan &{[(20)] [10] 0} on (0)(100)(100)(0)(100)(100)(100)(100)(100)(100)(10)(100)");  // allocate.go:113
+    Pod fits = MockPodWithPlan({70}, {11}, "wide", "fits");
+    CHECK(d.Allocate(fits).empty());
+    after[11] = 30;
+    CHECK((d.Status()["wide"] == after));
+    CHECK(d.Release(p).empty());
+    after[0] = 100;
+    after[10] = 40;
+    CHECK((d.Status()["wide"] == after));
+    CHECK(d.StatusJSON().find("\"wide\":{\"Rater\":{},\"Name\":\"wide\",\"GPUs\":[{\"Percent\":100,") != std::string::npos);
+    CHECK(d.StatusJSON().find("{\"Percent\":40,\"PercentTotal\":100,\"RemainLoad\":0},{\"Percent\":30,\"PercentTotal\":100,\"RemainLoad\":0}],") != std::string::npos);
+}
+
 static void TestLoadAwareScoring() {
     FakeCluster fc;
     fc.add("busy", 2);
@@ -457,6 +499,7 @@ int main() {
     TestBindCommitFailureLeavesPodUnknown();
     TestScheduleCycleAndRelease();
     TestAllocateFromAnnotationsAndRebuild();
+    TestTwelveGpuNode();
     TestLoadAwareScoring();
     TestAnnotatorNodeIngestion();
     TestControllerPodEvents();

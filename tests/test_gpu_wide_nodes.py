@@ -204,7 +204,56 @@ def test_single_pod_scheduling_call_on_mixed_widths(ngs, policy):
         assert_same_nodes(oc, d, n)
 
 
-def test_limits_and_the_batch_kernel(ngs):
+@pytest.mark.parametrize("policy", ["binpack", "spread", "random", "mixed"])
+@pytest.mark.parametrize("n", [700, 40000])
+def test_batches_on_mixed_widths(ngs, policy, n):
+    """ngs_schedule_batch (K6): wide rows are filtered, planned and bound from the global tables, in order with the others"""
+    oc, d, _ = mixed_pair(ngs, n, 1234 + n, p_used=0.5, min_g=5)
+    rng = np.random.default_rng(8)
+    P = 600
+    pc = np.zeros((P, 6), dtype=np.int32)
+    nc = rng.integers(1, 7, P).astype(np.int32)
+    for p in range(P):
+        pc[p, : nc[p]] = rng.integers(0, 13, nc[p]) * 5
+    pol = rng.integers(0, 3, P).astype(np.int32) if policy == "mixed" else np.full(P, POL[policy], dtype=np.int32)
+    with d:
+        for lo in (0, 300):  # two calls: the second starts from what the first left in the tables
+            a = d.schedule_batch(pc[lo:lo + 300], nc[lo:lo + 300], pol[lo:lo + 300], seed=3, seq0=lo)
+            b = oc.schedule_batch(pc[lo:lo + 300], nc[lo:lo + 300], pol[lo:lo + 300], seed=3, seq0=lo)
+            assert np.array_equal(a[0], b[0]), np.flatnonzero(a[0] != b[0])[:5]
+            assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+        assert_same_nodes(oc, d, min(n, 3000))
+
+
+@pytest.mark.parametrize("policy", ["binpack", "spread"])
+def test_load_aware_batches_on_mixed_widths(ngs, policy):
+    n = 1200
+    oc, d, widths = mixed_pair(ngs, n, 4321, p_used=0.5, min_g=7)
+    rng = np.random.default_rng(13)
+    lg, lo_ = load_ctx_pair(ngs)
+    with d:
+        for i in range(n):
+            for m in (0, 1):
+                d.load_add_node(i, m)
+                oc.load_add_node(i, m)
+                for card in range(int(widths[i])):
+                    if rng.random() < 0.3:
+                        continue
+                    v = float(rng.integers(0, 101)) / 100.0
+                    ts = NOW_S - int(rng.integers(0, 400))
+                    d.load_update(i, m, card, v, ts)
+                    oc.load_update(i, m, card, v, ts)
+        P = 200
+        pc = (rng.integers(0, 9, (P, 3)) * 5).astype(np.int32)
+        nc = np.full(P, 3, dtype=np.int32)
+        pol = np.full(P, POL[policy], dtype=np.int32)
+        a = d.schedule_batch(pc, nc, pol, load=lg)
+        b = oc.schedule_batch(pc, nc, pol, load=lo_)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+        assert_same_nodes(oc, d, n)
+
+
+def test_limits(ngs):
     with ngs.GpuDealer(64, device=0) as d:
         with pytest.raises(ngs.NgsError) as e:
             d.node_upsert(0, 13)
@@ -214,16 +263,9 @@ def test_limits_and_the_batch_kernel(ngs):
         gc[5] = 9
         with pytest.raises(ngs.NgsError):  # the bulk arrays are 8 cells wide
             d.snapshot_load(gc)
-        pc = np.full((4, 1), 50, dtype=np.int32)
-        nc = np.ones(4, dtype=np.int32)
-        d.schedule_batch(pc, nc, np.zeros(4, dtype=np.int32))  # fine: no wide node yet
         d.node_upsert(7, 12)
         g, fr, rl = d.node_get_wide(7)
         assert g == 12 and fr.tolist() == [100] * 12 and rl.tolist() == [0] * 12
-        before = [d.node_get_wide(i)[1].tolist() for i in range(64)]
-        with pytest.raises(ngs.NgsError) as e:
-            d.schedule_batch(pc, nc, np.zeros(4, dtype=np.int32))
-        assert e.value.status == ngs.ERR_UNSUPPORTED
-        assert before == [d.node_get_wide(i)[1].tolist() for i in range(64)]  # refused before anything was bound
-        d.node_upsert(7, 8)  # the node shrinks: the batch kernel takes the snapshot again
-        d.schedule_batch(pc, nc, np.zeros(4, dtype=np.int32))
+        d.node_upsert(7, 8)  # the node shrinks back
+        g, fr, rl = d.node_get_wide(7)
+        assert g == 8 and fr.tolist() == [100] * 8 + [0] * 4
