@@ -37,6 +37,19 @@ def main():
         oc.load_snapshot(gcount, free)
         for m, (value, ts, absent) in enumerate(tables):
             oc.load_update_bulk(m, value, ts, ok=np.repeat(~absent[:, None], 8, axis=1).astype(np.uint8))
+    # "wide": every 17th node has 9..12 GPUs (cells 8..11 in the second table plane, one-thread evaluation)
+    wide = len(sys.argv) > 2 and sys.argv[2] == "wide"
+    wide_rows = []
+    if wide:
+        wrng = np.random.default_rng(0x12)
+        for i in range(3, N, 17):
+            G = int(wrng.integers(9, 13))
+            fr = np.where(wrng.random(G) < 0.5, wrng.integers(0, 21, G) * 5, 100).astype(np.int32)
+            wide_rows.append(i)
+            if lo <= i < hi:
+                sd.local.node_set_wide(i, G, fr)
+            if rank == 0:
+                oc.node_set(i, fr)
     failures = 0
     seq = 0
     for rnd, (policy, load_on, P) in enumerate([(0, False, 300), (1, False, 300), (2, False, 200), (0, True, 300), (None, False, 300),
@@ -93,6 +106,22 @@ def main():
         if not np.array_equal(got, ofr):
             failures += 1
             print("snapshot MISMATCH", flush=True)
+    if wide:  # ... all twelve cells of the wide nodes
+        mine = np.zeros((len(wide_rows), 12), dtype=np.int32)
+        for k, i in enumerate(wide_rows):
+            if lo <= i < hi:
+                mine[k] = sd.local.node_get_wide(i)[1]
+        t = torch.from_numpy(mine).cuda()
+        dist.all_reduce(t)  # every row is non-zero on its owner only
+        if rank == 0:
+            got = t.cpu().numpy()
+            for k, i in enumerate(wide_rows):
+                G, ofr, _ = oc.node_get(i)
+                if got[k, :G].tolist() != ofr.tolist():
+                    failures += 1
+                    print(f"wide node {i}: {got[k]} vs {ofr}", flush=True)
+                    break
+    if rank == 0:
         print("SHARDED OK" if failures == 0 else f"SHARDED FAILED ({failures})", flush=True)
     sd.close()
     dist.destroy_process_group()
