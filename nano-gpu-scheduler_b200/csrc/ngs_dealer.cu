@@ -22,6 +22,9 @@
 #include <cuda_runtime.h>
 
 #include <pthread.h>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 
 #include <cmath>
 #include <atomic>
@@ -74,12 +77,10 @@ struct ngs_dealer {
     BindResult* h_bind = nullptr;  // mapped pinned: k_bind writes its answer here, the host polls the status word
     // verb staging in mapped pinned memory: the scan kernels write feasible / reason / score straight into host memory
     // and raise a flag; a call needs no copy command and no stream synchronisation
-    uint8_t* h_vfeas = nullptr;
     int8_t* h_vreason = nullptr;
     int32_t* h_vscore = nullptr;
     int32_t* h_vflag = nullptr;
-    uint8_t* d_vfeas = nullptr;  // device aliases
-    int8_t* d_vreason = nullptr;
+    int8_t* d_vreason = nullptr;  // device aliases
     int32_t* d_vscore = nullptr;
     int32_t* d_vflag = nullptr;
     uint32_t* d_vticket = nullptr;
@@ -207,18 +208,38 @@ uint32_t demand_generation(ngs_dealer* h, const PodDemand& pd, bool load_on) {
 int ensure_verb_stage(ngs_dealer* h, size_t n) {
     if (n <= h->vstage_cap) return NGS_OK;
     const size_t cap = n < 4096 ? 4096 : n;
-    cudaFreeHost(h->h_vfeas); cudaFreeHost(h->h_vreason); cudaFreeHost(h->h_vscore);
-    h->h_vfeas = nullptr; h->h_vreason = nullptr; h->h_vscore = nullptr;
+    cudaFreeHost(h->h_vreason); cudaFreeHost(h->h_vscore);
+    h->h_vreason = nullptr; h->h_vscore = nullptr;
     h->vstage_cap = 0;
     h->sc_valid = false;
-    CU(h, cudaHostAlloc(&h->h_vfeas, cap, cudaHostAllocMapped));
     CU(h, cudaHostAlloc(&h->h_vreason, cap, cudaHostAllocMapped));
     CU(h, cudaHostAlloc(&h->h_vscore, cap * 4, cudaHostAllocMapped));
-    CU(h, cudaHostGetDevicePointer(&h->d_vfeas, h->h_vfeas, 0));
     CU(h, cudaHostGetDevicePointer(&h->d_vreason, h->h_vreason, 0));
     CU(h, cudaHostGetDevicePointer(&h->d_vscore, h->h_vscore, 0));
     h->vstage_cap = cap;
     return NGS_OK;
+}
+
+// feasible[i] = (status[i] == NGS_REASON_OK), eight nodes per step (NGS_REASON_OK is 0: a byte-is-zero test in a 64-bit word)
+static_assert(NGS_REASON_OK == 0, "expand_feasible tests for zero bytes");
+void expand_feasible(uint8_t* feasible, const int8_t* status, size_t n) {
+    const uint64_t lo7 = 0x7F7F7F7F7F7F7F7FULL, hi = 0x8080808080808080ULL;
+    size_t i = 0;
+#if defined(__SSE2__)
+    const __m128i zero = _mm_setzero_si128(), one = _mm_set1_epi8(1);
+    for (; i + 16 <= n; i += 16) {
+        const __m128i x = _mm_loadu_si128(reinterpret_cast<const __m128i*>(status + i));
+        _mm_storeu_si128(reinterpret_cast<__m128i*>(feasible + i), _mm_and_si128(_mm_cmpeq_epi8(x, zero), one));
+    }
+#endif
+    for (; i + 8 <= n; i += 8) {
+        uint64_t x;
+        memcpy(&x, status + i, 8);
+        const uint64_t nonzero = (((x & lo7) + lo7) | x) & hi;  // bit 7 of every byte that is not 0
+        const uint64_t ok = (nonzero ^ hi) >> 7;                 // 1 in every byte that is 0
+        memcpy(feasible + i, &ok, 8);
+    }
+    for (; i < n; i++) feasible[i] = status[i] == NGS_REASON_OK ? 1 : 0;
 }
 
 // wait for a verb kernel's flag in mapped host memory (no stream synchronisation); keeps an eye on the stream
@@ -549,7 +570,7 @@ int ngs_destroy(ngs_dealer* h) {
     cudaFree(h->T.free_hi); cudaFree(h->T.rl_hi); cudaFree(h->T.tenths_hi); cudaFree(h->T.ts_hi);
     cudaFree(h->d_idx); cudaFree(h->d_feas); cudaFree(h->d_reason); cudaFree(h->d_score); cudaFree(h->d_plan); cudaFree(h->d_nem);
     cudaFreeHost(h->h_bind); cudaFree(h->d_small); cudaFreeHost(h->h_small);
-    cudaFreeHost(h->h_vfeas); cudaFreeHost(h->h_vreason); cudaFreeHost(h->h_vscore); cudaFreeHost(h->h_vflag); cudaFree(h->d_vticket);
+    cudaFreeHost(h->h_vreason); cudaFreeHost(h->h_vscore); cudaFreeHost(h->h_vflag); cudaFree(h->d_vticket);
     cudaFree(h->d_dem); cudaFree(h->d_keys); cudaFree(h->d_one);
     cudaFreeHost(h->h_pod_in); cudaFreeHost(h->h_pod_out);
     cudaFree(h->d_err); cudaFreeHost(h->h_err);
@@ -899,8 +920,9 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
     vd.ticket = h->d_vticket;
     vd.flag = h->d_vflag;
     vd.seq = ++h->vseq;
-    uint8_t* o_feas = feasible ? h->d_vfeas : nullptr;
-    int8_t* o_reason = reason ? h->d_vreason : nullptr;
+    // one status byte per node travels (NGS_REASON_*); `feasible` is derived from it on the host
+    uint8_t* o_feas = nullptr;
+    int8_t* o_reason = (reason || feasible) ? h->d_vreason : nullptr;
     int32_t* o_score = h->d_vscore;
     if (!idx && mode == MODE_ASSUME && !want_plan) {
         rc = launch_scan(h, n, pd, lp, gen, o_feas, o_reason, o_score, vd);
@@ -919,7 +941,7 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
     }
     rc = wait_flag(h, h->h_vflag, vd.seq, "scan kernel");
     if (rc) return rc;
-    if (feasible) memcpy(feasible, h->h_vfeas, n);
+    if (feasible) expand_feasible(feasible, h->h_vreason, n);
     if (reason) memcpy(reason, h->h_vreason, n);
     if (score) memcpy(score, h->h_vscore, (size_t)n * 4);
     if (mode == MODE_ASSUME) {  // (a Score pass serves cached values per node: not a filter call's result)
@@ -931,7 +953,7 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
     }
     h->stats.kernel_launches++;
     h->stats.node_evals += n;
-    h->stats.d2h_bytes += (feasible ? n : 0) + (reason ? n : 0) + (size_t)n * 4 +
+    h->stats.d2h_bytes += ((feasible || reason) ? n : 0) + (size_t)n * 4 +
                           (plan ? (size_t)n * n_containers * 4 : 0) + (n_emitted ? (size_t)n * 4 : 0);
     return NGS_OK;
 }

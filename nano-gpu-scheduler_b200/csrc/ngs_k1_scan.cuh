@@ -26,6 +26,24 @@ __device__ __forceinline__ void verb_done(const VerbDone& vd) {
     }
 }
 
+// One status byte per row from every thread of a 256-thread CTA (rows base + threadIdx.x, base a multiple of 256), written
+// as two 128-byte warp stores.  The verbs' outputs go straight into mapped host memory, where what counts is the bytes one
+// warp instruction writes: 32 (a warp of byte stores) drain at a third of the rate of 128 (profiles/r02/mapped_write_bench.txt).
+// Every thread of the CTA must call; `in` = the thread's row exists.
+__device__ __forceinline__ void store_codes_cta(int8_t* __restrict__ out, uint32_t base, uint32_t n, bool in, int code, uint8_t* s_code) {
+    s_code[threadIdx.x] = in ? (uint8_t)code : (uint8_t)0;
+    __syncthreads();
+    if (threadIdx.x < 64) {
+        const uint32_t k = base + threadIdx.x * 4;
+        if (k + 3 < n) {
+            *reinterpret_cast<uint32_t*>(out + k) = *reinterpret_cast<const uint32_t*>(s_code + threadIdx.x * 4);
+        } else {
+            for (uint32_t j = 0; j < 4 && k + j < n; j++) out[k + j] = (int8_t)s_code[threadIdx.x * 4 + j];
+        }
+    }
+    __syncthreads();  // (s_code is rewritten in the caller's next round)
+}
+
 // K1.  DealerImpl.Assume / DealerImpl.Score fan-out (dealer.go:109-134, 138-153): one thread
 // per candidate.  MODE_ASSUME recomputes every candidate (cleanPlan + Assume, dealer.go:123-124);
 // MODE_SCORE serves NodeInfo.Score (node.go:59-68) from the per-node cache when it holds a
@@ -41,14 +59,16 @@ __global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables
     __shared__ SortedDemand dem;
     __shared__ double s_pair[121];
     __shared__ WideCtx s_wcx;
+    __shared__ __align__(16) uint8_t s_code[256];
     if (threadIdx.x == 0) sort_demand(pd.percent, pd.n, pd.policy, &dem);
     wide_ctx_fill(&s_wcx, T, lp, threadIdx.x == 32);
     if (lp.enabled) fill_usage_pair_table(s_pair, threadIdx.x, blockDim.x);
     __syncthreads();
     const int C = pd.n;
-    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
-        const uint32_t gidx = idx ? idx[k] : T.first + k;
-        const uint32_t row = gidx - T.first;
+    // (CTA-uniform trip count: the status bytes below are stored by the CTA as a whole)
+    for (uint32_t k0 = blockIdx.x * blockDim.x; k0 < n; k0 += gridDim.x * blockDim.x) {
+        const uint32_t k = k0 + threadIdx.x;
+        const bool in = k < n;
         RowEval ev;
         ev.known = false;
         ev.feasible = false;
@@ -56,12 +76,17 @@ __global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables
         ev.emit = 0;
         ev.n_emit = 0;
         bool cached = false;
-        if (gidx >= T.first && row < T.n) {
-            if (mode == MODE_SCORE && T.tag[row] == gen && T.gcount[row] != 0) {
-                ev.known = ev.feasible = cached = true;
-                ev.score = T.cscore[row];
-            } else {
-                ev = eval_row_global<PLAN>(T, row, &dem, lp, true, &s_wcx, s_pair);
+        uint32_t row = 0;
+        if (in) {
+            const uint32_t gidx = idx ? idx[k] : T.first + k;
+            row = gidx - T.first;
+            if (gidx >= T.first && row < T.n) {
+                if (mode == MODE_SCORE && T.tag[row] == gen && T.gcount[row] != 0) {
+                    ev.known = ev.feasible = cached = true;
+                    ev.score = T.cscore[row];
+                } else {
+                    ev = eval_row_global<PLAN>(T, row, &dem, lp, true, &s_wcx, s_pair);
+                }
             }
         }
         const bool ok = ev.known && ev.feasible;
@@ -76,10 +101,10 @@ __global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables
                 T.tag[row] = 0;  // dealer.go:123 cleared it, the failed Assume caches nothing
             }
         }
-        if (feasible) feasible[k] = ok ? 1 : 0;
-        if (reason) reason[k] = !ev.known ? NGS_REASON_UNKNOWN_NODE : (ok ? NGS_REASON_OK : NGS_REASON_INFEASIBLE);
-        if (score) score[k] = ok ? ev.score : NGS_SCORE_MIN;
-        if (PLAN) {
+        if (feasible && in) feasible[k] = ok ? 1 : 0;
+        if (reason) store_codes_cta(reason, k0, n, in, !ev.known ? NGS_REASON_UNKNOWN_NODE : (ok ? NGS_REASON_OK : NGS_REASON_INFEASIBLE), s_code);
+        if (score && in) score[k] = ok ? ev.score : NGS_SCORE_MIN;
+        if (PLAN && in) {
             if (plan) {
                 int32_t* out = plan + (size_t)k * C;
                 if (ev.known) write_plan(out, &dem, dem.policy != NGS_POLICY_RANDOM, ok, ev.emit, ev.n_emit);
@@ -145,6 +170,7 @@ __global__ void __launch_bounds__(SCAN_TILE, NGS_SCAN_BLOCKS) k_scan_tma(Tables 
     __shared__ SortedDemand dem;
     __shared__ __align__(8) uint64_t bars[NGS_SCAN_STAGES];
     __shared__ WideCtx s_wcx;
+    __shared__ __align__(16) uint8_t s_code[SCAN_TILE];
     const uint32_t tid = threadIdx.x;
     const uint32_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     const bool want_rl = !T.rl_zero;
@@ -196,13 +222,14 @@ __global__ void __launch_bounds__(SCAN_TILE, NGS_SCAN_BLOCKS) k_scan_tma(Tables 
             const uint32_t next = tile + NGS_SCAN_STAGES * gridDim.x;
             if (next < ntiles) issue(next, stage);
         }
-        if (row < n) {
-            const RowEval ev = eval_row_values<false>(T, row, in, &dem, lp, true, nullptr, &s_wcx);
-            const bool ok = ev.known && ev.feasible;
-            if (feasible) feasible[row] = ok ? 1 : 0;
-            if (reason) reason[row] = !ev.known ? NGS_REASON_UNKNOWN_NODE : (ok ? NGS_REASON_OK : NGS_REASON_INFEASIBLE);
-            if (score) score[row] = ok ? ev.score : NGS_SCORE_MIN;
-        }
+        RowEval ev;
+        ev.known = ev.feasible = false;
+        ev.score = NGS_SCORE_MIN;
+        if (row < n) ev = eval_row_values<false>(T, row, in, &dem, lp, true, nullptr, &s_wcx);
+        const bool ok = ev.known && ev.feasible;
+        if (feasible && row < n) feasible[row] = ok ? 1 : 0;
+        if (reason) store_codes_cta(reason, tile * SCAN_TILE, n, row < n, !ev.known ? NGS_REASON_UNKNOWN_NODE : (ok ? NGS_REASON_OK : NGS_REASON_INFEASIBLE), s_code);
+        if (score && row < n) score[row] = ok ? ev.score : NGS_SCORE_MIN;
     }
     verb_done(vd);
 }
