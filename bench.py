@@ -450,7 +450,9 @@ def run_verbs(ngs, cfg, gcount, free, tables, load, local_rank, cycles=200):
     vp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
     lref = None if load is None else C.c_void_p(C.addressof(load))
     pol = C.c_int(cfg["policy"])
-    for label, idx in (("idx_null", None), ("idx_list", np.arange(n, dtype=np.uint32))):
+    vptr = C.c_void_p(0)
+    for label, idx, view in (("idx_null", None, False), ("idx_list", np.arange(n, dtype=np.uint32), False), ("idx_null_score_view", None, True)):
+        score = np.zeros(n, dtype=np.int32)
         d = ngs.GpuDealer(n, device=local_rank)
         d.snapshot_load(gcount, free)
         if cfg["load"]:
@@ -468,8 +470,13 @@ def run_verbs(ngs, cfg, gcount, free, tables, load, local_rank, cycles=200):
             t0 = time.perf_counter()
             rc = lib.ngs_assume(d._h, p_idx, C.c_uint32(n), dem, cn, pol, lref, vp(feas), vp(reason), None, None, None)
             t1 = time.perf_counter()
-            rc |= lib.ngs_score(d._h, p_idx, C.c_uint32(n), dem, cn, pol, lref, vp(score))
-            t2 = time.perf_counter()
+            if view:  # the scores read where the kernels left them (what a binding that converts them anyway does)
+                rc |= lib.ngs_score_view(d._h, p_idx, C.c_uint32(n), dem, cn, pol, lref, C.byref(vptr))
+                t2 = time.perf_counter()
+                score = np.ctypeslib.as_array(C.cast(vptr, C.POINTER(C.c_int32)), shape=(n,))
+            else:
+                rc |= lib.ngs_score(d._h, p_idx, C.c_uint32(n), dem, cn, pol, lref, vp(score))
+                t2 = time.perf_counter()
             assert rc == 0, rc
             cand = np.flatnonzero(feas)
             dt_bind = 0.0
@@ -493,7 +500,8 @@ def run_verbs(ngs, cfg, gcount, free, tables, load, local_rank, cycles=200):
                       "value": n / float(np.mean(t_cycle)), "unit": UNIT,
                       "h2d_bytes_per_cycle": (st1["h2d_bytes"] - st0["h2d_bytes"]) / cycles, "d2h_bytes_per_cycle": (st1["d2h_bytes"] - st0["d2h_bytes"]) / cycles}
     out["what"] = (f"{cycles} pod cycles of ngs_assume (feasible + reason out) + ngs_score + ngs_bind on {n} candidates, host buffers in and out, "
-                   "wall clock per C call; idx_null = the candidate list is every row in order, idx_list = an explicit index list")
+                   "wall clock per C call; idx_null = the candidate list is every row in order, idx_list = an explicit index list, "
+                   "idx_null_score_view = ngs_score_view instead of ngs_score (no copy of the scores into a caller's buffer)")
     return out
 
 

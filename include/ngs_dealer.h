@@ -167,6 +167,11 @@ int ngs_assume_dev(ngs_dealer *h, uint32_t n, const int32_t *percent, int n_cont
  * demand, else a fresh evaluation; unknown / infeasible -> NGS_SCORE_MIN. */
 int ngs_score(ngs_dealer *h, const uint32_t *idx, uint32_t n, const int32_t *percent, int n_containers, int policy,
               const ngs_load_ctx *load, int32_t *score);
+/* ngs_score without the copy into a caller's buffer: *view receives a pointer to the n scores where the kernels left them
+ * (pinned host memory owned by the handle), readable until the next call on this handle.  What a binding that converts the
+ * scores element by element anyway (HostPriorityList, priority.go:29-37) reads from directly. */
+int ngs_score_view(ngs_dealer *h, const uint32_t *idx, uint32_t n, const int32_t *percent, int n_containers, int policy,
+                   const ngs_load_ctx *load, const int32_t **view);
 /* NodeInfo.Bind (node.go:70-84): cached or fresh plan -> GPUs.Allocate -> drop the node's cache. */
 int ngs_bind(ngs_dealer *h, uint32_t idx, const int32_t *percent, int n_containers, int policy, const ngs_load_ctx *load,
              int32_t *gpu_idx_out, int32_t *score_out);

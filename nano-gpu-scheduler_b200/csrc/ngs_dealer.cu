@@ -876,8 +876,10 @@ static int launch_scan(ngs_dealer* h, uint32_t n, const PodDemand& pd, const Loa
 }
 
 static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, const int32_t* percent, int n_containers, int policy,
-                      const ngs_load_ctx* load, uint8_t* feasible, int8_t* reason, int32_t* score, int32_t* plan, int32_t* n_emitted) {
+                      const ngs_load_ctx* load, uint8_t* feasible, int8_t* reason, int32_t* score, int32_t* plan, int32_t* n_emitted,
+                      const int32_t** score_view = nullptr) {
     if (!h) return NGS_ERR_INVALID;
+    if (score_view) *score_view = nullptr;
     PodDemand pd;
     LoadParams lp;
     int rc = make_demand(h, percent, n_containers, policy, &pd);
@@ -906,7 +908,8 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
     }
     // NodeInfo.Score right after NodeInfo.Assume: the filter call's scores are still in the staging area
     if (mode == MODE_SCORE && h->sc_valid && h->sc_gen == gen && h->sc_n == n && h->sc_sig == sig && h->sc_epoch == h->epoch) {
-        memcpy(score, h->h_vscore, (size_t)n * 4);
+        if (score) memcpy(score, h->h_vscore, (size_t)n * 4);
+        if (score_view) *score_view = h->h_vscore;
         h->stats.node_evals += n;
         return NGS_OK;
     }
@@ -944,6 +947,7 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
     if (feasible) expand_feasible(feasible, h->h_vreason, n);
     if (reason) memcpy(reason, h->h_vreason, n);
     if (score) memcpy(score, h->h_vscore, (size_t)n * 4);
+    if (score_view) *score_view = h->h_vscore;
     if (mode == MODE_ASSUME) {  // (a Score pass serves cached values per node: not a filter call's result)
         h->sc_valid = true;
         h->sc_gen = gen;
@@ -995,6 +999,12 @@ int ngs_score(ngs_dealer* h, const uint32_t* idx, uint32_t n, const int32_t* per
               const ngs_load_ctx* load, int32_t* score) {
     if (!score) return NGS_ERR_INVALID;
     return run_assume(h, MODE_SCORE, idx, n, percent, n_containers, policy, load, nullptr, nullptr, score, nullptr, nullptr);
+}
+
+int ngs_score_view(ngs_dealer* h, const uint32_t* idx, uint32_t n, const int32_t* percent, int n_containers, int policy,
+                   const ngs_load_ctx* load, const int32_t** view) {
+    if (!view) return NGS_ERR_INVALID;
+    return run_assume(h, MODE_SCORE, idx, n, percent, n_containers, policy, load, nullptr, nullptr, nullptr, nullptr, nullptr, view);
 }
 
 int ngs_bind(ngs_dealer* h, uint32_t idx, const int32_t* percent, int n_containers, int policy, const ngs_load_ctx* load,

@@ -194,6 +194,22 @@ class GpuDealer:
         self._check(self._lib.ngs_score(self._h, _p(ia), n, _p(d), len(d), policy, _ref(load), _p(score)))
         return score[:n]
 
+    def score_view(self, percent, policy, idx=None, load=None, n=None):
+        """score() without the copy: a read-only array over the handle's own pinned memory, valid until the next call"""
+        d = np.ascontiguousarray(percent, dtype=np.int32)
+        if idx is None:
+            n, ia = (self.n if n is None else n), None
+        else:
+            ia = np.ascontiguousarray(idx, dtype=np.uint32)
+            n = len(ia)
+        ptr = C.c_void_p(0)
+        self._check(self._lib.ngs_score_view(self._h, _p(ia), n, _p(d), len(d), policy, _ref(load), C.byref(ptr)))
+        if n == 0:
+            return np.zeros(0, dtype=np.int32)
+        a = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_int32)), shape=(n,))
+        a.flags.writeable = False
+        return a
+
     def bind(self, idx, percent, policy, load=None):
         """-> (status, gpu_idx[C], score); status != 0 leaves the snapshot untouched."""
         d = np.ascontiguousarray(percent, dtype=np.int32)

@@ -690,10 +690,10 @@ std::vector<int> Dealer::ScoreSet(const CandidateSet& cs, const Pod& pod, const 
     if (n == 0) return scores;
     ngs_load_ctx L;
     const bool has_load = load_ctx(spec, isLoadSchedule, &L);
-    static_assert(sizeof(int) == sizeof(int32_t), "scores are read straight into the result");
-    if (ngs_score(h_, cs.all_rows ? nullptr : cs.rows.data(), (uint32_t)n, demand.data(), (int)demand.size(), policy(), has_load ? &L : nullptr,
-                  scores.data()) != NGS_OK)
-        std::fill(scores.begin(), scores.end(), NGS_SCORE_MIN);
+    const int32_t* view = nullptr;  // the scores where the kernels left them: one copy (into the result), not two
+    if (ngs_score_view(h_, cs.all_rows ? nullptr : cs.rows.data(), (uint32_t)n, demand.data(), (int)demand.size(), policy(), has_load ? &L : nullptr,
+                       &view) == NGS_OK)
+        std::copy(view, view + n, scores.begin());
     return scores;
 }
 

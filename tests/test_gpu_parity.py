@@ -960,3 +960,22 @@ def test_many_rows_per_cta_all_policies(ngs, load):
             assert np.array_equal(a, b), (what, np.flatnonzero((np.asarray(a) != np.asarray(b)).reshape(P, -1).any(axis=1))[:8])
         assert (got[0] >= 0).sum() > P // 2
         assert_same_snapshot(oc, d)
+
+
+def test_score_view_is_score_without_the_copy(ngs):
+    """ngs_score_view: the scores where the kernels left them — after a filter call (cache hit) and on its own (fresh pass)"""
+    n = 5000
+    oc, d, _, _ = make_pair(ngs, n, 0.6, 0x5C0)
+    rng = np.random.default_rng(2)
+    with d:
+        for policy in (0, 1, 2):
+            for trial in range(6):
+                dem = (rng.integers(0, 13, int(rng.integers(1, 5))) * 5).astype(np.int32)
+                want = oc.assume(dem, policy)["score"]
+                if trial % 2 == 0:
+                    d.assume(dem, policy)  # Score right after Assume: served from the filter call's scores
+                v = d.score_view(dem, policy)
+                assert not v.flags.writeable and np.array_equal(v, want)
+                idx = rng.permutation(n)[:777].astype(np.uint32)
+                assert np.array_equal(d.score_view(dem, policy, idx=idx), want[idx])
+                assert np.array_equal(d.score(dem, policy), want)
