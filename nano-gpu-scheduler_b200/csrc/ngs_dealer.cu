@@ -864,12 +864,12 @@ static int launch_scan(ngs_dealer* h, uint32_t n, const PodDemand& pd, const Loa
         int grid = (int)((n + 255) / 256);
         const int max_grid = h->num_sms * NGS_K1_BLOCKS;
         if (grid > max_grid) grid = max_grid;
-        k_assume<false><<<grid, 256, 0, h->stream>>>(h->T, nullptr, n, pd, lp, MODE_ASSUME, gen, d_feas, d_reason, d_score, nullptr, nullptr, vd);
+        (h->n_wide ? k_assume<false, true> : k_assume<false, false>)<<<grid, 256, 0, h->stream>>>(h->T, nullptr, n, pd, lp, MODE_ASSUME, gen, d_feas, d_reason, d_score, nullptr, nullptr, vd, AssumePad{});
     } else {
         const size_t smem = (size_t)NGS_SCAN_STAGES * SCAN_STAGE_BYTES;
         uint32_t grid = (uint32_t)h->num_sms * NGS_SCAN_BLOCKS;
         if (grid > ntiles) grid = ntiles;
-        k_scan_tma<<<grid, SCAN_TILE, smem, h->stream>>>(h->T, n, pd, lp, d_feas, d_reason, d_score, vd);
+        (h->n_wide ? k_scan_tma<true> : k_scan_tma<false>)<<<grid, SCAN_TILE, smem, h->stream>>>(h->T, n, pd, lp, d_feas, d_reason, d_score, vd, ScanPad{});
     }
     CU(h, cudaGetLastError());
     return NGS_OK;
@@ -931,11 +931,11 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
         rc = launch_scan(h, n, pd, lp, gen, o_feas, o_reason, o_score, vd);
         if (rc) return rc;
     } else if (want_plan)
-        k_assume<true><<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, o_feas, o_reason, o_score,
-                                                     plan ? h->d_plan : nullptr, n_emitted ? h->d_nem : nullptr, vd);
+        (h->n_wide ? k_assume<true, true> : k_assume<true, false>)<<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, o_feas, o_reason, o_score,
+                                                     plan ? h->d_plan : nullptr, n_emitted ? h->d_nem : nullptr, vd, AssumePad{});
     else
-        k_assume<false><<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, o_feas, o_reason, o_score, nullptr,
-                                                      nullptr, vd);
+        (h->n_wide ? k_assume<false, true> : k_assume<false, false>)<<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, o_feas, o_reason, o_score, nullptr,
+                                                      nullptr, vd, AssumePad{});
     CU(h, cudaGetLastError());
     if (want_plan) {  // plans (the FailedNodes texts of the host mirror) still travel by copy commands
         if (plan && n_containers > 0) CU(h, cudaMemcpyAsync(plan, h->d_plan, (size_t)n * n_containers * 4, cudaMemcpyDeviceToHost, h->stream));
@@ -1021,7 +1021,7 @@ int ngs_bind(ngs_dealer* h, uint32_t idx, const int32_t* percent, int n_containe
     constexpr int32_t BIND_PENDING = 0x7FFFFFFE;
     *reinterpret_cast<volatile int32_t*>(&h->h_bind->status) = BIND_PENDING;
     h->epoch++;  // a row changes: scores kept from the last filter call are no longer the cache's
-    k_bind<<<1, 32, 0, h->stream>>>(h->T, idx, pd, lp, gen, h->d_bind);
+    (h->n_wide ? k_bind<true> : k_bind<false>)<<<1, 32, 0, h->stream>>>(h->T, idx, pd, lp, gen, h->d_bind);
     CU(h, cudaGetLastError());
     {   // the answer arrives in mapped host memory, status word last
         volatile int32_t* st = &h->h_bind->status;
@@ -1116,10 +1116,10 @@ int ngs_schedule_batch(ngs_dealer* h, uint32_t n_pods, const int32_t* percent, c
             h->xbatch++;
         }
         if (policy[0] == NGS_POLICY_RANDOM)
-            k_schedule_one_random<<<grid, 256, 0, h->stream>>>(h->T, pd, seed + seq0, h->d_one, reinterpret_cast<uint32_t*>(h->d_one + 1),
+            (h->n_wide ? k_schedule_one_random<true> : k_schedule_one_random<false>)<<<grid, 256, 0, h->stream>>>(h->T, pd, seed + seq0, h->d_one, reinterpret_cast<uint32_t*>(h->d_one + 1),
                                                                h->d_pod_out_dev, max_c, sh);
         else
-            k_schedule_one<<<grid, 256, 0, h->stream>>>(h->T, pd, lp, h->d_one, h->d_pod_out_dev, max_c, sh);
+            (h->n_wide ? k_schedule_one<true> : k_schedule_one<false>)<<<grid, 256, 0, h->stream>>>(h->T, pd, lp, h->d_one, h->d_pod_out_dev, max_c, sh, OnePad{});
         CU(h, cudaGetLastError());
         for (uint32_t spins = 1; hout[0] == ONE_PENDING; spins++) {
 #if defined(__x86_64__) || defined(__i386__)

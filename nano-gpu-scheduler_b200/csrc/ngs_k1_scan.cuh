@@ -51,17 +51,21 @@ __device__ __forceinline__ void store_codes_cta(int8_t* __restrict__ out, uint32
 #ifndef NGS_K1_BLOCKS
 #define NGS_K1_BLOCKS 4  // resident 256-thread blocks per SM for the feasibility/score scan
 #endif
-template <bool PLAN>
+// WIDE: the snapshot holds nodes of 9..12 GPUs (ngs_wide.cuh); the host launches those instantiations only then.
+using AssumePad = LaunchPad<56>;
+static_assert(param_block_bytes<Tables, const uint32_t*, uint32_t, PodDemand, LoadParams, int, uint32_t, uint8_t*, int8_t*, int32_t*, int32_t*, int32_t*,
+                                VerbDone, AssumePad>() % 64 == 32, "see LaunchPad");
+template <bool PLAN, bool WIDE>
 __global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables T, const uint32_t* __restrict__ idx, uint32_t n, PodDemand pd, LoadParams lp,
                                                 int mode, uint32_t gen, uint8_t* __restrict__ feasible,
                                                 int8_t* __restrict__ reason, int32_t* __restrict__ score,
-                                                int32_t* __restrict__ plan, int32_t* __restrict__ n_emitted, VerbDone vd) {
+                                                int32_t* __restrict__ plan, int32_t* __restrict__ n_emitted, VerbDone vd, AssumePad) {
     __shared__ SortedDemand dem;
     __shared__ double s_pair[121];
     __shared__ WideCtx s_wcx;
     __shared__ __align__(16) uint8_t s_code[256];
     if (threadIdx.x == 0) sort_demand(pd.percent, pd.n, pd.policy, &dem);
-    wide_ctx_fill(&s_wcx, T, lp, threadIdx.x == 32);
+    if (WIDE) wide_ctx_fill(&s_wcx, T, lp, threadIdx.x == 32);
     if (lp.enabled) fill_usage_pair_table(s_pair, threadIdx.x, blockDim.x);
     __syncthreads();
     const int C = pd.n;
@@ -85,7 +89,7 @@ __global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables
                     ev.known = ev.feasible = cached = true;
                     ev.score = T.cscore[row];
                 } else {
-                    ev = eval_row_global<PLAN>(T, row, &dem, lp, true, &s_wcx, s_pair);
+                    ev = eval_row_global<PLAN, WIDE>(T, row, &dem, lp, true, &s_wcx, s_pair);
                 }
             }
         }
@@ -163,9 +167,12 @@ __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem
                  : "memory");
 }
 
+using ScanPad = LaunchPad<24>;
+static_assert(param_block_bytes<Tables, uint32_t, PodDemand, LoadParams, uint8_t*, int8_t*, int32_t*, VerbDone, ScanPad>() % 64 == 32, "see LaunchPad");
+template <bool WIDE>
 __global__ void __launch_bounds__(SCAN_TILE, NGS_SCAN_BLOCKS) k_scan_tma(Tables T, uint32_t n, PodDemand pd, LoadParams lp_in,
                                                                        uint8_t* __restrict__ feasible, int8_t* __restrict__ reason,
-                                                                       int32_t* __restrict__ score, VerbDone vd) {
+                                                                       int32_t* __restrict__ score, VerbDone vd, ScanPad) {
     extern __shared__ __align__(128) unsigned char tiles[];
     __shared__ SortedDemand dem;
     __shared__ __align__(8) uint64_t bars[NGS_SCAN_STAGES];
@@ -198,7 +205,7 @@ __global__ void __launch_bounds__(SCAN_TILE, NGS_SCAN_BLOCKS) k_scan_tma(Tables 
         }
     }
     if (tid == 32) sort_demand(pd.percent, pd.n, pd.policy, &dem);
-    wide_ctx_fill(&s_wcx, T, lp, tid == 64);
+    if (WIDE) wide_ctx_fill(&s_wcx, T, lp, tid == 64);
     __syncthreads();
 
     uint32_t it = 0;
@@ -225,7 +232,7 @@ __global__ void __launch_bounds__(SCAN_TILE, NGS_SCAN_BLOCKS) k_scan_tma(Tables 
         RowEval ev;
         ev.known = ev.feasible = false;
         ev.score = NGS_SCORE_MIN;
-        if (row < n) ev = eval_row_values<false>(T, row, in, &dem, lp, true, nullptr, &s_wcx);
+        if (row < n) ev = eval_row_values<false, WIDE>(T, row, in, &dem, lp, true, nullptr, &s_wcx);
         const bool ok = ev.known && ev.feasible;
         if (feasible && row < n) feasible[row] = ok ? 1 : 0;
         if (reason) store_codes_cta(reason, tile * SCAN_TILE, n, row < n, !ev.known ? NGS_REASON_UNKNOWN_NODE : (ok ? NGS_REASON_OK : NGS_REASON_INFEASIBLE), s_code);

@@ -10,12 +10,15 @@ struct BindResult {
 
 // K3.  NodeInfo.Bind (node.go:70-84) for one row: cached or fresh plan, GPUs.Allocate, cleanPlan.
 // res may be mapped host memory: the status word is written last, behind a system-wide fence, and the host polls it
+static_assert(param_block_bytes<Tables, uint32_t, PodDemand, LoadParams, uint32_t, BindResult*>() % 64 >= 20 &&
+                  param_block_bytes<Tables, uint32_t, PodDemand, LoadParams, uint32_t, BindResult*>() % 64 <= 44, "see LaunchPad");
+template <bool WIDE>
 __global__ void k_bind(Tables T, uint32_t gidx, PodDemand pd, LoadParams lp, uint32_t gen, BindResult* res_out) {
     __shared__ SortedDemand dem;
     __shared__ BindResult s_res;
     __shared__ WideCtx s_wcx;
     if (threadIdx.x != 0) return;
-    wide_ctx_fill(&s_wcx, T, lp, true);
+    if (WIDE) wide_ctx_fill(&s_wcx, T, lp, true);
     BindResult* res = &s_res;
     struct Publish {  // whatever way the body returns: copy the result out, status last
         BindResult* from;
@@ -36,7 +39,7 @@ __global__ void k_bind(Tables T, uint32_t gidx, PodDemand pd, LoadParams lp, uin
         return;
     }
     const bool hit = T.tag[row] == gen;
-    RowEval ev = eval_row_global<true>(T, row, &dem, lp, !hit, &s_wcx);
+    RowEval ev = eval_row_global<true, WIDE>(T, row, &dem, lp, !hit, &s_wcx);
     if (!ev.feasible) {  // node.go:74-76
         res->status = NGS_ERR_INFEASIBLE;
         return;
@@ -45,7 +48,7 @@ __global__ void k_bind(Tables T, uint32_t gidx, PodDemand pd, LoadParams lp, uin
     write_plan(planv, &dem, dem.policy != NGS_POLICY_RANDOM, true, ev.emit, ev.n_emit);
     for (int k = 0; k < pd.n; k++) {  // GPUs.Allocate (allocate.go:102-118); the plan fits by construction
         res->gpu_idx[k] = planv[k];
-        if (planv[k] >= 0) *wide_free_cell(T, row, planv[k]) -= pd.percent[k];
+        if (planv[k] >= 0) *(WIDE ? wide_free_cell(T, row, planv[k]) : T.free + (size_t)row * 8 + planv[k]) -= pd.percent[k];
     }
     res->score = hit ? T.cscore[row] : ev.score;
     T.tag[row] = 0;  // node.go:82

@@ -58,10 +58,11 @@ __device__ __forceinline__ uint32_t block_scan_256(uint32_t v, uint32_t* s_warp 
 }
 
 // SampleRater on one row: feasibility only
+template <bool WIDE>
 __device__ __forceinline__ bool sample_row_feasible(const Tables& T, uint32_t row, const SortedDemand* dem, const WideCtx* wcx) {
     const int G = T.gcount[row];
     if (G == 0) return false;
-    if (G > 8) return (eval_wide_row(wcx, row, dem, 0u).x & 1u) != 0;  // ngs_wide.cuh
+    if (G > 8) return WIDE ? (eval_wide_row(wcx, row, dem, 0u).x & 1u) != 0 : false;  // ngs_wide.cuh
     uint32_t v[8];
     ld_row8(T.free + (size_t)row * 8, v);
     int f[8];
@@ -74,6 +75,10 @@ __device__ __forceinline__ bool sample_row_feasible(const Tables& T, uint32_t ro
 // On a sharded handle the last CTA of every rank trades the rank's number of feasible nodes with the peers (the slot arrays
 // of K5); rank r's feasible nodes follow those of the ranks before it, so every rank knows which rank holds the seeded pick.
 // That rank binds it and drops node and plan into every peer's mailbox; the others wait for the mailbox.
+// WIDE: the snapshot holds nodes of 9..12 GPUs (ngs_wide.cuh); the host launches that instantiation only then, so the
+// usual one carries none of that code (it cost the latency-critical path 0.65 us per pod when it was a run-time branch)
+static_assert(param_block_bytes<Tables, PodDemand, uint64_t, OneRec*, uint32_t*, int32_t*, int, OneShard>() % 64 == 32, "see LaunchPad");
+template <bool WIDE>
 __global__ void __launch_bounds__(256, 4) k_schedule_one_random(Tables T, PodDemand pd, uint64_t seed_seq, OneRec* rec, uint32_t* cnt, int32_t* out,
                                                                 int max_c, OneShard sh) {
     __shared__ SortedDemand dem;
@@ -85,7 +90,7 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one_random(Tables T, PodDem
     __shared__ WideCtx s_wcx;
     const uint32_t tid = threadIdx.x;
     if (tid == 0) sort_demand(pd.percent, pd.n, pd.policy, &dem);
-    if (tid == 32) {
+    if (WIDE && tid == 32) {
         LoadParams off;
         off.enabled = 0;  // SampleRater never looks at the load tables
         wide_ctx_fill(&s_wcx, T, off, true);
@@ -98,7 +103,7 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one_random(Tables T, PodDem
         uint32_t c = 0;
         const uint32_t r0 = cta * per_cta + tid * rpt;
         for (uint32_t j = 0; j < rpt; j++)
-            if (r0 + j < T.n && sample_row_feasible(T, r0 + j, &dem, &s_wcx)) c++;
+            if (r0 + j < T.n && sample_row_feasible<WIDE>(T, r0 + j, &dem, &s_wcx)) c++;
         return c;
     };
     uint32_t total;
@@ -210,13 +215,13 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one_random(Tables T, PodDem
             const uint32_t r0 = cta * per_cta + tid * rpt;
             for (uint32_t j = 0; j < rpt; j++) {
                 const uint32_t row = r0 + j;
-                if (row >= T.n || !sample_row_feasible(T, row, &dem, &s_wcx)) continue;
+                if (row >= T.n || !sample_row_feasible<WIDE>(T, row, &dem, &s_wcx)) continue;
                 if (left-- != 0) continue;
                 // NodeInfo.Bind (node.go:70-84) with SampleRater.Choose (rater.go:28-50)
                 const int G = T.gcount[row];
                 uint64_t emit = 0;
                 int n_emit = 0;
-                if (G > 8) {  // ngs_wide.cuh
+                if (WIDE && G > 8) {  // ngs_wide.cuh
                     const uint4 r = eval_wide_row(&s_wcx, row, &dem, WIDE_APPLY);
                     emit = (uint64_t)r.z | ((uint64_t)r.w << 32);
                     n_emit = (int)(r.x >> 8);
@@ -267,7 +272,11 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one_random(Tables T, PodDem
 }
 
 // out (mapped host memory): [0] status, [8] node, [9] score, [10 .. 10+max_c) gpu indexes
-__global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd, LoadParams lp, OneRec* rec, int32_t* out, int max_c, OneShard sh) {
+using OnePad = LaunchPad<32>;
+static_assert(param_block_bytes<Tables, PodDemand, LoadParams, OneRec*, int32_t*, int, OneShard, OnePad>() % 64 == 32, "see LaunchPad");
+template <bool WIDE>
+__global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd, LoadParams lp, OneRec* rec, int32_t* out, int max_c, OneShard sh,
+                                                         OnePad) {
     __shared__ SortedDemand dem;
     __shared__ double s_pair[121];
     __shared__ uint64_t s_wmax[8];
@@ -281,19 +290,29 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd,
     RowIn in;
     if (row < T.n) load_row(T, row, load_path, in);
     if (tid == 32) sort_demand(pd.percent, pd.n, pd.policy, &dem);
-    wide_ctx_fill(&s_wcx, T, lp, tid == 64);
+    if (WIDE) wide_ctx_fill(&s_wcx, T, lp, tid == 64);
     if (lp.enabled) fill_usage_pair_table(s_pair, tid, blockDim.x);
     __syncthreads();
     uint64_t best = 0;
     for (; row < T.n; row += gridDim.x * blockDim.x) {
         // Rate + Choose on the row as it stands; in load-aware mode this also leaves RemainLoad behind (allocate.go:193)
-        const RowEval ev = eval_row_values<false>(T, row, in, &dem, lp, true, s_pair, &s_wcx);
+        const RowEval ev = eval_row_values<false, false>(T, row, in, &dem, lp, true, s_pair, nullptr);
         if (ev.known && ev.feasible) {
             const uint64_t k = make_key(ev.score, T.first + row);
             best = k > best ? k : best;
         }
         const uint32_t nxt = row + gridDim.x * blockDim.x;
         if (nxt < T.n) load_row(T, nxt, load_path, in);
+    }
+    if (WIDE) {  // nodes of 9..12 GPUs (ngs_wide.cuh): a pass of their own over the GPU counts
+        for (row = blockIdx.x * blockDim.x + tid; row < T.n; row += gridDim.x * blockDim.x) {
+            if (T.gcount[row] <= 8) continue;
+            const uint4 w = eval_wide_row(&s_wcx, row, &dem, WIDE_RATE | (lp.enabled ? WIDE_LOAD : 0u));
+            if (w.x & 1u) {
+                const uint64_t k = make_key((int)w.y, T.first + row);
+                best = k > best ? k : best;
+            }
+        }
     }
     best = warp_max_u64(best);
     if (lane == 0) s_wmax[warp] = best;
@@ -351,7 +370,7 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd,
         const int rlc = (int)__ldcg(T.rl + (size_t)wrow * 8 + g) + 2;
         uint64_t emit = 0;
         int n_emit = 0, fr = 0;
-        if (G > 8) {  // ngs_wide.cuh: lane 0 plans and places, the plan goes to the other lanes
+        if (WIDE && G > 8) {  // ngs_wide.cuh: lane 0 plans and places, the plan goes to the other lanes
             if (lane == 0) {  // (no WIDE_LOAD: the plan is derived from the RemainLoad the scan left behind, as below)
                 const uint4 r = eval_wide_row(&s_wcx, wrow, &dem, WIDE_APPLY);
                 emit = (uint64_t)r.z | ((uint64_t)r.w << 32);

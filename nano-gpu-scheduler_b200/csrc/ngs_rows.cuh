@@ -45,8 +45,10 @@ struct RowIn {
     uint2 r8;           // RemainLoad (other passes; zeros when the table is known to hold only zeros)
 };
 
-// wcx: the CTA's context for rows of more than 8 GPUs (ngs_wide.cuh)
-template <bool PLAN>
+// wcx: the CTA's context for rows of more than 8 GPUs (ngs_wide.cuh).  WIDE_INLINE = false: such rows come back as
+// "unknown": the instantiations for snapshots without such nodes (the host picks per launch, from what the snapshot
+// holds) carry none of that code, and K7 evaluates such rows in a pass of its own.
+template <bool PLAN, bool WIDE_INLINE = true>
 __device__ __forceinline__ RowEval eval_row_values(const Tables& T, uint32_t row, const RowIn& in, const SortedDemand* dem,
                                                    const LoadParams& lp, bool do_rate, const double* pair, const WideCtx* wcx) {
     RowEval ev;
@@ -63,8 +65,10 @@ __device__ __forceinline__ RowEval eval_row_values(const Tables& T, uint32_t row
     const uint32_t (&ts)[2][8] = in.ts;
     const uint2 r8 = in.r8;
     if (G == 0) return ev;
-    if (G > 8)  // 9..12 GPUs: the row's cells are not all in `in`
+    if (G > 8) {  // 9..12 GPUs: the row's cells are not all in `in`
+        if (!WIDE_INLINE) return ev;
         return wide_row_eval(wcx, row, dem, (do_rate ? WIDE_RATE : 0u) | (lp.enabled ? WIDE_LOAD : 0u));
+    }
     ev.known = true;
     int f[8];
 #pragma unroll
@@ -150,10 +154,10 @@ __device__ __forceinline__ void load_row(const Tables& T, uint32_t row, bool loa
     }
 }
 
-template <bool PLAN>
+template <bool PLAN, bool WIDE_INLINE = true>
 __device__ __forceinline__ RowEval eval_row_global(const Tables& T, uint32_t row, const SortedDemand* dem, const LoadParams& lp,
                                                    bool do_rate, const WideCtx* wcx, const double* pair = nullptr) {
     RowIn in;
     load_row(T, row, lp.enabled && do_rate && dem->policy != NGS_POLICY_RANDOM, in);
-    return eval_row_values<PLAN>(T, row, in, dem, lp, do_rate, pair, wcx);
+    return eval_row_values<PLAN, WIDE_INLINE>(T, row, in, dem, lp, do_rate, pair, wcx);
 }

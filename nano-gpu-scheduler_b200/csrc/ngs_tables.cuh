@@ -30,3 +30,19 @@ struct RowEval {
     uint64_t emit;
     int n_emit;
 };
+
+// Launch-to-start latency on this driver depends on the size of a kernel's parameter block modulo 64: blocks of 64k+20 ..
+// 64k+44 bytes start 0.3-0.45 us sooner than the others (profiles/tools/param_size_bench.cu, profiles/r02/param_size_bench.txt;
+// found when four more table pointers made the single-pod kernel 0.5 us slower with identical SASS).  The latency-critical
+// kernels take a trailing LaunchPad that puts their block at 64k+32; the static_asserts beside them keep that true when a
+// parameter struct changes.
+template <int N>
+struct LaunchPad {
+    unsigned char b[N];
+};
+template <class... Ts>
+constexpr size_t param_block_bytes() {
+    size_t off = 0;
+    ((off = (off + alignof(Ts) - 1) / alignof(Ts) * alignof(Ts) + sizeof(Ts)), ...);
+    return off;
+}

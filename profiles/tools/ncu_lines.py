@@ -27,9 +27,10 @@ def sass_lines(so, kernel):
             m = re.match(r"\s*\.section\s+\.text\.(\S+?),", ln)
             if m:
                 # the mangled name carries the identifier's length: "10k_schedule" must not match "14k_schedule_one";
-                # "k_schedule<0>" selects the instantiation with a bool argument ("10k_scheduleILb0EE")
+                # "k_schedule<0, 0>" selects the instantiation with those bool arguments ("10k_scheduleILb0ELb0EE")
                 base, _, targ = kernel.partition("<")
-                want = "%d%s" % (len(base), base) + ("ILb%sEE" % targ.rstrip(">") if targ else "")
+                args = [a.strip() for a in targ.rstrip(">").split(",")] if targ else []  # bool template arguments: "0, 1"
+                want = "%d%s" % (len(base), base) + ("I" + "".join("Lb%sE" % a for a in args) + "E" if args else "")
                 active = want in m.group(1) or kernel == m.group(1)
                 cur_line = None
                 continue

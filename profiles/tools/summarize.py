@@ -71,7 +71,7 @@ kb = os.path.join(G, f"k1_bench_{rnd}.log")
 if os.path.exists(kb):
     json.dump([json.loads(l) for l in open(kb) if l.startswith("{")], open(os.path.join(OUT, "k_assume_roofline.json"), "w"), indent=1)
 hot = subprocess.run([sys.executable, os.path.join(ROOT, "profiles", "tools", "ncu_lines.py"), os.path.join(G, f"prof_sched_{rnd}.ncu-rep"),
-                      os.path.join(ROOT, "nano-gpu-scheduler_b200", "libngs_dealer.so"), "k_schedule<0>", "25"], capture_output=True, text=True).stdout
+                      os.path.join(ROOT, "nano-gpu-scheduler_b200", "libngs_dealer.so"), "k_schedule<0, 0>", "25"], capture_output=True, text=True).stdout
 open(os.path.join(OUT, "k_schedule_hot_lines.txt"), "w").write(hot)
 print(open(os.path.join(OUT, "launch_list_summary.txt")).read())
 print({k: b[k] for k in ("value", "ms_per_step", "gpu_launches", "clocks")}, b["e2e"], b["latency_us"], b["roofline"]["frac"], b.get("cpu_baseline", {}).get("value"))
