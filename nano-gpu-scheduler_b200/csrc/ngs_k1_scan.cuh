@@ -6,8 +6,11 @@
 enum { MODE_ASSUME = 0, MODE_SCORE = 1 };
 
 // How a verb kernel tells the host that its outputs are complete when they go straight into mapped host memory (no copy
-// command, no stream synchronisation): every thread makes its stores visible system-wide, the CTA that draws the last
-// ticket writes the call's sequence number into the host's flag word.  flag == nullptr: the caller synchronises the stream.
+// command, no stream synchronisation): after the CTA's barrier one thread makes the CTA's stores visible system-wide (a
+// fence is cumulative over what the barrier ordered before it - the pattern of a cooperative-groups grid sync, at system
+// scope; a fence in every thread cost 1.5 us more, profiles/r02/mapped_write_bench.txt) and draws a ticket; the CTA that
+// draws the last one writes the call's sequence number into the host's flag word.  flag == nullptr: the caller
+// synchronises the stream.
 struct VerbDone {
     uint32_t* ticket;  // device counter, zero between calls
     int32_t* flag;     // mapped host word
@@ -15,9 +18,9 @@ struct VerbDone {
 };
 __device__ __forceinline__ void verb_done(const VerbDone& vd) {
     if (vd.flag == nullptr) return;
-    __threadfence_system();
     __syncthreads();
     if (threadIdx.x == 0) {
+        __threadfence_system();
         if (atomicAdd(vd.ticket, 1u) == gridDim.x - 1) {
             *vd.ticket = 0;  // ready for the next call (ordered by the kernel boundary)
             __threadfence_system();

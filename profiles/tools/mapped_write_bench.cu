@@ -11,16 +11,17 @@
 
 __device__ unsigned int g_ticket;
 
-template <typename T>
+template <typename T, bool CTA_FENCE = false>
 __global__ void k_write(T* dst, size_t n_elems, volatile int* flag, int seq) {
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n_elems; i += (size_t)gridDim.x * blockDim.x) {
         T v;
         memset(&v, (int)(i & 0x7f), sizeof(T));
         dst[i] = v;
     }
-    __threadfence_system();
+    if (!CTA_FENCE) __threadfence_system();  // every thread fences its own stores ...
     __syncthreads();
     if (threadIdx.x == 0) {
+        if (CTA_FENCE) __threadfence_system();  // ... or one thread per CTA does, after the barrier (fences are cumulative)
         if (atomicAdd(&g_ticket, 1u) == gridDim.x - 1) {
             g_ticket = 0;
             __threadfence_system();
@@ -29,7 +30,7 @@ __global__ void k_write(T* dst, size_t n_elems, volatile int* flag, int seq) {
     }
 }
 
-template <typename T>
+template <typename T, bool CTA_FENCE = false>
 double run(void* d_dst, size_t bytes, int* h_flag, int* d_flag, int& seq, cudaStream_t st) {
     const size_t n = bytes / sizeof(T);
     int grid = (int)std::min<size_t>((n + 255) / 256, 148 * 4);
@@ -38,7 +39,7 @@ double run(void* d_dst, size_t bytes, int* h_flag, int* d_flag, int& seq, cudaSt
     for (int it = 0; it < 60; it++) {
         ++seq;
         auto t0 = std::chrono::steady_clock::now();
-        k_write<T><<<grid, 256, 0, st>>>((T*)d_dst, n, d_flag, seq);
+        k_write<T, CTA_FENCE><<<grid, 256, 0, st>>>((T*)d_dst, n, d_flag, seq);
         while (*(volatile int*)h_flag != seq) {}
         auto t1 = std::chrono::steady_clock::now();
         if (it >= 10) t.push_back(std::chrono::duration<double, std::micro>(t1 - t0).count());
@@ -69,7 +70,8 @@ int main() {
             const double a = run<uint8_t>(dst, bytes, h_flag, d_flag, seq, st);
             const double b = run<uint32_t>(dst, bytes, h_flag, d_flag, seq, st);
             const double c = run<uint4>(dst, bytes / 16 * 16, h_flag, d_flag, seq, st);
-            printf("%8zu   %s   %8.1f   %8.1f   %8.1f\n", bytes, dev ? "device" : "host  ", a, b, c);
+            const double e = run<uint32_t, true>(dst, bytes, h_flag, d_flag, seq, st);
+            printf("%8zu   %s   %8.1f   %8.1f   %8.1f   | one fence per CTA, u32: %8.1f\n", bytes, dev ? "device" : "host  ", a, b, c, e);
         }
     }
     return 0;

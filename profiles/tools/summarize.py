@@ -67,6 +67,11 @@ if os.path.exists(k1):
     m1 = raw_metrics(k1, WANT)
     m1["dram_bytes_per_eval"] = (dram_bytes(m1) / 4_000_000, "byte")
     json.dump(m1, open(os.path.join(OUT, "k_assume_load_on_ncu_full_summary.json"), "w"), indent=1)
+k0 = os.path.join(G, f"prof_k1_off_{rnd}.ncu-rep")
+if os.path.exists(k0):
+    m0 = raw_metrics(k0, WANT)
+    m0["dram_bytes_per_eval"] = (dram_bytes(m0) / 4_000_000, "byte")
+    json.dump(m0, open(os.path.join(OUT, "k_scan_tma_load_off_ncu_full_summary.json"), "w"), indent=1)
 kb = os.path.join(G, f"k1_bench_{rnd}.log")
 if os.path.exists(kb):
     json.dump([json.loads(l) for l in open(kb) if l.startswith("{")], open(os.path.join(OUT, "k_assume_roofline.json"), "w"), indent=1)
