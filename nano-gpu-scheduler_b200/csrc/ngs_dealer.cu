@@ -604,6 +604,15 @@ int ngs_debug_phases(ngs_dealer* h, unsigned long long* out, uint32_t* grid) {
 }
 #endif
 
+#ifdef NGS_K7_TIMING
+// profiling builds only: cycles from kernel entry to each stamp of the last k_schedule_one launch (its last CTA)
+int ngs_debug_k7(ngs_dealer* h, int32_t* out5) {
+    if (!h || !h->h_pod_out) return NGS_ERR_INVALID;
+    for (int i = 0; i < 5; i++) out5[i] = h->h_pod_out[32 + i];
+    return NGS_OK;
+}
+#endif
+
 int ngs_stats(ngs_dealer* h, ngs_stats_t* out) {
     if (!h || !out) return NGS_ERR_INVALID;
     *out = h->stats;

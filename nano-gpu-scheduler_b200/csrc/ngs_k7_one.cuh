@@ -284,6 +284,13 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd,
     __shared__ int32_t s_plan[NGS_MAX_CONTAINERS];  // the winner's plan in container order (last CTA only)
     __shared__ WideCtx s_wcx;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+#ifdef NGS_K7_TIMING
+    long long tk[8];
+    tk[0] = clock64();
+#define K7_STAMP(i) tk[i] = clock64()
+#else
+#define K7_STAMP(i) do { } while (0)
+#endif
     // the first row of every thread is requested before the demand is sorted: the loads do not depend on it
     const bool load_path = lp.enabled != 0;  // (binpack / spread only)
     uint32_t row = blockIdx.x * blockDim.x + tid;
@@ -293,6 +300,7 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd,
     if (WIDE) wide_ctx_fill(&s_wcx, T, lp, tid == 64);
     if (lp.enabled) fill_usage_pair_table(s_pair, tid, blockDim.x);
     __syncthreads();
+    K7_STAMP(1);
     uint64_t best = 0;
     for (; row < T.n; row += gridDim.x * blockDim.x) {
         // Rate + Choose on the row as it stands; in load-aware mode this also leaves RemainLoad behind (allocate.go:193)
@@ -314,6 +322,7 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd,
             }
         }
     }
+    K7_STAMP(2);
     best = warp_max_u64(best);
     if (lane == 0) s_wmax[warp] = best;
     __syncthreads();
@@ -326,6 +335,7 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd,
     }
     __syncthreads();
     if (!s_last || warp != 0) return;
+    K7_STAMP(3);
 
     // ---- warp 0 of the last CTA to arrive: every other CTA's key and RemainLoad rows are visible now ----
     __threadfence();
@@ -427,9 +437,13 @@ __global__ void __launch_bounds__(256, 4) k_schedule_one(Tables T, PodDemand pd,
         }
     }
     __syncwarp();
+    K7_STAMP(4);
     if ((int)lane < max_c) gout[lane] = lane < NGS_MAX_CONTAINERS ? s_plan[lane] : INT32_MIN;
     __syncwarp();
     if (lane == 0) {
+#ifdef NGS_K7_TIMING
+        for (int i = 0; i < 5; i++) out[32 + i] = (int32_t)(tk[i] - tk[0]);
+#endif
         __threadfence_system();  // the answer is in host memory before the status word says so
         *reinterpret_cast<volatile int32_t*>(out) = status;
     }
