@@ -617,6 +617,7 @@ def run_b200(args):
         # (world == 1: straight into the C entry point with pre-built argument buffers, so that the
         # number is the library's latency and not numpy's)
         lat = []
+        lat_serve = []
         lo = base
         n_lat = 60 if args.skip_e2e else 400
         if sd is None or int(policy[0]) != ngs.POLICY_RANDOM:
@@ -641,6 +642,21 @@ def run_b200(args):
                 t0 = time.perf_counter()
                 sd.schedule_batch(pc[lo + s:lo + s + 1], nc[lo + s:lo + s + 1], policy[lo + s:lo + s + 1], load=load, seed=1, seq0=s)
                 lat.append(time.perf_counter() - t0)
+        # the same call through the resident kernel (K8, ngs_serve_pod): no launch per pod
+        if sd is None and int(policy[0]) != ngs.POLICY_RANDOM:
+            import ctypes as C
+
+            lib = ngs._abi.load()
+            o1, o2, o3 = C.c_int32(0), C.c_int32(0), np.zeros(MAX_C, dtype=np.int32)
+            lref = None if load is None else C.c_void_p(C.addressof(load))
+            for s in range(n_lat):
+                a_pc = C.c_void_p(pc.ctypes.data + (lo + n_lat + s) * MAX_C * 4)
+                t0 = time.perf_counter()
+                rc = lib.ngs_serve_pod(d._h, a_pc, C.c_int(int(nc[lo + n_lat + s])), C.c_int(MAX_C), C.c_int(int(policy[lo + n_lat + s])), lref,
+                                       C.c_uint64(1), C.c_uint64(n_lat + s), C.byref(o1), C.byref(o2), o3.ctypes.data_as(C.c_void_p))
+                lat_serve.append(time.perf_counter() - t0)
+                assert rc == 0
+            lib.ngs_serve_stop(d._h)
         sampler.stop()
         # ---- parity: the configuration that was just timed, checked against the oracle where the driver can see it ----
         parity = parity_check(ngs, cfg, d, sd, dist, rank, world, n, load, args.parity_pods or (256 if world == 1 else 96), 10_000_000)
@@ -670,6 +686,9 @@ def run_b200(args):
                 "d2h_bytes_per_step": int(P * (MAX_C + 2) * 4), "ms_per_step": 1e3 * sum(e2e_times) / len(e2e_times)},
         "latency_us": {"p50": float(np.percentile(lat_us, 50)), "p99": float(np.percentile(lat_us, 99)),
                        "what": "one pod, host demand in -> (node, score, plan) on the host, ngs_schedule_batch with P=1 (filter + prioritize + bind of the whole cluster)"},
+        "latency_us_resident": None if len(lat_serve) <= 50 else {
+            "p50": float(np.percentile(np.array(lat_serve[50:]) * 1e6, 50)), "p99": float(np.percentile(np.array(lat_serve[50:]) * 1e6, 99)),
+            "what": "the same one-pod call through the resident kernel (ngs_serve_pod): launched once, requests and answers through mapped host memory"},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "parity_check": parity,

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define NGS_ABI_VERSION 3u /* 2: ngs_load_ctx holds 8 periods; NGS_NODE_INVALID_POD.  3: nodes of 9..12 GPUs (ngs_node_*_wide) */
+#define NGS_ABI_VERSION 3u /* 2: ngs_load_ctx holds 8 periods; NGS_NODE_INVALID_POD.  3: nodes of 9..12 GPUs (ngs_node_*_wide), ngs_score_view, ngs_serve_* */
 
 #define NGS_MAX_GPUS 8         /* cells per row of the bulk arrays (row = 8 x int32 = 2 x int4): what a node usually has */
 #define NGS_MAX_GPUS_WIDE 12   /* most GPUs a node may have (Go sort.Sort's <=12-element regime, as for containers); cells
@@ -207,6 +207,24 @@ int ngs_schedule_batch(ngs_dealer *h, uint32_t n_pods, const int32_t *percent, c
 int ngs_schedule_batch_dev(ngs_dealer *h, uint32_t n_pods, const int32_t *d_percent, const int32_t *d_n_containers,
                            int max_c, const int32_t *d_policy, const ngs_load_ctx *load, uint64_t seed, uint64_t seq0,
                            int32_t *d_node_out, int32_t *d_score_out, int32_t *d_gpu_idx_out);
+
+/* ---- the resident form of the one-pod call (no reference counterpart) ----
+ * ngs_schedule_batch with one pod costs one kernel launch per pod, and on this hardware a launch whose result the host
+ * can see takes longer than the kernel's own work.  ngs_serve_pod gives the same answer (same arguments as one pod of
+ * ngs_schedule_batch, bit for bit the same decision and table update) through a kernel that is launched once and then
+ * polls a request block in pinned host memory: the call writes the request there and spins on the answer.
+ *  - The kernel stays resident (it occupies the GPU's SMs with spinning CTAs) until ngs_serve_stop, until any other
+ *    entry point of this handle is called (each of them stops it first, which costs that call a stream synchronisation),
+ *    or until no request came for ngs_serve_idle_ms (default 20 ms); the next ngs_serve_pod starts it again (one
+ *    cooperative launch).  Work other handles or the caller queue on this GPU meanwhile runs only in whatever the
+ *    resident CTAs leave free, and work queued on ngs_stream() waits for the kernel to leave.
+ *  - Arg-max policies on unsharded handles are served by the resident kernel; NGS_POLICY_RANDOM and sharded handles
+ *    take the launched path (ngs_schedule_batch) from inside the call.
+ *  - One caller at a time, like every call on a handle. */
+int ngs_serve_pod(ngs_dealer *h, const int32_t *percent, int n_containers, int max_c, int policy, const ngs_load_ctx *load,
+                  uint64_t seed, uint64_t seq0, int32_t *node_out, int32_t *score_out, int32_t *gpu_idx_out);
+int ngs_serve_stop(ngs_dealer *h);
+int ngs_serve_idle_ms(ngs_dealer *h, double ms); /* 0 < ms <= 2000; stops the kernel if it runs */
 
 /* ---- node-range sharding over the GPUs of one box (no reference counterpart: the reference is a
  * single process) ----

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libngs_dealer.so")
 SOURCES = ["ngs_dealer.cu", "ngs_parse.cpp"]
-HEADERS = [os.path.join(CSRC, f) for f in ("ngs_device.cuh", "ngs_tables.cuh", "ngs_wide.cuh", "ngs_rows.cuh", "ngs_k1_scan.cuh", "ngs_k3_rows.cuh", "ngs_k6_batch.cuh", "ngs_k7_one.cuh")] + [
+HEADERS = [os.path.join(CSRC, f) for f in ("ngs_device.cuh", "ngs_tables.cuh", "ngs_wide.cuh", "ngs_rows.cuh", "ngs_k1_scan.cuh", "ngs_k3_rows.cuh", "ngs_k6_batch.cuh", "ngs_k7_one.cuh", "ngs_k8_serve.cuh")] + [
     os.path.join(HERE, "..", "include", "ngs_dealer.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

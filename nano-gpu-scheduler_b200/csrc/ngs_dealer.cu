@@ -47,6 +47,7 @@ namespace {
 #include "ngs_k3_rows.cuh"
 #include "ngs_k6_batch.cuh"
 #include "ngs_k7_one.cuh"
+#include "ngs_k8_serve.cuh"
 
 // ---------------------------------------------------------------------------------------------
 // host side
@@ -117,6 +118,17 @@ struct ngs_dealer {
     unsigned long long* d_xslots = nullptr;               // own buffer: [2 parities][BATCH_CHUNK][NGS_MAX_RANKS]
     unsigned long long* peer_xslots[NGS_MAX_RANKS] = {};  // peer-mapped bases (own entry = d_xslots)
     uint64_t xbatch = 0;                                  // launches so far: selects the parity half
+    // K8, the resident single-pod kernel (ngs_k8_serve.cuh)
+    bool serve_running = false;       // a k_serve launch has been queued and not yet been waited for
+    uint32_t serve_seq = 0;           // sequence number of the last request posted
+    uint32_t serve_launch = 0;        // id of the current launch (the kernel writes it to *h_serve_exit when it leaves)
+    uint32_t* h_serve_req = nullptr;  // mapped pinned: request block [SERVE_REQ_WORDS], exit word at [SERVE_REQ_WORDS]
+    uint32_t* d_serve_req = nullptr;  // device alias
+    int32_t* h_serve_out = nullptr;   // mapped pinned: answer block
+    int32_t* d_serve_out = nullptr;
+    ServeDev* d_serve_dev = nullptr;
+    int serve_grid_cap[2] = {0, 0};   // co-resident CTAs of k_serve<false> / <true>
+    double serve_idle_ms = 20.0;      // the kernel leaves after this long without a request
     // nodes with 9..12 GPUs (ngs_wide.cuh): which rows, so that the batch kernel can refuse them before it binds anything
     std::vector<uint8_t> wide_row;
     uint32_t n_wide = 0;
@@ -425,6 +437,89 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     return NGS_OK;
 }
 
+// ---- K8: the resident kernel's life cycle ----
+// first thing in every other entry point of a handle
+#define SERVE_OFF(h)                   \
+    do {                               \
+        if ((h)->serve_running) {      \
+            const int rc_ = serve_stop(h); \
+            if (rc_) return rc_;       \
+        }                              \
+    } while (0)
+
+uint32_t serve_next_seq(uint32_t s) {
+    s++;
+    return (s == 0 || s == SERVE_QUIT) ? 1u : s;
+}
+
+// stop the resident kernel (if any) before anything else touches the tables or the stream: it owns both while it runs
+int serve_stop(ngs_dealer* h) {
+    if (!h->serve_running) return NGS_OK;
+    cudaSetDevice(h->device);
+    volatile uint32_t* rq = h->h_serve_req;
+    if (rq[SERVE_REQ_WORDS] != h->serve_launch) {  // still there: a request with quit set
+        ServeBody b;
+        memset(&b, 0, sizeof(b));
+        b.quit = 1;
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(&b);
+        const uint32_t seq = h->serve_seq = serve_next_seq(h->serve_seq);
+        for (int i = 0; i < SERVE_BODY_WORDS; i++) rq[(i / 15) * 16 + i % 15] = i < SERVE_BODY_USED ? w[i] : 0u;
+        std::atomic_thread_fence(std::memory_order_seq_cst);
+        for (int c = 0; c < 4; c++) rq[c * 16 + 15] = seq;
+        std::atomic_thread_fence(std::memory_order_seq_cst);
+    }
+    h->serve_running = false;
+    CU(h, cudaStreamSynchronize(h->stream));
+    return NGS_OK;
+}
+
+// last_seq: the sequence number the kernel regards as already answered
+int serve_start(ngs_dealer* h, uint32_t last_seq) {
+    if (!h->coop) return fail(h, NGS_ERR_CUDA, "device lacks cooperative launch");
+    if (!h->h_serve_req) {
+        CU(h, cudaHostAlloc(&h->h_serve_req, (SERVE_REQ_WORDS + 16) * 4, cudaHostAllocMapped));
+        CU(h, cudaHostGetDevicePointer(&h->d_serve_req, h->h_serve_req, 0));
+        memset(h->h_serve_req, 0, (SERVE_REQ_WORDS + 16) * 4);
+        CU(h, cudaHostAlloc(&h->h_serve_out, 64 * 4, cudaHostAllocMapped));
+        CU(h, cudaHostGetDevicePointer(&h->d_serve_out, h->h_serve_out, 0));
+        memset(h->h_serve_out, 0, 64 * 4);
+        CU(h, cudaMalloc(&h->d_serve_dev, sizeof(ServeDev)));
+        int per_sm = 0;
+        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_serve<false>, 256, 0));
+        h->serve_grid_cap[0] = per_sm * h->num_sms;
+        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_serve<true>, 256, 0));
+        h->serve_grid_cap[1] = per_sm * h->num_sms;
+    }
+    const int wide = h->n_wide ? 1 : 0;
+    uint32_t grid = (h->T.n + 255) / 256;
+    if (grid > (uint32_t)h->num_sms * 4) grid = (uint32_t)h->num_sms * 4;
+    if (grid > (uint32_t)h->serve_grid_cap[wide]) grid = (uint32_t)h->serve_grid_cap[wide];
+    if (grid < 1) return fail(h, NGS_ERR_CUDA, "the resident kernel does not fit the device");
+    // the published word starts at the last sequence number: the kernel waits for the next one
+    ServeDev init;
+    memset(&init, 0, sizeof(init));
+    init.seq = last_seq;
+    CU(h, cudaMemcpyAsync(h->d_serve_dev, &init, sizeof(init), cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));  // (pageable source; and nothing else of this handle is in flight from here on)
+    h->serve_launch = h->serve_launch + 1 ? h->serve_launch + 1 : 1;
+    Tables T = h->T;
+    OneRec* rec = h->d_one;
+    ServeDev* dev = h->d_serve_dev;
+    const uint32_t* req = h->d_serve_req;
+    int32_t* out = h->d_serve_out;
+    uint32_t* exited = h->d_serve_req + SERVE_REQ_WORDS;
+    uint32_t launch_id = h->serve_launch;
+    int khz = 0;
+    cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, h->device);
+    long long idle_cycles = (long long)(h->serve_idle_ms * (khz > 0 ? khz : 1900000));
+    void* args[] = {&T, &rec, &dev, &req, &out, &exited, &last_seq, &launch_id, &idle_cycles};
+    const void* fn = wide ? (const void*)k_serve<true> : (const void*)k_serve<false>;
+    CU(h, cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(256), args, 0, h->stream));
+    h->serve_running = true;
+    h->stats.kernel_launches++;
+    return NGS_OK;
+}
+
 // the second plane of the tables (cells 8..11), created when the first node with more than 8 GPUs arrives
 int ensure_wide(ngs_dealer* h) {
     if (h->T.free_hi) return NGS_OK;
@@ -564,7 +659,9 @@ int ngs_create(ngs_dealer** out, int device, uint32_t max_nodes, uint32_t first_
 int ngs_destroy(ngs_dealer* h) {
     if (!h) return NGS_OK;
     cudaSetDevice(h->device);
+    if (h->serve_running) serve_stop(h);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    cudaFreeHost(h->h_serve_req); cudaFreeHost(h->h_serve_out); cudaFree(h->d_serve_dev);
     cudaFree(h->T.free); cudaFree(h->T.gcount); cudaFree(h->T.rl); cudaFree(h->T.tenths); cudaFree(h->T.ts);
     cudaFree(h->T.tag); cudaFree(h->T.cscore); cudaFree(const_cast<int16_t*>(h->T.blut));
     cudaFree(h->T.free_hi); cudaFree(h->T.rl_hi); cudaFree(h->T.tenths_hi); cudaFree(h->T.ts_hi);
@@ -587,6 +684,7 @@ void* ngs_stream(ngs_dealer* h) { return h ? (void*)h->stream : nullptr; }
 
 int ngs_sync(ngs_dealer* h) {
     if (!h) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     CU(h, cudaSetDevice(h->device));
     CU(h, cudaMemcpyAsync(h->h_err, h->d_err, 4, cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
@@ -621,6 +719,7 @@ int ngs_stats(ngs_dealer* h, ngs_stats_t* out) {
 
 int ngs_node_upsert(ngs_dealer* h, uint32_t idx, int gpu_count) {
     if (!h) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     if (idx < h->T.first || idx - h->T.first >= h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "node %u outside this shard", idx);
     if (gpu_count < 0) return fail(h, NGS_ERR_INVALID, "gpu_count %d", gpu_count);
     if (gpu_count > NGS_MAX_GPUS_WIDE) return fail(h, NGS_ERR_UNSUPPORTED, "gpu_count %d > NGS_MAX_GPUS_WIDE", gpu_count);
@@ -639,6 +738,7 @@ int ngs_node_upsert(ngs_dealer* h, uint32_t idx, int gpu_count) {
 
 int ngs_node_set_wide(ngs_dealer* h, uint32_t idx, int gpu_count, const int32_t* free, const int8_t* remain_load) {
     if (!h) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     if (idx < h->T.first || idx - h->T.first >= h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "node %u outside this shard", idx);
     if (gpu_count < 0) return fail(h, NGS_ERR_INVALID, "gpu_count %d", gpu_count);
     if (gpu_count > NGS_MAX_GPUS_WIDE) return fail(h, NGS_ERR_UNSUPPORTED, "gpu_count %d > NGS_MAX_GPUS_WIDE", gpu_count);
@@ -677,6 +777,7 @@ int ngs_node_set_wide(ngs_dealer* h, uint32_t idx, int gpu_count, const int32_t*
 
 int ngs_node_get_wide(ngs_dealer* h, uint32_t idx, int* gpu_count, int32_t* free, int8_t* remain_load) {
     if (!h) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     if (idx < h->T.first || idx - h->T.first >= h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "node %u outside this shard", idx);
     const uint32_t row = idx - h->T.first;
     CU(h, cudaSetDevice(h->device));
@@ -702,6 +803,7 @@ int ngs_node_get_wide(ngs_dealer* h, uint32_t idx, int* gpu_count, int32_t* free
 
 int ngs_snapshot_load(ngs_dealer* h, uint32_t first, uint32_t n, const uint8_t* gpu_count, const int32_t* free, const int8_t* remain_load) {
     if (!h || !gpu_count) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     if (first < h->T.first || (uint64_t)(first - h->T.first) + n > h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "rows [%u,%u) outside this shard", first, first + n);
     if (n == 0) return NGS_OK;
     const uint32_t r0 = first - h->T.first;
@@ -734,6 +836,7 @@ int ngs_snapshot_load(ngs_dealer* h, uint32_t first, uint32_t n, const uint8_t* 
 
 int ngs_snapshot_read(ngs_dealer* h, uint32_t first, uint32_t n, uint8_t* gpu_count, int32_t* free, int8_t* remain_load) {
     if (!h) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     if (first < h->T.first || (uint64_t)(first - h->T.first) + n > h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "rows [%u,%u) outside this shard", first, first + n);
     if (n == 0) return NGS_OK;
     const uint32_t r0 = first - h->T.first;
@@ -748,6 +851,7 @@ int ngs_snapshot_read(ngs_dealer* h, uint32_t first, uint32_t n, uint8_t* gpu_co
 
 int ngs_node_apply(ngs_dealer* h, uint32_t idx, const int32_t* gpu_idx, const int32_t* percent, int n_containers, int sign) {
     if (!h || sign == 0) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     PodDemand pd;
     int rc = make_demand(h, percent, n_containers, NGS_POLICY_BINPACK, &pd);
     if (rc) return rc;
@@ -769,6 +873,7 @@ int ngs_node_apply(ngs_dealer* h, uint32_t idx, const int32_t* gpu_idx, const in
 int ngs_release_batch(ngs_dealer* h, uint32_t n, const uint32_t* node, const int32_t* gpu_idx, const int32_t* percent,
                       const int32_t* n_containers, int max_c, int32_t* status_out) {
     if (!h || (n > 0 && (!node || !gpu_idx || !percent || !n_containers))) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     if (max_c < 1 || max_c > NGS_MAX_CONTAINERS) return fail(h, NGS_ERR_UNSUPPORTED, "max_c %d outside [1, NGS_MAX_CONTAINERS]", max_c);
     if (n == 0) return NGS_OK;
     CU(h, cudaSetDevice(h->device));
@@ -817,6 +922,7 @@ static uint8_t encode_tenths(double value, int value_ok, int64_t ts_sec, int ts_
 
 int ngs_load_add_node(ngs_dealer* h, uint32_t idx, int metric) {
     if (!h || metric < 0 || metric > 1) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     if (idx < h->T.first || idx - h->T.first >= h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "node %u outside this shard", idx);
     CU(h, cudaSetDevice(h->device));
     k_load_add_node<<<1, 32, 0, h->stream>>>(h->T, idx - h->T.first, metric);
@@ -827,6 +933,7 @@ int ngs_load_add_node(ngs_dealer* h, uint32_t idx, int metric) {
 
 int ngs_load_update(ngs_dealer* h, uint32_t idx, int metric, int card, double value, int value_ok, int64_t ts_sec, int ts_ok) {
     if (!h || metric < 0 || metric > 1) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     if (idx < h->T.first || idx - h->T.first >= h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "node %u outside this shard", idx);
     if (card < 0) return fail(h, NGS_ERR_INVALID, "card %d", card);
     if (card >= NGS_MAX_GPUS_WIDE) return NGS_OK;  // a card the kernels never look at (LoadUsage walks gpus only)
@@ -845,6 +952,7 @@ int ngs_load_update(ngs_dealer* h, uint32_t idx, int metric, int card, double va
 int ngs_load_update_bulk(ngs_dealer* h, int metric, uint32_t first, uint32_t n, const double* value, const uint8_t* value_ok,
                          const int64_t* ts_sec, const uint8_t* ts_ok) {
     if (!h || metric < 0 || metric > 1 || !value || !ts_sec) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     if (first < h->T.first || (uint64_t)(first - h->T.first) + n > h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "rows [%u,%u) outside this shard", first, first + n);
     if (n == 0) return NGS_OK;
     const size_t cells = (size_t)n * 8;
@@ -888,6 +996,7 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
                       const ngs_load_ctx* load, uint8_t* feasible, int8_t* reason, int32_t* score, int32_t* plan, int32_t* n_emitted,
                       const int32_t** score_view = nullptr) {
     if (!h) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     if (score_view) *score_view = nullptr;
     PodDemand pd;
     LoadParams lp;
@@ -982,6 +1091,7 @@ int ngs_assume(ngs_dealer* h, const uint32_t* idx, uint32_t n, const int32_t* pe
 int ngs_assume_dev(ngs_dealer* h, uint32_t n, const int32_t* percent, int n_containers, int policy, const ngs_load_ctx* load,
                    uint8_t* d_feasible, int32_t* d_score) {
     if (!h) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     PodDemand pd;
     LoadParams lp;
     int rc = make_demand(h, percent, n_containers, policy, &pd);
@@ -1019,6 +1129,7 @@ int ngs_score_view(ngs_dealer* h, const uint32_t* idx, uint32_t n, const int32_t
 int ngs_bind(ngs_dealer* h, uint32_t idx, const int32_t* percent, int n_containers, int policy, const ngs_load_ctx* load,
              int32_t* gpu_idx_out, int32_t* score_out) {
     if (!h) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     PodDemand pd;
     LoadParams lp;
     int rc = make_demand(h, percent, n_containers, policy, &pd);
@@ -1063,6 +1174,7 @@ int ngs_schedule_batch_dev(ngs_dealer* h, uint32_t n_pods, const int32_t* d_perc
                            const int32_t* d_policy, const ngs_load_ctx* load, uint64_t seed, uint64_t seq0, int32_t* d_node_out,
                            int32_t* d_score_out, int32_t* d_gpu_idx_out) {
     if (!h || !d_percent || !d_n_containers || !d_policy || !d_node_out || !d_score_out || !d_gpu_idx_out) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     if (max_c < 1 || max_c > NGS_MAX_CONTAINERS) return fail(h, NGS_ERR_UNSUPPORTED, "max_c %d outside [1, NGS_MAX_CONTAINERS]", max_c);
     if (n_pods > NGS_MAX_BATCH) return fail(h, NGS_ERR_UNSUPPORTED, "%u pods > NGS_MAX_BATCH", n_pods);
     LoadParams lp;
@@ -1084,6 +1196,7 @@ int ngs_schedule_batch(ngs_dealer* h, uint32_t n_pods, const int32_t* percent, c
                        const int32_t* policy, const ngs_load_ctx* load, uint64_t seed, uint64_t seq0, int32_t* node_out,
                        int32_t* score_out, int32_t* gpu_idx_out) {
     if (!h || !percent || !n_containers || !policy || !node_out || !score_out || !gpu_idx_out) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     if (max_c < 1 || max_c > NGS_MAX_CONTAINERS) return fail(h, NGS_ERR_UNSUPPORTED, "max_c %d outside [1, NGS_MAX_CONTAINERS]", max_c);
     if (n_pods > NGS_MAX_BATCH) return fail(h, NGS_ERR_UNSUPPORTED, "%u pods > NGS_MAX_BATCH", n_pods);
     for (uint32_t p = 0; p < n_pods; p++) {
@@ -1188,8 +1301,97 @@ int ngs_schedule_batch(ngs_dealer* h, uint32_t n_pods, const int32_t* percent, c
     return NGS_OK;
 }
 
+// K8: ngs_schedule_batch for one pod through the resident kernel (ngs_k8_serve.cuh)
+int ngs_serve_pod(ngs_dealer* h, const int32_t* percent, int n_containers, int max_c, int policy, const ngs_load_ctx* load, uint64_t seed,
+                  uint64_t seq0, int32_t* node_out, int32_t* score_out, int32_t* gpu_idx_out) {
+    if (!h || !percent || !node_out || !score_out || !gpu_idx_out) return NGS_ERR_INVALID;
+    if (max_c < 1 || max_c > NGS_MAX_CONTAINERS) return fail(h, NGS_ERR_UNSUPPORTED, "max_c %d outside [1, NGS_MAX_CONTAINERS]", max_c);
+    if (n_containers < 0 || n_containers > max_c) return fail(h, NGS_ERR_INVALID, "%d containers", n_containers);
+    if (policy == NGS_POLICY_RANDOM || h->world > 1) {  // not what the resident kernel does: the launched form (K7)
+        const int32_t nc = n_containers, pol = policy;
+        return ngs_schedule_batch(h, 1, percent, &nc, max_c, &pol, load, seed, seq0, node_out, score_out, gpu_idx_out);
+    }
+    ServeBody b;
+    memset(&b, 0, sizeof(b));
+    int rc = make_demand(h, percent, n_containers, policy, &b.pd);
+    if (rc) return rc;
+    rc = make_load(h, load, &b.lp);
+    if (rc) return rc;
+    CU(h, cudaSetDevice(h->device));
+    volatile uint32_t* rq = h->h_serve_req;
+    if (h->serve_running && rq[SERVE_REQ_WORDS] == h->serve_launch) {  // it left (idle): collect the launch
+        h->serve_running = false;
+        CU(h, cudaStreamSynchronize(h->stream));
+    }
+    if (!h->serve_running) {
+        rc = ensure_batch(h);
+        if (rc) return rc;
+        rc = serve_start(h, h->serve_seq);
+        if (rc) return rc;
+        rq = h->h_serve_req;
+    }
+    if (b.lp.enabled) h->T.rl_zero = 0;  // the load-aware Rate writes RemainLoad
+    b.rl_zero = h->T.rl_zero;
+    b.max_c = (uint32_t)max_c;
+    h->epoch++;  // the call binds the pod
+    const uint32_t seq = h->serve_seq = serve_next_seq(h->serve_seq);
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(&b);
+    for (int i = 0; i < SERVE_BODY_USED; i++) rq[(i / 15) * 16 + i % 15] = w[i];
+    std::atomic_thread_fence(std::memory_order_seq_cst);  // payload before the sequence words
+    for (int c = 0; c < 4; c++) rq[c * 16 + 15] = seq;
+    std::atomic_thread_fence(std::memory_order_seq_cst);
+    volatile int32_t* out = h->h_serve_out;
+    int restarts = 0;
+    for (uint64_t spins = 1; (uint32_t)out[0] != seq; spins++) {
+#if defined(__x86_64__) || defined(__i386__)
+        __builtin_ia32_pause();
+#endif
+        if ((spins & 0x3FFu) == 0) {
+            if (rq[SERVE_REQ_WORDS] == h->serve_launch && (uint32_t)out[0] != seq) {
+                // the kernel left (idle) just before the request arrived: start it again, the request is still in the block
+                h->serve_running = false;
+                CU(h, cudaStreamSynchronize(h->stream));
+                if (++restarts > 3) return fail(h, NGS_ERR_TIMEOUT, "the resident kernel keeps leaving before it answers");
+                rc = serve_start(h, seq == 1 ? SERVE_QUIT - 1 : seq - 1);
+                if (rc) return rc;
+            } else if ((spins & 0xFFFFFu) == 0) {
+                const cudaError_t q = cudaStreamQuery(h->stream);
+                if (q != cudaErrorNotReady && (uint32_t)out[0] != seq && rq[SERVE_REQ_WORDS] != h->serve_launch) {
+                    h->serve_running = false;
+                    return fail(h, NGS_ERR_CUDA, "the resident kernel ended without an answer: %s", cudaGetErrorString(q));
+                }
+                if (spins > (1ull << 33)) return fail(h, NGS_ERR_TIMEOUT, "the resident kernel did not answer");
+            }
+        }
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);
+    rc = out[1];
+    *node_out = out[8];
+    *score_out = out[9];
+    for (int k = 0; k < max_c; k++) gpu_idx_out[k] = out[10 + k];
+    h->stats.node_evals += h->T.n;
+    h->stats.pods_scheduled += 1;
+    h->stats.d2h_bytes += (size_t)(2 + max_c) * 4;
+    h->stats.h2d_bytes += sizeof(ServeBody);
+    if (rc != NGS_OK) return fail(h, rc, "resident kernel: %s", ngs_strerror(rc));
+    return NGS_OK;
+}
+
+int ngs_serve_stop(ngs_dealer* h) {
+    if (!h) return NGS_ERR_INVALID;
+    return serve_stop(h);
+}
+
+int ngs_serve_idle_ms(ngs_dealer* h, double ms) {
+    if (!h || !(ms > 0) || ms > 2000) return NGS_ERR_INVALID;
+    const int rc = serve_stop(h);
+    h->serve_idle_ms = ms;
+    return rc;
+}
+
 int ngs_xchg_export(ngs_dealer* h, void* handle_out) {
     if (!h || !handle_out) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     static_assert(sizeof(cudaIpcMemHandle_t) == NGS_IPC_HANDLE_BYTES, "IPC handle size");
     CU(h, cudaSetDevice(h->device));
     if (!h->d_xslots) {
@@ -1205,6 +1407,7 @@ int ngs_xchg_export(ngs_dealer* h, void* handle_out) {
 
 int ngs_xchg_attach(ngs_dealer* h, int rank, int world, const void* handles) {
     if (!h || !handles || world < 1 || world > NGS_MAX_RANKS || rank < 0 || rank >= world) return NGS_ERR_INVALID;
+    SERVE_OFF(h);
     if (!h->d_xslots) return fail(h, NGS_ERR_INVALID, "ngs_xchg_attach before ngs_xchg_export");
     CU(h, cudaSetDevice(h->device));
     const unsigned char* hb = static_cast<const unsigned char*>(handles);

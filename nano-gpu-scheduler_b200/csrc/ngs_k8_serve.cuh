@@ -1,0 +1,215 @@
+// ngs_k8_serve.cuh — K8, the resident form of K7: one pod's whole cycle (filter + prioritize + arg-max + bind) without
+// a kernel launch per pod.
+//
+// A launch whose completion the host can see costs 8-9 us on this box even for an empty kernel
+// (profiles/r02/param_size_bench.txt); K7's own work is about 7 us (profiles/r02/k7_phases.txt).  K8 is launched once
+// (cooperatively: every CTA must be resident, they wait for each other's requests) and then serves requests the host
+// drops into a 256-byte block of mapped pinned memory:
+//   host   : payload words, store fence, then the request's sequence number into the last word of each 64-byte chunk
+//   CTA 0  : warp 0 polls the block with one coalesced 256-byte read; a request is complete when the four sequence words
+//            agree (a 64-byte chunk is read at one point in time, and the host wrote its payload before its sequence
+//            word), copies it into device memory and publishes the sequence number there (release)
+//   all    : one thread per CTA spins on that word (acquire), the CTA reads the request and runs K7's body: scan of its
+//            rows, atomicMax of the best key, ticket; the CTA that draws the last ticket binds the winner and writes
+//            (node, score, plan) and then the sequence number into mapped host memory, where the host polls it
+// The kernel leaves when asked to (a request with quit set) or when no request arrived for idle_cycles; the host restarts
+// it on the next request.  Every wait is bounded.  Arg-max policies on unsharded handles; everything else goes through K7.
+// Same results as K7 and K6 (tests/test_gpu_serve.py).  Included by ngs_dealer.cu after ngs_k7_one.cuh.
+#pragma once
+
+constexpr int SERVE_REQ_WORDS = 64;    // the request block: 4 chunks of 16 words, the 16th of each = sequence number
+constexpr int SERVE_BODY_WORDS = 60;
+constexpr uint32_t SERVE_QUIT = 0xFFFFFFFFu;
+
+struct ServeBody {
+    PodDemand pd;
+    LoadParams lp;
+    uint32_t rl_zero;  // Tables::rl_zero for this request
+    uint32_t max_c;
+    uint32_t quit;
+};
+static_assert(sizeof(ServeBody) <= SERVE_BODY_WORDS * 4 && sizeof(ServeBody) % 4 == 0, "the request body has to fit the block");
+constexpr int SERVE_BODY_USED = (int)(sizeof(ServeBody) / 4);
+
+struct ServeDev {  // device memory: the request as CTA 0 publishes it to the other CTAs
+    uint32_t seq;
+    uint32_t pad[3];
+    uint32_t body[SERVE_BODY_WORDS];
+};
+
+// out (mapped host memory): [0] sequence number of the request answered, [1] status, [8] node, [9] score, [10 ..) gpu indexes
+template <bool WIDE>
+__global__ void __launch_bounds__(256, 3) k_serve(Tables T, OneRec* rec, ServeDev* dev, const uint32_t* req, int32_t* out, uint32_t* exited,
+                                                 uint32_t last_seq, uint32_t launch_id, long long idle_cycles) {
+    __shared__ ServeBody body;
+    __shared__ SortedDemand dem;
+    __shared__ double s_pair[121];
+    __shared__ uint64_t s_wmax[8];
+    __shared__ int s_last;
+    __shared__ int32_t s_plan[NGS_MAX_CONTAINERS];
+    __shared__ WideCtx s_wcx;
+    __shared__ uint32_t s_seq;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    fill_usage_pair_table(s_pair, tid, blockDim.x);  // (constant: once per launch)
+    uint32_t last = last_seq;
+    const long long wait_limit = idle_cycles * 2 + SPIN_TIMEOUT_CYCLES;
+    for (;;) {
+        // ---- the next request ----
+        if (blockIdx.x == 0 && warp == 0) {
+            const long long t0 = clock64();
+            uint32_t lo = 0, hi = 0, seq = last;
+            bool idle = false;
+            for (uint32_t spins = 0;; spins++) {
+                asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "l"(req + 2 * lane) : "memory");
+                const uint32_t s0 = __shfl_sync(FULL, hi, 7), s1 = __shfl_sync(FULL, hi, 15), s2 = __shfl_sync(FULL, hi, 23),
+                               s3 = __shfl_sync(FULL, hi, 31);
+                if (s0 == s1 && s1 == s2 && s2 == s3 && s0 != last) {
+                    seq = s0;
+                    break;
+                }
+                if ((spins & 15u) == 15u) {  // (lane 0's clock decides for the warp)
+                    idle = __shfl_sync(FULL, clock64() - t0 > idle_cycles ? 1 : 0, 0) != 0;
+                    if (idle) break;
+                }
+            }
+            if (!idle) {
+                // words 2*lane, 2*lane+1 of the block; word w = chunk w/16, position w%16 (position 15 = sequence number)
+                const uint32_t w0 = 2 * lane, w1 = w0 + 1;
+                dev->body[(w0 >> 4) * 15 + (w0 & 15u)] = lo;  // (w0 is even: never a sequence word)
+                if ((w1 & 15u) != 15u) dev->body[(w1 >> 4) * 15 + (w1 & 15u)] = hi;
+                __threadfence();
+            }
+            __syncwarp();
+            if (lane == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&dev->seq), "r"(idle ? SERVE_QUIT : seq) : "memory");
+        }
+        if (tid == 0) {
+            const long long t0 = clock64();
+            uint32_t v;
+            for (uint32_t spins = 0;; spins++) {
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&dev->seq) : "memory");
+                if (v != last) break;
+                if ((spins & 255u) == 255u && clock64() - t0 > wait_limit) {  // CTA 0 is gone: never expected
+                    v = SERVE_QUIT;
+                    break;
+                }
+            }
+            s_seq = v;
+        }
+        __syncthreads();
+        const uint32_t cur = s_seq;
+        if (cur == SERVE_QUIT) break;
+        last = cur;
+        if (tid < SERVE_BODY_USED) reinterpret_cast<uint32_t*>(&body)[tid] = __ldcg(dev->body + tid);
+        __syncthreads();
+        if (body.quit) break;
+
+        // ---- K7's body (ngs_k7_one.cuh), one GPU, arg-max policies ----
+        Tables Tq = T;
+        Tq.rl_zero = body.rl_zero;
+        const LoadParams& lp = body.lp;
+        const bool load_path = lp.enabled != 0;
+        uint32_t row = blockIdx.x * blockDim.x + tid;
+        RowIn in;
+        if (row < Tq.n) load_row(Tq, row, load_path, in);
+        if (tid == 32) sort_demand(body.pd.percent, body.pd.n, body.pd.policy, &dem);
+        if (WIDE && tid == 64) {
+            s_wcx.T = Tq;
+            s_wcx.lp = lp;
+        }
+        __syncthreads();
+        uint64_t best = 0;
+        for (; row < Tq.n; row += gridDim.x * blockDim.x) {
+            const RowEval ev = eval_row_values<false, false>(Tq, row, in, &dem, lp, true, s_pair, nullptr);
+            if (ev.known && ev.feasible) {
+                const uint64_t k = make_key(ev.score, Tq.first + row);
+                best = k > best ? k : best;
+            }
+            const uint32_t nxt = row + gridDim.x * blockDim.x;
+            if (nxt < Tq.n) load_row(Tq, nxt, load_path, in);
+        }
+        if (WIDE) {
+            for (row = blockIdx.x * blockDim.x + tid; row < Tq.n; row += gridDim.x * blockDim.x) {
+                if (Tq.gcount[row] <= 8) continue;
+                const uint4 w = eval_wide_row(&s_wcx, row, &dem, WIDE_RATE | (lp.enabled ? WIDE_LOAD : 0u));
+                if (w.x & 1u) {
+                    const uint64_t k = make_key((int)w.y, Tq.first + row);
+                    best = k > best ? k : best;
+                }
+            }
+        }
+        best = warp_max_u64(best);
+        if (lane == 0) s_wmax[warp] = best;
+        __syncthreads();
+        if (tid == 0) {
+            uint64_t m = 0;
+            for (uint32_t w = 0; w < blockDim.x / 32; w++) m = s_wmax[w] > m ? s_wmax[w] : m;
+            if (m) atomicMax(&rec->key, (unsigned long long)m);
+            __threadfence();  // this CTA's RemainLoad stores and its key, before the ticket
+            s_last = atomicAdd(&rec->arrived, 1u) == gridDim.x - 1 ? 1 : 0;
+        }
+        __syncthreads();
+        if (s_last && warp == 0) {
+            // ---- warp 0 of the last CTA to arrive: every CTA's key and RemainLoad rows are visible now ----
+            __threadfence();
+            unsigned long long key = 0;
+            if (lane == 0) {
+                key = atomicAdd(&rec->key, 0ull);
+                rec->key = 0;  // ready for the next request: nobody touches the record before the host has seen this answer
+                rec->arrived = 0;
+            }
+            key = __shfl_sync(FULL, key, 0);
+            int32_t* gout = out + 10;
+            if (lane < NGS_MAX_CONTAINERS) s_plan[lane] = INT32_MIN;
+            __syncwarp();
+            if (key == 0) {
+                if (lane == 0) {
+                    out[8] = -1;
+                    out[9] = NGS_SCORE_MIN;
+                }
+            } else {
+                const uint32_t wrow = key_node(key) - Tq.first;
+                const int g = (int)(lane & 7u), gbase = (int)(lane & 24u);
+                const int G = Tq.gcount[wrow];
+                const int cell = __ldcg(Tq.free + (size_t)wrow * 8 + g);
+                const int rlc = (Tq.rl_zero ? 0 : (int)__ldcg(Tq.rl + (size_t)wrow * 8 + g)) + 2;
+                uint64_t emit = 0;
+                int n_emit = 0, fr = 0;
+                if (WIDE && G > 8) {
+                    if (lane == 0) {
+                        const uint4 r = eval_wide_row(&s_wcx, wrow, &dem, WIDE_APPLY);
+                        emit = (uint64_t)r.z | ((uint64_t)r.w << 32);
+                    }
+                    emit = __shfl_sync(FULL, emit, 0);
+                } else {
+                    choose_group8<true>(g, gbase, cell, rlc, g < G, dem.policy == NGS_POLICY_SPREAD, &dem, &emit, &n_emit, &fr);
+                }
+                if (lane < 8) {
+                    if (g < G && G <= 8) Tq.free[(size_t)wrow * 8 + lane] = fr;  // GPUs.Allocate (allocate.go:102-118)
+                    for (int k = (int)lane; k < dem.C; k += 8) {                // rater.go:102-105
+                        const int e = (int)((emit >> (4 * k)) & 0xF);
+                        s_plan[dem.order[k]] = e == 0xF ? NGS_NOT_NEED_GPU : e;
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) {
+                    Tq.tag[wrow] = 0;  // node.go:82
+                    out[8] = (int32_t)(Tq.first + wrow);
+                    out[9] = key_score(key);
+                }
+            }
+            __syncwarp();
+            if (lane < body.max_c) gout[lane] = lane < NGS_MAX_CONTAINERS ? s_plan[lane] : INT32_MIN;
+            __syncwarp();
+            if (lane == 0) {
+                out[1] = NGS_OK;
+                __threadfence_system();  // the answer (and the bound row, for whoever reads the table next) before the word that says so
+                *reinterpret_cast<volatile int32_t*>(out) = (int32_t)cur;
+            }
+        }
+        // (the other CTAs, and the other warps of that one, go straight back to waiting)
+    }
+    if (blockIdx.x == 0 && tid == 0) {
+        __threadfence_system();
+        *reinterpret_cast<volatile uint32_t*>(exited) = launch_id;
+    }
+}

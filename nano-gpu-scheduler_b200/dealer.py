@@ -230,6 +230,21 @@ class GpuDealer:
                                                  _p(node), _p(score), _p(gidx)))
         return node[:P], score[:P], gidx[:P]
 
+    def serve_pod(self, percent, policy, load=None, seed=0, seq0=0):
+        """one pod through the resident kernel -> (node, score, gpu_idx[C]); same decision as schedule_batch with one pod"""
+        d = np.ascontiguousarray(percent, dtype=np.int32)
+        c = max(len(d), 1)
+        node, score = C.c_int32(0), C.c_int32(0)
+        gidx = np.full(c, INT32_MIN, dtype=np.int32)
+        self._check(self._lib.ngs_serve_pod(self._h, _p(d), len(d), c, policy, _ref(load), seed, seq0, C.byref(node), C.byref(score), _p(gidx)))
+        return node.value, score.value, gidx[: len(d)]
+
+    def serve_stop(self):
+        self._check(self._lib.ngs_serve_stop(self._h))
+
+    def serve_idle_ms(self, ms):
+        self._check(self._lib.ngs_serve_idle_ms(self._h, float(ms)))
+
     def schedule_batch_dev(self, n_pods, d_percent, d_ncont, max_c, d_policy, d_node, d_score, d_gidx, load=None, seed=0,
                            seq0=0):
         """device-pointer form: arguments are raw device addresses (e.g. torch.Tensor.data_ptr())."""

@@ -1,0 +1,110 @@
+"""K8, the resident single-pod kernel (ngs_serve_pod): the same decisions and table updates as the oracle (and hence as
+ngs_schedule_batch), across idle exits, restarts and other calls in between."""
+import time
+
+import numpy as np
+import pytest
+
+import oracle as o
+from tests.parity_util import fill_load_tables, load_ctx_pair, make_pair
+from tests.test_gpu_wide_nodes import assert_same_nodes, mixed_pair
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300)]
+
+
+@pytest.fixture(scope="module")
+def ngs(built):
+    import nano_gpu_scheduler_b200 as m
+
+    return m
+
+
+def one(oc, dem, policy, load, seq):
+    pc = np.zeros((1, 12), dtype=np.int32)
+    pc[0, : len(dem)] = dem
+    n, s, g = oc.schedule_batch(pc, np.array([len(dem)], dtype=np.int32), [policy], load=load, seed=9, seq0=seq)
+    return int(n[0]), int(s[0]), g[0, : len(dem)].tolist()
+
+
+def demands(rng, k):
+    for _ in range(k):
+        yield (rng.integers(0, 13, int(rng.integers(1, 6))) * 5).astype(np.int32)
+
+
+@pytest.mark.parametrize("policy", [0, 1])
+@pytest.mark.parametrize("load_on", [False, True])
+def test_served_pods_match_the_oracle(ngs, policy, load_on):
+    n = 30000
+    oc, d, _, _ = make_pair(ngs, n, 0.5, 0x5E7 + policy)
+    lg, lo = (None, None)
+    rng = np.random.default_rng(3)
+    with d:
+        if load_on:
+            fill_load_tables(oc, d, n, 0x5E7)
+            lg, lo = load_ctx_pair(ngs)
+        for seq, dem in enumerate(demands(rng, 300)):
+            node, score, gidx = d.serve_pod(dem, policy, load=lg, seed=9, seq0=seq)
+            assert (node, score, gidx.tolist()) == one(oc, dem, policy, lo, seq), (seq, dem)
+        d.serve_stop()
+        gc, fr, rl = d.snapshot_read()
+        ogc, ofr, orl = oc.snapshot()
+        assert np.array_equal(fr, ofr) and np.array_equal(rl, orl)
+
+
+def test_idle_exit_restart_and_other_calls_in_between(ngs):
+    n = 5000
+    oc, d, _, _ = make_pair(ngs, n, 0.4, 77)
+    rng = np.random.default_rng(5)
+    with d:
+        d.serve_idle_ms(2.0)
+        launches0 = d.stats()["kernel_launches"]
+        seq = 0
+        for round_ in range(4):
+            for dem in demands(rng, 25):
+                node, score, gidx = d.serve_pod(dem, 0, seed=9, seq0=seq)
+                assert (node, score, gidx.tolist()) == one(oc, dem, 0, None, seq)
+                seq += 1
+            if round_ == 0:
+                time.sleep(0.05)  # the kernel leaves on its own; the next pod starts it again
+            elif round_ == 1:
+                dem = np.array([20, 20], dtype=np.int32)  # another verb in between stops it first
+                a = d.assume(dem, 0)
+                b = oc.assume(dem, 0)
+                assert np.array_equal(a["feasible"], b["feasible"]) and np.array_equal(a["score"], b["score"])
+            elif round_ == 2:
+                d.node_apply(7, [0], [5], -1)
+                oc.node_apply(7, [0], [5], -1)
+        # random policy goes through the launched kernel from inside the call, same answer as the oracle
+        for dem in demands(rng, 10):
+            node, score, gidx = d.serve_pod(dem, 2, seed=9, seq0=seq)
+            assert (node, score, gidx.tolist()) == one(oc, dem, 2, None, seq)
+            seq += 1
+        assert d.stats()["kernel_launches"] - launches0 < 60  # 100 served pods took a handful of launches, not 100
+        d.serve_stop()
+        d.serve_stop()  # idempotent
+        gc, fr, rl = d.snapshot_read()
+        assert np.array_equal(fr, oc.snapshot()[1])
+
+
+def test_served_pods_on_clusters_with_wide_nodes(ngs):
+    n = 3000
+    oc, d, _ = mixed_pair(ngs, n, 4242, p_used=0.4, min_g=6)
+    rng = np.random.default_rng(8)
+    with d:
+        for seq, dem in enumerate(demands(rng, 150)):
+            policy = seq % 2
+            node, score, gidx = d.serve_pod(dem, policy, seed=9, seq0=seq)
+            assert (node, score, gidx.tolist()) == one(oc, dem, policy, None, seq), (seq, dem)
+        d.serve_stop()
+        assert_same_nodes(oc, d, n)
+
+
+def test_a_pod_that_fits_nowhere_and_bad_arguments(ngs):
+    with ngs.GpuDealer(64, device=0) as d:
+        d.snapshot_load(np.full(64, 2, dtype=np.uint8))
+        node, score, gidx = d.serve_pod([100, 100, 100], 0)
+        assert node == -1 and score == 0 and gidx.tolist() == [-(2**31)] * 3
+        with pytest.raises(ngs.NgsError):
+            d.serve_pod([-5], 0)
+        node, score, gidx = d.serve_pod([100, 100], 1)
+        assert node == 0 and sorted(gidx.tolist()) == [0, 1]
