@@ -465,7 +465,7 @@ int serve_stop(ngs_dealer* h) {
         const uint32_t seq = h->serve_seq = serve_next_seq(h->serve_seq);
         for (int i = 0; i < SERVE_BODY_WORDS; i++) rq[(i / 15) * 16 + i % 15] = i < SERVE_BODY_USED ? w[i] : 0u;
         std::atomic_thread_fence(std::memory_order_seq_cst);
-        for (int c = 0; c < 4; c++) rq[c * 16 + 15] = seq;
+        for (int c = 0; c < SERVE_CHUNKS; c++) rq[c * 16 + 15] = seq;
         std::atomic_thread_fence(std::memory_order_seq_cst);
     }
     h->serve_running = false;
@@ -499,6 +499,7 @@ int serve_start(ngs_dealer* h, uint32_t last_seq) {
     ServeDev init;
     memset(&init, 0, sizeof(init));
     init.seq = last_seq;
+    init.prev_row = 0xFFFFFFFFu;
     CU(h, cudaMemcpyAsync(h->d_serve_dev, &init, sizeof(init), cudaMemcpyHostToDevice, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));  // (pageable source; and nothing else of this handle is in flight from here on)
     h->serve_launch = h->serve_launch + 1 ? h->serve_launch + 1 : 1;
@@ -702,6 +703,14 @@ int ngs_debug_phases(ngs_dealer* h, unsigned long long* out, uint32_t* grid) {
 }
 #endif
 
+#ifdef NGS_K8_TIMING
+// profiling builds only: nanoseconds from CTA 0 seeing the last served request to each stamp of the CTA that answered it
+int ngs_debug_k8(ngs_dealer* h, int32_t* out5) {
+    if (!h || !h->h_serve_out) return NGS_ERR_INVALID;
+    for (int i = 0; i < 5; i++) out5[i] = h->h_serve_out[32 + i];
+    return NGS_OK;
+}
+#endif
 #ifdef NGS_K7_TIMING
 // profiling builds only: cycles from kernel entry to each stamp of the last k_schedule_one launch (its last CTA)
 int ngs_debug_k7(ngs_dealer* h, int32_t* out5) {
@@ -1313,8 +1322,10 @@ int ngs_serve_pod(ngs_dealer* h, const int32_t* percent, int n_containers, int m
     }
     ServeBody b;
     memset(&b, 0, sizeof(b));
-    int rc = make_demand(h, percent, n_containers, policy, &b.pd);
+    PodDemand pd;
+    int rc = make_demand(h, percent, n_containers, policy, &pd);
     if (rc) return rc;
+    sort_demand(pd.percent, pd.n, pd.policy, &b.dem);
     rc = make_load(h, load, &b.lp);
     if (rc) return rc;
     CU(h, cudaSetDevice(h->device));
@@ -1338,7 +1349,7 @@ int ngs_serve_pod(ngs_dealer* h, const int32_t* percent, int n_containers, int m
     const uint32_t* w = reinterpret_cast<const uint32_t*>(&b);
     for (int i = 0; i < SERVE_BODY_USED; i++) rq[(i / 15) * 16 + i % 15] = w[i];
     std::atomic_thread_fence(std::memory_order_seq_cst);  // payload before the sequence words
-    for (int c = 0; c < 4; c++) rq[c * 16 + 15] = seq;
+    for (int c = 0; c < SERVE_CHUNKS; c++) rq[c * 16 + 15] = seq;
     std::atomic_thread_fence(std::memory_order_seq_cst);
     volatile int32_t* out = h->h_serve_out;
     int restarts = 0;

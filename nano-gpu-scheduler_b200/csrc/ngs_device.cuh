@@ -76,8 +76,8 @@ struct LoadParams {
 };
 
 // sort.Sort(sortableDemand) (rater.go:81,134) with the Go 1.16 small-slice rule, then the
-// traversal order of rater.go:82.  Serial, executed by one thread per block.
-__device__ inline void sort_demand(const int32_t* percent, int C, int policy, SortedDemand* out) {
+// traversal order of rater.go:82.  Serial, executed by one thread per block (or by the host, for the resident kernel).
+__host__ __device__ inline void sort_demand(const int32_t* percent, int C, int policy, SortedDemand* out) {
     int key[NGS_MAX_CONTAINERS], idx[NGS_MAX_CONTAINERS];
     for (int i = 0; i < NGS_MAX_CONTAINERS; i++) {
         key[i] = i < C ? percent[i] : 0;

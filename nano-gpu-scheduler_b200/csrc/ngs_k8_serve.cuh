@@ -5,8 +5,9 @@
 // (profiles/r02/param_size_bench.txt); K7's own work is about 7 us (profiles/r02/k7_phases.txt).  K8 is launched once
 // (cooperatively: every CTA must be resident, they wait for each other's requests) and then serves requests the host
 // drops into a 256-byte block of mapped pinned memory:
-//   host   : payload words, store fence, then the request's sequence number into the last word of each 64-byte chunk
-//   CTA 0  : warp 0 polls the block with one coalesced 256-byte read; a request is complete when the four sequence words
+//   host   : payload words (the demand already sorted), store fence, then the request's sequence number into the last
+//            word of each 64-byte chunk
+//   CTA 0  : warp 0 polls the block with one coalesced 512-byte read; a request is complete when the eight sequence words
 //            agree (a 64-byte chunk is read at one point in time, and the host wrote its payload before its sequence
 //            word), copies it into device memory and publishes the sequence number there (release)
 //   all    : one thread per CTA spins on that word (acquire), the CTA reads the request and runs K7's body: scan of its
@@ -17,12 +18,13 @@
 // Same results as K7 and K6 (tests/test_gpu_serve.py).  Included by ngs_dealer.cu after ngs_k7_one.cuh.
 #pragma once
 
-constexpr int SERVE_REQ_WORDS = 64;    // the request block: 4 chunks of 16 words, the 16th of each = sequence number
-constexpr int SERVE_BODY_WORDS = 60;
+constexpr int SERVE_CHUNKS = 8;
+constexpr int SERVE_REQ_WORDS = SERVE_CHUNKS * 16;  // the request block: chunks of 16 words, the 16th of each = sequence number
+constexpr int SERVE_BODY_WORDS = SERVE_CHUNKS * 15;
 constexpr uint32_t SERVE_QUIT = 0xFFFFFFFFu;
 
 struct ServeBody {
-    PodDemand pd;
+    SortedDemand dem;  // sorted by the host (sort_demand): every CTA would otherwise spend 0.5 us on it per request
     LoadParams lp;
     uint32_t rl_zero;  // Tables::rl_zero for this request
     uint32_t max_c;
@@ -33,7 +35,8 @@ constexpr int SERVE_BODY_USED = (int)(sizeof(ServeBody) / 4);
 
 struct ServeDev {  // device memory: the request as CTA 0 publishes it to the other CTAs
     uint32_t seq;
-    uint32_t pad[3];
+    uint32_t prev_row;  // the row the previous request was bound to (0xFFFFFFFF: none): the one row that changed since
+    uint32_t pad[2];
     uint32_t body[SERVE_BODY_WORDS];
 };
 
@@ -42,28 +45,40 @@ template <bool WIDE>
 __global__ void __launch_bounds__(256, 3) k_serve(Tables T, OneRec* rec, ServeDev* dev, const uint32_t* req, int32_t* out, uint32_t* exited,
                                                  uint32_t last_seq, uint32_t launch_id, long long idle_cycles) {
     __shared__ ServeBody body;
-    __shared__ SortedDemand dem;
     __shared__ double s_pair[121];
     __shared__ uint64_t s_wmax[8];
     __shared__ int s_last;
     __shared__ int32_t s_plan[NGS_MAX_CONTAINERS];
     __shared__ WideCtx s_wcx;
-    __shared__ uint32_t s_seq;
+    __shared__ uint32_t s_seq, s_prev_row;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     fill_usage_pair_table(s_pair, tid, blockDim.x);  // (constant: once per launch)
     uint32_t last = last_seq;
     const long long wait_limit = idle_cycles * 2 + SPIN_TIMEOUT_CYCLES;
+    // Between two requests the tables change in one row only (the one the last pod was bound to; everything else that
+    // writes them stops this kernel first), so every thread asks for its first row of the NEXT request before it starts
+    // waiting for it, in the load mode of the request just served; the loads land while the request travels.
+    RowIn in;
+    int pref_mode = -1;  // what `in` was requested for: -1 nothing, else (load-aware ? 2 : 0) | rl_zero
+    const uint32_t row_first = blockIdx.x * blockDim.x + tid;
+#ifdef NGS_K8_TIMING
+    unsigned long long tg[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#define K8_STAMP(i) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tg[i]))
+#else
+#define K8_STAMP(i) do { } while (0)
+#endif
     for (;;) {
         // ---- the next request ----
         if (blockIdx.x == 0 && warp == 0) {
             const long long t0 = clock64();
-            uint32_t lo = 0, hi = 0, seq = last;
+            uint32_t w0 = 0, w1 = 0, w2 = 0, w3 = 0, seq = last;
             bool idle = false;
             for (uint32_t spins = 0;; spins++) {
-                asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "l"(req + 2 * lane) : "memory");
-                const uint32_t s0 = __shfl_sync(FULL, hi, 7), s1 = __shfl_sync(FULL, hi, 15), s2 = __shfl_sync(FULL, hi, 23),
-                               s3 = __shfl_sync(FULL, hi, 31);
-                if (s0 == s1 && s1 == s2 && s2 == s3 && s0 != last) {
+                // words 4*lane .. 4*lane+3 of the block: the sequence words (position 15 of each 16-word chunk) are w3 of lanes 3, 7, .. 31
+                asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3) : "l"(req + 4 * lane) : "memory");
+                const uint32_t s0 = __shfl_sync(FULL, w3, 3);
+                const bool same = __all_sync(FULL, (lane & 3u) != 3u || w3 == s0);
+                if (same && s0 != last) {
                     seq = s0;
                     break;
                 }
@@ -72,11 +87,20 @@ __global__ void __launch_bounds__(256, 3) k_serve(Tables T, OneRec* rec, ServeDe
                     if (idle) break;
                 }
             }
+#ifdef NGS_K8_TIMING
+            if (lane == 0) {
+                unsigned long long t;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                reinterpret_cast<unsigned long long*>(dev->pad)[0] = t;  // when CTA 0 saw the request
+            }
+#endif
             if (!idle) {
-                // words 2*lane, 2*lane+1 of the block; word w = chunk w/16, position w%16 (position 15 = sequence number)
-                const uint32_t w0 = 2 * lane, w1 = w0 + 1;
-                dev->body[(w0 >> 4) * 15 + (w0 & 15u)] = lo;  // (w0 is even: never a sequence word)
-                if ((w1 & 15u) != 15u) dev->body[(w1 >> 4) * 15 + (w1 & 15u)] = hi;
+                // block word w = chunk w/16, position w%16 -> body word 15 * (w/16) + w%16
+                const uint32_t b = (lane >> 2) * 15u + (lane & 3u) * 4u;
+                dev->body[b] = w0;
+                dev->body[b + 1] = w1;
+                dev->body[b + 2] = w2;
+                if ((lane & 3u) != 3u) dev->body[b + 3] = w3;
                 __threadfence();
             }
             __syncwarp();
@@ -96,10 +120,12 @@ __global__ void __launch_bounds__(256, 3) k_serve(Tables T, OneRec* rec, ServeDe
             s_seq = v;
         }
         __syncthreads();
+        K8_STAMP(0);  // this CTA has seen the published request
         const uint32_t cur = s_seq;
         if (cur == SERVE_QUIT) break;
         last = cur;
         if (tid < SERVE_BODY_USED) reinterpret_cast<uint32_t*>(&body)[tid] = __ldcg(dev->body + tid);
+        if (tid == 64) s_prev_row = __ldcg(&dev->prev_row);
         __syncthreads();
         if (body.quit) break;
 
@@ -107,16 +133,17 @@ __global__ void __launch_bounds__(256, 3) k_serve(Tables T, OneRec* rec, ServeDe
         Tables Tq = T;
         Tq.rl_zero = body.rl_zero;
         const LoadParams& lp = body.lp;
+        const SortedDemand& dem = body.dem;
         const bool load_path = lp.enabled != 0;
-        uint32_t row = blockIdx.x * blockDim.x + tid;
-        RowIn in;
-        if (row < Tq.n) load_row(Tq, row, load_path, in);
-        if (tid == 32) sort_demand(body.pd.percent, body.pd.n, body.pd.policy, &dem);
+        uint32_t row = row_first;
+        const int mode = (load_path ? 2 : 0) | (int)(Tq.rl_zero & 1u);
+        if (row < Tq.n && (pref_mode != mode || row == s_prev_row)) load_row(Tq, row, load_path, in);
         if (WIDE && tid == 64) {
             s_wcx.T = Tq;
             s_wcx.lp = lp;
         }
         __syncthreads();
+        K8_STAMP(1);  // body read, demand sorted
         uint64_t best = 0;
         for (; row < Tq.n; row += gridDim.x * blockDim.x) {
             const RowEval ev = eval_row_values<false, false>(Tq, row, in, &dem, lp, true, s_pair, nullptr);
@@ -137,6 +164,7 @@ __global__ void __launch_bounds__(256, 3) k_serve(Tables T, OneRec* rec, ServeDe
                 }
             }
         }
+        K8_STAMP(2);  // rows evaluated
         best = warp_max_u64(best);
         if (lane == 0) s_wmax[warp] = best;
         __syncthreads();
@@ -148,6 +176,7 @@ __global__ void __launch_bounds__(256, 3) k_serve(Tables T, OneRec* rec, ServeDe
             s_last = atomicAdd(&rec->arrived, 1u) == gridDim.x - 1 ? 1 : 0;
         }
         __syncthreads();
+        K8_STAMP(3);  // ticket drawn
         if (s_last && warp == 0) {
             // ---- warp 0 of the last CTA to arrive: every CTA's key and RemainLoad rows are visible now ----
             __threadfence();
@@ -165,6 +194,7 @@ __global__ void __launch_bounds__(256, 3) k_serve(Tables T, OneRec* rec, ServeDe
                 if (lane == 0) {
                     out[8] = -1;
                     out[9] = NGS_SCORE_MIN;
+                    dev->prev_row = 0xFFFFFFFFu;
                 }
             } else {
                 const uint32_t wrow = key_node(key) - Tq.first;
@@ -195,18 +225,26 @@ __global__ void __launch_bounds__(256, 3) k_serve(Tables T, OneRec* rec, ServeDe
                     Tq.tag[wrow] = 0;  // node.go:82
                     out[8] = (int32_t)(Tq.first + wrow);
                     out[9] = key_score(key);
+                    dev->prev_row = wrow;
                 }
             }
             __syncwarp();
             if (lane < body.max_c) gout[lane] = lane < NGS_MAX_CONTAINERS ? s_plan[lane] : INT32_MIN;
             __syncwarp();
             if (lane == 0) {
+#ifdef NGS_K8_TIMING
+                K8_STAMP(4);
+                const unsigned long long t_seen = reinterpret_cast<const volatile unsigned long long*>(dev->pad)[0];
+                for (int i = 0; i < 5; i++) out[32 + i] = (int32_t)(tg[i] - t_seen);  // ns since CTA 0 saw the request
+#endif
                 out[1] = NGS_OK;
                 __threadfence_system();  // the answer (and the bound row, for whoever reads the table next) before the word that says so
                 *reinterpret_cast<volatile int32_t*>(out) = (int32_t)cur;
             }
         }
         // (the other CTAs, and the other warps of that one, go straight back to waiting)
+        if (row_first < Tq.n) load_row(Tq, row_first, load_path, in);
+        pref_mode = mode;
     }
     if (blockIdx.x == 0 && tid == 0) {
         __threadfence_system();
