@@ -451,9 +451,13 @@ def run_verbs(ngs, cfg, gcount, free, tables, load, local_rank, cycles=200):
     lref = None if load is None else C.c_void_p(C.addressof(load))
     pol = C.c_int(cfg["policy"])
     vptr = C.c_void_p(0)
-    for label, idx, view in (("idx_null", None, False), ("idx_list", np.arange(n, dtype=np.uint32), False), ("idx_null_score_view", None, True)):
+    for label, idx, view, resident in (("idx_null", None, False, False), ("idx_list", np.arange(n, dtype=np.uint32), False, False),
+                                       ("idx_null_score_view", None, True, False), ("idx_null_resident", None, True, True),
+                                       ("idx_list_resident", np.arange(n, dtype=np.uint32), True, True)):
         score = np.zeros(n, dtype=np.int32)
         d = ngs.GpuDealer(n, device=local_rank)
+        if resident:  # K8: the three verbs as requests to the resident kernel, no launch per call
+            assert lib.ngs_serve_verbs(d._h, 1) == 0
         d.snapshot_load(gcount, free)
         if cfg["load"]:
             for m, (value, ts, absent) in enumerate(tables):
@@ -501,7 +505,8 @@ def run_verbs(ngs, cfg, gcount, free, tables, load, local_rank, cycles=200):
                       "h2d_bytes_per_cycle": (st1["h2d_bytes"] - st0["h2d_bytes"]) / cycles, "d2h_bytes_per_cycle": (st1["d2h_bytes"] - st0["d2h_bytes"]) / cycles}
     out["what"] = (f"{cycles} pod cycles of ngs_assume (feasible + reason out) + ngs_score + ngs_bind on {n} candidates, host buffers in and out, "
                    "wall clock per C call; idx_null = the candidate list is every row in order, idx_list = an explicit index list, "
-                   "idx_null_score_view = ngs_score_view instead of ngs_score (no copy of the scores into a caller's buffer)")
+                   "idx_null_score_view = ngs_score_view instead of ngs_score (no copy of the scores into a caller's buffer), "
+                   "*_resident = ngs_serve_verbs on (the three verbs served by the resident kernel, scores read in place)")
     return out
 
 

@@ -223,8 +223,13 @@ int ngs_schedule_batch_dev(ngs_dealer *h, uint32_t n_pods, const int32_t *d_perc
  *  - One caller at a time, like every call on a handle. */
 int ngs_serve_pod(ngs_dealer *h, const int32_t *percent, int n_containers, int max_c, int policy, const ngs_load_ctx *load,
                   uint64_t seed, uint64_t seq0, int32_t *node_out, int32_t *score_out, int32_t *gpu_idx_out);
-int ngs_serve_stop(ngs_dealer *h);
+int ngs_serve_stop(ngs_dealer *h);               /* also switches ngs_serve_verbs off */
 int ngs_serve_idle_ms(ngs_dealer *h, double ms); /* 0 < ms <= 2000; stops the kernel if it runs */
+/* on != 0: from now on ngs_assume / ngs_score / ngs_score_view (without per-node plans) and ngs_bind of this handle are
+ * served by the resident kernel as requests, too - same results, no launch per call - and do not stop it; it is started
+ * by the first such call and again after every call that had to stop it (snapshot updates, load updates, batches, calls
+ * that want plans).  Unsharded handles.  The occupancy note above applies for as long as this is on. */
+int ngs_serve_verbs(ngs_dealer *h, int on);
 
 /* ---- node-range sharding over the GPUs of one box (no reference counterpart: the reference is a
  * single process) ----

@@ -28,7 +28,7 @@ SYMBOLS = [
     "ngs_stats", "ngs_node_upsert", "ngs_snapshot_load", "ngs_snapshot_read", "ngs_node_apply", "ngs_release_batch", "ngs_load_add_node",
     "ngs_load_update", "ngs_load_update_bulk", "ngs_parse_usage", "ngs_parse_update_time", "ngs_assume", "ngs_assume_dev", "ngs_score",
     "ngs_bind", "ngs_schedule_batch", "ngs_schedule_batch_dev", "ngs_xchg_export", "ngs_xchg_attach",
-    "ngs_schedule_batch_noalloc", "ngs_node_set_wide", "ngs_node_get_wide", "ngs_score_view", "ngs_serve_pod", "ngs_serve_stop", "ngs_serve_idle_ms",
+    "ngs_schedule_batch_noalloc", "ngs_node_set_wide", "ngs_node_get_wide", "ngs_score_view", "ngs_serve_pod", "ngs_serve_stop", "ngs_serve_idle_ms", "ngs_serve_verbs",
 ]
 NOALLOC_MAX_PODS = 256
 NOALLOC_MAX_CTAS = 160
@@ -113,6 +113,7 @@ def load():
     L.ngs_serve_pod.argtypes = [vp, vp, ci, ci, ci, vp, u64, u64, vp, vp, vp]
     L.ngs_serve_stop.argtypes = [vp]
     L.ngs_serve_idle_ms.argtypes = [vp, dbl]
+    L.ngs_serve_verbs.argtypes = [vp, ci]
     L.ngs_schedule_batch.argtypes = [vp, u32, vp, vp, ci, vp, vp, u64, u64, vp, vp, vp]
     L.ngs_schedule_batch_dev.argtypes = [vp, u32, vp, vp, ci, vp, vp, u64, u64, vp, vp, vp]
     L.ngs_xchg_export.argtypes = [vp, vp]

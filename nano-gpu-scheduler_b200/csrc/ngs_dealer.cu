@@ -127,8 +127,11 @@ struct ngs_dealer {
     int32_t* h_serve_out = nullptr;   // mapped pinned: answer block
     int32_t* d_serve_out = nullptr;
     ServeDev* d_serve_dev = nullptr;
-    int serve_grid_cap[2] = {0, 0};   // co-resident CTAs of k_serve<false> / <true>
+    int serve_grid_cap[4] = {0, 0, 0, 0};  // co-resident CTAs of k_serve<WIDE, VERBS>, index WIDE + 2 * VERBS
+    bool serve_kind_verbs = false;    // which instantiation is running
     double serve_idle_ms = 20.0;      // the kernel leaves after this long without a request
+    bool serve_verbs = false;         // ngs_assume / ngs_score / ngs_bind go through the resident kernel, too (ngs_serve_verbs)
+    cudaStream_t copy_stream = nullptr;  // uploads while the resident kernel holds the handle's stream
     // nodes with 9..12 GPUs (ngs_wide.cuh): which rows, so that the batch kernel can refuse them before it binds anything
     std::vector<uint8_t> wide_row;
     uint32_t n_wide = 0;
@@ -485,12 +488,17 @@ int serve_start(ngs_dealer* h, uint32_t last_seq) {
         memset(h->h_serve_out, 0, 64 * 4);
         CU(h, cudaMalloc(&h->d_serve_dev, sizeof(ServeDev)));
         int per_sm = 0;
-        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_serve<false>, 256, 0));
+        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_serve<false, false>, 256, 0));
         h->serve_grid_cap[0] = per_sm * h->num_sms;
-        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_serve<true>, 256, 0));
+        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_serve<true, false>, 256, 0));
         h->serve_grid_cap[1] = per_sm * h->num_sms;
+        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_serve<false, true>, 256, 0));
+        h->serve_grid_cap[2] = per_sm * h->num_sms;
+        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_serve<true, true>, 256, 0));
+        h->serve_grid_cap[3] = per_sm * h->num_sms;
     }
-    const int wide = h->n_wide ? 1 : 0;
+    const int wide = (h->n_wide ? 1 : 0) + (h->serve_verbs ? 2 : 0);
+    h->serve_kind_verbs = h->serve_verbs;
     uint32_t grid = (h->T.n + 255) / 256;
     if (grid > (uint32_t)h->num_sms * 4) grid = (uint32_t)h->num_sms * 4;
     if (grid > (uint32_t)h->serve_grid_cap[wide]) grid = (uint32_t)h->serve_grid_cap[wide];
@@ -514,10 +522,65 @@ int serve_start(ngs_dealer* h, uint32_t last_seq) {
     cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, h->device);
     long long idle_cycles = (long long)(h->serve_idle_ms * (khz > 0 ? khz : 1900000));
     void* args[] = {&T, &rec, &dev, &req, &out, &exited, &last_seq, &launch_id, &idle_cycles};
-    const void* fn = wide ? (const void*)k_serve<true> : (const void*)k_serve<false>;
+    const void* fns[4] = {(const void*)k_serve<false, false>, (const void*)k_serve<true, false>, (const void*)k_serve<false, true>,
+                          (const void*)k_serve<true, true>};
+    const void* fn = fns[wide];
     CU(h, cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(256), args, 0, h->stream));
     h->serve_running = true;
     h->stats.kernel_launches++;
+    return NGS_OK;
+}
+
+// K8: make sure the resident kernel runs, post one request and wait for its answer (out[0] == sequence number)
+int serve_request(ngs_dealer* h, ServeBody& b) {
+    volatile uint32_t* rq = h->h_serve_req;
+    if (h->serve_running && rq[SERVE_REQ_WORDS] == h->serve_launch) {  // it left (idle): collect the launch
+        h->serve_running = false;
+        CU(h, cudaStreamSynchronize(h->stream));
+    }
+    if (h->serve_running && h->serve_kind_verbs != h->serve_verbs) {  // the other instantiation is wanted now
+        const int rc = serve_stop(h);
+        if (rc) return rc;
+    }
+    if (!h->serve_running) {
+        int rc = ensure_batch(h);
+        if (rc) return rc;
+        rc = serve_start(h, h->serve_seq);
+        if (rc) return rc;
+        rq = h->h_serve_req;
+    }
+    b.rl_zero = h->T.rl_zero;
+    const uint32_t seq = h->serve_seq = serve_next_seq(h->serve_seq);
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(&b);
+    for (int i = 0; i < SERVE_BODY_USED; i++) rq[(i / 15) * 16 + i % 15] = w[i];
+    std::atomic_thread_fence(std::memory_order_seq_cst);  // payload before the sequence words
+    for (int c = 0; c < SERVE_CHUNKS; c++) rq[c * 16 + 15] = seq;
+    std::atomic_thread_fence(std::memory_order_seq_cst);
+    volatile int32_t* out = h->h_serve_out;
+    int restarts = 0;
+    for (uint64_t spins = 1; (uint32_t)out[0] != seq; spins++) {
+#if defined(__x86_64__) || defined(__i386__)
+        __builtin_ia32_pause();
+#endif
+        if ((spins & 0x3FFu) == 0) {
+            if (rq[SERVE_REQ_WORDS] == h->serve_launch && (uint32_t)out[0] != seq) {
+                // the kernel left (idle) just before the request arrived: start it again, the request is still in the block
+                h->serve_running = false;
+                CU(h, cudaStreamSynchronize(h->stream));
+                if (++restarts > 3) return fail(h, NGS_ERR_TIMEOUT, "the resident kernel keeps leaving before it answers");
+                const int rc = serve_start(h, seq == 1 ? SERVE_QUIT - 1 : seq - 1);
+                if (rc) return rc;
+            } else if ((spins & 0xFFFFFu) == 0) {
+                const cudaError_t q = cudaStreamQuery(h->stream);
+                if (q != cudaErrorNotReady && (uint32_t)out[0] != seq && rq[SERVE_REQ_WORDS] != h->serve_launch) {
+                    h->serve_running = false;
+                    return fail(h, NGS_ERR_CUDA, "the resident kernel ended without an answer: %s", cudaGetErrorString(q));
+                }
+                if (spins > (1ull << 33)) return fail(h, NGS_ERR_TIMEOUT, "the resident kernel did not answer");
+            }
+        }
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);
     return NGS_OK;
 }
 
@@ -663,6 +726,7 @@ int ngs_destroy(ngs_dealer* h) {
     if (h->serve_running) serve_stop(h);
     if (h->stream) cudaStreamSynchronize(h->stream);
     cudaFreeHost(h->h_serve_req); cudaFreeHost(h->h_serve_out); cudaFree(h->d_serve_dev);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     cudaFree(h->T.free); cudaFree(h->T.gcount); cudaFree(h->T.rl); cudaFree(h->T.tenths); cudaFree(h->T.ts);
     cudaFree(h->T.tag); cudaFree(h->T.cscore); cudaFree(const_cast<int16_t*>(h->T.blut));
     cudaFree(h->T.free_hi); cudaFree(h->T.rl_hi); cudaFree(h->T.tenths_hi); cudaFree(h->T.ts_hi);
@@ -1005,7 +1069,9 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
                       const ngs_load_ctx* load, uint8_t* feasible, int8_t* reason, int32_t* score, int32_t* plan, int32_t* n_emitted,
                       const int32_t** score_view = nullptr) {
     if (!h) return NGS_ERR_INVALID;
-    SERVE_OFF(h);
+    // K8: with ngs_serve_verbs on, the scan goes to the resident kernel as a request (no plans there: those calls stop it)
+    const bool resident = h->serve_verbs && h->world == 1 && !plan && !n_emitted;
+    if (!resident || n > h->verb_cap || n > h->vstage_cap) SERVE_OFF(h);  // (growing the scratch frees device memory: not under a running kernel)
     if (score_view) *score_view = nullptr;
     PodDemand pd;
     LoadParams lp;
@@ -1027,7 +1093,13 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
         if (h->idx_sig == 0 || h->idx_host.size() != n || memcmp(h->idx_host.data(), idx, (size_t)n * 4) != 0) {
             // a list the device does not hold yet
             h->idx_host.assign(idx, idx + n);
-            CU(h, cudaMemcpyAsync(h->d_idx, h->idx_host.data(), (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+            if (resident) {  // the handle's stream belongs to the resident kernel: the list goes up on a stream of its own
+                if (!h->copy_stream) CU(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+                CU(h, cudaMemcpyAsync(h->d_idx, h->idx_host.data(), (size_t)n * 4, cudaMemcpyHostToDevice, h->copy_stream));
+                CU(h, cudaStreamSynchronize(h->copy_stream));
+            } else {
+                CU(h, cudaMemcpyAsync(h->d_idx, h->idx_host.data(), (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+            }
             h->stats.h2d_bytes += (size_t)n * 4;
             h->idx_sig = h->idx_sig + 1 ? h->idx_sig + 1 : 1;
         }
@@ -1041,36 +1113,55 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
         return NGS_OK;
     }
     h->sc_valid = false;
-    const int block = 256;
-    int grid = (int)((n + block - 1) / block);
-    const int max_grid = h->num_sms * (want_plan ? 2 : NGS_K1_BLOCKS);  // exactly the resident blocks: measured best
-    if (grid > max_grid) grid = max_grid;
-    // per-node outputs go straight into mapped host memory; the scores are always produced (an ngs_score usually follows)
-    VerbDone vd;
-    vd.ticket = h->d_vticket;
-    vd.flag = h->d_vflag;
-    vd.seq = ++h->vseq;
-    // one status byte per node travels (NGS_REASON_*); `feasible` is derived from it on the host
-    uint8_t* o_feas = nullptr;
-    int8_t* o_reason = (reason || feasible) ? h->d_vreason : nullptr;
-    int32_t* o_score = h->d_vscore;
-    if (!idx && mode == MODE_ASSUME && !want_plan) {
-        rc = launch_scan(h, n, pd, lp, gen, o_feas, o_reason, o_score, vd);
+    if (resident) {
+        ServeBody b;
+        memset(&b, 0, sizeof(b));
+        sort_demand(pd.percent, pd.n, pd.policy, &b.dem);
+        b.lp = lp;
+        b.op = SERVE_OP_SCAN;
+        b.mode = (uint32_t)mode;
+        b.gen = gen;
+        b.n = n;
+        const unsigned long long p_idx = (unsigned long long)(idx ? h->d_idx : nullptr), p_reason = (unsigned long long)((reason || feasible) ? h->d_vreason : nullptr),
+                                 p_score = (unsigned long long)h->d_vscore;
+        b.idx_lo = (uint32_t)p_idx; b.idx_hi = (uint32_t)(p_idx >> 32);
+        b.reason_lo = (uint32_t)p_reason; b.reason_hi = (uint32_t)(p_reason >> 32);
+        b.score_lo = (uint32_t)p_score; b.score_hi = (uint32_t)(p_score >> 32);
+        rc = serve_request(h, b);
         if (rc) return rc;
-    } else if (want_plan)
-        (h->n_wide ? k_assume<true, true> : k_assume<true, false>)<<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, o_feas, o_reason, o_score,
-                                                     plan ? h->d_plan : nullptr, n_emitted ? h->d_nem : nullptr, vd, AssumePad{});
-    else
-        (h->n_wide ? k_assume<false, true> : k_assume<false, false>)<<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, o_feas, o_reason, o_score, nullptr,
-                                                      nullptr, vd, AssumePad{});
-    CU(h, cudaGetLastError());
-    if (want_plan) {  // plans (the FailedNodes texts of the host mirror) still travel by copy commands
-        if (plan && n_containers > 0) CU(h, cudaMemcpyAsync(plan, h->d_plan, (size_t)n * n_containers * 4, cudaMemcpyDeviceToHost, h->stream));
-        if (n_emitted) CU(h, cudaMemcpyAsync(n_emitted, h->d_nem, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
-        CU(h, cudaStreamSynchronize(h->stream));
+        if (h->h_serve_out[1] != NGS_OK) return fail(h, h->h_serve_out[1], "resident scan: %s", ngs_strerror(h->h_serve_out[1]));
+    } else {
+        const int block = 256;
+        int grid = (int)((n + block - 1) / block);
+        const int max_grid = h->num_sms * (want_plan ? 2 : NGS_K1_BLOCKS);  // exactly the resident blocks: measured best
+        if (grid > max_grid) grid = max_grid;
+        // per-node outputs go straight into mapped host memory; the scores are always produced (an ngs_score usually follows)
+        VerbDone vd;
+        vd.ticket = h->d_vticket;
+        vd.flag = h->d_vflag;
+        vd.seq = ++h->vseq;
+        // one status byte per node travels (NGS_REASON_*); `feasible` is derived from it on the host
+        uint8_t* o_feas = nullptr;
+        int8_t* o_reason = (reason || feasible) ? h->d_vreason : nullptr;
+        int32_t* o_score = h->d_vscore;
+        if (!idx && mode == MODE_ASSUME && !want_plan) {
+            rc = launch_scan(h, n, pd, lp, gen, o_feas, o_reason, o_score, vd);
+            if (rc) return rc;
+        } else if (want_plan)
+            (h->n_wide ? k_assume<true, true> : k_assume<true, false>)<<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, o_feas, o_reason, o_score,
+                                                         plan ? h->d_plan : nullptr, n_emitted ? h->d_nem : nullptr, vd, AssumePad{});
+        else
+            (h->n_wide ? k_assume<false, true> : k_assume<false, false>)<<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, o_feas, o_reason, o_score, nullptr,
+                                                          nullptr, vd, AssumePad{});
+        CU(h, cudaGetLastError());
+        if (want_plan) {  // plans (the FailedNodes texts of the host mirror) still travel by copy commands
+            if (plan && n_containers > 0) CU(h, cudaMemcpyAsync(plan, h->d_plan, (size_t)n * n_containers * 4, cudaMemcpyDeviceToHost, h->stream));
+            if (n_emitted) CU(h, cudaMemcpyAsync(n_emitted, h->d_nem, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
+            CU(h, cudaStreamSynchronize(h->stream));
+        }
+        rc = wait_flag(h, h->h_vflag, vd.seq, "scan kernel");
+        if (rc) return rc;
     }
-    rc = wait_flag(h, h->h_vflag, vd.seq, "scan kernel");
-    if (rc) return rc;
     if (feasible) expand_feasible(feasible, h->h_vreason, n);
     if (reason) memcpy(reason, h->h_vreason, n);
     if (score) memcpy(score, h->h_vscore, (size_t)n * 4);
@@ -1082,7 +1173,7 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
         h->sc_sig = sig;
         h->sc_epoch = h->epoch;
     }
-    h->stats.kernel_launches++;
+    if (!resident) h->stats.kernel_launches++;
     h->stats.node_evals += n;
     h->stats.d2h_bytes += ((feasible || reason) ? n : 0) + (size_t)n * 4 +
                           (plan ? (size_t)n * n_containers * 4 : 0) + (n_emitted ? (size_t)n * 4 : 0);
@@ -1138,7 +1229,8 @@ int ngs_score_view(ngs_dealer* h, const uint32_t* idx, uint32_t n, const int32_t
 int ngs_bind(ngs_dealer* h, uint32_t idx, const int32_t* percent, int n_containers, int policy, const ngs_load_ctx* load,
              int32_t* gpu_idx_out, int32_t* score_out) {
     if (!h) return NGS_ERR_INVALID;
-    SERVE_OFF(h);
+    const bool resident = h->serve_verbs && h->world == 1;  // K8: the bind travels to the resident kernel as a request
+    if (!resident) SERVE_OFF(h);
     PodDemand pd;
     LoadParams lp;
     int rc = make_demand(h, percent, n_containers, policy, &pd);
@@ -1147,6 +1239,28 @@ int ngs_bind(ngs_dealer* h, uint32_t idx, const int32_t* percent, int n_containe
     if (rc) return rc;
     CU(h, cudaSetDevice(h->device));
     const uint32_t gen = demand_generation(h, pd, lp.enabled != 0);
+    if (resident) {
+        ServeBody b;
+        memset(&b, 0, sizeof(b));
+        sort_demand(pd.percent, pd.n, pd.policy, &b.dem);
+        b.lp = lp;
+        b.op = SERVE_OP_BIND;
+        b.gen = gen;
+        b.node = idx;
+        h->epoch++;
+        rc = serve_request(h, b);
+        if (rc) return rc;
+        volatile int32_t* out = h->h_serve_out;
+        h->stats.node_evals++;
+        h->stats.d2h_bytes += sizeof(BindResult);
+        rc = out[1];
+        if (rc) return fail(h, rc, "bind on node %u: %s", idx, ngs_strerror(rc));
+        for (int i = 0; i < n_containers; i++)
+            if (gpu_idx_out) gpu_idx_out[i] = out[10 + i];
+        if (score_out) *score_out = out[9];
+        h->stats.pods_scheduled++;
+        return NGS_OK;
+    }
     constexpr int32_t BIND_PENDING = 0x7FFFFFFE;
     *reinterpret_cast<volatile int32_t*>(&h->h_bind->status) = BIND_PENDING;
     h->epoch++;  // a row changes: scores kept from the last filter call are no longer the cache's
@@ -1329,53 +1443,13 @@ int ngs_serve_pod(ngs_dealer* h, const int32_t* percent, int n_containers, int m
     rc = make_load(h, load, &b.lp);
     if (rc) return rc;
     CU(h, cudaSetDevice(h->device));
-    volatile uint32_t* rq = h->h_serve_req;
-    if (h->serve_running && rq[SERVE_REQ_WORDS] == h->serve_launch) {  // it left (idle): collect the launch
-        h->serve_running = false;
-        CU(h, cudaStreamSynchronize(h->stream));
-    }
-    if (!h->serve_running) {
-        rc = ensure_batch(h);
-        if (rc) return rc;
-        rc = serve_start(h, h->serve_seq);
-        if (rc) return rc;
-        rq = h->h_serve_req;
-    }
     if (b.lp.enabled) h->T.rl_zero = 0;  // the load-aware Rate writes RemainLoad
-    b.rl_zero = h->T.rl_zero;
     b.max_c = (uint32_t)max_c;
+    b.op = SERVE_OP_POD;
     h->epoch++;  // the call binds the pod
-    const uint32_t seq = h->serve_seq = serve_next_seq(h->serve_seq);
-    const uint32_t* w = reinterpret_cast<const uint32_t*>(&b);
-    for (int i = 0; i < SERVE_BODY_USED; i++) rq[(i / 15) * 16 + i % 15] = w[i];
-    std::atomic_thread_fence(std::memory_order_seq_cst);  // payload before the sequence words
-    for (int c = 0; c < SERVE_CHUNKS; c++) rq[c * 16 + 15] = seq;
-    std::atomic_thread_fence(std::memory_order_seq_cst);
+    rc = serve_request(h, b);
+    if (rc) return rc;
     volatile int32_t* out = h->h_serve_out;
-    int restarts = 0;
-    for (uint64_t spins = 1; (uint32_t)out[0] != seq; spins++) {
-#if defined(__x86_64__) || defined(__i386__)
-        __builtin_ia32_pause();
-#endif
-        if ((spins & 0x3FFu) == 0) {
-            if (rq[SERVE_REQ_WORDS] == h->serve_launch && (uint32_t)out[0] != seq) {
-                // the kernel left (idle) just before the request arrived: start it again, the request is still in the block
-                h->serve_running = false;
-                CU(h, cudaStreamSynchronize(h->stream));
-                if (++restarts > 3) return fail(h, NGS_ERR_TIMEOUT, "the resident kernel keeps leaving before it answers");
-                rc = serve_start(h, seq == 1 ? SERVE_QUIT - 1 : seq - 1);
-                if (rc) return rc;
-            } else if ((spins & 0xFFFFFu) == 0) {
-                const cudaError_t q = cudaStreamQuery(h->stream);
-                if (q != cudaErrorNotReady && (uint32_t)out[0] != seq && rq[SERVE_REQ_WORDS] != h->serve_launch) {
-                    h->serve_running = false;
-                    return fail(h, NGS_ERR_CUDA, "the resident kernel ended without an answer: %s", cudaGetErrorString(q));
-                }
-                if (spins > (1ull << 33)) return fail(h, NGS_ERR_TIMEOUT, "the resident kernel did not answer");
-            }
-        }
-    }
-    std::atomic_thread_fence(std::memory_order_acquire);
     rc = out[1];
     *node_out = out[8];
     *score_out = out[9];
@@ -1390,7 +1464,15 @@ int ngs_serve_pod(ngs_dealer* h, const int32_t* percent, int n_containers, int m
 
 int ngs_serve_stop(ngs_dealer* h) {
     if (!h) return NGS_ERR_INVALID;
+    h->serve_verbs = false;
     return serve_stop(h);
+}
+
+int ngs_serve_verbs(ngs_dealer* h, int on) {
+    if (!h) return NGS_ERR_INVALID;
+    if (on && h->world > 1) return fail(h, NGS_ERR_UNSUPPORTED, "the resident kernel serves unsharded handles");
+    h->serve_verbs = on != 0;
+    return on ? NGS_OK : serve_stop(h);
 }
 
 int ngs_serve_idle_ms(ngs_dealer* h, double ms) {

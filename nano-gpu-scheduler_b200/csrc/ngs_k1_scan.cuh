@@ -54,25 +54,15 @@ __device__ __forceinline__ void store_codes_cta(int8_t* __restrict__ out, uint32
 #ifndef NGS_K1_BLOCKS
 #define NGS_K1_BLOCKS 4  // resident 256-thread blocks per SM for the feasibility/score scan
 #endif
-// WIDE: the snapshot holds nodes of 9..12 GPUs (ngs_wide.cuh); the host launches those instantiations only then.
-using AssumePad = LaunchPad<56>;
-static_assert(param_block_bytes<Tables, const uint32_t*, uint32_t, PodDemand, LoadParams, int, uint32_t, uint8_t*, int8_t*, int32_t*, int32_t*, int32_t*,
-                                VerbDone, AssumePad>() % 64 == 32, "see LaunchPad");
+// The candidates of one call, 256 per CTA round (every thread of a 256-thread CTA must call; the status bytes are stored
+// by the CTA as a whole).  `dem`, `s_pair` (load-aware calls), `wcx` (WIDE) and `s_code` live in the caller's shared memory.
 template <bool PLAN, bool WIDE>
-__global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables T, const uint32_t* __restrict__ idx, uint32_t n, PodDemand pd, LoadParams lp,
-                                                int mode, uint32_t gen, uint8_t* __restrict__ feasible,
-                                                int8_t* __restrict__ reason, int32_t* __restrict__ score,
-                                                int32_t* __restrict__ plan, int32_t* __restrict__ n_emitted, VerbDone vd, AssumePad) {
-    __shared__ SortedDemand dem;
-    __shared__ double s_pair[121];
-    __shared__ WideCtx s_wcx;
-    __shared__ __align__(16) uint8_t s_code[256];
-    if (threadIdx.x == 0) sort_demand(pd.percent, pd.n, pd.policy, &dem);
-    if (WIDE) wide_ctx_fill(&s_wcx, T, lp, threadIdx.x == 32);
-    if (lp.enabled) fill_usage_pair_table(s_pair, threadIdx.x, blockDim.x);
-    __syncthreads();
-    const int C = pd.n;
-    // (CTA-uniform trip count: the status bytes below are stored by the CTA as a whole)
+__device__ __forceinline__ void assume_rows(const Tables& T, const uint32_t* __restrict__ idx, uint32_t n, const SortedDemand* dem,
+                                            const LoadParams& lp, int mode, uint32_t gen, uint8_t* __restrict__ feasible,
+                                            int8_t* __restrict__ reason, int32_t* __restrict__ score, int32_t* __restrict__ plan,
+                                            int32_t* __restrict__ n_emitted, const double* s_pair, const WideCtx* wcx, uint8_t* s_code) {
+    const int C = dem->C;
+    // (CTA-uniform trip count)
     for (uint32_t k0 = blockIdx.x * blockDim.x; k0 < n; k0 += gridDim.x * blockDim.x) {
         const uint32_t k = k0 + threadIdx.x;
         const bool in = k < n;
@@ -92,7 +82,7 @@ __global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables
                     ev.known = ev.feasible = cached = true;
                     ev.score = T.cscore[row];
                 } else {
-                    ev = eval_row_global<PLAN, WIDE>(T, row, &dem, lp, true, &s_wcx, s_pair);
+                    ev = eval_row_global<PLAN, WIDE>(T, row, dem, lp, true, wcx, s_pair);
                 }
             }
         }
@@ -114,12 +104,32 @@ __global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables
         if (PLAN && in) {
             if (plan) {
                 int32_t* out = plan + (size_t)k * C;
-                if (ev.known) write_plan(out, &dem, dem.policy != NGS_POLICY_RANDOM, ok, ev.emit, ev.n_emit);
+                if (ev.known) write_plan(out, dem, dem->policy != NGS_POLICY_RANDOM, ok, ev.emit, ev.n_emit);
                 else for (int j = 0; j < C; j++) out[j] = INT32_MIN;
             }
             if (n_emitted) n_emitted[k] = ev.known ? ev.n_emit : 0;
         }
     }
+}
+
+// WIDE: the snapshot holds nodes of 9..12 GPUs (ngs_wide.cuh); the host launches those instantiations only then.
+using AssumePad = LaunchPad<56>;
+static_assert(param_block_bytes<Tables, const uint32_t*, uint32_t, PodDemand, LoadParams, int, uint32_t, uint8_t*, int8_t*, int32_t*, int32_t*, int32_t*,
+                                VerbDone, AssumePad>() % 64 == 32, "see LaunchPad");
+template <bool PLAN, bool WIDE>
+__global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables T, const uint32_t* __restrict__ idx, uint32_t n, PodDemand pd, LoadParams lp,
+                                                int mode, uint32_t gen, uint8_t* __restrict__ feasible,
+                                                int8_t* __restrict__ reason, int32_t* __restrict__ score,
+                                                int32_t* __restrict__ plan, int32_t* __restrict__ n_emitted, VerbDone vd, AssumePad) {
+    __shared__ SortedDemand dem;
+    __shared__ double s_pair[121];
+    __shared__ WideCtx s_wcx;
+    __shared__ __align__(16) uint8_t s_code[256];
+    if (threadIdx.x == 0) sort_demand(pd.percent, pd.n, pd.policy, &dem);
+    if (WIDE) wide_ctx_fill(&s_wcx, T, lp, threadIdx.x == 32);
+    if (lp.enabled) fill_usage_pair_table(s_pair, threadIdx.x, blockDim.x);
+    __syncthreads();
+    assume_rows<PLAN, WIDE>(T, idx, n, &dem, lp, mode, gen, feasible, reason, score, plan, n_emitted, s_pair, &s_wcx, s_code);
     verb_done(vd);
 }
 

@@ -8,8 +8,36 @@ struct BindResult {
     int32_t gpu_idx[NGS_MAX_CONTAINERS];
 };
 
-// K3.  NodeInfo.Bind (node.go:70-84) for one row: cached or fresh plan, GPUs.Allocate, cleanPlan.
-// res may be mapped host memory: the status word is written last, behind a system-wide fence, and the host polls it
+// K3.  NodeInfo.Bind (node.go:70-84) for one row, by one thread: cached or fresh plan, GPUs.Allocate, cleanPlan.
+// Fills *res (status included) in memory the caller owns.
+template <bool WIDE>
+__device__ __forceinline__ void bind_row(const Tables& T, uint32_t gidx, int n_containers, const int32_t* percent, const SortedDemand* dem,
+                                         const LoadParams& lp, uint32_t gen, const WideCtx* wcx, BindResult* res) {
+    const uint32_t row = gidx - T.first;
+    for (int j = 0; j < NGS_MAX_CONTAINERS; j++) res->gpu_idx[j] = INT32_MIN;
+    res->score = NGS_SCORE_MIN;
+    if (gidx < T.first || row >= T.n || T.gcount[row] == 0) {
+        res->status = NGS_ERR_UNKNOWN_NODE;
+        return;
+    }
+    const bool hit = T.tag[row] == gen;
+    RowEval ev = eval_row_global<true, WIDE>(T, row, dem, lp, !hit, wcx);
+    if (!ev.feasible) {  // node.go:74-76
+        res->status = NGS_ERR_INFEASIBLE;
+        return;
+    }
+    int32_t planv[NGS_MAX_CONTAINERS];
+    write_plan(planv, dem, dem->policy != NGS_POLICY_RANDOM, true, ev.emit, ev.n_emit);
+    for (int k = 0; k < n_containers; k++) {  // GPUs.Allocate (allocate.go:102-118); the plan fits by construction
+        res->gpu_idx[k] = planv[k];
+        if (planv[k] >= 0) *(WIDE ? wide_free_cell(T, row, planv[k]) : T.free + (size_t)row * 8 + planv[k]) -= percent[k];
+    }
+    res->score = hit ? T.cscore[row] : ev.score;
+    T.tag[row] = 0;  // node.go:82
+    res->status = NGS_OK;
+}
+
+// res_out may be mapped host memory: the status word is written last, behind a system-wide fence, and the host polls it
 static_assert(param_block_bytes<Tables, uint32_t, PodDemand, LoadParams, uint32_t, BindResult*>() % 64 >= 20 &&
                   param_block_bytes<Tables, uint32_t, PodDemand, LoadParams, uint32_t, BindResult*>() % 64 <= 44, "see LaunchPad");
 template <bool WIDE>
@@ -19,40 +47,12 @@ __global__ void k_bind(Tables T, uint32_t gidx, PodDemand pd, LoadParams lp, uin
     __shared__ WideCtx s_wcx;
     if (threadIdx.x != 0) return;
     if (WIDE) wide_ctx_fill(&s_wcx, T, lp, true);
-    BindResult* res = &s_res;
-    struct Publish {  // whatever way the body returns: copy the result out, status last
-        BindResult* from;
-        BindResult* to;
-        __device__ ~Publish() {
-            for (int j = 0; j < NGS_MAX_CONTAINERS; j++) to->gpu_idx[j] = from->gpu_idx[j];
-            to->score = from->score;
-            __threadfence_system();
-            *reinterpret_cast<volatile int32_t*>(&to->status) = from->status;
-        }
-    } publish{res, res_out};
     sort_demand(pd.percent, pd.n, pd.policy, &dem);
-    const uint32_t row = gidx - T.first;
-    for (int j = 0; j < NGS_MAX_CONTAINERS; j++) res->gpu_idx[j] = INT32_MIN;
-    res->score = NGS_SCORE_MIN;
-    if (gidx < T.first || row >= T.n || T.gcount[row] == 0) {
-        res->status = NGS_ERR_UNKNOWN_NODE;
-        return;
-    }
-    const bool hit = T.tag[row] == gen;
-    RowEval ev = eval_row_global<true, WIDE>(T, row, &dem, lp, !hit, &s_wcx);
-    if (!ev.feasible) {  // node.go:74-76
-        res->status = NGS_ERR_INFEASIBLE;
-        return;
-    }
-    int32_t planv[NGS_MAX_CONTAINERS];
-    write_plan(planv, &dem, dem.policy != NGS_POLICY_RANDOM, true, ev.emit, ev.n_emit);
-    for (int k = 0; k < pd.n; k++) {  // GPUs.Allocate (allocate.go:102-118); the plan fits by construction
-        res->gpu_idx[k] = planv[k];
-        if (planv[k] >= 0) *(WIDE ? wide_free_cell(T, row, planv[k]) : T.free + (size_t)row * 8 + planv[k]) -= pd.percent[k];
-    }
-    res->score = hit ? T.cscore[row] : ev.score;
-    T.tag[row] = 0;  // node.go:82
-    res->status = NGS_OK;
+    bind_row<WIDE>(T, gidx, pd.n, pd.percent, &dem, lp, gen, &s_wcx, &s_res);
+    for (int j = 0; j < NGS_MAX_CONTAINERS; j++) res_out->gpu_idx[j] = s_res.gpu_idx[j];
+    res_out->score = s_res.score;
+    __threadfence_system();
+    *reinterpret_cast<volatile int32_t*>(&res_out->status) = s_res.status;
 }
 
 // K3.  GPUs.Allocate (sign>0, all-or-nothing) / GPUs.Release (sign<0) with a caller-given plan.

@@ -23,13 +23,26 @@ constexpr int SERVE_REQ_WORDS = SERVE_CHUNKS * 16;  // the request block: chunks
 constexpr int SERVE_BODY_WORDS = SERVE_CHUNKS * 15;
 constexpr uint32_t SERVE_QUIT = 0xFFFFFFFFu;
 
+enum { SERVE_OP_POD = 0, SERVE_OP_SCAN = 1, SERVE_OP_BIND = 2 };
 struct ServeBody {
     SortedDemand dem;  // sorted by the host (sort_demand): every CTA would otherwise spend 0.5 us on it per request
     LoadParams lp;
     uint32_t rl_zero;  // Tables::rl_zero for this request
     uint32_t max_c;
     uint32_t quit;
+    uint32_t op;       // SERVE_OP_POD: one pod's whole cycle; _SCAN: ngs_assume / ngs_score; _BIND: ngs_bind
+    // _SCAN (k_assume's arguments; the outputs are the handle's mapped staging arrays)
+    uint32_t mode, gen, n;
+    uint32_t idx_lo, idx_hi;        // device pointer to the candidate list, 0 = rows 0..n-1
+    uint32_t reason_lo, reason_hi;  // status bytes (0 = not wanted)
+    uint32_t score_lo, score_hi;
+    // _BIND
+    uint32_t node;
 };
+template <class P>
+__device__ __forceinline__ P* serve_ptr(uint32_t lo, uint32_t hi) {
+    return reinterpret_cast<P*>(((unsigned long long)hi << 32) | lo);
+}
 static_assert(sizeof(ServeBody) <= SERVE_BODY_WORDS * 4 && sizeof(ServeBody) % 4 == 0, "the request body has to fit the block");
 constexpr int SERVE_BODY_USED = (int)(sizeof(ServeBody) / 4);
 
@@ -40,9 +53,25 @@ struct ServeDev {  // device memory: the request as CTA 0 publishes it to the ot
     uint32_t body[SERVE_BODY_WORDS];
 };
 
-// out (mapped host memory): [0] sequence number of the request answered, [1] status, [8] node, [9] score, [10 ..) gpu indexes
+// The verbs' bodies.  cx: the request's tables and load parameters in shared memory.
 template <bool WIDE>
-__global__ void __launch_bounds__(256, 3) k_serve(Tables T, OneRec* rec, ServeDev* dev, const uint32_t* req, int32_t* out, uint32_t* exited,
+__device__ __forceinline__ void serve_scan(const WideCtx* cx, const ServeBody* body, const double* s_pair, uint8_t* s_code) {
+    assume_rows<false, WIDE>(cx->T, serve_ptr<const uint32_t>(body->idx_lo, body->idx_hi), body->n, &body->dem, cx->lp, (int)body->mode, body->gen, nullptr,
+                             serve_ptr<int8_t>(body->reason_lo, body->reason_hi), serve_ptr<int32_t>(body->score_lo, body->score_hi), nullptr, nullptr,
+                             s_pair, cx, s_code);
+}
+template <bool WIDE>
+__device__ __forceinline__ void serve_bind(const WideCtx* cx, const ServeBody* body, BindResult* res) {
+    bind_row<WIDE>(cx->T, body->node, body->dem.C, body->dem.raw, &body->dem, cx->lp, body->gen, cx, res);
+}
+
+// out (mapped host memory): [0] sequence number of the request answered, [1] status, [8] node, [9] score, [10 ..) gpu indexes
+// (_SCAN answers through the staging arrays and writes [0], [1] only; _BIND: [1] status, [9] score, [10 ..) gpu indexes)
+// VERBS: the instantiation that also serves ngs_assume / ngs_score / ngs_bind requests (ngs_serve_verbs).  Their bodies
+// next to the pod cycle's want more registers than three CTAs per SM leave (500 bytes of spills and 2 us per pod when they
+// were squeezed in), so that instantiation runs two CTAs per SM and the pod-only one stays as lean as it was.
+template <bool WIDE, bool VERBS>
+__global__ void __launch_bounds__(256, VERBS ? 2 : 3) k_serve(Tables T, OneRec* rec, ServeDev* dev, const uint32_t* req, int32_t* out, uint32_t* exited,
                                                  uint32_t last_seq, uint32_t launch_id, long long idle_cycles) {
     __shared__ ServeBody body;
     __shared__ double s_pair[121];
@@ -51,6 +80,8 @@ __global__ void __launch_bounds__(256, 3) k_serve(Tables T, OneRec* rec, ServeDe
     __shared__ int32_t s_plan[NGS_MAX_CONTAINERS];
     __shared__ WideCtx s_wcx;
     __shared__ uint32_t s_seq, s_prev_row;
+    __shared__ __align__(16) uint8_t s_code[256];
+    __shared__ BindResult s_bind;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     fill_usage_pair_table(s_pair, tid, blockDim.x);  // (constant: once per launch)
     uint32_t last = last_seq;
@@ -128,12 +159,50 @@ __global__ void __launch_bounds__(256, 3) k_serve(Tables T, OneRec* rec, ServeDe
         if (tid == 64) s_prev_row = __ldcg(&dev->prev_row);
         __syncthreads();
         if (body.quit) break;
-
-        // ---- K7's body (ngs_k7_one.cuh), one GPU, arg-max policies ----
         Tables Tq = T;
         Tq.rl_zero = body.rl_zero;
         const LoadParams& lp = body.lp;
         const SortedDemand& dem = body.dem;
+        if (VERBS && body.op != SERVE_OP_POD) {
+            // ---- the verbs: k_assume's and k_bind's bodies (ngs_k1_scan.cuh, ngs_k3_rows.cuh) ----
+            if (tid == 64) {
+                s_wcx.T = Tq;
+                s_wcx.lp = lp;
+            }
+            __syncthreads();
+            if (body.op == SERVE_OP_SCAN) {
+                serve_scan<WIDE>(&s_wcx, &body, s_pair, s_code);
+                __syncthreads();
+                if (tid == 0) {
+                    __threadfence_system();  // the CTA's outputs (cumulative over the barrier), before the ticket
+                    if (atomicAdd(&rec->arrived, 1u) == gridDim.x - 1) {
+                        rec->arrived = 0;
+                        out[1] = NGS_OK;
+                        __threadfence_system();
+                        *reinterpret_cast<volatile int32_t*>(out) = (int32_t)cur;
+                    }
+                }
+            } else if (blockIdx.x == 0 && tid == 0) {  // _BIND: one thread
+                serve_bind<WIDE>(&s_wcx, &body, &s_bind);
+                for (int j = 0; j < NGS_MAX_CONTAINERS; j++) out[10 + j] = s_bind.gpu_idx[j];
+                out[9] = s_bind.score;
+                out[1] = s_bind.status;
+                __threadfence_system();
+                *reinterpret_cast<volatile int32_t*>(out) = (int32_t)cur;
+            }
+            pref_mode = -1;  // rows may have changed (bind), and the scan's loads are not the pod cycle's
+            continue;
+        }
+        if (!VERBS && body.op != SERVE_OP_POD) {  // never posted to this instantiation: answer rather than hang the caller
+            if (blockIdx.x == 0 && tid == 0) {
+                out[1] = NGS_ERR_UNSUPPORTED;
+                __threadfence_system();
+                *reinterpret_cast<volatile int32_t*>(out) = (int32_t)cur;
+            }
+            continue;
+        }
+
+        // ---- K7's body (ngs_k7_one.cuh), one GPU, arg-max policies ----
         const bool load_path = lp.enabled != 0;
         uint32_t row = row_first;
         const int mode = (load_path ? 2 : 0) | (int)(Tq.rl_zero & 1u);

@@ -242,6 +242,10 @@ class GpuDealer:
     def serve_stop(self):
         self._check(self._lib.ngs_serve_stop(self._h))
 
+    def serve_verbs(self, on=True):
+        """assume / score / bind through the resident kernel as well"""
+        self._check(self._lib.ngs_serve_verbs(self._h, int(bool(on))))
+
     def serve_idle_ms(self, ms):
         self._check(self._lib.ngs_serve_idle_ms(self._h, float(ms)))
 

@@ -108,3 +108,76 @@ def test_a_pod_that_fits_nowhere_and_bad_arguments(ngs):
             d.serve_pod([-5], 0)
         node, score, gidx = d.serve_pod([100, 100], 1)
         assert node == 0 and sorted(gidx.tolist()) == [0, 1]
+
+
+@pytest.mark.parametrize("policy", [0, 1, 2])
+@pytest.mark.parametrize("load_on", [False, True])
+def test_verbs_through_the_resident_kernel_match_the_oracle(ngs, policy, load_on):
+    """ngs_serve_verbs: Assume -> Score -> Bind per pod as requests to the resident kernel, every answer against the oracle"""
+    n = 20000
+    oc, d, _, _ = make_pair(ngs, n, 0.5, 0xBEE + policy, hetero=True)
+    lg, lo = (None, None)
+    rng = np.random.default_rng(17)
+    with d:
+        if load_on:
+            fill_load_tables(oc, d, n, 0xBEE)
+            lg, lo = load_ctx_pair(ngs)
+        d.serve_verbs(True)
+        launches0 = d.stats()["kernel_launches"]
+        idx = rng.permutation(n)[:5000].astype(np.uint32)
+        for t, dem in enumerate(demands(rng, 120)):
+            use_idx = idx if t % 3 == 2 else None
+            a = d.assume(dem, policy, idx=use_idx, load=lg)
+            b = oc.assume(dem, policy, idx=use_idx, load=lo)
+            for k in ("feasible", "reason", "score"):
+                assert np.array_equal(a[k], b[k]), (t, k, dem)
+            sc = d.score_view(dem, policy, idx=use_idx, load=lg) if t % 2 else d.score(dem, policy, idx=use_idx, load=lg)
+            assert np.array_equal(sc, b["score"])
+            feas = np.flatnonzero(b["feasible"])
+            if len(feas) == 0:
+                continue
+            cand = feas if use_idx is None else use_idx[feas]
+            best = int(cand[np.argmax(b["score"][feas])]) if policy != 2 else int(cand[t % len(cand)])
+            ra = d.bind(best, dem, policy, load=lg)
+            rb = oc.bind(best, dem, policy, load=lo)
+            assert ra[0] == rb[0] == 0 and ra[1].tolist() == rb[1].tolist() and ra[2] == rb[2], (t, dem)
+            if t == 40:  # a bind that cannot succeed and an unknown node: the same errors through the same path, nothing changes
+                assert d.bind(best, [100] * 12, policy, load=lg)[0] == ngs.ERR_INFEASIBLE
+                assert oc.bind(best, [100] * 12, policy, load=lo)[0] != 0
+                assert d.bind(n + 5, dem, policy, load=lg)[0] == ngs.ERR_UNKNOWN_NODE
+            if t == 60:  # a release in between stops the kernel; the next verb starts it again
+                assert d.node_apply(best, ra[1], dem, -1) == oc.node_apply(best, rb[1], dem, -1) == 0
+        assert d.stats()["kernel_launches"] - launches0 < 30  # ~360 verb calls, a handful of launches
+        # a fresh score pass on its own (no filter call before it): also a request
+        dem = np.array([15, 10], dtype=np.int32)
+        assert np.array_equal(d.score(dem, policy, load=lg), oc.assume(dem, policy, load=lo)["score"])
+        # plans are not served by the resident kernel: the call stops it and answers the launched way
+        a = d.assume(dem, policy, load=lg, want_plan=True)
+        b = oc.assume(dem, policy, load=lo, want_plan=True)
+        assert np.array_equal(a["plan"], b["plan"]) and np.array_equal(a["n_emitted"], b["n_emitted"])
+        d.serve_stop()
+        gc, fr, rl = d.snapshot_read()
+        ogc, ofr, orl = oc.snapshot()
+        assert np.array_equal(fr, ofr) and np.array_equal(rl, orl)
+
+
+def test_verbs_through_the_resident_kernel_on_wide_nodes(ngs):
+    n = 2500
+    oc, d, _ = mixed_pair(ngs, n, 777, p_used=0.4, min_g=4)
+    rng = np.random.default_rng(23)
+    with d:
+        d.serve_verbs(True)
+        for t, dem in enumerate(demands(rng, 80)):
+            policy = t % 3
+            a = d.assume(dem, policy)
+            b = oc.assume(dem, policy)
+            assert np.array_equal(a["feasible"], b["feasible"]) and np.array_equal(a["score"], b["score"])
+            feas = np.flatnonzero(b["feasible"])
+            if len(feas) == 0:
+                continue
+            best = int(feas[np.argmax(b["score"][feas])])
+            ra = d.bind(best, dem, policy)
+            rb = oc.bind(best, dem, policy)
+            assert ra[0] == rb[0] == 0 and ra[1].tolist() == rb[1].tolist() and ra[2] == rb[2]
+        d.serve_stop()
+        assert_same_nodes(oc, d, n)
