@@ -451,9 +451,14 @@ def run_verbs(ngs, cfg, gcount, free, tables, load, local_rank, cycles=200):
     lref = None if load is None else C.c_void_p(C.addressof(load))
     pol = C.c_int(cfg["policy"])
     vptr = C.c_void_p(0)
+    plan = np.zeros((n, MAX_C), dtype=np.int32)
+    nem = np.zeros(n, dtype=np.int32)
     for label, idx, view, resident in (("idx_null", None, False, False), ("idx_list", np.arange(n, dtype=np.uint32), False, False),
                                        ("idx_null_score_view", None, True, False), ("idx_null_resident", None, True, True),
-                                       ("idx_list_resident", np.arange(n, dtype=np.uint32), True, True)):
+                                       ("idx_list_resident", np.arange(n, dtype=np.uint32), True, True),
+                                       ("idx_null_with_plans", None, True, False), ("idx_null_with_failed_plans", None, True, False)):
+        want_plans = label.endswith("plans")
+        f_assume = lib.ngs_assume_failed_plans if label.endswith("failed_plans") else lib.ngs_assume
         score = np.zeros(n, dtype=np.int32)
         d = ngs.GpuDealer(n, device=local_rank)
         if resident:  # K8: the three verbs as requests to the resident kernel, no launch per call
@@ -472,7 +477,8 @@ def run_verbs(ngs, cfg, gcount, free, tables, load, local_rank, cycles=200):
             dem = C.c_void_p(pc.ctypes.data + p * MAX_C * 4)
             cn = C.c_int(int(nc[p]))
             t0 = time.perf_counter()
-            rc = lib.ngs_assume(d._h, p_idx, C.c_uint32(n), dem, cn, pol, lref, vp(feas), vp(reason), None, None, None)
+            rc = f_assume(d._h, p_idx, C.c_uint32(n), dem, cn, pol, lref, vp(feas), vp(reason), None,
+                                vp(plan) if want_plans else None, vp(nem) if want_plans else None)
             t1 = time.perf_counter()
             if view:  # the scores read where the kernels left them (what a binding that converts them anyway does)
                 rc |= lib.ngs_score_view(d._h, p_idx, C.c_uint32(n), dem, cn, pol, lref, C.byref(vptr))
@@ -506,7 +512,10 @@ def run_verbs(ngs, cfg, gcount, free, tables, load, local_rank, cycles=200):
     out["what"] = (f"{cycles} pod cycles of ngs_assume (feasible + reason out) + ngs_score + ngs_bind on {n} candidates, host buffers in and out, "
                    "wall clock per C call; idx_null = the candidate list is every row in order, idx_list = an explicit index list, "
                    "idx_null_score_view = ngs_score_view instead of ngs_score (no copy of the scores into a caller's buffer), "
-                   "*_resident = ngs_serve_verbs on (the three verbs served by the resident kernel, scores read in place)")
+                   "*_resident = ngs_serve_verbs on (the three verbs served by the resident kernel, scores read in place), "
+                   "idx_null_with_plans = ngs_assume also returns every node's plan / partial plan and its length (what a binding needs "
+                   "for the FailedNodes texts of infeasible nodes, rater.go:99), idx_null_with_failed_plans = ngs_assume_failed_plans "
+                   "(plans of the infeasible nodes only: what those texts actually need)")
     return out
 
 

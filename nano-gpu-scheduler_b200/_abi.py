@@ -28,7 +28,7 @@ SYMBOLS = [
     "ngs_stats", "ngs_node_upsert", "ngs_snapshot_load", "ngs_snapshot_read", "ngs_node_apply", "ngs_release_batch", "ngs_load_add_node",
     "ngs_load_update", "ngs_load_update_bulk", "ngs_parse_usage", "ngs_parse_update_time", "ngs_assume", "ngs_assume_dev", "ngs_score",
     "ngs_bind", "ngs_schedule_batch", "ngs_schedule_batch_dev", "ngs_xchg_export", "ngs_xchg_attach",
-    "ngs_schedule_batch_noalloc", "ngs_node_set_wide", "ngs_node_get_wide", "ngs_score_view", "ngs_serve_pod", "ngs_serve_stop", "ngs_serve_idle_ms", "ngs_serve_verbs",
+    "ngs_schedule_batch_noalloc", "ngs_node_set_wide", "ngs_node_get_wide", "ngs_score_view", "ngs_serve_pod", "ngs_serve_stop", "ngs_serve_idle_ms", "ngs_serve_verbs", "ngs_assume_failed_plans",
 ]
 NOALLOC_MAX_PODS = 256
 NOALLOC_MAX_CTAS = 160
@@ -106,6 +106,7 @@ def load():
     L.ngs_parse_usage.argtypes = [C.c_char_p, C.POINTER(dbl)]
     L.ngs_parse_update_time.argtypes = [C.c_char_p, C.POINTER(i64)]
     L.ngs_assume.argtypes = [vp, vp, u32, vp, ci, ci, vp, vp, vp, vp, vp, vp]
+    L.ngs_assume_failed_plans.argtypes = [vp, vp, u32, vp, ci, ci, vp, vp, vp, vp, vp, vp]
     L.ngs_assume_dev.argtypes = [vp, u32, vp, ci, ci, vp, vp, vp]
     L.ngs_score.argtypes = [vp, vp, u32, vp, ci, ci, vp, vp]
     L.ngs_score_view.argtypes = [vp, vp, u32, vp, ci, ci, vp, C.POINTER(vp)]

@@ -70,10 +70,12 @@ struct ngs_dealer {
     uint8_t* d_feas = nullptr;
     int8_t* d_reason = nullptr;
     int32_t* d_score = nullptr;
-    int32_t* d_plan = nullptr;
-    int32_t* d_nem = nullptr;
+    int8_t* h_vplan = nullptr;   // mapped pinned: packed plans [cap][NGS_MAX_CONTAINERS] bytes (+ a word of padding), entries per node of a call: its C
+    uint8_t* h_vnem = nullptr;   // mapped pinned: emitted counts
+    int8_t* d_vplan = nullptr;   // device aliases
+    uint8_t* d_vnem = nullptr;
+    size_t vplan_cap = 0;        // candidates the two hold
     size_t verb_cap = 0;   // candidates the verb scratch holds
-    size_t plan_cap = 0;   // int32 entries d_plan holds
     BindResult* d_bind = nullptr;  // device alias of h_bind
     BindResult* h_bind = nullptr;  // mapped pinned: k_bind writes its answer here, the host polls the status word
     // verb staging in mapped pinned memory: the scan kernels write feasible / reason / score straight into host memory
@@ -257,6 +259,40 @@ void expand_feasible(uint8_t* feasible, const int8_t* status, size_t n) {
     for (; i < n; i++) feasible[i] = status[i] == NGS_REASON_OK ? 1 : 0;
 }
 
+// plan entries travel as one byte each (PLAN_NONE = INT32_MIN), emitted counts as one byte: widen into the caller's int32 arrays
+void widen_plan(int32_t* dst, const int8_t* src, size_t n) {
+    size_t i = 0;
+#if defined(__SSE2__)
+    const __m128i zero = _mm_setzero_si128(), none8 = _mm_set1_epi32(PLAN_NONE), none32 = _mm_set1_epi32(INT32_MIN);
+    for (; i + 16 <= n; i += 16) {
+        const __m128i x = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + i));
+        const __m128i lo16 = _mm_unpacklo_epi8(zero, x), hi16 = _mm_unpackhi_epi8(zero, x);  // byte in the high half of each 16-bit lane
+        __m128i q[4] = {_mm_unpacklo_epi16(zero, lo16), _mm_unpackhi_epi16(zero, lo16), _mm_unpacklo_epi16(zero, hi16), _mm_unpackhi_epi16(zero, hi16)};
+        for (int k = 0; k < 4; k++) {
+            const __m128i v = _mm_srai_epi32(q[k], 24);  // sign-extended
+            const __m128i m = _mm_cmpeq_epi32(v, none8);
+            _mm_storeu_si128(reinterpret_cast<__m128i*>(dst + i + 4 * k), _mm_or_si128(_mm_andnot_si128(m, v), _mm_and_si128(m, none32)));
+        }
+    }
+#endif
+    for (; i < n; i++) dst[i] = src[i] == PLAN_NONE ? INT32_MIN : (int32_t)src[i];
+}
+void widen_u8(int32_t* dst, const uint8_t* src, size_t n) {
+    size_t i = 0;
+#if defined(__SSE2__)
+    const __m128i zero = _mm_setzero_si128();
+    for (; i + 16 <= n; i += 16) {
+        const __m128i x = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + i));
+        const __m128i lo16 = _mm_unpacklo_epi8(x, zero), hi16 = _mm_unpackhi_epi8(x, zero);
+        _mm_storeu_si128(reinterpret_cast<__m128i*>(dst + i), _mm_unpacklo_epi16(lo16, zero));
+        _mm_storeu_si128(reinterpret_cast<__m128i*>(dst + i + 4), _mm_unpackhi_epi16(lo16, zero));
+        _mm_storeu_si128(reinterpret_cast<__m128i*>(dst + i + 8), _mm_unpacklo_epi16(hi16, zero));
+        _mm_storeu_si128(reinterpret_cast<__m128i*>(dst + i + 12), _mm_unpackhi_epi16(hi16, zero));
+    }
+#endif
+    for (; i < n; i++) dst[i] = src[i];
+}
+
 // wait for a verb kernel's flag in mapped host memory (no stream synchronisation); keeps an eye on the stream
 int wait_flag(ngs_dealer* h, volatile int32_t* flag, int32_t want, const char* what) {
     for (uint32_t spins = 1; *flag != want; spins++) {
@@ -279,23 +315,26 @@ int wait_flag(ngs_dealer* h, volatile int32_t* flag, int32_t want, const char* w
 int ensure_verb_scratch(ngs_dealer* h, size_t n, size_t plan_entries) {
     if (n > h->verb_cap) {
         size_t cap = n < 1024 ? 1024 : n;
-        cudaFree(h->d_idx); cudaFree(h->d_feas); cudaFree(h->d_reason); cudaFree(h->d_score); cudaFree(h->d_nem);
-        h->d_idx = nullptr; h->d_feas = nullptr; h->d_reason = nullptr; h->d_score = nullptr; h->d_nem = nullptr;
+        cudaFree(h->d_idx); cudaFree(h->d_feas); cudaFree(h->d_reason); cudaFree(h->d_score);
+        h->d_idx = nullptr; h->d_feas = nullptr; h->d_reason = nullptr; h->d_score = nullptr;
         h->verb_cap = 0;
         h->idx_sig = 0;
         CU(h, cudaMalloc(&h->d_idx, cap * 4));
         CU(h, cudaMalloc(&h->d_feas, cap));
         CU(h, cudaMalloc(&h->d_reason, cap));
         CU(h, cudaMalloc(&h->d_score, cap * 4));
-        CU(h, cudaMalloc(&h->d_nem, cap * 4));
         h->verb_cap = cap;
     }
-    if (plan_entries > h->plan_cap) {
-        cudaFree(h->d_plan);
-        h->d_plan = nullptr;
-        h->plan_cap = 0;
-        CU(h, cudaMalloc(&h->d_plan, plan_entries * 4));
-        h->plan_cap = plan_entries;
+    if (plan_entries && n > h->vplan_cap) {  // packed plans and emitted counts, written by the kernel straight into host memory
+        const size_t cap = n < 4096 ? 4096 : n;
+        cudaFreeHost(h->h_vplan); cudaFreeHost(h->h_vnem);
+        h->h_vplan = nullptr; h->h_vnem = nullptr;
+        h->vplan_cap = 0;
+        CU(h, cudaHostAlloc(&h->h_vplan, cap * NGS_MAX_CONTAINERS + 16, cudaHostAllocMapped));
+        CU(h, cudaHostAlloc(&h->h_vnem, cap + 16, cudaHostAllocMapped));
+        CU(h, cudaHostGetDevicePointer(&h->d_vplan, h->h_vplan, 0));
+        CU(h, cudaHostGetDevicePointer(&h->d_vnem, h->h_vnem, 0));
+        h->vplan_cap = cap;
     }
     return NGS_OK;
 }
@@ -730,7 +769,7 @@ int ngs_destroy(ngs_dealer* h) {
     cudaFree(h->T.free); cudaFree(h->T.gcount); cudaFree(h->T.rl); cudaFree(h->T.tenths); cudaFree(h->T.ts);
     cudaFree(h->T.tag); cudaFree(h->T.cscore); cudaFree(const_cast<int16_t*>(h->T.blut));
     cudaFree(h->T.free_hi); cudaFree(h->T.rl_hi); cudaFree(h->T.tenths_hi); cudaFree(h->T.ts_hi);
-    cudaFree(h->d_idx); cudaFree(h->d_feas); cudaFree(h->d_reason); cudaFree(h->d_score); cudaFree(h->d_plan); cudaFree(h->d_nem);
+    cudaFree(h->d_idx); cudaFree(h->d_feas); cudaFree(h->d_reason); cudaFree(h->d_score); cudaFreeHost(h->h_vplan); cudaFreeHost(h->h_vnem);
     cudaFreeHost(h->h_bind); cudaFree(h->d_small); cudaFreeHost(h->h_small);
     cudaFreeHost(h->h_vreason); cudaFreeHost(h->h_vscore); cudaFreeHost(h->h_vflag); cudaFree(h->d_vticket);
     cudaFree(h->d_dem); cudaFree(h->d_keys); cudaFree(h->d_one);
@@ -1067,7 +1106,7 @@ static int launch_scan(ngs_dealer* h, uint32_t n, const PodDemand& pd, const Loa
 
 static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, const int32_t* percent, int n_containers, int policy,
                       const ngs_load_ctx* load, uint8_t* feasible, int8_t* reason, int32_t* score, int32_t* plan, int32_t* n_emitted,
-                      const int32_t** score_view = nullptr) {
+                      const int32_t** score_view = nullptr, bool failed_plans_only = false) {
     if (!h) return NGS_ERR_INVALID;
     // K8: with ngs_serve_verbs on, the scan goes to the resident kernel as a request (no plans there: those calls stop it)
     const bool resident = h->serve_verbs && h->world == 1 && !plan && !n_emitted;
@@ -1142,25 +1181,36 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
         vd.seq = ++h->vseq;
         // one status byte per node travels (NGS_REASON_*); `feasible` is derived from it on the host
         uint8_t* o_feas = nullptr;
-        int8_t* o_reason = (reason || feasible) ? h->d_vreason : nullptr;
+        int8_t* o_reason = (reason || feasible || failed_plans_only) ? h->d_vreason : nullptr;
         int32_t* o_score = h->d_vscore;
         if (!idx && mode == MODE_ASSUME && !want_plan) {
             rc = launch_scan(h, n, pd, lp, gen, o_feas, o_reason, o_score, vd);
             if (rc) return rc;
         } else if (want_plan)
-            (h->n_wide ? k_assume<true, true> : k_assume<true, false>)<<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, o_feas, o_reason, o_score,
-                                                         plan ? h->d_plan : nullptr, n_emitted ? h->d_nem : nullptr, vd, AssumePad{});
+            (h->n_wide ? k_assume<true, true> : k_assume<true, false>)<<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp,
+                                                         mode | (failed_plans_only ? MODE_FAILED_PLANS_ONLY : 0), gen, o_feas, o_reason, o_score,
+                                                         plan ? h->d_vplan : nullptr, n_emitted ? h->d_vnem : nullptr, vd, AssumePad{});
         else
             (h->n_wide ? k_assume<false, true> : k_assume<false, false>)<<<grid, block, 0, h->stream>>>(h->T, idx ? h->d_idx : nullptr, n, pd, lp, mode, gen, o_feas, o_reason, o_score, nullptr,
                                                           nullptr, vd, AssumePad{});
         CU(h, cudaGetLastError());
-        if (want_plan) {  // plans (the FailedNodes texts of the host mirror) still travel by copy commands
-            if (plan && n_containers > 0) CU(h, cudaMemcpyAsync(plan, h->d_plan, (size_t)n * n_containers * 4, cudaMemcpyDeviceToHost, h->stream));
-            if (n_emitted) CU(h, cudaMemcpyAsync(n_emitted, h->d_nem, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
-            CU(h, cudaStreamSynchronize(h->stream));
-        }
         rc = wait_flag(h, h->h_vflag, vd.seq, "scan kernel");
         if (rc) return rc;
+    }
+    if (failed_plans_only) {
+        // only the infeasible candidates' rows are written: filling 4 bytes per entry for all of them is what a call with plans costs
+        const int8_t* st = h->h_vreason;
+        for (uint32_t i = 0; i < n; i++) {
+            if (st[i] != NGS_REASON_INFEASIBLE) continue;
+            n_emitted[i] = h->h_vnem[i];
+            for (int k = 0; k < n_containers; k++) {
+                const int8_t v = h->h_vplan[(size_t)i * n_containers + k];
+                plan[(size_t)i * n_containers + k] = v == PLAN_NONE ? INT32_MIN : (int32_t)v;
+            }
+        }
+    } else {
+        if (plan && n_containers > 0) widen_plan(plan, h->h_vplan, (size_t)n * n_containers);  // one byte per entry in the staging area
+        if (n_emitted) widen_u8(n_emitted, h->h_vnem, n);
     }
     if (feasible) expand_feasible(feasible, h->h_vreason, n);
     if (reason) memcpy(reason, h->h_vreason, n);
@@ -1175,14 +1225,19 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
     }
     if (!resident) h->stats.kernel_launches++;
     h->stats.node_evals += n;
-    h->stats.d2h_bytes += ((feasible || reason) ? n : 0) + (size_t)n * 4 +
-                          (plan ? (size_t)n * n_containers * 4 : 0) + (n_emitted ? (size_t)n * 4 : 0);
+    h->stats.d2h_bytes += ((feasible || reason) ? n : 0) + (size_t)n * 4 + (plan ? (size_t)n * n_containers : 0) + (n_emitted ? n : 0);
     return NGS_OK;
 }
 
 int ngs_assume(ngs_dealer* h, const uint32_t* idx, uint32_t n, const int32_t* percent, int n_containers, int policy,
                const ngs_load_ctx* load, uint8_t* feasible, int8_t* reason, int32_t* score, int32_t* plan, int32_t* n_emitted) {
     return run_assume(h, MODE_ASSUME, idx, n, percent, n_containers, policy, load, feasible, reason, score, plan, n_emitted);
+}
+
+int ngs_assume_failed_plans(ngs_dealer* h, const uint32_t* idx, uint32_t n, const int32_t* percent, int n_containers, int policy,
+                            const ngs_load_ctx* load, uint8_t* feasible, int8_t* reason, int32_t* score, int32_t* plan, int32_t* n_emitted) {
+    if (!plan || !n_emitted) return NGS_ERR_INVALID;
+    return run_assume(h, MODE_ASSUME, idx, n, percent, n_containers, policy, load, feasible, reason, score, plan, n_emitted, nullptr, true);
 }
 
 // DealerImpl.Assume + Score over rows [0, n) with the per-node outputs left in device memory

@@ -4,6 +4,9 @@
 #pragma once
 
 enum { MODE_ASSUME = 0, MODE_SCORE = 1 };
+// or-ed into the mode of a PLAN call: only candidates that turn out infeasible get their (partial) plan worked out - what the
+// FailedNodes texts need (rater.go:99,152); everyone else costs what a call without plans costs
+constexpr int MODE_FAILED_PLANS_ONLY = 4;
 
 // How a verb kernel tells the host that its outputs are complete when they go straight into mapped host memory (no copy
 // command, no stream synchronisation): after the CTA's barrier one thread makes the CTA's stores visible system-wide (a
@@ -55,12 +58,18 @@ __device__ __forceinline__ void store_codes_cta(int8_t* __restrict__ out, uint32
 #define NGS_K1_BLOCKS 4  // resident 256-thread blocks per SM for the feasibility/score scan
 #endif
 // The candidates of one call, 256 per CTA round (every thread of a 256-thread CTA must call; the status bytes are stored
-// by the CTA as a whole).  `dem`, `s_pair` (load-aware calls), `wcx` (WIDE) and `s_code` live in the caller's shared memory.
+// by the CTA as a whole).  `dem`, `s_pair` (load-aware calls), `wcx` (WIDE), `s_code` and `s_plan8` (PLAN: 256 x 12 bytes) live
+// in the caller's shared memory.  PLAN outputs travel packed, one byte per entry (PLAN_NONE = the INT32_MIN of the C ABI): they
+// go into mapped host memory, where bytes over PCIe are what the call costs; the host widens them.
+constexpr int PLAN_NONE = -128;
 template <bool PLAN, bool WIDE>
 __device__ __forceinline__ void assume_rows(const Tables& T, const uint32_t* __restrict__ idx, uint32_t n, const SortedDemand* dem,
                                             const LoadParams& lp, int mode, uint32_t gen, uint8_t* __restrict__ feasible,
-                                            int8_t* __restrict__ reason, int32_t* __restrict__ score, int32_t* __restrict__ plan,
-                                            int32_t* __restrict__ n_emitted, const double* s_pair, const WideCtx* wcx, uint8_t* s_code) {
+                                            int8_t* __restrict__ reason, int32_t* __restrict__ score, int8_t* __restrict__ plan,
+                                            uint8_t* __restrict__ n_emitted, const double* s_pair, const WideCtx* wcx, uint8_t* s_code,
+                                            int8_t* s_plan8 = nullptr) {
+    const bool failed_only = PLAN && (mode & MODE_FAILED_PLANS_ONLY) != 0;
+    mode &= 3;
     const int C = dem->C;
     // (CTA-uniform trip count)
     for (uint32_t k0 = blockIdx.x * blockDim.x; k0 < n; k0 += gridDim.x * blockDim.x) {
@@ -81,6 +90,9 @@ __device__ __forceinline__ void assume_rows(const Tables& T, const uint32_t* __r
                 if (mode == MODE_SCORE && T.tag[row] == gen && T.gcount[row] != 0) {
                     ev.known = ev.feasible = cached = true;
                     ev.score = T.cscore[row];
+                } else if (failed_only) {
+                    ev = eval_row_global<false, WIDE>(T, row, dem, lp, true, wcx, s_pair);
+                    if (ev.known && !ev.feasible) ev = eval_row_global<PLAN, WIDE>(T, row, dem, lp, true, wcx, s_pair);  // (same verdict, plus the partial plan)
                 } else {
                     ev = eval_row_global<PLAN, WIDE>(T, row, dem, lp, true, wcx, s_pair);
                 }
@@ -101,35 +113,45 @@ __device__ __forceinline__ void assume_rows(const Tables& T, const uint32_t* __r
         if (feasible && in) feasible[k] = ok ? 1 : 0;
         if (reason) store_codes_cta(reason, k0, n, in, !ev.known ? NGS_REASON_UNKNOWN_NODE : (ok ? NGS_REASON_OK : NGS_REASON_INFEASIBLE), s_code);
         if (score && in) score[k] = ok ? ev.score : NGS_SCORE_MIN;
-        if (PLAN && in) {
-            if (plan) {
-                int32_t* out = plan + (size_t)k * C;
-                if (ev.known) write_plan(out, dem, dem->policy != NGS_POLICY_RANDOM, ok, ev.emit, ev.n_emit);
-                else for (int j = 0; j < C; j++) out[j] = INT32_MIN;
+        if (PLAN) {
+            if (plan && C > 0) {
+                // C bytes per row: the CTA's 256 rows are one contiguous range of the output, stored as 32-bit words
+                int8_t* sp = s_plan8 + threadIdx.x * C;
+                int32_t tmp[NGS_MAX_CONTAINERS];
+                const bool have = in && ev.known && !(failed_only && ok);
+                if (have) write_plan(tmp, dem, dem->policy != NGS_POLICY_RANDOM, ok, ev.emit, ev.n_emit);
+                for (int j = 0; j < C; j++) sp[j] = (have && tmp[j] != INT32_MIN) ? (int8_t)tmp[j] : (int8_t)PLAN_NONE;
+                __syncthreads();
+                const size_t first = (size_t)k0 * C, end = ((size_t)n * C + 3) & ~(size_t)3;  // (the staging array is padded to whole words)
+                for (uint32_t w = threadIdx.x; w < 64u * (uint32_t)C; w += blockDim.x)
+                    if (first + 4 * (size_t)w < end)
+                        *reinterpret_cast<uint32_t*>(plan + first + 4 * (size_t)w) = *reinterpret_cast<const uint32_t*>(s_plan8 + 4 * w);
+                __syncthreads();
             }
-            if (n_emitted) n_emitted[k] = ev.known ? ev.n_emit : 0;
+            if (n_emitted) store_codes_cta(reinterpret_cast<int8_t*>(n_emitted), k0, n, in, (in && ev.known && !(failed_only && ok)) ? ev.n_emit : 0, s_code);
         }
     }
 }
 
 // WIDE: the snapshot holds nodes of 9..12 GPUs (ngs_wide.cuh); the host launches those instantiations only then.
 using AssumePad = LaunchPad<56>;
-static_assert(param_block_bytes<Tables, const uint32_t*, uint32_t, PodDemand, LoadParams, int, uint32_t, uint8_t*, int8_t*, int32_t*, int32_t*, int32_t*,
+static_assert(param_block_bytes<Tables, const uint32_t*, uint32_t, PodDemand, LoadParams, int, uint32_t, uint8_t*, int8_t*, int32_t*, int8_t*, uint8_t*,
                                 VerbDone, AssumePad>() % 64 == 32, "see LaunchPad");
 template <bool PLAN, bool WIDE>
 __global__ void __launch_bounds__(256, PLAN ? 2 : NGS_K1_BLOCKS) k_assume(Tables T, const uint32_t* __restrict__ idx, uint32_t n, PodDemand pd, LoadParams lp,
                                                 int mode, uint32_t gen, uint8_t* __restrict__ feasible,
                                                 int8_t* __restrict__ reason, int32_t* __restrict__ score,
-                                                int32_t* __restrict__ plan, int32_t* __restrict__ n_emitted, VerbDone vd, AssumePad) {
+                                                int8_t* __restrict__ plan, uint8_t* __restrict__ n_emitted, VerbDone vd, AssumePad) {
     __shared__ SortedDemand dem;
     __shared__ double s_pair[121];
     __shared__ WideCtx s_wcx;
     __shared__ __align__(16) uint8_t s_code[256];
+    __shared__ __align__(16) int8_t s_plan8[PLAN ? 256 * NGS_MAX_CONTAINERS : 16];
     if (threadIdx.x == 0) sort_demand(pd.percent, pd.n, pd.policy, &dem);
     if (WIDE) wide_ctx_fill(&s_wcx, T, lp, threadIdx.x == 32);
     if (lp.enabled) fill_usage_pair_table(s_pair, threadIdx.x, blockDim.x);
     __syncthreads();
-    assume_rows<PLAN, WIDE>(T, idx, n, &dem, lp, mode, gen, feasible, reason, score, plan, n_emitted, s_pair, &s_wcx, s_code);
+    assume_rows<PLAN, WIDE>(T, idx, n, &dem, lp, mode, gen, feasible, reason, score, plan, n_emitted, s_pair, &s_wcx, s_code, s_plan8);
     verb_done(vd);
 }
 

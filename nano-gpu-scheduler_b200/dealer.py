@@ -156,7 +156,8 @@ class GpuDealer:
         self._check(self._lib.ngs_load_update_bulk(self._h, metric, first, v.shape[0], _p(v), _p(vo), _p(t), _p(to)))
 
     # -- verbs ------------------------------------------------------------------------------
-    def assume(self, percent, policy, idx=None, load=None, want_plan=False, n=None):
+    def assume(self, percent, policy, idx=None, load=None, want_plan=False, n=None, failed_plans_only=False):
+        """failed_plans_only (with want_plan): plans / emitted counts of the infeasible candidates only (ngs_assume_failed_plans)"""
         d = np.ascontiguousarray(percent, dtype=np.int32)
         c = len(d)
         if idx is None:
@@ -169,8 +170,8 @@ class GpuDealer:
         score = np.zeros(max(n, 1), dtype=np.int32)
         plan = np.full((max(n, 1), max(c, 1)), INT32_MIN, dtype=np.int32) if want_plan else None
         nem = np.zeros(max(n, 1), dtype=np.int32) if want_plan else None
-        self._check(self._lib.ngs_assume(self._h, _p(ia), n, _p(d), c, policy, _ref(load), _p(feas), _p(reason),
-                                         _p(score), _p(plan), _p(nem)))
+        fn = self._lib.ngs_assume_failed_plans if (want_plan and failed_plans_only) else self._lib.ngs_assume
+        self._check(fn(self._h, _p(ia), n, _p(d), c, policy, _ref(load), _p(feas), _p(reason), _p(score), _p(plan), _p(nem)))
         res = dict(feasible=feas[:n], reason=reason[:n], score=score[:n])
         if want_plan:
             res["plan"] = plan[:n, :c]

@@ -609,8 +609,9 @@ AssumeResult Dealer::AssumeSet(const CandidateSet& cs, const Pod& pod, const Pol
     const int C = (int)r.demand.size();
     r.plan.resize(n * (size_t)(C > 0 ? C : 1));
     r.n_emitted.resize(n);
-    const int rc = ngs_assume(h_, cs.all_rows ? nullptr : cs.rows.data(), (uint32_t)n, r.demand.data(), C, policy(), has_load ? &L : nullptr,
-                              r.ok.data(), r.reason.data(), nullptr, r.plan.data(), r.n_emitted.data());
+    // (plans only where a FailedNodes text will quote them: the infeasible candidates' partial `indexes`)
+    const int rc = ngs_assume_failed_plans(h_, cs.all_rows ? nullptr : cs.rows.data(), (uint32_t)n, r.demand.data(), C, policy(), has_load ? &L : nullptr,
+                                           r.ok.data(), r.reason.data(), nullptr, r.plan.data(), r.n_emitted.data());
     if (rc != NGS_OK) {
         r.call_err = ngs_last_error(h_);
         std::fill(r.ok.begin(), r.ok.end(), 0);

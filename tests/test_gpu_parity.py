@@ -979,3 +979,28 @@ def test_score_view_is_score_without_the_copy(ngs):
                 idx = rng.permutation(n)[:777].astype(np.uint32)
                 assert np.array_equal(d.score_view(dem, policy, idx=idx), want[idx])
                 assert np.array_equal(d.score(dem, policy), want)
+
+
+@pytest.mark.parametrize("policy", [0, 1, 2])
+def test_assume_with_plans_for_the_infeasible_only(ngs, policy):
+    """ngs_assume_failed_plans: verdicts and scores as ngs_assume; plans / emitted counts for the infeasible candidates
+    (the oracle's partial `indexes`), the rows of everyone else untouched"""
+    n = 6000
+    oc, d, _, _ = make_pair(ngs, n, 0.8, 0xFA11 + policy, hetero=True)
+    rng = np.random.default_rng(4)
+    with d:
+        fill_load_tables(oc, d, n, 0xFA11)
+        lg, lo = load_ctx_pair(ngs)
+        for trial in range(12):
+            dem = (rng.integers(2, 17, int(rng.integers(1, 6))) * 5).astype(np.int32)
+            load_g, load_o = (lg, lo) if trial % 2 else (None, None)
+            idx = rng.permutation(n)[:1500].astype(np.uint32) if trial % 3 == 0 else None
+            a = d.assume(dem, policy, idx=idx, load=load_g, want_plan=True, failed_plans_only=True)
+            b = oc.assume(dem, policy, idx=idx, load=load_o, want_plan=True)
+            for k in ("feasible", "reason", "score"):
+                assert np.array_equal(a[k], b[k]), (trial, k)
+            bad = b["reason"] == ngs.REASON_INFEASIBLE
+            assert bad.any() and (~bad).any()
+            assert np.array_equal(a["n_emitted"][bad], b["n_emitted"][bad])
+            assert np.array_equal(a["plan"][bad], b["plan"][bad])
+            assert (a["n_emitted"][~bad] == 0).all() and (a["plan"][~bad] == -(2**31)).all()  # (as the wrapper initialised them)
