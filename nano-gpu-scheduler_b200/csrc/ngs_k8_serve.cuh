@@ -4,7 +4,7 @@
 // A launch whose completion the host can see costs 8-9 us on this box even for an empty kernel
 // (profiles/r02/param_size_bench.txt); K7's own work is about 7 us (profiles/r02/k7_phases.txt).  K8 is launched once
 // (cooperatively: every CTA must be resident, they wait for each other's requests) and then serves requests the host
-// drops into a 256-byte block of mapped pinned memory:
+// drops into a 512-byte block of mapped pinned memory:
 //   host   : payload words (the demand already sorted), store fence, then the request's sequence number into the last
 //            word of each 64-byte chunk
 //   CTA 0  : warp 0 polls the block with one coalesced 512-byte read; a request is complete when the eight sequence words
@@ -15,7 +15,9 @@
 //            (node, score, plan) and then the sequence number into mapped host memory, where the host polls it
 // The kernel leaves when asked to (a request with quit set) or when no request arrived for idle_cycles; the host restarts
 // it on the next request.  Every wait is bounded.  Arg-max policies on unsharded handles; everything else goes through K7.
-// Same results as K7 and K6 (tests/test_gpu_serve.py).  Included by ngs_dealer.cu after ngs_k7_one.cuh.
+// The VERBS instantiation also takes ngs_assume / ngs_score (SERVE_OP_SCAN: k_assume's body, every CTA, ticket at the end)
+// and ngs_bind (SERVE_OP_BIND: k_bind's body, one thread of CTA 0) as requests.
+// Same results as the launched kernels and the oracle (tests/test_gpu_serve.py).  Included by ngs_dealer.cu after ngs_k7_one.cuh.
 #pragma once
 
 constexpr int SERVE_CHUNKS = 8;
