@@ -26,6 +26,7 @@
 #include <emmintrin.h>
 #endif
 
+#include <chrono>
 #include <cmath>
 #include <atomic>
 #include <cstdarg>
@@ -597,6 +598,7 @@ int serve_request(ngs_dealer* h, ServeBody& b) {
     std::atomic_thread_fence(std::memory_order_seq_cst);
     volatile int32_t* out = h->h_serve_out;
     int restarts = 0;
+    const auto t_start = std::chrono::steady_clock::now();
     for (uint64_t spins = 1; (uint32_t)out[0] != seq; spins++) {
 #if defined(__x86_64__) || defined(__i386__)
         __builtin_ia32_pause();
@@ -615,7 +617,10 @@ int serve_request(ngs_dealer* h, ServeBody& b) {
                     h->serve_running = false;
                     return fail(h, NGS_ERR_CUDA, "the resident kernel ended without an answer: %s", cudaGetErrorString(q));
                 }
-                if (spins > (1ull << 33)) return fail(h, NGS_ERR_TIMEOUT, "the resident kernel did not answer");
+                if (std::chrono::steady_clock::now() - t_start > std::chrono::seconds(10)) {
+                    h->serve_running = false;  // (whatever is on the stream is left to ngs_destroy / the next synchronising call)
+                    return fail(h, NGS_ERR_TIMEOUT, "the resident kernel did not answer within 10 s");
+                }
             }
         }
     }
