@@ -456,9 +456,11 @@ def run_verbs(ngs, cfg, gcount, free, tables, load, local_rank, cycles=200):
     for label, idx, view, resident in (("idx_null", None, False, False), ("idx_list", np.arange(n, dtype=np.uint32), False, False),
                                        ("idx_null_score_view", None, True, False), ("idx_null_resident", None, True, True),
                                        ("idx_list_resident", np.arange(n, dtype=np.uint32), True, True),
-                                       ("idx_null_with_plans", None, True, False), ("idx_null_with_failed_plans", None, True, False)):
+                                       ("idx_null_with_plans", None, True, False), ("idx_null_with_failed_plans", None, True, False),
+                                       ("idx_null_with_failed_plans_resident", None, True, True)):
         want_plans = label.endswith("plans")
-        f_assume = lib.ngs_assume_failed_plans if label.endswith("failed_plans") else lib.ngs_assume
+        f_assume = lib.ngs_assume_failed_plans if "failed_plans" in label else lib.ngs_assume
+        want_plans = "plans" in label
         score = np.zeros(n, dtype=np.int32)
         d = ngs.GpuDealer(n, device=local_rank)
         if resident:  # K8: the three verbs as requests to the resident kernel, no launch per call

@@ -1114,8 +1114,8 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
                       const int32_t** score_view = nullptr, bool failed_plans_only = false) {
     if (!h) return NGS_ERR_INVALID;
     // K8: with ngs_serve_verbs on, the scan goes to the resident kernel as a request (no plans there: those calls stop it)
-    const bool resident = h->serve_verbs && h->world == 1 && !plan && !n_emitted;
-    if (!resident || n > h->verb_cap || n > h->vstage_cap) SERVE_OFF(h);  // (growing the scratch frees device memory: not under a running kernel)
+    const bool resident = h->serve_verbs && h->world == 1 && (plan != nullptr) == (n_emitted != nullptr);
+    if (!resident || n > h->verb_cap || n > h->vstage_cap || (plan && n > h->vplan_cap)) SERVE_OFF(h);  // (growing the scratch frees memory: not under a running kernel)
     if (score_view) *score_view = nullptr;
     PodDemand pd;
     LoadParams lp;
@@ -1166,11 +1166,18 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
         b.mode = (uint32_t)mode;
         b.gen = gen;
         b.n = n;
-        const unsigned long long p_idx = (unsigned long long)(idx ? h->d_idx : nullptr), p_reason = (unsigned long long)((reason || feasible) ? h->d_vreason : nullptr),
+        const unsigned long long p_idx = (unsigned long long)(idx ? h->d_idx : nullptr),
+                                 p_reason = (unsigned long long)((reason || feasible || failed_plans_only) ? h->d_vreason : nullptr),
                                  p_score = (unsigned long long)h->d_vscore;
         b.idx_lo = (uint32_t)p_idx; b.idx_hi = (uint32_t)(p_idx >> 32);
         b.reason_lo = (uint32_t)p_reason; b.reason_hi = (uint32_t)(p_reason >> 32);
         b.score_lo = (uint32_t)p_score; b.score_hi = (uint32_t)(p_score >> 32);
+        if (want_plan) {
+            const unsigned long long p_plan = (unsigned long long)h->d_vplan, p_nem = (unsigned long long)h->d_vnem;
+            b.plan_lo = (uint32_t)p_plan; b.plan_hi = (uint32_t)(p_plan >> 32);
+            b.nem_lo = (uint32_t)p_nem; b.nem_hi = (uint32_t)(p_nem >> 32);
+            if (failed_plans_only) b.mode |= MODE_FAILED_PLANS_ONLY;
+        }
         rc = serve_request(h, b);
         if (rc) return rc;
         if (h->h_serve_out[1] != NGS_OK) return fail(h, h->h_serve_out[1], "resident scan: %s", ngs_strerror(h->h_serve_out[1]));

@@ -38,6 +38,8 @@ struct ServeBody {
     uint32_t idx_lo, idx_hi;        // device pointer to the candidate list, 0 = rows 0..n-1
     uint32_t reason_lo, reason_hi;  // status bytes (0 = not wanted)
     uint32_t score_lo, score_hi;
+    uint32_t plan_lo, plan_hi;      // packed plans / emitted counts (0 = no plans: the cheaper instantiation of the scan)
+    uint32_t nem_lo, nem_hi;
     // _BIND
     uint32_t node;
 };
@@ -56,11 +58,22 @@ struct ServeDev {  // device memory: the request as CTA 0 publishes it to the ot
 };
 
 // The verbs' bodies.  cx: the request's tables and load parameters in shared memory.
+// (the scan with plans is the rarer request and the hungrier code: out of line, so that it does not set the register
+// allocation of everything else in the kernel)
 template <bool WIDE>
-__device__ __forceinline__ void serve_scan(const WideCtx* cx, const ServeBody* body, const double* s_pair, uint8_t* s_code) {
-    assume_rows<false, WIDE>(cx->T, serve_ptr<const uint32_t>(body->idx_lo, body->idx_hi), body->n, &body->dem, cx->lp, (int)body->mode, body->gen, nullptr,
-                             serve_ptr<int8_t>(body->reason_lo, body->reason_hi), serve_ptr<int32_t>(body->score_lo, body->score_hi), nullptr, nullptr,
-                             s_pair, cx, s_code);
+__device__ __noinline__ void serve_scan_plans(const WideCtx* cx, const ServeBody* body, const double* s_pair, uint8_t* s_code, int8_t* s_plan8) {
+    assume_rows<true, WIDE>(cx->T, serve_ptr<const uint32_t>(body->idx_lo, body->idx_hi), body->n, &body->dem, cx->lp, (int)body->mode, body->gen, nullptr,
+                            serve_ptr<int8_t>(body->reason_lo, body->reason_hi), serve_ptr<int32_t>(body->score_lo, body->score_hi),
+                            serve_ptr<int8_t>(body->plan_lo, body->plan_hi), serve_ptr<uint8_t>(body->nem_lo, body->nem_hi), s_pair, cx, s_code, s_plan8);
+}
+template <bool WIDE>
+__device__ __forceinline__ void serve_scan(const WideCtx* cx, const ServeBody* body, const double* s_pair, uint8_t* s_code, int8_t* s_plan8) {
+    if ((body->plan_lo | body->plan_hi) != 0)  // (CTA-uniform)
+        serve_scan_plans<WIDE>(cx, body, s_pair, s_code, s_plan8);
+    else
+        assume_rows<false, WIDE>(cx->T, serve_ptr<const uint32_t>(body->idx_lo, body->idx_hi), body->n, &body->dem, cx->lp, (int)body->mode, body->gen,
+                                 nullptr, serve_ptr<int8_t>(body->reason_lo, body->reason_hi), serve_ptr<int32_t>(body->score_lo, body->score_hi), nullptr,
+                                 nullptr, s_pair, cx, s_code);
 }
 template <bool WIDE>
 __device__ __forceinline__ void serve_bind(const WideCtx* cx, const ServeBody* body, BindResult* res) {
@@ -84,6 +97,7 @@ __global__ void __launch_bounds__(256, VERBS ? 2 : 3) k_serve(Tables T, OneRec* 
     __shared__ uint32_t s_seq, s_prev_row;
     __shared__ __align__(16) uint8_t s_code[256];
     __shared__ BindResult s_bind;
+    __shared__ __align__(16) int8_t s_plan8[VERBS ? 256 * NGS_MAX_CONTAINERS : 16];
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     fill_usage_pair_table(s_pair, tid, blockDim.x);  // (constant: once per launch)
     uint32_t last = last_seq;
@@ -173,7 +187,7 @@ __global__ void __launch_bounds__(256, VERBS ? 2 : 3) k_serve(Tables T, OneRec* 
             }
             __syncthreads();
             if (body.op == SERVE_OP_SCAN) {
-                serve_scan<WIDE>(&s_wcx, &body, s_pair, s_code);
+                serve_scan<WIDE>(&s_wcx, &body, s_pair, s_code, s_plan8);
                 __syncthreads();
                 if (tid == 0) {
                     __threadfence_system();  // the CTA's outputs (cumulative over the barrier), before the ticket

@@ -151,10 +151,18 @@ def test_verbs_through_the_resident_kernel_match_the_oracle(ngs, policy, load_on
         # a fresh score pass on its own (no filter call before it): also a request
         dem = np.array([15, 10], dtype=np.int32)
         assert np.array_equal(d.score(dem, policy, load=lg), oc.assume(dem, policy, load=lo)["score"])
-        # plans are not served by the resident kernel: the call stops it and answers the launched way
-        a = d.assume(dem, policy, load=lg, want_plan=True)
-        b = oc.assume(dem, policy, load=lo, want_plan=True)
-        assert np.array_equal(a["plan"], b["plan"]) and np.array_equal(a["n_emitted"], b["n_emitted"])
+        # plans travel through the resident kernel as well (packed, as from the launched scan): all of them, or the infeasible nodes' only
+        launches1 = d.stats()["kernel_launches"]
+        for dem in ([15, 10], [60, 55, 50], [100, 100, 95, 90]):
+            a = d.assume(dem, policy, load=lg, want_plan=True)
+            b = oc.assume(dem, policy, load=lo, want_plan=True)
+            assert np.array_equal(a["plan"], b["plan"]) and np.array_equal(a["n_emitted"], b["n_emitted"])
+            a = d.assume(dem, policy, load=lg, want_plan=True, failed_plans_only=True, idx=idx)
+            b = oc.assume(dem, policy, load=lo, want_plan=True, idx=idx)
+            bad = b["reason"] == ngs.REASON_INFEASIBLE
+            assert np.array_equal(a["feasible"], b["feasible"]) and np.array_equal(a["score"], b["score"])
+            assert np.array_equal(a["plan"][bad], b["plan"][bad]) and np.array_equal(a["n_emitted"][bad], b["n_emitted"][bad])
+        assert d.stats()["kernel_launches"] - launches1 <= 2  # (the plan staging may have to grow once: that stops the kernel)
         d.serve_stop()
         gc, fr, rl = d.snapshot_read()
         ogc, ofr, orl = oc.snapshot()
