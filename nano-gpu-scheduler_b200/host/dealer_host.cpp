@@ -428,6 +428,12 @@ bool Dealer::load_ctx(const PolicySpec& spec, bool isLoad, ngs_load_ctx* out) co
     return true;
 }
 
+Error Dealer::UseResidentKernel(bool on) {
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    if (!h_) return init_error_;
+    return ngs_serve_verbs(h_, on ? 1 : 0) == NGS_OK ? "" : Error(ngs_last_error(h_));
+}
+
 Error Dealer::getNodeInfo(const std::string& name, uint32_t* row) {  // dealer.go:271-301
     if (const uint32_t* known = index_.Find(name)) {
         *row = *known;

@@ -227,11 +227,12 @@ static void TestBindCommitFailureLeavesPodUnknown() {
     CHECK(r.second[0].find("periods") != std::string::npos);
 }
 
-static void TestScheduleCycleAndRelease() {
+static void ScheduleCycleAndRelease(bool resident) {
     FakeCluster fc;
     for (int i = 0; i < 6; i++) fc.add("node-" + std::to_string(i), 8);
     fc.add("small", 2);
     Dealer d(&fc, RaterKind::Binpack, 64);
+    if (resident) CHECK(d.UseResidentKernel(true).empty());  // the same cycle, the verbs served by the resident kernel
     std::vector<std::string> names = {"node-0", "node-1", "node-2", "node-3", "node-4", "node-5", "small"};
     std::vector<Pod> bound;
     for (int k = 0; k < 40; k++) {
@@ -497,7 +498,8 @@ int main() {
     TestNewDemandAndPlanFromPod();
     TestAssumeErrorTexts();
     TestBindCommitFailureLeavesPodUnknown();
-    TestScheduleCycleAndRelease();
+    ScheduleCycleAndRelease(false);
+    ScheduleCycleAndRelease(true);
     TestAllocateFromAnnotationsAndRebuild();
     TestTwelveGpuNode();
     TestLoadAwareScoring();
