@@ -659,7 +659,7 @@ def run_b200(args):
                 sd.schedule_batch(pc[lo + s:lo + s + 1], nc[lo + s:lo + s + 1], policy[lo + s:lo + s + 1], load=load, seed=1, seq0=s)
                 lat.append(time.perf_counter() - t0)
         # the same call through the resident kernel (K8, ngs_serve_pod): no launch per pod
-        if sd is None and int(policy[0]) != ngs.POLICY_RANDOM:
+        if sd is None and int(policy[0]) != ngs.POLICY_RANDOM and not args.skip_e2e:  # (not under a profiler: a kernel that waits for the host cannot be replayed)
             import ctypes as C
 
             lib = ngs._abi.load()
