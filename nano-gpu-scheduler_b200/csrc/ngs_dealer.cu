@@ -407,6 +407,9 @@ int launch_schedule(ngs_dealer* h, uint32_t P, const int32_t* d_percent, const i
     uint32_t grid = (N + 63) / 64;
     if (grid < 1) grid = 1;
     if (grid > (uint32_t)h->num_sms) grid = (uint32_t)h->num_sms;
+#ifdef NGS_K6_GRID_ENV
+    if (const char* e = getenv("NGS_K6_GRID")) grid = (uint32_t)atoi(e);  // (experiments only)
+#endif
     const uint32_t rpb = (N + grid - 1) / grid;
     const uint32_t block = schedule_block(rpb);
     const size_t smem = schedule_smem_bytes(rpb);
