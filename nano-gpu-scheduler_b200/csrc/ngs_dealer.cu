@@ -7,15 +7,19 @@
 //   tenths  uint8 [2][N][8] ceil(10*usage) per (metric, node, card); 255 = skip  nodeusage.go:82-111
 //   ts      uint32[2][N][8] update time, unix seconds                            stats.go:30-55
 //   tag     uint32[N], cscore int32[N]   per-node plan cache (NodeInfo.PlanCache, node.go:22)
+//   free_hi / rl_hi / tenths_hi / ts_hi   [..][N][4]: cells 8..11 of nodes with 9..12 GPUs, allocated with the first such node
 //
 // Kernels (one translation unit; the device code lives in headers included below):
 //   ngs_device.cuh    building blocks on one row held in registers (sort emulation, rates, usage, keys)
-//   ngs_rows.cuh      the tables as the kernels see them, evaluation of one row (GPUs.Choose)
+//   ngs_tables.cuh    the tables as the kernels see them;  ngs_wide.cuh  one-thread evaluation of rows with 9..12 GPUs
+//   ngs_rows.cuh      evaluation of one row (GPUs.Choose)
 //   ngs_k1_scan.cuh   K1  k_assume (one thread per candidate: feasibility / score / plan out) and
 //                         k_scan_tma (all rows, tiles staged by TMA bulk copies)
 //   ngs_k3_rows.cuh   K3  k_bind, k_apply, k_release_batch;  K4  k_load_update, k_load_add_node, k_upsert
 //   ngs_k6_batch.cuh  K6  k_schedule: persistent cooperative kernel, rows resident in shared memory, per pod
 //                         filter + score every row, grid-wide arg-max (K2), bind on the owner; K5 inside it
+//   ngs_k7_one.cuh    K7  k_schedule_one[_random]: one pod's whole cycle in one ordinary launch
+//   ngs_k8_serve.cuh  K8  k_serve: the resident form - launched once, serves pods (and the verbs) from requests in mapped host memory
 // This file: the handle, launch code and the C ABI.
 // All paths relative to /root/reference/pkg/dealer/.
 #include <cooperative_groups.h>
