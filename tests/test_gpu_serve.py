@@ -189,3 +189,24 @@ def test_verbs_through_the_resident_kernel_on_wide_nodes(ngs):
             assert ra[0] == rb[0] == 0 and ra[1].tolist() == rb[1].tolist() and ra[2] == rb[2]
         d.serve_stop()
         assert_same_nodes(oc, d, n)
+
+
+def test_requests_that_race_the_idle_exit(ngs):
+    """an idle limit about as long as the gap between requests: the kernel keeps leaving just before, while or after a request
+    arrives; every pod is still answered exactly once and exactly right"""
+    n = 4000
+    oc, d, _, _ = make_pair(ngs, n, 0.4, 1313)
+    rng = np.random.default_rng(31)
+    with d:
+        d.serve_idle_ms(0.06)
+        launches0 = d.stats()["kernel_launches"]
+        for seq, dem in enumerate(demands(rng, 400)):
+            if seq % 3:
+                t_end = time.perf_counter() + float(rng.integers(0, 120)) * 1e-6
+                while time.perf_counter() < t_end:
+                    pass
+            node, score, gidx = d.serve_pod(dem, seq % 2, seed=9, seq0=seq)
+            assert (node, score, gidx.tolist()) == one(oc, dem, seq % 2, None, seq), (seq, dem)
+        assert d.stats()["kernel_launches"] - launches0 > 20  # (it did leave and come back many times)
+        d.serve_stop()
+        assert np.array_equal(d.snapshot_read()[1], oc.snapshot()[1])
