@@ -138,6 +138,7 @@ struct ngs_dealer {
     bool serve_kind_verbs = false;    // which instantiation is running
     double serve_idle_ms = 20.0;      // the kernel leaves after this long without a request
     bool serve_verbs = false;         // ngs_assume / ngs_score / ngs_bind go through the resident kernel, too (ngs_serve_verbs)
+    uint32_t serve_prev_row = 0xFFFFFFFFu;  // the row the last served pod was bound to (told to the kernel with the next pod)
     cudaStream_t copy_stream = nullptr;  // uploads while the resident kernel holds the handle's stream
     // nodes with 9..12 GPUs (ngs_wide.cuh): which rows, so that the batch kernel can refuse them before it binds anything
     std::vector<uint8_t> wide_row;
@@ -513,9 +514,9 @@ int serve_stop(ngs_dealer* h) {
         b.quit = 1;
         const uint32_t* w = reinterpret_cast<const uint32_t*>(&b);
         const uint32_t seq = h->serve_seq = serve_next_seq(h->serve_seq);
-        for (int i = 0; i < SERVE_BODY_WORDS; i++) rq[(i / 15) * 16 + i % 15] = i < SERVE_BODY_USED ? w[i] : 0u;
+        for (int i = 0; i < SERVE_BODY_WORDS; i++) rq[serve_block_word(i)] = i < SERVE_BODY_USED ? w[i] : 0u;
         std::atomic_thread_fence(std::memory_order_seq_cst);
-        for (int c = 0; c < SERVE_CHUNKS; c++) rq[c * 16 + 15] = seq;
+        for (int q = 0; q < SERVE_REQ_WORDS / 4; q++) rq[4 * q + 3] = seq;
         std::atomic_thread_fence(std::memory_order_seq_cst);
     }
     h->serve_running = false;
@@ -553,8 +554,7 @@ int serve_start(ngs_dealer* h, uint32_t last_seq) {
     // the published word starts at the last sequence number: the kernel waits for the next one
     ServeDev init;
     memset(&init, 0, sizeof(init));
-    init.seq = last_seq;
-    init.prev_row = 0xFFFFFFFFu;
+    for (int q = 0; q < SERVE_REQ_WORDS / 4; q++) init.blk[4 * q + 3] = last_seq;
     CU(h, cudaMemcpyAsync(h->d_serve_dev, &init, sizeof(init), cudaMemcpyHostToDevice, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));  // (pageable source; and nothing else of this handle is in flight from here on)
     h->serve_launch = h->serve_launch + 1 ? h->serve_launch + 1 : 1;
@@ -599,9 +599,9 @@ int serve_request(ngs_dealer* h, ServeBody& b) {
     b.rl_zero = h->T.rl_zero;
     const uint32_t seq = h->serve_seq = serve_next_seq(h->serve_seq);
     const uint32_t* w = reinterpret_cast<const uint32_t*>(&b);
-    for (int i = 0; i < SERVE_BODY_USED; i++) rq[(i / 15) * 16 + i % 15] = w[i];
+    for (int i = 0; i < SERVE_BODY_USED; i++) rq[serve_block_word(i)] = w[i];
     std::atomic_thread_fence(std::memory_order_seq_cst);  // payload before the sequence words
-    for (int c = 0; c < SERVE_CHUNKS; c++) rq[c * 16 + 15] = seq;
+    for (int q = 0; q < SERVE_REQ_WORDS / 4; q++) rq[4 * q + 3] = seq;
     std::atomic_thread_fence(std::memory_order_seq_cst);
     volatile int32_t* out = h->h_serve_out;
     int restarts = 0;
@@ -1520,12 +1520,15 @@ int ngs_serve_pod(ngs_dealer* h, const int32_t* percent, int n_containers, int m
     if (b.lp.enabled) h->T.rl_zero = 0;  // the load-aware Rate writes RemainLoad
     b.max_c = (uint32_t)max_c;
     b.op = SERVE_OP_POD;
+    b.prev_row = h->serve_prev_row;
+    h->serve_prev_row = 0xFFFFFFFFu;
     h->epoch++;  // the call binds the pod
     rc = serve_request(h, b);
     if (rc) return rc;
     volatile int32_t* out = h->h_serve_out;
     rc = out[1];
     *node_out = out[8];
+    if (rc == NGS_OK && out[8] >= 0) h->serve_prev_row = (uint32_t)out[8] - h->T.first;
     *score_out = out[9];
     for (int k = 0; k < max_c; k++) gpu_idx_out[k] = out[10 + k];
     h->stats.node_evals += h->T.n;

@@ -4,15 +4,16 @@
 // A launch whose completion the host can see costs 8-9 us on this box even for an empty kernel
 // (profiles/r02/param_size_bench.txt); K7's own work is about 7 us (profiles/r02/k7_phases.txt).  K8 is launched once
 // (cooperatively: every CTA must be resident, they wait for each other's requests) and then serves requests the host
-// drops into a 512-byte block of mapped pinned memory:
-//   host   : payload words (the demand already sorted), store fence, then the request's sequence number into the last
-//            word of each 64-byte chunk
-//   CTA 0  : warp 0 polls the block with one coalesced 512-byte read; a request is complete when the eight sequence words
-//            agree (a 64-byte chunk is read at one point in time, and the host wrote its payload before its sequence
-//            word), copies it into device memory and publishes the sequence number there (release)
-//   all    : one thread per CTA spins on that word (acquire), the CTA reads the request and runs K7's body: scan of its
-//            rows, atomicMax of the best key, ticket; the CTA that draws the last ticket binds the winner and writes
-//            (node, score, plan) and then the sequence number into mapped host memory, where the host polls it
+// drops into a 512-byte block of mapped pinned memory.  The block is 32 quads of {3 payload words, sequence number}:
+//   host   : all payload words (the demand already sorted), store fence, then the request's sequence number into every quad
+//   CTA 0  : warp 0 polls the block with one coalesced 512-byte read, a quad per lane; the request is complete when the 32
+//            sequence words agree (a 64-byte line is read at one point in time, and the host wrote its payload before its
+//            sequence words); each lane then stores its quad - one 16-byte store - into a copy of the block in device memory
+//   all    : warp 0 of every other CTA polls that copy the same way (a 16-byte quad is stored and loaded as one access, so a
+//            lane sees a quad entirely old or entirely new: the request arrives with the read that finds it, no second trip
+//            for its body); the CTA then runs K7's body: scan of its rows, atomicMax of the best key, ticket; the CTA that
+//            draws the last ticket binds the winner and writes (node, score, plan) and then the sequence number into mapped
+//            host memory, where the host polls it
 // The kernel leaves when asked to (a request with quit set) or when no request arrived for idle_cycles; the host restarts
 // it on the next request.  Every wait is bounded.  Arg-max policies on unsharded handles; everything else goes through K7.
 // The VERBS instantiation also takes ngs_assume / ngs_score (SERVE_OP_SCAN: k_assume's body, every CTA, ticket at the end)
@@ -20,9 +21,8 @@
 // Same results as the launched kernels and the oracle (tests/test_gpu_serve.py).  Included by ngs_dealer.cu after ngs_k7_one.cuh.
 #pragma once
 
-constexpr int SERVE_CHUNKS = 8;
-constexpr int SERVE_REQ_WORDS = SERVE_CHUNKS * 16;  // the request block: chunks of 16 words, the 16th of each = sequence number
-constexpr int SERVE_BODY_WORDS = SERVE_CHUNKS * 15;
+constexpr int SERVE_REQ_WORDS = 128;  // the request block: 32 quads {3 payload words, sequence number}
+constexpr int SERVE_BODY_WORDS = 96;
 constexpr uint32_t SERVE_QUIT = 0xFFFFFFFFu;
 
 enum { SERVE_OP_POD = 0, SERVE_OP_SCAN = 1, SERVE_OP_BIND = 2 };
@@ -32,6 +32,7 @@ struct ServeBody {
     uint32_t rl_zero;  // Tables::rl_zero for this request
     uint32_t max_c;
     uint32_t quit;
+    uint32_t prev_row;  // the row the previous pod was bound to (0xFFFFFFFF: none, or not a pod): the one row that changed since
     uint32_t op;       // SERVE_OP_POD: one pod's whole cycle; _SCAN: ngs_assume / ngs_score; _BIND: ngs_bind
     // _SCAN (k_assume's arguments; the outputs are the handle's mapped staging arrays)
     uint32_t mode, gen, n;
@@ -50,12 +51,12 @@ __device__ __forceinline__ P* serve_ptr(uint32_t lo, uint32_t hi) {
 static_assert(sizeof(ServeBody) <= SERVE_BODY_WORDS * 4 && sizeof(ServeBody) % 4 == 0, "the request body has to fit the block");
 constexpr int SERVE_BODY_USED = (int)(sizeof(ServeBody) / 4);
 
-struct ServeDev {  // device memory: the request as CTA 0 publishes it to the other CTAs
-    uint32_t seq;
-    uint32_t prev_row;  // the row the previous request was bound to (0xFFFFFFFF: none): the one row that changed since
-    uint32_t pad[2];
-    uint32_t body[SERVE_BODY_WORDS];
+struct __align__(16) ServeDev {  // device memory: the request block as CTA 0 forwards it to the other CTAs
+    uint32_t blk[SERVE_REQ_WORDS];
+    unsigned long long t_seen;  // (profiling builds)
 };
+// body word i sits at block word 4 * (i / 3) + i % 3
+__host__ __device__ inline int serve_block_word(int i) { return 4 * (i / 3) + i % 3; }
 
 // The verbs' bodies.  cx: the request's tables and load parameters in shared memory.
 // (the scan with plans is the rarer request and the hungrier code: out of line, so that it does not set the register
@@ -94,7 +95,7 @@ __global__ void __launch_bounds__(256, VERBS ? 2 : 3) k_serve(Tables T, OneRec* 
     __shared__ int s_last;
     __shared__ int32_t s_plan[NGS_MAX_CONTAINERS];
     __shared__ WideCtx s_wcx;
-    __shared__ uint32_t s_seq, s_prev_row;
+    __shared__ uint32_t s_seq;
     __shared__ __align__(16) uint8_t s_code[256];
     __shared__ BindResult s_bind;
     __shared__ __align__(16) int8_t s_plan8[VERBS ? 256 * NGS_MAX_CONTAINERS : 16];
@@ -115,65 +116,44 @@ __global__ void __launch_bounds__(256, VERBS ? 2 : 3) k_serve(Tables T, OneRec* 
 #define K8_STAMP(i) do { } while (0)
 #endif
     for (;;) {
-        // ---- the next request ----
-        if (blockIdx.x == 0 && warp == 0) {
+        // ---- the next request: warp 0 of every CTA polls, CTA 0 the host's block, the others CTA 0's copy of it ----
+        if (warp == 0) {
             const long long t0 = clock64();
-            uint32_t w0 = 0, w1 = 0, w2 = 0, w3 = 0, seq = last;
-            bool idle = false;
+            uint32_t w0 = 0, w1 = 0, w2 = 0, w3 = last;
+            const bool first = blockIdx.x == 0;
             for (uint32_t spins = 0;; spins++) {
-                // words 4*lane .. 4*lane+3 of the block: the sequence words (position 15 of each 16-word chunk) are w3 of lanes 3, 7, .. 31
-                asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3) : "l"(req + 4 * lane) : "memory");
-                const uint32_t s0 = __shfl_sync(FULL, w3, 3);
-                const bool same = __all_sync(FULL, (lane & 3u) != 3u || w3 == s0);
-                if (same && s0 != last) {
-                    seq = s0;
-                    break;
-                }
+                if (first)
+                    asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3) : "l"(req + 4 * lane) : "memory");
+                else
+                    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3) : "l"(dev->blk + 4 * lane) : "memory");
+                const uint32_t s0 = __shfl_sync(FULL, w3, 0);
+                if (__all_sync(FULL, w3 == s0) && s0 != last) break;
                 if ((spins & 15u) == 15u) {  // (lane 0's clock decides for the warp)
-                    idle = __shfl_sync(FULL, clock64() - t0 > idle_cycles ? 1 : 0, 0) != 0;
-                    if (idle) break;
+                    const bool over = __shfl_sync(FULL, clock64() - t0 > (first ? idle_cycles : wait_limit) ? 1 : 0, 0) != 0;
+                    if (over) {  // CTA 0: nothing came for idle_cycles, everybody leaves; the others: CTA 0 is gone (never expected)
+                        w3 = SERVE_QUIT;
+                        break;
+                    }
                 }
             }
+            if (first) {
 #ifdef NGS_K8_TIMING
-            if (lane == 0) {
-                unsigned long long t;
-                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-                reinterpret_cast<unsigned long long*>(dev->pad)[0] = t;  // when CTA 0 saw the request
-            }
+                if (lane == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dev->t_seen));
 #endif
-            if (!idle) {
-                // block word w = chunk w/16, position w%16 -> body word 15 * (w/16) + w%16
-                const uint32_t b = (lane >> 2) * 15u + (lane & 3u) * 4u;
-                dev->body[b] = w0;
-                dev->body[b + 1] = w1;
-                dev->body[b + 2] = w2;
-                if ((lane & 3u) != 3u) dev->body[b + 3] = w3;
-                __threadfence();
+                *reinterpret_cast<uint4*>(dev->blk + 4 * lane) = make_uint4(w0, w1, w2, w3);  // one 16-byte store per quad
             }
-            __syncwarp();
-            if (lane == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&dev->seq), "r"(idle ? SERVE_QUIT : seq) : "memory");
-        }
-        if (tid == 0) {
-            const long long t0 = clock64();
-            uint32_t v;
-            for (uint32_t spins = 0;; spins++) {
-                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&dev->seq) : "memory");
-                if (v != last) break;
-                if ((spins & 255u) == 255u && clock64() - t0 > wait_limit) {  // CTA 0 is gone: never expected
-                    v = SERVE_QUIT;
-                    break;
-                }
-            }
-            s_seq = v;
+            uint32_t* bw = reinterpret_cast<uint32_t*>(&body);
+            if (3 * lane + 0 < (uint32_t)SERVE_BODY_USED) bw[3 * lane + 0] = w0;
+            if (3 * lane + 1 < (uint32_t)SERVE_BODY_USED) bw[3 * lane + 1] = w1;
+            if (3 * lane + 2 < (uint32_t)SERVE_BODY_USED) bw[3 * lane + 2] = w2;
+            if (lane == 0) s_seq = w3;
         }
         __syncthreads();
-        K8_STAMP(0);  // this CTA has seen the published request
+        K8_STAMP(0);  // this CTA holds the request
         const uint32_t cur = s_seq;
         if (cur == SERVE_QUIT) break;
         last = cur;
-        if (tid < SERVE_BODY_USED) reinterpret_cast<uint32_t*>(&body)[tid] = __ldcg(dev->body + tid);
-        if (tid == 64) s_prev_row = __ldcg(&dev->prev_row);
-        __syncthreads();
+        K8_STAMP(1);
         if (body.quit) break;
         Tables Tq = T;
         Tq.rl_zero = body.rl_zero;
@@ -222,13 +202,12 @@ __global__ void __launch_bounds__(256, VERBS ? 2 : 3) k_serve(Tables T, OneRec* 
         const bool load_path = lp.enabled != 0;
         uint32_t row = row_first;
         const int mode = (load_path ? 2 : 0) | (int)(Tq.rl_zero & 1u);
-        if (row < Tq.n && (pref_mode != mode || row == s_prev_row)) load_row(Tq, row, load_path, in);
+        if (row < Tq.n && (pref_mode != mode || row == body.prev_row)) load_row(Tq, row, load_path, in);
         if (WIDE && tid == 64) {
             s_wcx.T = Tq;
             s_wcx.lp = lp;
         }
         __syncthreads();
-        K8_STAMP(1);  // body read, demand sorted
         uint64_t best = 0;
         for (; row < Tq.n; row += gridDim.x * blockDim.x) {
             const RowEval ev = eval_row_values<false, false>(Tq, row, in, &dem, lp, true, s_pair, nullptr);
@@ -279,7 +258,6 @@ __global__ void __launch_bounds__(256, VERBS ? 2 : 3) k_serve(Tables T, OneRec* 
                 if (lane == 0) {
                     out[8] = -1;
                     out[9] = NGS_SCORE_MIN;
-                    dev->prev_row = 0xFFFFFFFFu;
                 }
             } else {
                 const uint32_t wrow = key_node(key) - Tq.first;
@@ -310,7 +288,6 @@ __global__ void __launch_bounds__(256, VERBS ? 2 : 3) k_serve(Tables T, OneRec* 
                     Tq.tag[wrow] = 0;  // node.go:82
                     out[8] = (int32_t)(Tq.first + wrow);
                     out[9] = key_score(key);
-                    dev->prev_row = wrow;
                 }
             }
             __syncwarp();
@@ -319,7 +296,7 @@ __global__ void __launch_bounds__(256, VERBS ? 2 : 3) k_serve(Tables T, OneRec* 
             if (lane == 0) {
 #ifdef NGS_K8_TIMING
                 K8_STAMP(4);
-                const unsigned long long t_seen = reinterpret_cast<const volatile unsigned long long*>(dev->pad)[0];
+                const unsigned long long t_seen = *reinterpret_cast<const volatile unsigned long long*>(&dev->t_seen);
                 for (int i = 0; i < 5; i++) out[32 + i] = (int32_t)(tg[i] - t_seen);  // ns since CTA 0 saw the request
 #endif
                 out[1] = NGS_OK;
