@@ -233,10 +233,11 @@ int ngs_serve_pod(ngs_dealer *h, const int32_t *percent, int n_containers, int m
                   uint64_t seed, uint64_t seq0, int32_t *node_out, int32_t *score_out, int32_t *gpu_idx_out);
 int ngs_serve_stop(ngs_dealer *h);               /* also switches ngs_serve_verbs off */
 int ngs_serve_idle_ms(ngs_dealer *h, double ms); /* 0 < ms <= 2000; stops the kernel if it runs */
-/* on != 0: from now on ngs_assume / ngs_score / ngs_score_view (without per-node plans) and ngs_bind of this handle are
- * served by the resident kernel as requests, too - same results, no launch per call - and do not stop it; it is started
- * by the first such call and again after every call that had to stop it (snapshot updates, load updates, batches, calls
- * that want plans).  Unsharded handles.  The occupancy note above applies for as long as this is on. */
+/* on != 0: from now on ngs_assume[_failed_plans] / ngs_score / ngs_score_view, ngs_bind, ngs_node_apply, ngs_load_update and
+ * ngs_load_add_node of this handle are served by the resident kernel as requests, too - same results, no launch per call -
+ * and do not stop it; it is started by the first verb and again after every call that had to stop it (bulk snapshot and
+ * load-table updates, node upserts, batches, ngs_sync, growing scratch).  Unsharded handles.  The occupancy note above
+ * applies for as long as this is on. */
 int ngs_serve_verbs(ngs_dealer *h, int on);
 
 /* ---- node-range sharding over the GPUs of one box (no reference counterpart: the reference is a

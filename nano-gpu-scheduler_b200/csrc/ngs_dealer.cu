@@ -975,12 +975,31 @@ int ngs_snapshot_read(ngs_dealer* h, uint32_t first, uint32_t n, uint8_t* gpu_co
 
 int ngs_node_apply(ngs_dealer* h, uint32_t idx, const int32_t* gpu_idx, const int32_t* percent, int n_containers, int sign) {
     if (!h || sign == 0) return NGS_ERR_INVALID;
-    SERVE_OFF(h);
+    const bool resident = h->serve_verbs && h->world == 1;  // K8: a request to the resident kernel, which keeps running
+    if (!resident) SERVE_OFF(h);
     PodDemand pd;
     int rc = make_demand(h, percent, n_containers, NGS_POLICY_BINPACK, &pd);
     if (rc) return rc;
     if (n_containers > 0 && !gpu_idx) return fail(h, NGS_ERR_INVALID, "apply: gpu_idx is NULL");
     CU(h, cudaSetDevice(h->device));
+    if (resident) {
+        ServeBody b;
+        memset(&b, 0, sizeof(b));
+        b.dem.C = n_containers;
+        for (int i = 0; i < n_containers; i++) {
+            b.dem.raw[i] = percent[i];
+            b.dem.d[i] = gpu_idx[i];
+        }
+        b.op = SERVE_OP_APPLY;
+        b.node = idx;
+        b.mode = (uint32_t)(int32_t)(sign > 0 ? 1 : -1);
+        h->epoch++;
+        rc = serve_request(h, b);
+        if (rc) return rc;
+        rc = h->h_serve_out[1];
+        if (rc) return fail(h, rc, "apply on node %u: %s", idx, ngs_strerror(rc));
+        return NGS_OK;
+    }
     for (int i = 0; i < n_containers; i++) h->h_small[i] = gpu_idx[i];
     CU(h, cudaMemcpyAsync(h->d_small, h->h_small, NGS_MAX_CONTAINERS * 4, cudaMemcpyHostToDevice, h->stream));
     h->epoch++;
@@ -1046,9 +1065,18 @@ static uint8_t encode_tenths(double value, int value_ok, int64_t ts_sec, int ts_
 
 int ngs_load_add_node(ngs_dealer* h, uint32_t idx, int metric) {
     if (!h || metric < 0 || metric > 1) return NGS_ERR_INVALID;
-    SERVE_OFF(h);
     if (idx < h->T.first || idx - h->T.first >= h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "node %u outside this shard", idx);
     CU(h, cudaSetDevice(h->device));
+    if (h->serve_running && h->serve_verbs && h->serve_kind_verbs) {  // K8: as a request, the resident kernel keeps running
+        ServeBody b;
+        memset(&b, 0, sizeof(b));
+        b.op = SERVE_OP_LOAD;
+        b.node = idx;
+        b.mode = (uint32_t)metric;
+        b.gen = 0xFFFFFFFFu;
+        return serve_request(h, b);
+    }
+    SERVE_OFF(h);
     k_load_add_node<<<1, 32, 0, h->stream>>>(h->T, idx - h->T.first, metric);
     CU(h, cudaGetLastError());
     h->stats.kernel_launches++;
@@ -1057,16 +1085,29 @@ int ngs_load_add_node(ngs_dealer* h, uint32_t idx, int metric) {
 
 int ngs_load_update(ngs_dealer* h, uint32_t idx, int metric, int card, double value, int value_ok, int64_t ts_sec, int ts_ok) {
     if (!h || metric < 0 || metric > 1) return NGS_ERR_INVALID;
-    SERVE_OFF(h);
     if (idx < h->T.first || idx - h->T.first >= h->T.n) return fail(h, NGS_ERR_UNKNOWN_NODE, "node %u outside this shard", idx);
     if (card < 0) return fail(h, NGS_ERR_INVALID, "card %d", card);
     if (card >= NGS_MAX_GPUS_WIDE) return NGS_OK;  // a card the kernels never look at (LoadUsage walks gpus only)
     CU(h, cudaSetDevice(h->device));
+    const uint8_t t10 = encode_tenths(value, value_ok, ts_sec, ts_ok);
+    // K8: as a request while the resident kernel (verbs instantiation) runs - it keeps running; a card beyond 7 before the
+    // second table plane exists takes the launched path, which allocates it
+    if (h->serve_running && h->serve_verbs && h->serve_kind_verbs && (card < NGS_MAX_GPUS || h->T.free_hi)) {
+        ServeBody b;
+        memset(&b, 0, sizeof(b));
+        b.op = SERVE_OP_LOAD;
+        b.node = idx;
+        b.mode = (uint32_t)metric;
+        b.gen = (uint32_t)card;
+        b.n = t10;
+        b.idx_lo = t10 == 255 ? 0u : (uint32_t)ts_sec;
+        return serve_request(h, b);
+    }
+    SERVE_OFF(h);
     if (card >= NGS_MAX_GPUS) {  // (an entry may arrive before its node does: nodeusage.go keeps them apart, too)
         const int rc = ensure_wide(h);
         if (rc) return rc;
     }
-    const uint8_t t10 = encode_tenths(value, value_ok, ts_sec, ts_ok);
     k_load_update<<<1, 32, 0, h->stream>>>(h->T, idx - h->T.first, metric, card, t10, t10 == 255 ? 0u : (uint32_t)ts_sec);
     CU(h, cudaGetLastError());
     h->stats.kernel_launches++;

@@ -55,49 +55,49 @@ __global__ void k_bind(Tables T, uint32_t gidx, PodDemand pd, LoadParams lp, uin
     *reinterpret_cast<volatile int32_t*>(&res_out->status) = s_res.status;
 }
 
-// K3.  GPUs.Allocate (sign>0, all-or-nothing) / GPUs.Release (sign<0) with a caller-given plan.
-__global__ void k_apply(Tables T, uint32_t gidx, PodDemand pd, const int32_t* __restrict__ gpu_idx_in, int sign, int32_t* status) {
-    if (threadIdx.x != 0) return;
+// K3.  GPUs.Allocate (sign>0, all-or-nothing) / GPUs.Release (sign<0) with a caller-given plan, by one thread.
+__device__ __forceinline__ int apply_row(const Tables& T, uint32_t gidx, int n, const int32_t* percent, const int32_t* gpu_idx_in, int sign) {
     const uint32_t row = gidx - T.first;
-    if (gidx < T.first || row >= T.n || T.gcount[row] == 0) {
-        *status = NGS_ERR_UNKNOWN_NODE;
-        return;
-    }
+    if (gidx < T.first || row >= T.n || T.gcount[row] == 0) return NGS_ERR_UNKNOWN_NODE;
     const int G = min((int)T.gcount[row], WIDE_MAX);
     int f[WIDE_MAX];
     for (int g = 0; g < G; g++) f[g] = *wide_free_cell(T, row, g);
     T.tag[row] = 0;  // node.go:87,92: cleanPlan runs before the apply, whatever its outcome
     int rc = NGS_OK;
     if (sign > 0) {
-        for (int k = 0; k < pd.n; k++) {
+        for (int k = 0; k < n; k++) {
             const int gi = gpu_idx_in[k];
             if (gi < 0) continue;  // allocate.go:105-107
-            if (gi >= G || f[gi] < pd.percent[k]) {  // allocate.go:108 (an index >= G panics in Go)
+            if (gi >= G || f[gi] < percent[k]) {  // allocate.go:108 (an index >= G panics in Go)
                 rc = NGS_ERR_APPLY;
                 break;
             }
-            f[gi] -= pd.percent[k];
+            f[gi] -= percent[k];
         }
         if (rc == NGS_OK)
             for (int g = 0; g < G; g++) *wide_free_cell(T, row, g) = f[g];
     } else {
-        for (int k = 0; k < pd.n; k++) {
+        for (int k = 0; k < n; k++) {
             const int gi = gpu_idx_in[k];
             if (gi < 0) continue;
             if (gi >= G) {  // allocate.go:125-127: earlier containers stay released
                 rc = NGS_ERR_APPLY;
                 break;
             }
-            if (f[gi] + pd.percent[k] > NGS_MAX_FREE) {
+            if (f[gi] + percent[k] > NGS_MAX_FREE) {
                 rc = NGS_ERR_RANGE;
                 break;
             }
-            f[gi] += pd.percent[k];
+            f[gi] += percent[k];
         }
         if (rc != NGS_ERR_RANGE)
             for (int g = 0; g < G; g++) *wide_free_cell(T, row, g) = f[g];
     }
-    *status = rc;
+    return rc;
+}
+__global__ void k_apply(Tables T, uint32_t gidx, PodDemand pd, const int32_t* __restrict__ gpu_idx_in, int sign, int32_t* status) {
+    if (threadIdx.x != 0) return;
+    *status = apply_row(T, gidx, pd.n, pd.percent, gpu_idx_in, sign);
 }
 
 // K3, batched: GPUs.Release (allocate.go:120-131) for many finished pods at once (the informer's

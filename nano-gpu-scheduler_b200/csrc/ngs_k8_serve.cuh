@@ -25,7 +25,7 @@ constexpr int SERVE_REQ_WORDS = 128;  // the request block: 32 quads {3 payload 
 constexpr int SERVE_BODY_WORDS = 96;
 constexpr uint32_t SERVE_QUIT = 0xFFFFFFFFu;
 
-enum { SERVE_OP_POD = 0, SERVE_OP_SCAN = 1, SERVE_OP_BIND = 2 };
+enum { SERVE_OP_POD = 0, SERVE_OP_SCAN = 1, SERVE_OP_BIND = 2, SERVE_OP_APPLY = 3, SERVE_OP_LOAD = 4 };
 struct ServeBody {
     SortedDemand dem;  // sorted by the host (sort_demand): every CTA would otherwise spend 0.5 us on it per request
     LoadParams lp;
@@ -43,6 +43,9 @@ struct ServeBody {
     uint32_t nem_lo, nem_hi;
     // _BIND
     uint32_t node;
+    // _APPLY (ngs_node_apply): node; dem.C containers with dem.raw[] = percent and dem.d[] = the GPU indexes; mode = sign (as int32)
+    // _LOAD (ngs_load_update / ngs_load_add_node): node; mode = metric, gen = card (0xFFFFFFFF: fresh empty maps for the node),
+    //       n = tenths code, idx_lo = update time in seconds
 };
 template <class P>
 __device__ __forceinline__ P* serve_ptr(uint32_t lo, uint32_t hi) {
@@ -178,11 +181,33 @@ __global__ void __launch_bounds__(256, VERBS ? 2 : 3) k_serve(Tables T, OneRec* 
                         *reinterpret_cast<volatile int32_t*>(out) = (int32_t)cur;
                     }
                 }
-            } else if (blockIdx.x == 0 && tid == 0) {  // _BIND: one thread
-                serve_bind<WIDE>(&s_wcx, &body, &s_bind);
-                for (int j = 0; j < NGS_MAX_CONTAINERS; j++) out[10 + j] = s_bind.gpu_idx[j];
-                out[9] = s_bind.score;
-                out[1] = s_bind.status;
+            } else if (blockIdx.x == 0 && tid == 0) {  // the single-row requests: one thread
+                if (body.op == SERVE_OP_BIND) {
+                    serve_bind<WIDE>(&s_wcx, &body, &s_bind);
+                    for (int j = 0; j < NGS_MAX_CONTAINERS; j++) out[10 + j] = s_bind.gpu_idx[j];
+                    out[9] = s_bind.score;
+                    out[1] = s_bind.status;
+                } else if (body.op == SERVE_OP_APPLY) {  // k_apply's body
+                    out[1] = apply_row(s_wcx.T, body.node, dem.C, dem.raw, dem.d, (int)body.mode);
+                } else {  // SERVE_OP_LOAD: k_load_update's / k_load_add_node's bodies
+                    const Tables& Tt = s_wcx.T;
+                    const uint32_t row = body.node - Tt.first;
+                    const int metric = (int)body.mode;
+                    if (body.gen == 0xFFFFFFFFu) {
+                        for (int c = 0; c < (Tt.tenths_hi ? WIDE_MAX : 8); c++) {
+                            bool hi;
+                            const size_t off = wide_usage_off(Tt, row, metric, c, &hi);
+                            (hi ? Tt.tenths_hi : Tt.tenths)[off] = 255;
+                            (hi ? Tt.ts_hi : Tt.ts)[off] = 0;
+                        }
+                    } else {
+                        bool hi;
+                        const size_t off = wide_usage_off(Tt, row, metric, (int)body.gen, &hi);
+                        (hi ? Tt.tenths_hi : Tt.tenths)[off] = (uint8_t)body.n;
+                        (hi ? Tt.ts_hi : Tt.ts)[off] = body.idx_lo;
+                    }
+                    out[1] = NGS_OK;
+                }
                 __threadfence_system();
                 *reinterpret_cast<volatile int32_t*>(out) = (int32_t)cur;
             }

@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 import oracle as o
-from tests.parity_util import fill_load_tables, load_ctx_pair, make_pair
+from tests.parity_util import NOW_S, fill_load_tables, load_ctx_pair, make_pair
 from tests.test_gpu_wide_nodes import assert_same_nodes, mixed_pair
 
 pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300)]
@@ -145,9 +145,21 @@ def test_verbs_through_the_resident_kernel_match_the_oracle(ngs, policy, load_on
                 assert d.bind(best, [100] * 12, policy, load=lg)[0] == ngs.ERR_INFEASIBLE
                 assert oc.bind(best, [100] * 12, policy, load=lo)[0] != 0
                 assert d.bind(n + 5, dem, policy, load=lg)[0] == ngs.ERR_UNKNOWN_NODE
-            if t == 60:  # a release in between stops the kernel; the next verb starts it again
+            if t % 20 == 5:  # releases and allocations in between are requests, too: the kernel keeps running
                 assert d.node_apply(best, ra[1], dem, -1) == oc.node_apply(best, rb[1], dem, -1) == 0
-        assert d.stats()["kernel_launches"] - launches0 < 30  # ~360 verb calls, a handful of launches
+                assert (d.node_apply(best, [0], [100], +1) == 0) == (oc.node_apply(best, [0], [100], +1) == 0)
+                assert d.node_apply(n + 9, [0], [5], -1) == ngs.ERR_UNKNOWN_NODE
+            if t % 10 == 7:  # ... and so are usage samples arriving from the metric sync
+                node_u = int(rng.integers(0, n))
+                for m in (0, 1):
+                    if t % 20 == 7:
+                        d.load_add_node(node_u, m)
+                        oc.load_add_node(node_u, m)
+                    for card in range(int(rng.integers(1, 9))):
+                        v, ts = float(rng.integers(0, 101)) / 100.0, NOW_S - int(rng.integers(0, 300))
+                        d.load_update(node_u, m, card, v, ts)
+                        oc.load_update(node_u, m, card, v, ts)
+        assert d.stats()["kernel_launches"] - launches0 < 12  # several hundred calls of six kinds, a handful of launches
         # a fresh score pass on its own (no filter call before it): also a request
         dem = np.array([15, 10], dtype=np.int32)
         assert np.array_equal(d.score(dem, policy, load=lg), oc.assume(dem, policy, load=lo)["score"])
