@@ -17,6 +17,7 @@
 #include <string>
 #include <string_view>
 #include <unordered_map>
+#include <memory>
 #include <utility>
 #include <vector>
 
@@ -100,11 +101,28 @@ struct CandidateSet {
     size_t n_missing = 0;
     bool all_rows = false;                   // names are exactly rows 0..n-1 in order: the C ABI's idx == NULL form
 };
+// an array that is NOT value-initialised: the plans of 100k candidates are 1.2 MB of which only the infeasible nodes' rows are
+// ever written or read (ngs_assume_failed_plans), and zero-filling it cost more than the device call
+template <class T>
+struct RawArray {
+    std::unique_ptr<T[]> p;
+    size_t n = 0;
+    void resize(size_t m) {
+        if (m > n) p.reset(new T[m]);
+        n = m;
+    }
+    T* data() { return p.get(); }
+    const T* data() const { return p.get(); }
+    const T* begin() const { return p.get(); }
+    T& operator[](size_t i) { return p[i]; }
+    const T& operator[](size_t i) const { return p[i]; }
+};
 // what one Assume over a CandidateSet brings back from the device
 struct AssumeResult {
     std::vector<uint8_t> ok;                 // Assume's []bool
     std::vector<int8_t> reason;              // NGS_REASON_*
-    std::vector<int32_t> demand, plan, n_emitted;
+    std::vector<int32_t> demand;
+    RawArray<int32_t> plan, n_emitted;       // valid for the candidates with reason == NGS_REASON_INFEASIBLE only
     std::string demand_text;                 // DemandString(demand), shared by every failure message
     std::vector<int32_t> free;               // rows [free_first, free_first + free.size()/kRowCells) read back once, for the messages
     uint32_t free_first = 0;
