@@ -163,7 +163,7 @@ int ngs_assume(ngs_dealer *h, const uint32_t *idx, uint32_t n, const int32_t *pe
  * plan / n_emitted (both required) are written for the INFEASIBLE candidates only - their partial `indexes` - and the
  * rows of every other candidate are LEFT AS THEY WERE (look at reason[] / feasible[] first).  The others' exact plan search
  * is skipped and their 4 bytes per entry are never written, so the call costs about what one without plans costs, where
- * ngs_assume with plans costs 2.5 times as much at 100k candidates. */
+ * ngs_assume with plans costs about twice as much at 100k candidates. */
 int ngs_assume_failed_plans(ngs_dealer *h, const uint32_t *idx, uint32_t n, const int32_t *percent, int n_containers,
                             int policy, const ngs_load_ctx *load, uint8_t *feasible, int8_t *reason, int32_t *score,
                             int32_t *plan, int32_t *n_emitted);

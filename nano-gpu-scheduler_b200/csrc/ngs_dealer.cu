@@ -1260,14 +1260,26 @@ static int run_assume(ngs_dealer* h, int mode, const uint32_t* idx, uint32_t n, 
     if (failed_plans_only) {
         // only the infeasible candidates' rows are written: filling 4 bytes per entry for all of them is what a call with plans costs
         const int8_t* st = h->h_vreason;
-        for (uint32_t i = 0; i < n; i++) {
-            if (st[i] != NGS_REASON_INFEASIBLE) continue;
+        auto take = [&](uint32_t i) {
             n_emitted[i] = h->h_vnem[i];
             for (int k = 0; k < n_containers; k++) {
                 const int8_t v = h->h_vplan[(size_t)i * n_containers + k];
                 plan[(size_t)i * n_containers + k] = v == PLAN_NONE ? INT32_MIN : (int32_t)v;
             }
+        };
+        uint32_t i = 0;
+#if defined(__SSE2__)
+        const __m128i bad = _mm_set1_epi8((char)NGS_REASON_INFEASIBLE);
+        for (; i + 16 <= n; i += 16) {  // sixteen status bytes per step: mostly nothing to do
+            unsigned m = (unsigned)_mm_movemask_epi8(_mm_cmpeq_epi8(_mm_loadu_si128(reinterpret_cast<const __m128i*>(st + i)), bad));
+            while (m) {
+                take(i + (uint32_t)__builtin_ctz(m));
+                m &= m - 1;
+            }
         }
+#endif
+        for (; i < n; i++)
+            if (st[i] == NGS_REASON_INFEASIBLE) take(i);
     } else {
         if (plan && n_containers > 0) widen_plan(plan, h->h_vplan, (size_t)n * n_containers);  // one byte per entry in the staging area
         if (n_emitted) widen_u8(n_emitted, h->h_vnem, n);
